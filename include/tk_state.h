@@ -1,0 +1,162 @@
+/*
+ * tk_state.h -- C ABI of libtkstate: the state.State path of triton-kubernetes,
+ * B200-native (CUDA, sm_100a).
+ *
+ * The reference has no FFI boundary of its own: state.State is a concrete Go
+ * type called directly from create/, destroy/, get/, shell/ and backend/.  This header is the
+ * boundary a maintainer would bind with cgo to swap that type's body for this library; each
+ * entry point cites the reference method it replaces (paths relative to the reference root).
+ * INTEGRATION.md shows the cgo stub.
+ *
+ * Conventions
+ *   - Every function returns TK_OK (0) or a TK_E* code; the Go error text (err.Error()) of the
+ *     failing call is available verbatim from tk_last_error(handle) -- or tk_last_error(NULL)
+ *     for a failed tk_state_new -- until the next call on that handle / thread.
+ *   - Strings are (pointer, length) pairs and may contain any byte, NUL included.
+ *   - Inputs are borrowed for the duration of the call only.
+ *   - Returned buffers belong to the handle and stay valid until the next call that returns the
+ *     same kind of buffer on that handle, or tk_state_free.
+ *   - A handle is not thread-safe (neither is state.State: plain Go maps); distinct handles are
+ *     independent.  A handle binds to the CUDA device that was current when it was created.
+ *   - Values (the `obj interface{}` arguments of the Go methods) cross the boundary as JSON
+ *     text, i.e. what json.Marshal(obj) gives on the Go side, plus a flag that says whether obj
+ *     was a map (TK_VALUE_MAP: keys sorted on output, visible to Get/Clusters/Nodes) or a
+ *     struct (TK_VALUE_RECORD: member order kept as given, opaque until the document is
+ *     re-parsed -- SURVEY.md 8a note 1, create/cluster.go:146-152).
+ *   - The bulk operations (New, Bytes, Clusters, Nodes) run on the GPU; there is no CPU
+ *     fallback.  Without a usable CUDA device they fail with TK_ECUDA and say so.
+ */
+#ifndef TK_STATE_H
+#define TK_STATE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define TK_API __attribute__((visibility("default")))
+#else
+#define TK_API
+#endif
+
+typedef struct tk_state tk_state;
+
+enum {
+    TK_OK = 0,
+    TK_ESYNTAX = 1,   /* json.Unmarshal failed (state.New, or a value argument) */
+    TK_ECOLLISION = 2,/* gabs.ErrPathCollision */
+    TK_ENOTOBJ = 3,   /* gabs.ErrNotObj */
+    TK_EKEYPARTS = 4, /* getClusterKeyParts: cluster key has fewer than three '_' parts */
+    TK_ECUDA = 5,     /* no device, or a CUDA call failed */
+    TK_ELIMIT = 6,    /* document exceeds a documented size limit */
+    TK_EARG = 7,      /* NULL where a pointer is required */
+    TK_EIO = 8        /* local backend: file system error */
+};
+
+enum { TK_VALUE_MAP = 0, TK_VALUE_RECORD = 1 };
+
+/* Size limits (documented in DESIGN.md): serialised document and string arena < 4 GiB each. */
+#define TK_MAX_DEPTH 10000
+
+/* state.New(name, raw) -- state/state.go:15-25 (gabs.ParseJSON, gabs.go:425-433). */
+TK_API int tk_state_new(const char *name, size_t name_len, const char *raw, size_t raw_len, tk_state **out);
+
+/* state.New(name, []byte("{}")) -- what backend/local/backend.go:54 and backend/manta/backend.go:131
+ * do for a manager that has no file yet.  Pure host work: needs no device, so the path
+ * operations (Get/Set/Add/Delete) can be exercised on a machine without a GPU. */
+TK_API int tk_state_new_empty(const char *name, size_t name_len, tk_state **out);
+
+/* Releases the document, its device buffers and its stream. */
+TK_API void tk_state_free(tk_state *s);
+
+/* State.Name -- state/state.go:11. */
+TK_API int tk_state_name(tk_state *s, const char **name, size_t *name_len);
+
+/* err.Error() of the last failing call; "" if none.  s may be NULL (thread-local slot). */
+TK_API const char *tk_last_error(tk_state *s);
+
+/* State.Get(path) -- state/state.go:27-34: the string at the dotted path, or "" for every
+ * kind of miss (never an error). */
+TK_API int tk_state_get(tk_state *s, const char *path, size_t path_len, const char **value, size_t *value_len);
+
+/* configJSON.SetP(obj, path) -- the body shared by SetManager / SetTerraformBackendConfig /
+ * AddCluster / AddNode (gabs.go:180-208). */
+TK_API int tk_state_set(tk_state *s, const char *path, size_t path_len, const char *json, size_t json_len, int value_kind);
+
+/* State.SetManager(obj) -- state/state.go:36-43 (path "module.cluster-manager"). */
+TK_API int tk_state_set_manager(tk_state *s, const char *json, size_t json_len, int value_kind);
+
+/* State.SetTerraformBackendConfig(path, obj) -- state/state.go:45-52. */
+TK_API int tk_state_set_terraform_backend_config(tk_state *s, const char *path, size_t path_len, const char *json,
+                                                 size_t json_len, int value_kind);
+
+/* State.AddCluster(provider, name, obj) -- state/state.go:55-62. */
+TK_API int tk_state_add_cluster(tk_state *s, const char *provider, size_t provider_len, const char *name,
+                                size_t name_len, const char *json, size_t json_len, int value_kind);
+
+/* State.AddNode(clusterKey, name, obj) -- state/state.go:65-77. */
+TK_API int tk_state_add_node(tk_state *s, const char *cluster_key, size_t cluster_key_len, const char *name,
+                             size_t name_len, const char *json, size_t json_len, int value_kind);
+
+/* State.Delete(path) -- state/state.go:79-86 (gabs.go:276-301). */
+TK_API int tk_state_delete(tk_state *s, const char *path, size_t path_len);
+
+/* State.Bytes() -- state/state.go:88-90: json.MarshalIndent(doc, "", "\t"); "{}" for a nil
+ * root.  Serialised on the GPU; *out is host memory owned by the handle. */
+TK_API int tk_state_bytes(tk_state *s, const char **out, size_t *out_len);
+
+/* State.Clusters() -- state/state.go:94-113 and State.Nodes(clusterKey) -- :117-147.
+ * The Go map[string]string result comes back as *count pairs packed into *blob as
+ *   { uint32 name_len; name bytes; uint32 key_len; key bytes }   (little endian)
+ * sorted by name (Go's map order is random; on duplicate names the bytewise greatest module
+ * key is kept, where Go keeps a random one).  The module keys are classified on the GPU. */
+TK_API int tk_state_clusters(tk_state *s, const uint8_t **blob, size_t *blob_len, size_t *count);
+TK_API int tk_state_nodes(tk_state *s, const char *cluster_key, size_t cluster_key_len, const uint8_t **blob,
+                          size_t *blob_len, size_t *count);
+
+/* getNewHostnames(existingNames, nodeName, nodesToAdd) -- create/node.go:350-380.
+ * existing: n (pointer, length) pairs.  Result: the new names joined by '\n', handle-less and
+ * owned by the calling thread until its next call of this function. */
+TK_API int tk_new_hostnames(const char *const *existing, const size_t *existing_len, size_t n, const char *node_name,
+                            size_t node_name_len, long long nodes_to_add, const char **out, size_t *out_len);
+
+/* ---- device-resident variants: what bench.py times with inputs already in HBM ------------ */
+
+/* Makes the device copy of the document current (flatten + host->device copy if the document
+ * changed since the last staging).  Bytes/Clusters/Nodes call this implicitly. */
+TK_API int tk_state_stage(tk_state *s);
+
+/* State.Bytes() leaving the text in device memory: *dev_out is a device pointer owned by the
+ * handle.  Runs only the kernels (the document must have been staged). */
+TK_API int tk_state_bytes_device(tk_state *s, const void **dev_out, size_t *out_len);
+
+/* The classification step of Clusters()/Nodes() alone: matching module keys are counted and
+ * their indices left in device memory; no host copy of the pairs is built. */
+TK_API int tk_state_prefix_count_device(tk_state *s, const char *prefix, size_t prefix_len, size_t *count);
+
+/* Measurement hooks for bench.py.  With timing enabled every kernel launch on this handle is
+ * bracketed by CUDA events on the handle's stream; tk_state_kernel_stats synchronises the stream
+ * and reports, for kernel number `kind` (0 .. until it returns TK_EARG), its name, the summed
+ * device time of the launches made while timing was on, how many those were, and all launches. */
+TK_API int tk_state_timing(tk_state *s, int enable);
+TK_API int tk_state_kernel_stats(tk_state *s, int kind, const char **name, double *ms,
+                                 unsigned long long *timed_launches, unsigned long long *launches);
+/* Bytes this handle has copied host->device and device->host so far. */
+TK_API int tk_state_copy_stats(tk_state *s, unsigned long long *h2d_bytes, unsigned long long *d2h_bytes);
+
+/* The handle's CUDA stream (a cudaStream_t), so a caller can time or order work on it. */
+TK_API void *tk_state_stream(tk_state *s);
+
+/* Number of kernels this library has launched in this process (for bench.py's gpu_launches). */
+TK_API unsigned long long tk_kernel_launches(void);
+
+/* Library/ABI version string. */
+TK_API const char *tk_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TK_STATE_H */

@@ -23,3 +23,21 @@ def oracle():
 
     O.build()
     return O
+
+
+def _product():
+    import importlib
+
+    return importlib.import_module("triton-kubernetes_b200")
+
+
+@pytest.fixture(scope="session")
+def tk():
+    """The product package (C ABI via ctypes).  Importing it needs the built library, not a GPU."""
+    return _product()
+
+
+@pytest.fixture(params=["oracle", pytest.param("gpu", marks=pytest.mark.gpu)])
+def impl(request, oracle):
+    """Runs a test once against the oracle (CPU) and once against the product on the GPU."""
+    return oracle if request.param == "oracle" else _product()

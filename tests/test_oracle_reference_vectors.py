@@ -1,8 +1,10 @@
-"""The oracle replayed against every vector the reference's own tests hold for this path.
+"""Every vector the reference's own tests hold for this path.
 
-Each test names the reference test it restates (paths relative to /root/reference).  These
-run on CPU (`-m "not gpu"`); the same vectors are replayed through the product's C-ABI in
-tests/test_state_parity_gpu.py.
+Each test names the reference test it restates (paths relative to /root/reference).  Tests
+that take `impl` run twice: against the oracle on CPU (`-m "not gpu"`) and, marked gpu,
+against the product through its C ABI on the B200.  Tests that take `oracle` replay the
+vendored gabs vectors, which need gabs-only calls (compact String(), Path fan-out) that the
+state.State surface does not have.
 """
 import pytest
 
@@ -14,37 +16,37 @@ KEY_PARTS_ERR = ("Could not get cluster key parts, cluster does not follow forma
 
 # ---- state/state_test.go ------------------------------------------------------------------
 
-def test_get(oracle):  # state/state_test.go:8-18
-    s = oracle.New("GetState", b'{"config":{"triton":{"key":"55fd4s","url":"https://api.storage.com"}}}')
+def test_get(impl):  # state/state_test.go:8-18
+    s = impl.New("GetState", b'{"config":{"triton":{"key":"55fd4s","url":"https://api.storage.com"}}}')
     assert s.Get("config.triton.key") == b"55fd4s"
 
 
-def test_set_manager(oracle):  # state/state_test.go:20-34
-    s = oracle.New("AddState", b"{}")
+def test_set_manager(impl):  # state/state_test.go:20-34
+    s = impl.New("AddState", b"{}")
     s.SetManager({"field": "test"})
     assert s.Get("module.cluster-manager.field") == b"test"
 
 
-def test_set_terraform_backend_config(oracle):  # state/state_test.go:36-50
-    s = oracle.New("AddState", b"{}")
+def test_set_terraform_backend_config(impl):  # state/state_test.go:36-50
+    s = impl.New("AddState", b"{}")
     s.SetTerraformBackendConfig("module.path.to.backend", {"field": "test"})
     assert s.Get("module.path.to.backend.field") == b"test"
 
 
-def test_add_cluster(oracle):  # state/state_test.go:53-67
-    s = oracle.New("AddState", b"{}")
+def test_add_cluster(impl):  # state/state_test.go:53-67
+    s = impl.New("AddState", b"{}")
     s.AddCluster("aws", "name", {"field": "test"})
     assert s.Get("module.cluster_aws_name.field") == b"test"
 
 
-def test_add_node(oracle):  # state/state_test.go:69-83
-    s = oracle.New("AddState", b"{}")
+def test_add_node(impl):  # state/state_test.go:69-83
+    s = impl.New("AddState", b"{}")
     s.AddNode("cluster_aws_cluster-name", "node-name", {"field": "test"})
     assert s.Get("module.node_aws_cluster-name_node-name.field") == b"test"
 
 
-def test_delete(oracle):  # state/state_test.go:86-101
-    s = oracle.New("DelState", b'{"config":{"triton":{"key":"55fd4s","url":"https://api.storage.com"}}}')
+def test_delete(impl):  # state/state_test.go:86-101
+    s = impl.New("DelState", b'{"config":{"triton":{"key":"55fd4s","url":"https://api.storage.com"}}}')
     s.Delete("config.triton.key")
     assert s.Get("config.triton.key") == b""
 
@@ -68,26 +70,26 @@ NODES_DOC = b"""{
     }"""
 
 
-def test_get_clusters(oracle):  # state/state_test.go:104-124
-    s = oracle.New("ClusterState", CLUSTERS_DOC)
+def test_get_clusters(impl):  # state/state_test.go:104-124
+    s = impl.New("ClusterState", CLUSTERS_DOC)
     c = s.Clusters()
     assert len(c) == 3
     assert c == {b"dev_cluster": b"cluster_1", b"beta_cluster": b"cluster_2", b"prod_cluster": b"cluster_3"}
 
 
-def test_get_nodes(oracle):  # state/state_test.go:126-156
-    ck = oracle.New("ClusterState", b'{"config":{"triton":{"key":"cluster_triton_dev-cluster","url":"https://api.storage.com"}}}').Get("config.triton.key")
-    s = oracle.New("NodeState", NODES_DOC)
+def test_get_nodes(impl):  # state/state_test.go:126-156
+    ck = impl.New("ClusterState", b'{"config":{"triton":{"key":"cluster_triton_dev-cluster","url":"https://api.storage.com"}}}').Get("config.triton.key")
+    s = impl.New("NodeState", NODES_DOC)
     n = s.Nodes(ck)
     assert len(n) == 3
     assert n == {b"dev-worker1": b"node_triton_dev-cluster_1", b"dev-etcd1": b"node_triton_dev-cluster_2",
                  b"dev-control1": b"node_triton_dev-cluster_3"}
 
 
-def test_get_nodes_without_cloud_provider(oracle):  # state/state_test.go:158-190, string at :184
-    ck = oracle.New("ClusterState", b'{"config":{"triton":{"key":"cluster_dev-cluster","url":"https://api.storage.com"}}}').Get("config.triton.key")
-    s = oracle.New("NodeState", NODES_DOC)
-    with pytest.raises(OracleError) as e:
+def test_get_nodes_without_cloud_provider(impl):  # state/state_test.go:158-190, string at :184
+    ck = impl.New("ClusterState", b'{"config":{"triton":{"key":"cluster_dev-cluster","url":"https://api.storage.com"}}}').Get("config.triton.key")
+    s = impl.New("NodeState", NODES_DOC)
+    with pytest.raises(Exception) as e:
         s.Nodes(ck)
     assert str(e.value) == KEY_PARTS_ERR
 
@@ -103,8 +105,8 @@ def test_get_nodes_without_cloud_provider(oracle):  # state/state_test.go:158-19
     (["test"], "test", 3, ["test-1", "test-2", "test-3"]),
     (["test-1", "test-2", "bar-3", "bar-4"], "test", 3, ["test-3", "test-4", "test-5"]),
 ])
-def test_get_new_hostnames(oracle, existing, name, count, expected):
-    assert oracle.getNewHostnames(existing, name, count) == expected
+def test_get_new_hostnames(impl, existing, name, count, expected):
+    assert impl.getNewHostnames(existing, name, count) == expected
 
 
 # ---- destroy/*_test.go, get/*_test.go fixtures that reach Clusters()/Nodes() ----------------
@@ -123,17 +125,17 @@ MOCK_NODE_HOST = b"""{
 }"""  # destroy/node_test.go:11-15
 
 
-def test_destroy_fixtures(oracle):
+def test_destroy_fixtures(impl):
     # destroy/node_test.go:81-97: "cluster_alpha" is not among the cluster names
-    assert b"cluster_alpha" not in oracle.New("NodeState", MOCK_CLUSTERS).Clusters()
+    assert b"cluster_alpha" not in impl.New("NodeState", MOCK_CLUSTERS).Clusters()
     # destroy/node_test.go:99-138: the cluster resolves, it has no nodes
-    s = oracle.New("NodeState", MOCK_NODE_HOST)
+    s = impl.New("NodeState", MOCK_NODE_HOST)
     assert s.Clusters() == {b"dev_cluster": b"cluster_triton_dev-cluster"}
     assert s.Nodes(b"cluster_triton_dev-cluster") == {}
 
 
-def test_get_cluster_no_clusters(oracle):  # get/cluster_test.go:63-87: empty "module" -> no clusters
-    assert oracle.New("s", b'{"module":{}}').Clusters() == {}
+def test_get_cluster_no_clusters(impl):  # get/cluster_test.go:63-87: empty "module" -> no clusters
+    assert impl.New("s", b'{"module":{}}').Clusters() == {}
 
 
 # ---- vendored gabs_test.go: compact, sorted-key output and the gabs error values ------------
@@ -283,28 +285,28 @@ def test_gabs_nil_set(oracle):  # gabs_test.go:1045-1056
 
 # ---- SURVEY.md 8a notes: behaviour the reference exhibits but does not test -----------------
 
-def test_record_is_opaque_until_reparsed(oracle):  # create/cluster.go:146-152 works around this
-    s = oracle.New("s", b"{}")
-    s.AddCluster("baremetal", "c1", Record([("source", "x"), ("name", "c1")]))
+def test_record_is_opaque_until_reparsed(impl):  # create/cluster.go:146-152 works around this
+    s = impl.New("s", b"{}")
+    s.AddCluster("baremetal", "c1", impl.Record([("source", "x"), ("name", "c1")]))
     assert s.Get("module.cluster_baremetal_c1.name") == b""
     assert s.Clusters() == {}
-    s2 = oracle.New("s", s.Bytes())
+    s2 = impl.New("s", s.Bytes())
     assert s2.Get("module.cluster_baremetal_c1.name") == b"c1"
     assert s2.Clusters() == {b"c1": b"cluster_baremetal_c1"}
 
 
-def test_dotted_cluster_name_nests(oracle):  # gabs.go:206-208 + create/cluster.go:314
-    s = oracle.New("s", b"{}")
+def test_dotted_cluster_name_nests(impl):  # gabs.go:206-208 + create/cluster.go:314
+    s = impl.New("s", b"{}")
     s.AddCluster("x", "a.b", {"name": "a.b"})
-    assert s.BytesCompact() == b'{"module":{"cluster_x_a":{"b":{"name":"a.b"}}}}'
+    assert s.Bytes() == b'{\n\t"module": {\n\t\t"cluster_x_a": {\n\t\t\t"b": {\n\t\t\t\t"name": "a.b"\n\t\t\t}\n\t\t}\n\t}\n}'
 
 
-def test_delete_absent_last_key_is_not_an_error(oracle):  # gabs.go:276-296
-    s = oracle.New("s", b'{"module":{"a":{}}}')
+def test_delete_absent_last_key_is_not_an_error(impl):  # gabs.go:276-296
+    s = impl.New("s", b'{"module":{"a":{}}}')
     s.Delete("module.nope")
     s.Delete("module.a.nope")
-    with pytest.raises(OracleError) as e:
+    with pytest.raises(Exception) as e:
         s.Delete("module.nope.deeper")
     assert str(e.value) == "not an object"
-    with pytest.raises(OracleError):
-        oracle.New("s", b"null").Delete("a")
+    with pytest.raises(Exception):
+        impl.New("s", b"null").Delete("a")

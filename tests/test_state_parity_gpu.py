@@ -1,0 +1,240 @@
+"""Parity proper: the CUDA path through the C ABI against the oracle, bit for bit.
+
+Everything here needs a B200 (`-m gpu`).  Nothing reads /root/reference.
+"""
+import importlib
+import json
+import random
+
+import pytest
+
+from test_abi_cpu import random_ops
+from test_oracle_encoding import ERROR_VECTORS, FLOAT_VECTORS, STRING_VECTORS, rand_tree
+
+pytestmark = pytest.mark.gpu
+
+synth = importlib.import_module("triton-kubernetes_b200.synth")
+
+
+def same(tk, oracle, raw):
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    assert a.Bytes() == b.Bytes()
+    return a, b
+
+
+def test_kernels_really_launch(tk):
+    before = tk.state.kernel_launches()
+    s = tk.New("x", b'{"module":{"cluster_a_b":{"name":"b"}}}')
+    s.Bytes(); s.Clusters(); s.Nodes("cluster_a_b")
+    assert tk.state.kernel_launches() - before >= 4   # row_offsets + emit + 2 x prefix_match
+
+
+@pytest.mark.parametrize("raw,want", [
+    (b"null", b"{}"), (b" {} ", b"{}"), (b"[]", b"[]"), (b'"s"', b'"s"'), (b"[[],{}]", b"[\n\t[],\n\t{}\n]"),
+    (b'{"a":{"b":[1]}}', b'{\n\t"a": {\n\t\t"b": [\n\t\t\t1\n\t\t]\n\t}\n}'), (b"true", b"true"), (b"-0", b"-0"),
+    (b'{"":""}', b'{\n\t"": ""\n}'),
+])
+def test_root_forms(tk, oracle, raw, want):
+    assert tk.New("x", raw).Bytes() == want == oracle.New("x", raw).Bytes()
+
+
+@pytest.mark.parametrize("src,want", STRING_VECTORS)
+def test_string_vectors(tk, src, want):
+    assert tk.New("x", src).Bytes() == want
+    assert tk.New("x", b"{" + src + b":1}").Bytes() == b"{\n\t" + want + b": 1\n}"
+
+
+def test_float_vectors(tk, oracle):
+    raw = ("[" + ",".join(s for s, _ in FLOAT_VECTORS) + "]").encode()
+    assert tk.New("x", raw).Bytes() == ("[\n\t" + ",\n\t".join(w for _, w in FLOAT_VECTORS) + "\n]").encode()
+
+
+@pytest.mark.parametrize("src,msg", ERROR_VECTORS)
+def test_error_vectors(tk, src, msg):
+    with pytest.raises(tk.StateError) as e:
+        tk.New("x", src)
+    assert str(e.value) == msg and e.value.code == tk.state.TK_ESYNTAX
+
+
+def test_raw_invalid_utf8_in_path_key(tk, oracle):
+    a, b = tk.State("x"), oracle.New("x", b"{}")
+    for s in (a, b):
+        s._set(b"a\xffb.\xe2\x80\xa8", b'"v\xc3"')
+    assert a.Bytes() == b.Bytes() == b'{\n\t"a\\ufffdb": {\n\t\t"\\u2028": "v\xef\xbf\xbd"\n\t}\n}'
+
+
+@pytest.mark.parametrize("seed", range(30))
+def test_random_documents(tk, oracle, seed):
+    rng = random.Random(77000 + seed)
+    tree = {"k%d" % i: rand_tree(rng) for i in range(rng.randrange(1, 40))}
+    raw = json.dumps(tree, ensure_ascii=rng.random() < 0.5).encode()
+    a, b = same(tk, oracle, raw)
+    # idempotence through the GPU path
+    assert tk.New("x", a.Bytes()).Bytes() == a.Bytes()
+
+
+def hostile_bytes(rng, n):
+    pool = [b"a", b"\\n", b"\\\"", b"\\u0000", b"\\u2028", b"\\ud83d\\ude00", b"\\ud83d", b"<", b"&", b"\xc3\xa9", b"\xe2\x80\xa8",
+            b"\xe2\x80\xa9", b"\xff", b"\xe2\x82", b"\xf0\x9f\x98\x80", b"\xed\xa0\x80", b"\x7f", b" ", b"\\t", b"\xc0\xaf", b"\xf4\x90\x80\x80"]
+    return b"".join(rng.choice(pool) for _ in range(n))
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_hostile_strings(tk, oracle, seed):
+    """Escapes, invalid UTF-8, U+2028/9 and multi-byte sequences at every alignment and across staging boundaries."""
+    rng = random.Random(4242 + seed)
+    members = []
+    for i in range(200):
+        k = hostile_bytes(rng, rng.randrange(0, 8))
+        v = hostile_bytes(rng, rng.randrange(0, 60))
+        members.append(b'"%d' % i + k + b'":"' + v + b'"')
+    same(tk, oracle, b"{" + b",".join(members) + b"}")
+
+
+@pytest.mark.parametrize("n", [1, 31, 32, 33, 255, 256, 257, 3000, 3071, 3072, 3073, 4095, 4096, 4097, 70000, 1 << 20])
+def test_long_strings(tk, oracle, n):
+    """One string of n bytes among short ones: covers a warp tile that outgrows its shared-memory staging."""
+    rng = random.Random(n)
+    body = hostile_bytes(rng, n // 2) if n < 5000 else (b"x<\\n" * (n // 4))
+    raw = b'{"a":"1","b":"' + body + b'","c":["' + b"y" * n + b'"],"d":"2"}'
+    same(tk, oracle, raw)
+
+
+@pytest.mark.parametrize("depth", [1, 2, 31, 100, 1000, 10000])
+def test_deep_nesting(tk, oracle, depth):
+    same(tk, oracle, b"[" * depth + b"]" * depth)
+    same(tk, oracle, b'{"a":' * depth + b'"x"' + b"}" * depth)
+
+
+@pytest.mark.parametrize("n", [0, 1, 255, 256, 257, 513, 5000])
+def test_row_counts_around_tile_boundaries(tk, oracle, n):
+    same(tk, oracle, b"[" + b",".join(b'"%d"' % i for i in range(n)) + b"]")
+    same(tk, oracle, b"{" + b",".join(b'"k%d":%d' % (i, i) for i in range(n)) + b"}")
+
+
+def test_duplicate_and_unsorted_keys(tk, oracle):
+    same(tk, oracle, b'{"b":1,"a":1,"B":1,"\xc3\xa9":1,"aa":1,"":1,"a\\u0000":1,"~":1,"a":{"z":1,"y":2},"\\u0061":3}')
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_op_sequences(tk, oracle, seed):
+    """Interleaved Set/Delete/Get with maps and records; Bytes/Clusters/Nodes compared along the way."""
+    rng = random.Random(900 + seed)
+    a, b = tk.New("x", b'{"module":{}}'), oracle.New("x", b'{"module":{}}')
+    for step, op in enumerate(random_ops(rng, 200)):
+        ra = rb = None
+        for s, mod in ((a, tk), (b, oracle)):
+            r = None
+            try:
+                if op[0] == "set":
+                    s._set(op[1], mod.Record(op[2]) if op[3] else op[2])
+                elif op[0] == "del":
+                    s.Delete(op[1])
+                else:
+                    r = s.Get(op[1])
+            except Exception as e:
+                r = str(e)
+            if s is a: ra = r
+            else: rb = r
+        assert ra == rb, op
+        if step % 20 == 19:
+            assert a.Bytes() == b.Bytes()
+            for call in ("Clusters", lambda s: s.Nodes("cluster_p_c")):
+                fa = (lambda s: s.Clusters()) if call == "Clusters" else call
+                try: xa = fa(a)
+                except Exception as e: xa = str(e)
+                try: xb = fa(b)
+                except Exception as e: xb = str(e)
+                assert xa == xb
+
+
+def test_records_serialise_in_given_order_and_stay_opaque(tk, oracle):
+    for mod in (tk, oracle):
+        s = mod.New("m", b"{}")
+        s.SetManager(mod.Record([("source", "s"), ("name", "m"), ("host", "h")]))
+        s.AddCluster("baremetal", "c1", mod.Record([("source", "x"), ("name", "c1"), ("k8s_version", "v")]))
+        s.AddNode("cluster_baremetal_c1", "n1", mod.Record([("source", "y"), ("hostname", "n1"),
+                  ("rancher_host_labels", mod.Record([("worker", "true")])), ("host", "10.0.0.1")]))
+        s.AddNode("cluster_baremetal_c1", "n2", {"hostname": "n2", "source": "y"})
+        if mod is tk:
+            got = (s.Bytes(), s.Clusters(), s.Nodes("cluster_baremetal_c1"), s.Get("module.cluster-manager.name"))
+        else:
+            want = (s.Bytes(), s.Clusters(), s.Nodes("cluster_baremetal_c1"), s.Get("module.cluster-manager.name"))
+    assert got == want
+    assert got[1] == {} and got[2] == {b"n2": b"node_baremetal_c1_n2"} and got[3] == b""
+    assert b'"source": "x",\n\t\t\t"name": "c1"' in got[0]       # declaration order kept
+    re = tk.New("m", got[0])                                         # create/cluster.go:146-152: reload
+    assert re.Clusters() == {b"c1": b"cluster_baremetal_c1"}
+    assert set(re.Nodes("cluster_baremetal_c1")) == {b"n1", b"n2"}
+
+
+def test_prefix_semantics(tk, oracle):
+    """strings.Index(key, prefix) == 0: overlapping names, children that are not maps, missing fields, duplicates."""
+    doc = {"module": {
+        "cluster_a_x": {"name": "x"}, "cluster_a_x_y": {"name": "x"}, "cluster_": {"name": "empty"}, "cluster": {"name": "no"},
+        "xcluster_a": {"name": "no"}, "cluster_b_arr": [{"name": "no"}], "cluster_b_str": "s", "cluster_b_null": None,
+        "cluster_b_noname": {"nam": "x"}, "cluster_b_numname": {"name": 1}, "cluster_c_z": {"name": "z"},
+        "node_a_x_1": {"hostname": "h1"}, "node_a_x_y_1": {"hostname": "h2"}, "node_a_x": {"hostname": "h3"},
+        "node_a_x_": {"hostname": "h4"}, "node_a_xy_1": {"hostname": "h5"}, "node_a_x_2": {"hostname": "h1"},
+        "node_a_x_3": {"hostname": 5}, "node_a_x_4": ["hostname"], "node_b_x_1": {"hostname": "h6"}}}
+    raw = json.dumps(doc).encode()
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    assert a.Clusters() == b.Clusters()
+    for ck in ("cluster_a_x", "cluster_a_x_y", "cluster_a_xy", "cluster_b_x", "cluster_a_", "cluster__", "a_b_c", "cluster_a_x_extra_parts"):
+        assert a.Nodes(ck) == b.Nodes(ck), ck
+    assert a.Nodes("cluster_a_x") == {b"h1": b"node_a_x_2", b"h2": b"node_a_x_y_1", b"h4": b"node_a_x_"}
+
+
+def test_long_prefix(tk, oracle):
+    name = "n" * 700                                   # longer than the kernel's shared-memory prefix buffer
+    doc = {"module": {"node_p_%s_1" % name: {"hostname": "a"}, "node_p_%sX_1" % name[:-1]: {"hostname": "b"},
+                      "node_p_%s_2" % name: {"hostname": "c"}}}
+    raw = json.dumps(doc).encode()
+    ck = "cluster_p_" + name
+    assert tk.New("x", raw).Nodes(ck) == oracle.New("x", raw).Nodes(ck) and len(oracle.New("x", raw).Nodes(ck)) == 2
+
+
+@pytest.mark.parametrize("clusters,nodes", [(3, 5), (40, 25)])
+def test_config4_small(tk, oracle, clusters, nodes):
+    raw = synth.document(clusters, nodes)
+    a, b = same(tk, oracle, raw)
+    assert a.Clusters() == b.Clusters() and len(a.Clusters()) == clusters
+    for c in range(clusters):
+        assert a.Nodes(synth.cluster_key(c)) == b.Nodes(synth.cluster_key(c))
+
+
+def test_config5_destroy_sweep_small(tk, oracle):
+    """destroy/cluster.go:126-158 at library granularity: Nodes(ck) -> Delete each node -> Delete the cluster."""
+    raw = synth.document(30, 12)
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    for s in (a, b):
+        for name, ck in sorted(s.Clusters().items()):
+            for host, nk in sorted(s.Nodes(ck).items()):
+                s.Delete(b"module." + nk)
+            s.Delete(b"module." + ck)
+            s.Delete(b"module." + ck)          # deleting an absent key is not an error
+    want = json.dumps({"module": {"cluster-manager": synth.manager_record()},
+                       "terraform": {"backend": {"local": {"path": "/root/.triton-kubernetes/bench/terraform.tfstate"}}}},
+                      indent="\t", sort_keys=True).encode()
+    assert a.Bytes() == b.Bytes() == want
+
+
+def test_config4_full_size(tk, oracle):
+    """BASELINE.json config #4 at full size: 1,000 clusters x 100 nodes, 62,177,405 bytes."""
+    raw = synth.document()
+    a = tk.New("bench", raw)
+    text = a.Bytes()
+    assert len(text) == 62177405
+    b = oracle.New("bench", raw)
+    assert text == b.Bytes()
+    ca = a.Clusters()
+    assert ca == b.Clusters() and len(ca) == 1000
+    for c in (0, 1, 499, 998, 999):
+        na = a.Nodes(synth.cluster_key(c))
+        assert na == b.Nodes(synth.cluster_key(c)) and len(na) == 100
+    # size-independent properties
+    again = tk.New("bench", text)
+    assert again.Bytes() == text                                    # serialise(parse(x)) is a fixed point
+    assert sum(len(a.Nodes(ck)) for ck in list(ca.values())[::50]) == 20 * 100
+    a.Delete("module." + synth.node_key(7, 7))
+    assert len(a.Nodes(synth.cluster_key(7))) == 99 and len(a.Bytes()) < len(text)

@@ -1,0 +1,273 @@
+// capi.cu -- the extern "C" surface declared in include/tk_state.h.
+#include <algorithm>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "doc.hpp"
+#include "engine.hpp"
+#include "kernels.cuh"
+#include "tk_state.h"
+
+using namespace tk;
+
+struct tk_state {
+    std::string name;
+    Document doc;
+    Engine eng;
+    std::string err;
+    std::string blob;  // last Clusters()/Nodes() result
+};
+
+static thread_local std::string g_err;        // for calls that have no handle
+static thread_local std::string g_hostnames;  // tk_new_hostnames result
+
+static int set_err(tk_state *s, int code, std::string msg) {
+    if (s) s->err = std::move(msg); else g_err = std::move(msg);
+    return code;
+}
+static std::string_view sv(const char *p, size_t n) { return p ? std::string_view(p, n) : std::string_view(); }
+
+extern "C" {
+
+const char *tk_version(void) { return "libtkstate 0.1 (sm_100a)"; }
+unsigned long long tk_kernel_launches(void) { return kernel_launch_count(); }
+
+const char *tk_last_error(tk_state *s) { return s ? s->err.c_str() : g_err.c_str(); }
+
+int tk_state_new(const char *name, size_t name_len, const char *raw, size_t raw_len, tk_state **out) {
+    if (!out) return set_err(nullptr, TK_EARG, "tk_state_new: out is NULL");
+    *out = nullptr;
+    auto *s = new tk_state();
+    s->name.assign(sv(name, name_len));
+    std::string err;
+    // the device is a hard requirement: fail here, loudly, rather than at the first bulk call
+    int rc = s->eng.init(&err);
+    if (rc) { delete s; return set_err(nullptr, rc, err); }
+    Node *root = nullptr;
+    if (!parse_value(sv(raw, raw_len), false, &root, &err)) { delete s; return set_err(nullptr, TK_ESYNTAX, err); }
+    s->doc.root = root;
+    *out = s;
+    return TK_OK;
+}
+
+int tk_state_new_empty(const char *name, size_t name_len, tk_state **out) {
+    if (!out) return set_err(nullptr, TK_EARG, "tk_state_new_empty: out is NULL");
+    auto *s = new tk_state();
+    s->name.assign(sv(name, name_len));
+    s->doc.root = new MapNode();
+    *out = s;
+    return TK_OK;
+}
+
+void tk_state_free(tk_state *s) { delete s; }
+
+int tk_state_name(tk_state *s, const char **name, size_t *name_len) {
+    if (!s || !name || !name_len) return set_err(s, TK_EARG, "tk_state_name: NULL argument");
+    *name = s->name.data();
+    *name_len = s->name.size();
+    return TK_OK;
+}
+
+int tk_state_get(tk_state *s, const char *path, size_t path_len, const char **value, size_t *value_len) {
+    if (!s || !value || !value_len) return set_err(s, TK_EARG, "tk_state_get: NULL argument");
+    std::string_view v = s->doc.get(sv(path, path_len));
+    *value = v.data() ? v.data() : "";
+    *value_len = v.size();
+    return TK_OK;
+}
+
+int tk_state_set(tk_state *s, const char *path, size_t path_len, const char *json, size_t json_len, int value_kind) {
+    if (!s) return set_err(s, TK_EARG, "tk_state_set: NULL handle");
+    Node *v = nullptr;
+    std::string err;
+    if (!parse_value(sv(json, json_len), value_kind == TK_VALUE_RECORD, &v, &err)) return set_err(s, TK_ESYNTAX, err);
+    int rc = s->doc.set(sv(path, path_len), v, &err);
+    if (rc) return set_err(s, rc, err);
+    return TK_OK;
+}
+
+int tk_state_set_manager(tk_state *s, const char *json, size_t json_len, int value_kind) {
+    static const char path[] = "module.cluster-manager";
+    return tk_state_set(s, path, sizeof path - 1, json, json_len, value_kind);
+}
+
+int tk_state_set_terraform_backend_config(tk_state *s, const char *path, size_t path_len, const char *json, size_t json_len,
+                                          int value_kind) {
+    return tk_state_set(s, path, path_len, json, json_len, value_kind);
+}
+
+int tk_state_add_cluster(tk_state *s, const char *provider, size_t provider_len, const char *name, size_t name_len,
+                         const char *json, size_t json_len, int value_kind) {
+    std::string path = "module.cluster_";
+    path.append(sv(provider, provider_len));
+    path.push_back('_');
+    path.append(sv(name, name_len));
+    return tk_state_set(s, path.data(), path.size(), json, json_len, value_kind);
+}
+
+int tk_state_add_node(tk_state *s, const char *cluster_key, size_t cluster_key_len, const char *name, size_t name_len,
+                      const char *json, size_t json_len, int value_kind) {
+    if (!s) return set_err(s, TK_EARG, "tk_state_add_node: NULL handle");
+    std::string_view provider, cname;
+    std::string err;
+    if (!cluster_key_parts(sv(cluster_key, cluster_key_len), &provider, &cname, &err)) return set_err(s, TK_EKEYPARTS, err);
+    std::string path = "module.node_";
+    path.append(provider);
+    path.push_back('_');
+    path.append(cname);
+    path.push_back('_');
+    path.append(sv(name, name_len));
+    return tk_state_set(s, path.data(), path.size(), json, json_len, value_kind);
+}
+
+int tk_state_delete(tk_state *s, const char *path, size_t path_len) {
+    if (!s) return set_err(s, TK_EARG, "tk_state_delete: NULL handle");
+    std::string err;
+    int rc = s->doc.del(sv(path, path_len), &err);
+    if (rc) return set_err(s, rc, err);
+    return TK_OK;
+}
+
+int tk_state_stage(tk_state *s) {
+    if (!s) return set_err(s, TK_EARG, "tk_state_stage: NULL handle");
+    std::string err;
+    int rc = s->eng.stage(s->doc, &err);
+    if (rc) return set_err(s, rc, err);
+    return TK_OK;
+}
+
+int tk_state_bytes(tk_state *s, const char **out, size_t *out_len) {
+    if (!s || !out || !out_len) return set_err(s, TK_EARG, "tk_state_bytes: NULL argument");
+    std::string err;
+    const void *p = nullptr;
+    int rc = s->eng.bytes(s->doc, true, &p, out_len, &err);
+    if (rc) return set_err(s, rc, err);
+    *out = static_cast<const char *>(p);
+    return TK_OK;
+}
+
+int tk_state_bytes_device(tk_state *s, const void **dev_out, size_t *out_len) {
+    if (!s || !dev_out || !out_len) return set_err(s, TK_EARG, "tk_state_bytes_device: NULL argument");
+    std::string err;
+    int rc = s->eng.bytes(s->doc, false, dev_out, out_len, &err);
+    if (rc) return set_err(s, rc, err);
+    return TK_OK;
+}
+
+int tk_state_prefix_count_device(tk_state *s, const char *prefix, size_t prefix_len, size_t *count) {
+    if (!s) return set_err(s, TK_EARG, "tk_state_prefix_count_device: NULL handle");
+    std::string err;
+    int rc = s->eng.prefix_hits(s->doc, sv(prefix, prefix_len), false, nullptr, count, &err);
+    if (rc) return set_err(s, rc, err);
+    return TK_OK;
+}
+
+int tk_state_timing(tk_state *s, int enable) {
+    if (!s) return set_err(s, TK_EARG, "tk_state_timing: NULL handle");
+    s->eng.set_timing(enable != 0);
+    return TK_OK;
+}
+
+int tk_state_kernel_stats(tk_state *s, int kind, const char **name, double *ms, unsigned long long *timed_launches,
+                          unsigned long long *launches) {
+    if (!s) return set_err(s, TK_EARG, "tk_state_kernel_stats: NULL handle");
+    if (kind < 0 || kind >= K_COUNT) return set_err(s, TK_EARG, "tk_state_kernel_stats: no such kernel");
+    std::string err;
+    int rc = s->eng.collect_times(&err);
+    if (rc) return set_err(s, rc, err);
+    if (name) *name = kernel_name(kind);
+    if (ms) *ms = s->eng.kernel_ms(kind);
+    if (timed_launches) *timed_launches = s->eng.timed_launches(kind);
+    if (launches) *launches = s->eng.launches(kind);
+    return TK_OK;
+}
+
+int tk_state_copy_stats(tk_state *s, unsigned long long *h2d_bytes, unsigned long long *d2h_bytes) {
+    if (!s) return set_err(s, TK_EARG, "tk_state_copy_stats: NULL handle");
+    if (h2d_bytes) *h2d_bytes = s->eng.h2d_bytes();
+    if (d2h_bytes) *d2h_bytes = s->eng.d2h_bytes();
+    return TK_OK;
+}
+
+void *tk_state_stream(tk_state *s) { return s ? (void *)s->eng.stream() : nullptr; }
+
+// Shared body of Clusters()/Nodes() (state/state.go:94-147): children of "module" whose key has
+// the prefix (classified on the GPU), mapped <field> -> key for children that are maps with a
+// string <field>.
+static int children_by_prefix(tk_state *s, std::string_view prefix, std::string_view field, const uint8_t **blob,
+                              size_t *blob_len, size_t *count) {
+    std::string err;
+    if (!s->doc.module_children()) return set_err(s, TK_ENOTOBJ, kErrNotObj);
+    std::vector<uint32_t> hits;
+    int rc = s->eng.prefix_hits(s->doc, prefix, true, &hits, nullptr, &err);
+    if (rc) return set_err(s, rc, err);
+    struct Pair { std::string_view name, key; };
+    std::vector<Pair> pairs;
+    pairs.reserve(hits.size());
+    for (uint32_t h : hits) {
+        auto *e = s->eng.module_entry(h);
+        const Node *child = e->second;
+        if (!child || child->kind != Kind::Map) continue;  // records (Go structs) are opaque
+        auto &m = static_cast<const MapNode *>(child)->m;
+        auto it = m.find(field);
+        if (it == m.end() || !it->second || it->second->kind != Kind::Str) continue;
+        pairs.push_back({static_cast<const StrNode *>(it->second)->s, e->first});
+    }
+    std::sort(pairs.begin(), pairs.end(), [](const Pair &a, const Pair &b) { return a.name != b.name ? a.name < b.name : a.key < b.key; });
+    s->blob.clear();
+    size_t kept = 0;
+    for (size_t i = 0; i < pairs.size(); i++) {
+        if (i + 1 < pairs.size() && pairs[i + 1].name == pairs[i].name) continue;  // greatest key wins
+        uint32_t l = (uint32_t)pairs[i].name.size();
+        s->blob.append(reinterpret_cast<const char *>(&l), 4);
+        s->blob.append(pairs[i].name);
+        l = (uint32_t)pairs[i].key.size();
+        s->blob.append(reinterpret_cast<const char *>(&l), 4);
+        s->blob.append(pairs[i].key);
+        kept++;
+    }
+    *blob = reinterpret_cast<const uint8_t *>(s->blob.data());
+    *blob_len = s->blob.size();
+    *count = kept;
+    return TK_OK;
+}
+
+int tk_state_clusters(tk_state *s, const uint8_t **blob, size_t *blob_len, size_t *count) {
+    if (!s || !blob || !blob_len || !count) return set_err(s, TK_EARG, "tk_state_clusters: NULL argument");
+    return children_by_prefix(s, "cluster_", "name", blob, blob_len, count);
+}
+
+int tk_state_nodes(tk_state *s, const char *cluster_key, size_t cluster_key_len, const uint8_t **blob, size_t *blob_len,
+                   size_t *count) {
+    if (!s || !blob || !blob_len || !count) return set_err(s, TK_EARG, "tk_state_nodes: NULL argument");
+    std::string_view provider, cname;
+    std::string err;
+    if (!cluster_key_parts(sv(cluster_key, cluster_key_len), &provider, &cname, &err)) return set_err(s, TK_EKEYPARTS, err);
+    std::string prefix = "node_";
+    prefix.append(provider);
+    prefix.push_back('_');
+    prefix.append(cname);
+    prefix.push_back('_');
+    return children_by_prefix(s, prefix, "hostname", blob, blob_len, count);
+}
+
+int tk_new_hostnames(const char *const *existing, const size_t *existing_len, size_t n, const char *node_name,
+                     size_t node_name_len, long long nodes_to_add, const char **out, size_t *out_len) {
+    if (!out || !out_len || (n && (!existing || !existing_len))) return set_err(nullptr, TK_EARG, "tk_new_hostnames: NULL argument");
+    std::vector<std::string_view> ex;
+    ex.reserve(n);
+    for (size_t i = 0; i < n; i++) ex.push_back(sv(existing[i], existing_len[i]));
+    g_hostnames.clear();
+    bool firstname = true;
+    for (auto &h : new_hostnames(ex, sv(node_name, node_name_len), nodes_to_add)) {
+        if (!firstname) g_hostnames.push_back('\n');
+        g_hostnames.append(h);
+        firstname = false;
+    }
+    *out = g_hostnames.data();
+    *out_len = g_hostnames.size();
+    return TK_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,399 @@
+// kernels.cu -- sm_100a kernels of the state.State bulk passes.
+//
+//   row_offsets_kernel   State.Bytes(), pass 1: escaped length of every output line and the
+//                        exclusive prefix sum of those lengths (single pass, decoupled look-back)
+//   emit_kernel          State.Bytes(), pass 2: every line written at its offset
+//   prefix_match_kernel  State.Clusters()/Nodes(): module keys that start with a prefix
+//
+// All three are HBM/L2-bound byte work (no flops): the design rules that matter are coalesced
+// 16-byte global accesses, shared-memory staging of the unaligned string bytes, and grids that
+// are many multiples of the 148 SMs.  Reference semantics restated here:
+//   encoding/json encodeState.string (HTML-safe escaping, \\ufffd for invalid UTF-8, U+2028/9)
+//   encoding/json Indent("", "\t")   (line layout, see tape.hpp)
+//   state/state.go:102-110,134-144   strings.Index(key, prefix) == 0
+#include "kernels.cuh"
+
+#include <atomic>
+
+namespace tk {
+
+static std::atomic<unsigned long long> g_launches{0};
+unsigned long long kernel_launch_count() { return g_launches.load(); }
+
+namespace {
+
+constexpr unsigned FULL = 0xffffffffu;
+constexpr int WARPS = EMIT_THREADS / 32;
+
+// ---- byte classification (encoding/json: htmlSafeSet) -----------------------------------
+
+// 1 bit per ASCII code: the byte is copied as is
+__device__ __forceinline__ bool ascii_plain(uint32_t c) {
+    // 0x00-0x1f escape; '"' 0x22, '&' 0x26, '<' 0x3c, '>' 0x3e, '\\' 0x5c escape; 0x7f is plain
+    const uint32_t w = (c < 32) ? 0u : (c < 64) ? 0xAFFFFFBBu : (c < 96) ? 0xEFFFFFFFu : 0xFFFFFFFFu;
+    return (w >> (c & 31)) & 1u;
+}
+
+// escaped size of one ASCII byte that is not plain
+__device__ __forceinline__ uint32_t ascii_esc_len(uint32_t c) {
+    return (c == '"' || c == '\\' || c == '\n' || c == '\r' || c == '\t') ? 2u : 6u;
+}
+
+// unicode/utf8.DecodeRune validity: length of the sequence starting at s[i], 0 if invalid
+__device__ __forceinline__ uint32_t utf8_seq_len(const uint8_t *s, uint32_t i, uint32_t n) {
+    const uint32_t c = s[i];
+    uint32_t lo = 0x80, hi = 0xBF, len;
+    if (c >= 0xC2 && c <= 0xDF) len = 2;
+    else if (c >= 0xE0 && c <= 0xEF) { len = 3; if (c == 0xE0) lo = 0xA0; if (c == 0xED) hi = 0x9F; }
+    else if (c >= 0xF0 && c <= 0xF4) { len = 4; if (c == 0xF0) lo = 0x90; if (c == 0xF4) hi = 0x8F; }
+    else return 0;
+    if (i + len > n) return 0;
+    const uint32_t c1 = s[i + 1];
+    if (c1 < lo || c1 > hi) return 0;
+    for (uint32_t k = 2; k < len; k++)
+        if ((s[i + k] & 0xC0) != 0x80) return 0;
+    return len;
+}
+
+// length of the JSON-escaped form of s[0, n) (without the surrounding quotes)
+__device__ __forceinline__ uint32_t escaped_len(const uint8_t *s, uint32_t n) {
+    uint32_t len = 0;
+    for (uint32_t i = 0; i < n;) {
+        const uint32_t c = s[i];
+        if (c < 0x80) {
+            len += ascii_plain(c) ? 1u : ascii_esc_len(c);
+            i++;
+            continue;
+        }
+        const uint32_t l = utf8_seq_len(s, i, n);
+        if (l == 0) { len += 6; i += 1; continue; }                                   // \\ufffd
+        if (l == 3 && c == 0xE2 && s[i + 1] == 0x80 && (s[i + 2] & 0xFE) == 0xA8) {    // U+2028 / U+2029
+            len += 6; i += 3; continue;
+        }
+        len += l;
+        i += l;
+    }
+    return len;
+}
+
+__device__ __forceinline__ uint8_t hex_digit(uint32_t v) { return (uint8_t)(v < 10 ? '0' + v : 'a' + (v - 10)); }
+
+// writes the escaped form of s[0, n) at dst[pos...]; returns the new pos
+__device__ __forceinline__ uint32_t put_escaped(uint8_t *dst, uint32_t pos, const uint8_t *s, uint32_t n) {
+    for (uint32_t i = 0; i < n;) {
+        const uint32_t c = s[i];
+        if (c < 0x80) {
+            i++;
+            if (ascii_plain(c)) { dst[pos++] = (uint8_t)c; continue; }
+            dst[pos++] = '\\';
+            switch (c) {
+            case '"': case '\\': dst[pos++] = (uint8_t)c; break;
+            case '\n': dst[pos++] = 'n'; break;
+            case '\r': dst[pos++] = 'r'; break;
+            case '\t': dst[pos++] = 't'; break;
+            default:
+                dst[pos++] = 'u'; dst[pos++] = '0'; dst[pos++] = '0';
+                dst[pos++] = hex_digit(c >> 4); dst[pos++] = hex_digit(c & 15);
+            }
+            continue;
+        }
+        const uint32_t l = utf8_seq_len(s, i, n);
+        if (l == 0) {
+            dst[pos++] = '\\'; dst[pos++] = 'u'; dst[pos++] = 'f'; dst[pos++] = 'f'; dst[pos++] = 'f'; dst[pos++] = 'd';
+            i += 1;
+            continue;
+        }
+        if (l == 3 && c == 0xE2 && s[i + 1] == 0x80 && (s[i + 2] & 0xFE) == 0xA8) {
+            dst[pos++] = '\\'; dst[pos++] = 'u'; dst[pos++] = '2'; dst[pos++] = '0'; dst[pos++] = '2';
+            dst[pos++] = (uint8_t)('8' + (s[i + 2] & 1));
+            i += 3;
+            continue;
+        }
+        for (uint32_t k = 0; k < l; k++) dst[pos++] = s[i + k];
+        i += l;
+    }
+    return pos;
+}
+
+struct Row { uint32_t meta, koff, klen, voff, vlen; };
+
+__device__ __forceinline__ Row load_row(const TapeView &t, uint32_t r) {
+    Row w;
+    w.meta = __ldg(t.meta + r); w.koff = __ldg(t.koff + r); w.klen = __ldg(t.klen + r);
+    w.voff = __ldg(t.voff + r); w.vlen = __ldg(t.vlen + r);
+    return w;
+}
+__device__ __forceinline__ bool row_has_value_bytes(const Row &w) { return (w.meta & 15u) <= ROW_RAW && w.vlen; }
+
+// Stages the arena bytes the 32 rows of a warp refer to into that warp's shared-memory slice with
+// coalesced 16-byte loads.  Returns true and sets *base (arena offset of slice byte 0) when the
+// span fits; the caller then reads arena byte x at slice[x - *base].
+__device__ __forceinline__ bool stage_warp_input(const TapeView &t, const Row &w, bool valid, uint4 *slice, uint32_t *base) {
+    uint32_t lo = 0xffffffffu, hi = 0;
+    if (valid) {
+        if ((w.meta & META_HAS_KEY) && w.klen) { lo = min(lo, w.koff); hi = max(hi, w.koff + w.klen); }
+        if (row_has_value_bytes(w)) { lo = min(lo, w.voff); hi = max(hi, w.voff + w.vlen); }
+    }
+    lo = __reduce_min_sync(FULL, lo);
+    hi = __reduce_max_sync(FULL, hi);
+    if (hi <= lo) { *base = 0; return true; }  // no string bytes at all
+    const uint32_t b = lo & ~15u;
+    if (hi - b > (uint32_t)WARP_IN_BYTES) return false;
+    const uint32_t chunks = (hi - b + 15u) >> 4;
+    const uint4 *src = reinterpret_cast<const uint4 *>(t.arena + b);
+    for (uint32_t c = threadIdx.x & 31; c < chunks; c += 32) slice[c] = __ldg(src + c);
+    __syncwarp();
+    *base = b;
+    return true;
+}
+
+__device__ __forceinline__ uint32_t row_out_len(const Row &w, const uint8_t *kp, const uint8_t *vp) {
+    uint32_t len = w.meta >> META_DEPTH_SHIFT;
+    if (w.meta & META_HAS_KEY) len += escaped_len(kp, w.klen) + 4;  // "key":<space>
+    switch (w.meta & 15u) {
+    case ROW_STR: len += escaped_len(vp, w.vlen) + 2; break;
+    case ROW_RAW: len += w.vlen; break;
+    case ROW_EMPTY_OBJ: case ROW_EMPTY_ARR: len += 2; break;
+    default: len += 1;
+    }
+    if (w.meta & META_COMMA) len += 1;
+    if (!(w.meta & META_LAST)) len += 1;
+    return len;
+}
+
+// ---- K1: line lengths + exclusive scan ------------------------------------------------------
+
+constexpr unsigned long long ST_AGG = 1ull << 62, ST_PREFIX = 2ull << 62, ST_MASK = (1ull << 62) - 1;
+
+__device__ __forceinline__ unsigned long long ld_status(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_status(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(EMIT_THREADS) row_offsets_kernel(TapeView t, uint32_t *__restrict__ off,
+                                                                  unsigned long long *scratch) {
+    __shared__ uint4 s_in[WARPS][WARP_IN_BYTES / 16];
+    __shared__ uint32_t s_warp_sum[WARPS];
+    __shared__ uint32_t s_tile;
+    __shared__ unsigned long long s_prefix;
+
+    // tiles are handed out in launch order so that a tile only ever waits on tiles already running
+    if (threadIdx.x == 0) s_tile = (uint32_t)atomicAdd(&scratch[0], 1ull);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t r = tile * EMIT_ROWS_PER_BLOCK + threadIdx.x;
+    const bool valid = r < t.n_rows;
+
+    Row w = {0, 0, 0, 0, 0};
+    if (valid) w = load_row(t, r);
+    uint32_t base;
+    const bool staged = stage_warp_input(t, w, valid, s_in[warp], &base);
+    const uint8_t *src = staged ? reinterpret_cast<const uint8_t *>(s_in[warp]) - base : t.arena;
+    const uint32_t len = valid ? row_out_len(w, src + w.koff, src + w.voff) : 0;
+
+    // inclusive scan inside the warp, then across the 8 warps
+    uint32_t incl = len;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t v = __shfl_up_sync(FULL, incl, d);
+        if (lane >= (uint32_t)d) incl += v;
+    }
+    if (lane == 31) s_warp_sum[warp] = incl;
+    __syncthreads();
+    uint32_t warp_excl = 0, block_sum = 0;
+#pragma unroll
+    for (int i = 0; i < WARPS; i++) {
+        const uint32_t v = s_warp_sum[i];
+        if ((uint32_t)i < warp) warp_excl += v;
+        block_sum += v;
+    }
+
+    // decoupled look-back over the tile status words (warp 0)
+    unsigned long long *status = scratch + 2;
+    if (warp == 0) {
+        unsigned long long prefix = 0;
+        if (tile == 0) {
+            if (lane == 0) st_status(status, ST_PREFIX | block_sum);
+        } else {
+            if (lane == 0) st_status(status + tile, ST_AGG | block_sum);
+            int look = (int)tile - 1;
+            for (;;) {
+                const int idx = look - (int)lane;
+                unsigned long long s = idx >= 0 ? ld_status(status + idx) : ST_PREFIX;
+                while (__any_sync(FULL, (s >> 62) == 0)) {
+                    if ((s >> 62) == 0) s = ld_status(status + idx);
+                }
+                const unsigned pm = __ballot_sync(FULL, (s >> 62) == 2);
+                const int first = pm ? __ffs(pm) - 1 : 32;
+                unsigned long long v = ((int)lane <= first) ? (s & ST_MASK) : 0ull;
+#pragma unroll
+                for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(FULL, v, d);
+                prefix += v;
+                if (pm) break;
+                look -= 32;
+            }
+            if (lane == 0) st_status(status + tile, ST_PREFIX | (prefix + block_sum));
+        }
+        if (lane == 0) {
+            s_prefix = prefix;
+            if ((tile + 1) * (uint32_t)EMIT_ROWS_PER_BLOCK >= t.n_rows) scratch[1] = prefix + block_sum;  // total
+        }
+    }
+    __syncthreads();
+    const unsigned long long o = s_prefix + warp_excl + (incl - len);
+    if (valid) off[r] = (uint32_t)o;
+    if (valid && r + 1 == t.n_rows) off[r + 1] = (uint32_t)(o + len);
+}
+
+// ---- K2: emit -------------------------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t put_line(uint8_t *dst, uint32_t pos, const Row &w, const uint8_t *kp, const uint8_t *vp) {
+    const uint32_t depth = w.meta >> META_DEPTH_SHIFT;
+    for (uint32_t i = 0; i < depth; i++) dst[pos++] = '\t';
+    if (w.meta & META_HAS_KEY) {
+        dst[pos++] = '"';
+        pos = put_escaped(dst, pos, kp, w.klen);
+        dst[pos++] = '"'; dst[pos++] = ':'; dst[pos++] = ' ';
+    }
+    switch (w.meta & 15u) {
+    case ROW_STR:
+        dst[pos++] = '"';
+        pos = put_escaped(dst, pos, vp, w.vlen);
+        dst[pos++] = '"';
+        break;
+    case ROW_RAW:
+        for (uint32_t i = 0; i < w.vlen; i++) dst[pos++] = vp[i];
+        break;
+    case ROW_OPEN_OBJ: dst[pos++] = '{'; break;
+    case ROW_OPEN_ARR: dst[pos++] = '['; break;
+    case ROW_CLOSE_OBJ: dst[pos++] = '}'; break;
+    case ROW_CLOSE_ARR: dst[pos++] = ']'; break;
+    case ROW_EMPTY_OBJ: dst[pos++] = '{'; dst[pos++] = '}'; break;
+    default: dst[pos++] = '['; dst[pos++] = ']'; break;
+    }
+    if (w.meta & META_COMMA) dst[pos++] = ',';
+    if (!(w.meta & META_LAST)) dst[pos++] = '\n';
+    return pos;
+}
+
+__global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const uint32_t *__restrict__ off,
+                                                           uint8_t *__restrict__ out) {
+    extern __shared__ uint4 emit_smem[];  // [WARPS][WARP_IN_BYTES/16] then [WARPS][WARP_OUT_BYTES/16]
+    uint4(*s_in)[WARP_IN_BYTES / 16] = reinterpret_cast<uint4(*)[WARP_IN_BYTES / 16]>(emit_smem);
+    uint4(*s_out)[WARP_OUT_BYTES / 16] = reinterpret_cast<uint4(*)[WARP_OUT_BYTES / 16]>(emit_smem + WARPS * (WARP_IN_BYTES / 16));
+
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t r0 = blockIdx.x * EMIT_ROWS_PER_BLOCK + warp * 32;  // first row of this warp's tile
+    if (r0 >= t.n_rows) return;
+    const uint32_t r = r0 + lane;
+    const bool valid = r < t.n_rows;
+
+    Row w = {0, 0, 0, 0, 0};
+    uint32_t o = 0;
+    if (valid) { w = load_row(t, r); o = __ldg(off + r); }
+    uint32_t base;
+    const bool staged = stage_warp_input(t, w, valid, s_in[warp], &base);
+    const uint8_t *src = staged ? reinterpret_cast<const uint8_t *>(s_in[warp]) - base : t.arena;
+
+    const uint32_t r_end = min(r0 + 32u, t.n_rows);
+    const uint32_t out0 = __ldg(off + r0), out1 = __ldg(off + r_end);  // off has n_rows + 1 entries
+    const uint32_t shift = out0 & 15u;                                  // same 16-byte phase as global
+    const uint32_t span = out1 - out0;
+
+    if (shift + span <= (uint32_t)WARP_OUT_BYTES) {
+        uint8_t *slice = reinterpret_cast<uint8_t *>(s_out[warp]);
+        if (valid) put_line(slice, o - out0 + shift, w, src + w.koff, src + w.voff);
+        __syncwarp();
+        // copy out: whole 16-byte chunks as vectors, the ragged head and tail bytewise
+        uint8_t *g = out + (out0 - shift);  // 16-byte aligned
+        const uint32_t end = shift + span;
+        const uint32_t chunks = (end + 15u) >> 4;
+        for (uint32_t c = lane; c < chunks; c += 32) {
+            const uint32_t b0 = c << 4;
+            if (b0 >= shift && b0 + 16 <= end) {
+                reinterpret_cast<uint4 *>(g)[c] = s_out[warp][c];
+            } else {
+                const uint32_t lo = max(b0, shift), hi = min(b0 + 16, end);
+                for (uint32_t b = lo; b < hi; b++) g[b] = slice[b];
+            }
+        }
+    } else if (valid) {
+        put_line(out, o, w, src + w.koff, src + w.voff);  // oversized tile: straight to global memory
+    }
+}
+
+// ---- K3: key prefix classification -------------------------------------------------------------
+
+constexpr int PREFIX_THREADS = 256;
+constexpr int PREFIX_SMEM = 256;
+
+__global__ void __launch_bounds__(PREFIX_THREADS) prefix_match_kernel(KeyIndexView k, const uint8_t *__restrict__ prefix,
+                                                                     uint32_t plen, uint32_t *hits) {
+    __shared__ uint8_t s_prefix[PREFIX_SMEM];
+    for (uint32_t i = threadIdx.x; i < min(plen, (uint32_t)PREFIX_SMEM); i += blockDim.x) s_prefix[i] = prefix[i];
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t n_round = (k.n_keys + 31u) & ~31u;  // keep warps converged for the ballot
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+        bool match = false;
+        if (i < k.n_keys) {
+            const uint32_t b = __ldg(k.koffs + i), e = __ldg(k.koffs + i + 1);
+            if (e - b >= plen) {
+                const uint8_t *key = k.keys + b;
+                uint32_t j = 0;
+                const uint32_t ps = min(plen, (uint32_t)PREFIX_SMEM);
+                while (j < ps && __ldg(key + j) == s_prefix[j]) j++;
+                if (j == ps) while (j < plen && __ldg(key + j) == __ldg(prefix + j)) j++;
+                match = (j == plen);
+            }
+        }
+        const unsigned m = __ballot_sync(FULL, match);
+        if (m) {
+            uint32_t slot = 0;
+            if (lane == (uint32_t)(__ffs(m) - 1)) slot = atomicAdd(hits, (uint32_t)__popc(m));
+            slot = __shfl_sync(FULL, slot, __ffs(m) - 1);
+            if (match) hits[1 + slot + __popc(m & ((1u << lane) - 1))] = i;
+        }
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_row_offsets(const TapeView &t, uint32_t *off, unsigned long long *scratch, cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words(t.n_rows) * sizeof(unsigned long long), s);
+    if (e != cudaSuccess) return e;
+    row_offsets_kernel<<<emit_tiles(t.n_rows), EMIT_THREADS, 0, s>>>(t, off, scratch);
+    g_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_emit(const TapeView &t, const uint32_t *off, uint8_t *out, cudaStream_t s) {
+    constexpr int smem = WARPS * (WARP_IN_BYTES + WARP_OUT_BYTES);
+    static bool configured = false;  // per process; every device runs the same image
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    emit_kernel<<<emit_tiles(t.n_rows), EMIT_THREADS, smem, s>>>(t, off, out);
+    g_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_prefix_match(const KeyIndexView &k, const uint8_t *prefix, uint32_t prefix_len, uint32_t *hits,
+                                cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(hits, 0, sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    if (k.n_keys == 0) return cudaSuccess;
+    const uint32_t blocks = min((k.n_keys + PREFIX_THREADS - 1) / PREFIX_THREADS, 148u * 8u);
+    prefix_match_kernel<<<blocks, PREFIX_THREADS, 0, s>>>(k, prefix, prefix_len, hits);
+    g_launches++;
+    return cudaGetLastError();
+}
+
+}  // namespace tk

@@ -1,0 +1,38 @@
+// kernels.cuh -- launch wrappers of the sm_100a kernels (implemented in kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "tape.hpp"
+
+namespace tk {
+
+// geometry shared by the two serialisation kernels
+constexpr int EMIT_THREADS = 256;                       // 8 warps, one 32-row warp tile each per step
+constexpr int EMIT_ROWS_PER_BLOCK = EMIT_THREADS;       // rows handled by one block
+constexpr int WARP_IN_BYTES = 3072;                     // per-warp staging of arena bytes
+constexpr int WARP_OUT_BYTES = 4096;                    // per-warp staging of output text
+
+inline uint32_t emit_tiles(uint32_t n_rows) { return (n_rows + EMIT_ROWS_PER_BLOCK - 1) / EMIT_ROWS_PER_BLOCK; }
+
+// scratch needed by row_offsets: 2 + tiles 64-bit words (tile counter, total, per-tile status)
+inline size_t scan_scratch_words(uint32_t n_rows) { return 2 + (size_t)emit_tiles(n_rows); }
+
+// K1: per-row output length (escaping included) and its exclusive prefix sum.
+//     off[r] = byte offset of line r (n_rows + 1 entries); scratch[1] = serialised length.
+//     scratch must hold scan_scratch_words(n) words; it is cleared on the stream first.
+cudaError_t launch_row_offsets(const TapeView &t, uint32_t *off, unsigned long long *scratch, cudaStream_t s);
+
+// K2: write every line at its offset.
+cudaError_t launch_emit(const TapeView &t, const uint32_t *off, uint8_t *out, cudaStream_t s);
+
+// K3: indices of the keys that start with prefix, appended (unordered) to hits[1..];
+//     hits[0] = count.  hits must hold n_keys + 1 words; hits[0] is cleared on the stream first.
+//     prefix is a device pointer.
+cudaError_t launch_prefix_match(const KeyIndexView &k, const uint8_t *prefix, uint32_t prefix_len, uint32_t *hits,
+                                cudaStream_t s);
+
+unsigned long long kernel_launch_count();
+
+}  // namespace tk
