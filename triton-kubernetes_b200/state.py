@@ -134,6 +134,8 @@ class State:
         h = c_void_p()
         if raw is None:
             rc = L.tk_state_new_empty(nm, len(nm), byref(h))
+        elif isinstance(raw, tuple):  # (address, length) of a caller-owned (e.g. pinned) buffer
+            rc = L.tk_state_new(nm, len(nm), ctypes.cast(raw[0], c_char_p), raw[1], byref(h))
         else:
             raw = _b(raw)
             rc = L.tk_state_new(nm, len(nm), raw, len(raw), byref(h))
