@@ -147,6 +147,35 @@ TK_API int tk_state_kernel_stats(tk_state *s, int kind, const char **name, doubl
 /* Bytes this handle has copied host->device and device->host so far. */
 TK_API int tk_state_copy_stats(tk_state *s, unsigned long long *h2d_bytes, unsigned long long *d2h_bytes);
 
+/* Allocation-free line-offset pass.  (No counterpart in the reference: this entry point exists
+ * only on the GPU side of the boundary.)
+ *
+ * For callers that cannot let a library allocate GPU memory: programs that gave all of it to
+ * their own pool at start-up, and latency-critical paths where cudaMalloc/cudaFree are unwelcome
+ * because they may synchronise the device and stall other streams.  It runs the first pass of
+ * State.Bytes() -- the escaped length of every output line and the running sum of those lengths
+ * -- on a line tape the caller already holds in device memory (layout: csrc/tape.hpp), writing
+ * n_rows + 1 offsets to off_out (off_out[r] = byte offset of line r, off_out[n_rows] = length of
+ * the whole text).  All pointers except err are device pointers owned by the caller; arena must
+ * be readable for 16 bytes past arena_bytes.  The work is enqueued on `stream` (a cudaStream_t,
+ * NULL = default stream) and the call returns without waiting for it.
+ *
+ * It calls no cudaMalloc, cudaFree or other allocating routine.  The scan's scratch (a tile
+ * counter, a total and one status word per 256 rows) is a fixed array inside the library,
+ * 65,552 bytes on every GPU that loads it, which limits n_rows to TK_NOALLOC_MAX_ROWS; larger
+ * tapes are rejected with TK_ELIMIT and a message in err.  Things to know:
+ *   - the first call on each device looks up the array's device address; make that first call
+ *     with the device current and before any stream capture begins;
+ *   - every call on a GPU uses the same array, which keeps the previous call's contents: the
+ *     part a call needs is cleared on `stream` first, and two calls whose GPU work overlaps
+ *     (different streams, or different threads) race on it -- serialise them.
+ * err (may be NULL) receives the error text; nothing is allocated for it either. */
+#define TK_NOALLOC_MAX_ROWS 2097152u
+TK_API int tk_row_offsets_noalloc(const uint32_t *meta, const uint32_t *koff, const uint32_t *klen,
+                                  const uint32_t *voff, const uint32_t *vlen, const uint8_t *arena,
+                                  uint32_t arena_bytes, uint32_t n_rows, uint32_t *off_out, void *stream,
+                                  char *err, size_t err_cap);
+
 /* The handle's CUDA stream (a cudaStream_t), so a caller can time or order work on it. */
 TK_API void *tk_state_stream(tk_state *s);
 

@@ -397,3 +397,96 @@ cudaError_t launch_prefix_match(const KeyIndexView &k, const uint8_t *prefix, ui
 }
 
 }  // namespace tk
+
+// ---------------------------------------------------------------------------------------------
+// tk_row_offsets_noalloc: the line-offset pass for callers that must not allocate.
+//
+// Who this is for: a host program that has handed all of its GPU memory to its own pool or
+// arena up front (so a cudaMalloc from a library would either fail or eat memory the program
+// has budgeted for something else), and code on a latency-critical path where cudaMalloc /
+// cudaFree are unwelcome because they can synchronise the whole device and stall unrelated
+// streams.  Such a caller owns every input and output buffer; the only thing the offset pass
+// needs beyond those is its small scan scratch (one tile counter, one total, one status word
+// per 256-row tile), and here that lives in the fixed array below instead of a cudaMalloc'd
+// buffer.  The price is a size limit and one shared scratch per GPU.
+// ---------------------------------------------------------------------------------------------
+
+#include <cstdio>
+#include <mutex>
+
+#include "tk_state.h"
+
+namespace {
+
+constexpr uint32_t NOALLOC_MAX_TILES = TK_NOALLOC_MAX_ROWS / tk::EMIT_ROWS_PER_BLOCK;
+// 2 + 8192 words = 65,552 bytes of device memory per GPU that loads this library, held until
+// the process exits.
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[2 + NOALLOC_MAX_TILES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+unsigned long long *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+void noalloc_err(char *err, size_t cap, const char *msg, cudaError_t e = cudaSuccess) {
+    if (!err || !cap) return;
+    if (e == cudaSuccess) snprintf(err, cap, "%s", msg);
+    else snprintf(err, cap, "%s: %s", msg, cudaGetErrorString(e));
+}
+
+}  // namespace
+
+extern "C" int tk_row_offsets_noalloc(const uint32_t *meta, const uint32_t *koff, const uint32_t *klen,
+                                      const uint32_t *voff, const uint32_t *vlen, const uint8_t *arena,
+                                      uint32_t arena_bytes, uint32_t n_rows, uint32_t *off_out, void *stream,
+                                      char *err, size_t err_cap) {
+    if (!meta || !koff || !klen || !voff || !vlen || !off_out || (arena_bytes && !arena)) {
+        noalloc_err(err, err_cap, "tk_row_offsets_noalloc: NULL argument");
+        return TK_EARG;
+    }
+    if (n_rows == 0 || n_rows > TK_NOALLOC_MAX_ROWS) {
+        if (err && err_cap)
+            snprintf(err, err_cap, "tk_row_offsets_noalloc: n_rows = %u is outside 1..%u (the fixed scratch holds one status word per %d rows)",
+                     n_rows, (unsigned)TK_NOALLOC_MAX_ROWS, tk::EMIT_ROWS_PER_BLOCK);
+        return TK_ELIMIT;
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= NOALLOC_MAX_DEVICES) {
+        noalloc_err(err, err_cap, "tk_row_offsets_noalloc: cudaGetDevice", e);
+        (void)cudaGetLastError();
+        return TK_ECUDA;
+    }
+    unsigned long long *scratch;
+    {
+        // Set-up, once per device and with that device current: in host code the array's name is
+        // only a stand-in, so ask the runtime for the address the kernel must be given.
+        std::lock_guard<std::mutex> lock(g_noalloc_mu);
+        if (!g_noalloc_ptr[dev]) {
+            void *p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess || !p) {
+                noalloc_err(err, err_cap, "tk_row_offsets_noalloc: cudaGetSymbolAddress", e);
+                (void)cudaGetLastError();
+                return TK_ECUDA;
+            }
+            g_noalloc_ptr[dev] = static_cast<unsigned long long *>(p);
+        }
+        scratch = g_noalloc_ptr[dev];
+    }
+    tk::TapeView t;
+    t.n_rows = n_rows; t.arena_bytes = arena_bytes;
+    t.meta = meta; t.koff = koff; t.klen = klen; t.voff = voff; t.vlen = vlen; t.arena = arena;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // the array still holds the previous call's counter and status words: they must start at zero
+    e = cudaMemsetAsync(scratch, 0, tk::scan_scratch_words(n_rows) * sizeof(unsigned long long), s);
+    if (e == cudaSuccess) {
+        tk::row_offsets_kernel<<<tk::emit_tiles(n_rows), tk::EMIT_THREADS, 0, s>>>(t, off_out, scratch);
+        tk::g_launches++;
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) {
+        noalloc_err(err, err_cap, "tk_row_offsets_noalloc: launch", e);
+        return TK_ECUDA;
+    }
+    return TK_OK;
+}
