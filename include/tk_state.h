@@ -176,6 +176,12 @@ TK_API int tk_row_offsets_noalloc(const uint32_t *meta, const uint32_t *koff, co
                                   uint32_t arena_bytes, uint32_t n_rows, uint32_t *off_out, void *stream,
                                   char *err, size_t err_cap);
 
+/* 1 if the document's host tree exists.  After state.New on text whose object keys are already
+ * in encoding/json's output order (strictly ascending, hence unique) the document lives only as
+ * the line tape on the device and Bytes() runs straight from it; the tree is built on the first
+ * point operation (Get/Set/Add/Delete/Clusters/Nodes), or at once when the keys need re-ordering. */
+TK_API int tk_state_host_tree_built(tk_state *s);
+
 /* The handle's CUDA stream (a cudaStream_t), so a caller can time or order work on it. */
 TK_API void *tk_state_stream(tk_state *s);
 

@@ -29,6 +29,22 @@ def test_kernels_really_launch(tk):
     assert tk.state.kernel_launches() - before >= 4   # row_offsets + emit + 2 x prefix_match
 
 
+def test_new_keeps_canonical_documents_on_the_device(tk, oracle):
+    """Text already in encoding/json's order is serialised straight from the tape the GPU parser built;
+    anything that needs re-ordering, de-duplication or number re-formatting builds the host tree."""
+    canon = oracle.New("x", synth.document(5, 4)).Bytes()
+    for raw, resident in [(canon, True), (b'{"a":{"b":1,"c":[true,null,"x"]},"b":"\u00e9\n"}', True),
+                          (b'{"b":1,"a":2}', False), (b'{"a":1,"a":2}', False), (b'{"a":1.50}', False),
+                          (b'{"a":{"y":1,"x":2}}', False), (b'[{"k":1},{"k":1}]', True), (b'{"a":"x","a\u0000":"y"}', True)]:
+        s = tk.New("x", raw)
+        assert s.host_tree_built == (not resident), raw[:40]
+        assert s.Bytes() == oracle.New("x", raw).Bytes()
+        assert s.host_tree_built == (not resident)          # Bytes() alone never builds the tree
+    s = tk.New("x", canon)
+    assert s.Get("module.cluster-manager.name") == b"bench" and s.host_tree_built
+    assert s.Bytes() == canon
+
+
 @pytest.mark.parametrize("raw,want", [
     (b"null", b"{}"), (b" {} ", b"{}"), (b"[]", b"[]"), (b'"s"', b'"s"'), (b"[[],{}]", b"[\n\t[],\n\t{}\n]"),
     (b'{"a":{"b":[1]}}', b'{\n\t"a": {\n\t\t"b": [\n\t\t\t1\n\t\t]\n\t}\n}'), (b"true", b"true"), (b"-0", b"-0"),

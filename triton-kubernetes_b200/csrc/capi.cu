@@ -28,10 +28,20 @@ static int set_err(tk_state *s, int code, std::string msg) {
 }
 static std::string_view sv(const char *p, size_t n) { return p ? std::string_view(p, n) : std::string_view(); }
 
+// The point operations work on the host tree; a document that so far exists only as the device
+// tape state.New produced gets its tree built here, once.
+static int ensure_host(tk_state *s) {
+    if (s->doc.host_valid) return TK_OK;
+    std::string err;
+    int rc = s->eng.materialise(&s->doc, &err);
+    if (rc) return set_err(s, rc, err);
+    return TK_OK;
+}
+
 extern "C" {
 
 const char *tk_version(void) { return "libtkstate 0.1 (sm_100a)"; }
-unsigned long long tk_kernel_launches(void) { return kernel_launch_count(); }
+unsigned long long tk_kernel_launches(void) { return kernel_launch_count() + parse_launch_count(); }
 
 const char *tk_last_error(tk_state *s) { return s ? s->err.c_str() : g_err.c_str(); }
 
@@ -41,12 +51,9 @@ int tk_state_new(const char *name, size_t name_len, const char *raw, size_t raw_
     auto *s = new tk_state();
     s->name.assign(sv(name, name_len));
     std::string err;
-    // the device is a hard requirement: fail here, loudly, rather than at the first bulk call
-    int rc = s->eng.init(&err);
+    // whole documents are parsed on the GPU; without a device this fails, loudly
+    int rc = s->eng.parse(raw, raw_len, &s->doc, &err);
     if (rc) { delete s; return set_err(nullptr, rc, err); }
-    Node *root = nullptr;
-    if (!parse_value(sv(raw, raw_len), false, &root, &err)) { delete s; return set_err(nullptr, TK_ESYNTAX, err); }
-    s->doc.root = root;
     *out = s;
     return TK_OK;
 }
@@ -71,6 +78,7 @@ int tk_state_name(tk_state *s, const char **name, size_t *name_len) {
 
 int tk_state_get(tk_state *s, const char *path, size_t path_len, const char **value, size_t *value_len) {
     if (!s || !value || !value_len) return set_err(s, TK_EARG, "tk_state_get: NULL argument");
+    if (int rc = ensure_host(s)) return rc;
     std::string_view v = s->doc.get(sv(path, path_len));
     *value = v.data() ? v.data() : "";
     *value_len = v.size();
@@ -79,6 +87,7 @@ int tk_state_get(tk_state *s, const char *path, size_t path_len, const char **va
 
 int tk_state_set(tk_state *s, const char *path, size_t path_len, const char *json, size_t json_len, int value_kind) {
     if (!s) return set_err(s, TK_EARG, "tk_state_set: NULL handle");
+    if (int rc = ensure_host(s)) return rc;
     Node *v = nullptr;
     std::string err;
     if (!parse_value(sv(json, json_len), value_kind == TK_VALUE_RECORD, &v, &err)) return set_err(s, TK_ESYNTAX, err);
@@ -123,6 +132,7 @@ int tk_state_add_node(tk_state *s, const char *cluster_key, size_t cluster_key_l
 
 int tk_state_delete(tk_state *s, const char *path, size_t path_len) {
     if (!s) return set_err(s, TK_EARG, "tk_state_delete: NULL handle");
+    if (int rc = ensure_host(s)) return rc;
     std::string err;
     int rc = s->doc.del(sv(path, path_len), &err);
     if (rc) return set_err(s, rc, err);
@@ -132,6 +142,7 @@ int tk_state_delete(tk_state *s, const char *path, size_t path_len) {
 int tk_state_stage(tk_state *s) {
     if (!s) return set_err(s, TK_EARG, "tk_state_stage: NULL handle");
     std::string err;
+    if (int rc = ensure_host(s)) return rc;
     int rc = s->eng.stage(s->doc, &err);
     if (rc) return set_err(s, rc, err);
     return TK_OK;
@@ -158,6 +169,7 @@ int tk_state_bytes_device(tk_state *s, const void **dev_out, size_t *out_len) {
 int tk_state_prefix_count_device(tk_state *s, const char *prefix, size_t prefix_len, size_t *count) {
     if (!s) return set_err(s, TK_EARG, "tk_state_prefix_count_device: NULL handle");
     std::string err;
+    if (int rc = ensure_host(s)) return rc;
     int rc = s->eng.prefix_hits(s->doc, sv(prefix, prefix_len), false, nullptr, count, &err);
     if (rc) return set_err(s, rc, err);
     return TK_OK;
@@ -190,6 +202,8 @@ int tk_state_copy_stats(tk_state *s, unsigned long long *h2d_bytes, unsigned lon
     return TK_OK;
 }
 
+int tk_state_host_tree_built(tk_state *s) { return s && s->doc.host_valid ? 1 : 0; }
+
 void *tk_state_stream(tk_state *s) { return s ? (void *)s->eng.stream() : nullptr; }
 
 // Shared body of Clusters()/Nodes() (state/state.go:94-147): children of "module" whose key has
@@ -198,6 +212,7 @@ void *tk_state_stream(tk_state *s) { return s ? (void *)s->eng.stream() : nullpt
 static int children_by_prefix(tk_state *s, std::string_view prefix, std::string_view field, const uint8_t **blob,
                               size_t *blob_len, size_t *count) {
     std::string err;
+    if (int rc = ensure_host(s)) return rc;
     if (!s->doc.module_children()) return set_err(s, TK_ENOTOBJ, kErrNotObj);
     std::vector<uint32_t> hits;
     int rc = s->eng.prefix_hits(s->doc, prefix, true, &hits, nullptr, &err);

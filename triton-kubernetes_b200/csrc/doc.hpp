@@ -61,6 +61,9 @@ std::vector<std::string_view> split(std::string_view s, char sep);
 struct Document {
     Node *root = nullptr;  // nullptr == nil
     uint64_t version = 1;  // bumped by every successful or partially applied mutation
+    // false while the document exists only as the device tape state.New produced; the point
+    // operations build the tree from that tape on first use (Engine::materialise)
+    bool host_valid = true;
     ~Document() { free_node(root); }
 
     // State.Get: string at path or empty view

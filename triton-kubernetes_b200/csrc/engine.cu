@@ -2,49 +2,98 @@
 #include "engine.hpp"
 
 #include <algorithm>
+#include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
 
 #include "kernels.cuh"
 #include "tk_state.h"
 
 namespace tk {
 
-template <class T>
-bool PinVec<T>::reserve(size_t want) {
-    if (want <= cap) return true;
-    size_t c = cap ? cap : 1024;
-    while (c < want) c *= 2;
-    T *q = nullptr;
-    if (cudaHostAlloc(reinterpret_cast<void **>(&q), c * sizeof(T), cudaHostAllocDefault) != cudaSuccess) {
-        (void)cudaGetLastError();
-        failed = true;
-        return false;
-    }
-    if (n) memcpy(q, p, n * sizeof(T));
-    if (p) cudaFreeHost(p);
-    p = q;
-    cap = c;
-    return true;
-}
-template struct PinVec<uint32_t>;
-template struct PinVec<uint8_t>;
-template struct PinVec<unsigned long long>;
+// ---------------------------------------------------------------------------- buffer pools
 
-cudaError_t DevBuf::reserve(size_t bytes) {
+namespace {
+
+size_t size_class(size_t bytes) {
+    if (bytes <= 256) return 256;
+    if (bytes > (size_t(1) << 30)) return (bytes + (size_t(1) << 28) - 1) & ~((size_t(1) << 28) - 1);
+    size_t c = 256;
+    while (c < bytes) c <<= 1;
+    return c;
+}
+
+struct Pool {
+    std::mutex mu;
+    std::map<std::pair<int, size_t>, std::vector<void *>> free_blocks;  // (device, size class) -> blocks
+};
+Pool g_dev_pool, g_pin_pool;
+
+}  // namespace
+
+void *pool_alloc_device(size_t bytes, size_t *got) {
+    const size_t c = size_class(bytes);
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+    {
+        std::lock_guard<std::mutex> lock(g_dev_pool.mu);
+        auto &v = g_dev_pool.free_blocks[{dev, c}];
+        if (!v.empty()) { void *p = v.back(); v.pop_back(); *got = c; return p; }
+    }
+    void *p = nullptr;
+    if (cudaMalloc(&p, c) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+    *got = c;
+    return p;
+}
+void pool_free_device(void *p, size_t bytes) {
+    if (!p) return;
+    int dev = 0;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) == cudaSuccess) dev = a.device; else (void)cudaGetLastError();
+    std::lock_guard<std::mutex> lock(g_dev_pool.mu);
+    g_dev_pool.free_blocks[{dev, bytes}].push_back(p);
+}
+void *pool_alloc_pinned(size_t bytes, size_t *got) {
+    const size_t c = size_class(bytes);
+    {
+        std::lock_guard<std::mutex> lock(g_pin_pool.mu);
+        auto &v = g_pin_pool.free_blocks[{0, c}];
+        if (!v.empty()) { void *p = v.back(); v.pop_back(); *got = c; return p; }
+    }
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, c, cudaHostAllocPortable) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+    *got = c;
+    return p;
+}
+void pool_free_pinned(void *p, size_t bytes) {
+    if (!p) return;
+    std::lock_guard<std::mutex> lock(g_pin_pool.mu);
+    g_pin_pool.free_blocks[{0, bytes}].push_back(p);
+}
+
+cudaError_t DevBuf::reserve(size_t bytes, size_t keep_bytes, cudaStream_t s) {
     if (bytes <= cap) return cudaSuccess;
-    size_t c = cap ? cap : 4096;
-    while (c < bytes) c *= 2;
-    void *q = nullptr;
-    cudaError_t e = cudaMalloc(&q, c);
-    if (e != cudaSuccess) return e;
-    if (p) cudaFree(p);  // contents are never carried over: every buffer is rewritten after a grow
+    size_t got = 0;
+    void *q = pool_alloc_device(bytes, &got);
+    if (!q) return cudaErrorMemoryAllocation;
+    if (p && keep_bytes) {
+        cudaError_t e = cudaMemcpyAsync(q, p, keep_bytes, cudaMemcpyDeviceToDevice, s);
+        if (e != cudaSuccess) { pool_free_device(q, got); return e; }
+        // the old block goes back to the pool; work queued on other streams never uses it
+        if ((e = cudaStreamSynchronize(s)) != cudaSuccess) { pool_free_device(q, got); return e; }
+    }
+    if (p) pool_free_device(p, cap);
     p = q;
-    cap = c;
+    cap = got;
     return cudaSuccess;
 }
 
 const char *kernel_name(int kind) {
-    static const char *const names[K_COUNT] = {"row_offsets_kernel", "emit_kernel", "prefix_match_kernel"};
+    static const char *const names[K_COUNT] = {"row_offsets_kernel", "emit_kernel", "prefix_match_kernel", "scan_tokens_kernel",
+                                               "token_prefix_kernel", "brackets_kernel", "sort_brackets (split passes)", "match_kernel",
+                                               "decode kernels", "rows_kernel", "key_order_kernel"};
     return kind >= 0 && kind < K_COUNT ? names[kind] : "";
 }
 
@@ -78,8 +127,6 @@ cudaError_t Engine::timed(int kind, F &&launch) {
     pending_.push_back({kind, a, b});
     return e;
 }
-
-void Engine::set_timing(bool on) { timing_ = on; }
 
 int Engine::collect_times(std::string *err) {
     if (!stream_) return TK_OK;
@@ -215,7 +262,6 @@ void Engine::flatten_keys(const Document &doc) {
     h_koffs_.clear(); h_keys_.clear();
     entries_.clear();
     const MapNode *mod = doc.module_children();
-    module_ok_ = mod != nullptr;
     h_koffs_.push(0);
     if (mod) {
         entries_.reserve(mod->m.size());
@@ -237,6 +283,8 @@ int Engine::stage_tape(const Document &doc, std::string *err) {
     int rc = init(err);
     if (rc) return rc;
     if (staged_version_ == doc.version) return TK_OK;
+    if (!doc.host_valid) { *err = "internal: no host tree to flatten"; return TK_EARG; }
+    tape_from_parse_ = false;
     flatten(doc);
     if (pin_failed_) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
     if (h_arena_.n >= 0xfffffff0ull || h_meta_.n >= 0xfffffff0ull) {
@@ -347,6 +395,279 @@ int Engine::prefix_hits(const Document &doc, std::string_view prefix, bool to_ho
         if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "copy hits", err);
     }
     hits->assign(h_hits_.p + 1, h_hits_.p + 1 + c);
+    return TK_OK;
+}
+
+}  // namespace tk
+
+// ============================================================================ state.New on the GPU
+
+namespace tk {
+
+int Engine::fetch_result(std::string *err) {
+    cudaError_t e;
+    if (!h_res_.reserve(1)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+    if ((e = copy_d2h(h_res_.p, d_res_.p, sizeof(ParseResult))) != cudaSuccess) return fail(e, "copy parse result", err);
+    if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "parse", err);
+    return TK_OK;
+}
+
+// text -> start of the arena, space padded to a whole number of 16 KiB tiles (+32)
+int Engine::upload_text(const char *raw, size_t n, std::string *err) {
+    int rc = init(err);
+    if (rc) return rc;
+    if (n >= 0xfff00000ull) { *err = "document too large: the text must stay below 4 GiB"; return TK_ELIMIT; }
+    const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 32;
+    cudaError_t e;
+    if ((e = d_arena_.reserve(padded)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
+    if (n && (e = copy_h2d(d_arena_.p, raw, n)) != cudaSuccess) return fail(e, "copy text", err);
+    if ((e = cudaMemsetAsync(d_arena_.as<uint8_t>() + n, ' ', padded - n, stream_)) != cudaSuccess) return fail(e, "pad text", err);
+    raw_len_ = n;
+    arena_used_ = padded;
+    staged_version_ = keys_version_ = total_version_ = 0;
+    return TK_OK;
+}
+
+// Every kernel of the pipeline, on the text already resident at the start of the arena.  Leaves
+// the tape (rows in input order) on the device and the verdict in *out.  Host synchronisations:
+// after P1 (token count sizes the later buffers), after P2a (row / bracket counts), after the
+// last kernel; two more only if some string needs decoding.
+int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
+    cudaError_t e;
+    const uint8_t *raw = d_arena_.as<uint8_t>();
+    memset(out, 0, sizeof *out);
+    if ((e = d_res_.reserve(sizeof(ParseResult))) != cudaSuccess) return fail(e, "cudaMalloc(result)", err);
+    ParseResult *d_res = d_res_.as<ParseResult>();
+    if (n == 0) { out->invalid = 1; return TK_OK; }
+
+    // ---- P1 (re-run with a larger token buffer in the rare case the estimate was too small)
+    size_t cap = n / 4 + 4096;
+    TokenBuffers tb{};
+    for (;;) {
+        if ((e = d_tok_pos_.reserve((cap + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(tokens)", err);
+        if ((e = d_tok_kind_.reserve(cap + 2)) != cudaSuccess) return fail(e, "cudaMalloc(tokens)", err);
+        if ((e = d_dec_bits_.reserve((cap + 31) / 32 * 4 + 8)) != cudaSuccess) return fail(e, "cudaMalloc(tokens)", err);
+        if ((e = d_scratch_.reserve(p1_scratch_words(n) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+        tb.pos = d_tok_pos_.as<uint32_t>(); tb.kind = d_tok_kind_.as<uint8_t>(); tb.decode_bits = d_dec_bits_.as<uint32_t>();
+        tb.cap = (uint32_t)cap;
+        if ((e = timed(K_SCAN_TOKENS, [&] { return launch_scan_tokens(raw, n, tb, d_scratch_.as<unsigned long long>(), d_res, stream_); })) != cudaSuccess)
+            return fail(e, "scan_tokens", err);
+        int rc = fetch_result(err);
+        if (rc) return rc;
+        if (h_res_.p->n_tokens <= cap) break;
+        if (h_res_.p->n_tokens >= 0x7ffffff0ull) { *err = "document too large: more than 2^31 tokens"; return TK_ELIMIT; }
+        cap = (size_t)h_res_.p->n_tokens;
+    }
+    *out = *h_res_.p;
+    if (out->n_tokens == 0 || out->end_in_string) out->invalid = 1;
+    if (out->invalid) return TK_OK;
+    const uint32_t n_tok = (uint32_t)out->n_tokens;
+
+    // ---- P2a
+    if ((e = d_tiles_.reserve((size_t)tok_tiles(n_tok) * sizeof(TilePrefix))) != cudaSuccess) return fail(e, "cudaMalloc(tiles)", err);
+    if ((e = d_scratch_.reserve((4 + 2 * (size_t)tok_tiles(n_tok)) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    TilePrefix *tiles = d_tiles_.as<TilePrefix>();
+    if ((e = timed(K_TOKEN_PREFIX, [&] { return launch_token_prefix(tb, n_tok, tiles, d_scratch_.as<unsigned long long>(), d_res, stream_); })) != cudaSuccess)
+        return fail(e, "token_prefix", err);
+    int rc = fetch_result(err);
+    if (rc) return rc;
+    *out = *h_res_.p;
+    if (out->invalid) return TK_OK;
+    const uint32_t n_rows = out->n_rows, n_br = out->n_brackets;
+
+    // ---- brackets: compact, sort by level, pair
+    BracketBuffers bb{};
+    {
+        uint32_t **slots[9] = {&bb.tok, &bb.lvkind, &bb.match, &bb.parent, &bb.row, &bb.sort_a, &bb.sort_b, &bb.key_a, &bb.key_b};
+        for (int i = 0; i < 9; i++) {
+            if ((e = d_br_[i].reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(brackets)", err);
+            *slots[i] = d_br_[i].as<uint32_t>();
+        }
+    }
+    if ((e = d_bitzeros_.reserve(16 * 4)) != cudaSuccess) return fail(e, "cudaMalloc(bitzeros)", err);
+    if ((e = d_flags_.reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(flags)", err);
+    if ((e = d_zrank_.reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(zrank)", err);
+    if ((e = d_scratch_.reserve(parse_scan_scratch_words(std::max(n_br, (n_tok + 31) / 32)) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    if ((e = timed(K_BRACKETS, [&] { return launch_brackets(tb, n_tok, tiles, bb, d_bitzeros_.as<unsigned int>(), stream_); })) != cudaSuccess)
+        return fail(e, "brackets", err);
+    bool in_a = true;
+    if ((e = timed(K_SORT_BRACKETS, [&] {
+             return launch_sort_brackets(bb, n_br, out->max_level, d_bitzeros_.as<unsigned int>(), d_flags_.as<uint32_t>(), d_zrank_.as<uint32_t>(),
+                                         d_scratch_.as<unsigned long long>(), &in_a, stream_);
+         })) != cudaSuccess)
+        return fail(e, "sort_brackets", err);
+    if ((e = timed(K_MATCH, [&] { return launch_match(bb, in_a ? bb.sort_a : bb.sort_b, in_a ? bb.key_a : bb.key_b, n_br, d_res, stream_); })) != cudaSuccess)
+        return fail(e, "match", err);
+
+    // ---- strings with escapes or non-ASCII bytes are decoded into a side arena behind the text
+    DecodeBuffers db{};
+    uint32_t n_dec = 0;
+    if (out->n_decode) {
+        const uint32_t words = (n_tok + 31) / 32;
+        if ((e = d_dec_counts_.reserve(((size_t)words + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(decode)", err);
+        if ((e = d_dec_offs_.reserve(((size_t)words + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(decode)", err);
+        if ((e = d_dec_tok_.reserve(((size_t)n_tok / 2 + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(decode)", err);
+        db.tok = d_dec_tok_.as<uint32_t>();
+        if (!h_words_.reserve(4)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+        unsigned long long *scratch = d_scratch_.as<unsigned long long>();
+        if ((e = timed(K_DECODE, [&] { return launch_decode_list(tb, n_tok, db, d_dec_counts_.as<uint32_t>(), d_dec_offs_.as<uint32_t>(), scratch, stream_); })) != cudaSuccess)
+            return fail(e, "decode_list", err);
+        if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy decode count", err);
+        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "decode_list", err);
+        n_dec = (uint32_t)h_words_.p[0];
+        if ((e = d_dec_off_.reserve(((size_t)n_dec + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(decode)", err);
+        if ((e = d_dec_len_.reserve(((size_t)n_dec + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(decode)", err);
+        db.off = d_dec_off_.as<uint32_t>(); db.len = d_dec_len_.as<uint32_t>();
+        if ((e = d_scratch_.reserve(parse_scan_scratch_words(n_dec) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+        scratch = d_scratch_.as<unsigned long long>();
+        if ((e = timed(K_DECODE, [&] { return launch_decode_lengths(raw, tb, db, n_dec, scratch, stream_); })) != cudaSuccess)
+            return fail(e, "decode_lengths", err);
+        if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy decode size", err);
+        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "decode_lengths", err);
+        const size_t side = (size_t)h_words_.p[0];
+        const size_t side_base = ((size_t)p1_tiles(n) * P1_TILE + 32 + 15) & ~size_t(15);
+        if (side_base + side >= 0xfffffff0ull) { *err = "document too large: text plus decoded strings must stay below 4 GiB"; return TK_ELIMIT; }
+        if ((e = d_arena_.reserve(side_base + side + 32, side_base, stream_)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
+        raw = d_arena_.as<uint8_t>();
+        if ((e = timed(K_DECODE, [&] { return launch_decode_write(d_arena_.as<uint8_t>(), (uint32_t)side_base, tb, db, n_dec, stream_); })) != cudaSuccess)
+            return fail(e, "decode_write", err);
+        arena_used_ = side_base + side;
+        out->side_bytes = side;
+    }
+
+    // ---- rows + grammar, then key order
+    DevBuf *rows[5] = {&d_meta_, &d_koff_, &d_klen_, &d_voff_, &d_vlen_};
+    for (int i = 0; i < 5; i++)
+        if ((e = rows[i]->reserve(((size_t)n_rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(rows)", err);
+    RowBuffers rb{d_meta_.as<uint32_t>(), d_koff_.as<uint32_t>(), d_klen_.as<uint32_t>(), d_voff_.as<uint32_t>(), d_vlen_.as<uint32_t>()};
+    if ((e = timed(K_ROWS, [&] { return launch_rows(raw, n, tb, n_tok, tiles, bb, db, n_dec, rb, n_rows, d_res, stream_); })) != cudaSuccess)
+        return fail(e, "rows", err);
+    if (n_rows && (e = timed(K_KEY_ORDER, [&] { return launch_key_order(raw, rb, n_rows, bb, d_res, stream_); })) != cudaSuccess)
+        return fail(e, "key_order", err);
+    rc = fetch_result(err);
+    if (rc) return rc;
+    const unsigned long long side = out->side_bytes;
+    *out = *h_res_.p;
+    out->side_bytes = side;
+    if (out->invalid) return TK_OK;
+
+    if ((e = d_off_.reserve(((size_t)n_rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(off)", err);
+    if ((e = d_scratch_.reserve(scan_scratch_words(n_rows) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    tape_.n_rows = n_rows;
+    tape_.arena_bytes = (uint32_t)arena_used_;
+    tape_.meta = rb.meta; tape_.koff = rb.koff; tape_.klen = rb.klen; tape_.voff = rb.voff; tape_.vlen = rb.vlen;
+    tape_.arena = d_arena_.as<uint8_t>();
+    tape_from_parse_ = true;
+    return TK_OK;
+}
+
+int Engine::parse(const char *raw, size_t n, Document *doc, std::string *err) {
+    int rc = upload_text(raw, n, err);
+    if (rc) return rc;
+    ParseResult r;
+    rc = parse_resident(n, &r, err);
+    if (rc) return rc;
+    if (r.invalid) {
+        // The GPU has established that json.Unmarshal fails; Go's wording of the FIRST error in
+        // byte order comes from re-reading the caller's text with the scanner restatement.
+        if (!syntax_error_text(std::string_view(raw, n), err))
+            *err = "internal: device and host validators disagree (device says invalid)";
+        return TK_ESYNTAX;
+    }
+    free_node(doc->root);
+    doc->root = nullptr;
+    doc->version = 1;
+    doc->host_valid = false;
+    staged_version_ = doc->version;  // the tape on the device IS this version of the document
+    if (r.not_canonical || r.n_rows == 1) {
+        // (a lone scalar root takes this path too: a nil root serialises as "{}", gabs.go:395-402)
+        // keys out of order or duplicated, or numbers whose text must be re-formatted: the ordered
+        // map insertions of the tree build put that right; Bytes() then flattens the tree
+        rc = materialise(doc, err);
+        if (rc) return rc;
+        staged_version_ = 0;
+    }
+    return TK_OK;
+}
+
+// Rows arrive in input order; a stack of open containers rebuilds the tree.  Map insertion keeps
+// the last duplicate (encoding/json objectInterface) and orders keys bytewise.
+int Engine::materialise(Document *doc, std::string *err) {
+    if (doc->host_valid) return TK_OK;
+    if (!tape_from_parse_ || !tape_.n_rows) { *err = "internal: no device tape to build the tree from"; return TK_EARG; }
+    const size_t n = tape_.n_rows;
+    cudaError_t e;
+    PinVec<uint32_t> *hrows[5] = {&h_meta_, &h_koff_, &h_klen_, &h_voff_, &h_vlen_};
+    const uint32_t *drows[5] = {tape_.meta, tape_.koff, tape_.klen, tape_.voff, tape_.vlen};
+    for (int i = 0; i < 5; i++) {
+        if (!hrows[i]->reserve(n)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+        if ((e = copy_d2h(hrows[i]->p, drows[i], n * 4)) != cudaSuccess) return fail(e, "copy rows", err);
+    }
+    if (!h_arena_.reserve(arena_used_ + 1)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+    if ((e = copy_d2h(h_arena_.p, d_arena_.p, arena_used_)) != cudaSuccess) return fail(e, "copy arena", err);
+    if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "copy tape", err);
+    for (int i = 0; i < 5; i++) hrows[i]->n = 0;  // scratch use only: the flattener starts from empty
+    h_arena_.n = 0;
+
+    const char *arena = reinterpret_cast<const char *>(h_arena_.p);
+    std::vector<Node *> stack;
+    Node *root = nullptr;
+    std::string range_err;
+    auto attach = [&](Node *v, uint32_t r) {
+        if (stack.empty()) { root = v; return; }
+        Node *top = stack.back();
+        if (top->kind == Kind::Map) {
+            auto &m = static_cast<MapNode *>(top)->m;
+            std::string_view key(arena + h_koff_.p[r], h_klen_.p[r]);
+            auto hint = m.end();
+            if (!m.empty() && std::prev(hint)->first < key) {
+                m.emplace_hint(hint, std::string(key), v);  // ascending input: O(1) append
+            } else {
+                auto it = m.find(key);
+                if (it != m.end()) { free_node(it->second); it->second = v; }
+                else m.emplace(std::string(key), v);
+            }
+        } else {
+            static_cast<ArrNode *>(top)->items.push_back(v);
+        }
+    };
+    for (uint32_t r = 0; r < n; r++) {
+        const uint32_t meta = h_meta_.p[r];
+        switch (meta & 15u) {
+        case ROW_STR: attach(new StrNode(std::string(arena + h_voff_.p[r], h_vlen_.p[r])), r); break;
+        case ROW_RAW: {
+            std::string_view t(arena + h_voff_.p[r], h_vlen_.p[r]);
+            Node *v = nullptr;
+            if (t == "true") v = new BoolNode(true);
+            else if (t == "false") v = new BoolNode(false);
+            else if (t == "null") v = nullptr;
+            else {
+                const std::string txt(t);
+                double d = strtod(txt.c_str(), nullptr);
+                if (std::isinf(d)) {
+                    if (range_err.empty()) range_err = "json: cannot unmarshal number " + txt + " into Go value of type float64";
+                    d = 0;
+                }
+                v = new NumNode(d);
+            }
+            attach(v, r);
+            break;
+        }
+        case ROW_OPEN_OBJ: { Node *v = new MapNode(); attach(v, r); stack.push_back(v); break; }
+        case ROW_OPEN_ARR: { Node *v = new ArrNode(); attach(v, r); stack.push_back(v); break; }
+        case ROW_EMPTY_OBJ: attach(new MapNode(), r); break;
+        case ROW_EMPTY_ARR: attach(new ArrNode(), r); break;
+        default: if (!stack.empty()) stack.pop_back(); break;  // closers
+        }
+    }
+    if (!range_err.empty()) {
+        free_node(root);
+        *err = range_err;
+        return TK_ESYNTAX;
+    }
+    free_node(doc->root);
+    doc->root = root;
+    doc->host_valid = true;
     return TK_OK;
 }
 

@@ -1,108 +1,129 @@
-// engine.hpp -- per-handle GPU context: pinned staging buffers, device buffers, the stream, and
-// the host flattener that turns the tree into the line tape (tape.hpp).
+// engine.hpp -- per-handle GPU context: the stream, device and pinned buffers (drawn from
+// process-wide pools so that creating a handle costs no cudaMalloc after warm-up), the GPU parse
+// driver (state.New), the host flattener (tree -> line tape) and the bulk operations.
 #pragma once
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstring>
 #include <string>
 #include <string_view>
 #include <vector>
 
 #include "doc.hpp"
+#include "parse.cuh"
 #include "tape.hpp"
 
 namespace tk {
 
-// grow-only pinned host array (cudaHostAlloc): host->device copies from it are true DMA
+// Process-wide caches of device and pinned-host blocks, keyed by power-of-two size.  Blocks go
+// back to the cache when a handle releases them and to the driver only at process exit.
+void *pool_alloc_device(size_t bytes, size_t *got);
+void pool_free_device(void *p, size_t bytes);
+void *pool_alloc_pinned(size_t bytes, size_t *got);
+void pool_free_pinned(void *p, size_t bytes);
+
+// grow-only pinned host array: host<->device copies from it are true DMA
 template <class T>
 struct PinVec {
     T *p = nullptr;
-    size_t n = 0, cap = 0;
+    size_t n = 0, cap = 0, cap_bytes = 0;
     bool failed = false;
-    ~PinVec() { if (p) cudaFreeHost(p); }
+    ~PinVec() { if (p) pool_free_pinned(p, cap_bytes); }
     PinVec() = default;
     PinVec(const PinVec &) = delete;
     PinVec &operator=(const PinVec &) = delete;
-    bool reserve(size_t want);
+    bool reserve(size_t want) {
+        if (want <= cap) return true;
+        size_t got = 0;
+        T *q = static_cast<T *>(pool_alloc_pinned(want * sizeof(T), &got));
+        if (!q) { failed = true; return false; }
+        if (n) memcpy(q, p, n * sizeof(T));
+        if (p) pool_free_pinned(p, cap_bytes);
+        p = q;
+        cap_bytes = got;
+        cap = got / sizeof(T);
+        return true;
+    }
     void clear() { n = 0; }
     inline void push(const T &v) {
-        if (n == cap && !reserve(n + 1)) return;
+        if (n == cap && !reserve(n ? n * 2 : 1024)) return;
         p[n++] = v;
     }
-    // appends len items and returns the index of the first
     inline size_t append(const T *src, size_t len) {
-        if (n + len > cap && !reserve(n + len)) return 0;
+        if (n + len > cap && !reserve((n + len) * 2)) return 0;
         if (len) memcpy(p + n, src, len * sizeof(T));
-        size_t at = n;
+        const size_t at = n;
         n += len;
         return at;
     }
 };
 
-// grow-only device array
+// grow-only device array; contents survive a grow only if keep_bytes says how many to carry over
 struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
-    ~DevBuf() { if (p) cudaFree(p); }
+    ~DevBuf() { if (p) pool_free_device(p, cap); }
     DevBuf() = default;
     DevBuf(const DevBuf &) = delete;
     DevBuf &operator=(const DevBuf &) = delete;
-    cudaError_t reserve(size_t bytes);
+    cudaError_t reserve(size_t bytes, size_t keep_bytes = 0, cudaStream_t s = nullptr);
     template <class T> T *as() const { return static_cast<T *>(p); }
 };
 
-enum KernelKind { K_ROW_OFFSETS = 0, K_EMIT = 1, K_PREFIX_MATCH = 2, K_COUNT = 3 };
+enum KernelKind {
+    K_ROW_OFFSETS = 0, K_EMIT, K_PREFIX_MATCH, K_SCAN_TOKENS, K_TOKEN_PREFIX, K_BRACKETS, K_SORT_BRACKETS, K_MATCH,
+    K_DECODE, K_ROWS, K_KEY_ORDER, K_COUNT
+};
 const char *kernel_name(int kind);
 
 class Engine {
 public:
-    // per-kernel device time, measured with events on the handle's stream while timing is on
-    void set_timing(bool on);
-    int collect_times(std::string *err);  // synchronises the stream
+    Engine() = default;
+    ~Engine();
+    Engine(const Engine &) = delete;
+    Engine &operator=(const Engine &) = delete;
+
+    int init(std::string *err);  // binds to the current device; TK_ECUDA + text if there is none
+    cudaStream_t stream() const { return stream_; }
+
+    // state.New: raw text -> line tape on the device.  On success either the tape is in output
+    // order (doc->host_valid stays false: the tree is built only if a point operation needs it)
+    // or the tree has been built from the tape on the host (keys out of order, duplicates, numbers
+    // that need re-formatting).  Invalid text: TK_ESYNTAX with Go's message.
+    int parse(const char *raw, size_t n, Document *doc, std::string *err);
+    // builds doc->root from the device tape (rows in input order); used by parse() and lazily by
+    // the point operations
+    int materialise(Document *doc, std::string *err);
+    // the device-only part of parse(), for bench.py: text already at the start of the arena
+    int parse_resident(size_t n, ParseResult *out, std::string *err);
+    int upload_text(const char *raw, size_t n, std::string *err);
+
+    int stage(const Document &doc, std::string *err);
+    int stage_tape(const Document &doc, std::string *err);
+    int stage_keys(const Document &doc, std::string *err);
+
+    int bytes(const Document &doc, bool to_host, const void **out, size_t *len, std::string *err);
+    int prefix_hits(const Document &doc, std::string_view prefix, bool to_host, std::vector<uint32_t> *hits, size_t *count,
+                    std::string *err);
+    const std::pair<const std::string, Node *> *module_entry(uint32_t i) const { return entries_[i]; }
+
+    // measurement hooks
+    void set_timing(bool on) { timing_ = on; }
+    int collect_times(std::string *err);
     double kernel_ms(int kind) const { return kernel_ms_[kind]; }
     unsigned long long timed_launches(int kind) const { return timed_launches_[kind]; }
     unsigned long long launches(int kind) const { return launches_[kind]; }
     unsigned long long h2d_bytes() const { return h2d_bytes_; }
     unsigned long long d2h_bytes() const { return d2h_bytes_; }
 
-    Engine() = default;
-    ~Engine();
-    Engine(const Engine &) = delete;
-    Engine &operator=(const Engine &) = delete;
-
-    // binds to the current device and creates the stream; TK_ECUDA + text if there is no device
-    int init(std::string *err);
-    cudaStream_t stream() const { return stream_; }
-
-    // flatten + upload whatever differs from doc.version: the line tape (for Bytes) and the
-    // packed module keys (for Clusters/Nodes) are staged independently
-    int stage(const Document &doc, std::string *err);
-    int stage_tape(const Document &doc, std::string *err);
-    int stage_keys(const Document &doc, std::string *err);
-
-    // State.Bytes(): text into pinned host memory (to_host) or left on the device
-    int bytes(const Document &doc, bool to_host, const void **out, size_t *len, std::string *err);
-
-    // prefix classification over the staged module keys; hit indices (unordered) into *hits
-    int prefix_hits(const Document &doc, std::string_view prefix, bool to_host, std::vector<uint32_t> *hits,
-                    size_t *count, std::string *err);
-
-    // module child i of the staged key index (valid while doc is unchanged)
-    const std::pair<const std::string, Node *> *module_entry(uint32_t i) const { return entries_[i]; }
-    bool module_is_object() const { return module_ok_; }
-
 private:
     int fail(cudaError_t e, const char *what, std::string *err);
     cudaError_t copy_h2d(void *dst, const void *src, size_t bytes);
     cudaError_t copy_d2h(void *dst, const void *src, size_t bytes);
     template <class F> cudaError_t timed(int kind, F &&launch);
-    struct Pending { int kind; cudaEvent_t a, b; };
-    std::vector<Pending> pending_;
-    std::vector<cudaEvent_t> free_events_;
-    bool timing_ = false;
-    double kernel_ms_[K_COUNT] = {0, 0, 0};
-    unsigned long long timed_launches_[K_COUNT] = {0, 0, 0}, launches_[K_COUNT] = {0, 0, 0};
-    unsigned long long h2d_bytes_ = 0, d2h_bytes_ = 0;
+    int fetch_result(std::string *err);
+
     void flatten(const Document &doc);
     void flatten_keys(const Document &doc);
     void flat_value(const Node *n, uint32_t depth, const std::string *key, bool comma, bool last);
@@ -114,23 +135,39 @@ private:
     uint64_t staged_version_ = 0, keys_version_ = 0;
     bool pin_failed_ = false;
 
+    struct Pending { int kind; cudaEvent_t a, b; };
+    std::vector<Pending> pending_;
+    std::vector<cudaEvent_t> free_events_;
+    bool timing_ = false;
+    double kernel_ms_[K_COUNT] = {};
+    unsigned long long timed_launches_[K_COUNT] = {}, launches_[K_COUNT] = {};
+    unsigned long long h2d_bytes_ = 0, d2h_bytes_ = 0;
+
     // host (pinned) tape + key index
     PinVec<uint32_t> h_meta_, h_koff_, h_klen_, h_voff_, h_vlen_, h_koffs_;
     PinVec<uint8_t> h_arena_, h_keys_;
     std::vector<const std::pair<const std::string, Node *> *> entries_;
-    bool module_ok_ = false;
 
-    // device mirrors and work buffers
+    // device tape, key index and work buffers
     DevBuf d_meta_, d_koff_, d_klen_, d_voff_, d_vlen_, d_arena_, d_koffs_, d_keys_;
     DevBuf d_off_, d_out_, d_scratch_, d_hits_, d_prefix_;
     TapeView tape_{};
     KeyIndexView keys_{};
+    size_t raw_len_ = 0;      // bytes of the parsed text at the start of d_arena_
+    size_t arena_used_ = 0;   // raw text (padded) + side arena
+    bool tape_from_parse_ = false;
+
+    // parse work buffers
+    DevBuf d_tok_pos_, d_tok_kind_, d_dec_bits_, d_tiles_, d_res_, d_bitzeros_;
+    DevBuf d_br_[9], d_flags_, d_zrank_, d_dec_tok_, d_dec_off_, d_dec_len_, d_dec_counts_, d_dec_offs_;
+    PinVec<ParseResult> h_res_;
+    PinVec<unsigned long long> h_words_;
 
     // results
     PinVec<uint8_t> h_out_;
     PinVec<uint32_t> h_hits_;
     PinVec<unsigned long long> h_total_;
-    uint64_t total_version_ = 0;  // version for which out_total_ is known
+    uint64_t total_version_ = 0;
     size_t out_total_ = 0;
 };
 

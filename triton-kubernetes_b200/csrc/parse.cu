@@ -1,0 +1,1063 @@
+// parse.cu -- sm_100a kernels of state.New (see parse.cuh for the pipeline).
+//
+// Reference semantics restated: Go encoding/json's scanner (validity), unquote (string
+// decoding: escapes, surrogate pairs, invalid UTF-8 -> U+FFFD) and objectInterface (member
+// order irrelevant, last duplicate wins -- the latter is resolved on the host when the GPU
+// reports that keys are not strictly ascending).
+#include "parse.cuh"
+
+#include <atomic>
+
+namespace tk {
+
+static std::atomic<unsigned long long> g_parse_launches{0};
+unsigned long long parse_launch_count() { return g_parse_launches.load(); }
+
+namespace {
+
+constexpr unsigned FULL = 0xffffffffu;
+typedef unsigned long long u64;
+
+// ---- status words for decoupled look-back -----------------------------------------------------
+constexpr u64 ST_AGG = 1ull << 62, ST_PREFIX = 2ull << 62, ST_MASK = (1ull << 62) - 1;
+
+__device__ __forceinline__ u64 ld_relaxed(const u64 *p) {
+    u64 v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed(u64 *p, u64 v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__device__ __forceinline__ u64 low_mask(int i) { return i >= 64 ? ~0ull : ((1ull << i) - 1); }
+
+// =================================================================================================
+// P1: bytes -> tokens
+// =================================================================================================
+
+constexpr uint32_t C_QUOTE = 1, C_BS = 2, C_WS = 4, C_ST = 8, C_CTRL = 16;
+
+__device__ __forceinline__ uint32_t byte_class(uint32_t c) {
+    uint32_t k = 0;
+    if (c == '"') k |= C_QUOTE;
+    if (c == '\\') k |= C_BS;
+    if (c == ' ' || c == '\t' || c == '\n' || c == '\r') k |= C_WS;
+    if (c == '{' || c == '}' || c == '[' || c == ']' || c == ':' || c == ',') k |= C_ST;
+    if (c < 0x20) k |= C_CTRL;
+    return k;
+}
+
+// 4 per-byte flag bits (bit j of every byte of x) gathered into a nibble
+__device__ __forceinline__ uint32_t gather4(uint32_t x, int j) {
+    return (((x >> j) & 0x01010101u) * 0x01020408u) >> 24;
+}
+
+// simdjson's branch-free escape finder: bits that are escaped by a preceding backslash run.
+// carry: in = first byte of this word is escaped; out = first byte of the next word is escaped.
+__device__ __forceinline__ u64 find_escaped(u64 backslash, u64 &carry) {
+    backslash &= ~carry;
+    const u64 follows_escape = (backslash << 1) | carry;
+    const u64 even_bits = 0x5555555555555555ull;
+    const u64 odd_sequence_starts = backslash & ~even_bits & ~follows_escape;
+    const u64 sum = odd_sequence_starts + backslash;
+    carry = sum < odd_sequence_starts ? 1ull : 0ull;
+    const u64 invert_mask = sum << 1;
+    return (even_bits ^ invert_mask) & follows_escape;
+}
+
+__device__ __forceinline__ u64 prefix_xor(u64 x) {
+    x ^= x << 1; x ^= x << 2; x ^= x << 4; x ^= x << 8; x ^= x << 16; x ^= x << 32;
+    return x;
+}
+
+// token mask of one 64-byte chunk, given the state before its first byte
+__device__ __forceinline__ u64 token_mask(u64 RQ, u64 SBx, u64 WS, u64 STm, bool s_in, bool prev_sc_if_out) {
+    const u64 SB = s_in ? ~SBx : SBx;    // state before each byte: 1 = inside a string
+    const u64 O = ~SB;
+    const u64 SC = O & ~(WS | STm | RQ);  // scalar characters
+    const u64 prev = (SC << 1) | ((!s_in && prev_sc_if_out) ? 1ull : 0ull);
+    return (STm & O) | RQ | (SC & ~prev) | (WS & O & prev);
+}
+
+__global__ void __launch_bounds__(P1_THREADS) scan_tokens_kernel(const uint8_t *__restrict__ raw, u64 n, TokenBuffers tb,
+                                                                u64 *scratch, ParseResult *res) {
+    __shared__ uint8_t s_lut[256];
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_warp_esc[P1_THREADS / 32];   // bit0 all_bs, bit1 trail
+    __shared__ uint32_t s_cin;                          // escape carry into the tile
+    __shared__ uint32_t s_warp_par[P1_THREADS / 32];
+    __shared__ u64 s_warp_cnt[P1_THREADS / 32];
+    __shared__ uint32_t s_v;                            // in-string state entering the tile
+    __shared__ u64 s_base;                              // tokens before the tile
+
+    s_lut[threadIdx.x] = (uint8_t)byte_class(threadIdx.x);
+    if (threadIdx.x == 0) s_tile = (uint32_t)atomicAdd(&scratch[0], 1ull);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t n_tiles = (uint32_t)((n + P1_TILE - 1) / P1_TILE);
+    u64 *statusA = scratch + 4;             // escape carry
+    u64 *statusB = scratch + 4 + n_tiles;   // quote parity + token counts
+    const u64 chunk = (u64)tile * P1_TILE + (u64)threadIdx.x * P1_BYTES_PER_THREAD;
+
+    // ---- load 64 bytes, build the class masks
+    u64 Q = 0, B = 0, WS = 0, STm = 0, CT = 0, NA = 0;
+    {
+        const uint4 *p = reinterpret_cast<const uint4 *>(raw + chunk);
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+            const uint4 q = __ldg(p + v);
+            const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint32_t x = w[k];
+                const uint32_t c4 = (uint32_t)s_lut[x & 0xff] | ((uint32_t)s_lut[(x >> 8) & 0xff] << 8) |
+                                    ((uint32_t)s_lut[(x >> 16) & 0xff] << 16) | ((uint32_t)s_lut[x >> 24] << 24);
+                const int sh = (v * 4 + k) * 4;
+                Q |= (u64)gather4(c4, 0) << sh;
+                B |= (u64)gather4(c4, 1) << sh;
+                WS |= (u64)gather4(c4, 2) << sh;
+                STm |= (u64)gather4(c4, 3) << sh;
+                CT |= (u64)gather4(c4, 4) << sh;
+                NA |= (u64)gather4(x, 7) << sh;
+            }
+        }
+    }
+
+    // ---- stage 1: escape carry.  A chunk's carry-out depends on its carry-in only if the chunk
+    //      is nothing but backslashes.
+    const bool all_bs = (B == ~0ull);
+    const uint32_t trail = all_bs ? 0u : ((uint32_t)__clzll((long long)~B) & 1u);  // odd trailing backslash run
+    const unsigned m_nb = __ballot_sync(FULL, !all_bs), m_tr = __ballot_sync(FULL, trail);
+    if (lane == 0) {
+        uint32_t e = 0;
+        if (m_nb == 0) e = 1;
+        else e = ((m_tr >> (31 - __clz(m_nb))) & 1u) << 1;
+        s_warp_esc[warp] = e;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // tile aggregate: published at once, so no tile ever waits on a chain
+        uint32_t agg = 1;  // all_bs so far
+        for (int i = 0; i < P1_THREADS / 32; i++)
+            if (!(s_warp_esc[i] & 1)) agg = s_warp_esc[i];
+        st_relaxed(statusA + tile, ST_AGG | agg);
+        uint32_t cin = 0;
+        for (int t = (int)tile - 1; t >= 0; t--) {
+            u64 s;
+            do { s = ld_relaxed(statusA + t); } while ((s >> 62) == 0);
+            if (!(s & 1)) { cin = (uint32_t)(s >> 1) & 1u; break; }
+        }
+        s_cin = cin;
+    }
+    __syncthreads();
+    u64 carry;
+    {
+        // carry into this thread's chunk: trail of the nearest earlier chunk that is not all backslashes
+        uint32_t c = s_cin;
+        for (uint32_t i = 0; i < warp; i++)
+            if (!(s_warp_esc[i] & 1)) c = (s_warp_esc[i] >> 1) & 1u;
+        const unsigned lower = m_nb & ((1u << lane) - 1);
+        if (lower) c = (m_tr >> (31 - __clz(lower))) & 1u;
+        carry = c;
+    }
+    const u64 E = find_escaped(B, carry);
+    const u64 RQ = Q & ~E;                       // real (unescaped) quotes
+    const u64 SBx = prefix_xor(RQ) ^ RQ;         // state before each byte, if the chunk started outside
+
+    // ---- stage 2: quote parity + token counts for both possible entry states
+    uint32_t pb = ' ';
+    if (chunk > 0) pb = __ldg(raw + chunk - 1);
+    const bool prev_sc_if_out = !(s_lut[pb] & (C_WS | C_ST | C_QUOTE));
+    const u64 T0 = token_mask(RQ, SBx, WS, STm, false, prev_sc_if_out);
+    const u64 T1 = token_mask(RQ, SBx, WS, STm, true, prev_sc_if_out);
+    const uint32_t par = (uint32_t)__popcll(RQ) & 1u;
+
+    // exclusive xor-scan of parity over the tile
+    uint32_t lp = par;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t v = __shfl_up_sync(FULL, lp, d);
+        if (lane >= (uint32_t)d) lp ^= v;
+    }
+    if (lane == 31) s_warp_par[warp] = lp;
+    __syncthreads();
+    uint32_t before = 0, tile_par = 0;
+    for (uint32_t i = 0; i < P1_THREADS / 32; i++) {
+        if (i < warp) before ^= s_warp_par[i];
+        tile_par ^= s_warp_par[i];
+    }
+    lp = lp ^ par ^ before;                      // parity of the quotes in earlier threads of the tile
+    // a: tokens if the tile is entered outside a string, b: if entered inside one
+    const uint32_t a = (uint32_t)__popcll(lp ? T1 : T0), b = (uint32_t)__popcll(lp ? T0 : T1);
+    u64 ab = (u64)a | ((u64)b << 32);
+    u64 incl = ab;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u64 v = __shfl_up_sync(FULL, incl, d);
+        if (lane >= (uint32_t)d) incl += v;
+    }
+    if (lane == 31) s_warp_cnt[warp] = incl;
+    __syncthreads();
+    u64 wbefore = 0, tile_cnt = 0;
+    for (uint32_t i = 0; i < P1_THREADS / 32; i++) {
+        if (i < warp) wbefore += s_warp_cnt[i];
+        tile_cnt += s_warp_cnt[i];
+    }
+    const u64 excl = wbefore + incl - ab;
+    const uint32_t cnt0 = (uint32_t)tile_cnt, cnt1 = (uint32_t)(tile_cnt >> 32);  // <= 16384 each
+
+    if (warp == 0) {
+        // look-back over (parity, cnt0, cnt1) aggregates; composition is ordered
+        uint32_t V = 0;
+        u64 base = 0;
+        if (tile > 0) {
+            if (lane == 0) st_relaxed(statusB + tile, ST_AGG | tile_par | ((u64)cnt0 << 1) | ((u64)cnt1 << 17));
+            uint32_t rp = 0, r0 = 0, r1 = 0;  // running aggregate of the tiles nearer than the window
+            int look = (int)tile - 1;
+            for (;;) {
+                const int idx = look - (int)lane;
+                u64 s = idx >= 0 ? ld_relaxed(statusB + idx) : ST_PREFIX;  // before tile 0: outside, 0 tokens
+                while (__any_sync(FULL, (s >> 62) == 0)) {
+                    if ((s >> 62) == 0) s = ld_relaxed(statusB + idx);
+                }
+                const unsigned pm = __ballot_sync(FULL, (s >> 62) == 2);
+                const int first = pm ? __ffs(pm) - 1 : 32;
+                // window aggregate of lanes [0, first): lane 0 is nearest.  Ordered reduction:
+                // (far then near): parity = pf ^ pn; cnt_s = cf_s + cn_(s ^ pf)
+                uint32_t p = 0, c0 = 0, c1 = 0;
+                if ((int)lane < first) { p = (uint32_t)s & 1u; c0 = (uint32_t)(s >> 1) & 0xffffu; c1 = (uint32_t)(s >> 17) & 0xffffu; }
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t fp = __shfl_down_sync(FULL, p, d), f0 = __shfl_down_sync(FULL, c0, d), f1 = __shfl_down_sync(FULL, c1, d);
+                    if (lane + d < 32) {
+                        const uint32_t n0 = f0 + (fp ? c1 : c0), n1 = f1 + (fp ? c0 : c1);
+                        p ^= fp; c0 = n0; c1 = n1;
+                    }
+                }
+                p = __shfl_sync(FULL, p, 0); c0 = __shfl_sync(FULL, c0, 0); c1 = __shfl_sync(FULL, c1, 0);
+                // fold: (window [farther]) then (running [nearer])
+                {
+                    const uint32_t n0 = c0 + (p ? r1 : r0), n1 = c1 + (p ? r0 : r1);
+                    rp ^= p; r0 = n0; r1 = n1;
+                }
+                if (pm) {
+                    const u64 pre = __shfl_sync(FULL, s, first);
+                    const uint32_t ps = (uint32_t)pre & 1u;
+                    const u64 pc = (pre & ST_MASK) >> 1;
+                    V = ps ^ rp;
+                    base = pc + (ps ? r1 : r0);
+                    break;
+                }
+                look -= 32;
+            }
+        }
+        const uint32_t s_out = V ^ tile_par;
+        const u64 total = base + (V ? cnt1 : cnt0);
+        if (lane == 0) {
+            st_relaxed(statusB + tile, ST_PREFIX | s_out | (total << 1));
+            s_v = V;
+            s_base = base;
+            if (tile + 1 == n_tiles) { res->n_tokens = total; res->end_in_string = s_out; }
+        }
+    }
+    __syncthreads();
+    const bool s_in = (s_v ^ lp) != 0;
+    const u64 T = s_in ? T1 : T0;
+    const u64 SB = s_in ? ~SBx : SBx;
+    u64 idx = s_base + (s_v ? (excl >> 32) : (excl & 0xffffffffull));
+
+    // ---- string body checks (scanner.go stateInString / stateInStringEsc*)
+    const u64 content = SB & ~RQ;
+    bool bad = (CT & content) != 0;
+    for (u64 e = E & content; e; e &= e - 1) {
+        const int i = __ffsll((long long)e) - 1;
+        const uint32_t c = __ldg(raw + chunk + i);
+        if (c == 'u') {
+            for (int k = 1; k <= 4; k++) {
+                const u64 at = chunk + i + k;
+                const uint32_t h = at < n ? __ldg(raw + at) : 0;
+                if (!((h >= '0' && h <= '9') || ((h | 0x20) >= 'a' && (h | 0x20) <= 'f'))) bad = true;
+            }
+        } else if (!(c == '"' || c == '\\' || c == '/' || c == 'b' || c == 'f' || c == 'n' || c == 'r' || c == 't')) {
+            bad = true;
+        }
+    }
+    if (bad) res->invalid = 1;
+
+    // ---- strings that need decoding: a backslash or a non-ASCII byte inside
+    for (u64 dmask = (B | NA) & content; dmask;) {
+        const int i = __ffsll((long long)dmask) - 1;
+        const u64 t = idx + (u64)__popcll(T & low_mask(i)) - 1;  // the string's opening-quote token
+        if (t < tb.cap) atomicOr(tb.decode_bits + (t >> 5), 1u << (t & 31));
+        res->n_decode = 1;
+        const u64 nq = RQ & ~low_mask(i + 1);
+        dmask = nq ? (dmask & ~low_mask(__ffsll((long long)nq) - 1)) : 0;
+    }
+
+    // ---- emit tokens in order
+    for (u64 t = T; t; t &= t - 1, idx++) {
+        const int i = __ffsll((long long)t) - 1;
+        if (idx >= tb.cap) continue;
+        const uint32_t c = __ldg(raw + chunk + i);
+        uint32_t k;
+        if ((RQ >> i) & 1) k = ((SB >> i) & 1) ? T_STR_CLOSE : T_STR_OPEN;
+        else if (c == '{') k = T_LBRACE;
+        else if (c == '}') k = T_RBRACE;
+        else if (c == '[') k = T_LBRACKET;
+        else if (c == ']') k = T_RBRACKET;
+        else if (c == ':') k = T_COLON;
+        else if (c == ',') k = T_COMMA;
+        else if ((WS >> i) & 1) k = T_SCALAR_END;
+        else k = T_SCALAR;
+        tb.pos[idx] = (uint32_t)(chunk + i);
+        tb.kind[idx] = (uint8_t)k;
+    }
+}
+
+// =================================================================================================
+// generic exclusive scan of u32 (single pass, decoupled look-back); total -> scratch[1]
+// =================================================================================================
+
+constexpr int SCAN_THREADS = 256, SCAN_ITEMS = 4, SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_u32_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
+                                                               uint32_t n, u64 *scratch) {
+    __shared__ uint32_t s_tile;
+    __shared__ u64 s_warp[SCAN_THREADS / 32];
+    __shared__ u64 s_prefix;
+    if (threadIdx.x == 0) s_tile = (uint32_t)atomicAdd(&scratch[0], 1ull);
+    __syncthreads();
+    const uint32_t tile = s_tile, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    uint32_t v[SCAN_ITEMS];
+    u64 sum = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = base + i < n ? in[base + i] : 0; sum += v[i]; }
+    u64 incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u64 x = __shfl_up_sync(FULL, incl, d);
+        if (lane >= (uint32_t)d) incl += x;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    u64 wbefore = 0, total = 0;
+    for (uint32_t i = 0; i < SCAN_THREADS / 32; i++) { if (i < warp) wbefore += s_warp[i]; total += s_warp[i]; }
+    u64 *status = scratch + 2;
+    if (warp == 0) {
+        u64 prefix = 0;
+        if (tile == 0) {
+            if (lane == 0) st_relaxed(status, ST_PREFIX | total);
+        } else {
+            if (lane == 0) st_relaxed(status + tile, ST_AGG | total);
+            int look = (int)tile - 1;
+            for (;;) {
+                const int idx = look - (int)lane;
+                u64 s = idx >= 0 ? ld_relaxed(status + idx) : ST_PREFIX;
+                while (__any_sync(FULL, (s >> 62) == 0)) { if ((s >> 62) == 0) s = ld_relaxed(status + idx); }
+                const unsigned pm = __ballot_sync(FULL, (s >> 62) == 2);
+                const int first = pm ? __ffs(pm) - 1 : 32;
+                u64 x = ((int)lane <= first) ? (s & ST_MASK) : 0ull;
+#pragma unroll
+                for (int d = 16; d; d >>= 1) x += __shfl_xor_sync(FULL, x, d);
+                prefix += x;
+                if (pm) break;
+                look -= 32;
+            }
+            if (lane == 0) st_relaxed(status + tile, ST_PREFIX | (prefix + total));
+        }
+        if (lane == 0) {
+            s_prefix = prefix;
+            if ((u64)(tile + 1) * SCAN_TILE >= n) scratch[1] = prefix + total;
+        }
+    }
+    __syncthreads();
+    u64 run = s_prefix + wbefore + incl - sum;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = (uint32_t)run; run += v[i]; }
+}
+
+inline size_t scan_scratch_words_u32(uint32_t n) { return 2 + (size_t)((n + SCAN_TILE - 1) / SCAN_TILE); }
+
+cudaError_t scan_u32(const uint32_t *in, uint32_t *out, uint32_t n, u64 *scratch, cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words_u32(n) * 8, s);
+    if (e != cudaSuccess) return e;
+    if (n == 0) return cudaSuccess;
+    scan_u32_kernel<<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(in, out, n, scratch);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+
+// =================================================================================================
+// P2a: per-tile prefixes over the token stream
+// =================================================================================================
+
+__device__ __forceinline__ bool is_opener(uint32_t k) { return k == T_LBRACE || k == T_LBRACKET; }
+__device__ __forceinline__ bool is_closer(uint32_t k) { return k == T_RBRACE || k == T_RBRACKET; }
+
+// does token i start a tape row?  (keys ride on their value's row; the closer of an empty
+// container rides on the opener's row)
+__device__ __forceinline__ bool emits_row(const uint8_t *kind, uint32_t i, uint32_t n_tok, uint32_t k) {
+    if (k == T_SCALAR) return true;
+    if (is_opener(k)) return true;
+    if (k == T_STR_OPEN) return !(i + 2 < n_tok && kind[i + 2] == T_COLON);
+    if (is_closer(k)) return !(i > 0 && is_opener(kind[i - 1]));
+    return false;
+}
+
+struct TokLocal { int depth_before; uint32_t rows_before, br_before; };
+
+// block-wide exclusive scan of (depth delta, row flag, bracket flag) for one 256-token tile
+__device__ __forceinline__ TokLocal tile_scan(int dd, uint32_t row, uint32_t br, int *tile_dd, uint32_t *tile_rows,
+                                              uint32_t *tile_br, int *tile_min_after, int *tile_max_after) {
+    __shared__ int s_d[TOK_TILE / 32];
+    __shared__ uint32_t s_r[TOK_TILE / 32], s_b[TOK_TILE / 32];
+    __shared__ int s_mn[TOK_TILE / 32], s_mx[TOK_TILE / 32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int d = dd;
+    uint32_t r = row, b = br;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int xd = __shfl_up_sync(FULL, d, o);
+        const uint32_t xr = __shfl_up_sync(FULL, r, o), xb = __shfl_up_sync(FULL, b, o);
+        if (lane >= (uint32_t)o) { d += xd; r += xr; b += xb; }
+    }
+    if (lane == 31) { s_d[warp] = d; s_r[warp] = r; s_b[warp] = b; }
+    __syncthreads();
+    int wd = 0, td = 0;
+    uint32_t wr = 0, wb = 0, tr = 0, tbk = 0;
+    for (uint32_t i = 0; i < TOK_TILE / 32; i++) {
+        if (i < warp) { wd += s_d[i]; wr += s_r[i]; wb += s_b[i]; }
+        td += s_d[i]; tr += s_r[i]; tbk += s_b[i];
+    }
+    const int after = wd + d;  // depth after this token, relative to the tile start
+    int mn = after, mx = after;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) { mn = min(mn, __shfl_xor_sync(FULL, mn, o)); mx = max(mx, __shfl_xor_sync(FULL, mx, o)); }
+    if (lane == 0) { s_mn[warp] = mn; s_mx[warp] = mx; }
+    __syncthreads();
+    mn = s_mn[0]; mx = s_mx[0];
+    for (uint32_t i = 1; i < TOK_TILE / 32; i++) { mn = min(mn, s_mn[i]); mx = max(mx, s_mx[i]); }
+    *tile_dd = td; *tile_rows = tr; *tile_br = tbk; *tile_min_after = mn; *tile_max_after = mx;
+    TokLocal t;
+    t.depth_before = after - dd;
+    t.rows_before = wr + r - row;
+    t.br_before = wb + b - br;
+    __syncthreads();
+    return t;
+}
+
+__global__ void __launch_bounds__(TOK_TILE) token_prefix_kernel(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, u64 *scratch,
+                                                               ParseResult *res) {
+    __shared__ uint32_t s_tile;
+    __shared__ int s_pd;
+    __shared__ uint32_t s_pr, s_pb;
+    if (threadIdx.x == 0) s_tile = (uint32_t)atomicAdd(&scratch[0], 1ull);
+    __syncthreads();
+    const uint32_t tile = s_tile, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t n_tiles = (n_tok + TOK_TILE - 1) / TOK_TILE;
+    const uint32_t i = tile * TOK_TILE + threadIdx.x;
+    uint32_t k = 0xff;
+    if (i < n_tok) k = tb.kind[i];
+    const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
+    const uint32_t row = (i < n_tok && emits_row(tb.kind, i, n_tok, k)) ? 1u : 0u;
+    const uint32_t br = (dd != 0) ? 1u : 0u;
+    int td, mn, mx;
+    uint32_t tr, tbk;
+    tile_scan(dd, row, br, &td, &tr, &tbk, &mn, &mx);
+
+    // two look-backs side by side: warp 0 carries (rows, brackets), warp 1 carries depth
+    u64 *statusX = scratch + 4, *statusY = scratch + 4 + n_tiles;
+    if (warp < 2) {
+        u64 *status = warp == 0 ? statusX : statusY;
+        // X: rows in bits 0-30, brackets in bits 31-61.  Y: depth + 2^40 (biased, stays positive)
+        const u64 mine = warp == 0 ? ((u64)tr | ((u64)tbk << 31)) : (u64)(long long)td;
+        u64 prefix = 0;
+        if (tile == 0) {
+            if (lane == 0) st_relaxed(status, ST_PREFIX | (warp == 0 ? mine : (u64)((long long)td + (1ll << 40))));
+        } else {
+            if (lane == 0) st_relaxed(status + tile, ST_AGG | (warp == 0 ? mine : (u64)((long long)td + (1ll << 40))));
+            int look = (int)tile - 1;
+            for (;;) {
+                const int idx = look - (int)lane;
+                u64 s = idx >= 0 ? ld_relaxed(status + idx) : (ST_PREFIX | (warp == 0 ? 0ull : (1ull << 40)));
+                while (__any_sync(FULL, (s >> 62) == 0)) { if ((s >> 62) == 0) s = ld_relaxed(status + idx); }
+                const unsigned pm = __ballot_sync(FULL, (s >> 62) == 2);
+                const int first = pm ? __ffs(pm) - 1 : 32;
+                u64 x = 0;
+                if ((int)lane <= first) x = warp == 0 ? (s & ST_MASK) : (u64)((long long)(s & ST_MASK) - (1ll << 40));
+#pragma unroll
+                for (int d = 16; d; d >>= 1) x += __shfl_xor_sync(FULL, x, d);
+                prefix += x;
+                if (pm) break;
+                look -= 32;
+            }
+            if (lane == 0) {
+                const u64 inc = prefix + mine;
+                st_relaxed(status + tile, ST_PREFIX | (warp == 0 ? inc : (u64)((long long)inc + (1ll << 40))));
+            }
+        }
+        if (lane == 0) {
+            if (warp == 0) { s_pr = (uint32_t)(prefix & 0x7fffffffu); s_pb = (uint32_t)((prefix >> 31) & 0x7fffffffu); }
+            else s_pd = (int)(long long)prefix;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        TilePrefix p;
+        p.depth = s_pd; p.rows = s_pr; p.brackets = s_pb; p.pad = 0;
+        tiles[tile] = p;
+        if (s_pd + mn < 0) res->invalid = 1;                                      // a closer with nothing open
+        const int hi = s_pd + mx;
+        if (hi > 10000) res->invalid = 1;                                         // exceeded max depth
+        if (hi > 0) atomicMax(&res->max_level, (unsigned)min(hi, 16383));
+        if (tile + 1 == n_tiles) {
+            res->n_rows = s_pr + tr;
+            res->n_brackets = s_pb + tbk;
+            res->final_depth = s_pd + td;
+            if (s_pd + td != 0) res->invalid = 1;
+        }
+    }
+}
+
+// =================================================================================================
+// P2b: bracket tokens with their level; identity permutation for the sort
+// =================================================================================================
+
+__global__ void __launch_bounds__(TOK_TILE) brackets_kernel(TokenBuffers tb, uint32_t n_tok, const TilePrefix *__restrict__ tiles,
+                                                           BracketBuffers bb, unsigned int *bit_zeros) {
+    __shared__ unsigned int s_zero[16];
+    if (threadIdx.x < 16) s_zero[threadIdx.x] = 0;
+    const uint32_t i = blockIdx.x * TOK_TILE + threadIdx.x;
+    uint32_t k = 0xff;
+    if (i < n_tok) k = tb.kind[i];
+    const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
+    int td, mn, mx;
+    uint32_t tr, tbk;
+    const TokLocal t = tile_scan(dd, 0, dd != 0, &td, &tr, &tbk, &mn, &mx);
+    const TilePrefix p = tiles[blockIdx.x];
+    if (dd != 0) {
+        const uint32_t b = p.brackets + t.br_before;
+        int level = p.depth + t.depth_before + (dd > 0 ? 1 : 0);
+        level = max(0, min(level, 16383));
+        bb.tok[b] = i;
+        bb.lvkind[b] = ((uint32_t)level << 8) | k;
+        bb.sort_a[b] = b;
+        bb.key_a[b] = (uint32_t)level;
+        bb.parent[b] = 0xffffffffu;
+        bb.match[b] = 0xffffffffu;
+        bb.row[b] = 0xffffffffu;
+        for (int bit = 0; bit < 14; bit++)
+            if (!((level >> bit) & 1)) atomicAdd(&s_zero[bit], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < 14 && s_zero[threadIdx.x]) atomicAdd(&bit_zeros[threadIdx.x], s_zero[threadIdx.x]);
+}
+
+// one stable split by bit `bit` of the key: zeros first
+__global__ void split_flags_kernel(const uint32_t *__restrict__ key, uint32_t n, int bit, uint32_t *__restrict__ flags) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = ((key[i] >> bit) & 1u) ? 0u : 1u;
+}
+__global__ void split_scatter_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict__ val, const uint32_t *__restrict__ zrank,
+                                     uint32_t n, int bit, const unsigned int *__restrict__ bit_zeros, uint32_t *__restrict__ key_out,
+                                     uint32_t *__restrict__ val_out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t n_zero = bit_zeros[bit];
+    const uint32_t k = key[i], z = zrank[i];
+    const uint32_t dst = ((k >> bit) & 1u) ? n_zero + (i - z) : z;
+    key_out[dst] = k;
+    val_out[dst] = val[i];
+}
+
+// =================================================================================================
+// P2d: pairs and enclosing openers from the level-sorted order
+// =================================================================================================
+
+__global__ void match_kernel(BracketBuffers bb, const uint32_t *__restrict__ sorted, const uint32_t *__restrict__ skey, uint32_t n_br,
+                             ParseResult *res) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_br) return;
+    // With depth never negative and ending at 0, every level's brackets alternate opener, closer:
+    // even positions of the sorted order are openers and j+1 is the partner.
+    if (j & 1) return;
+    const uint32_t o = sorted[j];
+    if (j + 1 >= n_br) { res->invalid = 1; return; }
+    const uint32_t c = sorted[j + 1];
+    const uint32_t ko = bb.lvkind[o] & 0xff, kc = bb.lvkind[c] & 0xff;
+    if (!((ko == T_LBRACE && kc == T_RBRACE) || (ko == T_LBRACKET && kc == T_RBRACKET)) || skey[j] != skey[j + 1] || c < o) {
+        res->invalid = 1;
+        return;
+    }
+    bb.match[o] = c;
+    bb.match[c] = o;
+    const uint32_t level = skey[j];
+    if (level <= 1) return;
+    // enclosing opener: the last bracket of level-1 that lies before o
+    uint32_t lo = 0, hi = n_br;  // first position whose (key, bracket) >= (level-1, o)
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        const uint32_t mk = skey[mid];
+        if (mk < level - 1 || (mk == level - 1 && sorted[mid] < o)) lo = mid + 1; else hi = mid;
+    }
+    if (lo == 0 || skey[lo - 1] != level - 1) { res->invalid = 1; return; }
+    bb.parent[o] = sorted[lo - 1];
+}
+
+// =================================================================================================
+// P3: strings that need decoding
+// =================================================================================================
+
+__global__ void decode_count_kernel(const uint32_t *__restrict__ bits, uint32_t n_words, uint32_t *__restrict__ counts) {
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w < n_words) counts[w] = __popc(bits[w]);
+}
+__global__ void decode_list_kernel(const uint32_t *__restrict__ bits, const uint32_t *__restrict__ offs, uint32_t n_words,
+                                   uint32_t *__restrict__ list) {
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= n_words) return;
+    uint32_t o = offs[w];
+    for (uint32_t b = bits[w]; b; b &= b - 1) list[o++] = w * 32 + (__ffs(b) - 1);
+}
+
+__device__ __forceinline__ uint32_t hex_val(uint32_t c) { return c <= '9' ? c - '0' : (c | 0x20) - 'a' + 10; }
+__device__ __forceinline__ bool is_hex(uint32_t c) { return (c >= '0' && c <= '9') || ((c | 0x20) >= 'a' && (c | 0x20) <= 'f'); }
+
+__device__ __forceinline__ uint32_t utf8_valid_len(const uint8_t *s, uint32_t i, uint32_t n) {
+    const uint32_t c = s[i];
+    uint32_t lo = 0x80, hi = 0xBF, len;
+    if (c >= 0xC2 && c <= 0xDF) len = 2;
+    else if (c >= 0xE0 && c <= 0xEF) { len = 3; if (c == 0xE0) lo = 0xA0; if (c == 0xED) hi = 0x9F; }
+    else if (c >= 0xF0 && c <= 0xF4) { len = 4; if (c == 0xF0) lo = 0x90; if (c == 0xF4) hi = 0x8F; }
+    else return 0;
+    if (i + len > n) return 0;
+    const uint32_t c1 = s[i + 1];
+    if (c1 < lo || c1 > hi) return 0;
+    for (uint32_t k = 2; k < len; k++)
+        if ((s[i + k] & 0xC0) != 0x80) return 0;
+    return len;
+}
+
+__device__ __forceinline__ uint32_t put_rune(uint8_t *dst, uint32_t w, uint32_t r) {
+    if (r > 0x10FFFF || (r >= 0xD800 && r <= 0xDFFF)) r = 0xFFFD;
+    if (r < 0x80) { if (dst) dst[w] = (uint8_t)r; return w + 1; }
+    if (r < 0x800) { if (dst) { dst[w] = 0xC0 | (r >> 6); dst[w + 1] = 0x80 | (r & 0x3F); } return w + 2; }
+    if (r < 0x10000) { if (dst) { dst[w] = 0xE0 | (r >> 12); dst[w + 1] = 0x80 | ((r >> 6) & 0x3F); dst[w + 2] = 0x80 | (r & 0x3F); } return w + 3; }
+    if (dst) { dst[w] = 0xF0 | (r >> 18); dst[w + 1] = 0x80 | ((r >> 12) & 0x3F); dst[w + 2] = 0x80 | ((r >> 6) & 0x3F); dst[w + 3] = 0x80 | (r & 0x3F); }
+    return w + 4;
+}
+
+// encoding/json unquote: s[0, n) is the text between the quotes.  dst == nullptr: length only.
+__device__ uint32_t unquote(const uint8_t *s, uint32_t n, uint8_t *dst) {
+    uint32_t w = 0;
+    for (uint32_t i = 0; i < n;) {
+        const uint32_t c = s[i];
+        if (c == '\\') {
+            if (i + 1 >= n) break;  // cannot happen in text that passed P1
+            const uint32_t e = s[i + 1];
+            i += 2;
+            uint32_t r;
+            switch (e) {
+            case 'b': r = '\b'; break;
+            case 'f': r = '\f'; break;
+            case 'n': r = '\n'; break;
+            case 'r': r = '\r'; break;
+            case 't': r = '\t'; break;
+            case 'u': {
+                if (i + 4 > n) { i = n; continue; }
+                r = (hex_val(s[i]) << 12) | (hex_val(s[i + 1]) << 8) | (hex_val(s[i + 2]) << 4) | hex_val(s[i + 3]);
+                i += 4;
+                if (r >= 0xD800 && r <= 0xDFFF) {
+                    bool pair = r < 0xDC00 && i + 6 <= n && s[i] == '\\' && s[i + 1] == 'u' && is_hex(s[i + 2]) && is_hex(s[i + 3]) &&
+                                is_hex(s[i + 4]) && is_hex(s[i + 5]);
+                    uint32_t r2 = 0;
+                    if (pair) {
+                        r2 = (hex_val(s[i + 2]) << 12) | (hex_val(s[i + 3]) << 8) | (hex_val(s[i + 4]) << 4) | hex_val(s[i + 5]);
+                        pair = r2 >= 0xDC00 && r2 <= 0xDFFF;
+                    }
+                    if (pair) { r = 0x10000 + ((r - 0xD800) << 10) + (r2 - 0xDC00); i += 6; }
+                    else r = 0xFFFD;
+                }
+                break;
+            }
+            default: r = e;  // " \ /
+            }
+            w = put_rune(dst, w, r);
+            continue;
+        }
+        if (c < 0x80) { if (dst) dst[w] = (uint8_t)c; w++; i++; continue; }
+        const uint32_t l = utf8_valid_len(s, i, n);
+        if (l == 0) { w = put_rune(dst, w, 0xFFFD); i++; continue; }
+        for (uint32_t k = 0; k < l; k++) { if (dst) dst[w + k] = s[i + k]; }
+        w += l;
+        i += l;
+    }
+    return w;
+}
+
+__global__ void decode_len_kernel(const uint8_t *__restrict__ raw, TokenBuffers tb, DecodeBuffers db, uint32_t n_dec) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_dec) return;
+    const uint32_t t = db.tok[j];
+    const uint32_t a = tb.pos[t] + 1, b = tb.pos[t + 1];  // the closing quote is the next token
+    db.len[j] = unquote(raw + a, b > a ? b - a : 0, nullptr);
+}
+__global__ void decode_write_kernel(uint8_t *arena, uint32_t side_base, TokenBuffers tb, DecodeBuffers db, uint32_t n_dec) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_dec) return;
+    const uint32_t t = db.tok[j];
+    const uint32_t a = tb.pos[t] + 1, b = tb.pos[t + 1];
+    const uint32_t o = db.off[j] + side_base;
+    db.off[j] = o;
+    unquote(arena + a, b > a ? b - a : 0, arena + o);
+}
+
+// =================================================================================================
+// P2e: grammar + rows
+// =================================================================================================
+
+// where string token t (an opening quote) keeps its bytes: in place, or decoded in the side arena
+__device__ __forceinline__ void string_ref(const TokenBuffers &tb, const DecodeBuffers &db, uint32_t n_dec, uint32_t t, uint32_t *off,
+                                           uint32_t *len) {
+    if ((tb.decode_bits[t >> 5] >> (t & 31)) & 1u) {
+        uint32_t lo = 0, hi = n_dec;
+        while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (db.tok[mid] < t) lo = mid + 1; else hi = mid; }
+        *off = db.off[lo];
+        *len = db.len[lo];
+        return;
+    }
+    *off = tb.pos[t] + 1;
+    *len = tb.pos[t + 1] - tb.pos[t] - 1;
+}
+
+// Go's number grammar (scanner.go state1/state0/stateDot/stateE...) and literals.  Returns 0 bad,
+// 1 valid, 2 valid and already in the text form floatEncoder would print.
+__device__ uint32_t check_scalar(const uint8_t *s, uint32_t n) {
+    if (n == 0) return 0;
+    if (s[0] == 't') return (n == 4 && s[1] == 'r' && s[2] == 'u' && s[3] == 'e') ? 2 : 0;
+    if (s[0] == 'f') return (n == 5 && s[1] == 'a' && s[2] == 'l' && s[3] == 's' && s[4] == 'e') ? 2 : 0;
+    if (s[0] == 'n') return (n == 4 && s[1] == 'u' && s[2] == 'l' && s[3] == 'l') ? 2 : 0;
+    uint32_t i = 0;
+    bool neg = false;
+    if (s[0] == '-') { neg = true; i = 1; if (n == 1) return 0; }
+    if (s[i] < '0' || s[i] > '9') return 0;
+    const uint32_t int_start = i;
+    if (s[i] == '0') i++;
+    else while (i < n && s[i] >= '0' && s[i] <= '9') i++;
+    const uint32_t int_digits = i - int_start;
+    bool plain = true;
+    if (i < n && s[i] == '.') {
+        plain = false;
+        i++;
+        if (i >= n || s[i] < '0' || s[i] > '9') return 0;
+        while (i < n && s[i] >= '0' && s[i] <= '9') i++;
+    }
+    if (i < n && (s[i] == 'e' || s[i] == 'E')) {
+        plain = false;
+        i++;
+        if (i < n && (s[i] == '+' || s[i] == '-')) i++;
+        if (i >= n || s[i] < '0' || s[i] > '9') return 0;
+        while (i < n && s[i] >= '0' && s[i] <= '9') i++;
+    }
+    if (i != n) return 0;
+    // integers of up to 15 digits are exact in float64 and print back unchanged ("-0" included)
+    (void)neg;
+    return (plain && int_digits <= 15) ? 2 : 1;
+}
+
+__device__ __forceinline__ uint32_t next_sig(const uint8_t *kind, uint32_t i, uint32_t n_tok) {  // kind of the next token, skipping scalar ends
+    i++;
+    if (i < n_tok && kind[i] == T_SCALAR_END) i++;
+    return i < n_tok ? kind[i] : 0xff;
+}
+
+enum { CT_TOP = 0, CT_OBJ = 1, CT_ARR = 2 };
+
+__global__ void __launch_bounds__(TOK_TILE) rows_kernel(const uint8_t *__restrict__ raw, u64 n, TokenBuffers tb, uint32_t n_tok,
+                                                       const TilePrefix *__restrict__ tiles, BracketBuffers bb, DecodeBuffers db,
+                                                       uint32_t n_dec, RowBuffers rb, uint32_t n_rows, ParseResult *res) {
+    const uint32_t i = blockIdx.x * TOK_TILE + threadIdx.x;
+    const uint8_t *kind = tb.kind;
+    uint32_t k = 0xff;
+    if (i < n_tok) k = kind[i];
+    const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
+    const uint32_t row = (i < n_tok && emits_row(kind, i, n_tok, k)) ? 1u : 0u;
+    int td, mn, mx;
+    uint32_t tr, tbk;
+    const TokLocal t = tile_scan(dd, row, dd != 0, &td, &tr, &tbk, &mn, &mx);
+    if (i >= n_tok || k == T_SCALAR_END || k == T_STR_CLOSE) return;
+    const TilePrefix p = tiles[blockIdx.x];
+    const int depth = p.depth + t.depth_before;
+    const uint32_t r = p.rows + t.rows_before;
+    const uint32_t brb = p.brackets + t.br_before;  // brackets before this token
+
+    // previous significant token
+    uint32_t pi = i, pk = 0xfe;  // 0xfe: start of input
+    if (i > 0) { pi = i - 1; if (kind[pi] == T_SCALAR_END) pi--; pk = kind[pi]; }
+
+    // container this token sits in (for a closer: the container it closes)
+    uint32_t ct = CT_TOP, my_b = 0xffffffffu;
+    if (dd != 0) my_b = brb;
+    if (is_closer(k)) {
+        const uint32_t o = bb.match[my_b];
+        if (o == 0xffffffffu) { res->invalid = 1; return; }
+        ct = (bb.lvkind[o] & 0xff) == T_LBRACE ? CT_OBJ : CT_ARR;
+    } else if (depth > 0) {
+        if (brb == 0) { res->invalid = 1; return; }
+        uint32_t b = brb - 1;  // nearest bracket before the token
+        if (is_closer(bb.lvkind[b] & 0xff)) {
+            const uint32_t o = bb.match[b];
+            b = o == 0xffffffffu ? 0xffffffffu : bb.parent[o];
+        }
+        if (b == 0xffffffffu) { res->invalid = 1; return; }
+        ct = (bb.lvkind[b] & 0xff) == T_LBRACE ? CT_OBJ : CT_ARR;
+    }
+
+    const bool prev_value_end = pk == T_STR_CLOSE || pk == T_SCALAR || is_closer(pk);
+    bool ok = true;
+    bool is_key = false;
+    switch (k) {
+    case T_COLON: {
+        // only after a key string inside an object
+        bool key_before = false;
+        if (pk == T_STR_CLOSE && pi >= 1) {
+            const uint32_t so = pi - 1;  // its opening quote
+            uint32_t qk = 0xfe;
+            if (so > 0) { uint32_t q = so - 1; if (kind[q] == T_SCALAR_END) q--; qk = kind[q]; }
+            key_before = qk == T_LBRACE || qk == T_COMMA;
+        }
+        ok = ct == CT_OBJ && key_before;
+        break;
+    }
+    case T_COMMA:
+        ok = ct != CT_TOP && prev_value_end;
+        if (ok && ct == CT_OBJ && pk == T_STR_CLOSE) {
+            // the string before the comma must have been a value, i.e. preceded by a colon
+            const uint32_t so = pi - 1;
+            uint32_t qk = 0xfe;
+            if (so > 0) { uint32_t q = so - 1; if (kind[q] == T_SCALAR_END) q--; qk = kind[q]; }
+            ok = qk == T_COLON;
+        }
+        break;
+    case T_RBRACE:
+        ok = ct == CT_OBJ && (pk == T_LBRACE || prev_value_end);
+        if (ok && pk == T_STR_CLOSE) {
+            const uint32_t so = pi - 1;
+            uint32_t qk = 0xfe;
+            if (so > 0) { uint32_t q = so - 1; if (kind[q] == T_SCALAR_END) q--; qk = kind[q]; }
+            ok = qk == T_COLON;
+        }
+        break;
+    case T_RBRACKET:
+        ok = ct == CT_ARR && (pk == T_LBRACKET || prev_value_end);
+        break;
+    default:  // value starts: string, scalar, opener
+        if (ct == CT_TOP) ok = pk == 0xfe;
+        else if (ct == CT_ARR) ok = pk == T_LBRACKET || pk == T_COMMA;
+        else {
+            if (k == T_STR_OPEN && (pk == T_LBRACE || pk == T_COMMA)) {
+                is_key = true;
+                ok = (i + 2 < n_tok) && kind[i + 2] == T_COLON;
+            } else {
+                ok = pk == T_COLON;
+            }
+        }
+        if (k == T_STR_OPEN && ok) ok = (i + 1 < n_tok) && kind[i + 1] == T_STR_CLOSE;
+        break;
+    }
+    if (!ok) { res->invalid = 1; return; }
+    if (k == T_COLON || k == T_COMMA || is_key) return;
+
+    // ---- this token owns a row?
+    if (is_closer(k)) {
+        if (is_opener(pk)) return;  // empty container: the opener's row says {} / []
+    }
+    if (!row || r >= n_rows) {
+        if (!row) { res->invalid = 1; }  // a value the row count did not foresee: token stream is inconsistent
+        return;
+    }
+    uint32_t meta = 0, koff = 0, klen = 0, voff = 0, vlen = 0;
+    uint32_t end_tok = i;  // last token of the value, to look for the comma after it
+    if (is_closer(k)) {
+        if (depth < 1) { res->invalid = 1; return; }
+        meta = (k == T_RBRACE ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR) | ((uint32_t)(depth - 1) << META_DEPTH_SHIFT);
+        koff = bb.match[my_b];  // P4 turns this into the opener's row
+    } else {
+        if (is_opener(k)) {
+            const bool empty = (i + 1 < n_tok) && is_closer(kind[i + 1]);
+            if (empty) { meta = (k == T_LBRACE ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR); end_tok = i + 1; }
+            else { meta = (k == T_LBRACE ? ROW_OPEN_OBJ : ROW_OPEN_ARR); bb.row[my_b] = r; }
+        } else if (k == T_STR_OPEN) {
+            meta = ROW_STR;
+            string_ref(tb, db, n_dec, i, &voff, &vlen);
+            end_tok = i + 1;
+        } else {  // scalar
+            meta = ROW_RAW;
+            voff = tb.pos[i];
+            const uint32_t e = (i + 1 < n_tok) ? tb.pos[i + 1] : (uint32_t)n;
+            vlen = e - voff;
+            const uint32_t c = check_scalar(raw + voff, vlen);
+            if (c == 0) { res->invalid = 1; return; }
+            if (c == 1) { res->need_host_numbers = 1; res->not_canonical = 1; }
+        }
+        meta |= (uint32_t)depth << META_DEPTH_SHIFT;
+        if (ct == CT_OBJ) {
+            // tokens before a value in an object: "key" : value -> i-3 open quote, i-2 close quote, i-1 colon
+            if (i < 3 || kind[i - 3] != T_STR_OPEN) { res->invalid = 1; return; }
+            const uint32_t ko = i - 3;
+            meta |= META_HAS_KEY;
+            string_ref(tb, db, n_dec, ko, &koff, &klen);
+            if (ko > 0) { uint32_t q = ko - 1; if (kind[q] == T_SCALAR_END) q--; if (kind[q] == T_COMMA) meta |= (1u << 7); }  // has an earlier sibling
+        }
+    }
+    // an opening row never carries the comma: it follows the closer and rides on the closing row
+    const uint32_t rk = meta & 15u;
+    if (rk != ROW_OPEN_OBJ && rk != ROW_OPEN_ARR && next_sig(kind, end_tok, n_tok) == T_COMMA) meta |= META_COMMA;
+    if (r + 1 == n_rows) meta |= META_LAST;
+    rb.meta[r] = meta; rb.koff[r] = koff; rb.klen[r] = klen; rb.voff[r] = voff; rb.vlen[r] = vlen;
+}
+
+// =================================================================================================
+// P4: are the keys of every object strictly ascending (bytewise, decoded)?
+// =================================================================================================
+
+__global__ void key_order_kernel(const uint8_t *__restrict__ arena, RowBuffers rb, uint32_t n_rows, BracketBuffers bb, ParseResult *res) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_rows) return;
+    uint32_t meta = rb.meta[r];
+    const uint32_t kind = meta & 15u;
+    if (kind == ROW_CLOSE_OBJ || kind == ROW_CLOSE_ARR) {
+        // nothing to compare; leave the opener's row in koff for the sibling lookup below
+        return;
+    }
+    if (!(meta & (1u << 7))) return;
+    rb.meta[r] = meta & ~(1u << 7);
+    if (r == 0) return;
+    uint32_t s = r - 1;  // previous sibling: the row before, or the opener of the container that just closed
+    const uint32_t sk = rb.meta[s] & 15u;
+    if (sk == ROW_CLOSE_OBJ || sk == ROW_CLOSE_ARR) {
+        const uint32_t ob = rb.koff[s];
+        if (ob == 0xffffffffu) { res->not_canonical = 1; return; }
+        s = bb.row[ob];
+        if (s == 0xffffffffu || s >= n_rows) { res->not_canonical = 1; return; }
+    }
+    const uint32_t ao = rb.koff[s], al = rb.klen[s], bo = rb.koff[r], bl = rb.klen[r];
+    const uint32_t m = min(al, bl);
+    int cmp = 0;
+    for (uint32_t i = 0; i < m; i++) {
+        const int x = arena[ao + i], y = arena[bo + i];
+        if (x != y) { cmp = x < y ? -1 : 1; break; }
+    }
+    if (cmp == 0) cmp = al < bl ? -1 : (al > bl ? 1 : 0);
+    if (cmp >= 0) res->not_canonical = 1;  // out of order or duplicated: the host re-orders
+}
+
+}  // namespace
+
+// =================================================================================================
+// launch wrappers
+// =================================================================================================
+
+cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, unsigned long long *scratch, ParseResult *res,
+                               cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(scratch, 0, p1_scratch_words(n) * 8, s);
+    if (e != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(res, 0, sizeof(ParseResult), s)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(tb.decode_bits, 0, ((size_t)tb.cap + 31) / 32 * 4 + 4, s)) != cudaSuccess) return e;
+    if (n == 0) return cudaSuccess;
+    scan_tokens_kernel<<<p1_tiles(n), P1_THREADS, 0, s>>>(raw, (u64)n, tb, scratch, res);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, unsigned long long *scratch, ParseResult *res,
+                                cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(scratch, 0, (4 + 2 * (size_t)tok_tiles(n_tok)) * 8, s);
+    if (e != cudaSuccess) return e;
+    token_prefix_kernel<<<tok_tiles(n_tok), TOK_TILE, 0, s>>>(tb, n_tok, tiles, scratch, res);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb, unsigned int *bit_zeros,
+                            cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(bit_zeros, 0, 16 * sizeof(unsigned int), s);
+    if (e != cudaSuccess) return e;
+    brackets_kernel<<<tok_tiles(n_tok), TOK_TILE, 0, s>>>(tb, n_tok, tiles, bb, bit_zeros);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sort_brackets(BracketBuffers bb, uint32_t n_br, uint32_t max_level, const unsigned int *bit_zeros,
+                                 uint32_t *flags, uint32_t *zrank, unsigned long long *scratch, bool *in_a, cudaStream_t s) {
+    *in_a = true;
+    if (n_br == 0) return cudaSuccess;
+    int bits = 0;
+    while ((1u << bits) <= max_level) bits++;
+    const uint32_t blocks = (n_br + 255) / 256;
+    for (int bit = 0; bit < bits; bit++) {
+        const uint32_t *key = *in_a ? bb.key_a : bb.key_b, *val = *in_a ? bb.sort_a : bb.sort_b;
+        uint32_t *key_o = *in_a ? bb.key_b : bb.key_a, *val_o = *in_a ? bb.sort_b : bb.sort_a;
+        split_flags_kernel<<<blocks, 256, 0, s>>>(key, n_br, bit, flags);
+        g_parse_launches++;
+        cudaError_t e = scan_u32(flags, zrank, n_br, scratch, s);
+        if (e != cudaSuccess) return e;
+        split_scatter_kernel<<<blocks, 256, 0, s>>>(key, val, zrank, n_br, bit, bit_zeros, key_o, val_o);
+        g_parse_launches++;
+        *in_a = !*in_a;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_match(BracketBuffers bb, const uint32_t *sorted, const uint32_t *sorted_key, uint32_t n_br, ParseResult *res,
+                         cudaStream_t s) {
+    if (n_br == 0) return cudaSuccess;
+    match_kernel<<<(n_br + 255) / 256, 256, 0, s>>>(bb, sorted, sorted_key, n_br, res);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_decode_list(TokenBuffers tb, uint32_t n_tok, DecodeBuffers db, uint32_t *counts, uint32_t *offs,
+                               unsigned long long *scratch, cudaStream_t s) {
+    const uint32_t words = (n_tok + 31) / 32;
+    decode_count_kernel<<<(words + 255) / 256, 256, 0, s>>>(tb.decode_bits, words, counts);
+    g_parse_launches++;
+    cudaError_t e = scan_u32(counts, offs, words, scratch, s);  // total -> scratch[1]
+    if (e != cudaSuccess) return e;
+    decode_list_kernel<<<(words + 255) / 256, 256, 0, s>>>(tb.decode_bits, offs, words, db.tok);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_decode_lengths(const uint8_t *raw, TokenBuffers tb, DecodeBuffers db, uint32_t n_dec, unsigned long long *scratch,
+                                  cudaStream_t s) {
+    decode_len_kernel<<<(n_dec + 127) / 128, 128, 0, s>>>(raw, tb, db, n_dec);
+    g_parse_launches++;
+    return scan_u32(db.len, db.off, n_dec, scratch, s);  // total decoded bytes -> scratch[1]
+}
+
+cudaError_t launch_decode_write(uint8_t *arena, uint32_t side_base, TokenBuffers tb, DecodeBuffers db, uint32_t n_dec, cudaStream_t s) {
+    decode_write_kernel<<<(n_dec + 127) / 128, 128, 0, s>>>(arena, side_base, tb, db, n_dec);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rows(const uint8_t *raw, size_t n, TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb,
+                        DecodeBuffers db, uint32_t n_dec, RowBuffers rb, uint32_t n_rows, ParseResult *res, cudaStream_t s) {
+    rows_kernel<<<tok_tiles(n_tok), TOK_TILE, 0, s>>>(raw, (u64)n, tb, n_tok, tiles, bb, db, n_dec, rb, n_rows, res);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_key_order(const uint8_t *arena, RowBuffers rb, uint32_t n_rows, BracketBuffers bb, ParseResult *res, cudaStream_t s) {
+    key_order_kernel<<<(n_rows + 255) / 256, 256, 0, s>>>(arena, rb, n_rows, bb, res);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+
+size_t parse_scan_scratch_words(uint32_t n) { return scan_scratch_words_u32(n); }
+
+}  // namespace tk

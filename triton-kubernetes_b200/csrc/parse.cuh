@@ -1,0 +1,121 @@
+// parse.cuh -- GPU side of state.New: raw JSON text -> validated line tape (tape.hpp), all on the
+// device.  Implemented in parse.cu; driven by Engine::parse (engine.cu).
+//
+// Pipeline (every kernel is byte/integer work bounded by HBM/L2 bandwidth):
+//   P1 scan_tokens     bytes -> token stream.  String/escape state is carried across the whole
+//                      text with a two-stage decoupled look-back (backslash-run carry, then
+//                      quote parity + token count); tokens (position, kind) are compacted in
+//                      order.  Also checks string bodies (control bytes, escape codes) and marks
+//                      strings that need decoding (escapes or non-ASCII bytes).
+//   P2a token_prefix   per 256-token tile: nesting depth, row count and bracket count before it
+//   P2b brackets       bracket tokens compacted with their nesting level
+//   P2c split sort     brackets stably sorted by level (one 1-bit split per level bit), which
+//                      puts every opener next to its closer
+//   P2d match          opener<->closer pairs, enclosing opener of every opener
+//   P3  decode         strings marked in P1 are unescaped / UTF-8-repaired into a side arena
+//   P2e rows           grammar check (Go's scanner rules restated as local token-pair rules) and
+//                      one tape row per value / closer, referring to the raw text in place
+//   P4  order          keys strictly ascending inside every object? (then the tape is already in
+//                      encoding/json's output order and Bytes() can run straight from it)
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "tape.hpp"
+
+namespace tk {
+
+enum TokKind : uint8_t {
+    T_LBRACE = 0, T_RBRACE = 1, T_LBRACKET = 2, T_RBRACKET = 3, T_COLON = 4, T_COMMA = 5,
+    T_STR_OPEN = 6, T_STR_CLOSE = 7, T_SCALAR = 8, T_SCALAR_END = 9
+};
+
+constexpr int P1_THREADS = 256;
+constexpr int P1_BYTES_PER_THREAD = 64;
+constexpr int P1_TILE = P1_THREADS * P1_BYTES_PER_THREAD;  // 16 KiB of text per block
+constexpr int TOK_TILE = 256;                              // tokens per block in the token passes
+
+// result block the kernels fill in device memory (one per parse)
+struct ParseResult {
+    unsigned long long n_tokens;
+    unsigned int invalid;         // != 0: json.Unmarshal would fail (the host phrases Go's message)
+    unsigned int end_in_string;   // text ended inside a string
+    unsigned int n_decode;        // strings that need decoding
+    unsigned int n_rows;
+    unsigned int n_brackets;
+    unsigned int max_level;
+    int final_depth;
+    unsigned int not_canonical;   // keys out of order / duplicated, or numbers not in canonical form
+    unsigned int need_host_numbers;
+    unsigned long long side_bytes; // decoded bytes written to the side arena
+};
+
+inline uint32_t p1_tiles(size_t n) { return (uint32_t)((n + P1_TILE - 1) / P1_TILE); }
+inline uint32_t tok_tiles(size_t t) { return (uint32_t)((t + TOK_TILE - 1) / TOK_TILE); }
+
+// scratch sizes in 64-bit words
+inline size_t p1_scratch_words(size_t n) { return 4 + 2 * (size_t)p1_tiles(n); }
+inline size_t tok_scratch_words(size_t t) { return 4 + (size_t)tok_tiles(t); }
+
+struct TokenBuffers {
+    uint32_t *pos;        // token byte offsets
+    uint8_t *kind;        // TokKind
+    uint32_t *decode_bits; // 1 bit per token: string needs decoding
+    uint32_t cap;         // capacity in tokens
+};
+
+struct TilePrefix { int depth; uint32_t rows; uint32_t brackets; uint32_t pad; };
+
+struct BracketBuffers {
+    uint32_t *tok;      // token index of bracket b (position order)
+    uint32_t *lvkind;   // level << 8 | TokKind
+    uint32_t *match;    // partner bracket
+    uint32_t *parent;   // enclosing opener (0xffffffff: none)
+    uint32_t *row;      // row index of an opener's row
+    uint32_t *sort_a, *sort_b;  // sorted permutations (ping-pong)
+    uint32_t *key_a, *key_b;    // level keys travelling with the permutation
+};
+
+struct DecodeBuffers {
+    uint32_t *tok;      // token index of the i-th string that needs decoding (ascending)
+    uint32_t *off;      // its offset in the arena after decoding
+    uint32_t *len;      // its decoded length
+};
+
+// raw must be readable (and space-padded) up to p1_tiles(n) * P1_TILE + 16 bytes.
+// scratch: p1_scratch_words(n) words.  Clears scratch, *res and tb.decode_bits on the stream first.
+cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, unsigned long long *scratch,
+                               ParseResult *res, cudaStream_t s);
+// scratch: 4 + 2 * tok_tiles(n_tok) words
+cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, unsigned long long *scratch,
+                                ParseResult *res, cudaStream_t s);
+// bit_zeros: 16 counters (device): brackets whose level has bit b clear
+cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb,
+                            unsigned int *bit_zeros, cudaStream_t s);
+// stable sort of the identity permutation (sort_a/key_a) by level; *in_a says which buffer holds
+// the result.  flags/zrank: n_br words each; scratch: parse_scan_scratch_words(n_br) words.
+cudaError_t launch_sort_brackets(BracketBuffers bb, uint32_t n_br, uint32_t max_level, const unsigned int *bit_zeros,
+                                 uint32_t *flags, uint32_t *zrank, unsigned long long *scratch, bool *in_a,
+                                 cudaStream_t s);
+cudaError_t launch_match(BracketBuffers bb, const uint32_t *sorted, const uint32_t *sorted_key, uint32_t n_br,
+                         ParseResult *res, cudaStream_t s);
+// strings that need decoding: ascending token list (count -> scratch[1]), then decoded lengths and
+// their exclusive sum (total -> scratch[1]), then the bytes at arena[side_base + off]
+cudaError_t launch_decode_list(TokenBuffers tb, uint32_t n_tok, DecodeBuffers db, uint32_t *counts, uint32_t *offs,
+                               unsigned long long *scratch, cudaStream_t s);
+cudaError_t launch_decode_lengths(const uint8_t *raw, TokenBuffers tb, DecodeBuffers db, uint32_t n_dec,
+                                  unsigned long long *scratch, cudaStream_t s);
+cudaError_t launch_decode_write(uint8_t *arena, uint32_t side_base, TokenBuffers tb, DecodeBuffers db, uint32_t n_dec,
+                                cudaStream_t s);
+// rows: the tape arrays are written in input order; arena = raw text (+ side arena)
+struct RowBuffers { uint32_t *meta, *koff, *klen, *voff, *vlen; };
+cudaError_t launch_rows(const uint8_t *raw, size_t n, TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles,
+                        BracketBuffers bb, DecodeBuffers db, uint32_t n_dec, RowBuffers rb, uint32_t n_rows,
+                        ParseResult *res, cudaStream_t s);
+cudaError_t launch_key_order(const uint8_t *arena, RowBuffers rb, uint32_t n_rows, BracketBuffers bb, ParseResult *res,
+                             cudaStream_t s);
+size_t parse_scan_scratch_words(uint32_t n);
+unsigned long long parse_launch_count();
+
+}  // namespace tk

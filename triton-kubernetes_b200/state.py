@@ -27,7 +27,7 @@ SYMBOLS = [
     "tk_state_add_node", "tk_state_delete", "tk_state_bytes", "tk_state_clusters", "tk_state_nodes",
     "tk_new_hostnames", "tk_state_stage", "tk_state_bytes_device", "tk_state_prefix_count_device",
     "tk_state_stream", "tk_kernel_launches", "tk_version", "tk_state_timing", "tk_state_kernel_stats",
-    "tk_state_copy_stats", "tk_row_offsets_noalloc",
+    "tk_state_copy_stats", "tk_row_offsets_noalloc", "tk_state_host_tree_built",
 ]
 
 _lib = None
@@ -72,6 +72,7 @@ def lib():
                                         POINTER(c_ulonglong)]
     L.tk_state_copy_stats.argtypes = [P, POINTER(c_ulonglong), POINTER(c_ulonglong)]
     L.tk_row_offsets_noalloc.argtypes = [P, P, P, P, P, P, ctypes.c_uint32, ctypes.c_uint32, P, P, c_char_p, c_size_t]
+    L.tk_state_host_tree_built.argtypes = [P]
     L.tk_kernel_launches.restype = c_ulonglong
     L.tk_version.restype = c_char_p
     _lib = L
@@ -233,6 +234,10 @@ class State:
         c = c_size_t()
         self._check(lib().tk_state_prefix_count_device(self._h, p, len(p), byref(c) if want_count else None))
         return c.value
+
+    @property
+    def host_tree_built(self) -> bool:
+        return bool(lib().tk_state_host_tree_built(self._h))
 
     def Timing(self, on: bool):
         self._check(lib().tk_state_timing(self._h, 1 if on else 0))
