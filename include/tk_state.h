@@ -23,8 +23,10 @@
  *     was a map (TK_VALUE_MAP: keys sorted on output, visible to Get/Clusters/Nodes) or a
  *     struct (TK_VALUE_RECORD: member order kept as given, opaque until the document is
  *     re-parsed -- SURVEY.md 8a note 1, create/cluster.go:146-152).
- *   - The bulk operations (New, Bytes, Clusters, Nodes) run on the GPU; there is no CPU
- *     fallback.  Without a usable CUDA device they fail with TK_ECUDA and say so.
+ *   - The bulk passes run on the GPU and have no CPU fallback: parsing a document (New),
+ *     serialising it (Bytes) and, for a document that New left on the device, classifying the
+ *     children of "module" (Clusters, Nodes).  Without a usable CUDA device they fail with
+ *     TK_ECUDA and say so.
  */
 #ifndef TK_STATE_H
 #define TK_STATE_H
@@ -112,7 +114,10 @@ TK_API int tk_state_bytes(tk_state *s, const char **out, size_t *out_len);
  * The Go map[string]string result comes back as *count pairs packed into *blob as
  *   { uint32 name_len; name bytes; uint32 key_len; key bytes }   (little endian)
  * sorted by name (Go's map order is random; on duplicate names the bytewise greatest module
- * key is kept, where Go keeps a random one).  The module keys are classified on the GPU. */
+ * key is kept, where Go keeps a random one).  For a document that lives on the device the
+ * children of "module" are classified and packed by one GPU pass per document version and each
+ * call is a binary search over that index; once the host tree exists (after a point operation)
+ * the same range lookup runs on the tree's ordered map. */
 TK_API int tk_state_clusters(tk_state *s, const uint8_t **blob, size_t *blob_len, size_t *count);
 TK_API int tk_state_nodes(tk_state *s, const char *cluster_key, size_t cluster_key_len, const uint8_t **blob,
                           size_t *blob_len, size_t *count);
@@ -124,6 +129,10 @@ TK_API int tk_new_hostnames(const char *const *existing, const size_t *existing_
                             size_t node_name_len, long long nodes_to_add, const char **out, size_t *out_len);
 
 /* ---- device-resident variants: what bench.py times with inputs already in HBM ------------ */
+
+/* state.New on text that is already in device memory (dev_raw: device pointer, borrowed for the
+ * call).  Same result as tk_state_new; no host->device copy of the text. */
+TK_API int tk_state_new_device(const char *name, size_t name_len, const void *dev_raw, size_t raw_len, tk_state **out);
 
 /* Makes the device copy of the document current (flatten + host->device copy if the document
  * changed since the last staging).  Bytes/Clusters/Nodes call this implicitly. */
@@ -142,6 +151,8 @@ TK_API int tk_state_prefix_count_device(tk_state *s, const char *prefix, size_t 
  * and reports, for kernel number `kind` (0 .. until it returns TK_EARG), its name, the summed
  * device time of the launches made while timing was on, how many those were, and all launches. */
 TK_API int tk_state_timing(tk_state *s, int enable);
+/* Handles created after this call start with timing on (or off): lets state.New itself be timed. */
+TK_API int tk_set_default_timing(int enable);
 TK_API int tk_state_kernel_stats(tk_state *s, int kind, const char **name, double *ms,
                                  unsigned long long *timed_launches, unsigned long long *launches);
 /* Bytes this handle has copied host->device and device->host so far. */

@@ -33,9 +33,9 @@ def test_new_keeps_canonical_documents_on_the_device(tk, oracle):
     """Text already in encoding/json's order is serialised straight from the tape the GPU parser built;
     anything that needs re-ordering, de-duplication or number re-formatting builds the host tree."""
     canon = oracle.New("x", synth.document(5, 4)).Bytes()
-    for raw, resident in [(canon, True), (b'{"a":{"b":1,"c":[true,null,"x"]},"b":"\u00e9\n"}', True),
+    for raw, resident in [(canon, True), (rb'{"a":{"b":1,"c":[true,null,"x"]},"b":"\u00e9\n"}', True),
                           (b'{"b":1,"a":2}', False), (b'{"a":1,"a":2}', False), (b'{"a":1.50}', False),
-                          (b'{"a":{"y":1,"x":2}}', False), (b'[{"k":1},{"k":1}]', True), (b'{"a":"x","a\u0000":"y"}', True)]:
+                          (b'{"a":{"y":1,"x":2}}', False), (b'[{"k":1},{"k":1}]', True), (rb'{"a":"x","a\u0000":"y"}', True)]:
         s = tk.New("x", raw)
         assert s.host_tree_built == (not resident), raw[:40]
         assert s.Bytes() == oracle.New("x", raw).Bytes()

@@ -45,14 +45,24 @@ unsigned long long tk_kernel_launches(void) { return kernel_launch_count() + par
 
 const char *tk_last_error(tk_state *s) { return s ? s->err.c_str() : g_err.c_str(); }
 
+static int new_from(const char *name, size_t name_len, const char *raw, size_t raw_len, bool on_device, tk_state **out);
+
 int tk_state_new(const char *name, size_t name_len, const char *raw, size_t raw_len, tk_state **out) {
+    return new_from(name, name_len, raw, raw_len, false, out);
+}
+int tk_state_new_device(const char *name, size_t name_len, const void *dev_raw, size_t raw_len, tk_state **out) {
+    return new_from(name, name_len, static_cast<const char *>(dev_raw), raw_len, true, out);
+}
+int tk_set_default_timing(int enable) { set_default_timing(enable != 0); return TK_OK; }
+
+static int new_from(const char *name, size_t name_len, const char *raw, size_t raw_len, bool on_device, tk_state **out) {
     if (!out) return set_err(nullptr, TK_EARG, "tk_state_new: out is NULL");
     *out = nullptr;
     auto *s = new tk_state();
     s->name.assign(sv(name, name_len));
     std::string err;
     // whole documents are parsed on the GPU; without a device this fails, loudly
-    int rc = s->eng.parse(raw, raw_len, &s->doc, &err);
+    int rc = s->eng.parse(raw, raw_len, on_device, &s->doc, &err);
     if (rc) { delete s; return set_err(nullptr, rc, err); }
     *out = s;
     return TK_OK;
@@ -212,34 +222,40 @@ void *tk_state_stream(tk_state *s) { return s ? (void *)s->eng.stream() : nullpt
 static int children_by_prefix(tk_state *s, std::string_view prefix, std::string_view field, const uint8_t **blob,
                               size_t *blob_len, size_t *count) {
     std::string err;
-    if (int rc = ensure_host(s)) return rc;
-    if (!s->doc.module_children()) return set_err(s, TK_ENOTOBJ, kErrNotObj);
-    std::vector<uint32_t> hits;
-    int rc = s->eng.prefix_hits(s->doc, prefix, true, &hits, nullptr, &err);
-    if (rc) return set_err(s, rc, err);
-    struct Pair { std::string_view name, key; };
-    std::vector<Pair> pairs;
-    pairs.reserve(hits.size());
-    for (uint32_t h : hits) {
-        auto *e = s->eng.module_entry(h);
-        const Node *child = e->second;
-        if (!child || child->kind != Kind::Map) continue;  // records (Go structs) are opaque
-        auto &m = static_cast<const MapNode *>(child)->m;
-        auto it = m.find(field);
-        if (it == m.end() || !it->second || it->second->kind != Kind::Str) continue;
-        pairs.push_back({static_cast<const StrNode *>(it->second)->s, e->first});
+    std::vector<std::pair<std::string_view, std::string_view>> pairs;  // (field value, module key)
+    if (!s->doc.host_valid && s->eng.device_resident(s->doc)) {
+        // the document lives on the device: one GPU pass per version builds the packed index
+        bool module_ok = false;
+        int rc = s->eng.index_lookup(s->doc, prefix, field == "hostname", &module_ok, &pairs, &err);
+        if (rc) return set_err(s, rc, err);
+        if (!module_ok) return set_err(s, TK_ENOTOBJ, kErrNotObj);
+    } else {
+        if (int rc = ensure_host(s)) return rc;
+        const MapNode *mod = s->doc.module_children();
+        if (!mod) return set_err(s, TK_ENOTOBJ, kErrNotObj);
+        // the tree keeps keys in bytewise order: keys with the prefix form one contiguous run
+        for (auto it = mod->m.lower_bound(prefix); it != mod->m.end(); ++it) {
+            const std::string &key = it->first;
+            if (key.size() < prefix.size() || key.compare(0, prefix.size(), prefix) != 0) break;
+            const Node *child = it->second;
+            if (!child || child->kind != Kind::Map) continue;  // records (Go structs) are opaque
+            auto &m = static_cast<const MapNode *>(child)->m;
+            auto f = m.find(field);
+            if (f == m.end() || !f->second || f->second->kind != Kind::Str) continue;
+            pairs.emplace_back(static_cast<const StrNode *>(f->second)->s, key);
+        }
     }
-    std::sort(pairs.begin(), pairs.end(), [](const Pair &a, const Pair &b) { return a.name != b.name ? a.name < b.name : a.key < b.key; });
+    std::sort(pairs.begin(), pairs.end());
     s->blob.clear();
     size_t kept = 0;
     for (size_t i = 0; i < pairs.size(); i++) {
-        if (i + 1 < pairs.size() && pairs[i + 1].name == pairs[i].name) continue;  // greatest key wins
-        uint32_t l = (uint32_t)pairs[i].name.size();
+        if (i + 1 < pairs.size() && pairs[i + 1].first == pairs[i].first) continue;  // greatest key wins
+        uint32_t l = (uint32_t)pairs[i].first.size();
         s->blob.append(reinterpret_cast<const char *>(&l), 4);
-        s->blob.append(pairs[i].name);
-        l = (uint32_t)pairs[i].key.size();
+        s->blob.append(pairs[i].first);
+        l = (uint32_t)pairs[i].second.size();
         s->blob.append(reinterpret_cast<const char *>(&l), 4);
-        s->blob.append(pairs[i].key);
+        s->blob.append(pairs[i].second);
         kept++;
     }
     *blob = reinterpret_cast<const uint8_t *>(s->blob.data());

@@ -2,6 +2,7 @@
 #include "engine.hpp"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -90,10 +91,13 @@ cudaError_t DevBuf::reserve(size_t bytes, size_t keep_bytes, cudaStream_t s) {
     return cudaSuccess;
 }
 
+static std::atomic<bool> g_default_timing{false};
+void set_default_timing(bool on) { g_default_timing = on; }
+
 const char *kernel_name(int kind) {
     static const char *const names[K_COUNT] = {"row_offsets_kernel", "emit_kernel", "prefix_match_kernel", "scan_tokens_kernel",
                                                "token_prefix_kernel", "brackets_kernel", "sort_brackets (split passes)", "match_kernel",
-                                               "decode kernels", "rows_kernel", "key_order_kernel"};
+                                               "decode kernels", "rows_kernel", "key_order_kernel", "module index kernels"};
     return kind >= 0 && kind < K_COUNT ? names[kind] : "";
 }
 
@@ -175,6 +179,7 @@ int Engine::init(std::string *err) {
     if (e != cudaSuccess) return fail(e, "cudaGetDevice", err);
     e = cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking);
     if (e != cudaSuccess) return fail(e, "cudaStreamCreate", err);
+    timing_ = g_default_timing.load();
     ready_ = true;
     return TK_OK;
 }
@@ -428,6 +433,22 @@ int Engine::upload_text(const char *raw, size_t n, std::string *err) {
     return TK_OK;
 }
 
+// the same for text that is already in device memory
+int Engine::upload_text_device(const void *dev_raw, size_t n, std::string *err) {
+    int rc = init(err);
+    if (rc) return rc;
+    if (n >= 0xfff00000ull) { *err = "document too large: the text must stay below 4 GiB"; return TK_ELIMIT; }
+    const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 32;
+    cudaError_t e;
+    if ((e = d_arena_.reserve(padded)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
+    if (n && (e = cudaMemcpyAsync(d_arena_.p, dev_raw, n, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return fail(e, "copy text", err);
+    if ((e = cudaMemsetAsync(d_arena_.as<uint8_t>() + n, ' ', padded - n, stream_)) != cudaSuccess) return fail(e, "pad text", err);
+    raw_len_ = n;
+    arena_used_ = padded;
+    staged_version_ = keys_version_ = total_version_ = 0;
+    return TK_OK;
+}
+
 // Every kernel of the pipeline, on the text already resident at the start of the arena.  Leaves
 // the tape (rows in input order) on the device and the verdict in *out.  Host synchronisations:
 // after P1 (token count sizes the later buffers), after P2a (row / bracket counts), after the
@@ -558,18 +579,27 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     tape_.meta = rb.meta; tape_.koff = rb.koff; tape_.klen = rb.klen; tape_.voff = rb.voff; tape_.vlen = rb.vlen;
     tape_.arena = d_arena_.as<uint8_t>();
     tape_from_parse_ = true;
+    bb_ = bb;
+    index_version_ = 0;
     return TK_OK;
 }
 
-int Engine::parse(const char *raw, size_t n, Document *doc, std::string *err) {
-    int rc = upload_text(raw, n, err);
+int Engine::parse(const char *raw, size_t n, bool raw_on_device, Document *doc, std::string *err) {
+    int rc = raw_on_device ? upload_text_device(raw, n, err) : upload_text(raw, n, err);
     if (rc) return rc;
     ParseResult r;
     rc = parse_resident(n, &r, err);
     if (rc) return rc;
     if (r.invalid) {
         // The GPU has established that json.Unmarshal fails; Go's wording of the FIRST error in
-        // byte order comes from re-reading the caller's text with the scanner restatement.
+        // byte order comes from re-reading the text with the scanner restatement.
+        std::string copy;
+        if (raw_on_device) {
+            copy.resize(n);
+            cudaError_t e = cudaMemcpy(copy.data(), d_arena_.p, n, cudaMemcpyDeviceToHost);
+            if (e != cudaSuccess) return fail(e, "copy text back", err);
+            raw = copy.data();
+        }
         if (!syntax_error_text(std::string_view(raw, n), err))
             *err = "internal: device and host validators disagree (device says invalid)";
         return TK_ESYNTAX;
@@ -668,6 +698,91 @@ int Engine::materialise(Document *doc, std::string *err) {
     free_node(doc->root);
     doc->root = root;
     doc->host_valid = true;
+    return TK_OK;
+}
+
+}  // namespace tk
+
+// ============================================================================ module index
+
+namespace tk {
+
+int Engine::build_index(const Document &doc, std::string *err) {
+    if (index_version_ == doc.version) return TK_OK;
+    if (!device_resident(doc)) { *err = "internal: module index needs the parser's tape"; return TK_EARG; }
+    cudaError_t e;
+    const size_t n = tape_.n_rows;
+    if ((e = d_minfo_.reserve(sizeof(ModuleInfo) + 16)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_cflags_.reserve((n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_crank_.reserve((n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_crefs_.reserve((n + 1) * sizeof(ChildRef))) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_csizes_.reserve((n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_coffs_.reserve((n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_centries_.reserve((n + 1) * sizeof(ChildEntry))) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_cpacked_.reserve(arena_used_ + 64)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_scratch_.reserve(parse_scan_scratch_words((uint32_t)n) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    if (!h_minfo_.reserve(1) || !h_words_.reserve(4)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+    ModuleInfo *info = d_minfo_.as<ModuleInfo>();
+    unsigned long long *scratch = d_scratch_.as<unsigned long long>();
+    uint32_t *flags = d_cflags_.as<uint32_t>(), *rank = d_crank_.as<uint32_t>(), *sizes = d_csizes_.as<uint32_t>(), *offs = d_coffs_.as<uint32_t>();
+    e = timed(K_MODULE_INDEX, [&] {
+        cudaError_t x;
+        if ((x = launch_find_module(tape_, bb_.match, bb_.row, info, stream_)) != cudaSuccess) return x;
+        if ((x = launch_child_flags(tape_, info, flags, stream_)) != cudaSuccess) return x;
+        if ((x = scan_u32(flags, rank, (uint32_t)n, scratch, stream_)) != cudaSuccess) return x;
+        if ((x = cudaMemcpyAsync(&info->n_children, scratch + 1, 4, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return x;
+        if ((x = cudaMemsetAsync(sizes, 0, (n + 1) * 4, stream_)) != cudaSuccess) return x;
+        if ((x = launch_child_entries(tape_, flags, rank, bb_.match, bb_.row, d_crefs_.as<ChildRef>(), sizes, stream_)) != cudaSuccess) return x;
+        return scan_u32(sizes, offs, (uint32_t)n, scratch, stream_);
+    });
+    if (e != cudaSuccess) return fail(e, "module index", err);
+    if ((e = copy_d2h(h_minfo_.p, info, sizeof(ModuleInfo))) != cudaSuccess) return fail(e, "copy module info", err);
+    if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy index size", err);
+    if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
+    const ModuleInfo mi = *h_minfo_.p;
+    const size_t bytes = (size_t)h_words_.p[0];
+    index_module_ok_ = mi.root_kind == ROW_OPEN_OBJ && (mi.module_kind == ROW_OPEN_OBJ || mi.module_kind == ROW_EMPTY_OBJ);
+    index_n_ = index_module_ok_ ? mi.n_children : 0;
+    if (index_n_) {
+        if ((e = timed(K_MODULE_INDEX, [&] {
+                 return launch_child_pack(tape_.arena, d_crefs_.as<ChildRef>(), offs, index_n_, d_centries_.as<ChildEntry>(), d_cpacked_.as<uint8_t>(), stream_);
+             })) != cudaSuccess)
+            return fail(e, "module index pack", err);
+        if (!h_centries_.reserve(index_n_) || !h_cpacked_.reserve(bytes + 1)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+        if ((e = copy_d2h(h_centries_.p, d_centries_.p, (size_t)index_n_ * sizeof(ChildEntry))) != cudaSuccess) return fail(e, "copy index", err);
+        if (bytes && (e = copy_d2h(h_cpacked_.p, d_cpacked_.p, bytes)) != cudaSuccess) return fail(e, "copy index", err);
+        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
+    }
+    index_version_ = doc.version;
+    return TK_OK;
+}
+
+int Engine::index_lookup(const Document &doc, std::string_view prefix, bool hostname, bool *module_ok,
+                         std::vector<std::pair<std::string_view, std::string_view>> *pairs, std::string *err) {
+    int rc = build_index(doc, err);
+    if (rc) return rc;
+    *module_ok = index_module_ok_;
+    pairs->clear();
+    if (!index_module_ok_) return TK_OK;
+    const ChildEntry *ent = h_centries_.p;
+    const char *bytes = reinterpret_cast<const char *>(h_cpacked_.p);
+    // children are in bytewise key order: the keys that start with prefix form one contiguous run
+    uint32_t lo = 0, hi = index_n_;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (std::string_view(bytes + ent[mid].off, ent[mid].klen) < prefix) lo = mid + 1; else hi = mid;
+    }
+    for (uint32_t i = lo; i < index_n_; i++) {
+        const ChildEntry &c = ent[i];
+        std::string_view key(bytes + c.off, c.klen);
+        if (key.size() < prefix.size() || key.compare(0, prefix.size(), prefix) != 0) break;
+        uint32_t o = c.off + c.klen;
+        std::string_view name, host;
+        const bool has_name = c.nlen != 0xffffffffu, has_host = c.hlen != 0xffffffffu;
+        if (has_name) { name = std::string_view(bytes + o, c.nlen); o += c.nlen; }
+        if (has_host) host = std::string_view(bytes + o, c.hlen);
+        if (hostname ? has_host : has_name) pairs->emplace_back(hostname ? host : name, key);
+    }
     return TK_OK;
 }
 

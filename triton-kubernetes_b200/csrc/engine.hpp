@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "doc.hpp"
+#include "index.cuh"
 #include "parse.cuh"
 #include "tape.hpp"
 
@@ -73,9 +74,10 @@ struct DevBuf {
 
 enum KernelKind {
     K_ROW_OFFSETS = 0, K_EMIT, K_PREFIX_MATCH, K_SCAN_TOKENS, K_TOKEN_PREFIX, K_BRACKETS, K_SORT_BRACKETS, K_MATCH,
-    K_DECODE, K_ROWS, K_KEY_ORDER, K_COUNT
+    K_DECODE, K_ROWS, K_KEY_ORDER, K_MODULE_INDEX, K_COUNT
 };
 const char *kernel_name(int kind);
+void set_default_timing(bool on);  // engines created from now on start with per-kernel timing on/off
 
 class Engine {
 public:
@@ -91,13 +93,14 @@ public:
     // order (doc->host_valid stays false: the tree is built only if a point operation needs it)
     // or the tree has been built from the tape on the host (keys out of order, duplicates, numbers
     // that need re-formatting).  Invalid text: TK_ESYNTAX with Go's message.
-    int parse(const char *raw, size_t n, Document *doc, std::string *err);
+    int parse(const char *raw, size_t n, bool raw_on_device, Document *doc, std::string *err);
     // builds doc->root from the device tape (rows in input order); used by parse() and lazily by
     // the point operations
     int materialise(Document *doc, std::string *err);
     // the device-only part of parse(), for bench.py: text already at the start of the arena
     int parse_resident(size_t n, ParseResult *out, std::string *err);
     int upload_text(const char *raw, size_t n, std::string *err);
+    int upload_text_device(const void *dev_raw, size_t n, std::string *err);
 
     int stage(const Document &doc, std::string *err);
     int stage_tape(const Document &doc, std::string *err);
@@ -107,6 +110,14 @@ public:
     int prefix_hits(const Document &doc, std::string_view prefix, bool to_host, std::vector<uint32_t> *hits, size_t *count,
                     std::string *err);
     const std::pair<const std::string, Node *> *module_entry(uint32_t i) const { return entries_[i]; }
+
+    // Clusters()/Nodes() for a document that lives on the device as the parser's tape: children of
+    // "module" whose key starts with prefix and that have the string field ("name" / "hostname").
+    // The packed index is built on the GPU once per document version; the lookup is a binary search.
+    // *module_ok false: "module" is missing or not an object (gabs.ErrNotObj).
+    bool device_resident(const Document &doc) const { return tape_from_parse_ && staged_version_ == doc.version; }
+    int index_lookup(const Document &doc, std::string_view prefix, bool hostname, bool *module_ok,
+                     std::vector<std::pair<std::string_view, std::string_view>> *pairs, std::string *err);
 
     // measurement hooks
     void set_timing(bool on) { timing_ = on; }
@@ -123,6 +134,7 @@ private:
     cudaError_t copy_d2h(void *dst, const void *src, size_t bytes);
     template <class F> cudaError_t timed(int kind, F &&launch);
     int fetch_result(std::string *err);
+    int build_index(const Document &doc, std::string *err);
 
     void flatten(const Document &doc);
     void flatten_keys(const Document &doc);
@@ -162,6 +174,16 @@ private:
     DevBuf d_br_[9], d_flags_, d_zrank_, d_dec_tok_, d_dec_off_, d_dec_len_, d_dec_counts_, d_dec_offs_;
     PinVec<ParseResult> h_res_;
     PinVec<unsigned long long> h_words_;
+
+    // module index
+    DevBuf d_minfo_, d_cflags_, d_crank_, d_crefs_, d_csizes_, d_coffs_, d_centries_, d_cpacked_;
+    PinVec<ModuleInfo> h_minfo_;
+    PinVec<ChildEntry> h_centries_;
+    PinVec<uint8_t> h_cpacked_;
+    uint64_t index_version_ = 0;
+    uint32_t index_n_ = 0;
+    bool index_module_ok_ = false;
+    BracketBuffers bb_{};  // bracket tables of the last parse (match / row are read by the index kernels)
 
     // results
     PinVec<uint8_t> h_out_;

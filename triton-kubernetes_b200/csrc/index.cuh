@@ -1,0 +1,28 @@
+// index.cuh -- launch wrappers of the module-index kernels (index.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "parse.cuh"
+#include "tape.hpp"
+
+namespace tk {
+
+struct ModuleInfo {
+    uint32_t root_kind;    // RowKind of row 0
+    uint32_t module_kind;  // RowKind of root's "module" member; 0xff if there is none
+    uint32_t module_row, module_end;
+    uint32_t n_children, pad;
+};
+struct ChildRef { uint32_t koff, klen, noff, nlen, hoff, hlen; };  // nlen / hlen == 0xffffffff: no such string field
+struct ChildEntry { uint32_t off, klen, nlen, hlen; };             // strings packed at off: key, name, hostname
+
+cudaError_t launch_find_module(const TapeView &t, const uint32_t *br_match, const uint32_t *br_row, ModuleInfo *info, cudaStream_t s);
+cudaError_t launch_child_flags(const TapeView &t, const ModuleInfo *info, uint32_t *flags, cudaStream_t s);
+cudaError_t launch_child_entries(const TapeView &t, const uint32_t *flags, const uint32_t *rank, const uint32_t *br_match,
+                                 const uint32_t *br_row, ChildRef *refs, uint32_t *sizes, cudaStream_t s);
+cudaError_t launch_child_pack(const uint8_t *arena, const ChildRef *refs, const uint32_t *off, uint32_t n, ChildEntry *entries,
+                              uint8_t *packed, cudaStream_t s);
+
+}  // namespace tk

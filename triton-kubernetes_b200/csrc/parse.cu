@@ -381,7 +381,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_u32_kernel(const uint32_t *
 
 inline size_t scan_scratch_words_u32(uint32_t n) { return 2 + (size_t)((n + SCAN_TILE - 1) / SCAN_TILE); }
 
-cudaError_t scan_u32(const uint32_t *in, uint32_t *out, uint32_t n, u64 *scratch, cudaStream_t s) {
+}  // namespace
+
+cudaError_t scan_u32(const uint32_t *in, uint32_t *out, uint32_t n, unsigned long long *scratch, cudaStream_t s) {
     cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words_u32(n) * 8, s);
     if (e != cudaSuccess) return e;
     if (n == 0) return cudaSuccess;
@@ -389,6 +391,9 @@ cudaError_t scan_u32(const uint32_t *in, uint32_t *out, uint32_t n, u64 *scratch
     g_parse_launches++;
     return cudaGetLastError();
 }
+void count_parse_launch() { g_parse_launches++; }
+
+namespace {
 
 // =================================================================================================
 // P2a: per-tile prefixes over the token stream
@@ -884,12 +889,13 @@ __global__ void __launch_bounds__(TOK_TILE) rows_kernel(const uint8_t *__restric
     if (is_closer(k)) {
         if (depth < 1) { res->invalid = 1; return; }
         meta = (k == T_RBRACE ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR) | ((uint32_t)(depth - 1) << META_DEPTH_SHIFT);
-        koff = bb.match[my_b];  // P4 turns this into the opener's row
+        koff = bb.match[my_b];  // the opener's bracket: key_order and the module index find its row through bb.row
+        bb.row[my_b] = r;
     } else {
         if (is_opener(k)) {
             const bool empty = (i + 1 < n_tok) && is_closer(kind[i + 1]);
             if (empty) { meta = (k == T_LBRACE ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR); end_tok = i + 1; }
-            else { meta = (k == T_LBRACE ? ROW_OPEN_OBJ : ROW_OPEN_ARR); bb.row[my_b] = r; }
+            else { meta = (k == T_LBRACE ? ROW_OPEN_OBJ : ROW_OPEN_ARR); bb.row[my_b] = r; voff = my_b; }  // voff of an opening row: its bracket
         } else if (k == T_STR_OPEN) {
             meta = ROW_STR;
             string_ref(tb, db, n_dec, i, &voff, &vlen);

@@ -116,6 +116,10 @@ cudaError_t launch_rows(const uint8_t *raw, size_t n, TokenBuffers tb, uint32_t 
 cudaError_t launch_key_order(const uint8_t *arena, RowBuffers rb, uint32_t n_rows, BracketBuffers bb, ParseResult *res,
                              cudaStream_t s);
 size_t parse_scan_scratch_words(uint32_t n);
+// exclusive scan of n u32 values (single pass, decoupled look-back); the total lands in scratch[1].
+// scratch: parse_scan_scratch_words(n) words, cleared on the stream first.
+cudaError_t scan_u32(const uint32_t *in, uint32_t *out, uint32_t n, unsigned long long *scratch, cudaStream_t s);
+void count_parse_launch();
 unsigned long long parse_launch_count();
 
 }  // namespace tk

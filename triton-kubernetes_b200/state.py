@@ -27,7 +27,8 @@ SYMBOLS = [
     "tk_state_add_node", "tk_state_delete", "tk_state_bytes", "tk_state_clusters", "tk_state_nodes",
     "tk_new_hostnames", "tk_state_stage", "tk_state_bytes_device", "tk_state_prefix_count_device",
     "tk_state_stream", "tk_kernel_launches", "tk_version", "tk_state_timing", "tk_state_kernel_stats",
-    "tk_state_copy_stats", "tk_row_offsets_noalloc", "tk_state_host_tree_built",
+    "tk_state_copy_stats", "tk_row_offsets_noalloc", "tk_state_host_tree_built", "tk_state_new_device",
+    "tk_set_default_timing",
 ]
 
 _lib = None
@@ -44,6 +45,8 @@ def lib():
     L = ctypes.CDLL(LIB_PATH)
     P = c_void_p
     L.tk_state_new.argtypes = [c_char_p, c_size_t, c_char_p, c_size_t, POINTER(P)]
+    L.tk_state_new_device.argtypes = [c_char_p, c_size_t, P, c_size_t, POINTER(P)]
+    L.tk_set_default_timing.argtypes = [c_int]
     L.tk_state_new_empty.argtypes = [c_char_p, c_size_t, POINTER(P)]
     L.tk_state_free.argtypes = [P]
     L.tk_state_free.restype = None
@@ -130,11 +133,13 @@ def _pairs(ptr, n) -> dict:
 class State:
     """state.State (state/state.go:10-13) backed by a tk_state handle."""
 
-    def __init__(self, name, raw=None):
+    def __init__(self, name, raw=None, device_ptr=None):
         L = lib()
         nm = _b(name)
         h = c_void_p()
-        if raw is None:
+        if device_ptr is not None:  # (device address, length): text already in HBM
+            rc = L.tk_state_new_device(nm, len(nm), device_ptr[0], device_ptr[1], byref(h))
+        elif raw is None:
             rc = L.tk_state_new_empty(nm, len(nm), byref(h))
         elif isinstance(raw, tuple):  # (address, length) of a caller-owned (e.g. pinned) buffer
             rc = L.tk_state_new(nm, len(nm), ctypes.cast(raw[0], c_char_p), raw[1], byref(h))
@@ -184,6 +189,18 @@ class State:
         b, n, c = c_void_p(), c_size_t(), c_size_t()
         self._check(lib().tk_state_clusters(self._h, byref(b), byref(n), byref(c)))
         return _pairs(b, n)
+
+    def ClustersCount(self) -> int:
+        """len(Clusters()) without building the Python dict."""
+        b, n, c = c_void_p(), c_size_t(), c_size_t()
+        self._check(lib().tk_state_clusters(self._h, byref(b), byref(n), byref(c)))
+        return c.value
+
+    def NodesCount(self, cluster_key) -> int:
+        ck = _b(cluster_key)
+        b, n, c = c_void_p(), c_size_t(), c_size_t()
+        self._check(lib().tk_state_nodes(self._h, ck, len(ck), byref(b), byref(n), byref(c)))
+        return c.value
 
     def Nodes(self, cluster_key) -> dict:
         ck = _b(cluster_key)
@@ -280,6 +297,15 @@ def getNewHostnames(existing, node_name, nodes_to_add):
         raise StateError(rc, lib().tk_last_error(None).decode("utf-8", "replace"))
     blob = ctypes.string_at(out.value, n.value) if n.value else b""
     return [x.decode() for x in blob.split(b"\n")] if blob else []
+
+
+def NewDevice(name, device_address, length) -> State:
+    """state.New on text already in device memory."""
+    return State(name, device_ptr=(device_address, length))
+
+
+def set_default_timing(on: bool):
+    lib().tk_set_default_timing(1 if on else 0)
 
 
 def kernel_launches() -> int:
