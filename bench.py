@@ -253,17 +253,27 @@ def run_ours(args, rank, local_rank, world):
     barrier()
 
     # ---- e2e: host text in, host text out, through the public API
+    phase = {"new": 0.0, "clusters": 0.0, "nodes_x1000": 0.0, "bytes": 0.0, "close": 0.0}
+
     def e2e_step():
+        t0 = time.perf_counter()
         s = tk.New("bench", (pinned.data_ptr(), len(text)))
+        t1 = time.perf_counter()
         nc = s.ClustersCount()
+        t2 = time.perf_counter()
         n = 0
         for ck in cks:
             n += s.NodesCount(ck)
+        t3 = time.perf_counter()
         addr, ln = s.BytesView()
+        t4 = time.perf_counter()
         stats = s.CopyStats()
+        phase["new"] += t1 - t0; phase["clusters"] += t2 - t1; phase["nodes_x1000"] += t3 - t2; phase["bytes"] += t4 - t3
         ok = (nc == args.clusters and n == args.clusters * args.nodes and ln == len(text)
               and ctypes.string_at(addr + ln - 64, 64) == text[-64:] and ctypes.string_at(addr, 64) == text[:64])
+        t5 = time.perf_counter()
         s.close()
+        phase["close"] += time.perf_counter() - t5
         return ok, stats
 
     for _ in range(args.warmup):
@@ -271,6 +281,8 @@ def run_ours(args, rank, local_rank, world):
         if not ok:
             raise SystemExit("bench.py: e2e step returned a wrong result")
     barrier()
+    for k in phase:
+        phase[k] = 0.0
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     t0 = time.perf_counter()
@@ -317,7 +329,8 @@ def run_ours(args, rank, local_rank, world):
                                        "(the module index is copied to the host once per step: Clusters/Nodes look it up there)",
                        "clusters": args.clusters, "nodes_per_cluster": args.nodes, "document_bytes": len(text)},
             "e2e": {"value": world * OPS_PER_STEP * args.steps / (ms_e2e * 1e-3), "unit": "ops/s",
-                    "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": copy_stats[0], "d2h_bytes_per_step": copy_stats[1]},
+                    "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": copy_stats[0], "d2h_bytes_per_step": copy_stats[1],
+                    "phase_ms": {k: v / args.steps * 1e3 for k, v in phase.items()}},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
         }
         if world == 1:

@@ -17,6 +17,7 @@ struct tk_state {
     Engine eng;
     std::string err;
     std::string blob;  // last Clusters()/Nodes() result
+    std::vector<std::pair<std::string_view, std::string_view>> pairs;
 };
 
 static thread_local std::string g_err;        // for calls that have no handle
@@ -222,7 +223,8 @@ void *tk_state_stream(tk_state *s) { return s ? (void *)s->eng.stream() : nullpt
 static int children_by_prefix(tk_state *s, std::string_view prefix, std::string_view field, const uint8_t **blob,
                               size_t *blob_len, size_t *count) {
     std::string err;
-    std::vector<std::pair<std::string_view, std::string_view>> pairs;  // (field value, module key)
+    auto &pairs = s->pairs;  // (field value, module key); kept on the handle so a sweep of calls re-uses its storage
+    pairs.clear();
     if (!s->doc.host_valid && s->eng.device_resident(s->doc)) {
         // the document lives on the device: one GPU pass per version builds the packed index
         bool module_ok = false;
@@ -245,19 +247,24 @@ static int children_by_prefix(tk_state *s, std::string_view prefix, std::string_
             pairs.emplace_back(static_cast<const StrNode *>(f->second)->s, key);
         }
     }
-    std::sort(pairs.begin(), pairs.end());
-    s->blob.clear();
+    // pairs arrive in key order, which for the usual naming is name order too: sort only if needed
+    if (!std::is_sorted(pairs.begin(), pairs.end())) std::sort(pairs.begin(), pairs.end());
+    size_t bytes = 0;
+    for (auto &p : pairs) bytes += 8 + p.first.size() + p.second.size();
+    s->blob.resize(bytes);
+    char *w = s->blob.data();
     size_t kept = 0;
     for (size_t i = 0; i < pairs.size(); i++) {
         if (i + 1 < pairs.size() && pairs[i + 1].first == pairs[i].first) continue;  // greatest key wins
         uint32_t l = (uint32_t)pairs[i].first.size();
-        s->blob.append(reinterpret_cast<const char *>(&l), 4);
-        s->blob.append(pairs[i].first);
+        memcpy(w, &l, 4); w += 4;
+        memcpy(w, pairs[i].first.data(), l); w += l;
         l = (uint32_t)pairs[i].second.size();
-        s->blob.append(reinterpret_cast<const char *>(&l), 4);
-        s->blob.append(pairs[i].second);
+        memcpy(w, &l, 4); w += 4;
+        memcpy(w, pairs[i].second.data(), l); w += l;
         kept++;
     }
+    s->blob.resize((size_t)(w - s->blob.data()));
     *blob = reinterpret_cast<const uint8_t *>(s->blob.data());
     *blob_len = s->blob.size();
     *count = kept;

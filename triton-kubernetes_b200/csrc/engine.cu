@@ -186,11 +186,27 @@ int Engine::init(std::string *err) {
 
 // ---------------------------------------------------------------------------- flatten
 
+// every byte printable ASCII other than " \\ < > & : the escaped form is the byte string itself
+static bool is_plain(const char *s, size_t n) {
+    static const struct Table {
+        bool plain[256];
+        Table() {
+            for (int c = 0; c < 256; c++)
+                plain[c] = c >= 0x20 && c < 0x80 && c != '"' && c != '\\' && c != '<' && c != '>' && c != '&';
+        }
+    } t;
+    for (size_t i = 0; i < n; i++)
+        if (!t.plain[(unsigned char)s[i]]) return false;
+    return true;
+}
+
 void Engine::push_row(uint32_t kind, uint32_t depth, const std::string *key, const char *val, size_t vlen, bool comma, bool last) {
     uint32_t meta = kind | (depth << META_DEPTH_SHIFT);
     uint32_t koff = 0, klen = 0, voff = 0;
+    if (kind == ROW_STR && is_plain(val, vlen)) meta |= META_VAL_PLAIN;
     if (key) {
         meta |= META_HAS_KEY;
+        if (is_plain(key->data(), key->size())) meta |= META_KEY_PLAIN;
         koff = (uint32_t)h_arena_.append(reinterpret_cast<const uint8_t *>(key->data()), key->size());
         klen = (uint32_t)key->size();
     }

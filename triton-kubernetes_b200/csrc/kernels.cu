@@ -147,11 +147,13 @@ __device__ __forceinline__ bool stage_warp_input(const TapeView &t, const Row &w
     return true;
 }
 
-__device__ __forceinline__ uint32_t row_out_len(const Row &w, const uint8_t *kp, const uint8_t *vp) {
+// Output length of one line.  A plain string (tape.hpp) is as long escaped as raw, so only the
+// rare non-plain ones have their bytes examined.
+__device__ __forceinline__ uint32_t row_out_len(const Row &w, const uint8_t *src) {
     uint32_t len = w.meta >> META_DEPTH_SHIFT;
-    if (w.meta & META_HAS_KEY) len += escaped_len(kp, w.klen) + 4;  // "key":<space>
+    if (w.meta & META_HAS_KEY) len += ((w.meta & META_KEY_PLAIN) ? w.klen : escaped_len(src + w.koff, w.klen)) + 4;  // "key":<space>
     switch (w.meta & 15u) {
-    case ROW_STR: len += escaped_len(vp, w.vlen) + 2; break;
+    case ROW_STR: len += ((w.meta & META_VAL_PLAIN) ? w.vlen : escaped_len(src + w.voff, w.vlen)) + 2; break;
     case ROW_RAW: len += w.vlen; break;
     case ROW_EMPTY_OBJ: case ROW_EMPTY_ARR: len += 2; break;
     default: len += 1;
@@ -159,6 +161,11 @@ __device__ __forceinline__ uint32_t row_out_len(const Row &w, const uint8_t *kp,
     if (w.meta & META_COMMA) len += 1;
     if (!(w.meta & META_LAST)) len += 1;
     return len;
+}
+
+__device__ __forceinline__ bool row_needs_bytes(const Row &w) {
+    return ((w.meta & META_HAS_KEY) && !(w.meta & META_KEY_PLAIN) && w.klen) ||
+           ((w.meta & 15u) == ROW_STR && !(w.meta & META_VAL_PLAIN) && w.vlen);
 }
 
 // ---- K1: line lengths + exclusive scan ------------------------------------------------------
@@ -191,10 +198,14 @@ __global__ void __launch_bounds__(EMIT_THREADS) row_offsets_kernel(TapeView t, u
 
     Row w = {0, 0, 0, 0, 0};
     if (valid) w = load_row(t, r);
-    uint32_t base;
-    const bool staged = stage_warp_input(t, w, valid, s_in[warp], &base);
-    const uint8_t *src = staged ? reinterpret_cast<const uint8_t *>(s_in[warp]) - base : t.arena;
-    const uint32_t len = valid ? row_out_len(w, src + w.koff, src + w.voff) : 0;
+    // string bytes are only looked at for rows with a non-plain string; a warp without any skips
+    // the staging altogether and the pass reads nothing but the row descriptors
+    const uint8_t *src = t.arena;
+    if (__any_sync(FULL, valid && row_needs_bytes(w))) {
+        uint32_t base;
+        if (stage_warp_input(t, w, valid, s_in[warp], &base)) src = reinterpret_cast<const uint8_t *>(s_in[warp]) - base;
+    }
+    const uint32_t len = valid ? row_out_len(w, src) : 0;
 
     // inclusive scan inside the warp, then across the 8 warps
     uint32_t incl = len;
@@ -252,23 +263,39 @@ __global__ void __launch_bounds__(EMIT_THREADS) row_offsets_kernel(TapeView t, u
 
 // ---- K2: emit -------------------------------------------------------------------------------
 
-__device__ __forceinline__ uint32_t put_line(uint8_t *dst, uint32_t pos, const Row &w, const uint8_t *kp, const uint8_t *vp) {
+constexpr uint32_t LANE_COPY_MAX = 16;  // plain runs up to this many bytes are copied by the row's own lane
+
+// A plain byte run of one row: short ones are copied at once by the lane, long ones are left for the
+// whole warp to copy together (emit_kernel, phase 2) so that one long string does not hold 31 lanes idle.
+struct Deferred { uint32_t src, dst, len; };
+
+__device__ __forceinline__ uint32_t put_plain(uint8_t *dst, uint32_t pos, const uint8_t *src, uint32_t off, uint32_t len, Deferred *d) {
+    if (len <= LANE_COPY_MAX) {
+        for (uint32_t i = 0; i < len; i++) dst[pos + i] = src[off + i];
+    } else {
+        d->src = off; d->dst = pos; d->len = len;
+    }
+    return pos + len;
+}
+
+// one line, written at dst[pos...]; src is indexed by arena offset
+__device__ __forceinline__ void put_line(uint8_t *dst, uint32_t pos, const Row &w, const uint8_t *src, Deferred *dk, Deferred *dv) {
     const uint32_t depth = w.meta >> META_DEPTH_SHIFT;
     for (uint32_t i = 0; i < depth; i++) dst[pos++] = '\t';
     if (w.meta & META_HAS_KEY) {
         dst[pos++] = '"';
-        pos = put_escaped(dst, pos, kp, w.klen);
+        if (w.meta & META_KEY_PLAIN) pos = put_plain(dst, pos, src, w.koff, w.klen, dk);
+        else pos = put_escaped(dst, pos, src + w.koff, w.klen);
         dst[pos++] = '"'; dst[pos++] = ':'; dst[pos++] = ' ';
     }
     switch (w.meta & 15u) {
     case ROW_STR:
         dst[pos++] = '"';
-        pos = put_escaped(dst, pos, vp, w.vlen);
+        if (w.meta & META_VAL_PLAIN) pos = put_plain(dst, pos, src, w.voff, w.vlen, dv);
+        else pos = put_escaped(dst, pos, src + w.voff, w.vlen);
         dst[pos++] = '"';
         break;
-    case ROW_RAW:
-        for (uint32_t i = 0; i < w.vlen; i++) dst[pos++] = vp[i];
-        break;
+    case ROW_RAW: pos = put_plain(dst, pos, src, w.voff, w.vlen, dv); break;
     case ROW_OPEN_OBJ: dst[pos++] = '{'; break;
     case ROW_OPEN_ARR: dst[pos++] = '['; break;
     case ROW_CLOSE_OBJ: dst[pos++] = '}'; break;
@@ -278,7 +305,14 @@ __device__ __forceinline__ uint32_t put_line(uint8_t *dst, uint32_t pos, const R
     }
     if (w.meta & META_COMMA) dst[pos++] = ',';
     if (!(w.meta & META_LAST)) dst[pos++] = '\n';
-    return pos;
+}
+
+__device__ __forceinline__ void warp_copy_deferred(uint8_t *dst, const uint8_t *src, const Deferred &d, uint32_t lane) {
+    for (unsigned m = __ballot_sync(FULL, d.len != 0); m; m &= m - 1) {
+        const int l = __ffs(m) - 1;
+        const uint32_t so = __shfl_sync(FULL, d.src, l), dof = __shfl_sync(FULL, d.dst, l), n = __shfl_sync(FULL, d.len, l);
+        for (uint32_t i = lane; i < n; i += 32) dst[dof + i] = src[so + i];
+    }
 }
 
 __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const uint32_t *__restrict__ off,
@@ -304,26 +338,30 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const ui
     const uint32_t out0 = __ldg(off + r0), out1 = __ldg(off + r_end);  // off has n_rows + 1 entries
     const uint32_t shift = out0 & 15u;                                  // same 16-byte phase as global
     const uint32_t span = out1 - out0;
+    const bool fits = shift + span <= (uint32_t)WARP_OUT_BYTES;        // else: straight to global memory
 
-    if (shift + span <= (uint32_t)WARP_OUT_BYTES) {
-        uint8_t *slice = reinterpret_cast<uint8_t *>(s_out[warp]);
-        if (valid) put_line(slice, o - out0 + shift, w, src + w.koff, src + w.voff);
-        __syncwarp();
-        // copy out: whole 16-byte chunks as vectors, the ragged head and tail bytewise
-        uint8_t *g = out + (out0 - shift);  // 16-byte aligned
-        const uint32_t end = shift + span;
-        const uint32_t chunks = (end + 15u) >> 4;
-        for (uint32_t c = lane; c < chunks; c += 32) {
-            const uint32_t b0 = c << 4;
-            if (b0 >= shift && b0 + 16 <= end) {
-                reinterpret_cast<uint4 *>(g)[c] = s_out[warp][c];
-            } else {
-                const uint32_t lo = max(b0, shift), hi = min(b0 + 16, end);
-                for (uint32_t b = lo; b < hi; b++) g[b] = slice[b];
-            }
+    uint8_t *slice = reinterpret_cast<uint8_t *>(s_out[warp]);
+    uint8_t *dst = fits ? slice : out;
+    Deferred dk = {0, 0, 0}, dv = {0, 0, 0};
+    // phase 1: every lane writes its own line, leaving long plain runs for phase 2
+    if (valid) put_line(dst, fits ? o - out0 + shift : o, w, src, &dk, &dv);
+    // phase 2: the warp copies the long runs together, 32 bytes per step
+    warp_copy_deferred(dst, src, dk, lane);
+    warp_copy_deferred(dst, src, dv, lane);
+    if (!fits) return;
+    __syncwarp();
+    // copy out: whole 16-byte chunks as vectors, the ragged head and tail bytewise
+    uint8_t *g = out + (out0 - shift);  // 16-byte aligned
+    const uint32_t end = shift + span;
+    const uint32_t chunks = (end + 15u) >> 4;
+    for (uint32_t c = lane; c < chunks; c += 32) {
+        const uint32_t b0 = c << 4;
+        if (b0 >= shift && b0 + 16 <= end) {
+            reinterpret_cast<uint4 *>(g)[c] = s_out[warp][c];
+        } else {
+            const uint32_t lo = max(b0, shift), hi = min(b0 + 16, end);
+            for (uint32_t b = lo; b < hi; b++) g[b] = slice[b];
         }
-    } else if (valid) {
-        put_line(out, o, w, src + w.koff, src + w.voff);  // oversized tile: straight to global memory
     }
 }
 

@@ -36,7 +36,7 @@ __device__ __forceinline__ u64 low_mask(int i) { return i >= 64 ? ~0ull : ((1ull
 // P1: bytes -> tokens
 // =================================================================================================
 
-constexpr uint32_t C_QUOTE = 1, C_BS = 2, C_WS = 4, C_ST = 8, C_CTRL = 16;
+constexpr uint32_t C_QUOTE = 1, C_BS = 2, C_WS = 4, C_ST = 8, C_CTRL = 16, C_HTML = 32;
 
 __device__ __forceinline__ uint32_t byte_class(uint32_t c) {
     uint32_t k = 0;
@@ -45,6 +45,7 @@ __device__ __forceinline__ uint32_t byte_class(uint32_t c) {
     if (c == ' ' || c == '\t' || c == '\n' || c == '\r') k |= C_WS;
     if (c == '{' || c == '}' || c == '[' || c == ']' || c == ':' || c == ',') k |= C_ST;
     if (c < 0x20) k |= C_CTRL;
+    if (c == '<' || c == '>' || c == '&') k |= C_HTML;  // escaped on output: such strings are not plain
     return k;
 }
 
@@ -102,7 +103,7 @@ __global__ void __launch_bounds__(P1_THREADS) scan_tokens_kernel(const uint8_t *
     const u64 chunk = (u64)tile * P1_TILE + (u64)threadIdx.x * P1_BYTES_PER_THREAD;
 
     // ---- load 64 bytes, build the class masks
-    u64 Q = 0, B = 0, WS = 0, STm = 0, CT = 0, NA = 0;
+    u64 Q = 0, B = 0, WS = 0, STm = 0, CT = 0, NA = 0, HT = 0;
     {
         const uint4 *p = reinterpret_cast<const uint4 *>(raw + chunk);
 #pragma unroll
@@ -120,6 +121,7 @@ __global__ void __launch_bounds__(P1_THREADS) scan_tokens_kernel(const uint8_t *
                 WS |= (u64)gather4(c4, 2) << sh;
                 STm |= (u64)gather4(c4, 3) << sh;
                 CT |= (u64)gather4(c4, 4) << sh;
+                HT |= (u64)gather4(c4, 5) << sh;
                 NA |= (u64)gather4(x, 7) << sh;
             }
         }
@@ -286,8 +288,9 @@ __global__ void __launch_bounds__(P1_THREADS) scan_tokens_kernel(const uint8_t *
     }
     if (bad) res->invalid = 1;
 
-    // ---- strings that need decoding: a backslash or a non-ASCII byte inside
-    for (u64 dmask = (B | NA) & content; dmask;) {
+    // ---- strings that are not plain: a backslash, a non-ASCII byte or one of < > & inside.  They
+    //      are decoded into the side arena and take the escaping path when serialised.
+    for (u64 dmask = (B | NA | HT) & content; dmask;) {
         const int i = __ffsll((long long)dmask) - 1;
         const u64 t = idx + (u64)__popcll(T & low_mask(i)) - 1;  // the string's opening-quote token
         if (t < tb.cap) atomicOr(tb.decode_bits + (t >> 5), 1u << (t & 31));
@@ -454,37 +457,55 @@ __device__ __forceinline__ TokLocal tile_scan(int dd, uint32_t row, uint32_t br,
     return t;
 }
 
+// Each block takes PREFIX_SUB consecutive 256-token tiles, so the (latency-bound) look-back runs
+// once per 4,096 tokens while the later passes still get one prefix per 256-token tile.
+constexpr int PREFIX_SUB = 16;
+
 __global__ void __launch_bounds__(TOK_TILE) token_prefix_kernel(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, u64 *scratch,
                                                                ParseResult *res) {
-    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_blk;
     __shared__ int s_pd;
     __shared__ uint32_t s_pr, s_pb;
-    if (threadIdx.x == 0) s_tile = (uint32_t)atomicAdd(&scratch[0], 1ull);
+    __shared__ int s_sub_d[PREFIX_SUB];       // running totals before each sub-tile, relative to the block
+    __shared__ uint32_t s_sub_r[PREFIX_SUB], s_sub_b[PREFIX_SUB];
+    if (threadIdx.x == 0) s_blk = (uint32_t)atomicAdd(&scratch[0], 1ull);
     __syncthreads();
-    const uint32_t tile = s_tile, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t blk = s_blk, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t n_tiles = (n_tok + TOK_TILE - 1) / TOK_TILE;
-    const uint32_t i = tile * TOK_TILE + threadIdx.x;
-    uint32_t k = 0xff;
-    if (i < n_tok) k = tb.kind[i];
-    const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
-    const uint32_t row = (i < n_tok && emits_row(tb.kind, i, n_tok, k)) ? 1u : 0u;
-    const uint32_t br = (dd != 0) ? 1u : 0u;
-    int td, mn, mx;
-    uint32_t tr, tbk;
-    tile_scan(dd, row, br, &td, &tr, &tbk, &mn, &mx);
+    const uint32_t n_blocks = (n_tiles + PREFIX_SUB - 1) / PREFIX_SUB;
+    int run_d = 0, blk_mn = 0x7fffffff, blk_mx = -0x7fffffff;
+    uint32_t run_r = 0, run_b = 0;
+    for (int sub = 0; sub < PREFIX_SUB; sub++) {
+        const uint32_t tile = blk * PREFIX_SUB + sub;
+        if (tile >= n_tiles) break;   // uniform across the block
+        const uint32_t i = tile * TOK_TILE + threadIdx.x;
+        uint32_t k = 0xff;
+        if (i < n_tok) k = tb.kind[i];
+        const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
+        const uint32_t row = (i < n_tok && emits_row(tb.kind, i, n_tok, k)) ? 1u : 0u;
+        int td, mn, mx;
+        uint32_t tr, tbk;
+        tile_scan(dd, row, dd != 0, &td, &tr, &tbk, &mn, &mx);
+        if (threadIdx.x == 0) { s_sub_d[sub] = run_d; s_sub_r[sub] = run_r; s_sub_b[sub] = run_b; }
+        blk_mn = min(blk_mn, run_d + mn);
+        blk_mx = max(blk_mx, run_d + mx);
+        run_d += td; run_r += tr; run_b += tbk;
+    }
+    const int td = run_d;
+    const uint32_t tr = run_r, tbk = run_b;
 
     // two look-backs side by side: warp 0 carries (rows, brackets), warp 1 carries depth
-    u64 *statusX = scratch + 4, *statusY = scratch + 4 + n_tiles;
+    u64 *statusX = scratch + 4, *statusY = scratch + 4 + n_blocks;
     if (warp < 2) {
         u64 *status = warp == 0 ? statusX : statusY;
         // X: rows in bits 0-30, brackets in bits 31-61.  Y: depth + 2^40 (biased, stays positive)
         const u64 mine = warp == 0 ? ((u64)tr | ((u64)tbk << 31)) : (u64)(long long)td;
         u64 prefix = 0;
-        if (tile == 0) {
+        if (blk == 0) {
             if (lane == 0) st_relaxed(status, ST_PREFIX | (warp == 0 ? mine : (u64)((long long)td + (1ll << 40))));
         } else {
-            if (lane == 0) st_relaxed(status + tile, ST_AGG | (warp == 0 ? mine : (u64)((long long)td + (1ll << 40))));
-            int look = (int)tile - 1;
+            if (lane == 0) st_relaxed(status + blk, ST_AGG | (warp == 0 ? mine : (u64)((long long)td + (1ll << 40))));
+            int look = (int)blk - 1;
             for (;;) {
                 const int idx = look - (int)lane;
                 u64 s = idx >= 0 ? ld_relaxed(status + idx) : (ST_PREFIX | (warp == 0 ? 0ull : (1ull << 40)));
@@ -501,7 +522,7 @@ __global__ void __launch_bounds__(TOK_TILE) token_prefix_kernel(TokenBuffers tb,
             }
             if (lane == 0) {
                 const u64 inc = prefix + mine;
-                st_relaxed(status + tile, ST_PREFIX | (warp == 0 ? inc : (u64)((long long)inc + (1ll << 40))));
+                st_relaxed(status + blk, ST_PREFIX | (warp == 0 ? inc : (u64)((long long)inc + (1ll << 40))));
             }
         }
         if (lane == 0) {
@@ -510,15 +531,20 @@ __global__ void __launch_bounds__(TOK_TILE) token_prefix_kernel(TokenBuffers tb,
         }
     }
     __syncthreads();
+    if (threadIdx.x < PREFIX_SUB) {
+        const uint32_t tile = blk * PREFIX_SUB + threadIdx.x;
+        if (tile < n_tiles) {
+            TilePrefix p;
+            p.depth = s_pd + s_sub_d[threadIdx.x]; p.rows = s_pr + s_sub_r[threadIdx.x]; p.brackets = s_pb + s_sub_b[threadIdx.x]; p.pad = 0;
+            tiles[tile] = p;
+        }
+    }
     if (threadIdx.x == 0) {
-        TilePrefix p;
-        p.depth = s_pd; p.rows = s_pr; p.brackets = s_pb; p.pad = 0;
-        tiles[tile] = p;
-        if (s_pd + mn < 0) res->invalid = 1;                                      // a closer with nothing open
-        const int hi = s_pd + mx;
+        if (s_pd + blk_mn < 0) res->invalid = 1;                                  // a closer with nothing open
+        const int hi = s_pd + blk_mx;
         if (hi > 10000) res->invalid = 1;                                         // exceeded max depth
         if (hi > 0) atomicMax(&res->max_level, (unsigned)min(hi, 16383));
-        if (tile + 1 == n_tiles) {
+        if (blk + 1 == n_blocks) {
             res->n_rows = s_pr + tr;
             res->n_brackets = s_pb + tbk;
             res->final_depth = s_pd + td;
@@ -898,6 +924,7 @@ __global__ void __launch_bounds__(TOK_TILE) rows_kernel(const uint8_t *__restric
             else { meta = (k == T_LBRACE ? ROW_OPEN_OBJ : ROW_OPEN_ARR); bb.row[my_b] = r; voff = my_b; }  // voff of an opening row: its bracket
         } else if (k == T_STR_OPEN) {
             meta = ROW_STR;
+            if (!((tb.decode_bits[i >> 5] >> (i & 31)) & 1u)) meta |= META_VAL_PLAIN;
             string_ref(tb, db, n_dec, i, &voff, &vlen);
             end_tok = i + 1;
         } else {  // scalar
@@ -915,6 +942,7 @@ __global__ void __launch_bounds__(TOK_TILE) rows_kernel(const uint8_t *__restric
             if (i < 3 || kind[i - 3] != T_STR_OPEN) { res->invalid = 1; return; }
             const uint32_t ko = i - 3;
             meta |= META_HAS_KEY;
+            if (!((tb.decode_bits[ko >> 5] >> (ko & 31)) & 1u)) meta |= META_KEY_PLAIN;
             string_ref(tb, db, n_dec, ko, &koff, &klen);
             if (ko > 0) { uint32_t q = ko - 1; if (kind[q] == T_SCALAR_END) q--; if (kind[q] == T_COMMA) meta |= (1u << 7); }  // has an earlier sibling
         }
@@ -981,9 +1009,10 @@ cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, un
 
 cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, unsigned long long *scratch, ParseResult *res,
                                 cudaStream_t s) {
-    cudaError_t e = cudaMemsetAsync(scratch, 0, (4 + 2 * (size_t)tok_tiles(n_tok)) * 8, s);
+    const uint32_t blocks = (tok_tiles(n_tok) + PREFIX_SUB - 1) / PREFIX_SUB;
+    cudaError_t e = cudaMemsetAsync(scratch, 0, (4 + 2 * (size_t)blocks) * 8, s);
     if (e != cudaSuccess) return e;
-    token_prefix_kernel<<<tok_tiles(n_tok), TOK_TILE, 0, s>>>(tb, n_tok, tiles, scratch, res);
+    token_prefix_kernel<<<blocks, TOK_TILE, 0, s>>>(tb, n_tok, tiles, scratch, res);
     g_parse_launches++;
     return cudaGetLastError();
 }

@@ -197,10 +197,17 @@ class State:
         return c.value
 
     def NodesCount(self, cluster_key) -> int:
-        ck = _b(cluster_key)
-        b, n, c = c_void_p(), c_size_t(), c_size_t()
-        self._check(lib().tk_state_nodes(self._h, ck, len(ck), byref(b), byref(n), byref(c)))
-        return c.value
+        """len(Nodes(ck)) without building the Python dict; out-parameters are reused across calls
+        so that a sweep over many clusters measures the library, not ctypes object churn."""
+        out = self.__dict__.get("_nc")
+        if out is None:
+            b, n, c = c_void_p(), c_size_t(), c_size_t()
+            out = self._nc = (lib().tk_state_nodes, byref(b), byref(n), byref(c), c)
+        ck = cluster_key if isinstance(cluster_key, bytes) else _b(cluster_key)
+        rc = out[0](self._h, ck, len(ck), out[1], out[2], out[3])
+        if rc != TK_OK:
+            self._check(rc)
+        return out[4].value
 
     def Nodes(self, cluster_key) -> dict:
         ck = _b(cluster_key)
