@@ -4,15 +4,16 @@
 One STEP is one pass of the hot path over the 62,177,405-byte synthetic document:
     state.New(text) -> Clusters() -> Nodes(ck) for each of the 1,000 cluster keys -> Bytes()
 = 1,003 state.State operations (destroy/cluster.go:64-161 and get/cluster.go:65-118 walk a
-document this way).
+document this way).  The step itself is a compiled loop over the C ABI (tools/bench_driver.c), for
+both arms, so that Python call overhead is not measured as if it were the library.
 
-  value  the step with its input already resident in HBM (kernels only, output left in HBM),
-         timed with CUDA events on the stream the library launches on
-  e2e    the same step through the public C ABI with HOST buffers: pinned host text in,
-         host->device copies, kernels, device->host copy of the result text, all inside the
+  value  the step with the text already resident in HBM and the result left in HBM, timed with
+         CUDA events (start on an idle device, end on the stream the library launches on)
+  e2e    the same step through the public C ABI with HOST buffers: pinned host text in, the
+         host->device copy, kernels, and the device->host copy of the result text, all inside the
          timed region
   --impl reference   the CPU oracle (oracle/tk_oracle.c, a restatement of the reference's Go
-         code; the Go toolchain is absent) on the host cores, same step, same metric
+         code; the Go toolchain is absent) on every host core, same step, same metric
 
 Under torchrun (N > 1) every rank runs the step on its own document on its own GPU (the path
 shards by document: one manager per worker, no exchange step, so no collective in the data
@@ -28,6 +29,7 @@ import subprocess
 import sys
 import threading
 import time
+from ctypes import POINTER, byref, c_char_p, c_double, c_int, c_size_t, c_void_p
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -40,13 +42,37 @@ WORKLOAD = ("config #4: synthetic state document, 1000 clusters x 100 nodes (62,
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--clusters", type=int, default=1000, help=argparse.SUPPRESS)
     ap.add_argument("--nodes", type=int, default=100, help=argparse.SUPPRESS)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help=argparse.SUPPRESS)
     return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------ driver
+
+def driver():
+    """tools/libtkbench.so: built on first use (gcc is part of the image, here and on the GPU box)."""
+    src, lib = os.path.join(ROOT, "tools", "bench_driver.c"), os.path.join(ROOT, "tools", "libtkbench.so")
+    if not os.path.exists(lib) or os.path.getmtime(lib) < os.path.getmtime(src):
+        subprocess.check_call(["gcc", "-O2", "-fPIC", "-shared", "-I" + os.path.join(ROOT, "include"), "-o", lib, src,
+                               "-L" + os.path.join(ROOT, "triton-kubernetes_b200"), "-ltkstate",
+                               "-Wl,-rpath," + os.path.join(ROOT, "triton-kubernetes_b200")])
+    importlib.import_module("triton-kubernetes_b200").state.lib()   # libtkstate first, by full path
+    D = ctypes.CDLL(lib)
+    D.tkb_product_step.argtypes = [c_void_p, c_size_t, c_int, c_int, POINTER(c_char_p), POINTER(c_size_t), c_size_t, c_size_t,
+                                   c_size_t, POINTER(c_double), POINTER(c_void_p), POINTER(c_void_p), POINTER(c_size_t)]
+    D.tkb_oracle_step.argtypes = [POINTER(c_void_p), c_char_p, c_size_t, POINTER(c_char_p), POINTER(c_size_t), c_size_t, c_size_t,
+                                  c_size_t, c_size_t]
+    return D
+
+
+def key_arrays(cks):
+    arr = (c_char_p * len(cks))(*cks)
+    lens = (c_size_t * len(cks))(*[len(k) for k in cks])
+    return arr, lens
 
 
 # ------------------------------------------------------------------------------------ clocks
@@ -94,73 +120,67 @@ class ClockSampler:
 
 # ------------------------------------------------------------------------------------ CPU arm
 
-def oracle_step(O, text, cluster_keys):
-    s = O.New("bench", text)
-    cl = s.Clusters()
-    n = 0
-    for ck in cluster_keys:
-        n += s.NodesCount(ck)
-    out = s.Bytes()
-    return len(cl), n, out
+class OracleArm:
+    def __init__(self, text, cks, clusters, nodes):
+        from oracle import oracle as O
+        O.build()
+        L = O.lib()
+        self.D = driver()
+        names = ["ora_new", "ora_free", "ora_free_buf", "ora_clusters", "ora_nodes", "ora_bytes"]
+        self.fns = (c_void_p * len(names))(*[ctypes.cast(getattr(L, n), c_void_p).value for n in names])
+        self.text, self.cks, self.clusters, self.nodes = text, cks, clusters, nodes
+        self.arr, self.lens = key_arrays(cks)
+
+    def step(self):
+        rc = self.D.tkb_oracle_step(self.fns, self.text, len(self.text), self.arr, self.lens, len(self.cks), self.clusters,
+                                    self.clusters * self.nodes, len(self.text))
+        if rc:
+            raise SystemExit("bench.py: oracle step failed (%d)" % rc)
+
+    def run(self, threads, steps_per_thread=None, seconds=None):
+        """Whole steps on `threads` host threads (ctypes releases the GIL); returns (steps, seconds)."""
+        done = [0] * threads
+        t0 = time.perf_counter()
+
+        def work(i):
+            while True:
+                self.step()
+                done[i] += 1
+                if steps_per_thread is not None and done[i] >= steps_per_thread:
+                    return
+                if seconds is not None and time.perf_counter() - t0 >= seconds:
+                    return
+
+        ts = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+        for t in ts: t.start()
+        for t in ts: t.join()
+        return sum(done), time.perf_counter() - t0
 
 
-def cpu_baseline(text, cluster_keys, seconds, threads=1):
-    """The oracle timed on `threads` host threads (ctypes releases the GIL), each running whole steps."""
+def oracle_text(args):
+    synth = importlib.import_module("triton-kubernetes_b200.synth")
     from oracle import oracle as O
     O.build()
-    O.lib()
-    done = [0] * threads
-    stop_at = [None]
-
-    def work(i):
-        while True:
-            oracle_step(O, text, cluster_keys)
-            done[i] += 1
-            if time.perf_counter() >= stop_at[0]:
-                return
-
-    t0 = time.perf_counter()
-    stop_at[0] = t0 + seconds
-    ts = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
-    for t in ts: t.start()
-    for t in ts: t.join()
-    dt = time.perf_counter() - t0
-    steps = sum(done)
-    return {"value": steps * OPS_PER_STEP / dt, "unit": "ops/s", "cores": threads, "kind": "port",
-            "sample": "%d full passes of the 62,177,405-byte document in %.1f s (oracle/tk_oracle.c, gcc -O2)" % (steps, dt),
-            "ms_per_step": dt / steps * 1e3 * threads}
+    return O.New("bench", synth.document(args.clusters, args.nodes)).Bytes()
 
 
 def run_reference(args, rank, world):
     if rank != 0:
         return
     synth = importlib.import_module("triton-kubernetes_b200.synth")
-    from oracle import oracle as O
-    O.build()
-    text = O.New("bench", synth.document(args.clusters, args.nodes)).Bytes()
+    text = oracle_text(args)
     cks = [synth.cluster_key(c).encode() for c in range(args.clusters)]
+    arm = OracleArm(text, cks, args.clusters, args.nodes)
     threads = os.cpu_count() or 1
-    for _ in range(min(args.warmup, 1)):
-        oracle_step(O, text, cks)
-    per_thread = max(1, args.steps)
-
-    def work():
-        for _ in range(per_thread):
-            oracle_step(O, text, cks)
-
-    t0 = time.perf_counter()
-    ts = [threading.Thread(target=work) for _ in range(threads)]
-    for t in ts: t.start()
-    for t in ts: t.join()
-    dt = time.perf_counter() - t0
-    steps = per_thread * threads
+    arm.run(threads, steps_per_thread=min(args.warmup, 1))
+    steps, dt = arm.run(threads, steps_per_thread=max(1, args.steps))
     value = steps * OPS_PER_STEP / dt
     line = {
         "impl": "reference", "metric": "state.State ops/sec", "value": value, "unit": "ops/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / per_thread * 1e3, "higher_is_better": True,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / max(1, args.steps) * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": WORKLOAD, "note": "CPU oracle (C restatement of the reference's Go path; no Go toolchain here), "
-                   "%d host threads each running %d whole steps on its own copy of the document" % (threads, per_thread)},
+                   "%d host threads each running %d whole steps on its own parse of the document" % (threads, max(1, args.steps))},
         "cpu_baseline": {"value": value, "unit": "ops/s", "cores": threads, "kind": "port",
                          "sample": "%d full passes in %.1f s" % (steps, dt)},
         "e2e": {"value": value, "unit": "ops/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -182,11 +202,12 @@ def run_ours(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=dev)
     tk = importlib.import_module("triton-kubernetes_b200")
     synth = importlib.import_module("triton-kubernetes_b200.synth")
-    peaks = {}
+    D = driver()
+    L = tk.state.lib()
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except OSError:
-        pass
+        peaks = {}
     hbm_peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
 
     # ---- synthetic input: the persisted (tab-indented) form of the document, in pinned memory
@@ -194,10 +215,13 @@ def run_ours(args, rank, local_rank, world):
     text = seed.Bytes()
     seed.close()
     cks = [synth.cluster_key(c).encode() for c in range(args.clusters)]
-    node_prefixes = [("node_baremetal_c%04d_" % c).encode() for c in range(args.clusters)]
+    arr, lens = key_arrays(cks)
     pinned = torch.empty(len(text), dtype=torch.uint8, pin_memory=True)
     ctypes.memmove(pinned.data_ptr(), text, len(text))
+    dev_text = torch.empty(len(text), dtype=torch.uint8, device=dev)
+    dev_text.copy_(pinned)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    torch.cuda.synchronize()
 
     def barrier():
         torch.cuda.synchronize()
@@ -205,45 +229,51 @@ def run_ours(args, rank, local_rank, world):
             dist.barrier()
             torch.cuda.synchronize()
 
-    # ---- value: text resident in HBM; New + Clusters + 1000 x Nodes + Bytes, result left in HBM
-    dev_text = torch.empty(len(text), dtype=torch.uint8, device=dev)
-    dev_text.copy_(pinned)
-    torch.cuda.synchronize()
+    phase = (c_double * 5)()
 
-    def resident_step():
-        s = tk.state.NewDevice("bench", dev_text.data_ptr(), len(text))
-        nc = s.ClustersCount()
-        n = 0
-        for ck in cks:
-            n += s.NodesCount(ck)
-        _, ln = s.BytesDevice()
-        return s, (nc == args.clusters and n == args.clusters * args.nodes and ln == len(text))
+    def step(device_text, to_host):
+        """One step through the C driver; returns the handle (caller frees) and the result view."""
+        h, out, n = c_void_p(), c_void_p(), c_size_t()
+        src = dev_text.data_ptr() if device_text else pinned.data_ptr()
+        rc = D.tkb_product_step(src, len(text), 1 if device_text else 0, 1 if to_host else 0, arr, lens, len(cks), args.clusters,
+                                args.clusters * args.nodes, phase, byref(h), byref(out), byref(n))
+        if rc or n.value != len(text):
+            raise SystemExit("bench.py: step failed (%d): %s" % (rc, L.tk_last_error(h if h.value else None)))
+        return h, out.value
+
+    def kernel_stats(h, acc):
+        kind = 0
+        while True:
+            name, ms, tl, ln = c_char_p(), c_double(), ctypes.c_ulonglong(), ctypes.c_ulonglong()
+            if L.tk_state_kernel_stats(h, kind, byref(name), byref(ms), byref(tl), byref(ln)) != 0:
+                return
+            a = acc.setdefault(name.value.decode(), {"ms": 0.0, "timed": 0})
+            a["ms"] += ms.value; a["timed"] += tl.value
+            kind += 1
 
     def timed_resident(steps, per_kernel):
-        tk.state.set_default_timing(per_kernel)
+        L.tk_set_default_timing(1 if per_kernel else 0)
         total, stats = 0.0, {}
         for _ in range(steps):
             flush.zero_()
             torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            s, ok = resident_step()
-            b.record(torch.cuda.ExternalStream(s.stream, device=dev))
+            h, _ = step(True, False)
+            b.record(torch.cuda.ExternalStream(L.tk_state_stream(h), device=dev))
             b.synchronize()
             total += a.elapsed_time(b)
-            if not ok:
-                raise SystemExit("bench.py: resident step returned a wrong result")
             if per_kernel:
-                for name, st in s.KernelStats().items():
-                    acc = stats.setdefault(name, {"ms": 0.0, "timed": 0})
-                    acc["ms"] += st["ms"]; acc["timed"] += st["timed"]
-            s.close()
-        tk.state.set_default_timing(False)
+                kernel_stats(h, stats)
+            L.tk_state_free(h)
+        L.tk_set_default_timing(0)
         return total, stats
 
+    # ---- value: text resident in HBM, result left in HBM
     for _ in range(args.warmup):
-        s, ok = resident_step()
-        s.close()
+        h, _ = step(True, False)
+        torch.cuda.synchronize()
+        L.tk_state_free(h)
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -252,50 +282,36 @@ def run_ours(args, rank, local_rank, world):
     launches = tk.state.kernel_launches() - launches0
     barrier()
 
-    # ---- e2e: host text in, host text out, through the public API
-    phase = {"new": 0.0, "clusters": 0.0, "nodes_x1000": 0.0, "bytes": 0.0, "close": 0.0}
-
+    # ---- e2e: pinned host text in, host text out
     def e2e_step():
-        t0 = time.perf_counter()
-        s = tk.New("bench", (pinned.data_ptr(), len(text)))
-        t1 = time.perf_counter()
-        nc = s.ClustersCount()
-        t2 = time.perf_counter()
-        n = 0
-        for ck in cks:
-            n += s.NodesCount(ck)
-        t3 = time.perf_counter()
-        addr, ln = s.BytesView()
-        t4 = time.perf_counter()
-        stats = s.CopyStats()
-        phase["new"] += t1 - t0; phase["clusters"] += t2 - t1; phase["nodes_x1000"] += t3 - t2; phase["bytes"] += t4 - t3
-        ok = (nc == args.clusters and n == args.clusters * args.nodes and ln == len(text)
-              and ctypes.string_at(addr + ln - 64, 64) == text[-64:] and ctypes.string_at(addr, 64) == text[:64])
-        t5 = time.perf_counter()
-        s.close()
-        phase["close"] += time.perf_counter() - t5
-        return ok, stats
-
-    for _ in range(args.warmup):
-        ok, copy_stats = e2e_step()
+        h, out = step(False, True)
+        ok = ctypes.string_at(out + len(text) - 64, 64) == text[-64:] and ctypes.string_at(out, 64) == text[:64]
+        a, b = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+        L.tk_state_copy_stats(h, byref(a), byref(b))
+        L.tk_state_free(h)
         if not ok:
             raise SystemExit("bench.py: e2e step returned a wrong result")
+        return a.value, b.value
+
+    for _ in range(args.warmup):
+        copy_stats = e2e_step()
     barrier()
-    for k in phase:
-        phase[k] = 0.0
+    for i in range(5):
+        phase[i] = 0.0
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ok, copy_stats = e2e_step()
+        copy_stats = e2e_step()
     torch.cuda.synchronize()
     b.record()
     b.synchronize()
     ms_e2e = max(a.elapsed_time(b), (time.perf_counter() - t0) * 1e3)
+    phase_ms = {k: phase[i] / args.steps for i, k in enumerate(("new", "clusters", "nodes_x%d" % len(cks), "bytes"))}
     barrier()
     clocks = sampler.stop()
 
-    # ---- per-kernel device times for the roofline (same steps again, events around every launch)
+    # ---- per-kernel device times for the roofline (the same steps again, events around every launch)
     _, stats = timed_resident(args.steps, per_kernel=True)
     kern = {}
     for name, st in stats.items():
@@ -304,15 +320,16 @@ def run_ours(args, rank, local_rank, world):
                           "ms_per_step": st["ms"] / args.steps}
     # algorithmic bytes per launch: New = input length, Bytes = output length
     algo = {"scan_tokens_kernel": len(text), "emit_kernel": len(text), "row_offsets_kernel": len(text)}
-    dominant = max((k for k in kern if k in algo), key=lambda k: kern[k]["ms_per_step"])
-    achieved = algo[dominant] / (kern[dominant]["avg_us"] * 1e-6) / 1e9
     for k, v in kern.items():
         if k in algo:
             v["algorithmic_bytes"] = algo[k]
             v["gbs"] = algo[k] / (v["avg_us"] * 1e-6) / 1e9
+    dominant = max((k for k in kern if k in algo), key=lambda k: kern[k]["ms_per_step"])
+    achieved = kern[dominant]["gbs"]
     roofline = {"kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": algo[dominant], "avg_launch_us": kern[dominant]["avg_us"], "kernels": kern}
+                "algorithmic_bytes_per_launch": algo[dominant], "avg_launch_us": kern[dominant]["avg_us"],
+                "kernel_ms_per_step_total": sum(v["ms_per_step"] for v in kern.values()), "kernels": kern}
 
     # ---- max over ranks
     if world > 1:
@@ -327,14 +344,20 @@ def run_ours(args, rank, local_rank, world):
             "config": {"workload": WORKLOAD, "l2": "flushed (256 MiB write) between timed steps",
                        "value_covers": "the whole step with the text already in HBM and the result left in HBM "
                                        "(the module index is copied to the host once per step: Clusters/Nodes look it up there)",
+                       "driver": "tools/bench_driver.c (the step is a compiled loop over the C ABI)",
                        "clusters": args.clusters, "nodes_per_cluster": args.nodes, "document_bytes": len(text)},
             "e2e": {"value": world * OPS_PER_STEP * args.steps / (ms_e2e * 1e-3), "unit": "ops/s",
                     "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": copy_stats[0], "d2h_bytes_per_step": copy_stats[1],
-                    "phase_ms": {k: v / args.steps * 1e3 for k, v in phase.items()}},
+                    "phase_ms": phase_ms},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
         }
         if world == 1:
-            line["cpu_baseline"] = cpu_baseline(text, cks, args.cpu_seconds, threads=1)
+            arm = OracleArm(text, cks, args.clusters, args.nodes)
+            steps, dt = arm.run(1, seconds=args.cpu_seconds)
+            line["cpu_baseline"] = {"value": steps * OPS_PER_STEP / dt, "unit": "ops/s", "cores": 1, "kind": "port",
+                                    "ms_per_step": dt / steps * 1e3,
+                                    "sample": "%d full passes of the %d-byte document in %.1f s (oracle/tk_oracle.c, gcc -O2, one thread)"
+                                              % (steps, len(text), dt)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

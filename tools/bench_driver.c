@@ -1,0 +1,92 @@
+/* bench_driver.c -- the benchmark step as a compiled loop over the C ABI.
+ *
+ * bench.py drives the library from Python; a Python-level loop of 1,000 Nodes() calls costs
+ * ~3 us of ctypes overhead per call, which would be measured as if it were the library.  This
+ * driver runs one whole step (New -> Clusters -> Nodes(ck) for every cluster key -> Bytes) in C,
+ * for the product (through include/tk_state.h) and for the CPU oracle (through function pointers
+ * bench.py hands in, so that nothing here links the oracle).  Bench infrastructure, not product.
+ */
+#define _GNU_SOURCE
+#include <stddef.h>
+#include <stdint.h>
+#include <string.h>
+#include <time.h>
+
+#include "tk_state.h"
+
+static double now_ms(void) {
+    struct timespec t;
+    clock_gettime(CLOCK_MONOTONIC, &t);
+    return t.tv_sec * 1e3 + t.tv_nsec * 1e-6;
+}
+
+/* One step through the product.  text: host pointer (device_text == 0) or device pointer.
+ * to_host: Bytes() into host memory (e2e) or left on the device (value).
+ * phase_ms[5]: new, clusters, nodes, bytes, (unused).  Returns 0 on success, else a TK_E* code
+ * (or -1 for a wrong result).  *keep receives the handle (the caller frees it after its events). */
+int tkb_product_step(const void *text, size_t n, int device_text, int to_host, const char *const *cks, const size_t *ck_lens,
+                     size_t n_cks, size_t want_clusters, size_t want_nodes, double *phase_ms, tk_state **keep,
+                     const char **out_text, size_t *out_len) {
+    tk_state *s = NULL;
+    const uint8_t *blob;
+    size_t blob_len, count, nodes = 0;
+    double t0 = now_ms();
+    int rc = device_text ? tk_state_new_device("bench", 5, text, n, &s) : tk_state_new("bench", 5, (const char *)text, n, &s);
+    if (rc) return rc;
+    *keep = s;
+    double t1 = now_ms();
+    rc = tk_state_clusters(s, &blob, &blob_len, &count);
+    if (rc) return rc;
+    if (count != want_clusters) return -1;
+    double t2 = now_ms();
+    for (size_t i = 0; i < n_cks; i++) {
+        rc = tk_state_nodes(s, cks[i], ck_lens[i], &blob, &blob_len, &count);
+        if (rc) return rc;
+        nodes += count;
+    }
+    if (nodes != want_nodes) return -1;
+    double t3 = now_ms();
+    if (to_host) rc = tk_state_bytes(s, out_text, out_len);
+    else rc = tk_state_bytes_device(s, (const void **)out_text, out_len);
+    if (rc) return rc;
+    double t4 = now_ms();
+    phase_ms[0] += t1 - t0; phase_ms[1] += t2 - t1; phase_ms[2] += t3 - t2; phase_ms[3] += t4 - t3;
+    return 0;
+}
+
+/* The same step through the CPU oracle (oracle/tk_oracle.c), via its exported functions. */
+typedef void *(*ora_new_fn)(const char *, size_t, char *, size_t);
+typedef void (*ora_free_fn)(void *);
+typedef void (*ora_free_buf_fn)(char *);
+typedef int (*ora_clusters_fn)(void *, char **, size_t *, size_t *, char *, size_t);
+typedef int (*ora_nodes_fn)(void *, const char *, size_t, char **, size_t *, size_t *, char *, size_t);
+typedef int (*ora_bytes_fn)(void *, int, char **, size_t *);
+
+int tkb_oracle_step(void **fns, const char *text, size_t n, const char *const *cks, const size_t *ck_lens, size_t n_cks,
+                    size_t want_clusters, size_t want_nodes, size_t want_len) {
+    ora_new_fn f_new = (ora_new_fn)fns[0];
+    ora_free_fn f_free = (ora_free_fn)fns[1];
+    ora_free_buf_fn f_free_buf = (ora_free_buf_fn)fns[2];
+    ora_clusters_fn f_clusters = (ora_clusters_fn)fns[3];
+    ora_nodes_fn f_nodes = (ora_nodes_fn)fns[4];
+    ora_bytes_fn f_bytes = (ora_bytes_fn)fns[5];
+    char err[512];
+    char *out;
+    size_t out_len, count, nodes = 0;
+    void *h = f_new(text, n, err, sizeof err);
+    if (!h) return 1;
+    if (f_clusters(h, &out, &out_len, &count, err, sizeof err)) { f_free(h); return 1; }
+    f_free_buf(out);
+    if (count != want_clusters) { f_free(h); return -1; }
+    for (size_t i = 0; i < n_cks; i++) {
+        if (f_nodes(h, cks[i], ck_lens[i], &out, &out_len, &count, err, sizeof err)) { f_free(h); return 1; }
+        f_free_buf(out);
+        nodes += count;
+    }
+    if (nodes != want_nodes) { f_free(h); return -1; }
+    f_bytes(h, 1, &out, &out_len);
+    int ok = out_len == want_len;
+    f_free_buf(out);
+    f_free(h);
+    return ok ? 0 : -1;
+}

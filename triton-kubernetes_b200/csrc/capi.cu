@@ -17,6 +17,7 @@ struct tk_state {
     Engine eng;
     std::string err;
     std::string blob;  // last Clusters()/Nodes() result
+    std::string prefix;
     std::vector<std::pair<std::string_view, std::string_view>> pairs;
 };
 
@@ -282,7 +283,8 @@ int tk_state_nodes(tk_state *s, const char *cluster_key, size_t cluster_key_len,
     std::string_view provider, cname;
     std::string err;
     if (!cluster_key_parts(sv(cluster_key, cluster_key_len), &provider, &cname, &err)) return set_err(s, TK_EKEYPARTS, err);
-    std::string prefix = "node_";
+    std::string &prefix = s->prefix;  // kept on the handle: no allocation per call in a sweep
+    prefix.assign("node_");
     prefix.append(provider);
     prefix.push_back('_');
     prefix.append(cname);

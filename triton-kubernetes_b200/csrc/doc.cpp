@@ -476,15 +476,18 @@ const MapNode *Document::module_children() const {
 }
 
 bool cluster_key_parts(std::string_view cluster_key, std::string_view *provider, std::string_view *name, std::string *err) {
-    auto parts = split(cluster_key, '_');
-    if (parts.size() < 3) {
+    // strings.Split(clusterKey, "_"): parts[1] and parts[2]; at least three parts = two underscores
+    const size_t a = cluster_key.find('_');
+    const size_t b = a == std::string_view::npos ? a : cluster_key.find('_', a + 1);
+    if (b == std::string_view::npos) {
         *err = "Could not get cluster key parts, cluster does not follow format `cluster_{provider}_{clusterName}` '";
         err->append(cluster_key);
         err->push_back('\'');
         return false;
     }
-    *provider = parts[1];
-    *name = parts[2];
+    const size_t c = cluster_key.find('_', b + 1);
+    *provider = cluster_key.substr(a + 1, b - a - 1);
+    *name = cluster_key.substr(b + 1, c == std::string_view::npos ? std::string_view::npos : c - b - 1);
     return true;
 }
 

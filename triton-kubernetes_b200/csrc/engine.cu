@@ -783,15 +783,23 @@ int Engine::index_lookup(const Document &doc, std::string_view prefix, bool host
     const ChildEntry *ent = h_centries_.p;
     const char *bytes = reinterpret_cast<const char *>(h_cpacked_.p);
     // children are in bytewise key order: the keys that start with prefix form one contiguous run
-    uint32_t lo = 0, hi = index_n_;
-    while (lo < hi) {
-        const uint32_t mid = (lo + hi) >> 1;
-        if (std::string_view(bytes + ent[mid].off, ent[mid].klen) < prefix) lo = mid + 1; else hi = mid;
+    auto key_at = [&](uint32_t i) { return std::string_view(bytes + ent[i].off, ent[i].klen); };
+    auto has_prefix = [&](std::string_view k) { return k.size() >= prefix.size() && memcmp(k.data(), prefix.data(), prefix.size()) == 0; };
+    uint32_t lo = 0;
+    if (index_hint_ < index_n_ && has_prefix(key_at(index_hint_)) && (index_hint_ == 0 || key_at(index_hint_ - 1) < prefix)) {
+        lo = index_hint_;  // a sweep over clusters in order: this run starts where the previous one ended
+    } else {
+        uint32_t hi = index_n_;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (key_at(mid) < prefix) lo = mid + 1; else hi = mid;
+        }
     }
-    for (uint32_t i = lo; i < index_n_; i++) {
+    uint32_t i = lo;
+    for (; i < index_n_; i++) {
         const ChildEntry &c = ent[i];
         std::string_view key(bytes + c.off, c.klen);
-        if (key.size() < prefix.size() || key.compare(0, prefix.size(), prefix) != 0) break;
+        if (!has_prefix(key)) break;
         uint32_t o = c.off + c.klen;
         std::string_view name, host;
         const bool has_name = c.nlen != 0xffffffffu, has_host = c.hlen != 0xffffffffu;
@@ -799,6 +807,7 @@ int Engine::index_lookup(const Document &doc, std::string_view prefix, bool host
         if (has_host) host = std::string_view(bytes + o, c.hlen);
         if (hostname ? has_host : has_name) pairs->emplace_back(hostname ? host : name, key);
     }
+    index_hint_ = i;
     return TK_OK;
 }
 

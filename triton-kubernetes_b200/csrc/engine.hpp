@@ -181,7 +181,7 @@ private:
     PinVec<ChildEntry> h_centries_;
     PinVec<uint8_t> h_cpacked_;
     uint64_t index_version_ = 0;
-    uint32_t index_n_ = 0;
+    uint32_t index_n_ = 0, index_hint_ = 0;
     bool index_module_ok_ = false;
     BracketBuffers bb_{};  // bracket tables of the last parse (match / row are read by the index kernels)
 
