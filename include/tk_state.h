@@ -128,6 +128,41 @@ TK_API int tk_state_nodes(tk_state *s, const char *cluster_key, size_t cluster_k
 TK_API int tk_new_hostnames(const char *const *existing, const size_t *existing_len, size_t n, const char *node_name,
                             size_t node_name_len, long long nodes_to_add, const char **out, size_t *out_len);
 
+/* ---- renderer records -- SURVEY.md 8a row 14 ------------------------------------------------
+ * The reference builds one Go struct per provider x {manager, cluster, node} and hands it to
+ * SetManager / AddCluster / AddNode (base structs create/manager.go:16-27, create/cluster.go:24-43,
+ * create/node.go:19-41; provider structs in create/{manager,cluster,node}_<provider>.go).
+ * tk_render_record turns a flat JSON object of settings {json field name: value} into that
+ * struct's JSON text as encoding/json would marshal it -- declaration order, embedded base struct
+ * first, omitempty applied -- ready to pass on with TK_VALUE_RECORD.  Results are owned by the
+ * calling thread until its next record call. */
+TK_API int tk_render_record(const char *struct_name, size_t struct_name_len, const char *settings_json, size_t settings_len,
+                            const char **out, size_t *out_len);
+/* ("manager"|"cluster"|"node", "triton"|"aws"|"gcp"|"azure"|"baremetal"|"vsphere") -> Go struct name */
+TK_API int tk_record_struct_name(const char *kind, const char *provider, const char **out, size_t *out_len);
+/* `<url>//terraform/modules/<dir>?ref=<ref>` -- create/manager.go:160-171, create/cluster.go:299-311,
+ * create/node.go:209-221.  NULL url / ref: the defaults github.com/joyent/triton-kubernetes, master. */
+TK_API int tk_module_source(const char *kind, const char *provider, const char *source_url, const char *source_ref,
+                            const char **out, size_t *out_len);
+/* table number `index` (0 .. until TK_EARG): struct name and its fields as JSON, for the tests */
+TK_API int tk_record_table(size_t index, const char **struct_name, const char **fields_json, size_t *fields_len);
+
+/* ---- local backend -- backend/local/backend.go:14-132 ------------------
+ * backend.Backend (backend/backend.go:7-27) over <root>/<name>/main.tf.json.  root_dir NULL means
+ * ~/.triton-kubernetes as in the reference; tests point it elsewhere. */
+typedef struct tk_backend tk_backend;
+TK_API int tk_local_backend_new(const char *root_dir, size_t root_dir_len, tk_backend **out);   /* local.New, :28-41 */
+TK_API void tk_backend_free(tk_backend *b);
+TK_API const char *tk_backend_last_error(tk_backend *b);                                       /* b may be NULL */
+TK_API int tk_backend_state(tk_backend *b, const char *name, size_t name_len, tk_state **out); /* State, :43-66 */
+TK_API int tk_backend_delete_state(tk_backend *b, const char *name, size_t name_len);          /* DeleteState, :68-77 */
+TK_API int tk_backend_persist_state(tk_backend *b, tk_state *s);                               /* PersistState, :79-100 */
+/* States, :102-121: directory names joined by '\n', sorted */
+TK_API int tk_backend_states(tk_backend *b, const char **names, size_t *names_len, size_t *count);
+/* StateTerraformConfig, :123-132: the path "terraform.backend.local" and the record {"path": ...} */
+TK_API int tk_backend_state_terraform_config(tk_backend *b, const char *name, size_t name_len, const char **path,
+                                             size_t *path_len, const char **record_json, size_t *record_len);
+
 /* ---- device-resident variants: what bench.py times with inputs already in HBM ------------ */
 
 /* state.New on text that is already in device memory (dev_raw: device pointer, borrowed for the

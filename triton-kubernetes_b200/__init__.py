@@ -3,5 +3,6 @@
 The package directory name carries a hyphen (it follows the reference's name), so import it
 with importlib:  tk = importlib.import_module("triton-kubernetes_b200").
 """
-from . import state  # noqa: F401
+from . import backend_local, records, state  # noqa: F401
+from .backend_local import LocalBackend  # noqa: F401
 from .state import New, Record, State, StateError, getNewHostnames  # noqa: F401

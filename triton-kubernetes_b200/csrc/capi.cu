@@ -6,20 +6,13 @@
 
 #include "doc.hpp"
 #include "engine.hpp"
+#include "handle.hpp"
 #include "kernels.cuh"
+#include "records.hpp"
 #include "tk_state.h"
 
 using namespace tk;
 
-struct tk_state {
-    std::string name;
-    Document doc;
-    Engine eng;
-    std::string err;
-    std::string blob;  // last Clusters()/Nodes() result
-    std::string prefix;
-    std::vector<std::pair<std::string_view, std::string_view>> pairs;
-};
 
 static thread_local std::string g_err;        // for calls that have no handle
 static thread_local std::string g_hostnames;  // tk_new_hostnames result
@@ -307,6 +300,57 @@ int tk_new_hostnames(const char *const *existing, const size_t *existing_len, si
     }
     *out = g_hostnames.data();
     *out_len = g_hostnames.size();
+    return TK_OK;
+}
+
+// ---- renderer records -------------------------------------------------------
+
+static thread_local std::string g_record;  // result of the record calls below
+
+int tk_render_record(const char *struct_name, size_t struct_name_len, const char *settings_json, size_t settings_len,
+                     const char **out, size_t *out_len) {
+    if (!out || !out_len) return set_err(nullptr, TK_EARG, "tk_render_record: NULL argument");
+    const RecordSpec *spec = find_record(sv(struct_name, struct_name_len));
+    if (!spec) return set_err(nullptr, TK_EARG, "tk_render_record: no such record struct: " + std::string(sv(struct_name, struct_name_len)));
+    Node *settings = nullptr;
+    std::string err;
+    if (settings_len && !parse_value(sv(settings_json, settings_len), false, &settings, &err)) return set_err(nullptr, TK_ESYNTAX, err);
+    g_record.clear();
+    const bool ok = render_record(*spec, settings, &g_record, &err);
+    free_node(settings);
+    if (!ok) return set_err(nullptr, TK_EARG, err);
+    *out = g_record.data();
+    *out_len = g_record.size();
+    return TK_OK;
+}
+
+int tk_record_struct_name(const char *kind, const char *provider, const char **out, size_t *out_len) {
+    if (!kind || !provider || !out || !out_len) return set_err(nullptr, TK_EARG, "tk_record_struct_name: NULL argument");
+    g_record = record_struct_name(kind, provider);
+    if (g_record.empty()) return set_err(nullptr, TK_EARG, std::string("no record struct for ") + kind + " / " + provider);
+    *out = g_record.data();
+    *out_len = g_record.size();
+    return TK_OK;
+}
+
+int tk_module_source(const char *kind, const char *provider, const char *source_url, const char *source_ref, const char **out,
+                     size_t *out_len) {
+    if (!kind || !provider || !out || !out_len) return set_err(nullptr, TK_EARG, "tk_module_source: NULL argument");
+    if (!module_source(kind, provider, source_url ? source_url : "", source_ref ? source_ref : "", &g_record))
+        return set_err(nullptr, TK_EARG, std::string("no terraform module for ") + kind + " / " + provider);
+    *out = g_record.data();
+    *out_len = g_record.size();
+    return TK_OK;
+}
+
+int tk_record_table(size_t index, const char **struct_name, const char **fields_json, size_t *fields_len) {
+    const RecordSpec *spec = record_at(index);
+    if (!spec) return TK_EARG;
+    g_record.clear();
+    record_table_json(*spec, &g_record);
+    if (struct_name) *struct_name = spec->go_name;
+    if (fields_json) *fields_json = g_record.data();
+    if (fields_len) *fields_len = g_record.size();
     return TK_OK;
 }
 

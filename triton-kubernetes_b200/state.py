@@ -28,7 +28,9 @@ SYMBOLS = [
     "tk_new_hostnames", "tk_state_stage", "tk_state_bytes_device", "tk_state_prefix_count_device",
     "tk_state_stream", "tk_kernel_launches", "tk_version", "tk_state_timing", "tk_state_kernel_stats",
     "tk_state_copy_stats", "tk_row_offsets_noalloc", "tk_state_host_tree_built", "tk_state_new_device",
-    "tk_set_default_timing",
+    "tk_set_default_timing", "tk_render_record", "tk_record_struct_name", "tk_module_source", "tk_record_table",
+    "tk_local_backend_new", "tk_backend_free", "tk_backend_last_error", "tk_backend_state", "tk_backend_delete_state",
+    "tk_backend_persist_state", "tk_backend_states", "tk_backend_state_terraform_config",
 ]
 
 _lib = None
@@ -47,6 +49,20 @@ def lib():
     L.tk_state_new.argtypes = [c_char_p, c_size_t, c_char_p, c_size_t, POINTER(P)]
     L.tk_state_new_device.argtypes = [c_char_p, c_size_t, P, c_size_t, POINTER(P)]
     L.tk_set_default_timing.argtypes = [c_int]
+    L.tk_render_record.argtypes = [c_char_p, c_size_t, c_char_p, c_size_t, POINTER(P), POINTER(c_size_t)]
+    L.tk_record_struct_name.argtypes = [c_char_p, c_char_p, POINTER(P), POINTER(c_size_t)]
+    L.tk_module_source.argtypes = [c_char_p, c_char_p, c_char_p, c_char_p, POINTER(P), POINTER(c_size_t)]
+    L.tk_record_table.argtypes = [c_size_t, POINTER(c_char_p), POINTER(P), POINTER(c_size_t)]
+    L.tk_local_backend_new.argtypes = [c_char_p, c_size_t, POINTER(P)]
+    L.tk_backend_free.argtypes = [P]
+    L.tk_backend_free.restype = None
+    L.tk_backend_last_error.argtypes = [P]
+    L.tk_backend_last_error.restype = c_char_p
+    L.tk_backend_state.argtypes = [P, c_char_p, c_size_t, POINTER(P)]
+    L.tk_backend_delete_state.argtypes = [P, c_char_p, c_size_t]
+    L.tk_backend_persist_state.argtypes = [P, P]
+    L.tk_backend_states.argtypes = [P, POINTER(P), POINTER(c_size_t), POINTER(c_size_t)]
+    L.tk_backend_state_terraform_config.argtypes = [P, c_char_p, c_size_t, POINTER(P), POINTER(c_size_t), POINTER(P), POINTER(c_size_t)]
     L.tk_state_new_empty.argtypes = [c_char_p, c_size_t, POINTER(P)]
     L.tk_state_free.argtypes = [P]
     L.tk_state_free.restype = None
@@ -133,10 +149,13 @@ def _pairs(ptr, n) -> dict:
 class State:
     """state.State (state/state.go:10-13) backed by a tk_state handle."""
 
-    def __init__(self, name, raw=None, device_ptr=None):
+    def __init__(self, name, raw=None, device_ptr=None, handle=None):
         L = lib()
         nm = _b(name)
         h = c_void_p()
+        if handle is not None:  # adopt a handle another call produced (the local backend)
+            self._h = handle
+            return
         if device_ptr is not None:  # (device address, length): text already in HBM
             rc = L.tk_state_new_device(nm, len(nm), device_ptr[0], device_ptr[1], byref(h))
         elif raw is None:
