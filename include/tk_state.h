@@ -202,8 +202,8 @@ TK_API int tk_state_copy_stats(tk_state *s, unsigned long long *h2d_bytes, unsig
  * State.Bytes() -- the escaped length of every output line and the running sum of those lengths
  * -- on a line tape the caller already holds in device memory (layout: csrc/tape.hpp), writing
  * n_rows + 1 offsets to off_out (off_out[r] = byte offset of line r, off_out[n_rows] = length of
- * the whole text).  All pointers except err are device pointers owned by the caller; arena must
- * be readable for 16 bytes past arena_bytes.  The work is enqueued on `stream` (a cudaStream_t,
+ * the whole text).  All pointers except err are device pointers owned by the caller; the row
+ * arrays must be 16-byte aligned and arena readable for 16 bytes past arena_bytes.  The work is enqueued on `stream` (a cudaStream_t,
  * NULL = default stream) and the call returns without waiting for it.
  *
  * It calls no cudaMalloc, cudaFree or other allocating routine.  The scan's scratch (a tile

@@ -482,8 +482,8 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     TokenBuffers tb{};
     for (;;) {
         if ((e = d_tok_pos_.reserve((cap + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(tokens)", err);
-        if ((e = d_tok_kind_.reserve(cap + 2)) != cudaSuccess) return fail(e, "cudaMalloc(tokens)", err);
-        if ((e = d_dec_bits_.reserve((cap + 31) / 32 * 4 + 8)) != cudaSuccess) return fail(e, "cudaMalloc(tokens)", err);
+        if ((e = d_tok_kind_.reserve(cap + 4096 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(tokens)", err);
+        if ((e = d_dec_bits_.reserve((cap + 31) / 32 * 4 + 1024)) != cudaSuccess) return fail(e, "cudaMalloc(tokens)", err);
         if ((e = d_scratch_.reserve(p1_scratch_words(n) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
         tb.pos = d_tok_pos_.as<uint32_t>(); tb.kind = d_tok_kind_.as<uint8_t>(); tb.decode_bits = d_dec_bits_.as<uint32_t>();
         tb.cap = (uint32_t)cap;
@@ -515,8 +515,8 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     // ---- brackets: compact, sort by level, pair
     BracketBuffers bb{};
     {
-        uint32_t **slots[9] = {&bb.tok, &bb.lvkind, &bb.match, &bb.parent, &bb.row, &bb.sort_a, &bb.sort_b, &bb.key_a, &bb.key_b};
-        for (int i = 0; i < 9; i++) {
+        uint32_t **slots[10] = {&bb.tok, &bb.lvkind, &bb.match, &bb.parent, &bb.row, &bb.sort_a, &bb.sort_b, &bb.key_a, &bb.key_b, &bb.ct};
+        for (int i = 0; i < 10; i++) {
             if ((e = d_br_[i].reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(brackets)", err);
             *slots[i] = d_br_[i].as<uint32_t>();
         }
@@ -525,7 +525,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     if ((e = d_flags_.reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(flags)", err);
     if ((e = d_zrank_.reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(zrank)", err);
     if ((e = d_scratch_.reserve(parse_scan_scratch_words(std::max(n_br, (n_tok + 31) / 32)) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
-    if ((e = timed(K_BRACKETS, [&] { return launch_brackets(tb, n_tok, tiles, bb, d_bitzeros_.as<unsigned int>(), stream_); })) != cudaSuccess)
+    if ((e = timed(K_BRACKETS, [&] { return launch_brackets(tb, n_tok, tiles, bb, d_bitzeros_.as<unsigned int>(), out->max_level, stream_); })) != cudaSuccess)
         return fail(e, "brackets", err);
     bool in_a = true;
     if ((e = timed(K_SORT_BRACKETS, [&] {

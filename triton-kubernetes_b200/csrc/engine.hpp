@@ -171,7 +171,7 @@ private:
 
     // parse work buffers
     DevBuf d_tok_pos_, d_tok_kind_, d_dec_bits_, d_tiles_, d_res_, d_bitzeros_;
-    DevBuf d_br_[9], d_flags_, d_zrank_, d_dec_tok_, d_dec_off_, d_dec_len_, d_dec_counts_, d_dec_offs_;
+    DevBuf d_br_[10], d_flags_, d_zrank_, d_dec_tok_, d_dec_off_, d_dec_len_, d_dec_counts_, d_dec_offs_;
     PinVec<ParseResult> h_res_;
     PinVec<unsigned long long> h_words_;
 

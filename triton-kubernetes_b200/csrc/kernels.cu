@@ -181,10 +181,12 @@ __device__ __forceinline__ void st_status(unsigned long long *p, unsigned long l
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+constexpr int RO_ITEMS = 8;                             // consecutive rows per thread
+constexpr int RO_TILE = EMIT_THREADS * RO_ITEMS;        // 2,048 rows per block: one look-back per 2,048 rows
+
 __global__ void __launch_bounds__(EMIT_THREADS) row_offsets_kernel(TapeView t, uint32_t *__restrict__ off,
                                                                   unsigned long long *scratch) {
-    __shared__ uint4 s_in[WARPS][WARP_IN_BYTES / 16];
-    __shared__ uint32_t s_warp_sum[WARPS];
+    __shared__ unsigned long long s_warp_sum[WARPS];
     __shared__ uint32_t s_tile;
     __shared__ unsigned long long s_prefix;
 
@@ -193,33 +195,52 @@ __global__ void __launch_bounds__(EMIT_THREADS) row_offsets_kernel(TapeView t, u
     __syncthreads();
     const uint32_t tile = s_tile;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t r = tile * EMIT_ROWS_PER_BLOCK + threadIdx.x;
-    const bool valid = r < t.n_rows;
+    const uint32_t r0 = tile * RO_TILE + threadIdx.x * RO_ITEMS;
 
-    Row w = {0, 0, 0, 0, 0};
-    if (valid) w = load_row(t, r);
-    // string bytes are only looked at for rows with a non-plain string; a warp without any skips
-    // the staging altogether and the pass reads nothing but the row descriptors
-    const uint8_t *src = t.arena;
-    if (__any_sync(FULL, valid && row_needs_bytes(w))) {
-        uint32_t base;
-        if (stage_warp_input(t, w, valid, s_in[warp], &base)) src = reinterpret_cast<const uint8_t *>(s_in[warp]) - base;
+    // a plain string is as long escaped as raw, so the common row needs nothing but its descriptor;
+    // the rare non-plain string is read straight from the arena
+    uint32_t len[RO_ITEMS];
+    unsigned long long sum = 0;
+    if (r0 + RO_ITEMS <= t.n_rows) {
+        uint32_t meta[RO_ITEMS], klen[RO_ITEMS], vlen[RO_ITEMS];
+#pragma unroll
+        for (int q = 0; q < RO_ITEMS / 4; q++) {
+            const uint4 m = __ldg(reinterpret_cast<const uint4 *>(t.meta + r0) + q);
+            const uint4 k = __ldg(reinterpret_cast<const uint4 *>(t.klen + r0) + q);
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(t.vlen + r0) + q);
+            meta[q * 4] = m.x; meta[q * 4 + 1] = m.y; meta[q * 4 + 2] = m.z; meta[q * 4 + 3] = m.w;
+            klen[q * 4] = k.x; klen[q * 4 + 1] = k.y; klen[q * 4 + 2] = k.z; klen[q * 4 + 3] = k.w;
+            vlen[q * 4] = v.x; vlen[q * 4 + 1] = v.y; vlen[q * 4 + 2] = v.z; vlen[q * 4 + 3] = v.w;
+        }
+#pragma unroll
+        for (int j = 0; j < RO_ITEMS; j++) {
+            Row w = {meta[j], 0, klen[j], 0, vlen[j]};
+            if (row_needs_bytes(w)) { w.koff = __ldg(t.koff + r0 + j); w.voff = __ldg(t.voff + r0 + j); }
+            len[j] = row_out_len(w, t.arena);
+            sum += len[j];
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < RO_ITEMS; j++) {
+            len[j] = 0;
+            if (r0 + j < t.n_rows) len[j] = row_out_len(load_row(t, r0 + j), t.arena);
+            sum += len[j];
+        }
     }
-    const uint32_t len = valid ? row_out_len(w, src) : 0;
 
-    // inclusive scan inside the warp, then across the 8 warps
-    uint32_t incl = len;
+    // inclusive scan of the per-thread sums inside the warp, then across the 8 warps
+    unsigned long long incl = sum;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t v = __shfl_up_sync(FULL, incl, d);
+        const unsigned long long v = __shfl_up_sync(FULL, incl, d);
         if (lane >= (uint32_t)d) incl += v;
     }
     if (lane == 31) s_warp_sum[warp] = incl;
     __syncthreads();
-    uint32_t warp_excl = 0, block_sum = 0;
+    unsigned long long warp_excl = 0, block_sum = 0;
 #pragma unroll
     for (int i = 0; i < WARPS; i++) {
-        const uint32_t v = s_warp_sum[i];
+        const unsigned long long v = s_warp_sum[i];
         if ((uint32_t)i < warp) warp_excl += v;
         block_sum += v;
     }
@@ -252,13 +273,17 @@ __global__ void __launch_bounds__(EMIT_THREADS) row_offsets_kernel(TapeView t, u
         }
         if (lane == 0) {
             s_prefix = prefix;
-            if ((tile + 1) * (uint32_t)EMIT_ROWS_PER_BLOCK >= t.n_rows) scratch[1] = prefix + block_sum;  // total
+            if ((unsigned long long)(tile + 1) * RO_TILE >= t.n_rows) scratch[1] = prefix + block_sum;  // total
         }
     }
     __syncthreads();
-    const unsigned long long o = s_prefix + warp_excl + (incl - len);
-    if (valid) off[r] = (uint32_t)o;
-    if (valid && r + 1 == t.n_rows) off[r + 1] = (uint32_t)(o + len);
+    unsigned long long o = s_prefix + warp_excl + (incl - sum);
+#pragma unroll
+    for (int j = 0; j < RO_ITEMS; j++) {
+        if (r0 + j < t.n_rows) off[r0 + j] = (uint32_t)o;
+        o += len[j];
+        if (r0 + j + 1 == t.n_rows) off[r0 + j + 1] = (uint32_t)o;
+    }
 }
 
 // ---- K2: emit -------------------------------------------------------------------------------
@@ -332,7 +357,6 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const ui
     if (valid) { w = load_row(t, r); o = __ldg(off + r); }
     uint32_t base;
     const bool staged = stage_warp_input(t, w, valid, s_in[warp], &base);
-    const uint8_t *src = staged ? reinterpret_cast<const uint8_t *>(s_in[warp]) - base : t.arena;
 
     const uint32_t r_end = min(r0 + 32u, t.n_rows);
     const uint32_t out0 = __ldg(off + r0), out1 = __ldg(off + r_end);  // off has n_rows + 1 entries
@@ -341,13 +365,26 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const ui
     const bool fits = shift + span <= (uint32_t)WARP_OUT_BYTES;        // else: straight to global memory
 
     uint8_t *slice = reinterpret_cast<uint8_t *>(s_out[warp]);
-    uint8_t *dst = fits ? slice : out;
     Deferred dk = {0, 0, 0}, dv = {0, 0, 0};
-    // phase 1: every lane writes its own line, leaving long plain runs for phase 2
-    if (valid) put_line(dst, fits ? o - out0 + shift : o, w, src, &dk, &dv);
-    // phase 2: the warp copies the long runs together, 32 bytes per step
-    warp_copy_deferred(dst, src, dk, lane);
-    warp_copy_deferred(dst, src, dv, lane);
+    if (staged && fits) {
+        // the usual case, kept apart so that every access below is a 32-bit shared-memory access:
+        // arena byte x is s_src[x - base]; output byte y is slice[y - out0 + shift]
+        const uint8_t *s_src = reinterpret_cast<const uint8_t *>(s_in[warp]);
+        Row v = w;
+        v.koff -= base; v.voff -= base;
+        // phase 1: every lane writes its own line, leaving long plain runs for phase 2
+        if (valid) put_line(slice, o - out0 + shift, v, s_src, &dk, &dv);
+        // phase 2: the warp copies the long runs together, 32 bytes per step
+        warp_copy_deferred(slice, s_src, dk, lane);
+        warp_copy_deferred(slice, s_src, dv, lane);
+    } else {
+        // a tile that outgrew its staging: same steps on generic pointers
+        const uint8_t *src = staged ? reinterpret_cast<const uint8_t *>(s_in[warp]) - base : t.arena;
+        uint8_t *dst = fits ? slice : out;
+        if (valid) put_line(dst, fits ? o - out0 + shift : o, w, src, &dk, &dv);
+        warp_copy_deferred(dst, src, dk, lane);
+        warp_copy_deferred(dst, src, dv, lane);
+    }
     if (!fits) return;
     __syncwarp();
     // copy out: whole 16-byte chunks as vectors, the ragged head and tail bytewise
@@ -405,7 +442,7 @@ __global__ void __launch_bounds__(PREFIX_THREADS) prefix_match_kernel(KeyIndexVi
 cudaError_t launch_row_offsets(const TapeView &t, uint32_t *off, unsigned long long *scratch, cudaStream_t s) {
     cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words(t.n_rows) * sizeof(unsigned long long), s);
     if (e != cudaSuccess) return e;
-    row_offsets_kernel<<<emit_tiles(t.n_rows), EMIT_THREADS, 0, s>>>(t, off, scratch);
+    row_offsets_kernel<<<(t.n_rows + RO_TILE - 1) / RO_TILE, EMIT_THREADS, 0, s>>>(t, off, scratch);
     g_launches++;
     return cudaGetLastError();
 }
@@ -481,6 +518,10 @@ extern "C" int tk_row_offsets_noalloc(const uint32_t *meta, const uint32_t *koff
         noalloc_err(err, err_cap, "tk_row_offsets_noalloc: NULL argument");
         return TK_EARG;
     }
+    if ((reinterpret_cast<uintptr_t>(meta) | reinterpret_cast<uintptr_t>(klen) | reinterpret_cast<uintptr_t>(vlen)) & 15u) {
+        noalloc_err(err, err_cap, "tk_row_offsets_noalloc: meta, klen and vlen must be 16-byte aligned");
+        return TK_EARG;
+    }
     if (n_rows == 0 || n_rows > TK_NOALLOC_MAX_ROWS) {
         if (err && err_cap)
             snprintf(err, err_cap, "tk_row_offsets_noalloc: n_rows = %u is outside 1..%u (the fixed scratch holds one status word per %d rows)",
@@ -518,7 +559,7 @@ extern "C" int tk_row_offsets_noalloc(const uint32_t *meta, const uint32_t *koff
     // the array still holds the previous call's counter and status words: they must start at zero
     e = cudaMemsetAsync(scratch, 0, tk::scan_scratch_words(n_rows) * sizeof(unsigned long long), s);
     if (e == cudaSuccess) {
-        tk::row_offsets_kernel<<<tk::emit_tiles(n_rows), tk::EMIT_THREADS, 0, s>>>(t, off_out, scratch);
+        tk::row_offsets_kernel<<<(n_rows + tk::RO_TILE - 1) / tk::RO_TILE, tk::EMIT_THREADS, 0, s>>>(t, off_out, scratch);
         tk::g_launches++;
         e = cudaGetLastError();
     }

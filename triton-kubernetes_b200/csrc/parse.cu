@@ -457,44 +457,104 @@ __device__ __forceinline__ TokLocal tile_scan(int dd, uint32_t row, uint32_t br,
     return t;
 }
 
-// Each block takes PREFIX_SUB consecutive 256-token tiles, so the (latency-bound) look-back runs
-// once per 4,096 tokens while the later passes still get one prefix per 256-token tile.
-constexpr int PREFIX_SUB = 16;
+// ---- token passes with TP_ITEMS consecutive tokens per thread: one block-wide scan per 4,096
+//      tokens; the per-256-token TilePrefix array is still what the later passes index.
 
-__global__ void __launch_bounds__(TOK_TILE) token_prefix_kernel(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, u64 *scratch,
-                                                               ParseResult *res) {
+constexpr int TP_ITEMS = 16;
+constexpr int TP_THREADS = 256;
+constexpr int TP_BLOCK = TP_THREADS * TP_ITEMS;        // 4,096 tokens = 16 tiles of TOK_TILE
+constexpr int TP_TILES = TP_BLOCK / TOK_TILE;
+
+// kinds of tokens [base - 4, base + TP_ITEMS + 4) as bytes k[0 .. 23]; 0xff outside the stream
+struct KindWindow {
+    uint32_t w[6];
+    __device__ __forceinline__ uint32_t at(int j) const { return (w[(j + 4) >> 2] >> (((j + 4) & 3) * 8)) & 0xffu; }  // j in [-4, 20)
+};
+__device__ __forceinline__ KindWindow load_kinds(const uint8_t *kind, uint32_t base, uint32_t n_tok) {
+    KindWindow kw;
+    const uint32_t *p = reinterpret_cast<const uint32_t *>(kind);  // base is a multiple of 16
+#pragma unroll
+    for (int q = 0; q < 6; q++) {
+        const long long first = (long long)base - 4 + q * 4;
+        uint32_t v = 0xffffffffu;
+        if (first >= 0 && first < (long long)n_tok) {
+            v = __ldg(p + (first >> 2));
+            if (first + 4 > (long long)n_tok) v |= 0xffffffffu << ((n_tok - (uint32_t)first) * 8);  // tokens past the end read as 0xff
+        }
+        kw.w[q] = v;
+    }
+    return kw;
+}
+__device__ __forceinline__ bool emits_row_k(uint32_t k, uint32_t prev, uint32_t next2) {
+    if (k == T_SCALAR || is_opener(k)) return true;
+    if (k == T_STR_OPEN) return next2 != T_COLON;
+    if (is_closer(k)) return !is_opener(prev);
+    return false;
+}
+
+// exclusive block scan of (depth delta, rows, brackets) over TP_THREADS threads, plus block totals
+__device__ __forceinline__ void block_scan3(int d, uint32_t r, uint32_t b, int *ed, uint32_t *er, uint32_t *eb, int *td, uint32_t *tr,
+                                            uint32_t *tbk) {
+    __shared__ int s_d[TP_THREADS / 32];
+    __shared__ uint32_t s_r[TP_THREADS / 32], s_b[TP_THREADS / 32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int xd = d;
+    uint32_t xr = r, xb = b;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int yd = __shfl_up_sync(FULL, xd, o);
+        const uint32_t yr = __shfl_up_sync(FULL, xr, o), yb = __shfl_up_sync(FULL, xb, o);
+        if (lane >= (uint32_t)o) { xd += yd; xr += yr; xb += yb; }
+    }
+    if (lane == 31) { s_d[warp] = xd; s_r[warp] = xr; s_b[warp] = xb; }
+    __syncthreads();
+    int wd = 0, sd = 0;
+    uint32_t wr = 0, wb = 0, sr = 0, sb = 0;
+#pragma unroll
+    for (uint32_t i = 0; i < TP_THREADS / 32; i++) {
+        if (i < warp) { wd += s_d[i]; wr += s_r[i]; wb += s_b[i]; }
+        sd += s_d[i]; sr += s_r[i]; sb += s_b[i];
+    }
+    *ed = wd + xd - d; *er = wr + xr - r; *eb = wb + xb - b;
+    *td = sd; *tr = sr; *tbk = sb;
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(TP_THREADS) token_prefix_kernel(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, u64 *scratch,
+                                                                 ParseResult *res) {
     __shared__ uint32_t s_blk;
     __shared__ int s_pd;
     __shared__ uint32_t s_pr, s_pb;
-    __shared__ int s_sub_d[PREFIX_SUB];       // running totals before each sub-tile, relative to the block
-    __shared__ uint32_t s_sub_r[PREFIX_SUB], s_sub_b[PREFIX_SUB];
+    __shared__ int s_mn[TP_THREADS / 32], s_mx[TP_THREADS / 32];
     if (threadIdx.x == 0) s_blk = (uint32_t)atomicAdd(&scratch[0], 1ull);
     __syncthreads();
     const uint32_t blk = s_blk, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t n_tiles = (n_tok + TOK_TILE - 1) / TOK_TILE;
-    const uint32_t n_blocks = (n_tiles + PREFIX_SUB - 1) / PREFIX_SUB;
-    int run_d = 0, blk_mn = 0x7fffffff, blk_mx = -0x7fffffff;
-    uint32_t run_r = 0, run_b = 0;
-    for (int sub = 0; sub < PREFIX_SUB; sub++) {
-        const uint32_t tile = blk * PREFIX_SUB + sub;
-        if (tile >= n_tiles) break;   // uniform across the block
-        const uint32_t i = tile * TOK_TILE + threadIdx.x;
-        uint32_t k = 0xff;
-        if (i < n_tok) k = tb.kind[i];
-        const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
-        const uint32_t row = (i < n_tok && emits_row(tb.kind, i, n_tok, k)) ? 1u : 0u;
-        int td, mn, mx;
-        uint32_t tr, tbk;
-        tile_scan(dd, row, dd != 0, &td, &tr, &tbk, &mn, &mx);
-        if (threadIdx.x == 0) { s_sub_d[sub] = run_d; s_sub_r[sub] = run_r; s_sub_b[sub] = run_b; }
-        blk_mn = min(blk_mn, run_d + mn);
-        blk_mx = max(blk_mx, run_d + mx);
-        run_d += td; run_r += tr; run_b += tbk;
-    }
-    const int td = run_d;
-    const uint32_t tr = run_r, tbk = run_b;
+    const uint32_t n_blocks = (n_tok + TP_BLOCK - 1) / TP_BLOCK;
+    const uint32_t base = blk * TP_BLOCK + threadIdx.x * TP_ITEMS;
 
-    // two look-backs side by side: warp 0 carries (rows, brackets), warp 1 carries depth
+    // ---- this thread's 16 tokens
+    const KindWindow kw = load_kinds(tb.kind, base, n_tok);
+    int d = 0, mn = 0x7fffffff, mx = -0x7fffffff;
+    uint32_t r = 0, b = 0;
+#pragma unroll
+    for (int j = 0; j < TP_ITEMS; j++) {
+        const uint32_t k = kw.at(j);
+        const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
+        d += dd;
+        b += dd != 0;
+        r += emits_row_k(k, kw.at(j - 1), kw.at(j + 2)) ? 1u : 0u;
+        if (k != 0xff) { mn = min(mn, d); mx = max(mx, d); }
+    }
+    int ed, td;
+    uint32_t er, eb, tr, tbk;
+    block_scan3(d, r, b, &ed, &er, &eb, &td, &tr, &tbk);
+    if (mn != 0x7fffffff) { mn += ed; mx += ed; }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) { mn = min(mn, __shfl_xor_sync(FULL, mn, o)); mx = max(mx, __shfl_xor_sync(FULL, mx, o)); }
+    if (lane == 0) { s_mn[warp] = mn; s_mx[warp] = mx; }
+
+    // ---- two look-backs side by side: warp 0 carries (rows, brackets), warp 1 carries depth
     u64 *statusX = scratch + 4, *statusY = scratch + 4 + n_blocks;
     if (warp < 2) {
         u64 *status = warp == 0 ? statusX : statusY;
@@ -515,7 +575,7 @@ __global__ void __launch_bounds__(TOK_TILE) token_prefix_kernel(TokenBuffers tb,
                 u64 x = 0;
                 if ((int)lane <= first) x = warp == 0 ? (s & ST_MASK) : (u64)((long long)(s & ST_MASK) - (1ll << 40));
 #pragma unroll
-                for (int d = 16; d; d >>= 1) x += __shfl_xor_sync(FULL, x, d);
+                for (int o = 16; o; o >>= 1) x += __shfl_xor_sync(FULL, x, o);
                 prefix += x;
                 if (pm) break;
                 look -= 32;
@@ -531,19 +591,24 @@ __global__ void __launch_bounds__(TOK_TILE) token_prefix_kernel(TokenBuffers tb,
         }
     }
     __syncthreads();
-    if (threadIdx.x < PREFIX_SUB) {
-        const uint32_t tile = blk * PREFIX_SUB + threadIdx.x;
+    // one TilePrefix per 256 tokens: every 16th thread stands at a tile boundary
+    if ((threadIdx.x & (TOK_TILE / TP_ITEMS - 1)) == 0) {
+        const uint32_t tile = blk * TP_TILES + threadIdx.x / (TOK_TILE / TP_ITEMS);
         if (tile < n_tiles) {
             TilePrefix p;
-            p.depth = s_pd + s_sub_d[threadIdx.x]; p.rows = s_pr + s_sub_r[threadIdx.x]; p.brackets = s_pb + s_sub_b[threadIdx.x]; p.pad = 0;
+            p.depth = s_pd + ed; p.rows = s_pr + er; p.brackets = s_pb + eb; p.pad = 0;
             tiles[tile] = p;
         }
     }
     if (threadIdx.x == 0) {
-        if (s_pd + blk_mn < 0) res->invalid = 1;                                  // a closer with nothing open
-        const int hi = s_pd + blk_mx;
-        if (hi > 10000) res->invalid = 1;                                         // exceeded max depth
-        if (hi > 0) atomicMax(&res->max_level, (unsigned)min(hi, 16383));
+        int bmn = s_mn[0], bmx = s_mx[0];
+        for (uint32_t i = 1; i < TP_THREADS / 32; i++) { bmn = min(bmn, s_mn[i]); bmx = max(bmx, s_mx[i]); }
+        if (bmn != 0x7fffffff) {
+            if (s_pd + bmn < 0) res->invalid = 1;                                 // a closer with nothing open
+            const int hi = s_pd + bmx;
+            if (hi > 10000) res->invalid = 1;                                     // exceeded max depth
+            if (hi > 0) atomicMax(&res->max_level, (unsigned)min(hi, 16383));
+        }
         if (blk + 1 == n_blocks) {
             res->n_rows = s_pr + tr;
             res->n_brackets = s_pb + tbk;
@@ -557,34 +622,52 @@ __global__ void __launch_bounds__(TOK_TILE) token_prefix_kernel(TokenBuffers tb,
 // P2b: bracket tokens with their level; identity permutation for the sort
 // =================================================================================================
 
-__global__ void __launch_bounds__(TOK_TILE) brackets_kernel(TokenBuffers tb, uint32_t n_tok, const TilePrefix *__restrict__ tiles,
-                                                           BracketBuffers bb, unsigned int *bit_zeros) {
+__global__ void __launch_bounds__(TP_THREADS) brackets_kernel(TokenBuffers tb, uint32_t n_tok, const TilePrefix *__restrict__ tiles,
+                                                             BracketBuffers bb, unsigned int *bit_zeros, int n_bits) {
     __shared__ unsigned int s_zero[16];
     if (threadIdx.x < 16) s_zero[threadIdx.x] = 0;
-    const uint32_t i = blockIdx.x * TOK_TILE + threadIdx.x;
-    uint32_t k = 0xff;
-    if (i < n_tok) k = tb.kind[i];
-    const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
-    int td, mn, mx;
-    uint32_t tr, tbk;
-    const TokLocal t = tile_scan(dd, 0, dd != 0, &td, &tr, &tbk, &mn, &mx);
-    const TilePrefix p = tiles[blockIdx.x];
-    if (dd != 0) {
-        const uint32_t b = p.brackets + t.br_before;
-        int level = p.depth + t.depth_before + (dd > 0 ? 1 : 0);
-        level = max(0, min(level, 16383));
-        bb.tok[b] = i;
-        bb.lvkind[b] = ((uint32_t)level << 8) | k;
-        bb.sort_a[b] = b;
-        bb.key_a[b] = (uint32_t)level;
-        bb.parent[b] = 0xffffffffu;
-        bb.match[b] = 0xffffffffu;
-        bb.row[b] = 0xffffffffu;
-        for (int bit = 0; bit < 14; bit++)
-            if (!((level >> bit) & 1)) atomicAdd(&s_zero[bit], 1u);
+    const uint32_t base = blockIdx.x * TP_BLOCK + threadIdx.x * TP_ITEMS;
+    const KindWindow kw = load_kinds(tb.kind, base, n_tok);
+    int d = 0;
+    uint32_t b = 0;
+#pragma unroll
+    for (int j = 0; j < TP_ITEMS; j++) {
+        const uint32_t k = kw.at(j);
+        const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
+        d += dd;
+        b += dd != 0;
+    }
+    int ed, td;
+    uint32_t er, eb, tr, tbk;
+    block_scan3(d, 0, b, &ed, &er, &eb, &td, &tr, &tbk);
+    if (b != 0) {
+        const TilePrefix p = tiles[blockIdx.x * TP_TILES];
+        int depth = p.depth + ed;
+        uint32_t bi = p.brackets + eb;
+#pragma unroll
+        for (int j = 0; j < TP_ITEMS; j++) {
+            const uint32_t k = kw.at(j);
+            const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
+            if (dd != 0) {
+                int level = depth + (dd > 0 ? 1 : 0);
+                level = max(0, min(level, 16383));
+                bb.tok[bi] = base + j;
+                bb.lvkind[bi] = ((uint32_t)level << 8) | k;
+                bb.sort_a[bi] = bi;
+                bb.key_a[bi] = (uint32_t)level;
+                bb.parent[bi] = 0xffffffffu;
+                bb.match[bi] = 0xffffffffu;
+                bb.row[bi] = 0xffffffffu;
+                bb.ct[bi] = 0;
+                for (int bit = 0; bit < n_bits; bit++)
+                    if (!((level >> bit) & 1)) atomicAdd(&s_zero[bit], 1u);
+                bi++;
+            }
+            depth += dd;
+        }
     }
     __syncthreads();
-    if (threadIdx.x < 14 && s_zero[threadIdx.x]) atomicAdd(&bit_zeros[threadIdx.x], s_zero[threadIdx.x]);
+    if (threadIdx.x < (unsigned)n_bits && s_zero[threadIdx.x]) atomicAdd(&bit_zeros[threadIdx.x], s_zero[threadIdx.x]);
 }
 
 // one stable split by bit `bit` of the key: zeros first
@@ -608,6 +691,8 @@ __global__ void split_scatter_kernel(const uint32_t *__restrict__ key, const uin
 // P2d: pairs and enclosing openers from the level-sorted order
 // =================================================================================================
 
+enum { CT_TOP = 0, CT_OBJ = 1, CT_ARR = 2 };
+
 __global__ void match_kernel(BracketBuffers bb, const uint32_t *__restrict__ sorted, const uint32_t *__restrict__ skey, uint32_t n_br,
                              ParseResult *res) {
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -626,16 +711,25 @@ __global__ void match_kernel(BracketBuffers bb, const uint32_t *__restrict__ sor
     bb.match[o] = c;
     bb.match[c] = o;
     const uint32_t level = skey[j];
-    if (level <= 1) return;
-    // enclosing opener: the last bracket of level-1 that lies before o
-    uint32_t lo = 0, hi = n_br;  // first position whose (key, bracket) >= (level-1, o)
-    while (lo < hi) {
-        const uint32_t mid = (lo + hi) >> 1;
-        const uint32_t mk = skey[mid];
-        if (mk < level - 1 || (mk == level - 1 && sorted[mid] < o)) lo = mid + 1; else hi = mid;
+    const uint32_t inside = ko == T_LBRACE ? CT_OBJ : CT_ARR;   // the container this pair delimits
+    uint32_t outside = CT_TOP;                                    // the container the pair sits in
+    if (level > 1) {
+        // enclosing opener: the last bracket of level-1 that lies before o
+        uint32_t lo = 0, hi = n_br;  // first position whose (key, bracket) >= (level-1, o)
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            const uint32_t mk = skey[mid];
+            if (mk < level - 1 || (mk == level - 1 && sorted[mid] < o)) lo = mid + 1; else hi = mid;
+        }
+        if (lo == 0 || skey[lo - 1] != level - 1) { res->invalid = 1; return; }
+        const uint32_t par = sorted[lo - 1];
+        bb.parent[o] = par;
+        outside = (bb.lvkind[par] & 0xff) == T_LBRACE ? CT_OBJ : CT_ARR;
     }
-    if (lo == 0 || skey[lo - 1] != level - 1) { res->invalid = 1; return; }
-    bb.parent[o] = sorted[lo - 1];
+    // per bracket: bits 0-1 the container tokens AFTER it sit in, bits 2-3 the container the
+    // bracket token itself is judged in (an opener: where it sits; a closer: what it closes)
+    bb.ct[o] = inside | (outside << 2);
+    bb.ct[c] = outside | (inside << 2);
 }
 
 // =================================================================================================
@@ -805,154 +899,177 @@ __device__ __forceinline__ uint32_t next_sig(const uint8_t *kind, uint32_t i, ui
     return i < n_tok ? kind[i] : 0xff;
 }
 
-enum { CT_TOP = 0, CT_OBJ = 1, CT_ARR = 2 };
 
-__global__ void __launch_bounds__(TOK_TILE) rows_kernel(const uint8_t *__restrict__ raw, u64 n, TokenBuffers tb, uint32_t n_tok,
-                                                       const TilePrefix *__restrict__ tiles, BracketBuffers bb, DecodeBuffers db,
-                                                       uint32_t n_dec, RowBuffers rb, uint32_t n_rows, ParseResult *res) {
-    const uint32_t i = blockIdx.x * TOK_TILE + threadIdx.x;
-    const uint8_t *kind = tb.kind;
-    uint32_t k = 0xff;
-    if (i < n_tok) k = kind[i];
-    const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
-    const uint32_t row = (i < n_tok && emits_row(kind, i, n_tok, k)) ? 1u : 0u;
-    int td, mn, mx;
-    uint32_t tr, tbk;
-    const TokLocal t = tile_scan(dd, row, dd != 0, &td, &tr, &tbk, &mn, &mx);
-    if (i >= n_tok || k == T_SCALAR_END || k == T_STR_CLOSE) return;
-    const TilePrefix p = tiles[blockIdx.x];
-    const int depth = p.depth + t.depth_before;
-    const uint32_t r = p.rows + t.rows_before;
-    const uint32_t brb = p.brackets + t.br_before;  // brackets before this token
+constexpr int RW_ITEMS = 8;                        // consecutive tokens per thread: about one object member
+constexpr int RW_BLOCK = TP_THREADS * RW_ITEMS;   // 2,048 tokens per block = 8 tiles of TOK_TILE
 
-    // previous significant token
-    uint32_t pi = i, pk = 0xfe;  // 0xfe: start of input
-    if (i > 0) { pi = i - 1; if (kind[pi] == T_SCALAR_END) pi--; pk = kind[pi]; }
+// Go's scanner grammar as a table: for the container a token sits in and the token's kind, the
+// set of kinds the previous significant token may have.  A string is a KEY exactly when a colon
+// follows its closing quote, so "key in value position", "value in key position", "key in an
+// array" and the like all show up as a (previous, current) pair the table does not allow.
+enum { G_START = 0, G_LBRACE, G_RBRACE, G_LBRACKET, G_RBRACKET, G_COLON, G_COMMA, G_KEY_OPEN, G_KEY_CLOSE, G_VAL_OPEN, G_VAL_CLOSE, G_SCALAR, G_N };
+constexpr uint32_t gbit(int k) { return 1u << k; }
+constexpr uint32_t G_VALUE_END = gbit(G_VAL_CLOSE) | gbit(G_SCALAR) | gbit(G_RBRACE) | gbit(G_RBRACKET);
+// allowed[container][current kind] = mask of allowed previous kinds
+__constant__ uint32_t g_allowed[3][G_N] = {
+    // CT_TOP: one value, nothing after it
+    {0, gbit(G_START), 0, gbit(G_START), 0, 0, 0, 0, 0, gbit(G_START), gbit(G_VAL_OPEN), gbit(G_START)},
+    // CT_OBJ
+    {0, gbit(G_COLON), gbit(G_LBRACE) | G_VALUE_END, gbit(G_COLON), 0, gbit(G_KEY_CLOSE), G_VALUE_END,
+     gbit(G_LBRACE) | gbit(G_COMMA), gbit(G_KEY_OPEN), gbit(G_COLON), gbit(G_VAL_OPEN), gbit(G_COLON)},
+    // CT_ARR
+    {0, gbit(G_LBRACKET) | gbit(G_COMMA), 0, gbit(G_LBRACKET) | gbit(G_COMMA), gbit(G_LBRACKET) | G_VALUE_END, 0, G_VALUE_END,
+     0, 0, gbit(G_LBRACKET) | gbit(G_COMMA), gbit(G_VAL_OPEN), gbit(G_LBRACKET) | gbit(G_COMMA)},
+};
 
-    // container this token sits in (for a closer: the container it closes)
-    uint32_t ct = CT_TOP, my_b = 0xffffffffu;
-    if (dd != 0) my_b = brb;
-    if (is_closer(k)) {
-        const uint32_t o = bb.match[my_b];
-        if (o == 0xffffffffu) { res->invalid = 1; return; }
-        ct = (bb.lvkind[o] & 0xff) == T_LBRACE ? CT_OBJ : CT_ARR;
-    } else if (depth > 0) {
-        if (brb == 0) { res->invalid = 1; return; }
-        uint32_t b = brb - 1;  // nearest bracket before the token
-        if (is_closer(bb.lvkind[b] & 0xff)) {
-            const uint32_t o = bb.match[b];
-            b = o == 0xffffffffu ? 0xffffffffu : bb.parent[o];
-        }
-        if (b == 0xffffffffu) { res->invalid = 1; return; }
-        ct = (bb.lvkind[b] & 0xff) == T_LBRACE ? CT_OBJ : CT_ARR;
-    }
-
-    const bool prev_value_end = pk == T_STR_CLOSE || pk == T_SCALAR || is_closer(pk);
-    bool ok = true;
-    bool is_key = false;
+// kind of token x in grammar terms; `next` is the kind of the token after x (needed for quotes)
+__device__ __forceinline__ uint32_t gkind(uint32_t k, uint32_t next, uint32_t next2) {
     switch (k) {
-    case T_COLON: {
-        // only after a key string inside an object
-        bool key_before = false;
-        if (pk == T_STR_CLOSE && pi >= 1) {
-            const uint32_t so = pi - 1;  // its opening quote
-            uint32_t qk = 0xfe;
-            if (so > 0) { uint32_t q = so - 1; if (kind[q] == T_SCALAR_END) q--; qk = kind[q]; }
-            key_before = qk == T_LBRACE || qk == T_COMMA;
-        }
-        ok = ct == CT_OBJ && key_before;
-        break;
+    case T_LBRACE: return G_LBRACE;
+    case T_RBRACE: return G_RBRACE;
+    case T_LBRACKET: return G_LBRACKET;
+    case T_RBRACKET: return G_RBRACKET;
+    case T_COLON: return G_COLON;
+    case T_COMMA: return G_COMMA;
+    case T_STR_OPEN: return next2 == T_COLON ? G_KEY_OPEN : G_VAL_OPEN;   // open, close, colon
+    case T_STR_CLOSE: return next == T_COLON ? G_KEY_CLOSE : G_VAL_CLOSE;
+    default: return G_SCALAR;
     }
-    case T_COMMA:
-        ok = ct != CT_TOP && prev_value_end;
-        if (ok && ct == CT_OBJ && pk == T_STR_CLOSE) {
-            // the string before the comma must have been a value, i.e. preceded by a colon
-            const uint32_t so = pi - 1;
-            uint32_t qk = 0xfe;
-            if (so > 0) { uint32_t q = so - 1; if (kind[q] == T_SCALAR_END) q--; qk = kind[q]; }
-            ok = qk == T_COLON;
-        }
-        break;
-    case T_RBRACE:
-        ok = ct == CT_OBJ && (pk == T_LBRACE || prev_value_end);
-        if (ok && pk == T_STR_CLOSE) {
-            const uint32_t so = pi - 1;
-            uint32_t qk = 0xfe;
-            if (so > 0) { uint32_t q = so - 1; if (kind[q] == T_SCALAR_END) q--; qk = kind[q]; }
-            ok = qk == T_COLON;
-        }
-        break;
-    case T_RBRACKET:
-        ok = ct == CT_ARR && (pk == T_LBRACKET || prev_value_end);
-        break;
-    default:  // value starts: string, scalar, opener
-        if (ct == CT_TOP) ok = pk == 0xfe;
-        else if (ct == CT_ARR) ok = pk == T_LBRACKET || pk == T_COMMA;
-        else {
-            if (k == T_STR_OPEN && (pk == T_LBRACE || pk == T_COMMA)) {
-                is_key = true;
-                ok = (i + 2 < n_tok) && kind[i + 2] == T_COLON;
-            } else {
-                ok = pk == T_COLON;
-            }
-        }
-        if (k == T_STR_OPEN && ok) ok = (i + 1 < n_tok) && kind[i + 1] == T_STR_CLOSE;
-        break;
-    }
-    if (!ok) { res->invalid = 1; return; }
-    if (k == T_COLON || k == T_COMMA || is_key) return;
+}
 
-    // ---- this token owns a row?
-    if (is_closer(k)) {
-        if (is_opener(pk)) return;  // empty container: the opener's row says {} / []
+// grammar check of token i and, if it owns one, its tape row
+// (inlined once into the non-unrolled token loop of rows_kernel; ct and dbits are the block's
+// slices of bb.ct and tb.decode_bits, staged in shared memory and indexable by global number)
+__device__ __forceinline__ void token_row(const uint8_t *__restrict__ raw, u64 n, const TokenBuffers &tb, uint32_t n_tok,
+                                          const BracketBuffers &bb, const uint8_t *ct_s, const uint32_t *dbits, const DecodeBuffers &db,
+                                          uint32_t n_dec, const RowBuffers &rb, uint32_t n_rows, ParseResult *res, uint32_t i,
+                                          uint32_t k, int depth, uint32_t r, uint32_t brb, uint32_t row, int dd) {
+    const uint8_t *kind = tb.kind;   // readable 8 tokens either side of i; 0xff outside the stream
+    const uint32_t k1 = kind[i + 1], k2 = kind[i + 2];
+    const uint32_t next = k1 == T_SCALAR_END ? k2 : k1;   // next significant token
+
+    // previous significant token, in grammar terms
+    uint32_t pg = G_START;
+    if (i > 0) {
+        uint32_t pi = i - 1;
+        if (kind[pi] == T_SCALAR_END) pi--;
+        pg = gkind(kind[pi], kind[pi + 1] == T_SCALAR_END ? kind[pi + 2] : kind[pi + 1], kind[pi + 2]);
     }
-    if (!row || r >= n_rows) {
-        if (!row) { res->invalid = 1; }  // a value the row count did not foresee: token stream is inconsistent
-        return;
-    }
+    const uint32_t g = gkind(k, k1, k2);
+
+    // container: one look-up in the per-bracket table match_kernel filled
+    uint32_t ct = CT_TOP;
+    const uint32_t my_b = brb;   // for a bracket token: its own index
+    if (dd != 0) ct = (ct_s[my_b] >> 2) & 3u;
+    else if (brb > 0) ct = ct_s[brb - 1] & 3u;
+    if (ct > CT_ARR) ct = CT_TOP;   // unmatched bracket: match_kernel has already said invalid
+    if (!((g_allowed[ct][g] >> pg) & 1u)) { res->invalid = 1; return; }
+    if (g == G_VAL_OPEN && k1 != T_STR_CLOSE) { res->invalid = 1; return; }   // unterminated (cannot pass P1, kept as a guard)
+    if (!row) return;   // colons, commas, keys, closers of empty containers
+    if (r >= n_rows) { res->invalid = 1; return; }
+
     uint32_t meta = 0, koff = 0, klen = 0, voff = 0, vlen = 0;
-    uint32_t end_tok = i;  // last token of the value, to look for the comma after it
-    if (is_closer(k)) {
+    uint32_t after = next;  // the significant token after the value, to look for the comma
+    if (dd < 0) {
         if (depth < 1) { res->invalid = 1; return; }
         meta = (k == T_RBRACE ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR) | ((uint32_t)(depth - 1) << META_DEPTH_SHIFT);
         koff = bb.match[my_b];  // the opener's bracket: key_order and the module index find its row through bb.row
         bb.row[my_b] = r;
     } else {
-        if (is_opener(k)) {
-            const bool empty = (i + 1 < n_tok) && is_closer(kind[i + 1]);
-            if (empty) { meta = (k == T_LBRACE ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR); end_tok = i + 1; }
+        if (dd > 0) {
+            if (is_closer(k1)) { meta = (k == T_LBRACE ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR); after = k2 == T_SCALAR_END ? kind[i + 3] : k2; }
             else { meta = (k == T_LBRACE ? ROW_OPEN_OBJ : ROW_OPEN_ARR); bb.row[my_b] = r; voff = my_b; }  // voff of an opening row: its bracket
         } else if (k == T_STR_OPEN) {
             meta = ROW_STR;
-            if (!((tb.decode_bits[i >> 5] >> (i & 31)) & 1u)) meta |= META_VAL_PLAIN;
-            string_ref(tb, db, n_dec, i, &voff, &vlen);
-            end_tok = i + 1;
+            if (!((dbits[i >> 5] >> (i & 31)) & 1u)) { meta |= META_VAL_PLAIN; voff = tb.pos[i] + 1; vlen = tb.pos[i + 1] - voff; }
+            else string_ref(tb, db, n_dec, i, &voff, &vlen);
+            after = k2 == T_SCALAR_END ? kind[i + 3] : k2;
         } else {  // scalar
             meta = ROW_RAW;
             voff = tb.pos[i];
-            const uint32_t e = (i + 1 < n_tok) ? tb.pos[i + 1] : (uint32_t)n;
-            vlen = e - voff;
+            vlen = tb.pos[i + 1] - voff;   // positions past the last token read as the text length
             const uint32_t c = check_scalar(raw + voff, vlen);
             if (c == 0) { res->invalid = 1; return; }
             if (c == 1) { res->need_host_numbers = 1; res->not_canonical = 1; }
         }
         meta |= (uint32_t)depth << META_DEPTH_SHIFT;
         if (ct == CT_OBJ) {
-            // tokens before a value in an object: "key" : value -> i-3 open quote, i-2 close quote, i-1 colon
-            if (i < 3 || kind[i - 3] != T_STR_OPEN) { res->invalid = 1; return; }
+            // "key" : value -> i-3 opening quote, i-2 closing quote, i-1 colon (the table has vouched for them)
             const uint32_t ko = i - 3;
             meta |= META_HAS_KEY;
-            if (!((tb.decode_bits[ko >> 5] >> (ko & 31)) & 1u)) meta |= META_KEY_PLAIN;
-            string_ref(tb, db, n_dec, ko, &koff, &klen);
+            if (!((dbits[ko >> 5] >> (ko & 31)) & 1u)) { meta |= META_KEY_PLAIN; koff = tb.pos[ko] + 1; klen = tb.pos[ko + 1] - koff; }
+            else string_ref(tb, db, n_dec, ko, &koff, &klen);
             if (ko > 0) { uint32_t q = ko - 1; if (kind[q] == T_SCALAR_END) q--; if (kind[q] == T_COMMA) meta |= (1u << 7); }  // has an earlier sibling
         }
     }
     // an opening row never carries the comma: it follows the closer and rides on the closing row
     const uint32_t rk = meta & 15u;
-    if (rk != ROW_OPEN_OBJ && rk != ROW_OPEN_ARR && next_sig(kind, end_tok, n_tok) == T_COMMA) meta |= META_COMMA;
+    if (rk != ROW_OPEN_OBJ && rk != ROW_OPEN_ARR && after == T_COMMA) meta |= META_COMMA;
     if (r + 1 == n_rows) meta |= META_LAST;
     rb.meta[r] = meta; rb.koff[r] = koff; rb.klen[r] = klen; rb.voff[r] = voff; rb.vlen[r] = vlen;
 }
+
+__global__ void __launch_bounds__(TP_THREADS) rows_kernel(const uint8_t *__restrict__ raw, u64 n, TokenBuffers tb, uint32_t n_tok,
+                                                         const TilePrefix *__restrict__ tiles, BracketBuffers bb, DecodeBuffers db,
+                                                         uint32_t n_dec, RowBuffers rb, uint32_t n_rows, ParseResult *res) {
+    // Token kinds and positions of this block (plus a halo of 8 on each side for the neighbour
+    // look-ups of the grammar rules) are staged in shared memory with coalesced loads; threads then
+    // walk 8 consecutive tokens each without striding through global memory.
+    constexpr int HALO = 8;
+    __shared__ uint8_t s_kind[RW_BLOCK + 2 * HALO];
+    __shared__ uint32_t s_pos[RW_BLOCK + 2 * HALO];
+    const long long blk0 = (long long)blockIdx.x * RW_BLOCK - HALO;
+    for (int x = threadIdx.x; x < RW_BLOCK + 2 * HALO; x += TP_THREADS) {
+        const long long i = blk0 + x;
+        const bool in = i >= 0 && i < (long long)n_tok;
+        s_kind[x] = in ? tb.kind[i] : (uint8_t)0xff;
+        s_pos[x] = in ? tb.pos[i] : (uint32_t)n;
+    }
+    __syncthreads();
+    tb.kind = s_kind - blk0;   // indexable by global token number inside the staged window
+    tb.pos = s_pos - blk0;
+    const uint32_t base = blockIdx.x * RW_BLOCK + threadIdx.x * RW_ITEMS;
+    const uint8_t *kind = tb.kind;
+    // first pass: what this thread's tokens add to depth, row count and bracket count
+    int d = 0;
+    uint32_t r = 0, b = 0, rowbits = 0;
+#pragma unroll
+    for (int j = 0; j < RW_ITEMS; j++) {
+        const uint32_t i = base + j;
+        const uint32_t k = i < n_tok ? kind[i] : 0xffu;
+        const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
+        const uint32_t row = (i < n_tok && emits_row(kind, i, n_tok, k)) ? 1u : 0u;
+        d += dd; b += dd != 0; r += row; rowbits |= row << j;
+    }
+    int ed, td;
+    uint32_t er, eb, tr, tbk;
+    block_scan3(d, r, b, &ed, &er, &eb, &td, &tr, &tbk);
+    const TilePrefix p = tiles[blockIdx.x * (RW_BLOCK / TOK_TILE)];
+    int depth = p.depth + ed;
+    uint32_t rr = p.rows + er, brb = p.brackets + eb;
+    // the block's slice of the per-bracket container table and of the decode bitmap, staged too
+    __shared__ uint8_t s_ct[RW_BLOCK + 1];
+    __shared__ uint32_t s_dbits[RW_BLOCK / 32 + 2];
+    const uint32_t b_first = p.brackets > 0 ? p.brackets - 1 : 0;           // first bracket any token here can ask about
+    const uint32_t b_count = p.brackets + tbk - b_first;                     // <= RW_BLOCK + 1
+    for (uint32_t x = threadIdx.x; x < b_count; x += TP_THREADS) s_ct[x] = (uint8_t)bb.ct[b_first + x];
+    const long long w_first = (blk0 < 0 ? 0 : blk0) >> 5;                    // decode-bit words from the halo's first token on
+    for (uint32_t x = threadIdx.x; x < RW_BLOCK / 32 + 2; x += TP_THREADS) s_dbits[x] = tb.decode_bits[w_first + x];
+    __syncthreads();
+    const uint8_t *ct_s = s_ct - b_first;
+    const uint32_t *dbits = s_dbits - w_first;
+    // second pass: the tokens in order, with the running state
+#pragma unroll 1
+    for (int j = 0; j < RW_ITEMS; j++) {
+        const uint32_t k = kind[base + j];
+        const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
+        const uint32_t row = (rowbits >> j) & 1u;
+        if (k != 0xffu && k != T_SCALAR_END && k != T_STR_CLOSE)
+            token_row(raw, n, tb, n_tok, bb, ct_s, dbits, db, n_dec, rb, n_rows, res, base + j, k, depth, rr, brb, row, dd);
+        depth += dd; rr += row; brb += dd != 0;
+    }
+}
+
 
 // =================================================================================================
 // P4: are the keys of every object strictly ascending (bytewise, decoded)?
@@ -1009,19 +1126,21 @@ cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, un
 
 cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, unsigned long long *scratch, ParseResult *res,
                                 cudaStream_t s) {
-    const uint32_t blocks = (tok_tiles(n_tok) + PREFIX_SUB - 1) / PREFIX_SUB;
+    const uint32_t blocks = (n_tok + TP_BLOCK - 1) / TP_BLOCK;
     cudaError_t e = cudaMemsetAsync(scratch, 0, (4 + 2 * (size_t)blocks) * 8, s);
     if (e != cudaSuccess) return e;
-    token_prefix_kernel<<<blocks, TOK_TILE, 0, s>>>(tb, n_tok, tiles, scratch, res);
+    token_prefix_kernel<<<blocks, TP_THREADS, 0, s>>>(tb, n_tok, tiles, scratch, res);
     g_parse_launches++;
     return cudaGetLastError();
 }
 
 cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb, unsigned int *bit_zeros,
-                            cudaStream_t s) {
+                            uint32_t max_level, cudaStream_t s) {
     cudaError_t e = cudaMemsetAsync(bit_zeros, 0, 16 * sizeof(unsigned int), s);
     if (e != cudaSuccess) return e;
-    brackets_kernel<<<tok_tiles(n_tok), TOK_TILE, 0, s>>>(tb, n_tok, tiles, bb, bit_zeros);
+    int bits = 0;
+    while ((1u << bits) <= max_level) bits++;
+    brackets_kernel<<<(n_tok + TP_BLOCK - 1) / TP_BLOCK, TP_THREADS, 0, s>>>(tb, n_tok, tiles, bb, bit_zeros, bits);
     g_parse_launches++;
     return cudaGetLastError();
 }
@@ -1082,7 +1201,7 @@ cudaError_t launch_decode_write(uint8_t *arena, uint32_t side_base, TokenBuffers
 
 cudaError_t launch_rows(const uint8_t *raw, size_t n, TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb,
                         DecodeBuffers db, uint32_t n_dec, RowBuffers rb, uint32_t n_rows, ParseResult *res, cudaStream_t s) {
-    rows_kernel<<<tok_tiles(n_tok), TOK_TILE, 0, s>>>(raw, (u64)n, tb, n_tok, tiles, bb, db, n_dec, rb, n_rows, res);
+    rows_kernel<<<(n_tok + RW_BLOCK - 1) / RW_BLOCK, TP_THREADS, 0, s>>>(raw, (u64)n, tb, n_tok, tiles, bb, db, n_dec, rb, n_rows, res);
     g_parse_launches++;
     return cudaGetLastError();
 }

@@ -72,7 +72,8 @@ struct BracketBuffers {
     uint32_t *lvkind;   // level << 8 | TokKind
     uint32_t *match;    // partner bracket
     uint32_t *parent;   // enclosing opener (0xffffffff: none)
-    uint32_t *row;      // row index of an opener's row
+    uint32_t *row;      // row index of an opener's row / a closer's row
+    uint32_t *ct;       // container kinds around the bracket (see match_kernel)
     uint32_t *sort_a, *sort_b;  // sorted permutations (ping-pong)
     uint32_t *key_a, *key_b;    // level keys travelling with the permutation
 };
@@ -92,7 +93,7 @@ cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *til
                                 ParseResult *res, cudaStream_t s);
 // bit_zeros: 16 counters (device): brackets whose level has bit b clear
 cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb,
-                            unsigned int *bit_zeros, cudaStream_t s);
+                            unsigned int *bit_zeros, uint32_t max_level, cudaStream_t s);
 // stable sort of the identity permutation (sort_a/key_a) by level; *in_a says which buffer holds
 // the result.  flags/zrank: n_br words each; scratch: parse_scan_scratch_words(n_br) words.
 cudaError_t launch_sort_brackets(BracketBuffers bb, uint32_t n_br, uint32_t max_level, const unsigned int *bit_zeros,
