@@ -254,3 +254,57 @@ def test_config4_full_size(tk, oracle):
     assert sum(len(a.Nodes(ck)) for ck in list(ca.values())[::50]) == 20 * 100
     a.Delete("module." + synth.node_key(7, 7))
     assert len(a.Nodes(synth.cluster_key(7))) == 99 and len(a.Bytes()) < len(text)
+
+
+def _module_doc(rng, n):
+    """Children of "module" with every oddity Clusters()/Nodes() must cope with."""
+    mod = {}
+    for i in range(n):
+        kind = rng.choice(["cluster", "node", "node", "node", "other"])
+        prov = rng.choice(["a", "b", "aa"])
+        cl = rng.choice(["x", "y", "x_y", "xy"])
+        key = {"cluster": "cluster_%s_%s" % (prov, cl), "node": "node_%s_%s_%d" % (prov, cl, rng.randrange(40)),
+               "other": "zz%d" % i}[kind]
+        r = rng.random()
+        name = rng.choice(["n%d" % rng.randrange(12), "dup", "", "é", "a<b"])
+        if r < 0.6:
+            child = {"name": name, "hostname": rng.choice(["h%d" % rng.randrange(30), "dup", "h<1>"]), "x": {"name": "inner"}}
+        elif r < 0.7:
+            child = {"name": name}
+        elif r < 0.8:
+            child = {"hostname": 5, "name": None}
+        elif r < 0.9:
+            child = rng.choice([[{"name": "in-array"}], "string", 7, None, {}])
+        else:
+            child = {"hostname": "only-host"}
+        mod[key] = child
+    return {"module": mod, "other": {"cluster_a_x": {"name": "not-in-module"}}}
+
+
+@pytest.mark.parametrize("seed", range(25))
+def test_index_lookups_on_device_resident_documents(tk, oracle, seed):
+    """Clusters()/Nodes() answered from the GPU-built index (document never leaves the device): runs of
+    children in ascending field order come straight out of the packed records, anything else (duplicate
+    or descending names, children without the field) takes the sort path -- both must match the oracle."""
+    rng = random.Random(5150 + seed)
+    raw = oracle.New("x", json.dumps(_module_doc(rng, rng.choice([0, 1, 5, 60, 400]))).encode()).Bytes()   # canonical key order
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    assert not a.host_tree_built
+    assert a.Clusters() == b.Clusters()
+    for prov in ("a", "b", "aa", "zz"):
+        for cl in ("x", "y", "xy", "x_y", ""):
+            ck = "cluster_%s_%s" % (prov, cl)
+            assert a.Nodes(ck) == b.Nodes(ck), ck
+    assert not a.host_tree_built                        # none of it needed the host tree
+    assert a.Bytes() == raw
+
+
+@pytest.mark.parametrize("raw,err", [(b'{"module":[1]}', "not an object"), (b'{"module":"s"}', "not an object"), (b'{"x":1}', "not an object"),
+                                     (b'[{"module":{}}]', "not an object"), (b'{"module":null}', "not an object")])
+def test_index_module_not_an_object(tk, raw, err):
+    s = tk.New("x", raw)
+    for call in (s.Clusters, lambda: s.Nodes("cluster_a_b")):
+        with pytest.raises(tk.StateError) as e:
+            call()
+        assert str(e.value) == err
+    assert tk.New("x", b'{"module":{}}').Clusters() == {}

@@ -220,8 +220,13 @@ static int children_by_prefix(tk_state *s, std::string_view prefix, std::string_
     auto &pairs = s->pairs;  // (field value, module key); kept on the handle so a sweep of calls re-uses its storage
     pairs.clear();
     if (!s->doc.host_valid && s->eng.device_resident(s->doc)) {
-        // the document lives on the device: one GPU pass per version builds the packed index
-        bool module_ok = false;
+        // the document lives on the device: one GPU pass per version builds the packed index, and
+        // the finished answer is usually a byte range of the result records packed alongside it
+        bool module_ok = false, direct = false;
+        int rc0 = s->eng.index_lookup_direct(s->doc, prefix, field == "hostname", &module_ok, &direct, blob, blob_len, count, &err);
+        if (rc0) return set_err(s, rc0, err);
+        if (!module_ok) return set_err(s, TK_ENOTOBJ, kErrNotObj);
+        if (direct) return TK_OK;
         int rc = s->eng.index_lookup(s->doc, prefix, field == "hostname", &module_ok, &pairs, &err);
         if (rc) return set_err(s, rc, err);
         if (!module_ok) return set_err(s, TK_ENOTOBJ, kErrNotObj);

@@ -811,4 +811,115 @@ int Engine::index_lookup(const Document &doc, std::string_view prefix, bool host
     return TK_OK;
 }
 
+// first and one-past-last child whose key starts with prefix (children are in bytewise key order)
+void Engine::index_range(std::string_view prefix, uint32_t *lo_out, uint32_t *hi_out) {
+    const ChildEntry *ent = h_centries_.p;
+    const char *bytes = reinterpret_cast<const char *>(h_cpacked_.p);
+    auto key_at = [&](uint32_t i) { return std::string_view(bytes + ent[i].off, ent[i].klen); };
+    auto has_prefix = [&](uint32_t i) { return ent[i].klen >= prefix.size() && memcmp(bytes + ent[i].off, prefix.data(), prefix.size()) == 0; };
+    uint32_t lo = 0;
+    if (index_hint_ < index_n_ && has_prefix(index_hint_) && (index_hint_ == 0 || key_at(index_hint_ - 1) < prefix)) {
+        lo = index_hint_;  // a sweep over clusters in order: this run starts where the previous one ended
+    } else {
+        uint32_t hi = index_n_;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (key_at(mid) < prefix) lo = mid + 1; else hi = mid;
+        }
+    }
+    // end of the run: gallop, then bisect (runs are short next to the index); keys with the prefix
+    // are contiguous, so has_prefix is true ... true false ... from lo on
+    uint32_t a = lo;
+    if (lo < index_n_ && has_prefix(lo)) {
+        uint32_t last_good = lo, step = 1, bad = index_n_;
+        for (;;) {
+            const uint64_t probe = (uint64_t)last_good + step;
+            if (probe >= index_n_) break;
+            if (has_prefix((uint32_t)probe)) { last_good = (uint32_t)probe; step <<= 1; }
+            else { bad = (uint32_t)probe; break; }
+        }
+        a = last_good + 1;
+        uint32_t b = bad;
+        while (a < b) {
+            const uint32_t mid = (a + b) >> 1;
+            if (has_prefix(mid)) a = mid + 1; else b = mid;
+        }
+    }
+    *lo_out = lo;
+    *hi_out = a;
+    index_hint_ = a;
+}
+
+// Result records of one field, packed on the GPU in child order, plus the per-child prefix tables
+// (bytes before, records before, order violations before).  Built on the first query of that kind.
+int Engine::build_field_blob(const Document &doc, int which, std::string *err) {
+    if (field_version_[which] == doc.version) return TK_OK;
+    const uint32_t n = index_n_;
+    cudaError_t e;
+    if ((e = d_fcs_.reserve(((size_t)n + 1) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_fcs_excl_.reserve(((size_t)n + 1) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_fviol_.reserve(((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_fviol_excl_.reserve(((size_t)n + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_foff_.reserve(((size_t)n + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_fcnt_.reserve(((size_t)n + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_fblob_.reserve(arena_used_ + 8 * (size_t)n + 64)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_scratch_.reserve(parse_scan_scratch_words(n) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    if (!h_foff_[which].reserve((size_t)n + 1) || !h_fcnt_[which].reserve((size_t)n + 1) || !h_fviol_[which].reserve((size_t)n + 1) || !h_words_.reserve(4)) {
+        *err = "cuda: pinned host allocation failed";
+        return TK_ECUDA;
+    }
+    unsigned long long *scratch = d_scratch_.as<unsigned long long>();
+    if (n) {
+        e = timed(K_MODULE_INDEX, [&] {
+            cudaError_t x;
+            const ChildRef *refs = d_crefs_.as<ChildRef>();
+            if ((x = launch_field_sizes(tape_.arena, refs, n, which, d_fcs_.as<unsigned long long>(), d_fviol_.as<uint32_t>(), stream_)) != cudaSuccess) return x;
+            if ((x = scan_u32(d_fviol_.as<uint32_t>(), d_fviol_excl_.as<uint32_t>(), n, scratch, stream_)) != cudaSuccess) return x;
+            if ((x = cudaMemcpyAsync(d_fviol_excl_.as<uint32_t>() + n, scratch + 1, 4, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return x;
+            if ((x = scan_u64(d_fcs_.as<unsigned long long>(), d_fcs_excl_.as<unsigned long long>(), n, scratch, stream_)) != cudaSuccess) return x;
+            return launch_field_pack(tape_.arena, refs, n, which, d_fcs_excl_.as<unsigned long long>(), d_fcs_.as<unsigned long long>(),
+                                     d_fblob_.as<uint8_t>(), d_foff_.as<uint32_t>(), d_fcnt_.as<uint32_t>(), stream_);
+        });
+        if (e != cudaSuccess) return fail(e, "field blob", err);
+        if ((e = copy_d2h(h_foff_[which].p, d_foff_.p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+        if ((e = copy_d2h(h_fcnt_[which].p, d_fcnt_.p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+        if ((e = copy_d2h(h_fviol_[which].p, d_fviol_excl_.p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+        if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy index", err);
+        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "field blob", err);
+        const size_t bytes = (uint32_t)h_words_.p[0];
+        if (!h_fblob_[which].reserve(bytes + 1)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+        if (bytes) {
+            if ((e = copy_d2h(h_fblob_[which].p, d_fblob_.p, bytes)) != cudaSuccess) return fail(e, "copy index", err);
+            if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "field blob", err);
+        }
+    }
+    field_version_[which] = doc.version;
+    return TK_OK;
+}
+
+int Engine::index_lookup_direct(const Document &doc, std::string_view prefix, bool hostname, bool *module_ok, bool *direct,
+                                const uint8_t **blob, size_t *blob_len, size_t *count, std::string *err) {
+    int rc = build_index(doc, err);
+    if (rc) return rc;
+    *module_ok = index_module_ok_;
+    *direct = true;
+    *blob = reinterpret_cast<const uint8_t *>("");
+    *blob_len = 0;
+    *count = 0;
+    if (!index_module_ok_ || index_n_ == 0) return TK_OK;
+    const int which = hostname ? 1 : 0;
+    if ((rc = build_field_blob(doc, which, err))) return rc;
+    uint32_t lo, hi;
+    index_range(prefix, &lo, &hi);
+    if (lo == hi) return TK_OK;
+    // order violations strictly inside the run (child lo may compare with a child outside it)
+    const uint32_t *viol = h_fviol_[which].p;
+    if (viol[hi] - viol[lo + 1] != 0) { *direct = false; return TK_OK; }
+    const uint32_t *off = h_foff_[which].p, *cnt = h_fcnt_[which].p;
+    *blob = h_fblob_[which].p + off[lo];
+    *blob_len = off[hi] - off[lo];
+    *count = cnt[hi] - cnt[lo];
+    return TK_OK;
+}
+
 }  // namespace tk

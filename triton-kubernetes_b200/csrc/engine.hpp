@@ -118,6 +118,11 @@ public:
     bool device_resident(const Document &doc) const { return tape_from_parse_ && staged_version_ == doc.version; }
     int index_lookup(const Document &doc, std::string_view prefix, bool hostname, bool *module_ok,
                      std::vector<std::pair<std::string_view, std::string_view>> *pairs, std::string *err);
+    // The same query answered without copying when possible: *blob / *blob_len / *count describe the
+    // finished C-ABI result inside the pre-packed blob of that field.  *direct false: the run is not
+    // in strictly ascending field order (or has gaps) -- use index_lookup and sort.
+    int index_lookup_direct(const Document &doc, std::string_view prefix, bool hostname, bool *module_ok, bool *direct,
+                            const uint8_t **blob, size_t *blob_len, size_t *count, std::string *err);
 
     // measurement hooks
     void set_timing(bool on) { timing_ = on; }
@@ -135,6 +140,8 @@ private:
     template <class F> cudaError_t timed(int kind, F &&launch);
     int fetch_result(std::string *err);
     int build_index(const Document &doc, std::string *err);
+    int build_field_blob(const Document &doc, int which, std::string *err);
+    void index_range(std::string_view prefix, uint32_t *lo, uint32_t *hi);
 
     void flatten(const Document &doc);
     void flatten_keys(const Document &doc);
@@ -183,6 +190,11 @@ private:
     uint64_t index_version_ = 0;
     uint32_t index_n_ = 0, index_hint_ = 0;
     bool index_module_ok_ = false;
+    // per field (0 name, 1 hostname): the packed result records and their per-child prefix tables
+    DevBuf d_fcs_, d_fcs_excl_, d_fviol_, d_fviol_excl_, d_fblob_, d_foff_, d_fcnt_;
+    PinVec<uint8_t> h_fblob_[2];
+    PinVec<uint32_t> h_foff_[2], h_fcnt_[2], h_fviol_[2];
+    uint64_t field_version_[2] = {0, 0};
     BracketBuffers bb_{};  // bracket tables of the last parse (match / row are read by the index kernels)
 
     // results

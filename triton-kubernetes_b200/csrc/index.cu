@@ -89,7 +89,90 @@ __global__ void child_pack_kernel(const uint8_t *__restrict__ arena, const Child
     if (c.hlen != 0xffffffffu) { for (uint32_t k = 0; k < c.hlen; k++) packed[o + k] = arena[c.hoff + k]; }
 }
 
+// ---- result blobs: Clusters()/Nodes() answers laid out ahead of time -------------------------------
+// For one field ("name" or "hostname"), every child that has it contributes the record the C ABI
+// returns for it -- { u32 field_len, field, u32 key_len, key } -- and the records are packed in
+// child (= key) order.  The answer to a prefix query is then the byte range of a run of children,
+// provided the field values in that run ascend strictly (the ABI returns pairs sorted by field,
+// one per value); `viol` counts the places where they do not, so the host can tell in O(1).
+
+__device__ __forceinline__ bool field_of(const ChildRef &c, int which, uint32_t *off, uint32_t *len) {
+    *off = which ? c.hoff : c.noff;
+    *len = which ? c.hlen : c.nlen;
+    return *len != 0xffffffffu;
+}
+
+// per child: (has field) << 32 | record bytes, and the order-violation flag
+__global__ void field_sizes_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, int which,
+                                   unsigned long long *cs, uint32_t *viol) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t fo, fl;
+    const ChildRef c = refs[i];
+    const bool has = field_of(c, which, &fo, &fl);
+    cs[i] = has ? ((1ull << 32) | (8ull + fl + c.klen)) : 0ull;
+    uint32_t v = 0;
+    if (has && i > 0) {
+        uint32_t po, pl;
+        const ChildRef p = refs[i - 1];
+        v = 1;  // a predecessor without the field, or with a field value that is not smaller
+        if (field_of(p, which, &po, &pl)) {
+            const uint32_t m = min(pl, fl);
+            int cmp = 0;
+            for (uint32_t k = 0; k < m; k++) {
+                const int x = arena[po + k], y = arena[fo + k];
+                if (x != y) { cmp = x < y ? -1 : 1; break; }
+            }
+            if (cmp == 0) cmp = pl < fl ? -1 : (pl > fl ? 1 : 0);
+            if (cmp < 0) v = 0;
+        }
+    }
+    viol[i] = v;
+}
+
+__device__ __forceinline__ void put_u32(uint8_t *p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); }
+
+// records written at their offsets; off[i] / cnt[i] = bytes / records before child i (n + 1 entries)
+__global__ void field_pack_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, int which,
+                                  const unsigned long long *__restrict__ cs_excl, const unsigned long long *__restrict__ cs, uint8_t *blob,
+                                  uint32_t *off, uint32_t *cnt) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned long long e = cs_excl[i];
+    const uint32_t o = (uint32_t)e;
+    off[i] = o;
+    cnt[i] = (uint32_t)(e >> 32);
+    if (i + 1 == n) {
+        const unsigned long long t = e + cs[i];
+        off[n] = (uint32_t)t;
+        cnt[n] = (uint32_t)(t >> 32);
+    }
+    uint32_t fo, fl;
+    const ChildRef c = refs[i];
+    if (!field_of(c, which, &fo, &fl)) return;
+    uint8_t *w = blob + o;
+    put_u32(w, fl);
+    for (uint32_t k = 0; k < fl; k++) w[4 + k] = arena[fo + k];
+    put_u32(w + 4 + fl, c.klen);
+    for (uint32_t k = 0; k < c.klen; k++) w[8 + fl + k] = arena[c.koff + k];
+}
+
 }  // namespace
+
+cudaError_t launch_field_sizes(const uint8_t *arena, const ChildRef *refs, uint32_t n, int which, unsigned long long *cs, uint32_t *viol,
+                               cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    field_sizes_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, n, which, cs, viol);
+    count_parse_launch();
+    return cudaGetLastError();
+}
+cudaError_t launch_field_pack(const uint8_t *arena, const ChildRef *refs, uint32_t n, int which, const unsigned long long *cs_excl,
+                              const unsigned long long *cs, uint8_t *blob, uint32_t *off, uint32_t *cnt, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    field_pack_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, n, which, cs_excl, cs, blob, off, cnt);
+    count_parse_launch();
+    return cudaGetLastError();
+}
 
 cudaError_t launch_find_module(const TapeView &t, const uint32_t *br_match, const uint32_t *br_row, ModuleInfo *info, cudaStream_t s) {
     ModuleInfo init;

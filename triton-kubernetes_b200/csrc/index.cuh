@@ -25,4 +25,13 @@ cudaError_t launch_child_entries(const TapeView &t, const uint32_t *flags, const
 cudaError_t launch_child_pack(const uint8_t *arena, const ChildRef *refs, const uint32_t *off, uint32_t n, ChildEntry *entries,
                               uint8_t *packed, cudaStream_t s);
 
+// which: 0 = "name" (Clusters), 1 = "hostname" (Nodes).  cs[i] = has << 32 | record bytes; viol[i] = 1
+// where child i's field value does not strictly exceed its predecessor's (or the predecessor has none)
+cudaError_t launch_field_sizes(const uint8_t *arena, const ChildRef *refs, uint32_t n, int which, unsigned long long *cs, uint32_t *viol,
+                               cudaStream_t s);
+// cs_excl = exclusive scan of cs.  Writes the records into blob and, per child, the bytes and the
+// records before it (off, cnt: n + 1 entries each)
+cudaError_t launch_field_pack(const uint8_t *arena, const ChildRef *refs, uint32_t n, int which, const unsigned long long *cs_excl,
+                              const unsigned long long *cs, uint8_t *blob, uint32_t *off, uint32_t *cnt, cudaStream_t s);
+
 }  // namespace tk

@@ -325,8 +325,9 @@ __global__ void __launch_bounds__(P1_THREADS) scan_tokens_kernel(const uint8_t *
 
 constexpr int SCAN_THREADS = 256, SCAN_ITEMS = 4, SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
-__global__ void __launch_bounds__(SCAN_THREADS) scan_u32_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
-                                                               uint32_t n, u64 *scratch) {
+// T = uint32_t or u64 (two 32-bit running sums packed into one word); sums are carried as u64
+template <class T>
+__global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const T *__restrict__ in, T *__restrict__ out, uint32_t n, u64 *scratch) {
     __shared__ uint32_t s_tile;
     __shared__ u64 s_warp[SCAN_THREADS / 32];
     __shared__ u64 s_prefix;
@@ -334,10 +335,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_u32_kernel(const uint32_t *
     __syncthreads();
     const uint32_t tile = s_tile, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
-    uint32_t v[SCAN_ITEMS];
+    T v[SCAN_ITEMS];
     u64 sum = 0;
 #pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = base + i < n ? in[base + i] : 0; sum += v[i]; }
+    for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = base + i < n ? in[base + i] : T(0); sum += v[i]; }
     u64 incl = sum;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -348,6 +349,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_u32_kernel(const uint32_t *
     __syncthreads();
     u64 wbefore = 0, total = 0;
     for (uint32_t i = 0; i < SCAN_THREADS / 32; i++) { if (i < warp) wbefore += s_warp[i]; total += s_warp[i]; }
+    // status words carry 62 payload bits: a packed pair must keep its high half below 2^30
     u64 *status = scratch + 2;
     if (warp == 0) {
         u64 prefix = 0;
@@ -379,7 +381,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_u32_kernel(const uint32_t *
     __syncthreads();
     u64 run = s_prefix + wbefore + incl - sum;
 #pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = (uint32_t)run; run += v[i]; }
+    for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = (T)run; run += v[i]; }
 }
 
 inline size_t scan_scratch_words_u32(uint32_t n) { return 2 + (size_t)((n + SCAN_TILE - 1) / SCAN_TILE); }
@@ -390,7 +392,15 @@ cudaError_t scan_u32(const uint32_t *in, uint32_t *out, uint32_t n, unsigned lon
     cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words_u32(n) * 8, s);
     if (e != cudaSuccess) return e;
     if (n == 0) return cudaSuccess;
-    scan_u32_kernel<<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(in, out, n, scratch);
+    scan_kernel<uint32_t><<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(in, out, n, scratch);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+cudaError_t scan_u64(const unsigned long long *in, unsigned long long *out, uint32_t n, unsigned long long *scratch, cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words_u32(n) * 8, s);
+    if (e != cudaSuccess) return e;
+    if (n == 0) return cudaSuccess;
+    scan_kernel<u64><<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(in, out, n, scratch);
     g_parse_launches++;
     return cudaGetLastError();
 }

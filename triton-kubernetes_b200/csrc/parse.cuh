@@ -120,6 +120,8 @@ size_t parse_scan_scratch_words(uint32_t n);
 // exclusive scan of n u32 values (single pass, decoupled look-back); the total lands in scratch[1].
 // scratch: parse_scan_scratch_words(n) words, cleared on the stream first.
 cudaError_t scan_u32(const uint32_t *in, uint32_t *out, uint32_t n, unsigned long long *scratch, cudaStream_t s);
+// same for 64-bit words holding two packed sums (high half must stay below 2^30)
+cudaError_t scan_u64(const unsigned long long *in, unsigned long long *out, uint32_t n, unsigned long long *scratch, cudaStream_t s);
 void count_parse_launch();
 unsigned long long parse_launch_count();
 
