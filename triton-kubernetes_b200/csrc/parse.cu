@@ -44,7 +44,7 @@ __device__ __forceinline__ uint32_t byte_class(uint32_t c) {
     if (c == '\\') k |= C_BS;
     if (c == ' ' || c == '\t' || c == '\n' || c == '\r') k |= C_WS;
     if (c == '{' || c == '}' || c == '[' || c == ']' || c == ':' || c == ',') k |= C_ST;
-    if (c < 0x20) k |= C_CTRL;
+    if (c < 0x20 && c != '\t' && c != '\n' && c != '\r') k |= C_CTRL;  // tab, newline, return: found through C_WS
     if (c == '<' || c == '>' || c == '&') k |= C_HTML;  // escaped on output: such strings are not plain
     return k;
 }
@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(P1_THREADS) scan_tokens_kernel(const uint8_t *
     __shared__ uint32_t s_v;                            // in-string state entering the tile
     __shared__ u64 s_base;                              // tokens before the tile
 
-    s_lut[threadIdx.x] = (uint8_t)byte_class(threadIdx.x);
+    for (int c = threadIdx.x; c < 256; c += P1_THREADS) s_lut[c] = (uint8_t)byte_class(c);
     if (threadIdx.x == 0) s_tile = (uint32_t)atomicAdd(&scratch[0], 1ull);
     __syncthreads();
     const uint32_t tile = s_tile;
@@ -117,12 +117,16 @@ __global__ void __launch_bounds__(P1_THREADS) scan_tokens_kernel(const uint8_t *
                                     ((uint32_t)s_lut[(x >> 16) & 0xff] << 16) | ((uint32_t)s_lut[x >> 24] << 24);
                 const int sh = (v * 4 + k) * 4;
                 Q |= (u64)gather4(c4, 0) << sh;
-                B |= (u64)gather4(c4, 1) << sh;
                 WS |= (u64)gather4(c4, 2) << sh;
                 STm |= (u64)gather4(c4, 3) << sh;
-                CT |= (u64)gather4(c4, 4) << sh;
-                HT |= (u64)gather4(c4, 5) << sh;
-                NA |= (u64)gather4(x, 7) << sh;
+                // backslashes, control bytes, < > & and non-ASCII bytes are rare in these documents:
+                // their masks are only gathered for a word that holds one
+                if ((c4 & 0x32323232u) | (x & 0x80808080u)) {
+                    B |= (u64)gather4(c4, 1) << sh;
+                    CT |= (u64)gather4(c4, 4) << sh;
+                    HT |= (u64)gather4(c4, 5) << sh;
+                    NA |= (u64)gather4(x, 7) << sh;
+                }
             }
         }
     }
@@ -273,6 +277,8 @@ __global__ void __launch_bounds__(P1_THREADS) scan_tokens_kernel(const uint8_t *
     // ---- string body checks (scanner.go stateInString / stateInStringEsc*)
     const u64 content = SB & ~RQ;
     bool bad = (CT & content) != 0;
+    for (u64 m = WS & content; m; m &= m - 1)  // white space inside a string: only the space itself is allowed raw
+        if (__ldg(raw + chunk + (__ffsll((long long)m) - 1)) != ' ') bad = true;
     for (u64 e = E & content; e; e &= e - 1) {
         const int i = __ffsll((long long)e) - 1;
         const uint32_t c = __ldg(raw + chunk + i);
@@ -680,21 +686,72 @@ __global__ void __launch_bounds__(TP_THREADS) brackets_kernel(TokenBuffers tb, u
     if (threadIdx.x < (unsigned)n_bits && s_zero[threadIdx.x]) atomicAdd(&bit_zeros[threadIdx.x], s_zero[threadIdx.x]);
 }
 
-// one stable split by bit `bit` of the key: zeros first
-__global__ void split_flags_kernel(const uint32_t *__restrict__ key, uint32_t n, int bit, uint32_t *__restrict__ flags) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) flags[i] = ((key[i] >> bit) & 1u) ? 0u : 1u;
-}
-__global__ void split_scatter_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict__ val, const uint32_t *__restrict__ zrank,
-                                     uint32_t n, int bit, const unsigned int *__restrict__ bit_zeros, uint32_t *__restrict__ key_out,
-                                     uint32_t *__restrict__ val_out) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+// One stable split of (key, value) pairs by bit `bit` of the key, zeros first, in a single kernel:
+// the zero flags are scanned (decoupled look-back) and every pair is scattered to its place.
+__global__ void __launch_bounds__(SCAN_THREADS) split_pass_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict__ val, uint32_t n,
+                                                                 int bit, const unsigned int *__restrict__ bit_zeros,
+                                                                 uint32_t *__restrict__ key_out, uint32_t *__restrict__ val_out, u64 *scratch) {
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_warp[SCAN_THREADS / 32];
+    __shared__ uint32_t s_prefix;
+    if (threadIdx.x == 0) s_tile = (uint32_t)atomicAdd(&scratch[0], 1ull);
+    __syncthreads();
+    const uint32_t tile = s_tile, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    uint32_t k[SCAN_ITEMS], v[SCAN_ITEMS], sum = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) {
+        k[i] = base + i < n ? key[base + i] : 0xffffffffu;
+        v[i] = base + i < n ? val[base + i] : 0u;
+        sum += base + i < n ? (((k[i] >> bit) & 1u) ^ 1u) : 0u;
+    }
+    uint32_t incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t x = __shfl_up_sync(FULL, incl, d);
+        if (lane >= (uint32_t)d) incl += x;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t wbefore = 0, total = 0;
+    for (uint32_t i = 0; i < SCAN_THREADS / 32; i++) { if (i < warp) wbefore += s_warp[i]; total += s_warp[i]; }
+    u64 *status = scratch + 2;
+    if (warp == 0) {
+        u64 prefix = 0;
+        if (tile == 0) {
+            if (lane == 0) st_relaxed(status, ST_PREFIX | total);
+        } else {
+            if (lane == 0) st_relaxed(status + tile, ST_AGG | total);
+            int look = (int)tile - 1;
+            for (;;) {
+                const int idx = look - (int)lane;
+                u64 s = idx >= 0 ? ld_relaxed(status + idx) : ST_PREFIX;
+                while (__any_sync(FULL, (s >> 62) == 0)) { if ((s >> 62) == 0) s = ld_relaxed(status + idx); }
+                const unsigned pm = __ballot_sync(FULL, (s >> 62) == 2);
+                const int first = pm ? __ffs(pm) - 1 : 32;
+                u64 x = ((int)lane <= first) ? (s & ST_MASK) : 0ull;
+#pragma unroll
+                for (int d = 16; d; d >>= 1) x += __shfl_xor_sync(FULL, x, d);
+                prefix += x;
+                if (pm) break;
+                look -= 32;
+            }
+            if (lane == 0) st_relaxed(status + tile, ST_PREFIX | (prefix + total));
+        }
+        if (lane == 0) s_prefix = (uint32_t)prefix;
+    }
+    __syncthreads();
+    uint32_t z = s_prefix + wbefore + incl - sum;   // zeros before this thread's first item
     const uint32_t n_zero = bit_zeros[bit];
-    const uint32_t k = key[i], z = zrank[i];
-    const uint32_t dst = ((k >> bit) & 1u) ? n_zero + (i - z) : z;
-    key_out[dst] = k;
-    val_out[dst] = val[i];
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) {
+        if (base + i >= n) break;
+        const uint32_t one = (k[i] >> bit) & 1u;
+        const uint32_t dst = one ? n_zero + (base + i - z) : z;
+        key_out[dst] = k[i];
+        val_out[dst] = v[i];
+        z += one ^ 1u;
+    }
 }
 
 // =================================================================================================
@@ -1161,15 +1218,14 @@ cudaError_t launch_sort_brackets(BracketBuffers bb, uint32_t n_br, uint32_t max_
     if (n_br == 0) return cudaSuccess;
     int bits = 0;
     while ((1u << bits) <= max_level) bits++;
-    const uint32_t blocks = (n_br + 255) / 256;
+    const uint32_t blocks = (n_br + SCAN_TILE - 1) / SCAN_TILE;
+    (void)flags; (void)zrank;
     for (int bit = 0; bit < bits; bit++) {
         const uint32_t *key = *in_a ? bb.key_a : bb.key_b, *val = *in_a ? bb.sort_a : bb.sort_b;
         uint32_t *key_o = *in_a ? bb.key_b : bb.key_a, *val_o = *in_a ? bb.sort_b : bb.sort_a;
-        split_flags_kernel<<<blocks, 256, 0, s>>>(key, n_br, bit, flags);
-        g_parse_launches++;
-        cudaError_t e = scan_u32(flags, zrank, n_br, scratch, s);
+        cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words_u32(n_br) * 8, s);
         if (e != cudaSuccess) return e;
-        split_scatter_kernel<<<blocks, 256, 0, s>>>(key, val, zrank, n_br, bit, bit_zeros, key_o, val_o);
+        split_pass_kernel<<<blocks, SCAN_THREADS, 0, s>>>(key, val, n_br, bit, bit_zeros, key_o, val_o, scratch);
         g_parse_launches++;
         *in_a = !*in_a;
     }

@@ -31,9 +31,9 @@ enum TokKind : uint8_t {
     T_STR_OPEN = 6, T_STR_CLOSE = 7, T_SCALAR = 8, T_SCALAR_END = 9
 };
 
-constexpr int P1_THREADS = 256;
+constexpr int P1_THREADS = 128;
 constexpr int P1_BYTES_PER_THREAD = 64;
-constexpr int P1_TILE = P1_THREADS * P1_BYTES_PER_THREAD;  // 16 KiB of text per block
+constexpr int P1_TILE = P1_THREADS * P1_BYTES_PER_THREAD;  // 8 KiB of text per block
 constexpr int TOK_TILE = 256;                              // tokens per block in the token passes
 
 // result block the kernels fill in device memory (one per parse)
