@@ -288,13 +288,37 @@ __global__ void __launch_bounds__(EMIT_THREADS) row_offsets_kernel(TapeView t, u
 
 // ---- K2: emit -------------------------------------------------------------------------------
 
-constexpr uint32_t LANE_COPY_MAX = 16;  // plain runs up to this many bytes are copied by the row's own lane
+constexpr uint32_t LANE_COPY_MAX = 16;    // generic path: plain runs up to this many bytes are copied by the row's own lane
+constexpr uint32_t LANE_WORDS_MAX = 128;  // shared-memory path: up to this many bytes, 4 at a time
 
-// A plain byte run of one row: short ones are copied at once by the lane, long ones are left for the
-// whole warp to copy together (emit_kernel, phase 2) so that one long string does not hold 31 lanes idle.
+// A plain byte run of one row that is left for the whole warp to copy together (emit_kernel,
+// phase 2), so that one long string does not hold 31 lanes idle.
 struct Deferred { uint32_t src, dst, len; };
 
+template <bool SMEM>
 __device__ __forceinline__ uint32_t put_plain(uint8_t *dst, uint32_t pos, const uint8_t *src, uint32_t off, uint32_t len, Deferred *d) {
+    if (SMEM) {
+        // both buffers are shared memory: copy aligned 32-bit words, realigning the source with a
+        // funnel shift (the staged slice is readable a word past the run)
+        if (len > LANE_WORDS_MAX) { d->src = off; d->dst = pos; d->len = len; return pos + len; }
+        uint32_t n = len, di = pos, si = off;
+        while (n && (di & 3u)) { dst[di++] = src[si++]; n--; }
+        if (n >= 4) {
+            const uint32_t sh = (si & 3u) * 8u;
+            const uint32_t *sw = reinterpret_cast<const uint32_t *>(src + (si & ~3u));
+            uint32_t *dw = reinterpret_cast<uint32_t *>(dst + di);
+            uint32_t lo = sw[0];
+            const uint32_t words = n >> 2;
+            for (uint32_t k = 0; k < words; k++) {
+                const uint32_t hi = sw[k + 1];
+                dw[k] = __funnelshift_r(lo, hi, sh);
+                lo = hi;
+            }
+            di += words * 4; si += words * 4; n &= 3u;
+        }
+        while (n) { dst[di++] = src[si++]; n--; }
+        return pos + len;
+    }
     if (len <= LANE_COPY_MAX) {
         for (uint32_t i = 0; i < len; i++) dst[pos + i] = src[off + i];
     } else {
@@ -304,23 +328,24 @@ __device__ __forceinline__ uint32_t put_plain(uint8_t *dst, uint32_t pos, const 
 }
 
 // one line, written at dst[pos...]; src is indexed by arena offset
+template <bool SMEM>
 __device__ __forceinline__ void put_line(uint8_t *dst, uint32_t pos, const Row &w, const uint8_t *src, Deferred *dk, Deferred *dv) {
     const uint32_t depth = w.meta >> META_DEPTH_SHIFT;
     for (uint32_t i = 0; i < depth; i++) dst[pos++] = '\t';
     if (w.meta & META_HAS_KEY) {
         dst[pos++] = '"';
-        if (w.meta & META_KEY_PLAIN) pos = put_plain(dst, pos, src, w.koff, w.klen, dk);
+        if (w.meta & META_KEY_PLAIN) pos = put_plain<SMEM>(dst, pos, src, w.koff, w.klen, dk);
         else pos = put_escaped(dst, pos, src + w.koff, w.klen);
         dst[pos++] = '"'; dst[pos++] = ':'; dst[pos++] = ' ';
     }
     switch (w.meta & 15u) {
     case ROW_STR:
         dst[pos++] = '"';
-        if (w.meta & META_VAL_PLAIN) pos = put_plain(dst, pos, src, w.voff, w.vlen, dv);
+        if (w.meta & META_VAL_PLAIN) pos = put_plain<SMEM>(dst, pos, src, w.voff, w.vlen, dv);
         else pos = put_escaped(dst, pos, src + w.voff, w.vlen);
         dst[pos++] = '"';
         break;
-    case ROW_RAW: pos = put_plain(dst, pos, src, w.voff, w.vlen, dv); break;
+    case ROW_RAW: pos = put_plain<SMEM>(dst, pos, src, w.voff, w.vlen, dv); break;
     case ROW_OPEN_OBJ: dst[pos++] = '{'; break;
     case ROW_OPEN_ARR: dst[pos++] = '['; break;
     case ROW_CLOSE_OBJ: dst[pos++] = '}'; break;
@@ -373,7 +398,7 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const ui
         Row v = w;
         v.koff -= base; v.voff -= base;
         // phase 1: every lane writes its own line, leaving long plain runs for phase 2
-        if (valid) put_line(slice, o - out0 + shift, v, s_src, &dk, &dv);
+        if (valid) put_line<true>(slice, o - out0 + shift, v, s_src, &dk, &dv);
         // phase 2: the warp copies the long runs together, 32 bytes per step
         warp_copy_deferred(slice, s_src, dk, lane);
         warp_copy_deferred(slice, s_src, dv, lane);
@@ -381,7 +406,7 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const ui
         // a tile that outgrew its staging: same steps on generic pointers
         const uint8_t *src = staged ? reinterpret_cast<const uint8_t *>(s_in[warp]) - base : t.arena;
         uint8_t *dst = fits ? slice : out;
-        if (valid) put_line(dst, fits ? o - out0 + shift : o, w, src, &dk, &dv);
+        if (valid) put_line<false>(dst, fits ? o - out0 + shift : o, w, src, &dk, &dv);
         warp_copy_deferred(dst, src, dk, lane);
         warp_copy_deferred(dst, src, dv, lane);
     }
