@@ -723,100 +723,118 @@ int Engine::materialise(Document *doc, std::string *err) {
 
 namespace tk {
 
+// One pass per document version (csrc/index.cu): children of "module" found and ranked, their key /
+// name / hostname strings located, then keys and per-field result records packed and copied to the
+// host together with the prefix tables.  Two synchronisations: one to learn the number of children
+// (it sizes the second half), one at the end.
 int Engine::build_index(const Document &doc, std::string *err) {
     if (index_version_ == doc.version) return TK_OK;
     if (!device_resident(doc)) { *err = "internal: module index needs the parser's tape"; return TK_EARG; }
     cudaError_t e;
-    const size_t n = tape_.n_rows;
-    if ((e = d_minfo_.reserve(sizeof(ModuleInfo) + 16)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_cflags_.reserve((n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_crank_.reserve((n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_crefs_.reserve((n + 1) * sizeof(ChildRef))) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_csizes_.reserve((n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_coffs_.reserve((n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_centries_.reserve((n + 1) * sizeof(ChildEntry))) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_cpacked_.reserve(arena_used_ + 64)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_scratch_.reserve(parse_scan_scratch_words((uint32_t)n) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
-    if (!h_minfo_.reserve(1) || !h_words_.reserve(4)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+    const size_t rows = tape_.n_rows;
+    if ((e = d_minfo_.reserve(sizeof(ModuleInfo) + 64)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_cflags_.reserve((rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_crank_.reserve((rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    if ((e = d_scratch_.reserve(parse_scan_scratch_words((uint32_t)rows) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    if (!h_minfo_.reserve(1) || !h_words_.reserve(8)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
     ModuleInfo *info = d_minfo_.as<ModuleInfo>();
+    unsigned long long *parked = reinterpret_cast<unsigned long long *>(d_minfo_.as<char>() + 32);  // scan totals kept across scans
     unsigned long long *scratch = d_scratch_.as<unsigned long long>();
-    uint32_t *flags = d_cflags_.as<uint32_t>(), *rank = d_crank_.as<uint32_t>(), *sizes = d_csizes_.as<uint32_t>(), *offs = d_coffs_.as<uint32_t>();
+    uint32_t *flags = d_cflags_.as<uint32_t>(), *rank = d_crank_.as<uint32_t>();
     e = timed(K_MODULE_INDEX, [&] {
         cudaError_t x;
         if ((x = launch_find_module(tape_, bb_.match, bb_.row, info, stream_)) != cudaSuccess) return x;
         if ((x = launch_child_flags(tape_, info, flags, stream_)) != cudaSuccess) return x;
-        if ((x = scan_u32(flags, rank, (uint32_t)n, scratch, stream_)) != cudaSuccess) return x;
-        if ((x = cudaMemcpyAsync(&info->n_children, scratch + 1, 4, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return x;
-        if ((x = cudaMemsetAsync(sizes, 0, (n + 1) * 4, stream_)) != cudaSuccess) return x;
-        if ((x = launch_child_entries(tape_, flags, rank, bb_.match, bb_.row, d_crefs_.as<ChildRef>(), sizes, stream_)) != cudaSuccess) return x;
-        return scan_u32(sizes, offs, (uint32_t)n, scratch, stream_);
+        return scan_u32(flags, rank, (uint32_t)rows, scratch, stream_);  // number of children -> scratch[1]
     });
     if (e != cudaSuccess) return fail(e, "module index", err);
     if ((e = copy_d2h(h_minfo_.p, info, sizeof(ModuleInfo))) != cudaSuccess) return fail(e, "copy module info", err);
-    if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy index size", err);
+    if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy child count", err);
     if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
     const ModuleInfo mi = *h_minfo_.p;
-    const size_t bytes = (size_t)h_words_.p[0];
     index_module_ok_ = mi.root_kind == ROW_OPEN_OBJ && (mi.module_kind == ROW_OPEN_OBJ || mi.module_kind == ROW_EMPTY_OBJ);
-    index_n_ = index_module_ok_ ? mi.n_children : 0;
-    if (index_n_) {
-        if ((e = timed(K_MODULE_INDEX, [&] {
-                 return launch_child_pack(tape_.arena, d_crefs_.as<ChildRef>(), offs, index_n_, d_centries_.as<ChildEntry>(), d_cpacked_.as<uint8_t>(), stream_);
-             })) != cudaSuccess)
-            return fail(e, "module index pack", err);
-        if (!h_centries_.reserve(index_n_) || !h_cpacked_.reserve(bytes + 1)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
-        if ((e = copy_d2h(h_centries_.p, d_centries_.p, (size_t)index_n_ * sizeof(ChildEntry))) != cudaSuccess) return fail(e, "copy index", err);
-        if (bytes && (e = copy_d2h(h_cpacked_.p, d_cpacked_.p, bytes)) != cudaSuccess) return fail(e, "copy index", err);
+    const uint32_t n = index_module_ok_ ? (uint32_t)h_words_.p[0] : 0;
+    index_n_ = n;
+    index_hint_ = 0;
+    if (n) {
+        DevBuf *need4[] = {&d_ckeyb_, &d_ckey_excl_, &d_cviol_[0], &d_cviol_[1], &d_cviol_excl_[0], &d_cviol_excl_[1], &d_ckey_off_,
+                           &d_foff_[0], &d_foff_[1], &d_fcnt_[0], &d_fcnt_[1]};
+        for (DevBuf *b : need4)
+            if ((e = b->reserve(((size_t)n + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+        DevBuf *need8[] = {&d_crec_[0], &d_crec_[1], &d_crec_excl_[0], &d_crec_excl_[1]};
+        for (DevBuf *b : need8)
+            if ((e = b->reserve(((size_t)n + 2) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+        if ((e = d_crefs_.reserve(((size_t)n + 1) * sizeof(ChildRef))) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+        // keys and records cannot outgrow the strings they are copied from
+        const size_t cap = arena_used_ + 8 * (size_t)n + 64;
+        if ((e = d_ckeys_.reserve(cap)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+        if ((e = d_fblob_[0].reserve(cap)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+        if ((e = d_fblob_[1].reserve(cap)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+        ChildRef *refs = d_crefs_.as<ChildRef>();
+        IndexTables tb;
+        tb.key_excl = d_ckey_excl_.as<uint32_t>();
+        tb.keys = d_ckeys_.as<uint8_t>();
+        tb.key_off = d_ckey_off_.as<uint32_t>();
+        for (int f = 0; f < 2; f++) {
+            tb.rec[f] = d_crec_[f].as<unsigned long long>();
+            tb.rec_excl[f] = d_crec_excl_[f].as<unsigned long long>();
+            tb.blob[f] = d_fblob_[f].as<uint8_t>();
+            tb.off[f] = d_foff_[f].as<uint32_t>();
+            tb.cnt[f] = d_fcnt_[f].as<uint32_t>();
+        }
+        e = timed(K_MODULE_INDEX, [&] {
+            cudaError_t x;
+            if ((x = cudaMemsetAsync(refs, 0xff, (size_t)n * sizeof(ChildRef), stream_)) != cudaSuccess) return x;
+            if ((x = launch_child_refs(tape_, info, flags, rank, refs, stream_)) != cudaSuccess) return x;
+            if ((x = launch_child_sizes(tape_.arena, refs, n, d_ckeyb_.as<uint32_t>(), d_crec_[0].as<unsigned long long>(),
+                                        d_crec_[1].as<unsigned long long>(), d_cviol_[0].as<uint32_t>(), d_cviol_[1].as<uint32_t>(), stream_)) != cudaSuccess) return x;
+            if ((x = scan_u32(d_ckeyb_.as<uint32_t>(), d_ckey_excl_.as<uint32_t>(), n, scratch, stream_)) != cudaSuccess) return x;
+            if ((x = cudaMemcpyAsync(parked, scratch + 1, 8, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return x;   // key bytes
+            for (int f = 0; f < 2; f++) {
+                if ((x = scan_u32(d_cviol_[f].as<uint32_t>(), d_cviol_excl_[f].as<uint32_t>(), n, scratch, stream_)) != cudaSuccess) return x;
+                if ((x = cudaMemcpyAsync(d_cviol_excl_[f].as<uint32_t>() + n, scratch + 1, 4, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return x;
+                if ((x = scan_u64(d_crec_[f].as<unsigned long long>(), d_crec_excl_[f].as<unsigned long long>(), n, scratch, stream_)) != cudaSuccess) return x;
+                if ((x = cudaMemcpyAsync(parked + 1 + f, scratch + 1, 8, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return x;  // count << 32 | bytes
+            }
+            return launch_child_pack(tape_.arena, refs, n, tb, stream_);
+        });
+        if (e != cudaSuccess) return fail(e, "module index", err);
+        if ((e = copy_d2h(h_words_.p, parked, 24)) != cudaSuccess) return fail(e, "copy index sizes", err);
+        if (!h_key_off_.reserve((size_t)n + 1)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+        if ((e = copy_d2h(h_key_off_.p, d_ckey_off_.p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+        for (int f = 0; f < 2; f++) {
+            if (!h_foff_[f].reserve((size_t)n + 1) || !h_fcnt_[f].reserve((size_t)n + 1) || !h_fviol_[f].reserve((size_t)n + 1)) {
+                *err = "cuda: pinned host allocation failed";
+                return TK_ECUDA;
+            }
+            if ((e = copy_d2h(h_foff_[f].p, d_foff_[f].p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+            if ((e = copy_d2h(h_fcnt_[f].p, d_fcnt_[f].p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+            if ((e = copy_d2h(h_fviol_[f].p, d_cviol_excl_[f].p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+        }
+        // blob sizes are bounded by what the tables say once they arrive; copy with the upper bounds
+        // the host can compute now: keys <= key offsets' last entry is not known yet, so synchronise
+        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
+        const size_t key_bytes = (size_t)h_words_.p[0];
+        const size_t rec_bytes[2] = {(size_t)(uint32_t)h_words_.p[1], (size_t)(uint32_t)h_words_.p[2]};
+        if (!h_ckeys_.reserve(key_bytes + 1) || !h_fblob_[0].reserve(rec_bytes[0] + 1) || !h_fblob_[1].reserve(rec_bytes[1] + 1)) {
+            *err = "cuda: pinned host allocation failed";
+            return TK_ECUDA;
+        }
+        if (key_bytes && (e = copy_d2h(h_ckeys_.p, d_ckeys_.p, key_bytes)) != cudaSuccess) return fail(e, "copy index", err);
+        for (int f = 0; f < 2; f++)
+            if (rec_bytes[f] && (e = copy_d2h(h_fblob_[f].p, d_fblob_[f].p, rec_bytes[f])) != cudaSuccess) return fail(e, "copy index", err);
         if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
     }
     index_version_ = doc.version;
     return TK_OK;
 }
 
-int Engine::index_lookup(const Document &doc, std::string_view prefix, bool hostname, bool *module_ok,
-                         std::vector<std::pair<std::string_view, std::string_view>> *pairs, std::string *err) {
-    int rc = build_index(doc, err);
-    if (rc) return rc;
-    *module_ok = index_module_ok_;
-    pairs->clear();
-    if (!index_module_ok_) return TK_OK;
-    const ChildEntry *ent = h_centries_.p;
-    const char *bytes = reinterpret_cast<const char *>(h_cpacked_.p);
-    // children are in bytewise key order: the keys that start with prefix form one contiguous run
-    auto key_at = [&](uint32_t i) { return std::string_view(bytes + ent[i].off, ent[i].klen); };
-    auto has_prefix = [&](std::string_view k) { return k.size() >= prefix.size() && memcmp(k.data(), prefix.data(), prefix.size()) == 0; };
-    uint32_t lo = 0;
-    if (index_hint_ < index_n_ && has_prefix(key_at(index_hint_)) && (index_hint_ == 0 || key_at(index_hint_ - 1) < prefix)) {
-        lo = index_hint_;  // a sweep over clusters in order: this run starts where the previous one ended
-    } else {
-        uint32_t hi = index_n_;
-        while (lo < hi) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (key_at(mid) < prefix) lo = mid + 1; else hi = mid;
-        }
-    }
-    uint32_t i = lo;
-    for (; i < index_n_; i++) {
-        const ChildEntry &c = ent[i];
-        std::string_view key(bytes + c.off, c.klen);
-        if (!has_prefix(key)) break;
-        uint32_t o = c.off + c.klen;
-        std::string_view name, host;
-        const bool has_name = c.nlen != 0xffffffffu, has_host = c.hlen != 0xffffffffu;
-        if (has_name) { name = std::string_view(bytes + o, c.nlen); o += c.nlen; }
-        if (has_host) host = std::string_view(bytes + o, c.hlen);
-        if (hostname ? has_host : has_name) pairs->emplace_back(hostname ? host : name, key);
-    }
-    index_hint_ = i;
-    return TK_OK;
-}
-
 // first and one-past-last child whose key starts with prefix (children are in bytewise key order)
 void Engine::index_range(std::string_view prefix, uint32_t *lo_out, uint32_t *hi_out) {
-    const ChildEntry *ent = h_centries_.p;
-    const char *bytes = reinterpret_cast<const char *>(h_cpacked_.p);
-    auto key_at = [&](uint32_t i) { return std::string_view(bytes + ent[i].off, ent[i].klen); };
-    auto has_prefix = [&](uint32_t i) { return ent[i].klen >= prefix.size() && memcmp(bytes + ent[i].off, prefix.data(), prefix.size()) == 0; };
+    const uint32_t *ko = h_key_off_.p;
+    const char *keys = reinterpret_cast<const char *>(h_ckeys_.p);
+    auto key_at = [&](uint32_t i) { return std::string_view(keys + ko[i], ko[i + 1] - ko[i]); };
+    auto has_prefix = [&](uint32_t i) { return ko[i + 1] - ko[i] >= prefix.size() && memcmp(keys + ko[i], prefix.data(), prefix.size()) == 0; };
     uint32_t lo = 0;
     if (index_hint_ < index_n_ && has_prefix(index_hint_) && (index_hint_ == 0 || key_at(index_hint_ - 1) < prefix)) {
         lo = index_hint_;  // a sweep over clusters in order: this run starts where the previous one ended
@@ -850,53 +868,32 @@ void Engine::index_range(std::string_view prefix, uint32_t *lo_out, uint32_t *hi
     index_hint_ = a;
 }
 
-// Result records of one field, packed on the GPU in child order, plus the per-child prefix tables
-// (bytes before, records before, order violations before).  Built on the first query of that kind.
-int Engine::build_field_blob(const Document &doc, int which, std::string *err) {
-    if (field_version_[which] == doc.version) return TK_OK;
-    const uint32_t n = index_n_;
-    cudaError_t e;
-    if ((e = d_fcs_.reserve(((size_t)n + 1) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_fcs_excl_.reserve(((size_t)n + 1) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_fviol_.reserve(((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_fviol_excl_.reserve(((size_t)n + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_foff_.reserve(((size_t)n + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_fcnt_.reserve(((size_t)n + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_fblob_.reserve(arena_used_ + 8 * (size_t)n + 64)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_scratch_.reserve(parse_scan_scratch_words(n) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
-    if (!h_foff_[which].reserve((size_t)n + 1) || !h_fcnt_[which].reserve((size_t)n + 1) || !h_fviol_[which].reserve((size_t)n + 1) || !h_words_.reserve(4)) {
-        *err = "cuda: pinned host allocation failed";
-        return TK_ECUDA;
+// the run's (field value, key) pairs, for the caller to sort: used when the run is not in field order
+int Engine::index_lookup(const Document &doc, std::string_view prefix, bool hostname, bool *module_ok,
+                         std::vector<std::pair<std::string_view, std::string_view>> *pairs, std::string *err) {
+    int rc = build_index(doc, err);
+    if (rc) return rc;
+    *module_ok = index_module_ok_;
+    pairs->clear();
+    if (!index_module_ok_ || index_n_ == 0) return TK_OK;
+    const int f = hostname ? 1 : 0;
+    uint32_t lo, hi;
+    index_range(prefix, &lo, &hi);
+    const uint32_t *off = h_foff_[f].p, *cnt = h_fcnt_[f].p;
+    const char *blob = reinterpret_cast<const char *>(h_fblob_[f].p);
+    for (uint32_t i = lo; i < hi; i++) {
+        if (cnt[i + 1] == cnt[i]) continue;  // this child has no such string field
+        const char *rec = blob + off[i];
+        uint32_t fl, kl;
+        memcpy(&fl, rec, 4);
+        memcpy(&kl, rec + 4 + fl, 4);
+        pairs->emplace_back(std::string_view(rec + 4, fl), std::string_view(rec + 8 + fl, kl));
     }
-    unsigned long long *scratch = d_scratch_.as<unsigned long long>();
-    if (n) {
-        e = timed(K_MODULE_INDEX, [&] {
-            cudaError_t x;
-            const ChildRef *refs = d_crefs_.as<ChildRef>();
-            if ((x = launch_field_sizes(tape_.arena, refs, n, which, d_fcs_.as<unsigned long long>(), d_fviol_.as<uint32_t>(), stream_)) != cudaSuccess) return x;
-            if ((x = scan_u32(d_fviol_.as<uint32_t>(), d_fviol_excl_.as<uint32_t>(), n, scratch, stream_)) != cudaSuccess) return x;
-            if ((x = cudaMemcpyAsync(d_fviol_excl_.as<uint32_t>() + n, scratch + 1, 4, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return x;
-            if ((x = scan_u64(d_fcs_.as<unsigned long long>(), d_fcs_excl_.as<unsigned long long>(), n, scratch, stream_)) != cudaSuccess) return x;
-            return launch_field_pack(tape_.arena, refs, n, which, d_fcs_excl_.as<unsigned long long>(), d_fcs_.as<unsigned long long>(),
-                                     d_fblob_.as<uint8_t>(), d_foff_.as<uint32_t>(), d_fcnt_.as<uint32_t>(), stream_);
-        });
-        if (e != cudaSuccess) return fail(e, "field blob", err);
-        if ((e = copy_d2h(h_foff_[which].p, d_foff_.p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
-        if ((e = copy_d2h(h_fcnt_[which].p, d_fcnt_.p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
-        if ((e = copy_d2h(h_fviol_[which].p, d_fviol_excl_.p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
-        if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy index", err);
-        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "field blob", err);
-        const size_t bytes = (uint32_t)h_words_.p[0];
-        if (!h_fblob_[which].reserve(bytes + 1)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
-        if (bytes) {
-            if ((e = copy_d2h(h_fblob_[which].p, d_fblob_.p, bytes)) != cudaSuccess) return fail(e, "copy index", err);
-            if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "field blob", err);
-        }
-    }
-    field_version_[which] = doc.version;
     return TK_OK;
 }
 
+// The same query answered without copying when possible: the finished C-ABI result is a byte range
+// of the field's record blob.
 int Engine::index_lookup_direct(const Document &doc, std::string_view prefix, bool hostname, bool *module_ok, bool *direct,
                                 const uint8_t **blob, size_t *blob_len, size_t *count, std::string *err) {
     int rc = build_index(doc, err);
@@ -907,16 +904,15 @@ int Engine::index_lookup_direct(const Document &doc, std::string_view prefix, bo
     *blob_len = 0;
     *count = 0;
     if (!index_module_ok_ || index_n_ == 0) return TK_OK;
-    const int which = hostname ? 1 : 0;
-    if ((rc = build_field_blob(doc, which, err))) return rc;
+    const int f = hostname ? 1 : 0;
     uint32_t lo, hi;
     index_range(prefix, &lo, &hi);
     if (lo == hi) return TK_OK;
     // order violations strictly inside the run (child lo may compare with a child outside it)
-    const uint32_t *viol = h_fviol_[which].p;
+    const uint32_t *viol = h_fviol_[f].p;
     if (viol[hi] - viol[lo + 1] != 0) { *direct = false; return TK_OK; }
-    const uint32_t *off = h_foff_[which].p, *cnt = h_fcnt_[which].p;
-    *blob = h_fblob_[which].p + off[lo];
+    const uint32_t *off = h_foff_[f].p, *cnt = h_fcnt_[f].p;
+    *blob = h_fblob_[f].p + off[lo];
     *blob_len = off[hi] - off[lo];
     *count = cnt[hi] - cnt[lo];
     return TK_OK;

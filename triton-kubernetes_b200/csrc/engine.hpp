@@ -140,7 +140,6 @@ private:
     template <class F> cudaError_t timed(int kind, F &&launch);
     int fetch_result(std::string *err);
     int build_index(const Document &doc, std::string *err);
-    int build_field_blob(const Document &doc, int which, std::string *err);
     void index_range(std::string_view prefix, uint32_t *lo, uint32_t *hi);
 
     void flatten(const Document &doc);
@@ -182,19 +181,15 @@ private:
     PinVec<ParseResult> h_res_;
     PinVec<unsigned long long> h_words_;
 
-    // module index
-    DevBuf d_minfo_, d_cflags_, d_crank_, d_crefs_, d_csizes_, d_coffs_, d_centries_, d_cpacked_;
+    // module index (csrc/index.cu)
+    DevBuf d_minfo_, d_cflags_, d_crank_, d_crefs_, d_ckeyb_, d_ckey_excl_, d_ckeys_, d_ckey_off_;
+    DevBuf d_crec_[2], d_crec_excl_[2], d_cviol_[2], d_cviol_excl_[2], d_fblob_[2], d_foff_[2], d_fcnt_[2];
     PinVec<ModuleInfo> h_minfo_;
-    PinVec<ChildEntry> h_centries_;
-    PinVec<uint8_t> h_cpacked_;
+    PinVec<uint8_t> h_ckeys_, h_fblob_[2];
+    PinVec<uint32_t> h_key_off_, h_foff_[2], h_fcnt_[2], h_fviol_[2];
     uint64_t index_version_ = 0;
     uint32_t index_n_ = 0, index_hint_ = 0;
     bool index_module_ok_ = false;
-    // per field (0 name, 1 hostname): the packed result records and their per-child prefix tables
-    DevBuf d_fcs_, d_fcs_excl_, d_fviol_, d_fviol_excl_, d_fblob_, d_foff_, d_fcnt_;
-    PinVec<uint8_t> h_fblob_[2];
-    PinVec<uint32_t> h_foff_[2], h_fcnt_[2], h_fviol_[2];
-    uint64_t field_version_[2] = {0, 0};
     BracketBuffers bb_{};  // bracket tables of the last parse (match / row are read by the index kernels)
 
     // results

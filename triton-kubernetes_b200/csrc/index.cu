@@ -48,53 +48,35 @@ __global__ void child_flags_kernel(TapeView t, const ModuleInfo *__restrict__ in
     flags[r] = f;
 }
 
-// entry of every child: where its key, "name" and "hostname" strings are, and their total size
-__global__ void child_entries_kernel(TapeView t, const uint32_t *__restrict__ flags, const uint32_t *__restrict__ rank,
-                                     const uint32_t *__restrict__ br_match, const uint32_t *__restrict__ br_row, ChildRef *refs,
-                                     uint32_t *sizes) {
+// Where every child's key, "name" and "hostname" strings are.  One thread per ROW: a child's own
+// row records the key, and each depth-3 string member called name / hostname records itself in
+// the slot of the child it belongs to -- the last child row before it, i.e. slot rank[r] - 1.
+// refs must have been filled with 0xff bytes (absent fields read as length 0xffffffff).
+__global__ void child_refs_kernel(TapeView t, const ModuleInfo *__restrict__ info, const uint32_t *__restrict__ flags,
+                                  const uint32_t *__restrict__ rank, ChildRef *refs) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= t.n_rows || !flags[r]) return;
-    ChildRef c;
-    c.koff = t.koff[r]; c.klen = t.klen[r];
-    c.noff = c.hoff = 0;
-    c.nlen = c.hlen = 0xffffffffu;  // absent, or not a string
-    if ((t.meta[r] & 15u) == ROW_OPEN_OBJ) {
-        const uint32_t end = br_row[br_match[t.voff[r]]];
-        for (uint32_t m = r + 1; m < end; m++) {
-            const uint32_t meta = t.meta[m];
-            if (row_depth(meta) != 3 || !(meta & META_HAS_KEY) || (meta & 15u) != ROW_STR) continue;
-            const uint32_t ko = t.koff[m], kl = t.klen[m];
-            if (key_is(t.arena, ko, kl, "name", 4)) { c.noff = t.voff[m]; c.nlen = t.vlen[m]; }
-            else if (key_is(t.arena, ko, kl, "hostname", 8)) { c.hoff = t.voff[m]; c.hlen = t.vlen[m]; }
-        }
+    if (r >= t.n_rows || info->module_kind != ROW_OPEN_OBJ || r <= info->module_row || r >= info->module_end) return;
+    const uint32_t meta = t.meta[r];
+    if (flags[r]) {
+        ChildRef *c = refs + rank[r];
+        c->koff = t.koff[r];
+        c->klen = t.klen[r];
+        return;
     }
-    const uint32_t i = rank[r];
-    refs[i] = c;
-    sizes[i] = c.klen + (c.nlen == 0xffffffffu ? 0 : c.nlen) + (c.hlen == 0xffffffffu ? 0 : c.hlen);
+    if (row_depth(meta) != 3 || !(meta & META_HAS_KEY) || (meta & 15u) != ROW_STR) return;
+    const uint32_t ko = t.koff[r], kl = t.klen[r];
+    ChildRef *c = refs + (rank[r] - 1);
+    if (key_is(t.arena, ko, kl, "name", 4)) { c->noff = t.voff[r]; c->nlen = t.vlen[r]; }
+    else if (key_is(t.arena, ko, kl, "hostname", 8)) { c->hoff = t.voff[r]; c->hlen = t.vlen[r]; }
 }
 
-// strings of child i copied to packed[off[i] ...): key, then name, then hostname
-__global__ void child_pack_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, const uint32_t *__restrict__ off,
-                                  uint32_t n, ChildEntry *entries, uint8_t *packed) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const ChildRef c = refs[i];
-    uint32_t o = off[i];
-    ChildEntry e;
-    e.off = o; e.klen = c.klen; e.nlen = c.nlen; e.hlen = c.hlen;
-    entries[i] = e;
-    for (uint32_t k = 0; k < c.klen; k++) packed[o + k] = arena[c.koff + k];
-    o += c.klen;
-    if (c.nlen != 0xffffffffu) { for (uint32_t k = 0; k < c.nlen; k++) packed[o + k] = arena[c.noff + k]; o += c.nlen; }
-    if (c.hlen != 0xffffffffu) { for (uint32_t k = 0; k < c.hlen; k++) packed[o + k] = arena[c.hoff + k]; }
-}
-
-// ---- result blobs: Clusters()/Nodes() answers laid out ahead of time -------------------------------
-// For one field ("name" or "hostname"), every child that has it contributes the record the C ABI
-// returns for it -- { u32 field_len, field, u32 key_len, key } -- and the records are packed in
-// child (= key) order.  The answer to a prefix query is then the byte range of a run of children,
-// provided the field values in that run ascend strictly (the ABI returns pairs sorted by field,
-// one per value); `viol` counts the places where they do not, so the host can tell in O(1).
+// ---- what goes to the host -------------------------------------------------------------------
+// (1) the keys, packed in child (= bytewise key) order, for the prefix search;
+// (2) per field ("name" for Clusters, "hostname" for Nodes) the finished C-ABI result records of
+//     the children that have it -- { u32 field_len, field, u32 key_len, key } -- packed in child
+//     order, so that the answer to a prefix query is the byte range of a run of children provided
+//     the field values in the run ascend strictly (the ABI returns pairs sorted by field, one per
+//     value); `viol` marks the places where they do not, so the host can tell in O(1).
 
 __device__ __forceinline__ bool field_of(const ChildRef &c, int which, uint32_t *off, uint32_t *len) {
     *off = which ? c.hoff : c.noff;
@@ -102,74 +84,85 @@ __device__ __forceinline__ bool field_of(const ChildRef &c, int which, uint32_t 
     return *len != 0xffffffffu;
 }
 
-// per child: (has field) << 32 | record bytes, and the order-violation flag
-__global__ void field_sizes_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, int which,
-                                   unsigned long long *cs, uint32_t *viol) {
+__device__ __forceinline__ uint32_t order_violation(const uint8_t *arena, const ChildRef &p, const ChildRef &c, int which) {
+    uint32_t fo, fl, po, pl;
+    if (!field_of(c, which, &fo, &fl)) return 0;
+    if (!field_of(p, which, &po, &pl)) return 1;  // a predecessor without the field: not a clean run
+    const uint32_t m = min(pl, fl);
+    for (uint32_t k = 0; k < m; k++) {
+        const int x = arena[po + k], y = arena[fo + k];
+        if (x != y) return x < y ? 0u : 1u;
+    }
+    return pl < fl ? 0u : 1u;
+}
+
+// per child: key bytes, (has field) << 32 | record bytes for both fields, and the violation flags
+__global__ void child_sizes_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, uint32_t *key_bytes,
+                                   unsigned long long *rec_n, unsigned long long *rec_h, uint32_t *viol_n, uint32_t *viol_h) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    uint32_t fo, fl;
     const ChildRef c = refs[i];
-    const bool has = field_of(c, which, &fo, &fl);
-    cs[i] = has ? ((1ull << 32) | (8ull + fl + c.klen)) : 0ull;
-    uint32_t v = 0;
-    if (has && i > 0) {
-        uint32_t po, pl;
+    key_bytes[i] = c.klen;
+    rec_n[i] = c.nlen != 0xffffffffu ? ((1ull << 32) | (8ull + c.nlen + c.klen)) : 0ull;
+    rec_h[i] = c.hlen != 0xffffffffu ? ((1ull << 32) | (8ull + c.hlen + c.klen)) : 0ull;
+    uint32_t vn = 0, vh = 0;
+    if (i > 0) {
         const ChildRef p = refs[i - 1];
-        v = 1;  // a predecessor without the field, or with a field value that is not smaller
-        if (field_of(p, which, &po, &pl)) {
-            const uint32_t m = min(pl, fl);
-            int cmp = 0;
-            for (uint32_t k = 0; k < m; k++) {
-                const int x = arena[po + k], y = arena[fo + k];
-                if (x != y) { cmp = x < y ? -1 : 1; break; }
-            }
-            if (cmp == 0) cmp = pl < fl ? -1 : (pl > fl ? 1 : 0);
-            if (cmp < 0) v = 0;
-        }
+        vn = order_violation(arena, p, c, 0);
+        vh = order_violation(arena, p, c, 1);
     }
-    viol[i] = v;
+    viol_n[i] = vn;
+    viol_h[i] = vh;
 }
 
 __device__ __forceinline__ void put_u32(uint8_t *p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); }
 
-// records written at their offsets; off[i] / cnt[i] = bytes / records before child i (n + 1 entries)
-__global__ void field_pack_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, int which,
-                                  const unsigned long long *__restrict__ cs_excl, const unsigned long long *__restrict__ cs, uint8_t *blob,
-                                  uint32_t *off, uint32_t *cnt) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const unsigned long long e = cs_excl[i];
-    const uint32_t o = (uint32_t)e;
-    off[i] = o;
-    cnt[i] = (uint32_t)(e >> 32);
-    if (i + 1 == n) {
-        const unsigned long long t = e + cs[i];
-        off[n] = (uint32_t)t;
-        cnt[n] = (uint32_t)(t >> 32);
-    }
-    uint32_t fo, fl;
-    const ChildRef c = refs[i];
-    if (!field_of(c, which, &fo, &fl)) return;
-    uint8_t *w = blob + o;
+__device__ __forceinline__ void put_record(uint8_t *w, const uint8_t *arena, uint32_t fo, uint32_t fl, const ChildRef &c) {
     put_u32(w, fl);
     for (uint32_t k = 0; k < fl; k++) w[4 + k] = arena[fo + k];
     put_u32(w + 4 + fl, c.klen);
     for (uint32_t k = 0; k < c.klen; k++) w[8 + fl + k] = arena[c.koff + k];
 }
 
+// keys and records written at their offsets; tables get their n + 1 entries
+__global__ void child_pack_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, IndexTables tb) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const ChildRef c = refs[i];
+    const uint32_t ko = tb.key_excl[i];
+    const unsigned long long en = tb.rec_excl[0][i], eh = tb.rec_excl[1][i];
+    tb.key_off[i] = ko;
+    tb.off[0][i] = (uint32_t)en; tb.cnt[0][i] = (uint32_t)(en >> 32);
+    tb.off[1][i] = (uint32_t)eh; tb.cnt[1][i] = (uint32_t)(eh >> 32);
+    if (i + 1 == n) {
+        tb.key_off[n] = ko + c.klen;
+        const unsigned long long tn = en + tb.rec[0][i], th = eh + tb.rec[1][i];
+        tb.off[0][n] = (uint32_t)tn; tb.cnt[0][n] = (uint32_t)(tn >> 32);
+        tb.off[1][n] = (uint32_t)th; tb.cnt[1][n] = (uint32_t)(th >> 32);
+    }
+    for (uint32_t k = 0; k < c.klen; k++) tb.keys[ko + k] = arena[c.koff + k];
+    if (c.nlen != 0xffffffffu) put_record(tb.blob[0] + (uint32_t)en, arena, c.noff, c.nlen, c);
+    if (c.hlen != 0xffffffffu) put_record(tb.blob[1] + (uint32_t)eh, arena, c.hoff, c.hlen, c);
+}
+
 }  // namespace
 
-cudaError_t launch_field_sizes(const uint8_t *arena, const ChildRef *refs, uint32_t n, int which, unsigned long long *cs, uint32_t *viol,
-                               cudaStream_t s) {
-    if (n == 0) return cudaSuccess;
-    field_sizes_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, n, which, cs, viol);
+cudaError_t launch_child_refs(const TapeView &t, const ModuleInfo *info, const uint32_t *flags, const uint32_t *rank, ChildRef *refs,
+                              cudaStream_t s) {
+    child_refs_kernel<<<(t.n_rows + 255) / 256, 256, 0, s>>>(t, info, flags, rank, refs);
     count_parse_launch();
     return cudaGetLastError();
 }
-cudaError_t launch_field_pack(const uint8_t *arena, const ChildRef *refs, uint32_t n, int which, const unsigned long long *cs_excl,
-                              const unsigned long long *cs, uint8_t *blob, uint32_t *off, uint32_t *cnt, cudaStream_t s) {
+cudaError_t launch_child_sizes(const uint8_t *arena, const ChildRef *refs, uint32_t n, uint32_t *key_bytes, unsigned long long *rec_n,
+                               unsigned long long *rec_h, uint32_t *viol_n, uint32_t *viol_h, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    field_pack_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, n, which, cs_excl, cs, blob, off, cnt);
+    child_sizes_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, n, key_bytes, rec_n, rec_h, viol_n, viol_h);
+    count_parse_launch();
+    return cudaGetLastError();
+}
+cudaError_t launch_child_pack(const uint8_t *arena, const ChildRef *refs, uint32_t n, const IndexTables &tb, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    child_pack_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, n, tb);
     count_parse_launch();
     return cudaGetLastError();
 }
@@ -186,21 +179,6 @@ cudaError_t launch_find_module(const TapeView &t, const uint32_t *br_match, cons
 
 cudaError_t launch_child_flags(const TapeView &t, const ModuleInfo *info, uint32_t *flags, cudaStream_t s) {
     child_flags_kernel<<<(t.n_rows + 255) / 256, 256, 0, s>>>(t, info, flags);
-    count_parse_launch();
-    return cudaGetLastError();
-}
-
-cudaError_t launch_child_entries(const TapeView &t, const uint32_t *flags, const uint32_t *rank, const uint32_t *br_match,
-                                 const uint32_t *br_row, ChildRef *refs, uint32_t *sizes, cudaStream_t s) {
-    child_entries_kernel<<<(t.n_rows + 255) / 256, 256, 0, s>>>(t, flags, rank, br_match, br_row, refs, sizes);
-    count_parse_launch();
-    return cudaGetLastError();
-}
-
-cudaError_t launch_child_pack(const uint8_t *arena, const ChildRef *refs, const uint32_t *off, uint32_t n, ChildEntry *entries,
-                              uint8_t *packed, cudaStream_t s) {
-    if (n == 0) return cudaSuccess;
-    child_pack_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, off, n, entries, packed);
     count_parse_launch();
     return cudaGetLastError();
 }
