@@ -116,6 +116,25 @@ def test_long_strings(tk, oracle, n):
     same(tk, oracle, raw)
 
 
+@pytest.mark.parametrize("run", [1, 2, 3, 7, 8, 9, 62, 63, 64, 65, 66, 127, 128, 129, 511, 512, 513, 575, 576, 577, 2047, 2048, 8191, 8192, 8193,
+                                 16385, 40000, 40001])
+@pytest.mark.parametrize("lead", [0, 1, 5, 61, 62, 63, 2040, 8185])
+def test_backslash_runs(tk, oracle, run, lead):
+    """A run of backslashes before a quote, of every parity and at every alignment against the
+    64-byte chunks, the warps and the 8 KiB tiles of the token scan.  Short runs are resolved by the
+    look-behind of the fast kernel; runs past 512 bytes send the parse through the carry protocol.
+    An odd run escapes the quote: the string then ends at the next one (or the text is invalid)."""
+    raw = b'{"k":"' + b"x" * lead + b"\\" * run + b'","z":"\\\\"}'
+    try:
+        want = oracle.New("x", raw).Bytes()
+    except oracle.OracleError as e:
+        with pytest.raises(tk.StateError) as got:
+            tk.New("x", raw)
+        assert str(got.value) == str(e)
+        return
+    assert tk.New("x", raw).Bytes() == want
+
+
 @pytest.mark.parametrize("depth", [1, 2, 31, 100, 1000, 10000])
 def test_deep_nesting(tk, oracle, depth):
     same(tk, oracle, b"[" * depth + b"]" * depth)

@@ -480,6 +480,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     // ---- P1 (re-run with a larger token buffer in the rare case the estimate was too small)
     size_t cap = n / 4 + 4096;
     TokenBuffers tb{};
+    bool carry_protocol = false;  // set when the fast kernel met a backslash run longer than its look-behind
     for (;;) {
         if ((e = d_tok_pos_.reserve((cap + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(tokens)", err);
         if ((e = d_tok_kind_.reserve(cap + 4096 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(tokens)", err);
@@ -487,10 +488,11 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
         if ((e = d_scratch_.reserve(p1_scratch_words(n) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
         tb.pos = d_tok_pos_.as<uint32_t>(); tb.kind = d_tok_kind_.as<uint8_t>(); tb.decode_bits = d_dec_bits_.as<uint32_t>();
         tb.cap = (uint32_t)cap;
-        if ((e = timed(K_SCAN_TOKENS, [&] { return launch_scan_tokens(raw, n, tb, d_scratch_.as<unsigned long long>(), d_res, stream_); })) != cudaSuccess)
+        if ((e = timed(K_SCAN_TOKENS, [&] { return launch_scan_tokens(raw, n, tb, d_scratch_.as<unsigned long long>(), d_res, carry_protocol, stream_); })) != cudaSuccess)
             return fail(e, "scan_tokens", err);
         int rc = fetch_result(err);
         if (rc) return rc;
+        if (h_res_.p->slow_scan && !carry_protocol) { carry_protocol = true; continue; }
         if (h_res_.p->n_tokens <= cap) break;
         if (h_res_.p->n_tokens >= 0x7ffffff0ull) { *err = "document too large: more than 2^31 tokens"; return TK_ELIMIT; }
         cap = (size_t)h_res_.p->n_tokens;

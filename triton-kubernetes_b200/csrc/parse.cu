@@ -6,6 +6,7 @@
 // reports that keys are not strictly ascending).
 #include "parse.cuh"
 
+#include <algorithm>
 #include <atomic>
 
 namespace tk {
@@ -36,6 +37,7 @@ __device__ __forceinline__ u64 low_mask(int i) { return i >= 64 ? ~0ull : ((1ull
 // P1: bytes -> tokens
 // =================================================================================================
 
+// ---- byte classes of the carry-protocol kernel (scan_tokens_kernel): one flag byte per text byte
 constexpr uint32_t C_QUOTE = 1, C_BS = 2, C_WS = 4, C_ST = 8, C_CTRL = 16, C_HTML = 32;
 
 __device__ __forceinline__ uint32_t byte_class(uint32_t c) {
@@ -53,6 +55,41 @@ __device__ __forceinline__ uint32_t byte_class(uint32_t c) {
 __device__ __forceinline__ uint32_t gather4(uint32_t x, int j) {
     return (((x >> j) & 0x01010101u) * 0x01020408u) >> 24;
 }
+
+// ---- byte classes of the fast kernel (scan_tokens_fast_kernel).
+// The kernel needs, per 64-byte chunk, one 64-bit mask per class.  Each class flag
+// of a byte is looked up ALREADY AT ITS PLACE: table j (for byte j of a 32-bit word) holds the
+// quote flag at bit j, white space at bit 8 + j, structural at bit 16 + j and "rare" at bit 24 + j,
+// so OR-ing the four look-ups of a word gives one nibble per class, an odd word is shifted left by
+// 4, and a byte permute of four such pairs yields 32 mask bits per class without any bit gathering.
+// "Rare" bytes (backslash, control bytes other than tab/newline/return, < > &, non-ASCII) are told
+// apart afterwards, one by one, only in chunks that have any.
+constexpr bool is_ws(uint32_t c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; }
+constexpr bool is_struct(uint32_t c) { return c == '{' || c == '}' || c == '[' || c == ']' || c == ':' || c == ','; }
+constexpr bool is_rare(uint32_t c) { return c == '\\' || (c < 0x20 && !is_ws(c)) || c == '<' || c == '>' || c == '&' || c >= 0x80; }
+
+struct ClassLut { uint32_t v[4 * 256]; };
+constexpr ClassLut make_class_lut() {
+    ClassLut t{};
+    for (uint32_t j = 0; j < 4; j++)
+        for (uint32_t c = 0; c < 256; c++)
+            t.v[j * 256 + c] = ((c == '"' ? 1u : 0u) << j) | ((is_ws(c) ? 1u : 0u) << (8 + j)) | ((is_struct(c) ? 1u : 0u) << (16 + j)) |
+                               ((is_rare(c) ? 1u : 0u) << (24 + j));
+    return t;
+}
+__device__ const ClassLut g_class_lut = make_class_lut();
+
+// token kind of the byte a token starts at (a closing quote is T_STR_OPEN + 1)
+struct KindLut { uint8_t v[256]; };
+constexpr KindLut make_kind_lut() {
+    KindLut t{};
+    for (uint32_t c = 0; c < 256; c++)
+        t.v[c] = c == '{' ? T_LBRACE : c == '}' ? T_RBRACE : c == '[' ? T_LBRACKET : c == ']' ? T_RBRACKET : c == ':' ? T_COLON
+               : c == ',' ? T_COMMA : c == '"' ? T_STR_OPEN : is_ws(c) ? T_SCALAR_END : T_SCALAR;
+    return t;
+}
+__device__ const KindLut g_kind_lut = make_kind_lut();
+static_assert(T_STR_CLOSE == T_STR_OPEN + 1, "a closing quote is the opening kind plus the in-string bit");
 
 // simdjson's branch-free escape finder: bits that are escaped by a preceding backslash run.
 // carry: in = first byte of this word is escaped; out = first byte of the next word is escaped.
@@ -324,6 +361,11 @@ __global__ void __launch_bounds__(P1_THREADS) scan_tokens_kernel(const uint8_t *
         tb.kind[idx] = (uint8_t)k;
     }
 }
+
+// =================================================================================================
+// P1, fast path (count / prefix / emit): see scan_fast.cuh
+// =================================================================================================
+#include "scan_fast.cuh"
 
 // =================================================================================================
 // generic exclusive scan of u32 (single pass, decoupled look-back); total -> scratch[1]
@@ -1179,15 +1221,50 @@ __global__ void key_order_kernel(const uint8_t *__restrict__ arena, RowBuffers r
 // launch wrappers
 // =================================================================================================
 
-cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, unsigned long long *scratch, ParseResult *res,
-                               cudaStream_t s) {
-    cudaError_t e = cudaMemsetAsync(scratch, 0, p1_scratch_words(n) * 8, s);
+// resident blocks of the persistent fast kernel on the current device (asked once per device)
+static cudaError_t fast_scan_grid(uint32_t *count_blocks, uint32_t *emit_blocks) {
+    static std::atomic<uint32_t> cached[64][2];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
-    if ((e = cudaMemsetAsync(res, 0, sizeof(ParseResult), s)) != cudaSuccess) return e;
+    const bool slot = dev >= 0 && dev < 64;
+    uint32_t g0 = slot ? cached[dev][0].load() : 0, g1 = slot ? cached[dev][1].load() : 0;
+    if (!g0 || !g1) {
+        int a = 0, b = 0, sms = 0;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, scan_count_kernel, P1_THREADS, 0)) != cudaSuccess) return e;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, scan_emit_kernel, P1_THREADS, 0)) != cudaSuccess) return e;
+        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+        g0 = (uint32_t)(a > 0 ? a : 1) * (uint32_t)(sms > 0 ? sms : 1);
+        g1 = (uint32_t)(b > 0 ? b : 1) * (uint32_t)(sms > 0 ? sms : 1);
+        if (slot) { cached[dev][0].store(g0); cached[dev][1].store(g1); }
+    }
+    *count_blocks = g0;
+    *emit_blocks = g1;
+    return cudaSuccess;
+}
+
+cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, unsigned long long *scratch, ParseResult *res,
+                               bool carry_protocol, cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(res, 0, sizeof(ParseResult), s);
+    if (e != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(tb.decode_bits, 0, ((size_t)tb.cap + 31) / 32 * 4 + 4, s)) != cudaSuccess) return e;
     if (n == 0) return cudaSuccess;
-    scan_tokens_kernel<<<p1_tiles(n), P1_THREADS, 0, s>>>(raw, (u64)n, tb, scratch, res);
-    g_parse_launches++;
+    const uint32_t n_tiles = p1_tiles(n);
+    if (carry_protocol) {
+        if ((e = cudaMemsetAsync(scratch, 0, p1_scratch_words(n) * 8, s)) != cudaSuccess) return e;
+        scan_tokens_kernel<<<n_tiles, P1_THREADS, 0, s>>>(raw, (u64)n, tb, scratch, res);
+        g_parse_launches++;
+        return cudaGetLastError();
+    }
+    // fast path: every word of both tables is written before it is read, nothing to clear
+    u64 *tile_pre = scratch + 4;
+    uint32_t *tile_agg = reinterpret_cast<uint32_t *>(scratch + 4 + n_tiles);
+    uint32_t g_count = 0, g_emit = 0;
+    if ((e = fast_scan_grid(&g_count, &g_emit)) != cudaSuccess) return e;
+    scan_count_kernel<<<std::min(n_tiles, g_count), P1_THREADS, 0, s>>>(raw, n_tiles, tile_agg, res);
+    scan_prefix_kernel<<<1, PFX_THREADS, 0, s>>>(tile_agg, n_tiles, tile_pre, res);
+    scan_emit_kernel<<<std::min(n_tiles, g_emit), P1_THREADS, 0, s>>>(raw, (u64)n, n_tiles, tb, tile_pre, res);
+    g_parse_launches += 3;
     return cudaGetLastError();
 }
 

@@ -31,7 +31,10 @@ enum TokKind : uint8_t {
     T_STR_OPEN = 6, T_STR_CLOSE = 7, T_SCALAR = 8, T_SCALAR_END = 9
 };
 
-constexpr int P1_THREADS = 128;
+#ifndef TK_P1_THREADS
+#define TK_P1_THREADS 128
+#endif
+constexpr int P1_THREADS = TK_P1_THREADS;
 constexpr int P1_BYTES_PER_THREAD = 64;
 constexpr int P1_TILE = P1_THREADS * P1_BYTES_PER_THREAD;  // 8 KiB of text per block
 constexpr int TOK_TILE = 256;                              // tokens per block in the token passes
@@ -49,6 +52,8 @@ struct ParseResult {
     unsigned int not_canonical;   // keys out of order / duplicated, or numbers not in canonical form
     unsigned int need_host_numbers;
     unsigned long long side_bytes; // decoded bytes written to the side arena
+    unsigned int slow_scan;       // P1 met a backslash run longer than its local look-behind: run the carry protocol
+    unsigned int pad;
 };
 
 inline uint32_t p1_tiles(size_t n) { return (uint32_t)((n + P1_TILE - 1) / P1_TILE); }
@@ -86,8 +91,11 @@ struct DecodeBuffers {
 
 // raw must be readable (and space-padded) up to p1_tiles(n) * P1_TILE + 16 bytes.
 // scratch: p1_scratch_words(n) words.  Clears scratch, *res and tb.decode_bits on the stream first.
+// carry_protocol false: every thread finds the backslash-run carry into its 64 bytes by looking at
+// most 512 bytes behind it, and sets res->slow_scan if that was not enough (the caller then runs
+// the kernel again with carry_protocol true: the carry travels by decoupled look-back).
 cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, unsigned long long *scratch,
-                               ParseResult *res, cudaStream_t s);
+                               ParseResult *res, bool carry_protocol, cudaStream_t s);
 // scratch: 4 + 2 * tok_tiles(n_tok) words
 cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, unsigned long long *scratch,
                                 ParseResult *res, cudaStream_t s);

@@ -15,7 +15,7 @@ import os
 from ctypes import POINTER, byref, c_char_p, c_int, c_longlong, c_size_t, c_ulonglong, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtkstate.so")
+LIB_PATH = os.environ.get("TK_STATE_LIB") or os.path.join(_HERE, "libtkstate.so")   # the override is for A/B builds in development
 
 TK_OK, TK_ESYNTAX, TK_ECOLLISION, TK_ENOTOBJ, TK_EKEYPARTS, TK_ECUDA, TK_ELIMIT, TK_EARG, TK_EIO = range(9)
 TK_VALUE_MAP, TK_VALUE_RECORD = 0, 1
