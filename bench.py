@@ -7,11 +7,19 @@ One STEP is one pass of the hot path over the 62,177,405-byte synthetic document
 document this way).  The step itself is a compiled loop over the C ABI (tools/bench_driver.c), for
 both arms, so that Python call overhead is not measured as if it were the library.
 
-  value  the step with the text already resident in HBM and the result left in HBM, timed with
-         CUDA events (start on an idle device, end on the stream the library launches on)
+  value  the step with the text already resident in HBM and the result left in HBM
   e2e    the same step through the public C ABI with HOST buffers: pinned host text in, the
          host->device copy, kernels, and the device->host copy of the result text, all inside the
          timed region
+
+Both are whole-job throughput: K steps with `--inflight` documents in flight per GPU (default 4) --
+that many host threads each run whole steps on their own handle, i.e. their own stream and
+buffers, so one document's copies and host-side waits overlap another's kernels.  The path shards
+by document and the CPU arm runs one document per host thread the same way.  The
+timed region is bracketed by CUDA events recorded on an idle device before the first step and
+after every thread has waited for its last one.  The latency of a single document (one in flight;
+for `value` with L2 flushed before every step) is reported beside it in config.latency_ms_per_step,
+and the per-kernel times for the roofline come from that serial, L2-flushed run.
   --impl reference   the CPU oracle (oracle/tk_oracle.c, a restatement of the reference's Go
          code; the Go toolchain is absent) on every host core, same step, same metric
 
@@ -48,6 +56,9 @@ def parse_args():
     ap.add_argument("--clusters", type=int, default=1000, help=argparse.SUPPRESS)
     ap.add_argument("--nodes", type=int, default=100, help=argparse.SUPPRESS)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help=argparse.SUPPRESS)
+    ap.add_argument("--inflight", type=int, default=0,
+                    help="documents in flight per GPU: that many host threads each run whole steps on their own handle and "
+                         "stream (default: 4, fewer if the host has under 4 cores per rank)")
     return ap.parse_args()
 
 
@@ -229,13 +240,14 @@ def run_ours(args, rank, local_rank, world):
             dist.barrier()
             torch.cuda.synchronize()
 
-    phase = (c_double * 5)()
+    R_COPIES = 4   # the resident input rotates over 4 device copies (249 MB > L2) when steps overlap
+    dev_copies = [dev_text] + [dev_text.clone() for _ in range(R_COPIES - 1)]
+    torch.cuda.synchronize()
 
-    def step(device_text, to_host):
+    def step(src_ptr, device_text, to_host, phase):
         """One step through the C driver; returns the handle (caller frees) and the result view."""
         h, out, n = c_void_p(), c_void_p(), c_size_t()
-        src = dev_text.data_ptr() if device_text else pinned.data_ptr()
-        rc = D.tkb_product_step(src, len(text), 1 if device_text else 0, 1 if to_host else 0, arr, lens, len(cks), args.clusters,
+        rc = D.tkb_product_step(src_ptr, len(text), 1 if device_text else 0, 1 if to_host else 0, arr, lens, len(cks), args.clusters,
                                 args.clusters * args.nodes, phase, byref(h), byref(out), byref(n))
         if rc or n.value != len(text):
             raise SystemExit("bench.py: step failed (%d): %s" % (rc, L.tk_last_error(h if h.value else None)))
@@ -252,14 +264,15 @@ def run_ours(args, rank, local_rank, world):
             kind += 1
 
     def timed_resident(steps, per_kernel):
+        """Serial steps (one document at a time), L2 flushed before each: latency and per-kernel times."""
         L.tk_set_default_timing(1 if per_kernel else 0)
-        total, stats = 0.0, {}
+        total, stats, phase = 0.0, {}, (c_double * 5)()
         for _ in range(steps):
             flush.zero_()
             torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            h, _ = step(True, False)
+            h, _ = step(dev_text.data_ptr(), True, False, phase)
             b.record(torch.cuda.ExternalStream(L.tk_state_stream(h), device=dev))
             b.synchronize()
             total += a.elapsed_time(b)
@@ -269,46 +282,75 @@ def run_ours(args, rank, local_rank, world):
         L.tk_set_default_timing(0)
         return total, stats
 
-    # ---- value: text resident in HBM, result left in HBM
-    for _ in range(args.warmup):
-        h, _ = step(True, False)
+    def run_overlapped(steps, inflight, to_host):
+        """`steps` whole steps, `inflight` at a time: each host thread runs whole steps on its own
+        handle (own stream, own buffers).  Timed with CUDA events recorded on an idle device before
+        the first step and after every thread has waited for its last one; returns (ms, phases, copy stats)."""
+        lock, nxt, errs, copy, phases = threading.Lock(), [0], [], [0, 0], []
+
+        def work():
+            torch.cuda.set_device(local_rank)
+            phase = (c_double * 5)()
+            phases.append(phase)
+            while True:
+                with lock:
+                    i = nxt[0]
+                    nxt[0] += 1
+                if i >= steps or errs:
+                    return
+                try:
+                    src = pinned.data_ptr() if to_host else dev_copies[i % R_COPIES].data_ptr()
+                    h, out = step(src, not to_host, to_host, phase)
+                    if to_host:
+                        ok = ctypes.string_at(out + len(text) - 64, 64) == text[-64:] and ctypes.string_at(out, 64) == text[:64]
+                        a, b = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+                        L.tk_state_copy_stats(h, byref(a), byref(b))
+                        copy[0], copy[1] = a.value, b.value
+                        if not ok:
+                            errs.append("a step returned a wrong result")
+                    else:
+                        torch.cuda.ExternalStream(L.tk_state_stream(h), device=dev).synchronize()
+                    L.tk_state_free(h)
+                except BaseException as e:  # noqa: BLE001 -- reported by the caller
+                    errs.append(repr(e))
+
         torch.cuda.synchronize()
-        L.tk_state_free(h)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        t0 = time.perf_counter()
+        ts = [threading.Thread(target=work) for _ in range(max(1, inflight))]
+        for t in ts: t.start()
+        for t in ts: t.join()
+        torch.cuda.synchronize()
+        b.record()
+        b.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        if errs:
+            raise SystemExit("bench.py: " + errs[0])
+        ph = [sum(p[i] for p in phases) / steps for i in range(4)]
+        return max(a.elapsed_time(b), wall), ph, tuple(copy)
+
+    inflight = args.inflight if args.inflight > 0 else max(1, min(4, (os.cpu_count() or 1) // max(1, world)))
+    # ---- value: text resident in HBM, result left in HBM
+    run_overlapped(max(args.warmup, inflight), inflight, False)
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
     launches0 = tk.state.kernel_launches()
-    ms_value, _ = timed_resident(args.steps, per_kernel=False)
+    ms_value, _, _ = run_overlapped(args.steps, inflight, False)
     launches = tk.state.kernel_launches() - launches0
     barrier()
+    ms_serial, _ = timed_resident(min(args.steps, 10), per_kernel=False)
+    ms_serial /= min(args.steps, 10)
 
     # ---- e2e: pinned host text in, host text out
-    def e2e_step():
-        h, out = step(False, True)
-        ok = ctypes.string_at(out + len(text) - 64, 64) == text[-64:] and ctypes.string_at(out, 64) == text[:64]
-        a, b = ctypes.c_ulonglong(), ctypes.c_ulonglong()
-        L.tk_state_copy_stats(h, byref(a), byref(b))
-        L.tk_state_free(h)
-        if not ok:
-            raise SystemExit("bench.py: e2e step returned a wrong result")
-        return a.value, b.value
-
-    for _ in range(args.warmup):
-        copy_stats = e2e_step()
+    run_overlapped(max(args.warmup, inflight), inflight, True)
     barrier()
-    for i in range(5):
-        phase[i] = 0.0
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        copy_stats = e2e_step()
-    torch.cuda.synchronize()
-    b.record()
-    b.synchronize()
-    ms_e2e = max(a.elapsed_time(b), (time.perf_counter() - t0) * 1e3)
-    phase_ms = {k: phase[i] / args.steps for i, k in enumerate(("new", "clusters", "nodes_x%d" % len(cks), "bytes"))}
+    ms_e2e, ph, copy_stats = run_overlapped(args.steps, inflight, True)
+    phase_ms = {k: ph[i] for i, k in enumerate(("new", "clusters", "nodes_x%d" % len(cks), "bytes"))}
     barrier()
+    ms_e2e_serial, _, _ = run_overlapped(min(args.steps, 10), 1, True)
+    ms_e2e_serial /= min(args.steps, 10)
     clocks = sampler.stop()
 
     # ---- per-kernel device times for the roofline (the same steps again, events around every launch)
@@ -341,7 +383,12 @@ def run_ours(args, rank, local_rank, world):
             "metric": "state.State ops/sec", "value": world * OPS_PER_STEP * args.steps / (ms_value * 1e-3), "unit": "ops/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_value / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "l2": "flushed (256 MiB write) between timed steps",
+            "config": {"workload": WORKLOAD, "documents_in_flight": inflight,
+                       "l2": ("every step reads one of %d device copies of the text in turn and streams about 400 MB of its own "
+                              "buffers: far more than the 126 MB L2 between two uses of anything" % R_COPIES) if inflight > 1 else
+                             "inputs rotate over %d device copies (249 MB > L2); the serial latency run flushes L2 (256 MiB write) "
+                             "before every step" % R_COPIES,
+                       "latency_ms_per_step": {"value_serial_l2_flushed": ms_serial, "e2e_serial": ms_e2e_serial},
                        "value_covers": "the whole step with the text already in HBM and the result left in HBM "
                                        "(the module index is copied to the host once per step: Clusters/Nodes look it up there)",
                        "driver": "tools/bench_driver.c (the step is a compiled loop over the C ABI)",

@@ -64,7 +64,7 @@ void *pool_alloc_pinned(size_t bytes, size_t *got) {
         if (!v.empty()) { void *p = v.back(); v.pop_back(); *got = c; return p; }
     }
     void *p = nullptr;
-    if (cudaHostAlloc(&p, c, cudaHostAllocPortable) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+    if (cudaHostAlloc(&p, c, cudaHostAllocPortable | cudaHostAllocMapped) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
     *got = c;
     return p;
 }
@@ -105,8 +105,21 @@ cudaError_t Engine::copy_h2d(void *dst, const void *src, size_t bytes) {
     h2d_bytes_ += bytes;
     return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream_);
 }
+// Small results (counts, the parse verdict: at most a few words) are written into pinned host
+// memory by a kernel.  A DMA copy of them would wait in the copy engine's queue behind the bulk
+// transfers of every other document in flight on this GPU, and the host waits for each of them.
+__global__ void publish_words_kernel(uint32_t *host_dst, const uint32_t *dev_src, uint32_t words) {
+    for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) host_dst[i] = dev_src[i];
+}
+
 cudaError_t Engine::copy_d2h(void *dst, const void *src, size_t bytes) {
     d2h_bytes_ += bytes;
+    if (bytes <= 256 && bytes % 4 == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 3) == 0) {
+        // every small destination in this file is a pinned block from pool_alloc_pinned (mapped)
+        publish_words_kernel<<<1, 32, 0, stream_>>>(static_cast<uint32_t *>(dst), static_cast<const uint32_t *>(src), (uint32_t)(bytes / 4));
+        count_parse_launch();
+        return cudaGetLastError();
+    }
     return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream_);
 }
 
@@ -146,12 +159,25 @@ int Engine::collect_times(std::string *err) {
     return TK_OK;
 }
 
+// streams are recycled like the buffers: a handle takes an idle one and gives it back drained
+namespace {
+struct StreamPool {
+    std::mutex mu;
+    std::map<int, std::vector<cudaStream_t>> idle;   // per device
+} g_stream_pool;
+}  // namespace
+
 Engine::~Engine() {
     for (auto &p : pending_) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto ev : free_events_) cudaEventDestroy(ev);
     if (stream_) {
-        cudaStreamSynchronize(stream_);
-        cudaStreamDestroy(stream_);
+        if (cudaStreamSynchronize(stream_) == cudaSuccess) {
+            std::lock_guard<std::mutex> lock(g_stream_pool.mu);
+            g_stream_pool.idle[device_].push_back(stream_);
+        } else {
+            (void)cudaGetLastError();
+            cudaStreamDestroy(stream_);
+        }
     }
 }
 
@@ -177,8 +203,15 @@ int Engine::init(std::string *err) {
     }
     e = cudaGetDevice(&device_);
     if (e != cudaSuccess) return fail(e, "cudaGetDevice", err);
-    e = cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking);
-    if (e != cudaSuccess) return fail(e, "cudaStreamCreate", err);
+    {
+        std::lock_guard<std::mutex> lock(g_stream_pool.mu);
+        auto &idle = g_stream_pool.idle[device_];
+        if (!idle.empty()) { stream_ = idle.back(); idle.pop_back(); }
+    }
+    if (!stream_) {
+        e = cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking);
+        if (e != cudaSuccess) return fail(e, "cudaStreamCreate", err);
+    }
     timing_ = g_default_timing.load();
     ready_ = true;
     return TK_OK;
@@ -740,7 +773,7 @@ int Engine::build_index(const Document &doc, std::string *err) {
     if ((e = d_scratch_.reserve(parse_scan_scratch_words((uint32_t)rows) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
     if (!h_minfo_.reserve(1) || !h_words_.reserve(8)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
     ModuleInfo *info = d_minfo_.as<ModuleInfo>();
-    unsigned long long *parked = reinterpret_cast<unsigned long long *>(d_minfo_.as<char>() + 32);  // scan totals kept across scans
+    unsigned long long *totals = reinterpret_cast<unsigned long long *>(d_minfo_.as<char>() + 32);  // per field: records << 32 | blob bytes
     unsigned long long *scratch = d_scratch_.as<unsigned long long>();
     uint32_t *flags = d_cflags_.as<uint32_t>(), *rank = d_crank_.as<uint32_t>();
     e = timed(K_MODULE_INDEX, [&] {
@@ -756,118 +789,128 @@ int Engine::build_index(const Document &doc, std::string *err) {
     const ModuleInfo mi = *h_minfo_.p;
     index_module_ok_ = mi.root_kind == ROW_OPEN_OBJ && (mi.module_kind == ROW_OPEN_OBJ || mi.module_kind == ROW_EMPTY_OBJ);
     const uint32_t n = index_module_ok_ ? (uint32_t)h_words_.p[0] : 0;
-    index_n_ = n;
-    index_hint_ = 0;
+    index_m_[0] = index_m_[1] = 0;
+    index_hint_[0] = index_hint_[1] = 0;
     if (n) {
-        DevBuf *need4[] = {&d_ckeyb_, &d_ckey_excl_, &d_cviol_[0], &d_cviol_[1], &d_cviol_excl_[0], &d_cviol_excl_[1], &d_ckey_off_,
-                           &d_foff_[0], &d_foff_[1], &d_fcnt_[0], &d_fcnt_[1]};
+        DevBuf *need4[] = {&d_cviol_[0], &d_cviol_[1], &d_foff_[0], &d_foff_[1]};
         for (DevBuf *b : need4)
             if ((e = b->reserve(((size_t)n + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
         DevBuf *need8[] = {&d_crec_[0], &d_crec_[1], &d_crec_excl_[0], &d_crec_excl_[1]};
         for (DevBuf *b : need8)
             if ((e = b->reserve(((size_t)n + 2) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+        const size_t bit_words = ((size_t)n + 31) / 32 + 1;
+        if ((e = d_fviolbits_[0].reserve(bit_words * 4)) != cudaSuccess || (e = d_fviolbits_[1].reserve(bit_words * 4)) != cudaSuccess)
+            return fail(e, "cudaMalloc(index)", err);
         if ((e = d_crefs_.reserve(((size_t)n + 1) * sizeof(ChildRef))) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-        // keys and records cannot outgrow the strings they are copied from
+        // records cannot outgrow the strings they are copied from
         const size_t cap = arena_used_ + 8 * (size_t)n + 64;
-        if ((e = d_ckeys_.reserve(cap)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
         if ((e = d_fblob_[0].reserve(cap)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
         if ((e = d_fblob_[1].reserve(cap)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
         ChildRef *refs = d_crefs_.as<ChildRef>();
         IndexTables tb;
-        tb.key_excl = d_ckey_excl_.as<uint32_t>();
-        tb.keys = d_ckeys_.as<uint8_t>();
-        tb.key_off = d_ckey_off_.as<uint32_t>();
         for (int f = 0; f < 2; f++) {
             tb.rec[f] = d_crec_[f].as<unsigned long long>();
             tb.rec_excl[f] = d_crec_excl_[f].as<unsigned long long>();
+            tb.viol[f] = d_cviol_[f].as<uint32_t>();
             tb.blob[f] = d_fblob_[f].as<uint8_t>();
             tb.off[f] = d_foff_[f].as<uint32_t>();
-            tb.cnt[f] = d_fcnt_[f].as<uint32_t>();
+            tb.viol_bits[f] = d_fviolbits_[f].as<uint32_t>();
         }
+        tb.totals = totals;
         e = timed(K_MODULE_INDEX, [&] {
             cudaError_t x;
             if ((x = cudaMemsetAsync(refs, 0xff, (size_t)n * sizeof(ChildRef), stream_)) != cudaSuccess) return x;
+            for (int f = 0; f < 2; f++)
+                if ((x = cudaMemsetAsync(d_fviolbits_[f].p, 0, bit_words * 4, stream_)) != cudaSuccess) return x;
             if ((x = launch_child_refs(tape_, info, flags, rank, refs, stream_)) != cudaSuccess) return x;
-            if ((x = launch_child_sizes(tape_.arena, refs, n, d_ckeyb_.as<uint32_t>(), d_crec_[0].as<unsigned long long>(),
-                                        d_crec_[1].as<unsigned long long>(), d_cviol_[0].as<uint32_t>(), d_cviol_[1].as<uint32_t>(), stream_)) != cudaSuccess) return x;
-            if ((x = scan_u32(d_ckeyb_.as<uint32_t>(), d_ckey_excl_.as<uint32_t>(), n, scratch, stream_)) != cudaSuccess) return x;
-            if ((x = cudaMemcpyAsync(parked, scratch + 1, 8, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return x;   // key bytes
-            for (int f = 0; f < 2; f++) {
-                if ((x = scan_u32(d_cviol_[f].as<uint32_t>(), d_cviol_excl_[f].as<uint32_t>(), n, scratch, stream_)) != cudaSuccess) return x;
-                if ((x = cudaMemcpyAsync(d_cviol_excl_[f].as<uint32_t>() + n, scratch + 1, 4, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return x;
+            if ((x = launch_child_sizes(tape_.arena, refs, n, d_crec_[0].as<unsigned long long>(), d_crec_[1].as<unsigned long long>(),
+                                        d_cviol_[0].as<uint32_t>(), d_cviol_[1].as<uint32_t>(), stream_)) != cudaSuccess) return x;
+            for (int f = 0; f < 2; f++)
                 if ((x = scan_u64(d_crec_[f].as<unsigned long long>(), d_crec_excl_[f].as<unsigned long long>(), n, scratch, stream_)) != cudaSuccess) return x;
-                if ((x = cudaMemcpyAsync(parked + 1 + f, scratch + 1, 8, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return x;  // count << 32 | bytes
-            }
             return launch_child_pack(tape_.arena, refs, n, tb, stream_);
         });
         if (e != cudaSuccess) return fail(e, "module index", err);
-        if ((e = copy_d2h(h_words_.p, parked, 24)) != cudaSuccess) return fail(e, "copy index sizes", err);
-        if (!h_key_off_.reserve((size_t)n + 1)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
-        if ((e = copy_d2h(h_key_off_.p, d_ckey_off_.p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+        if ((e = copy_d2h(h_words_.p, totals, 16)) != cudaSuccess) return fail(e, "copy index sizes", err);
+        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
         for (int f = 0; f < 2; f++) {
-            if (!h_foff_[f].reserve((size_t)n + 1) || !h_fcnt_[f].reserve((size_t)n + 1) || !h_fviol_[f].reserve((size_t)n + 1)) {
+            const uint32_t m = (uint32_t)(h_words_.p[f] >> 32);
+            const size_t bytes = (size_t)(uint32_t)h_words_.p[f];
+            index_m_[f] = m;
+            if (!m) continue;
+            if (!h_foff_[f].reserve((size_t)m + 1) || !h_fviolbits_[f].reserve(((size_t)m + 31) / 32 + 1) || !h_fblob_[f].reserve(bytes + 1)) {
                 *err = "cuda: pinned host allocation failed";
                 return TK_ECUDA;
             }
-            if ((e = copy_d2h(h_foff_[f].p, d_foff_[f].p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
-            if ((e = copy_d2h(h_fcnt_[f].p, d_fcnt_[f].p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
-            if ((e = copy_d2h(h_fviol_[f].p, d_cviol_excl_[f].p, ((size_t)n + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+            if ((e = copy_d2h(h_foff_[f].p, d_foff_[f].p, ((size_t)m + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+            if ((e = copy_d2h(h_fviolbits_[f].p, d_fviolbits_[f].p, (((size_t)m + 31) / 32) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+            if ((e = copy_d2h(h_fblob_[f].p, d_fblob_[f].p, bytes)) != cudaSuccess) return fail(e, "copy index", err);
         }
-        // blob sizes are bounded by what the tables say once they arrive; copy with the upper bounds
-        // the host can compute now: keys <= key offsets' last entry is not known yet, so synchronise
-        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
-        const size_t key_bytes = (size_t)h_words_.p[0];
-        const size_t rec_bytes[2] = {(size_t)(uint32_t)h_words_.p[1], (size_t)(uint32_t)h_words_.p[2]};
-        if (!h_ckeys_.reserve(key_bytes + 1) || !h_fblob_[0].reserve(rec_bytes[0] + 1) || !h_fblob_[1].reserve(rec_bytes[1] + 1)) {
-            *err = "cuda: pinned host allocation failed";
-            return TK_ECUDA;
-        }
-        if (key_bytes && (e = copy_d2h(h_ckeys_.p, d_ckeys_.p, key_bytes)) != cudaSuccess) return fail(e, "copy index", err);
-        for (int f = 0; f < 2; f++)
-            if (rec_bytes[f] && (e = copy_d2h(h_fblob_[f].p, d_fblob_[f].p, rec_bytes[f])) != cudaSuccess) return fail(e, "copy index", err);
         if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
     }
     index_version_ = doc.version;
     return TK_OK;
 }
 
-// first and one-past-last child whose key starts with prefix (children are in bytewise key order)
-void Engine::index_range(std::string_view prefix, uint32_t *lo_out, uint32_t *hi_out) {
-    const uint32_t *ko = h_key_off_.p;
-    const char *keys = reinterpret_cast<const char *>(h_ckeys_.p);
-    auto key_at = [&](uint32_t i) { return std::string_view(keys + ko[i], ko[i + 1] - ko[i]); };
-    auto has_prefix = [&](uint32_t i) { return ko[i + 1] - ko[i] >= prefix.size() && memcmp(keys + ko[i], prefix.data(), prefix.size()) == 0; };
+// Record j of field f (the j-th child, in key order, that has the field): { u32 field_len, field,
+// u32 key_len, key } at blob + off[j].
+struct Engine::IndexView {
+    const uint32_t *off;
+    const char *blob;
+    uint32_t m;
+    std::string_view key(uint32_t j) const {
+        const char *rec = blob + off[j];
+        uint32_t fl, kl;
+        memcpy(&fl, rec, 4);
+        memcpy(&kl, rec + 4 + fl, 4);
+        return std::string_view(rec + 8 + fl, kl);
+    }
+    std::string_view field(uint32_t j) const {
+        const char *rec = blob + off[j];
+        uint32_t fl;
+        memcpy(&fl, rec, 4);
+        return std::string_view(rec + 4, fl);
+    }
+    bool has_prefix(uint32_t j, std::string_view prefix) const {
+        const std::string_view k = key(j);
+        return k.size() >= prefix.size() && memcmp(k.data(), prefix.data(), prefix.size()) == 0;
+    }
+};
+
+// first and one-past-last record of field f whose key starts with prefix (records are in bytewise key order)
+void Engine::index_range(int f, std::string_view prefix, uint32_t *lo_out, uint32_t *hi_out) {
+    const IndexView v{h_foff_[f].p, reinterpret_cast<const char *>(h_fblob_[f].p), index_m_[f]};
     uint32_t lo = 0;
-    if (index_hint_ < index_n_ && has_prefix(index_hint_) && (index_hint_ == 0 || key_at(index_hint_ - 1) < prefix)) {
-        lo = index_hint_;  // a sweep over clusters in order: this run starts where the previous one ended
+    const uint32_t hint = index_hint_[f];
+    if (hint < v.m && v.has_prefix(hint, prefix) && (hint == 0 || v.key(hint - 1) < prefix)) {
+        lo = hint;  // a sweep over clusters in order: this run starts where the previous one ended
     } else {
-        uint32_t hi = index_n_;
+        uint32_t hi = v.m;
         while (lo < hi) {
             const uint32_t mid = (lo + hi) >> 1;
-            if (key_at(mid) < prefix) lo = mid + 1; else hi = mid;
+            if (v.key(mid) < prefix) lo = mid + 1; else hi = mid;
         }
     }
     // end of the run: gallop, then bisect (runs are short next to the index); keys with the prefix
     // are contiguous, so has_prefix is true ... true false ... from lo on
     uint32_t a = lo;
-    if (lo < index_n_ && has_prefix(lo)) {
-        uint32_t last_good = lo, step = 1, bad = index_n_;
+    if (lo < v.m && v.has_prefix(lo, prefix)) {
+        uint32_t last_good = lo, step = 1, bad = v.m;
         for (;;) {
             const uint64_t probe = (uint64_t)last_good + step;
-            if (probe >= index_n_) break;
-            if (has_prefix((uint32_t)probe)) { last_good = (uint32_t)probe; step <<= 1; }
+            if (probe >= v.m) break;
+            if (v.has_prefix((uint32_t)probe, prefix)) { last_good = (uint32_t)probe; step <<= 1; }
             else { bad = (uint32_t)probe; break; }
         }
         a = last_good + 1;
         uint32_t b = bad;
         while (a < b) {
             const uint32_t mid = (a + b) >> 1;
-            if (has_prefix(mid)) a = mid + 1; else b = mid;
+            if (v.has_prefix(mid, prefix)) a = mid + 1; else b = mid;
         }
     }
     *lo_out = lo;
     *hi_out = a;
-    index_hint_ = a;
+    index_hint_[f] = a;
 }
 
 // the run's (field value, key) pairs, for the caller to sort: used when the run is not in field order
@@ -877,20 +920,12 @@ int Engine::index_lookup(const Document &doc, std::string_view prefix, bool host
     if (rc) return rc;
     *module_ok = index_module_ok_;
     pairs->clear();
-    if (!index_module_ok_ || index_n_ == 0) return TK_OK;
     const int f = hostname ? 1 : 0;
+    if (!index_module_ok_ || index_m_[f] == 0) return TK_OK;
     uint32_t lo, hi;
-    index_range(prefix, &lo, &hi);
-    const uint32_t *off = h_foff_[f].p, *cnt = h_fcnt_[f].p;
-    const char *blob = reinterpret_cast<const char *>(h_fblob_[f].p);
-    for (uint32_t i = lo; i < hi; i++) {
-        if (cnt[i + 1] == cnt[i]) continue;  // this child has no such string field
-        const char *rec = blob + off[i];
-        uint32_t fl, kl;
-        memcpy(&fl, rec, 4);
-        memcpy(&kl, rec + 4 + fl, 4);
-        pairs->emplace_back(std::string_view(rec + 4, fl), std::string_view(rec + 8 + fl, kl));
-    }
+    index_range(f, prefix, &lo, &hi);
+    const IndexView v{h_foff_[f].p, reinterpret_cast<const char *>(h_fblob_[f].p), index_m_[f]};
+    for (uint32_t j = lo; j < hi; j++) pairs->emplace_back(v.field(j), v.key(j));
     return TK_OK;
 }
 
@@ -905,18 +940,25 @@ int Engine::index_lookup_direct(const Document &doc, std::string_view prefix, bo
     *blob = reinterpret_cast<const uint8_t *>("");
     *blob_len = 0;
     *count = 0;
-    if (!index_module_ok_ || index_n_ == 0) return TK_OK;
     const int f = hostname ? 1 : 0;
+    if (!index_module_ok_ || index_m_[f] == 0) return TK_OK;
     uint32_t lo, hi;
-    index_range(prefix, &lo, &hi);
+    index_range(f, prefix, &lo, &hi);
     if (lo == hi) return TK_OK;
-    // order violations strictly inside the run (child lo may compare with a child outside it)
-    const uint32_t *viol = h_fviol_[f].p;
-    if (viol[hi] - viol[lo + 1] != 0) { *direct = false; return TK_OK; }
-    const uint32_t *off = h_foff_[f].p, *cnt = h_fcnt_[f].p;
+    // order violations strictly inside the run (record lo may compare with a child outside it):
+    // any bit set among records lo + 1 .. hi - 1
+    const uint32_t *bits = h_fviolbits_[f].p;
+    for (uint32_t j = lo + 1; j < hi;) {
+        const uint32_t w = j >> 5, first = j & 31, last = std::min<uint32_t>(32, hi - (w << 5));   // bits [first, last) of word w
+        uint32_t mask = last >= 32 ? 0xffffffffu : ((1u << last) - 1);
+        mask &= ~((1u << first) - 1);
+        if (bits[w] & mask) { *direct = false; return TK_OK; }
+        j = (w + 1) << 5;
+    }
+    const uint32_t *off = h_foff_[f].p;
     *blob = h_fblob_[f].p + off[lo];
     *blob_len = off[hi] - off[lo];
-    *count = cnt[hi] - cnt[lo];
+    *count = hi - lo;
     return TK_OK;
 }
 

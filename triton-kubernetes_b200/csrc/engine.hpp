@@ -140,7 +140,8 @@ private:
     template <class F> cudaError_t timed(int kind, F &&launch);
     int fetch_result(std::string *err);
     int build_index(const Document &doc, std::string *err);
-    void index_range(std::string_view prefix, uint32_t *lo, uint32_t *hi);
+    struct IndexView;
+    void index_range(int field, std::string_view prefix, uint32_t *lo, uint32_t *hi);
 
     void flatten(const Document &doc);
     void flatten_keys(const Document &doc);
@@ -182,13 +183,13 @@ private:
     PinVec<unsigned long long> h_words_;
 
     // module index (csrc/index.cu)
-    DevBuf d_minfo_, d_cflags_, d_crank_, d_crefs_, d_ckeyb_, d_ckey_excl_, d_ckeys_, d_ckey_off_;
-    DevBuf d_crec_[2], d_crec_excl_[2], d_cviol_[2], d_cviol_excl_[2], d_fblob_[2], d_foff_[2], d_fcnt_[2];
+    DevBuf d_minfo_, d_cflags_, d_crank_, d_crefs_;
+    DevBuf d_crec_[2], d_crec_excl_[2], d_cviol_[2], d_fviolbits_[2], d_fblob_[2], d_foff_[2];
     PinVec<ModuleInfo> h_minfo_;
-    PinVec<uint8_t> h_ckeys_, h_fblob_[2];
-    PinVec<uint32_t> h_key_off_, h_foff_[2], h_fcnt_[2], h_fviol_[2];
+    PinVec<uint8_t> h_fblob_[2];
+    PinVec<uint32_t> h_foff_[2], h_fviolbits_[2];
     uint64_t index_version_ = 0;
-    uint32_t index_n_ = 0, index_hint_ = 0;
+    uint32_t index_m_[2] = {0, 0}, index_hint_[2] = {0, 0};   // per field: records in the index, where the last run ended
     bool index_module_ok_ = false;
     BracketBuffers bb_{};  // bracket tables of the last parse (match / row are read by the index kernels)
 

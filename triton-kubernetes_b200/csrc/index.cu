@@ -3,11 +3,11 @@
 //
 // state/state.go:94-147 scan every child of "module" for a key prefix and read one string field
 // of each hit ("name" for clusters, "hostname" for nodes).  Here one bulk pass per document
-// version classifies all module children at once and packs, per child, its key and those two
-// fields into a small arena (about 5 MB for the 101,001 children of config #4).  The arena goes
-// to the host once; because the children are in bytewise key order, each Clusters()/Nodes() call
-// is then a binary search for the prefix range over that packed index instead of a 3.5 MB scan
-// and a kernel launch per call.
+// version classifies all module children at once and packs, per field, the result records of the
+// children that have it (about 6.4 MB for the 101,001 children of config #4).  The records go to
+// the host once; because the children are in bytewise key order, each Clusters()/Nodes() call is
+// then a binary search for the prefix range over them instead of a 3.5 MB scan and a kernel
+// launch per call.
 #include "index.cuh"
 
 namespace tk {
@@ -71,12 +71,12 @@ __global__ void child_refs_kernel(TapeView t, const ModuleInfo *__restrict__ inf
 }
 
 // ---- what goes to the host -------------------------------------------------------------------
-// (1) the keys, packed in child (= bytewise key) order, for the prefix search;
-// (2) per field ("name" for Clusters, "hostname" for Nodes) the finished C-ABI result records of
-//     the children that have it -- { u32 field_len, field, u32 key_len, key } -- packed in child
-//     order, so that the answer to a prefix query is the byte range of a run of children provided
-//     the field values in the run ascend strictly (the ABI returns pairs sorted by field, one per
-//     value); `viol` marks the places where they do not, so the host can tell in O(1).
+// Per field ("name" for Clusters, "hostname" for Nodes) the finished C-ABI result records of the
+// children that have it -- { u32 field_len, field, u32 key_len, key } -- packed in child (= bytewise
+// key) order, with one offset per record.  The host finds the run of records whose key starts with
+// the prefix by binary search over the records themselves, and the answer to the query is the byte
+// range of that run provided the field values in it ascend strictly (the ABI returns pairs sorted
+// by field, one per value); a bitmap marks the records where they do not.
 
 __device__ __forceinline__ bool field_of(const ChildRef &c, int which, uint32_t *off, uint32_t *len) {
     *off = which ? c.hoff : c.noff;
@@ -96,13 +96,12 @@ __device__ __forceinline__ uint32_t order_violation(const uint8_t *arena, const 
     return pl < fl ? 0u : 1u;
 }
 
-// per child: key bytes, (has field) << 32 | record bytes for both fields, and the violation flags
-__global__ void child_sizes_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, uint32_t *key_bytes,
+// per child: (has field) << 32 | record bytes for both fields, and the violation flags
+__global__ void child_sizes_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n,
                                    unsigned long long *rec_n, unsigned long long *rec_h, uint32_t *viol_n, uint32_t *viol_h) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const ChildRef c = refs[i];
-    key_bytes[i] = c.klen;
     rec_n[i] = c.nlen != 0xffffffffu ? ((1ull << 32) | (8ull + c.nlen + c.klen)) : 0ull;
     rec_h[i] = c.hlen != 0xffffffffu ? ((1ull << 32) | (8ull + c.hlen + c.klen)) : 0ull;
     uint32_t vn = 0, vh = 0;
@@ -124,25 +123,31 @@ __device__ __forceinline__ void put_record(uint8_t *w, const uint8_t *arena, uin
     for (uint32_t k = 0; k < c.klen; k++) w[8 + fl + k] = arena[c.koff + k];
 }
 
-// keys and records written at their offsets; tables get their n + 1 entries
+// Records written at their offsets.  Per field the children that have it form a compact list (in
+// child = key order): off[j] is where record j starts (m + 1 entries), bit j of viol_bits says that
+// record j does not sort strictly after the child before it.  The last child also leaves the
+// totals (records << 32 | bytes) for the host.  viol_bits must have been cleared.
 __global__ void child_pack_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, IndexTables tb) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const ChildRef c = refs[i];
-    const uint32_t ko = tb.key_excl[i];
-    const unsigned long long en = tb.rec_excl[0][i], eh = tb.rec_excl[1][i];
-    tb.key_off[i] = ko;
-    tb.off[0][i] = (uint32_t)en; tb.cnt[0][i] = (uint32_t)(en >> 32);
-    tb.off[1][i] = (uint32_t)eh; tb.cnt[1][i] = (uint32_t)(eh >> 32);
-    if (i + 1 == n) {
-        tb.key_off[n] = ko + c.klen;
-        const unsigned long long tn = en + tb.rec[0][i], th = eh + tb.rec[1][i];
-        tb.off[0][n] = (uint32_t)tn; tb.cnt[0][n] = (uint32_t)(tn >> 32);
-        tb.off[1][n] = (uint32_t)th; tb.cnt[1][n] = (uint32_t)(th >> 32);
+#pragma unroll
+    for (int f = 0; f < 2; f++) {
+        const unsigned long long ex = tb.rec_excl[f][i];
+        const uint32_t byte_off = (uint32_t)ex, j = (uint32_t)(ex >> 32);
+        uint32_t fo, fl;
+        const bool has = field_of(c, f, &fo, &fl);
+        if (has) {
+            tb.off[f][j] = byte_off;
+            if (tb.viol[f][i]) atomicOr(tb.viol_bits[f] + (j >> 5), 1u << (j & 31));
+            put_record(tb.blob[f] + byte_off, arena, fo, fl, c);
+        }
+        if (i + 1 == n) {
+            const unsigned long long total = ex + tb.rec[f][i];
+            tb.off[f][(uint32_t)(total >> 32)] = (uint32_t)total;
+            tb.totals[f] = total;
+        }
     }
-    for (uint32_t k = 0; k < c.klen; k++) tb.keys[ko + k] = arena[c.koff + k];
-    if (c.nlen != 0xffffffffu) put_record(tb.blob[0] + (uint32_t)en, arena, c.noff, c.nlen, c);
-    if (c.hlen != 0xffffffffu) put_record(tb.blob[1] + (uint32_t)eh, arena, c.hoff, c.hlen, c);
 }
 
 }  // namespace
@@ -153,10 +158,10 @@ cudaError_t launch_child_refs(const TapeView &t, const ModuleInfo *info, const u
     count_parse_launch();
     return cudaGetLastError();
 }
-cudaError_t launch_child_sizes(const uint8_t *arena, const ChildRef *refs, uint32_t n, uint32_t *key_bytes, unsigned long long *rec_n,
+cudaError_t launch_child_sizes(const uint8_t *arena, const ChildRef *refs, uint32_t n, unsigned long long *rec_n,
                                unsigned long long *rec_h, uint32_t *viol_n, uint32_t *viol_h, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    child_sizes_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, n, key_bytes, rec_n, rec_h, viol_n, viol_h);
+    child_sizes_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, n, rec_n, rec_h, viol_n, viol_h);
     count_parse_launch();
     return cudaGetLastError();
 }
@@ -168,10 +173,12 @@ cudaError_t launch_child_pack(const uint8_t *arena, const ChildRef *refs, uint32
 }
 
 cudaError_t launch_find_module(const TapeView &t, const uint32_t *br_match, const uint32_t *br_row, ModuleInfo *info, cudaStream_t s) {
-    ModuleInfo init;
-    init.root_kind = 0xff; init.module_kind = 0xff; init.module_row = 0; init.module_end = 0; init.n_children = 0; init.pad = 0;
-    cudaError_t e = cudaMemcpyAsync(info, &init, sizeof init, cudaMemcpyHostToDevice, s);  // 24 bytes from pageable memory: staged by the driver
+    // root_kind / module_kind = 0xffffffff ("none"), the rest 0.  Memsets, not a host-to-device copy:
+    // a copy would queue behind the bulk transfers of other documents on the copy engine.
+    static_assert(offsetof(ModuleInfo, root_kind) == 0 && offsetof(ModuleInfo, module_kind) == 4, "the two kinds lead the block");
+    cudaError_t e = cudaMemsetAsync(info, 0, sizeof(ModuleInfo), s);
     if (e != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(info, 0xff, 8, s)) != cudaSuccess) return e;
     find_module_kernel<<<(t.n_rows + 255) / 256, 256, 0, s>>>(t, br_match, br_row, info);
     count_parse_launch();
     return cudaGetLastError();

@@ -17,15 +17,15 @@ struct ModuleInfo {
 };
 struct ChildRef { uint32_t koff, klen, noff, nlen, hoff, hlen; };  // nlen / hlen == 0xffffffff: no such string field
 
-// device-side views of everything child_pack_kernel writes (field 0 = "name", 1 = "hostname")
+// device-side views of what child_pack_kernel reads and writes (field 0 = "name", 1 = "hostname")
 struct IndexTables {
-    const uint32_t *key_excl;                 // exclusive scan of key lengths
-    const unsigned long long *rec[2];         // (has field) << 32 | record bytes, per child
-    const unsigned long long *rec_excl[2];    // its exclusive scan
-    uint8_t *keys;                            // packed keys
-    uint32_t *key_off;                        // n + 1 offsets into keys
-    uint8_t *blob[2];                         // packed result records per field
-    uint32_t *off[2], *cnt[2];                // n + 1 entries each: record bytes / records before child i
+    const unsigned long long *rec[2];         // per child: (has field) << 32 | record bytes
+    const unsigned long long *rec_excl[2];    // its exclusive scan: (records before) << 32 | bytes before
+    const uint32_t *viol[2];                  // per child: 1 if its field does not sort strictly after the previous child's
+    uint8_t *blob[2];                         // packed result records of the children that have the field
+    uint32_t *off[2];                         // m + 1 offsets into blob, m = number of such children
+    uint32_t *viol_bits[2];                   // m bits, cleared beforehand
+    unsigned long long *totals;               // [2]: m << 32 | blob bytes
 };
 
 cudaError_t launch_find_module(const TapeView &t, const uint32_t *br_match, const uint32_t *br_row, ModuleInfo *info, cudaStream_t s);
@@ -33,7 +33,7 @@ cudaError_t launch_child_flags(const TapeView &t, const ModuleInfo *info, uint32
 // refs must be pre-filled with 0xff bytes
 cudaError_t launch_child_refs(const TapeView &t, const ModuleInfo *info, const uint32_t *flags, const uint32_t *rank, ChildRef *refs,
                               cudaStream_t s);
-cudaError_t launch_child_sizes(const uint8_t *arena, const ChildRef *refs, uint32_t n, uint32_t *key_bytes, unsigned long long *rec_n,
+cudaError_t launch_child_sizes(const uint8_t *arena, const ChildRef *refs, uint32_t n, unsigned long long *rec_n,
                                unsigned long long *rec_h, uint32_t *viol_n, uint32_t *viol_h, cudaStream_t s);
 cudaError_t launch_child_pack(const uint8_t *arena, const ChildRef *refs, uint32_t n, const IndexTables &tb, cudaStream_t s);
 
