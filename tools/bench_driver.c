@@ -54,6 +54,161 @@ int tkb_product_step(const void *text, size_t n, int device_text, int to_host, c
     return 0;
 }
 
+/* ---- per-operation loops (SURVEY.md 8d, config #4 op mix; tools/op_mix.py).  Each returns the
+ * seconds the loop took, or a negative number on the first failing call.  strs/lens are parallel
+ * arrays; `total` calls cycle through the n entries in order. */
+double tkb_get_loop(tk_state *s, const char *const *paths, const size_t *lens, size_t n, size_t total, size_t *value_bytes) {
+    const char *v;
+    size_t vl, sum = 0;
+    double t0 = now_ms();
+    for (size_t i = 0, k = 0; i < total; i++, k = (k + 1 == n ? 0 : k + 1)) {
+        if (tk_state_get(s, paths[k], lens[k], &v, &vl)) return -1.0;
+        sum += vl;
+    }
+    *value_bytes = sum;
+    return (now_ms() - t0) * 1e-3;
+}
+
+double tkb_add_node_loop(tk_state *s, const char *const *cks, const size_t *ck_lens, const char *const *names, const size_t *name_lens,
+                         const char *const *jsons, const size_t *json_lens, size_t n, int value_kind) {
+    double t0 = now_ms();
+    for (size_t i = 0; i < n; i++)
+        if (tk_state_add_node(s, cks[i], ck_lens[i], names[i], name_lens[i], jsons[i], json_lens[i], value_kind)) return -1.0;
+    return (now_ms() - t0) * 1e-3;
+}
+
+double tkb_delete_loop(tk_state *s, const char *const *paths, const size_t *lens, size_t n) {
+    double t0 = now_ms();
+    for (size_t i = 0; i < n; i++)
+        if (tk_state_delete(s, paths[i], lens[i])) return -1.0;
+    return (now_ms() - t0) * 1e-3;
+}
+
+double tkb_nodes_loop(tk_state *s, const char *const *cks, const size_t *ck_lens, size_t n, size_t *pairs) {
+    const uint8_t *blob;
+    size_t blob_len, count, sum = 0;
+    double t0 = now_ms();
+    for (size_t i = 0; i < n; i++) {
+        if (tk_state_nodes(s, cks[i], ck_lens[i], &blob, &blob_len, &count)) return -1.0;
+        sum += count;
+    }
+    *pairs = sum;
+    return (now_ms() - t0) * 1e-3;
+}
+
+/* config #5 at library granularity: per cluster Nodes(ck), Delete("module." + key) for each pair, then
+ * Delete of the cluster key.  cluster_paths[i] = "module." + cks[i]. */
+double tkb_destroy_sweep(tk_state *s, const char *const *cks, const size_t *ck_lens, const char *const *cluster_paths,
+                         const size_t *cluster_path_lens, size_t n, size_t *deleted) {
+    const uint8_t *blob;
+    size_t blob_len, count, done = 0;
+    char path[512];
+    double t0 = now_ms();
+    memcpy(path, "module.", 7);
+    for (size_t i = 0; i < n; i++) {
+        if (tk_state_nodes(s, cks[i], ck_lens[i], &blob, &blob_len, &count)) return -1.0;
+        /* the blob belongs to the handle and a Delete may recycle it: take the keys out first */
+        size_t bytes = blob_len;
+        uint8_t *copy = (uint8_t *)__builtin_alloca(bytes ? bytes : 1);
+        memcpy(copy, blob, bytes);
+        for (size_t at = 0, k = 0; k < count; k++) {
+            uint32_t fl, kl;
+            memcpy(&fl, copy + at, 4); at += 4 + fl;
+            memcpy(&kl, copy + at, 4); at += 4;
+            if (kl + 7 >= sizeof path) return -2.0;
+            memcpy(path + 7, copy + at, kl); at += kl;
+            if (tk_state_delete(s, path, 7 + kl)) return -1.0;
+            done++;
+        }
+        if (tk_state_delete(s, cluster_paths[i], cluster_path_lens[i])) return -1.0;
+        done++;
+    }
+    *deleted = done;
+    return (now_ms() - t0) * 1e-3;
+}
+
+/* the same loops through the CPU oracle's exported functions */
+typedef int (*ora_get_fn)(void *, const char *, size_t, const char **, size_t *);
+typedef int (*ora_add_node_fn)(void *, const char *, size_t, const char *, size_t, const char *, size_t, int, char *, size_t);
+typedef int (*ora_delete_fn)(void *, const char *, size_t, char *, size_t);
+typedef int (*ora_nodes_fn2)(void *, const char *, size_t, char **, size_t *, size_t *, char *, size_t);
+typedef void (*ora_free_buf_fn2)(char *);
+
+double tkb_ora_get_loop(void *fn, void *h, const char *const *paths, const size_t *lens, size_t n, size_t total, size_t *value_bytes) {
+    ora_get_fn f = (ora_get_fn)fn;
+    const char *v;
+    size_t vl, sum = 0;
+    double t0 = now_ms();
+    for (size_t i = 0, k = 0; i < total; i++, k = (k + 1 == n ? 0 : k + 1)) {
+        if (f(h, paths[k], lens[k], &v, &vl)) return -1.0;
+        sum += vl;
+    }
+    *value_bytes = sum;
+    return (now_ms() - t0) * 1e-3;
+}
+
+double tkb_ora_add_node_loop(void *fn, void *h, const char *const *cks, const size_t *ck_lens, const char *const *names,
+                             const size_t *name_lens, const char *const *jsons, const size_t *json_lens, size_t n, int is_record) {
+    ora_add_node_fn f = (ora_add_node_fn)fn;
+    char err[256];
+    double t0 = now_ms();
+    for (size_t i = 0; i < n; i++)
+        if (f(h, cks[i], ck_lens[i], names[i], name_lens[i], jsons[i], json_lens[i], is_record, err, sizeof err)) return -1.0;
+    return (now_ms() - t0) * 1e-3;
+}
+
+double tkb_ora_delete_loop(void *fn, void *h, const char *const *paths, const size_t *lens, size_t n) {
+    ora_delete_fn f = (ora_delete_fn)fn;
+    char err[256];
+    double t0 = now_ms();
+    for (size_t i = 0; i < n; i++)
+        if (f(h, paths[i], lens[i], err, sizeof err)) return -1.0;
+    return (now_ms() - t0) * 1e-3;
+}
+
+double tkb_ora_nodes_loop(void *fn_nodes, void *fn_free, void *h, const char *const *cks, const size_t *ck_lens, size_t n, size_t *pairs) {
+    ora_nodes_fn2 f = (ora_nodes_fn2)fn_nodes;
+    ora_free_buf_fn2 fr = (ora_free_buf_fn2)fn_free;
+    char err[256], *out;
+    size_t out_len, count, sum = 0;
+    double t0 = now_ms();
+    for (size_t i = 0; i < n; i++) {
+        if (f(h, cks[i], ck_lens[i], &out, &out_len, &count, err, sizeof err)) return -1.0;
+        fr(out);
+        sum += count;
+    }
+    *pairs = sum;
+    return (now_ms() - t0) * 1e-3;
+}
+
+double tkb_ora_destroy_sweep(void *fn_nodes, void *fn_free, void *fn_delete, void *h, const char *const *cks, const size_t *ck_lens,
+                             const char *const *cluster_paths, const size_t *cluster_path_lens, size_t n, size_t *deleted) {
+    ora_nodes_fn2 f = (ora_nodes_fn2)fn_nodes;
+    ora_free_buf_fn2 fr = (ora_free_buf_fn2)fn_free;
+    ora_delete_fn del = (ora_delete_fn)fn_delete;
+    char err[256], *out, path[512];
+    size_t out_len, count, done = 0;
+    double t0 = now_ms();
+    memcpy(path, "module.", 7);
+    for (size_t i = 0; i < n; i++) {
+        if (f(h, cks[i], ck_lens[i], &out, &out_len, &count, err, sizeof err)) return -1.0;
+        for (size_t at = 0, k = 0; k < count; k++) {
+            uint32_t fl, kl;
+            memcpy(&fl, out + at, 4); at += 4 + fl;
+            memcpy(&kl, out + at, 4); at += 4;
+            if (kl + 7 >= sizeof path) { fr(out); return -2.0; }
+            memcpy(path + 7, out + at, kl); at += kl;
+            if (del(h, path, 7 + kl, err, sizeof err)) { fr(out); return -1.0; }
+            done++;
+        }
+        fr(out);
+        if (del(h, cluster_paths[i], cluster_path_lens[i], err, sizeof err)) return -1.0;
+        done++;
+    }
+    *deleted = done;
+    return (now_ms() - t0) * 1e-3;
+}
+
 /* The same step through the CPU oracle (oracle/tk_oracle.c), via its exported functions. */
 typedef void *(*ora_new_fn)(const char *, size_t, char *, size_t);
 typedef void (*ora_free_fn)(void *);

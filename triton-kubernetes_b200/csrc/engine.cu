@@ -537,7 +537,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
 
     // ---- P2a
     if ((e = d_tiles_.reserve((size_t)tok_tiles(n_tok) * sizeof(TilePrefix))) != cudaSuccess) return fail(e, "cudaMalloc(tiles)", err);
-    if ((e = d_scratch_.reserve((4 + 2 * (size_t)tok_tiles(n_tok)) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    if ((e = d_scratch_.reserve(tok_scratch_words(n_tok) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
     TilePrefix *tiles = d_tiles_.as<TilePrefix>();
     if ((e = timed(K_TOKEN_PREFIX, [&] { return launch_token_prefix(tb, n_tok, tiles, d_scratch_.as<unsigned long long>(), d_res, stream_); })) != cudaSuccess)
         return fail(e, "token_prefix", err);
@@ -550,17 +550,24 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     // ---- brackets: compact, sort by level, pair
     BracketBuffers bb{};
     {
-        uint32_t **slots[10] = {&bb.tok, &bb.lvkind, &bb.match, &bb.parent, &bb.row, &bb.sort_a, &bb.sort_b, &bb.key_a, &bb.key_b, &bb.ct};
-        for (int i = 0; i < 10; i++) {
+        uint32_t **slots[6] = {&bb.tok, &bb.lvkind, &bb.sort_a, &bb.sort_b, &bb.key_a, &bb.key_b};
+        for (int i = 0; i < 6; i++) {
             if ((e = d_br_[i].reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(brackets)", err);
             *slots[i] = d_br_[i].as<uint32_t>();
         }
+        // match / parent / row / ct share one block: launch_brackets fills all four with 0xff at once
+        const size_t stride = ((size_t)n_br + 4) & ~size_t(3);
+        if ((e = d_br_[6].reserve(4 * stride * 4)) != cudaSuccess) return fail(e, "cudaMalloc(brackets)", err);
+        bb.match = d_br_[6].as<uint32_t>();
+        bb.parent = bb.match + stride;
+        bb.row = bb.parent + stride;
+        bb.ct = bb.row + stride;
     }
     if ((e = d_bitzeros_.reserve(16 * 4)) != cudaSuccess) return fail(e, "cudaMalloc(bitzeros)", err);
     if ((e = d_flags_.reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(flags)", err);
     if ((e = d_zrank_.reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(zrank)", err);
     if ((e = d_scratch_.reserve(parse_scan_scratch_words(std::max(n_br, (n_tok + 31) / 32)) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
-    if ((e = timed(K_BRACKETS, [&] { return launch_brackets(tb, n_tok, tiles, bb, d_bitzeros_.as<unsigned int>(), out->max_level, stream_); })) != cudaSuccess)
+    if ((e = timed(K_BRACKETS, [&] { return launch_brackets(tb, n_tok, tiles, bb, n_br, d_bitzeros_.as<unsigned int>(), out->max_level, stream_); })) != cudaSuccess)
         return fail(e, "brackets", err);
     bool in_a = true;
     if ((e = timed(K_SORT_BRACKETS, [&] {

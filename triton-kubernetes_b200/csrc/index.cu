@@ -88,12 +88,7 @@ __device__ __forceinline__ uint32_t order_violation(const uint8_t *arena, const 
     uint32_t fo, fl, po, pl;
     if (!field_of(c, which, &fo, &fl)) return 0;
     if (!field_of(p, which, &po, &pl)) return 1;  // a predecessor without the field: not a clean run
-    const uint32_t m = min(pl, fl);
-    for (uint32_t k = 0; k < m; k++) {
-        const int x = arena[po + k], y = arena[fo + k];
-        if (x != y) return x < y ? 0u : 1u;
-    }
-    return pl < fl ? 0u : 1u;
+    return compare_bytes(arena, po, pl, fo, fl) < 0 ? 0u : 1u;
 }
 
 // per child: (has field) << 32 | record bytes for both fields, and the violation flags

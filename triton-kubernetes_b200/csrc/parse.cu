@@ -473,54 +473,12 @@ __device__ __forceinline__ bool emits_row(const uint8_t *kind, uint32_t i, uint3
     return false;
 }
 
-struct TokLocal { int depth_before; uint32_t rows_before, br_before; };
-
-// block-wide exclusive scan of (depth delta, row flag, bracket flag) for one 256-token tile
-__device__ __forceinline__ TokLocal tile_scan(int dd, uint32_t row, uint32_t br, int *tile_dd, uint32_t *tile_rows,
-                                              uint32_t *tile_br, int *tile_min_after, int *tile_max_after) {
-    __shared__ int s_d[TOK_TILE / 32];
-    __shared__ uint32_t s_r[TOK_TILE / 32], s_b[TOK_TILE / 32];
-    __shared__ int s_mn[TOK_TILE / 32], s_mx[TOK_TILE / 32];
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int d = dd;
-    uint32_t r = row, b = br;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int xd = __shfl_up_sync(FULL, d, o);
-        const uint32_t xr = __shfl_up_sync(FULL, r, o), xb = __shfl_up_sync(FULL, b, o);
-        if (lane >= (uint32_t)o) { d += xd; r += xr; b += xb; }
-    }
-    if (lane == 31) { s_d[warp] = d; s_r[warp] = r; s_b[warp] = b; }
-    __syncthreads();
-    int wd = 0, td = 0;
-    uint32_t wr = 0, wb = 0, tr = 0, tbk = 0;
-    for (uint32_t i = 0; i < TOK_TILE / 32; i++) {
-        if (i < warp) { wd += s_d[i]; wr += s_r[i]; wb += s_b[i]; }
-        td += s_d[i]; tr += s_r[i]; tbk += s_b[i];
-    }
-    const int after = wd + d;  // depth after this token, relative to the tile start
-    int mn = after, mx = after;
-#pragma unroll
-    for (int o = 16; o; o >>= 1) { mn = min(mn, __shfl_xor_sync(FULL, mn, o)); mx = max(mx, __shfl_xor_sync(FULL, mx, o)); }
-    if (lane == 0) { s_mn[warp] = mn; s_mx[warp] = mx; }
-    __syncthreads();
-    mn = s_mn[0]; mx = s_mx[0];
-    for (uint32_t i = 1; i < TOK_TILE / 32; i++) { mn = min(mn, s_mn[i]); mx = max(mx, s_mx[i]); }
-    *tile_dd = td; *tile_rows = tr; *tile_br = tbk; *tile_min_after = mn; *tile_max_after = mx;
-    TokLocal t;
-    t.depth_before = after - dd;
-    t.rows_before = wr + r - row;
-    t.br_before = wb + b - br;
-    __syncthreads();
-    return t;
-}
-
 // ---- token passes with TP_ITEMS consecutive tokens per thread: one block-wide scan per 4,096
 //      tokens; the per-256-token TilePrefix array is still what the later passes index.
 
 constexpr int TP_ITEMS = 16;
 constexpr int TP_THREADS = 256;
-constexpr int TP_BLOCK = TP_THREADS * TP_ITEMS;        // 4,096 tokens = 16 tiles of TOK_TILE
+constexpr int TP_BLOCK = TP_THREADS * TP_ITEMS;        // 4,096 tokens = 2 blocks of TOK_TILE
 constexpr int TP_TILES = TP_BLOCK / TOK_TILE;
 
 // kinds of tokens [base - 4, base + TP_ITEMS + 4) as bytes k[0 .. 23]; 0xff outside the stream
@@ -578,25 +536,47 @@ __device__ __forceinline__ void block_scan3(int d, uint32_t r, uint32_t b, int *
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(TP_THREADS) token_prefix_kernel(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, u64 *scratch,
-                                                                 ParseResult *res) {
-    __shared__ uint32_t s_blk;
-    __shared__ int s_pd;
-    __shared__ uint32_t s_pr, s_pb;
-    __shared__ int s_mn[TP_THREADS / 32], s_mx[TP_THREADS / 32];
-    if (threadIdx.x == 0) s_blk = (uint32_t)atomicAdd(&scratch[0], 1ull);
-    __syncthreads();
-    const uint32_t blk = s_blk, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t n_tiles = (n_tok + TOK_TILE - 1) / TOK_TILE;
-    const uint32_t n_blocks = (n_tok + TP_BLOCK - 1) / TP_BLOCK;
-    const uint32_t base = blk * TP_BLOCK + threadIdx.x * TP_ITEMS;
+// ---- P2a in two launches, neither waiting on another block:
+//   token_agg     per block of TOK_TILE (2,048) tokens: depth change, rows, brackets, and the lowest /
+//                 highest depth reached inside it relative to its start;
+//   token_blocks  one block folds those in order: the TilePrefix of every token block, the totals
+//                 and the depth checks (a closer with nothing open, the 10,000 limit, the end at 0).
+struct TokAgg { int d, mn, mx; uint32_t rows, brackets; };
 
-    // ---- this thread's 16 tokens
-    const KindWindow kw = load_kinds(tb.kind, base, n_tok);
+// kinds of tokens [base - 4, base + 12) as bytes; 0xff outside the stream (base is a multiple of 8)
+struct KindWindow8 {
+    uint32_t w[4];
+    __device__ __forceinline__ uint32_t at(int j) const { return (w[(j + 4) >> 2] >> (((j + 4) & 3) * 8)) & 0xffu; }  // j in [-4, 12)
+};
+__device__ __forceinline__ KindWindow8 load_kinds8(const uint8_t *kind, uint32_t base, uint32_t n_tok) {
+    KindWindow8 kw;
+    const uint32_t *p = reinterpret_cast<const uint32_t *>(kind);
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const long long first = (long long)base - 4 + q * 4;
+        uint32_t v = 0xffffffffu;
+        if (first >= 0 && first < (long long)n_tok) {
+            v = __ldg(p + (first >> 2));
+            if (first + 4 > (long long)n_tok) v |= 0xffffffffu << ((n_tok - (uint32_t)first) * 8);  // tokens past the end read as 0xff
+        }
+        kw.w[q] = v;
+    }
+    return kw;
+}
+
+constexpr int TA_ITEMS = TOK_TILE / TP_THREADS;   // 8 tokens per thread
+static_assert(TA_ITEMS == 8, "token_agg_kernel reads its tokens through KindWindow8");
+
+__global__ void __launch_bounds__(TP_THREADS) token_agg_kernel(TokenBuffers tb, uint32_t n_tok, TokAgg *__restrict__ agg) {
+    __shared__ int s_d[TP_THREADS / 32], s_mn[TP_THREADS / 32], s_mx[TP_THREADS / 32];
+    __shared__ uint32_t s_r[TP_THREADS / 32], s_b[TP_THREADS / 32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t base = blockIdx.x * TOK_TILE + threadIdx.x * TA_ITEMS;
+    const KindWindow8 kw = load_kinds8(tb.kind, base, n_tok);
     int d = 0, mn = 0x7fffffff, mx = -0x7fffffff;
     uint32_t r = 0, b = 0;
 #pragma unroll
-    for (int j = 0; j < TP_ITEMS; j++) {
+    for (int j = 0; j < TA_ITEMS; j++) {
         const uint32_t k = kw.at(j);
         const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
         d += dd;
@@ -604,75 +584,107 @@ __global__ void __launch_bounds__(TP_THREADS) token_prefix_kernel(TokenBuffers t
         r += emits_row_k(k, kw.at(j - 1), kw.at(j + 2)) ? 1u : 0u;
         if (k != 0xff) { mn = min(mn, d); mx = max(mx, d); }
     }
-    int ed, td;
-    uint32_t er, eb, tr, tbk;
-    block_scan3(d, r, b, &ed, &er, &eb, &td, &tr, &tbk);
-    if (mn != 0x7fffffff) { mn += ed; mx += ed; }
+    // depth before this thread (inclusive warp scan, then the warps before), to place mn / mx
+    int xd = d;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(FULL, xd, o);
+        if (lane >= (uint32_t)o) xd += y;
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) { r += __shfl_xor_sync(FULL, r, o); b += __shfl_xor_sync(FULL, b, o); }
+    if (lane == 31) s_d[warp] = xd;
+    if (lane == 0) { s_r[warp] = r; s_b[warp] = b; }
+    __syncthreads();
+    int before = xd - d;
+    for (uint32_t i = 0; i < warp; i++) before += s_d[i];
+    if (mn != 0x7fffffff) { mn += before; mx += before; }
 #pragma unroll
     for (int o = 16; o; o >>= 1) { mn = min(mn, __shfl_xor_sync(FULL, mn, o)); mx = max(mx, __shfl_xor_sync(FULL, mx, o)); }
     if (lane == 0) { s_mn[warp] = mn; s_mx[warp] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        TokAgg a;
+        a.d = 0; a.rows = 0; a.brackets = 0; a.mn = 0x7fffffff; a.mx = -0x7fffffff;
+        for (uint32_t i = 0; i < TP_THREADS / 32; i++) {
+            a.d += s_d[i]; a.rows += s_r[i]; a.brackets += s_b[i];
+            a.mn = min(a.mn, s_mn[i]); a.mx = max(a.mx, s_mx[i]);
+        }
+        agg[blockIdx.x] = a;
+    }
+}
 
-    // ---- two look-backs side by side: warp 0 carries (rows, brackets), warp 1 carries depth
-    u64 *statusX = scratch + 4, *statusY = scratch + 4 + n_blocks;
-    if (warp < 2) {
-        u64 *status = warp == 0 ? statusX : statusY;
-        // X: rows in bits 0-30, brackets in bits 31-61.  Y: depth + 2^40 (biased, stays positive)
-        const u64 mine = warp == 0 ? ((u64)tr | ((u64)tbk << 31)) : (u64)(long long)td;
-        u64 prefix = 0;
-        if (blk == 0) {
-            if (lane == 0) st_relaxed(status, ST_PREFIX | (warp == 0 ? mine : (u64)((long long)td + (1ll << 40))));
-        } else {
-            if (lane == 0) st_relaxed(status + blk, ST_AGG | (warp == 0 ? mine : (u64)((long long)td + (1ll << 40))));
-            int look = (int)blk - 1;
-            for (;;) {
-                const int idx = look - (int)lane;
-                u64 s = idx >= 0 ? ld_relaxed(status + idx) : (ST_PREFIX | (warp == 0 ? 0ull : (1ull << 40)));
-                while (__any_sync(FULL, (s >> 62) == 0)) { if ((s >> 62) == 0) s = ld_relaxed(status + idx); }
-                const unsigned pm = __ballot_sync(FULL, (s >> 62) == 2);
-                const int first = pm ? __ffs(pm) - 1 : 32;
-                u64 x = 0;
-                if ((int)lane <= first) x = warp == 0 ? (s & ST_MASK) : (u64)((long long)(s & ST_MASK) - (1ll << 40));
+constexpr int TBP_THREADS = 1024, TBP_ITEMS = 4;   // one round covers 4,096 token blocks = 8.4 M tokens
+__global__ void __launch_bounds__(TBP_THREADS) token_blocks_kernel(const TokAgg *__restrict__ agg, uint32_t n_blocks, TilePrefix *__restrict__ tiles,
+                                                                  ParseResult *res) {
+    __shared__ int s_d[TBP_THREADS / 32];
+    __shared__ uint32_t s_r[TBP_THREADS / 32], s_b[TBP_THREADS / 32];
+    __shared__ int s_lo, s_hi;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { s_lo = 0; s_hi = 0; }
+    int run_d = 0;               // totals of the rounds before (the same in every thread)
+    uint32_t run_r = 0, run_b = 0;
+    for (uint32_t base = 0; base < n_blocks; base += TBP_THREADS * TBP_ITEMS) {
+        const uint32_t first = base + threadIdx.x * TBP_ITEMS;
+        TokAgg a[TBP_ITEMS];
+        int d = 0;
+        uint32_t r = 0, b = 0;
 #pragma unroll
-                for (int o = 16; o; o >>= 1) x += __shfl_xor_sync(FULL, x, o);
-                prefix += x;
-                if (pm) break;
-                look -= 32;
-            }
-            if (lane == 0) {
-                const u64 inc = prefix + mine;
-                st_relaxed(status + blk, ST_PREFIX | (warp == 0 ? inc : (u64)((long long)inc + (1ll << 40))));
+        for (int j = 0; j < TBP_ITEMS; j++) {
+            a[j].d = 0; a[j].rows = 0; a[j].brackets = 0; a[j].mn = 0x7fffffff; a[j].mx = -0x7fffffff;
+            if (first + j < n_blocks) a[j] = agg[first + j];
+            d += a[j].d; r += a[j].rows; b += a[j].brackets;
+        }
+        int xd = d;
+        uint32_t xr = r, xb = b;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int yd = __shfl_up_sync(FULL, xd, o);
+            const uint32_t yr = __shfl_up_sync(FULL, xr, o), yb = __shfl_up_sync(FULL, xb, o);
+            if (lane >= (uint32_t)o) { xd += yd; xr += yr; xb += yb; }
+        }
+        __syncthreads();   // the previous round has finished with the shared totals (and s_lo / s_hi are set)
+        if (lane == 31) { s_d[warp] = xd; s_r[warp] = xr; s_b[warp] = xb; }
+        __syncthreads();
+        // the warps before this one: every warp folds the 32 warp totals with one shuffle scan
+        int wd = s_d[lane];
+        uint32_t wr = s_r[lane], wb = s_b[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int yd = __shfl_up_sync(FULL, wd, o);
+            const uint32_t yr = __shfl_up_sync(FULL, wr, o), yb = __shfl_up_sync(FULL, wb, o);
+            if (lane >= (uint32_t)o) { wd += yd; wr += yr; wb += yb; }
+        }
+        const int td = __shfl_sync(FULL, wd, 31);
+        const uint32_t tr = __shfl_sync(FULL, wr, 31), tbk = __shfl_sync(FULL, wb, 31);
+        const uint32_t src = warp ? warp - 1 : 0;
+        int bd = __shfl_sync(FULL, wd, src);
+        uint32_t br = __shfl_sync(FULL, wr, src), bb2 = __shfl_sync(FULL, wb, src);
+        if (warp == 0) { bd = 0; br = 0; bb2 = 0; }
+        TilePrefix p;
+        p.depth = run_d + bd + xd - d; p.rows = run_r + br + xr - r; p.brackets = run_b + bb2 + xb - b; p.pad = 0;
+#pragma unroll
+        for (int j = 0; j < TBP_ITEMS; j++) {
+            if (first + j < n_blocks) {
+                tiles[first + j] = p;
+                if (a[j].mn != 0x7fffffff) {
+                    if (p.depth + a[j].mn < 0) atomicMin(&s_lo, p.depth + a[j].mn);
+                    if (p.depth + a[j].mx > 0) atomicMax(&s_hi, p.depth + a[j].mx);
+                }
+                p.depth += a[j].d; p.rows += a[j].rows; p.brackets += a[j].brackets;
             }
         }
-        if (lane == 0) {
-            if (warp == 0) { s_pr = (uint32_t)(prefix & 0x7fffffffu); s_pb = (uint32_t)((prefix >> 31) & 0x7fffffffu); }
-            else s_pd = (int)(long long)prefix;
-        }
+        run_d += td; run_r += tr; run_b += tbk;
     }
     __syncthreads();
-    // one TilePrefix per 256 tokens: every 16th thread stands at a tile boundary
-    if ((threadIdx.x & (TOK_TILE / TP_ITEMS - 1)) == 0) {
-        const uint32_t tile = blk * TP_TILES + threadIdx.x / (TOK_TILE / TP_ITEMS);
-        if (tile < n_tiles) {
-            TilePrefix p;
-            p.depth = s_pd + ed; p.rows = s_pr + er; p.brackets = s_pb + eb; p.pad = 0;
-            tiles[tile] = p;
-        }
-    }
     if (threadIdx.x == 0) {
-        int bmn = s_mn[0], bmx = s_mx[0];
-        for (uint32_t i = 1; i < TP_THREADS / 32; i++) { bmn = min(bmn, s_mn[i]); bmx = max(bmx, s_mx[i]); }
-        if (bmn != 0x7fffffff) {
-            if (s_pd + bmn < 0) res->invalid = 1;                                 // a closer with nothing open
-            const int hi = s_pd + bmx;
-            if (hi > 10000) res->invalid = 1;                                     // exceeded max depth
-            if (hi > 0) atomicMax(&res->max_level, (unsigned)min(hi, 16383));
-        }
-        if (blk + 1 == n_blocks) {
-            res->n_rows = s_pr + tr;
-            res->n_brackets = s_pb + tbk;
-            res->final_depth = s_pd + td;
-            if (s_pd + td != 0) res->invalid = 1;
-        }
+        if (s_lo < 0) res->invalid = 1;                    // a closer with nothing open
+        if (s_hi > 10000) res->invalid = 1;                // exceeded max depth
+        res->max_level = (unsigned)min(s_hi, 16383);
+        res->n_rows = run_r;
+        res->n_brackets = run_b;
+        res->final_depth = run_d;
+        if (run_d != 0) res->invalid = 1;
     }
 }
 
@@ -712,11 +724,7 @@ __global__ void __launch_bounds__(TP_THREADS) brackets_kernel(TokenBuffers tb, u
                 bb.tok[bi] = base + j;
                 bb.lvkind[bi] = ((uint32_t)level << 8) | k;
                 bb.sort_a[bi] = bi;
-                bb.key_a[bi] = (uint32_t)level;
-                bb.parent[bi] = 0xffffffffu;
-                bb.match[bi] = 0xffffffffu;
-                bb.row[bi] = 0xffffffffu;
-                bb.ct[bi] = 0;
+                bb.key_a[bi] = (uint32_t)level;   // (parent / match / row / ct are cleared in bulk by the launch wrapper)
                 for (int bit = 0; bit < n_bits; bit++)
                     if (!((level >> bit) & 1)) atomicAdd(&s_zero[bit], 1u);
                 bi++;
@@ -975,8 +983,7 @@ __device__ uint32_t check_scalar(const uint8_t *s, uint32_t n) {
     if (s[0] == 'f') return (n == 5 && s[1] == 'a' && s[2] == 'l' && s[3] == 's' && s[4] == 'e') ? 2 : 0;
     if (s[0] == 'n') return (n == 4 && s[1] == 'u' && s[2] == 'l' && s[3] == 'l') ? 2 : 0;
     uint32_t i = 0;
-    bool neg = false;
-    if (s[0] == '-') { neg = true; i = 1; if (n == 1) return 0; }
+    if (s[0] == '-') { i = 1; if (n == 1) return 0; }
     if (s[i] < '0' || s[i] > '9') return 0;
     const uint32_t int_start = i;
     if (s[i] == '0') i++;
@@ -998,19 +1005,13 @@ __device__ uint32_t check_scalar(const uint8_t *s, uint32_t n) {
     }
     if (i != n) return 0;
     // integers of up to 15 digits are exact in float64 and print back unchanged ("-0" included)
-    (void)neg;
     return (plain && int_digits <= 15) ? 2 : 1;
 }
 
-__device__ __forceinline__ uint32_t next_sig(const uint8_t *kind, uint32_t i, uint32_t n_tok) {  // kind of the next token, skipping scalar ends
-    i++;
-    if (i < n_tok && kind[i] == T_SCALAR_END) i++;
-    return i < n_tok ? kind[i] : 0xff;
-}
 
 
 constexpr int RW_ITEMS = 8;                        // consecutive tokens per thread: about one object member
-constexpr int RW_BLOCK = TP_THREADS * RW_ITEMS;   // 2,048 tokens per block = 8 tiles of TOK_TILE
+constexpr int RW_BLOCK = TP_THREADS * RW_ITEMS;   // 2,048 tokens per block = TOK_TILE
 
 // Go's scanner grammar as a table: for the container a token sits in and the token's kind, the
 // set of kinds the previous significant token may have.  A string is a KEY exactly when a colon
@@ -1205,13 +1206,7 @@ __global__ void key_order_kernel(const uint8_t *__restrict__ arena, RowBuffers r
         if (s == 0xffffffffu || s >= n_rows) { res->not_canonical = 1; return; }
     }
     const uint32_t ao = rb.koff[s], al = rb.klen[s], bo = rb.koff[r], bl = rb.klen[r];
-    const uint32_t m = min(al, bl);
-    int cmp = 0;
-    for (uint32_t i = 0; i < m; i++) {
-        const int x = arena[ao + i], y = arena[bo + i];
-        if (x != y) { cmp = x < y ? -1 : 1; break; }
-    }
-    if (cmp == 0) cmp = al < bl ? -1 : (al > bl ? 1 : 0);
+    int cmp = compare_bytes(arena, ao, al, bo, bl);
     if (cmp >= 0) res->not_canonical = 1;  // out of order or duplicated: the host re-orders
 }
 
@@ -1270,18 +1265,21 @@ cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, un
 
 cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, unsigned long long *scratch, ParseResult *res,
                                 cudaStream_t s) {
-    const uint32_t blocks = (n_tok + TP_BLOCK - 1) / TP_BLOCK;
-    cudaError_t e = cudaMemsetAsync(scratch, 0, (4 + 2 * (size_t)blocks) * 8, s);
-    if (e != cudaSuccess) return e;
-    token_prefix_kernel<<<blocks, TP_THREADS, 0, s>>>(tb, n_tok, tiles, scratch, res);
-    g_parse_launches++;
+    const uint32_t blocks = tok_tiles(n_tok);
+    TokAgg *agg = reinterpret_cast<TokAgg *>(scratch);   // tok_scratch_words(n_tok) words hold it
+    token_agg_kernel<<<blocks, TP_THREADS, 0, s>>>(tb, n_tok, agg);
+    token_blocks_kernel<<<1, TBP_THREADS, 0, s>>>(agg, blocks, tiles, res);
+    g_parse_launches += 2;
     return cudaGetLastError();
 }
 
-cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb, unsigned int *bit_zeros,
-                            uint32_t max_level, cudaStream_t s) {
+cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb, uint32_t n_br,
+                            unsigned int *bit_zeros, uint32_t max_level, cudaStream_t s) {
     cudaError_t e = cudaMemsetAsync(bit_zeros, 0, 16 * sizeof(unsigned int), s);
     if (e != cudaSuccess) return e;
+    // match / parent / row / ct are four equal slices of one block (engine.cu): "none" everywhere.
+    // For ct that reads as container kind 3, which rows_kernel treats as the top level.
+    if ((e = cudaMemsetAsync(bb.match, 0xff, (size_t)(bb.ct - bb.match) * 4 + (size_t)n_br * 4, s)) != cudaSuccess) return e;
     int bits = 0;
     while ((1u << bits) <= max_level) bits++;
     brackets_kernel<<<(n_tok + TP_BLOCK - 1) / TP_BLOCK, TP_THREADS, 0, s>>>(tb, n_tok, tiles, bb, bit_zeros, bits);

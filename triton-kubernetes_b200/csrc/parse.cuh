@@ -7,7 +7,8 @@
 //                      quote parity + token count); tokens (position, kind) are compacted in
 //                      order.  Also checks string bodies (control bytes, escape codes) and marks
 //                      strings that need decoding (escapes or non-ASCII bytes).
-//   P2a token_prefix   per 256-token tile: nesting depth, row count and bracket count before it
+//   P2a token_prefix   per 2,048-token block: nesting depth, row count and bracket count before it
+//                      (per-block aggregates, then one block folds them in order)
 //   P2b brackets       bracket tokens compacted with their nesting level
 //   P2c split sort     brackets stably sorted by level (one 1-bit split per level bit), which
 //                      puts every opener next to its closer
@@ -37,7 +38,7 @@ enum TokKind : uint8_t {
 constexpr int P1_THREADS = TK_P1_THREADS;
 constexpr int P1_BYTES_PER_THREAD = 64;
 constexpr int P1_TILE = P1_THREADS * P1_BYTES_PER_THREAD;  // 8 KiB of text per block
-constexpr int TOK_TILE = 256;                              // tokens per block in the token passes
+constexpr int TOK_TILE = 2048;                             // tokens per TilePrefix entry (what the token passes index by)
 
 // result block the kernels fill in device memory (one per parse)
 struct ParseResult {
@@ -61,7 +62,7 @@ inline uint32_t tok_tiles(size_t t) { return (uint32_t)((t + TOK_TILE - 1) / TOK
 
 // scratch sizes in 64-bit words
 inline size_t p1_scratch_words(size_t n) { return 4 + 2 * (size_t)p1_tiles(n); }
-inline size_t tok_scratch_words(size_t t) { return 4 + (size_t)tok_tiles(t); }
+inline size_t tok_scratch_words(size_t t) { return 4 + 3 * (size_t)tok_tiles(t); }   // 20 bytes per token block
 
 struct TokenBuffers {
     uint32_t *pos;        // token byte offsets
@@ -75,7 +76,7 @@ struct TilePrefix { int depth; uint32_t rows; uint32_t brackets; uint32_t pad; }
 struct BracketBuffers {
     uint32_t *tok;      // token index of bracket b (position order)
     uint32_t *lvkind;   // level << 8 | TokKind
-    uint32_t *match;    // partner bracket
+    uint32_t *match;    // partner bracket  (match / parent / row / ct: four slices of one block, cleared to 0xff together)
     uint32_t *parent;   // enclosing opener (0xffffffff: none)
     uint32_t *row;      // row index of an opener's row / a closer's row
     uint32_t *ct;       // container kinds around the bracket (see match_kernel)
@@ -96,11 +97,11 @@ struct DecodeBuffers {
 // the kernel again with carry_protocol true: the carry travels by decoupled look-back).
 cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, unsigned long long *scratch,
                                ParseResult *res, bool carry_protocol, cudaStream_t s);
-// scratch: 4 + 2 * tok_tiles(n_tok) words
+// scratch: tok_scratch_words(n_tok) words
 cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, unsigned long long *scratch,
                                 ParseResult *res, cudaStream_t s);
 // bit_zeros: 16 counters (device): brackets whose level has bit b clear
-cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb,
+cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb, uint32_t n_br,
                             unsigned int *bit_zeros, uint32_t max_level, cudaStream_t s);
 // stable sort of the identity permutation (sort_a/key_a) by level; *in_a says which buffer holds
 // the result.  flags/zrank: n_br words each; scratch: parse_scan_scratch_words(n_br) words.

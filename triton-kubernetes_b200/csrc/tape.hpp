@@ -42,6 +42,25 @@ struct TapeView {        // pointers may be host (pinned) or device
     const uint8_t *arena;  // allocation padded so that 16 bytes past arena_bytes are readable
 };
 
+#ifdef __CUDACC__
+// Bytes base[off .. off+3] as one big-endian number, so that comparing numbers compares byte
+// strings.  base must be 4-byte aligned and readable 7 bytes past off (every arena is padded).
+__device__ __forceinline__ uint32_t load4_be(const uint8_t *base, uint32_t off) {
+    const uint32_t *w = reinterpret_cast<const uint32_t *>(base + (off & ~3u));
+    return __byte_perm(__funnelshift_r(w[0], w[1], (off & 3u) * 8), 0, 0x0123);
+}
+// memcmp-style order of two byte strings of the arena (bytewise, the shorter first on a tie): -1, 0, 1
+__device__ __forceinline__ int compare_bytes(const uint8_t *arena, uint32_t ao, uint32_t al, uint32_t bo, uint32_t bl) {
+    const uint32_t m = al < bl ? al : bl;
+    for (uint32_t i = 0; i < m; i += 4) {
+        uint32_t x = load4_be(arena, ao + i), y = load4_be(arena, bo + i);
+        if (m - i < 4) { const uint32_t mask = 0xffffffffu << ((4 - (m - i)) * 8); x &= mask; y &= mask; }
+        if (x != y) return x < y ? -1 : 1;
+    }
+    return al < bl ? -1 : (al > bl ? 1 : 0);
+}
+#endif
+
 // Packed keys of the children of "module", in bytewise key order: key i is
 // keys[koffs[i], koffs[i+1]).  This is the array Clusters()/Nodes() classify.
 struct KeyIndexView {
