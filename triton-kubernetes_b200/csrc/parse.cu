@@ -463,15 +463,9 @@ namespace {
 __device__ __forceinline__ bool is_opener(uint32_t k) { return k == T_LBRACE || k == T_LBRACKET; }
 __device__ __forceinline__ bool is_closer(uint32_t k) { return k == T_RBRACE || k == T_RBRACKET; }
 
-// does token i start a tape row?  (keys ride on their value's row; the closer of an empty
-// container rides on the opener's row)
-__device__ __forceinline__ bool emits_row(const uint8_t *kind, uint32_t i, uint32_t n_tok, uint32_t k) {
-    if (k == T_SCALAR) return true;
-    if (is_opener(k)) return true;
-    if (k == T_STR_OPEN) return !(i + 2 < n_tok && kind[i + 2] == T_COLON);
-    if (is_closer(k)) return !(i > 0 && is_opener(kind[i - 1]));
-    return false;
-}
+// Which tokens start a tape row: scalars, openers, the opening quote of a string VALUE (no colon
+// two tokens on), and closers other than the one of an empty container (which rides on the
+// opener's row); keys ride on their value's row.  See emits_row_k and pass 1 of rows_kernel.
 
 // ---- token passes with TP_ITEMS consecutive tokens per thread: one block-wide scan per 4,096
 //      tokens; the per-256-token TilePrefix array is still what the later passes index.
@@ -1032,134 +1026,66 @@ __constant__ uint32_t g_allowed[3][G_N] = {
      0, 0, gbit(G_LBRACKET) | gbit(G_COMMA), gbit(G_VAL_OPEN), gbit(G_LBRACKET) | gbit(G_COMMA)},
 };
 
-// kind of token x in grammar terms; `next` is the kind of the token after x (needed for quotes)
-__device__ __forceinline__ uint32_t gkind(uint32_t k, uint32_t next, uint32_t next2) {
-    switch (k) {
-    case T_LBRACE: return G_LBRACE;
-    case T_RBRACE: return G_RBRACE;
-    case T_LBRACKET: return G_LBRACKET;
-    case T_RBRACKET: return G_RBRACKET;
-    case T_COLON: return G_COLON;
-    case T_COMMA: return G_COMMA;
-    case T_STR_OPEN: return next2 == T_COLON ? G_KEY_OPEN : G_VAL_OPEN;   // open, close, colon
-    case T_STR_CLOSE: return next == T_COLON ? G_KEY_CLOSE : G_VAL_CLOSE;
-    default: return G_SCALAR;
-    }
+// kind of a token in grammar terms, without branches.  colon_after: for an opening quote, is token
+// i + 2 a colon (open, close, colon); for a closing quote, is token i + 1 one.  k is 0 .. 8.
+__device__ __forceinline__ uint32_t gkind(uint32_t k, bool colon_after) {
+    // T:  {  }  [  ]  :  ,  "open  "close  scalar   ->   G:  1  2  3  4  5  6  7|9  8|10  11
+    const uint32_t base = k >= 8 ? (uint32_t)G_SCALAR : ((0x87654321u >> (k * 4)) & 15u);
+    return base + (((k - T_STR_OPEN) < 2u && !colon_after) ? 2u : 0u);
 }
+static_assert(G_KEY_OPEN == 7 && G_VAL_OPEN == 9 && G_KEY_CLOSE == 8 && G_VAL_CLOSE == 10 && G_SCALAR == 11 && G_COMMA == 6, "gkind's table");
 
-// grammar check of token i and, if it owns one, its tape row
-// (inlined once into the non-unrolled token loop of rows_kernel; ct and dbits are the block's
-// slices of bb.ct and tb.decode_bits, staged in shared memory and indexable by global number)
-__device__ __forceinline__ void token_row(const uint8_t *__restrict__ raw, u64 n, const TokenBuffers &tb, uint32_t n_tok,
-                                          const BracketBuffers &bb, const uint8_t *ct_s, const uint32_t *dbits, const DecodeBuffers &db,
-                                          uint32_t n_dec, const RowBuffers &rb, uint32_t n_rows, ParseResult *res, uint32_t i,
-                                          uint32_t k, int depth, uint32_t r, uint32_t brb, uint32_t row, int dd) {
-    const uint8_t *kind = tb.kind;   // readable 8 tokens either side of i; 0xff outside the stream
-    const uint32_t k1 = kind[i + 1], k2 = kind[i + 2];
-    const uint32_t next = k1 == T_SCALAR_END ? k2 : k1;   // next significant token
-
-    // previous significant token, in grammar terms
-    uint32_t pg = G_START;
-    if (i > 0) {
-        uint32_t pi = i - 1;
-        if (kind[pi] == T_SCALAR_END) pi--;
-        pg = gkind(kind[pi], kind[pi + 1] == T_SCALAR_END ? kind[pi + 2] : kind[pi + 1], kind[pi + 2]);
-    }
-    const uint32_t g = gkind(k, k1, k2);
-
-    // container: one look-up in the per-bracket table match_kernel filled
-    uint32_t ct = CT_TOP;
-    const uint32_t my_b = brb;   // for a bracket token: its own index
-    if (dd != 0) ct = (ct_s[my_b] >> 2) & 3u;
-    else if (brb > 0) ct = ct_s[brb - 1] & 3u;
-    if (ct > CT_ARR) ct = CT_TOP;   // unmatched bracket: match_kernel has already said invalid
-    if (!((g_allowed[ct][g] >> pg) & 1u)) { res->invalid = 1; return; }
-    if (g == G_VAL_OPEN && k1 != T_STR_CLOSE) { res->invalid = 1; return; }   // unterminated (cannot pass P1, kept as a guard)
-    if (!row) return;   // colons, commas, keys, closers of empty containers
-    if (r >= n_rows) { res->invalid = 1; return; }
-
-    uint32_t meta = 0, koff = 0, klen = 0, voff = 0, vlen = 0;
-    uint32_t after = next;  // the significant token after the value, to look for the comma
-    if (dd < 0) {
-        if (depth < 1) { res->invalid = 1; return; }
-        meta = (k == T_RBRACE ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR) | ((uint32_t)(depth - 1) << META_DEPTH_SHIFT);
-        koff = bb.match[my_b];  // the opener's bracket: key_order and the module index find its row through bb.row
-        bb.row[my_b] = r;
-    } else {
-        if (dd > 0) {
-            if (is_closer(k1)) { meta = (k == T_LBRACE ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR); after = k2 == T_SCALAR_END ? kind[i + 3] : k2; }
-            else { meta = (k == T_LBRACE ? ROW_OPEN_OBJ : ROW_OPEN_ARR); bb.row[my_b] = r; voff = my_b; }  // voff of an opening row: its bracket
-        } else if (k == T_STR_OPEN) {
-            meta = ROW_STR;
-            if (!((dbits[i >> 5] >> (i & 31)) & 1u)) { meta |= META_VAL_PLAIN; voff = tb.pos[i] + 1; vlen = tb.pos[i + 1] - voff; }
-            else string_ref(tb, db, n_dec, i, &voff, &vlen);
-            after = k2 == T_SCALAR_END ? kind[i + 3] : k2;
-        } else {  // scalar
-            meta = ROW_RAW;
-            voff = tb.pos[i];
-            vlen = tb.pos[i + 1] - voff;   // positions past the last token read as the text length
-            const uint32_t c = check_scalar(raw + voff, vlen);
-            if (c == 0) { res->invalid = 1; return; }
-            if (c == 1) { res->need_host_numbers = 1; res->not_canonical = 1; }
-        }
-        meta |= (uint32_t)depth << META_DEPTH_SHIFT;
-        if (ct == CT_OBJ) {
-            // "key" : value -> i-3 opening quote, i-2 closing quote, i-1 colon (the table has vouched for them)
-            const uint32_t ko = i - 3;
-            meta |= META_HAS_KEY;
-            if (!((dbits[ko >> 5] >> (ko & 31)) & 1u)) { meta |= META_KEY_PLAIN; koff = tb.pos[ko] + 1; klen = tb.pos[ko + 1] - koff; }
-            else string_ref(tb, db, n_dec, ko, &koff, &klen);
-            if (ko > 0) { uint32_t q = ko - 1; if (kind[q] == T_SCALAR_END) q--; if (kind[q] == T_COMMA) meta |= (1u << 7); }  // has an earlier sibling
-        }
-    }
-    // an opening row never carries the comma: it follows the closer and rides on the closing row
-    const uint32_t rk = meta & 15u;
-    if (rk != ROW_OPEN_OBJ && rk != ROW_OPEN_ARR && after == T_COMMA) meta |= META_COMMA;
-    if (r + 1 == n_rows) meta |= META_LAST;
-    rb.meta[r] = meta; rb.koff[r] = koff; rb.klen[r] = klen; rb.voff[r] = voff; rb.vlen[r] = vlen;
-}
-
+// Three passes over a block of 2,048 tokens (256 threads x 8 consecutive tokens):
+//   1  per token: depth change, bracket, "owns a row" -> block scan;
+//   2  per token, walking the thread's 8 in order with the previous token's grammar kind carried
+//      along: the grammar check, and every row-owning token is listed in shared memory at its
+//      row's place (token, brackets before it, depth before it);
+//   3  per ROW: thread t takes the block's t-th row, so that neighbouring threads do the same kind
+//      of work and write neighbouring rows.
 __global__ void __launch_bounds__(TP_THREADS) rows_kernel(const uint8_t *__restrict__ raw, u64 n, TokenBuffers tb, uint32_t n_tok,
                                                          const TilePrefix *__restrict__ tiles, BracketBuffers bb, DecodeBuffers db,
                                                          uint32_t n_dec, RowBuffers rb, uint32_t n_rows, ParseResult *res) {
-    // Token kinds and positions of this block (plus a halo of 8 on each side for the neighbour
-    // look-ups of the grammar rules) are staged in shared memory with coalesced loads; threads then
-    // walk 8 consecutive tokens each without striding through global memory.
     constexpr int HALO = 8;
     __shared__ uint8_t s_kind[RW_BLOCK + 2 * HALO];
     __shared__ uint32_t s_pos[RW_BLOCK + 2 * HALO];
+    __shared__ uint8_t s_ct[RW_BLOCK + 1];
+    __shared__ uint32_t s_dbits[RW_BLOCK / 32 + 2];
+    __shared__ uint32_t s_allowed[3 * G_N];
+    __shared__ uint32_t s_row[RW_BLOCK];    // token (11 bits) | brackets before it, from the block's first (12 bits)
+    __shared__ uint16_t s_rowd[RW_BLOCK];   // depth before the token
     const long long blk0 = (long long)blockIdx.x * RW_BLOCK - HALO;
     for (int x = threadIdx.x; x < RW_BLOCK + 2 * HALO; x += TP_THREADS) {
         const long long i = blk0 + x;
         const bool in = i >= 0 && i < (long long)n_tok;
         s_kind[x] = in ? tb.kind[i] : (uint8_t)0xff;
-        s_pos[x] = in ? tb.pos[i] : (uint32_t)n;
+        s_pos[x] = in ? tb.pos[i] : (uint32_t)n;   // positions past the last token read as the text length
     }
+    if (threadIdx.x < 3 * G_N) s_allowed[threadIdx.x] = g_allowed[threadIdx.x / G_N][threadIdx.x % G_N];
     __syncthreads();
-    tb.kind = s_kind - blk0;   // indexable by global token number inside the staged window
-    tb.pos = s_pos - blk0;
-    const uint32_t base = blockIdx.x * RW_BLOCK + threadIdx.x * RW_ITEMS;
-    const uint8_t *kind = tb.kind;
-    // first pass: what this thread's tokens add to depth, row count and bracket count
+    const uint8_t *kind = s_kind - blk0;   // indexable by global token number inside the staged window
+    const uint32_t *pos = s_pos - blk0;
+    const uint32_t tok0 = blockIdx.x * RW_BLOCK;
+    const uint32_t base = tok0 + threadIdx.x * RW_ITEMS;
+
+    // ---- pass 1
     int d = 0;
     uint32_t r = 0, b = 0, rowbits = 0;
 #pragma unroll
     for (int j = 0; j < RW_ITEMS; j++) {
         const uint32_t i = base + j;
-        const uint32_t k = i < n_tok ? kind[i] : 0xffu;
-        const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
-        const uint32_t row = (i < n_tok && emits_row(kind, i, n_tok, k)) ? 1u : 0u;
-        d += dd; b += dd != 0; r += row; rowbits |= row << j;
+        const uint32_t k = kind[i];   // 0xff past the end
+        const bool op = is_opener(k), cl = is_closer(k);
+        const uint32_t row = (k == T_SCALAR || op || (k == T_STR_OPEN && kind[i + 2] != T_COLON) || (cl && !is_opener(kind[i - 1]))) ? 1u : 0u;
+        d += (op ? 1 : 0) - (cl ? 1 : 0);
+        b += (op || cl) ? 1u : 0u;
+        r += row;
+        rowbits |= row << j;
     }
     int ed, td;
     uint32_t er, eb, tr, tbk;
     block_scan3(d, r, b, &ed, &er, &eb, &td, &tr, &tbk);
-    const TilePrefix p = tiles[blockIdx.x * (RW_BLOCK / TOK_TILE)];
-    int depth = p.depth + ed;
-    uint32_t rr = p.rows + er, brb = p.brackets + eb;
-    // the block's slice of the per-bracket container table and of the decode bitmap, staged too
-    __shared__ uint8_t s_ct[RW_BLOCK + 1];
-    __shared__ uint32_t s_dbits[RW_BLOCK / 32 + 2];
+    const TilePrefix p = tiles[blockIdx.x];
+    // the block's slice of the per-bracket container table and of the decode bitmap
     const uint32_t b_first = p.brackets > 0 ? p.brackets - 1 : 0;           // first bracket any token here can ask about
     const uint32_t b_count = p.brackets + tbk - b_first;                     // <= RW_BLOCK + 1
     for (uint32_t x = threadIdx.x; x < b_count; x += TP_THREADS) s_ct[x] = (uint8_t)bb.ct[b_first + x];
@@ -1168,15 +1094,102 @@ __global__ void __launch_bounds__(TP_THREADS) rows_kernel(const uint8_t *__restr
     __syncthreads();
     const uint8_t *ct_s = s_ct - b_first;
     const uint32_t *dbits = s_dbits - w_first;
-    // second pass: the tokens in order, with the running state
-#pragma unroll 1
-    for (int j = 0; j < RW_ITEMS; j++) {
-        const uint32_t k = kind[base + j];
-        const int dd = is_opener(k) ? 1 : is_closer(k) ? -1 : 0;
-        const uint32_t row = (rowbits >> j) & 1u;
-        if (k != 0xffu && k != T_SCALAR_END && k != T_STR_CLOSE)
-            token_row(raw, n, tb, n_tok, bb, ct_s, dbits, db, n_dec, rb, n_rows, res, base + j, k, depth, rr, brb, row, dd);
-        depth += dd; rr += row; brb += dd != 0;
+
+    // ---- pass 2
+    {
+        uint32_t g_prev = G_START;   // grammar kind of the significant token before the thread's first one
+        if (base > 0) {
+            uint32_t pi = base - 1;
+            if (kind[pi] == T_SCALAR_END) pi--;
+            const uint32_t kp = kind[pi];
+            if (kp != 0xffu) g_prev = gkind(kp, kind[pi + (kp == T_STR_OPEN ? 2 : 1)] == T_COLON);
+        }
+        int depth = p.depth + ed;
+        uint32_t brb = p.brackets + eb, slot = er;
+        bool bad = false;
+#pragma unroll 2
+        for (int j = 0; j < RW_ITEMS; j++) {
+            const uint32_t i = base + j, k = kind[i];
+            const bool op = is_opener(k), cl = is_closer(k), br = op || cl;
+            if (k != 0xffu && k != T_SCALAR_END) {
+                const uint32_t g = gkind(k, kind[i + (k == T_STR_OPEN ? 2 : 1)] == T_COLON);
+                // container: the bracket's own entry for a bracket, else what follows the bracket before
+                uint32_t ct = CT_TOP;
+                if (br || brb > 0) {
+                    const uint32_t e = ct_s[br ? brb : brb - 1];
+                    ct = br ? (e >> 2) & 3u : e & 3u;
+                    if (ct > CT_ARR) ct = CT_TOP;   // unmatched bracket: match_kernel has already said invalid
+                }
+                if (k != T_STR_CLOSE && !((s_allowed[ct * G_N + g] >> g_prev) & 1u)) bad = true;
+                if (g == G_VAL_OPEN && kind[i + 1] != T_STR_CLOSE) bad = true;   // unterminated (cannot pass P1, kept as a guard)
+                g_prev = g;
+                if ((rowbits >> j) & 1u) {
+                    s_row[slot] = (i - tok0) | ((brb - p.brackets) << 11);
+                    s_rowd[slot] = (uint16_t)min(max(depth, 0), 65535);
+                    slot++;
+                }
+            }
+            depth += (op ? 1 : 0) - (cl ? 1 : 0);
+            brb += br ? 1u : 0u;
+        }
+        if (bad) res->invalid = 1;
+    }
+    __syncthreads();
+
+    // ---- pass 3
+    for (uint32_t slot = threadIdx.x; slot < tr; slot += TP_THREADS) {
+        const uint32_t e = s_row[slot];
+        const uint32_t i = tok0 + (e & 2047u), my_b = p.brackets + (e >> 11);
+        const uint32_t depth = s_rowd[slot];
+        const uint32_t rr = p.rows + slot;
+        if (rr >= n_rows) { res->invalid = 1; continue; }
+        const uint32_t k = kind[i], k1 = kind[i + 1], k2 = kind[i + 2];
+        const bool op = is_opener(k), cl = is_closer(k);
+        uint32_t ct = CT_TOP;
+        if (op || cl || my_b > 0) {
+            const uint32_t c = ct_s[(op || cl) ? my_b : my_b - 1];
+            ct = (op || cl) ? (c >> 2) & 3u : c & 3u;
+            if (ct > CT_ARR) ct = CT_TOP;
+        }
+        uint32_t meta = 0, koff = 0, klen = 0, voff = 0, vlen = 0;
+        uint32_t after = k1 == T_SCALAR_END ? k2 : k1;   // the significant token after the value, to look for the comma
+        if (cl) {
+            if (depth < 1) { res->invalid = 1; continue; }
+            meta = (k == T_RBRACE ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR) | ((depth - 1) << META_DEPTH_SHIFT);
+            koff = bb.match[my_b];  // the opener's bracket: key_order and the module index find its row through bb.row
+            bb.row[my_b] = rr;
+        } else {
+            if (op) {
+                if (is_closer(k1)) { meta = (k == T_LBRACE ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR); after = k2 == T_SCALAR_END ? kind[i + 3] : k2; }
+                else { meta = (k == T_LBRACE ? ROW_OPEN_OBJ : ROW_OPEN_ARR); bb.row[my_b] = rr; voff = my_b; }  // voff of an opening row: its bracket
+            } else if (k == T_STR_OPEN) {
+                meta = ROW_STR;
+                if (!((dbits[i >> 5] >> (i & 31)) & 1u)) { meta |= META_VAL_PLAIN; voff = pos[i] + 1; vlen = pos[i + 1] - voff; }
+                else { tb.pos = const_cast<uint32_t *>(pos); string_ref(tb, db, n_dec, i, &voff, &vlen); }
+                after = k2 == T_SCALAR_END ? kind[i + 3] : k2;
+            } else {  // scalar
+                meta = ROW_RAW;
+                voff = pos[i];
+                vlen = pos[i + 1] - voff;
+                const uint32_t c = check_scalar(raw + voff, vlen);
+                if (c == 0) { res->invalid = 1; continue; }
+                if (c == 1) { res->need_host_numbers = 1; res->not_canonical = 1; }
+            }
+            meta |= depth << META_DEPTH_SHIFT;
+            if (ct == CT_OBJ && i >= 3) {   // (i < 3 only in text the grammar pass has already rejected)
+                // "key" : value -> i-3 opening quote, i-2 closing quote, i-1 colon (the table has vouched for them)
+                const uint32_t ko = i - 3;
+                meta |= META_HAS_KEY;
+                if (!((dbits[ko >> 5] >> (ko & 31)) & 1u)) { meta |= META_KEY_PLAIN; koff = pos[ko] + 1; klen = pos[ko + 1] - koff; }
+                else { tb.pos = const_cast<uint32_t *>(pos); string_ref(tb, db, n_dec, ko, &koff, &klen); }
+                if (ko > 0) { uint32_t q = ko - 1; if (kind[q] == T_SCALAR_END) q--; if (kind[q] == T_COMMA) meta |= (1u << 7); }  // has an earlier sibling
+            }
+        }
+        // an opening row never carries the comma: it follows the closer and rides on the closing row
+        const uint32_t rk = meta & 15u;
+        if (rk != ROW_OPEN_OBJ && rk != ROW_OPEN_ARR && after == T_COMMA) meta |= META_COMMA;
+        if (rr + 1 == n_rows) meta |= META_LAST;
+        rb.meta[rr] = meta; rb.koff[rr] = koff; rb.klen[rr] = klen; rb.voff[rr] = voff; rb.vlen[rr] = vlen;
     }
 }
 
