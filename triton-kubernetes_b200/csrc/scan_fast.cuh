@@ -43,21 +43,37 @@ __device__ __forceinline__ uint32_t compose(uint32_t far, uint32_t near) {
 }
 static_assert(P1_TILE <= 32767, "token counts of a tile must fit the 15-bit fields of compose()");
 
+// The four look-ups of one text word.  Shifts, logic ops and compares all issue on the integer ALU
+// pipe (one warp instruction per two cycles per scheduler), the busiest pipe of these kernels, so
+// the byte offsets are formed with multiplies -- x >> s as the high half of x * 2^(32-s) -- which
+// issue on the FMA pipe, leaving one AND per byte on the ALU pipe.
 __device__ __forceinline__ uint32_t class_word(const uint32_t *lut, uint32_t x) {
-    return lut[x & 0xffu] | lut[256 + ((x >> 8) & 0xffu)] | lut[512 + ((x >> 16) & 0xffu)] | lut[768 + (x >> 24)];
+    const char *b = reinterpret_cast<const char *>(lut);
+    const uint32_t i0 = (x * 4u) & 0x3fcu, i1 = __umulhi(x, 1u << 26) & 0x3fcu, i2 = __umulhi(x, 1u << 18) & 0x3fcu,
+                   i3 = __umulhi(x, 1u << 10) & 0x3fcu;
+    return *reinterpret_cast<const uint32_t *>(b + i0) | *reinterpret_cast<const uint32_t *>(b + 1024 + i1) |
+           *reinterpret_cast<const uint32_t *>(b + 2048 + i2) | *reinterpret_cast<const uint32_t *>(b + 3072 + i3);
 }
 
 struct ChunkMasks { u64 Q, WS, ST, R; };   // quotes, white space, structural, rare -- one bit per byte of a 64-byte chunk
 
-__device__ __forceinline__ ChunkMasks classify64(const uint32_t *s_lut, const uint8_t *chunk_ptr) {
-    uint32_t Qw[2], WSw[2], STw[2], Rw[2];
+struct Chunk64 { uint4 q[4]; };   // the 64 text bytes of one thread
+__device__ __forceinline__ Chunk64 load_chunk(const uint8_t *chunk_ptr) {
+    Chunk64 c;
     const uint4 *p = reinterpret_cast<const uint4 *>(chunk_ptr);
+#pragma unroll
+    for (int v = 0; v < 4; v++) c.q[v] = __ldg(p + v);
+    return c;
+}
+
+__device__ __forceinline__ ChunkMasks classify64(const uint32_t *s_lut, const Chunk64 &c) {
+    uint32_t Qw[2], WSw[2], STw[2], Rw[2];
 #pragma unroll
     for (int h = 0; h < 2; h++) {
         uint32_t y[4];
 #pragma unroll
         for (int v = 0; v < 2; v++) {
-            const uint4 q = __ldg(p + h * 2 + v);
+            const uint4 q = c.q[h * 2 + v];
             y[v * 2 + 0] = class_word(s_lut, q.x) | (class_word(s_lut, q.y) << 4);
             y[v * 2 + 1] = class_word(s_lut, q.z) | (class_word(s_lut, q.w) << 4);
         }
@@ -127,7 +143,7 @@ __global__ void __launch_bounds__(P1_THREADS) scan_count_kernel(const uint8_t *_
     uint32_t it = 0;
     for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it ^= 1) {
         const u64 chunk = (u64)tile * P1_TILE + (u64)threadIdx.x * P1_BYTES_PER_THREAD;
-        const ChunkMasks m = classify64(s_lut, raw + chunk);
+        const ChunkMasks m = classify64(s_lut, load_chunk(raw + chunk));
         u64 B = 0;
         for (u64 r = m.R; r; r &= r - 1) {   // only backslashes matter here
             const int i = __ffsll((long long)r) - 1;
@@ -241,7 +257,7 @@ __global__ void __launch_bounds__(P1_THREADS) scan_emit_kernel(const uint8_t *__
         const u64 pre = tile_pre[tile];
         const uint32_t V = (uint32_t)pre & 1u;          // in-string state entering the tile
         const u64 base = pre >> 1;                      // tokens before the tile
-        const ChunkMasks m = classify64(s_lut, raw + chunk);
+        const ChunkMasks m = classify64(s_lut, load_chunk(raw + chunk));
         // rare bytes, told apart one by one
         u64 B = 0, CT = 0, NA = 0, HT = 0;
         for (u64 r = m.R; r; r &= r - 1) {
