@@ -638,6 +638,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     tape_.arena = d_arena_.as<uint8_t>();
     tape_from_parse_ = true;
     bb_ = bb;
+    parsed_ = *out;
     index_version_ = 0;
     return TK_OK;
 }
@@ -774,28 +775,27 @@ int Engine::build_index(const Document &doc, std::string *err) {
     if (!device_resident(doc)) { *err = "internal: module index needs the parser's tape"; return TK_EARG; }
     cudaError_t e;
     const size_t rows = tape_.n_rows;
-    if ((e = d_minfo_.reserve(sizeof(ModuleInfo) + 64)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_cflags_.reserve((rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_crank_.reserve((rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    if ((e = d_scratch_.reserve(parse_scan_scratch_words((uint32_t)rows) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
-    if (!h_minfo_.reserve(1) || !h_words_.reserve(8)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
-    ModuleInfo *info = d_minfo_.as<ModuleInfo>();
-    unsigned long long *totals = reinterpret_cast<unsigned long long *>(d_minfo_.as<char>() + 32);  // per field: records << 32 | blob bytes
-    unsigned long long *scratch = d_scratch_.as<unsigned long long>();
-    uint32_t *flags = d_cflags_.as<uint32_t>(), *rank = d_crank_.as<uint32_t>();
-    e = timed(K_MODULE_INDEX, [&] {
-        cudaError_t x;
-        if ((x = launch_find_module(tape_, bb_.match, bb_.row, info, stream_)) != cudaSuccess) return x;
-        if ((x = launch_child_flags(tape_, info, flags, stream_)) != cudaSuccess) return x;
-        return scan_u32(flags, rank, (uint32_t)rows, scratch, stream_);  // number of children -> scratch[1]
-    });
-    if (e != cudaSuccess) return fail(e, "module index", err);
-    if ((e = copy_d2h(h_minfo_.p, info, sizeof(ModuleInfo))) != cudaSuccess) return fail(e, "copy module info", err);
-    if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy child count", err);
-    if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
-    const ModuleInfo mi = *h_minfo_.p;
-    index_module_ok_ = mi.root_kind == ROW_OPEN_OBJ && (mi.module_kind == ROW_OPEN_OBJ || mi.module_kind == ROW_EMPTY_OBJ);
-    const uint32_t n = index_module_ok_ ? (uint32_t)h_words_.p[0] : 0;
+    // the parse has already said where "module" is (rows_kernel) and what kind of value it has
+    index_module_ok_ = parsed_.root_kind == ROW_OPEN_OBJ && parsed_.module_row != 0 &&
+                       (parsed_.module_kind == ROW_OPEN_OBJ || parsed_.module_kind == ROW_EMPTY_OBJ);
+    const uint32_t module_row = parsed_.module_row - 1;
+    uint32_t n = 0;
+    if ((e = d_minfo_.reserve(64)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    unsigned long long *totals = d_minfo_.as<unsigned long long>();  // per field: records << 32 | blob bytes
+    unsigned long long *scratch = nullptr;
+    uint32_t *rank = nullptr;
+    if (index_module_ok_ && parsed_.module_kind == ROW_OPEN_OBJ) {
+        if ((e = d_crank_.reserve((rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+        if ((e = d_scratch_.reserve(parse_scan_scratch_words((uint32_t)rows) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+        if (!h_words_.reserve(8)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+        scratch = d_scratch_.as<unsigned long long>();
+        rank = d_crank_.as<uint32_t>();
+        e = timed(K_MODULE_INDEX, [&] { return scan_child_rank(tape_, module_row, bb_.match, bb_.row, rank, scratch, stream_); });  // children -> scratch[1]
+        if (e != cudaSuccess) return fail(e, "module index", err);
+        if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy child count", err);
+        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
+        n = (uint32_t)h_words_.p[0];
+    }
     index_m_[0] = index_m_[1] = 0;
     index_hint_[0] = index_hint_[1] = 0;
     if (n) {
@@ -829,7 +829,7 @@ int Engine::build_index(const Document &doc, std::string *err) {
             if ((x = cudaMemsetAsync(refs, 0xff, (size_t)n * sizeof(ChildRef), stream_)) != cudaSuccess) return x;
             for (int f = 0; f < 2; f++)
                 if ((x = cudaMemsetAsync(d_fviolbits_[f].p, 0, bit_words * 4, stream_)) != cudaSuccess) return x;
-            if ((x = launch_child_refs(tape_, info, flags, rank, refs, stream_)) != cudaSuccess) return x;
+            if ((x = launch_child_refs(tape_, module_row, bb_.match, bb_.row, rank, refs, stream_)) != cudaSuccess) return x;
             if ((x = launch_child_sizes(tape_.arena, refs, n, d_crec_[0].as<unsigned long long>(), d_crec_[1].as<unsigned long long>(),
                                         d_cviol_[0].as<uint32_t>(), d_cviol_[1].as<uint32_t>(), stream_)) != cudaSuccess) return x;
             for (int f = 0; f < 2; f++)

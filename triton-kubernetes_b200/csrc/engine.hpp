@@ -183,15 +183,15 @@ private:
     PinVec<unsigned long long> h_words_;
 
     // module index (csrc/index.cu)
-    DevBuf d_minfo_, d_cflags_, d_crank_, d_crefs_;
+    DevBuf d_minfo_, d_crank_, d_crefs_;
     DevBuf d_crec_[2], d_crec_excl_[2], d_cviol_[2], d_fviolbits_[2], d_fblob_[2], d_foff_[2];
-    PinVec<ModuleInfo> h_minfo_;
     PinVec<uint8_t> h_fblob_[2];
     PinVec<uint32_t> h_foff_[2], h_fviolbits_[2];
     uint64_t index_version_ = 0;
     uint32_t index_m_[2] = {0, 0}, index_hint_[2] = {0, 0};   // per field: records in the index, where the last run ended
     bool index_module_ok_ = false;
     BracketBuffers bb_{};  // bracket tables of the last parse (match / row are read by the index kernels)
+    ParseResult parsed_{};  // its verdict: where "module" is, among other things
 
     // results
     PinVec<uint8_t> h_out_;

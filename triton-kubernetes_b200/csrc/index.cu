@@ -21,43 +21,19 @@ __device__ __forceinline__ bool key_is(const uint8_t *arena, uint32_t off, uint3
     return true;
 }
 
-// the "module" member of the root object and the row that closes it
-__global__ void find_module_kernel(TapeView t, const uint32_t *__restrict__ br_match, const uint32_t *__restrict__ br_row, ModuleInfo *info) {
-    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= t.n_rows) return;
-    const uint32_t meta = t.meta[r];
-    if (r == 0) info->root_kind = meta & 15u;
-    if (row_depth(meta) != 1 || !(meta & META_HAS_KEY)) return;
-    if (!key_is(t.arena, t.koff[r], t.klen[r], "module", 6)) return;
-    const uint32_t kind = meta & 15u;
-    info->module_kind = kind;
-    info->module_row = r;
-    if (kind == ROW_OPEN_OBJ) info->module_end = br_row[br_match[t.voff[r]]];  // voff of an opening row: its bracket
-    else info->module_end = r;
-}
-
-// 1 for every row that starts a child of "module"
-__global__ void child_flags_kernel(TapeView t, const ModuleInfo *__restrict__ info, uint32_t *__restrict__ flags) {
-    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= t.n_rows) return;
-    uint32_t f = 0;
-    if (info->module_kind == ROW_OPEN_OBJ && r > info->module_row && r < info->module_end) {
-        const uint32_t meta = t.meta[r], kind = meta & 15u;
-        f = (row_depth(meta) == 2 && kind != ROW_CLOSE_OBJ && kind != ROW_CLOSE_ARR) ? 1u : 0u;
-    }
-    flags[r] = f;
-}
-
 // Where every child's key, "name" and "hostname" strings are.  One thread per ROW: a child's own
 // row records the key, and each depth-3 string member called name / hostname records itself in
-// the slot of the child it belongs to -- the last child row before it, i.e. slot rank[r] - 1.
-// refs must have been filled with 0xff bytes (absent fields read as length 0xffffffff).
-__global__ void child_refs_kernel(TapeView t, const ModuleInfo *__restrict__ info, const uint32_t *__restrict__ flags,
+// the slot of the child it belongs to -- the last child row before it, i.e. slot rank[r] - 1
+// (rank comes from scan_child_rank, parse.cu).  refs must have been filled with 0xff bytes (absent
+// fields read as length 0xffffffff).
+__global__ void child_refs_kernel(TapeView t, uint32_t module_row, const uint32_t *__restrict__ br_match, const uint32_t *__restrict__ br_row,
                                   const uint32_t *__restrict__ rank, ChildRef *refs) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= t.n_rows || info->module_kind != ROW_OPEN_OBJ || r <= info->module_row || r >= info->module_end) return;
+    if (r >= t.n_rows || r <= module_row) return;
+    const uint32_t module_end = closing_row(t, module_row, br_match, br_row);
+    if (r >= module_end) return;
     const uint32_t meta = t.meta[r];
-    if (flags[r]) {
+    if (starts_child(meta, r, module_row, module_end)) {
         ChildRef *c = refs + rank[r];
         c->koff = t.koff[r];
         c->klen = t.klen[r];
@@ -109,47 +85,62 @@ __global__ void child_sizes_kernel(const uint8_t *__restrict__ arena, const Chil
     viol_h[i] = vh;
 }
 
-__device__ __forceinline__ void put_u32(uint8_t *p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); }
-
-__device__ __forceinline__ void put_record(uint8_t *w, const uint8_t *arena, uint32_t fo, uint32_t fl, const ChildRef &c) {
-    put_u32(w, fl);
-    for (uint32_t k = 0; k < fl; k++) w[4 + k] = arena[fo + k];
-    put_u32(w + 4 + fl, c.klen);
-    for (uint32_t k = 0; k < c.klen; k++) w[8 + fl + k] = arena[c.koff + k];
-}
-
 // Records written at their offsets.  Per field the children that have it form a compact list (in
 // child = key order): off[j] is where record j starts (m + 1 entries), bit j of viol_bits says that
 // record j does not sort strictly after the child before it.  The last child also leaves the
 // totals (records << 32 | bytes) for the host.  viol_bits must have been cleared.
-__global__ void child_pack_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, IndexTables tb) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const ChildRef c = refs[i];
+// One warp per 32 children: every lane fetches its child's references, then the warp writes the 32
+// records one after another, a lane per byte, so that the stores of a record are contiguous.
+__global__ void __launch_bounds__(128) child_pack_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, IndexTables tb) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;   // this lane's child
+    ChildRef c;
+    c.koff = 0; c.klen = 0; c.noff = 0; c.nlen = 0xffffffffu; c.hoff = 0; c.hlen = 0xffffffffu;
+    if (i < n) c = refs[i];
 #pragma unroll
     for (int f = 0; f < 2; f++) {
-        const unsigned long long ex = tb.rec_excl[f][i];
-        const uint32_t byte_off = (uint32_t)ex, j = (uint32_t)(ex >> 32);
         uint32_t fo, fl;
-        const bool has = field_of(c, f, &fo, &fl);
-        if (has) {
-            tb.off[f][j] = byte_off;
-            if (tb.viol[f][i]) atomicOr(tb.viol_bits[f] + (j >> 5), 1u << (j & 31));
-            put_record(tb.blob[f] + byte_off, arena, fo, fl, c);
+        const bool has = i < n && field_of(c, f, &fo, &fl);
+        uint32_t byte_off = 0;
+        if (i < n) {
+            const unsigned long long ex = tb.rec_excl[f][i];
+            byte_off = (uint32_t)ex;
+            const uint32_t j = (uint32_t)(ex >> 32);
+            if (has) {
+                tb.off[f][j] = byte_off;
+                if (tb.viol[f][i]) atomicOr(tb.viol_bits[f] + (j >> 5), 1u << (j & 31));
+            }
+            if (i + 1 == n) {
+                const unsigned long long total = ex + tb.rec[f][i];
+                tb.off[f][(uint32_t)(total >> 32)] = (uint32_t)total;
+                tb.totals[f] = total;
+            }
         }
-        if (i + 1 == n) {
-            const unsigned long long total = ex + tb.rec[f][i];
-            tb.off[f][(uint32_t)(total >> 32)] = (uint32_t)total;
-            tb.totals[f] = total;
+        const unsigned who = __ballot_sync(0xffffffffu, has);
+        for (unsigned m = who; m; m &= m - 1) {
+            const int src = __ffs(m) - 1;
+            const uint32_t r_fo = __shfl_sync(0xffffffffu, fo, src), r_fl = __shfl_sync(0xffffffffu, fl, src);
+            const uint32_t r_ko = __shfl_sync(0xffffffffu, c.koff, src), r_kl = __shfl_sync(0xffffffffu, c.klen, src);
+            uint8_t *w = tb.blob[f] + __shfl_sync(0xffffffffu, byte_off, src);
+            // { u32 field_len, field, u32 key_len, key }
+            const uint32_t total = 8 + r_fl + r_kl;
+            for (uint32_t x = lane; x < total; x += 32) {
+                uint32_t v;
+                if (x < 4) v = r_fl >> (8 * x);
+                else if (x < 4 + r_fl) v = arena[r_fo + x - 4];
+                else if (x < 8 + r_fl) v = r_kl >> (8 * (x - 4 - r_fl));
+                else v = arena[r_ko + x - 8 - r_fl];
+                w[x] = (uint8_t)v;
+            }
         }
     }
 }
 
 }  // namespace
 
-cudaError_t launch_child_refs(const TapeView &t, const ModuleInfo *info, const uint32_t *flags, const uint32_t *rank, ChildRef *refs,
-                              cudaStream_t s) {
-    child_refs_kernel<<<(t.n_rows + 255) / 256, 256, 0, s>>>(t, info, flags, rank, refs);
+cudaError_t launch_child_refs(const TapeView &t, uint32_t module_row, const uint32_t *br_match, const uint32_t *br_row, const uint32_t *rank,
+                              ChildRef *refs, cudaStream_t s) {
+    child_refs_kernel<<<(t.n_rows + 255) / 256, 256, 0, s>>>(t, module_row, br_match, br_row, rank, refs);
     count_parse_launch();
     return cudaGetLastError();
 }
@@ -163,24 +154,6 @@ cudaError_t launch_child_sizes(const uint8_t *arena, const ChildRef *refs, uint3
 cudaError_t launch_child_pack(const uint8_t *arena, const ChildRef *refs, uint32_t n, const IndexTables &tb, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
     child_pack_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, n, tb);
-    count_parse_launch();
-    return cudaGetLastError();
-}
-
-cudaError_t launch_find_module(const TapeView &t, const uint32_t *br_match, const uint32_t *br_row, ModuleInfo *info, cudaStream_t s) {
-    // root_kind / module_kind = 0xffffffff ("none"), the rest 0.  Memsets, not a host-to-device copy:
-    // a copy would queue behind the bulk transfers of other documents on the copy engine.
-    static_assert(offsetof(ModuleInfo, root_kind) == 0 && offsetof(ModuleInfo, module_kind) == 4, "the two kinds lead the block");
-    cudaError_t e = cudaMemsetAsync(info, 0, sizeof(ModuleInfo), s);
-    if (e != cudaSuccess) return e;
-    if ((e = cudaMemsetAsync(info, 0xff, 8, s)) != cudaSuccess) return e;
-    find_module_kernel<<<(t.n_rows + 255) / 256, 256, 0, s>>>(t, br_match, br_row, info);
-    count_parse_launch();
-    return cudaGetLastError();
-}
-
-cudaError_t launch_child_flags(const TapeView &t, const ModuleInfo *info, uint32_t *flags, cudaStream_t s) {
-    child_flags_kernel<<<(t.n_rows + 255) / 256, 256, 0, s>>>(t, info, flags);
     count_parse_launch();
     return cudaGetLastError();
 }

@@ -9,12 +9,6 @@
 
 namespace tk {
 
-struct ModuleInfo {
-    uint32_t root_kind;    // RowKind of row 0
-    uint32_t module_kind;  // RowKind of root's "module" member; 0xff if there is none
-    uint32_t module_row, module_end;
-    uint32_t n_children, pad;
-};
 struct ChildRef { uint32_t koff, klen, noff, nlen, hoff, hlen; };  // nlen / hlen == 0xffffffff: no such string field
 
 // device-side views of what child_pack_kernel reads and writes (field 0 = "name", 1 = "hostname")
@@ -28,11 +22,9 @@ struct IndexTables {
     unsigned long long *totals;               // [2]: m << 32 | blob bytes
 };
 
-cudaError_t launch_find_module(const TapeView &t, const uint32_t *br_match, const uint32_t *br_row, ModuleInfo *info, cudaStream_t s);
-cudaError_t launch_child_flags(const TapeView &t, const ModuleInfo *info, uint32_t *flags, cudaStream_t s);
 // refs must be pre-filled with 0xff bytes
-cudaError_t launch_child_refs(const TapeView &t, const ModuleInfo *info, const uint32_t *flags, const uint32_t *rank, ChildRef *refs,
-                              cudaStream_t s);
+cudaError_t launch_child_refs(const TapeView &t, uint32_t module_row, const uint32_t *br_match, const uint32_t *br_row, const uint32_t *rank,
+                              ChildRef *refs, cudaStream_t s);
 cudaError_t launch_child_sizes(const uint8_t *arena, const ChildRef *refs, uint32_t n, unsigned long long *rec_n,
                                unsigned long long *rec_h, uint32_t *viol_n, uint32_t *viol_h, cudaStream_t s);
 cudaError_t launch_child_pack(const uint8_t *arena, const ChildRef *refs, uint32_t n, const IndexTables &tb, cudaStream_t s);

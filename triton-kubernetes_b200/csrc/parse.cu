@@ -374,8 +374,22 @@ __global__ void __launch_bounds__(P1_THREADS) scan_tokens_kernel(const uint8_t *
 constexpr int SCAN_THREADS = 256, SCAN_ITEMS = 4, SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
 // T = uint32_t or u64 (two 32-bit running sums packed into one word); sums are carried as u64
-template <class T>
-__global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const T *__restrict__ in, T *__restrict__ out, uint32_t n, u64 *scratch) {
+// In: anything with `T operator()(uint32_t i) const` (a plain array, or values computed on the fly)
+template <class T> struct ArrayIn {
+    const T *p;
+    __device__ __forceinline__ T operator()(uint32_t i) const { return p[i]; }
+};
+struct ChildFlagIn {   // 1 for every row that starts a child of the object opened at row `first`
+    TapeView t;
+    uint32_t first;
+    const uint32_t *br_match, *br_row;
+    __device__ __forceinline__ uint32_t operator()(uint32_t r) const {
+        return starts_child(t.meta[r], r, first, closing_row(t, first, br_match, br_row)) ? 1u : 0u;
+    }
+};
+
+template <class T, class In>
+__global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const In in, T *__restrict__ out, uint32_t n, u64 *scratch) {
     __shared__ uint32_t s_tile;
     __shared__ u64 s_warp[SCAN_THREADS / 32];
     __shared__ u64 s_prefix;
@@ -386,7 +400,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const T *__restrict_
     T v[SCAN_ITEMS];
     u64 sum = 0;
 #pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = base + i < n ? in[base + i] : T(0); sum += v[i]; }
+    for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = base + i < n ? in(base + i) : T(0); sum += v[i]; }
     u64 incl = sum;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -440,7 +454,7 @@ cudaError_t scan_u32(const uint32_t *in, uint32_t *out, uint32_t n, unsigned lon
     cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words_u32(n) * 8, s);
     if (e != cudaSuccess) return e;
     if (n == 0) return cudaSuccess;
-    scan_kernel<uint32_t><<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(in, out, n, scratch);
+    scan_kernel<uint32_t><<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(ArrayIn<uint32_t>{in}, out, n, scratch);
     g_parse_launches++;
     return cudaGetLastError();
 }
@@ -448,7 +462,17 @@ cudaError_t scan_u64(const unsigned long long *in, unsigned long long *out, uint
     cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words_u32(n) * 8, s);
     if (e != cudaSuccess) return e;
     if (n == 0) return cudaSuccess;
-    scan_kernel<u64><<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(in, out, n, scratch);
+    scan_kernel<u64><<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(ArrayIn<u64>{in}, out, n, scratch);
+    g_parse_launches++;
+    return cudaGetLastError();
+}
+cudaError_t scan_child_rank(const TapeView &t, uint32_t module_row, const uint32_t *br_match, const uint32_t *br_row, uint32_t *rank,
+                            unsigned long long *scratch, cudaStream_t s) {
+    const uint32_t n = t.n_rows;
+    cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words_u32(n) * 8, s);
+    if (e != cudaSuccess) return e;
+    if (n == 0) return cudaSuccess;
+    scan_kernel<uint32_t><<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(ChildFlagIn{t, module_row, br_match, br_row}, rank, n, scratch);
     g_parse_launches++;
     return cudaGetLastError();
 }
@@ -1190,6 +1214,15 @@ __global__ void __launch_bounds__(TP_THREADS) rows_kernel(const uint8_t *__restr
         if (rk != ROW_OPEN_OBJ && rk != ROW_OPEN_ARR && after == T_COMMA) meta |= META_COMMA;
         if (rr + 1 == n_rows) meta |= META_LAST;
         rb.meta[rr] = meta; rb.koff[rr] = koff; rb.klen[rr] = klen; rb.voff[rr] = voff; rb.vlen[rr] = vlen;
+        // what the module index (index.cu) starts from: the root's kind and its "module" member
+        if (rr == 0) res->root_kind = meta & 15u;
+        if (depth == 1 && (meta & META_HAS_KEY) && klen == 6) {
+            const uint8_t *kp = raw + koff;
+            if (kp[0] == 'm' && kp[1] == 'o' && kp[2] == 'd' && kp[3] == 'u' && kp[4] == 'l' && kp[5] == 'e') {
+                res->module_row = rr + 1;
+                res->module_kind = meta & 15u;
+            }
+        }
     }
 }
 
