@@ -96,7 +96,7 @@ void set_default_timing(bool on) { g_default_timing = on; }
 
 const char *kernel_name(int kind) {
     static const char *const names[K_COUNT] = {"row_offsets_kernel", "emit_kernel", "prefix_match_kernel", "scan_tokens_kernel",
-                                               "token_prefix_kernel", "brackets_kernel", "sort_brackets (split passes)", "match_kernel",
+                                               "token_prefix_kernel", "brackets_kernel", "sort_brackets (radix passes)", "match_kernel",
                                                "decode kernels", "rows_kernel", "key_order_kernel", "module index kernels"};
     return kind >= 0 && kind < K_COUNT ? names[kind] : "";
 }
@@ -563,16 +563,12 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
         bb.row = bb.parent + stride;
         bb.ct = bb.row + stride;
     }
-    if ((e = d_bitzeros_.reserve(16 * 4)) != cudaSuccess) return fail(e, "cudaMalloc(bitzeros)", err);
-    if ((e = d_flags_.reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(flags)", err);
-    if ((e = d_zrank_.reserve(((size_t)n_br + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(zrank)", err);
     if ((e = d_scratch_.reserve(parse_scan_scratch_words(std::max(n_br, (n_tok + 31) / 32)) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
-    if ((e = timed(K_BRACKETS, [&] { return launch_brackets(tb, n_tok, tiles, bb, n_br, d_bitzeros_.as<unsigned int>(), out->max_level, stream_); })) != cudaSuccess)
+    if ((e = timed(K_BRACKETS, [&] { return launch_brackets(tb, n_tok, tiles, bb, n_br, stream_); })) != cudaSuccess)
         return fail(e, "brackets", err);
     bool in_a = true;
     if ((e = timed(K_SORT_BRACKETS, [&] {
-             return launch_sort_brackets(bb, n_br, out->max_level, d_bitzeros_.as<unsigned int>(), d_flags_.as<uint32_t>(), d_zrank_.as<uint32_t>(),
-                                         d_scratch_.as<unsigned long long>(), &in_a, stream_);
+             return launch_sort_brackets(bb, n_br, out->max_level, d_scratch_.as<unsigned long long>(), &in_a, stream_);
          })) != cudaSuccess)
         return fail(e, "sort_brackets", err);
     if ((e = timed(K_MATCH, [&] { return launch_match(bb, in_a ? bb.sort_a : bb.sort_b, in_a ? bb.key_a : bb.key_b, n_br, d_res, stream_); })) != cudaSuccess)

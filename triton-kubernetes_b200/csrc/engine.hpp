@@ -177,8 +177,8 @@ private:
     bool tape_from_parse_ = false;
 
     // parse work buffers
-    DevBuf d_tok_pos_, d_tok_kind_, d_dec_bits_, d_tiles_, d_res_, d_bitzeros_;
-    DevBuf d_br_[10], d_flags_, d_zrank_, d_dec_tok_, d_dec_off_, d_dec_len_, d_dec_counts_, d_dec_offs_;
+    DevBuf d_tok_pos_, d_tok_kind_, d_dec_bits_, d_tiles_, d_res_;
+    DevBuf d_br_[7], d_dec_tok_, d_dec_off_, d_dec_len_, d_dec_counts_, d_dec_offs_;
     PinVec<ParseResult> h_res_;
     PinVec<unsigned long long> h_words_;
 

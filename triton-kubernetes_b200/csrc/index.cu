@@ -89,11 +89,15 @@ __global__ void child_sizes_kernel(const uint8_t *__restrict__ arena, const Chil
 // child = key order): off[j] is where record j starts (m + 1 entries), bit j of viol_bits says that
 // record j does not sort strictly after the child before it.  The last child also leaves the
 // totals (records << 32 | bytes) for the host.  viol_bits must have been cleared.
-// One warp per 32 children: every lane fetches its child's references, then the warp writes the 32
-// records one after another, a lane per byte, so that the stores of a record are contiguous.
+// One warp per PACK_CHILDREN children: the first lanes fetch one child's references each, then the
+// warp writes the records one after another, a lane per byte, so that the stores of a record are
+// contiguous.  (Few children per warp: the copy loop is a chain of L2 round trips, and it is the
+// number of warps in flight that hides them.)
+constexpr uint32_t PACK_CHILDREN = 8;
 __global__ void __launch_bounds__(128) child_pack_kernel(const uint8_t *__restrict__ arena, const ChildRef *__restrict__ refs, uint32_t n, IndexTables tb) {
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;   // this lane's child
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t i = lane < PACK_CHILDREN ? warp * PACK_CHILDREN + lane : n;   // this lane's child (none for the other lanes)
     ChildRef c;
     c.koff = 0; c.klen = 0; c.noff = 0; c.nlen = 0xffffffffu; c.hoff = 0; c.hlen = 0xffffffffu;
     if (i < n) c = refs[i];
@@ -153,7 +157,8 @@ cudaError_t launch_child_sizes(const uint8_t *arena, const ChildRef *refs, uint3
 }
 cudaError_t launch_child_pack(const uint8_t *arena, const ChildRef *refs, uint32_t n, const IndexTables &tb, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    child_pack_kernel<<<(n + 127) / 128, 128, 0, s>>>(arena, refs, n, tb);
+    const uint32_t warps = (n + PACK_CHILDREN - 1) / PACK_CHILDREN;
+    child_pack_kernel<<<(warps + 3) / 4, 128, 0, s>>>(arena, refs, n, tb);
     count_parse_launch();
     return cudaGetLastError();
 }

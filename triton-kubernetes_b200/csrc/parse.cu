@@ -711,9 +711,7 @@ __global__ void __launch_bounds__(TBP_THREADS) token_blocks_kernel(const TokAgg 
 // =================================================================================================
 
 __global__ void __launch_bounds__(TP_THREADS) brackets_kernel(TokenBuffers tb, uint32_t n_tok, const TilePrefix *__restrict__ tiles,
-                                                             BracketBuffers bb, unsigned int *bit_zeros, int n_bits) {
-    __shared__ unsigned int s_zero[16];
-    if (threadIdx.x < 16) s_zero[threadIdx.x] = 0;
+                                                             BracketBuffers bb) {
     const uint32_t base = blockIdx.x * TP_BLOCK + threadIdx.x * TP_ITEMS;
     const KindWindow kw = load_kinds(tb.kind, base, n_tok);
     int d = 0;
@@ -743,82 +741,119 @@ __global__ void __launch_bounds__(TP_THREADS) brackets_kernel(TokenBuffers tb, u
                 bb.lvkind[bi] = ((uint32_t)level << 8) | k;
                 bb.sort_a[bi] = bi;
                 bb.key_a[bi] = (uint32_t)level;   // (parent / match / row / ct are cleared in bulk by the launch wrapper)
-                for (int bit = 0; bit < n_bits; bit++)
-                    if (!((level >> bit) & 1)) atomicAdd(&s_zero[bit], 1u);
                 bi++;
             }
             depth += dd;
         }
     }
-    __syncthreads();
-    if (threadIdx.x < (unsigned)n_bits && s_zero[threadIdx.x]) atomicAdd(&bit_zeros[threadIdx.x], s_zero[threadIdx.x]);
 }
 
-// One stable split of (key, value) pairs by bit `bit` of the key, zeros first, in a single kernel:
-// the zero flags are scanned (decoupled look-back) and every pair is scattered to its place.
-__global__ void __launch_bounds__(SCAN_THREADS) split_pass_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict__ val, uint32_t n,
-                                                                 int bit, const unsigned int *__restrict__ bit_zeros,
-                                                                 uint32_t *__restrict__ key_out, uint32_t *__restrict__ val_out, u64 *scratch) {
-    __shared__ uint32_t s_tile;
-    __shared__ uint32_t s_warp[SCAN_THREADS / 32];
-    __shared__ uint32_t s_prefix;
-    if (threadIdx.x == 0) s_tile = (uint32_t)atomicAdd(&scratch[0], 1ull);
+// Stable sort of (key, value) pairs by 3 key bits at a time, in three launches per digit and with
+// no block waiting on another: per-tile histograms, one block that turns them into the start of
+// every (bucket, tile) run, and a scatter that ranks each pair inside its tile.  Nesting levels up
+// to 7 -- every document the reference writes -- take a single digit.
+constexpr int RS_BITS = 3, RS_BUCKETS = 1 << RS_BITS;
+
+// eight 16-bit counters (a tile has 1,024 pairs) in two words, so that a scan adds them all at once
+struct Count8 {
+    u64 a, b;
+    __device__ __forceinline__ void inc(uint32_t bucket) { if (bucket < 4) a += 1ull << (16 * bucket); else b += 1ull << (16 * (bucket - 4)); }
+    __device__ __forceinline__ uint32_t get(uint32_t bucket) const { return (uint32_t)((bucket < 4 ? a >> (16 * bucket) : b >> (16 * (bucket - 4))) & 0xffffu); }
+};
+
+__global__ void __launch_bounds__(SCAN_THREADS) radix_hist_kernel(const uint32_t *__restrict__ key, uint32_t n, int shift, uint32_t *__restrict__ hist,
+                                                                 uint32_t tiles) {
+    __shared__ u64 s_a[SCAN_THREADS / 32], s_b[SCAN_THREADS / 32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    Count8 c{0, 0};
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++)
+        if (base + i < n) c.inc((key[base + i] >> shift) & (RS_BUCKETS - 1));
+#pragma unroll
+    for (int o = 16; o; o >>= 1) { c.a += __shfl_xor_sync(FULL, c.a, o); c.b += __shfl_xor_sync(FULL, c.b, o); }
+    if (lane == 0) { s_a[warp] = c.a; s_b[warp] = c.b; }
     __syncthreads();
-    const uint32_t tile = s_tile, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
-    uint32_t k[SCAN_ITEMS], v[SCAN_ITEMS], sum = 0;
+    if (threadIdx.x < RS_BUCKETS) {
+        Count8 t{0, 0};
+        for (uint32_t w = 0; w < SCAN_THREADS / 32; w++) { t.a += s_a[w]; t.b += s_b[w]; }
+        hist[threadIdx.x * tiles + blockIdx.x] = t.get(threadIdx.x);   // bucket-major
+    }
+}
+
+// in place: hist[bucket][tile] -> number of pairs that sort before the first pair of that run
+constexpr int RB_THREADS = 1024, RB_ITEMS = 4;
+__global__ void __launch_bounds__(RB_THREADS) radix_base_kernel(uint32_t *hist, uint32_t entries) {
+    __shared__ uint32_t s_w[RB_THREADS / 32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t run = 0;
+    for (uint32_t base = 0; base < entries; base += RB_THREADS * RB_ITEMS) {
+        const uint32_t first = base + threadIdx.x * RB_ITEMS;
+        uint32_t v[RB_ITEMS], sum = 0;
+#pragma unroll
+        for (int j = 0; j < RB_ITEMS; j++) { v[j] = first + j < entries ? hist[first + j] : 0u; sum += v[j]; }
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, incl, o);
+            if (lane >= (uint32_t)o) incl += y;
+        }
+        __syncthreads();   // the previous round has finished with s_w
+        if (lane == 31) s_w[warp] = incl;
+        __syncthreads();
+        uint32_t w = s_w[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, w, o);
+            if (lane >= (uint32_t)o) w += y;
+        }
+        const uint32_t total = __shfl_sync(FULL, w, 31);
+        uint32_t before = __shfl_sync(FULL, w, warp ? warp - 1 : 0);
+        if (warp == 0) before = 0;
+        uint32_t x = run + before + incl - sum;
+#pragma unroll
+        for (int j = 0; j < RB_ITEMS; j++) {
+            if (first + j < entries) hist[first + j] = x;
+            x += v[j];
+        }
+        run += total;
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) radix_scatter_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict__ val, uint32_t n,
+                                                                    int shift, const uint32_t *__restrict__ run_base, uint32_t tiles,
+                                                                    uint32_t *__restrict__ key_out, uint32_t *__restrict__ val_out) {
+    __shared__ u64 s_a[SCAN_THREADS / 32], s_b[SCAN_THREADS / 32];
+    __shared__ uint32_t s_base[RS_BUCKETS];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    if (threadIdx.x < RS_BUCKETS) s_base[threadIdx.x] = run_base[threadIdx.x * tiles + blockIdx.x];
+    uint32_t k[SCAN_ITEMS], v[SCAN_ITEMS];
+    Count8 mine{0, 0};
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; i++) {
-        k[i] = base + i < n ? key[base + i] : 0xffffffffu;
+        k[i] = base + i < n ? key[base + i] : 0u;
         v[i] = base + i < n ? val[base + i] : 0u;
-        sum += base + i < n ? (((k[i] >> bit) & 1u) ^ 1u) : 0u;
+        if (base + i < n) mine.inc((k[i] >> shift) & (RS_BUCKETS - 1));
     }
-    uint32_t incl = sum;
+    Count8 incl = mine;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t x = __shfl_up_sync(FULL, incl, d);
-        if (lane >= (uint32_t)d) incl += x;
+    for (int o = 1; o < 32; o <<= 1) {
+        const u64 ya = __shfl_up_sync(FULL, incl.a, o), yb = __shfl_up_sync(FULL, incl.b, o);
+        if (lane >= (uint32_t)o) { incl.a += ya; incl.b += yb; }
     }
-    if (lane == 31) s_warp[warp] = incl;
+    if (lane == 31) { s_a[warp] = incl.a; s_b[warp] = incl.b; }
     __syncthreads();
-    uint32_t wbefore = 0, total = 0;
-    for (uint32_t i = 0; i < SCAN_THREADS / 32; i++) { if (i < warp) wbefore += s_warp[i]; total += s_warp[i]; }
-    u64 *status = scratch + 2;
-    if (warp == 0) {
-        u64 prefix = 0;
-        if (tile == 0) {
-            if (lane == 0) st_relaxed(status, ST_PREFIX | total);
-        } else {
-            if (lane == 0) st_relaxed(status + tile, ST_AGG | total);
-            int look = (int)tile - 1;
-            for (;;) {
-                const int idx = look - (int)lane;
-                u64 s = idx >= 0 ? ld_relaxed(status + idx) : ST_PREFIX;
-                while (__any_sync(FULL, (s >> 62) == 0)) { if ((s >> 62) == 0) s = ld_relaxed(status + idx); }
-                const unsigned pm = __ballot_sync(FULL, (s >> 62) == 2);
-                const int first = pm ? __ffs(pm) - 1 : 32;
-                u64 x = ((int)lane <= first) ? (s & ST_MASK) : 0ull;
-#pragma unroll
-                for (int d = 16; d; d >>= 1) x += __shfl_xor_sync(FULL, x, d);
-                prefix += x;
-                if (pm) break;
-                look -= 32;
-            }
-            if (lane == 0) st_relaxed(status + tile, ST_PREFIX | (prefix + total));
-        }
-        if (lane == 0) s_prefix = (uint32_t)prefix;
-    }
-    __syncthreads();
-    uint32_t z = s_prefix + wbefore + incl - sum;   // zeros before this thread's first item
-    const uint32_t n_zero = bit_zeros[bit];
+    Count8 before{incl.a - mine.a, incl.b - mine.b};   // pairs of each bucket earlier in the tile
+    for (uint32_t w = 0; w < warp; w++) { before.a += s_a[w]; before.b += s_b[w]; }
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; i++) {
         if (base + i >= n) break;
-        const uint32_t one = (k[i] >> bit) & 1u;
-        const uint32_t dst = one ? n_zero + (base + i - z) : z;
+        const uint32_t bucket = (k[i] >> shift) & (RS_BUCKETS - 1);
+        const uint32_t dst = s_base[bucket] + before.get(bucket);
+        before.inc(bucket);
         key_out[dst] = k[i];
         val_out[dst] = v[i];
-        z += one ^ 1u;
     }
 }
 
@@ -1319,35 +1354,31 @@ cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *til
     return cudaGetLastError();
 }
 
-cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb, uint32_t n_br,
-                            unsigned int *bit_zeros, uint32_t max_level, cudaStream_t s) {
-    cudaError_t e = cudaMemsetAsync(bit_zeros, 0, 16 * sizeof(unsigned int), s);
-    if (e != cudaSuccess) return e;
+cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb, uint32_t n_br, cudaStream_t s) {
+    cudaError_t e;
     // match / parent / row / ct are four equal slices of one block (engine.cu): "none" everywhere.
     // For ct that reads as container kind 3, which rows_kernel treats as the top level.
     if ((e = cudaMemsetAsync(bb.match, 0xff, (size_t)(bb.ct - bb.match) * 4 + (size_t)n_br * 4, s)) != cudaSuccess) return e;
-    int bits = 0;
-    while ((1u << bits) <= max_level) bits++;
-    brackets_kernel<<<(n_tok + TP_BLOCK - 1) / TP_BLOCK, TP_THREADS, 0, s>>>(tb, n_tok, tiles, bb, bit_zeros, bits);
+    brackets_kernel<<<(n_tok + TP_BLOCK - 1) / TP_BLOCK, TP_THREADS, 0, s>>>(tb, n_tok, tiles, bb);
     g_parse_launches++;
     return cudaGetLastError();
 }
 
-cudaError_t launch_sort_brackets(BracketBuffers bb, uint32_t n_br, uint32_t max_level, const unsigned int *bit_zeros,
-                                 uint32_t *flags, uint32_t *zrank, unsigned long long *scratch, bool *in_a, cudaStream_t s) {
+cudaError_t launch_sort_brackets(BracketBuffers bb, uint32_t n_br, uint32_t max_level, unsigned long long *scratch, bool *in_a,
+                                 cudaStream_t s) {
     *in_a = true;
     if (n_br == 0) return cudaSuccess;
     int bits = 0;
     while ((1u << bits) <= max_level) bits++;
-    const uint32_t blocks = (n_br + SCAN_TILE - 1) / SCAN_TILE;
-    (void)flags; (void)zrank;
-    for (int bit = 0; bit < bits; bit++) {
+    const uint32_t tiles = (n_br + SCAN_TILE - 1) / SCAN_TILE;
+    uint32_t *hist = reinterpret_cast<uint32_t *>(scratch);   // RS_BUCKETS x tiles words
+    for (int shift = 0; shift < bits; shift += RS_BITS) {
         const uint32_t *key = *in_a ? bb.key_a : bb.key_b, *val = *in_a ? bb.sort_a : bb.sort_b;
         uint32_t *key_o = *in_a ? bb.key_b : bb.key_a, *val_o = *in_a ? bb.sort_b : bb.sort_a;
-        cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words_u32(n_br) * 8, s);
-        if (e != cudaSuccess) return e;
-        split_pass_kernel<<<blocks, SCAN_THREADS, 0, s>>>(key, val, n_br, bit, bit_zeros, key_o, val_o, scratch);
-        g_parse_launches++;
+        radix_hist_kernel<<<tiles, SCAN_THREADS, 0, s>>>(key, n_br, shift, hist, tiles);
+        radix_base_kernel<<<1, RB_THREADS, 0, s>>>(hist, RS_BUCKETS * tiles);
+        radix_scatter_kernel<<<tiles, SCAN_THREADS, 0, s>>>(key, val, n_br, shift, hist, tiles, key_o, val_o);
+        g_parse_launches += 3;
         *in_a = !*in_a;
     }
     return cudaGetLastError();
@@ -1399,6 +1430,6 @@ cudaError_t launch_key_order(const uint8_t *arena, RowBuffers rb, uint32_t n_row
     return cudaGetLastError();
 }
 
-size_t parse_scan_scratch_words(uint32_t n) { return scan_scratch_words_u32(n); }
+size_t parse_scan_scratch_words(uint32_t n) { return 4 * scan_scratch_words_u32(n); }   // (the radix sort keeps 8 x u32 per tile)
 
 }  // namespace tk

@@ -10,8 +10,8 @@
 //   P2a token_prefix   per 2,048-token block: nesting depth, row count and bracket count before it
 //                      (per-block aggregates, then one block folds them in order)
 //   P2b brackets       bracket tokens compacted with their nesting level
-//   P2c split sort     brackets stably sorted by level (one 1-bit split per level bit), which
-//                      puts every opener next to its closer
+//   P2c radix sort     brackets stably sorted by level (3 bits per pass: histogram, run starts,
+//                      scatter), which puts every opener next to its closer
 //   P2d match          opener<->closer pairs, enclosing opener of every opener
 //   P3  decode         strings marked in P1 are unescaped / UTF-8-repaired into a side arena
 //   P2e rows           grammar check (Go's scanner rules restated as local token-pair rules) and
@@ -102,13 +102,10 @@ cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, un
 // scratch: tok_scratch_words(n_tok) words
 cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, unsigned long long *scratch,
                                 ParseResult *res, cudaStream_t s);
-// bit_zeros: 16 counters (device): brackets whose level has bit b clear
-cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb, uint32_t n_br,
-                            unsigned int *bit_zeros, uint32_t max_level, cudaStream_t s);
-// stable sort of the identity permutation (sort_a/key_a) by level; *in_a says which buffer holds
-// the result.  flags/zrank: n_br words each; scratch: parse_scan_scratch_words(n_br) words.
-cudaError_t launch_sort_brackets(BracketBuffers bb, uint32_t n_br, uint32_t max_level, const unsigned int *bit_zeros,
-                                 uint32_t *flags, uint32_t *zrank, unsigned long long *scratch, bool *in_a,
+cudaError_t launch_brackets(TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles, BracketBuffers bb, uint32_t n_br, cudaStream_t s);
+// stable sort of the identity permutation (sort_a/key_a) by level, 3 bits per pass; *in_a says which
+// buffer holds the result.  scratch: parse_scan_scratch_words(n_br) words.
+cudaError_t launch_sort_brackets(BracketBuffers bb, uint32_t n_br, uint32_t max_level, unsigned long long *scratch, bool *in_a,
                                  cudaStream_t s);
 cudaError_t launch_match(BracketBuffers bb, const uint32_t *sorted, const uint32_t *sorted_key, uint32_t n_br,
                          ParseResult *res, cudaStream_t s);
