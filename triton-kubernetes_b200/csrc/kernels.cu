@@ -412,18 +412,20 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const ui
     }
     if (!fits) return;
     __syncwarp();
-    // copy out: whole 16-byte chunks as vectors, the ragged head and tail bytewise
+    // copy out: whole 16-byte chunks as vectors; the ragged first and last chunk (shared with the
+    // neighbouring warps' tiles) a byte per lane -- lanes 0..15 the first, 16..31 the last
     uint8_t *g = out + (out0 - shift);  // 16-byte aligned
     const uint32_t end = shift + span;
     const uint32_t chunks = (end + 15u) >> 4;
     for (uint32_t c = lane; c < chunks; c += 32) {
         const uint32_t b0 = c << 4;
-        if (b0 >= shift && b0 + 16 <= end) {
-            reinterpret_cast<uint4 *>(g)[c] = s_out[warp][c];
-        } else {
-            const uint32_t lo = max(b0, shift), hi = min(b0 + 16, end);
-            for (uint32_t b = lo; b < hi; b++) g[b] = slice[b];
-        }
+        if (b0 >= shift && b0 + 16 <= end) reinterpret_cast<uint4 *>(g)[c] = s_out[warp][c];
+    }
+    if (chunks) {
+        const uint32_t b = lane < 16 ? lane : ((chunks - 1) << 4) + (lane - 16);
+        const bool head = lane < 16 && (shift != 0 || end < 16);
+        const bool tail = lane >= 16 && chunks > 1 && (end & 15u) != 0;
+        if ((head || tail) && b >= shift && b < end) g[b] = slice[b];
     }
 }
 
