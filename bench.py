@@ -282,16 +282,40 @@ def run_ours(args, rank, local_rank, world):
         L.tk_set_default_timing(0)
         return total, stats
 
-    def run_overlapped(steps, inflight, to_host):
+    def run_overlapped(steps, inflight, to_host, warmup):
         """`steps` whole steps, `inflight` at a time: each host thread runs whole steps on its own
-        handle (own stream, own buffers).  Timed with CUDA events recorded on an idle device before
-        the first step and after every thread has waited for its last one; returns (ms, phases, copy stats)."""
+        handle (own stream, own buffers).  The same threads first run the warm-up steps and meet at a
+        barrier, so that the clock starts on a device that is idle but has not had time to drop its
+        clocks; the timed region is bracketed by CUDA events (start after that barrier and a device
+        synchronize, end after every thread has waited for its last step).
+        Returns (ms, phases, copy stats, kernel launches inside the timed region)."""
+        inflight = max(1, inflight)
         lock, nxt, errs, copy, phases = threading.Lock(), [0], [], [0, 0], []
+        warmed, go = threading.Barrier(inflight + 1), threading.Barrier(inflight + 1)
 
-        def work():
+        def one(i, phase):
+            src = pinned.data_ptr() if to_host else dev_copies[i % R_COPIES].data_ptr()
+            h, out = step(src, not to_host, to_host, phase)
+            if to_host:
+                ok = ctypes.string_at(out + len(text) - 64, 64) == text[-64:] and ctypes.string_at(out, 64) == text[:64]
+                a, b = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+                L.tk_state_copy_stats(h, byref(a), byref(b))
+                copy[0], copy[1] = a.value, b.value
+                if not ok:
+                    errs.append("a step returned a wrong result")
+            L.tk_state_free(h)   # waits for the handle's stream (the emit kernel of a resident step is still queued)
+
+        def work(w):
             torch.cuda.set_device(local_rank)
-            phase = (c_double * 5)()
+            scratch_phase, phase = (c_double * 5)(), (c_double * 5)()
             phases.append(phase)
+            try:
+                for k in range(max(1, -(-warmup // inflight))):
+                    one(w + k * inflight, scratch_phase)
+            except BaseException as e:  # noqa: BLE001 -- reported by the caller
+                errs.append(repr(e))
+            warmed.wait()
+            go.wait()
             while True:
                 with lock:
                     i = nxt[0]
@@ -299,57 +323,44 @@ def run_ours(args, rank, local_rank, world):
                 if i >= steps or errs:
                     return
                 try:
-                    src = pinned.data_ptr() if to_host else dev_copies[i % R_COPIES].data_ptr()
-                    h, out = step(src, not to_host, to_host, phase)
-                    if to_host:
-                        ok = ctypes.string_at(out + len(text) - 64, 64) == text[-64:] and ctypes.string_at(out, 64) == text[:64]
-                        a, b = ctypes.c_ulonglong(), ctypes.c_ulonglong()
-                        L.tk_state_copy_stats(h, byref(a), byref(b))
-                        copy[0], copy[1] = a.value, b.value
-                        if not ok:
-                            errs.append("a step returned a wrong result")
-                    else:
-                        torch.cuda.ExternalStream(L.tk_state_stream(h), device=dev).synchronize()
-                    L.tk_state_free(h)
-                except BaseException as e:  # noqa: BLE001 -- reported by the caller
+                    one(i, phase)
+                except BaseException as e:  # noqa: BLE001
                     errs.append(repr(e))
 
-        torch.cuda.synchronize()
+        ts = [threading.Thread(target=work, args=(w,)) for w in range(inflight)]
+        for t in ts: t.start()
+        warmed.wait()
+        barrier()
+        launches0 = tk.state.kernel_launches()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         t0 = time.perf_counter()
-        ts = [threading.Thread(target=work) for _ in range(max(1, inflight))]
-        for t in ts: t.start()
+        go.wait()
         for t in ts: t.join()
         torch.cuda.synchronize()
         b.record()
         b.synchronize()
         wall = (time.perf_counter() - t0) * 1e3
+        launches = tk.state.kernel_launches() - launches0
         if errs:
             raise SystemExit("bench.py: " + errs[0])
         ph = [sum(p[i] for p in phases) / steps for i in range(4)]
-        return max(a.elapsed_time(b), wall), ph, tuple(copy)
+        return max(a.elapsed_time(b), wall), ph, tuple(copy), launches
 
     inflight = args.inflight if args.inflight > 0 else max(1, min(4, (os.cpu_count() or 1) // max(1, world)))
-    # ---- value: text resident in HBM, result left in HBM
-    run_overlapped(max(args.warmup, inflight), inflight, False)
-    barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    launches0 = tk.state.kernel_launches()
-    ms_value, _, _ = run_overlapped(args.steps, inflight, False)
-    launches = tk.state.kernel_launches() - launches0
+    # ---- value: text resident in HBM, result left in HBM
+    ms_value, _, _, launches = run_overlapped(args.steps, inflight, False, args.warmup)
     barrier()
     ms_serial, _ = timed_resident(min(args.steps, 10), per_kernel=False)
     ms_serial /= min(args.steps, 10)
 
     # ---- e2e: pinned host text in, host text out
-    run_overlapped(max(args.warmup, inflight), inflight, True)
-    barrier()
-    ms_e2e, ph, copy_stats = run_overlapped(args.steps, inflight, True)
+    ms_e2e, ph, copy_stats, _ = run_overlapped(args.steps, inflight, True, args.warmup)
     phase_ms = {k: ph[i] for i, k in enumerate(("new", "clusters", "nodes_x%d" % len(cks), "bytes"))}
     barrier()
-    ms_e2e_serial, _, _ = run_overlapped(min(args.steps, 10), 1, True)
+    ms_e2e_serial, _, _, _ = run_overlapped(min(args.steps, 10), 1, True, 1)
     ms_e2e_serial /= min(args.steps, 10)
     clocks = sampler.stop()
 
@@ -361,15 +372,25 @@ def run_ours(args, rank, local_rank, world):
             kern[name] = {"launches_per_step": st["timed"] / args.steps, "avg_us": st["ms"] / st["timed"] * 1e3,
                           "ms_per_step": st["ms"] / args.steps}
     # algorithmic bytes per launch: New = input length, Bytes = output length
-    algo = {"scan_tokens_kernel": len(text), "emit_kernel": len(text), "row_offsets_kernel": len(text)}
+    algo = {"scan_count_kernel": len(text), "scan_emit_kernel": len(text), "emit_kernel": len(text), "row_offsets_kernel": len(text)}
     for k, v in kern.items():
         if k in algo:
             v["algorithmic_bytes"] = algo[k]
             v["gbs"] = algo[k] / (v["avg_us"] * 1e-6) / 1e9
     dominant = max((k for k in kern if k in algo), key=lambda k: kern[k]["ms_per_step"])
     achieved = kern[dominant]["gbs"]
+    # DRAM bytes of that kernel from the committed ncu capture (tools/ncu_traffic.py), if there is one
+    traffic, traffic_src = None, None
+    try:
+        import glob
+        newest = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_traffic.json")))[-1]
+        k = json.load(open(newest))["kernels"].get(dominant)
+        if k:
+            traffic, traffic_src = k["dram_read_bytes"] + k["dram_write_bytes"], os.path.relpath(newest, ROOT)
+    except (IndexError, OSError, ValueError, KeyError):
+        pass
     roofline = {"kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo[dominant], "avg_launch_us": kern[dominant]["avg_us"],
                 "kernel_ms_per_step_total": sum(v["ms_per_step"] for v in kern.values()), "kernels": kern}
 

@@ -109,7 +109,9 @@ def main():
         return o.value, n.value
 
     prod = {}
-    h = p_new(pinned.data_ptr(), len(text)); p_bytes(h); L.tk_state_free(h)   # warm-up: pools, module load
+    h = p_new(pinned.data_ptr(), len(text)); p_bytes(h)                      # warm-up: buffer pools, module load
+    wb, wl, wc = c_void_p(), c_size_t(), c_size_t()
+    L.tk_state_clusters(h, byref(wb), byref(wl), byref(wc)); L.tk_state_free(h)
     ts, tb = [], []
     for _ in range(args.reps):
         t0 = time.perf_counter(); h = p_new(pinned.data_ptr(), len(text)); ts.append(time.perf_counter() - t0)

@@ -95,9 +95,10 @@ static std::atomic<bool> g_default_timing{false};
 void set_default_timing(bool on) { g_default_timing = on; }
 
 const char *kernel_name(int kind) {
-    static const char *const names[K_COUNT] = {"row_offsets_kernel", "emit_kernel", "prefix_match_kernel", "scan_tokens_kernel",
-                                               "token_prefix_kernel", "brackets_kernel", "sort_brackets (radix passes)", "match_kernel",
-                                               "decode kernels", "rows_kernel", "key_order_kernel", "module index kernels"};
+    static const char *const names[K_COUNT] = {"row_offsets_kernel", "emit_kernel", "prefix_match_kernel", "scan_tokens_kernel (carry protocol)",
+                                               "token_agg + token_blocks kernels", "brackets_kernel", "sort_brackets (radix passes)", "match_kernel",
+                                               "decode kernels", "rows_kernel", "key_order_kernel", "module index kernels",
+                                               "scan_count_kernel", "scan_prefix_kernel", "scan_emit_kernel"};
     return kind >= 0 && kind < K_COUNT ? names[kind] : "";
 }
 
@@ -521,8 +522,12 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
         if ((e = d_scratch_.reserve(p1_scratch_words(n) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
         tb.pos = d_tok_pos_.as<uint32_t>(); tb.kind = d_tok_kind_.as<uint8_t>(); tb.decode_bits = d_dec_bits_.as<uint32_t>();
         tb.cap = (uint32_t)cap;
-        if ((e = timed(K_SCAN_TOKENS, [&] { return launch_scan_tokens(raw, n, tb, d_scratch_.as<unsigned long long>(), d_res, carry_protocol, stream_); })) != cudaSuccess)
-            return fail(e, "scan_tokens", err);
+        static const int kinds[2][3] = {{K_SCAN_COUNT, K_SCAN_PREFIX, K_SCAN_EMIT}, {K_SCAN_TOKENS, K_SCAN_TOKENS, K_SCAN_TOKENS}};
+        for (int stage = 0; stage < (carry_protocol ? 1 : 3); stage++)
+            if ((e = timed(kinds[carry_protocol ? 1 : 0][stage], [&] {
+                     return launch_scan_tokens(raw, n, tb, d_scratch_.as<unsigned long long>(), d_res, carry_protocol, stage, stream_);
+                 })) != cudaSuccess)
+                return fail(e, "scan_tokens", err);
         int rc = fetch_result(err);
         if (rc) return rc;
         if (h_res_.p->slow_scan && !carry_protocol) { carry_protocol = true; continue; }

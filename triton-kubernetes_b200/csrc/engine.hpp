@@ -74,7 +74,7 @@ struct DevBuf {
 
 enum KernelKind {
     K_ROW_OFFSETS = 0, K_EMIT, K_PREFIX_MATCH, K_SCAN_TOKENS, K_TOKEN_PREFIX, K_BRACKETS, K_SORT_BRACKETS, K_MATCH,
-    K_DECODE, K_ROWS, K_KEY_ORDER, K_MODULE_INDEX, K_COUNT
+    K_DECODE, K_ROWS, K_KEY_ORDER, K_MODULE_INDEX, K_SCAN_COUNT, K_SCAN_PREFIX, K_SCAN_EMIT, K_COUNT
 };
 const char *kernel_name(int kind);
 void set_default_timing(bool on);  // engines created from now on start with per-kernel timing on/off

@@ -97,8 +97,10 @@ struct DecodeBuffers {
 // carry_protocol false: every thread finds the backslash-run carry into its 64 bytes by looking at
 // most 512 bytes behind it, and sets res->slow_scan if that was not enough (the caller then runs
 // the kernel again with carry_protocol true: the carry travels by decoupled look-back).
+// stage: 0 clears and counts (or, with carry_protocol, runs the whole single-pass kernel), 1 folds the
+// tile counts, 2 emits the tokens -- three calls, so that the caller can time the kernels apart.
 cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, unsigned long long *scratch,
-                               ParseResult *res, bool carry_protocol, cudaStream_t s);
+                               ParseResult *res, bool carry_protocol, int stage, cudaStream_t s);
 // scratch: tok_scratch_words(n_tok) words
 cudaError_t launch_token_prefix(TokenBuffers tb, uint32_t n_tok, TilePrefix *tiles, unsigned long long *scratch,
                                 ParseResult *res, cudaStream_t s);
