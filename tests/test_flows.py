@@ -286,3 +286,83 @@ def test_create_ladders(oracle, tmp_path):
     assert e(nc, dict(cluster_manager="dev", cluster_cloud_provider="baremetal", name="ok")) == "k8s_version must be specified"
     nn = flows.create.new_node
     assert e(nn, dict(cluster_manager="dev")) == "not an object"       # an empty manager has no "module": Clusters() fails (create/node.go:97-100)
+
+
+# ------------------------------------------------------------------ vSphere cluster + nodes (config #3, the other provider with no cloud API calls)
+
+VSPHERE_CLUSTER = dict(cluster_manager="dev", cluster_cloud_provider="vsphere", name="v1", k8s_version="v1.9.5-rancher1-1",
+                       k8s_network_provider="flannel", private_registry="", k8s_registry="",
+                       vsphere_user="admin@vsphere.local", vsphere_password="p<w>&d", vsphere_server="vc.example", vsphere_datacenter_name="dc1",
+                       vsphere_datastore_name="ds1", vsphere_resource_pool_name="pool", vsphere_network_name="VM Network",
+                       vsphere_template_name="ubuntu-tpl", ssh_user="ubuntu", key_path="~/.ssh/id_rsa",
+                       nodes=[dict(rancher_host_label="etcd", node_count=1, hostname="v1-e"),
+                              dict(rancher_host_label="worker", node_count=2, hostname="v1-w")])
+
+
+def run_vsphere(make_env, root, log, monkeypatch):
+    stub_dir = os.path.join(root, "bin")
+    os.makedirs(stub_dir, exist_ok=True)
+    stub = os.path.join(stub_dir, "terraform")
+    open(stub, "w").write(STUB)
+    os.chmod(stub, os.stat(stub).st_mode | stat.S_IEXEC)
+    monkeypatch.setenv("PATH", stub_dir + os.pathsep + os.environ["PATH"])
+    monkeypatch.setenv("TK_STUB_LOG", log)
+    monkeypatch.setenv("HOME", "/home/tester")
+    store = os.path.join(root, "store")
+    flows.create.new_manager(make_env(store, MANAGER))
+    env = make_env(store, VSPHERE_CLUSTER)
+    flows.create.new_cluster(env)
+    created = open(os.path.join(store, "dev", "main.tf.json"), "rb").read()
+    env2 = make_env(store, dict(cluster_manager="dev", cluster_name="v1", rancher_host_label="worker", node_count="2", hostname="v1-w",
+                                vsphere_template_name="tpl2", ssh_user="root", key_path="/keys/k"))
+    added = flows.create.new_node(env2)
+    grown = open(os.path.join(store, "dev", "main.tf.json"), "rb").read()
+    return created, grown, list(env.out), added
+
+
+def check_vsphere(created, grown, out, added):
+    doc = json.loads(created)
+    assert sorted(doc["module"]) == ["cluster-manager", "cluster_vsphere_v1", "node_vsphere_v1_v1-e-1", "node_vsphere_v1_v1-w-1", "node_vsphere_v1_v1-w-2"]
+    c = doc["module"]["cluster_vsphere_v1"]
+    assert c["source"].endswith("//terraform/modules/vsphere-rancher-k8s?ref=master") and c["vsphere_network_name"] == "VM Network"
+    n = doc["module"]["node_vsphere_v1_v1-w-2"]
+    assert n["source"].endswith("//terraform/modules/vsphere-rancher-k8s-host?ref=master")
+    assert n["vsphere_user"] == "admin@vsphere.local" and n["vsphere_password"] == "p<w>&d"        # copied from the cluster block
+    assert n["vsphere_datastore_name"] == "${module.cluster_vsphere_v1.vsphere_datastore_name}"    # referenced, not copied
+    assert n["vsphere_template_name"] == "ubuntu-tpl" and n["key_path"] == "/home/tester/.ssh/id_rsa" and n["hostname"] == "v1-w-2"
+    assert b"p\\u003cw\\u003e\\u0026d" in created                                                  # escapeHTML on the way to disk
+    assert out == ["1 node added: v1-e-1", "2 nodes added: v1-w-1, v1-w-2"]
+    assert added == ["v1-w-3", "v1-w-4"]
+    g = json.loads(grown)["module"]
+    assert g["node_vsphere_v1_v1-w-4"]["vsphere_template_name"] == "tpl2" and g["node_vsphere_v1_v1-w-4"]["key_path"] == "/keys/k"
+
+
+def test_vsphere_cluster_and_nodes_on_the_oracle(oracle, tmp_path, monkeypatch):
+    check_vsphere(*run_vsphere(oracle_factory(oracle), str(tmp_path), str(tmp_path / "stub.log"), monkeypatch))
+
+
+@pytest.mark.gpu
+def test_vsphere_product_matches_oracle(tk, oracle, tmp_path, monkeypatch):
+    a = run_vsphere(product_factory(tk), str(tmp_path / "gpu"), str(tmp_path / "gpu.log"), monkeypatch)
+    b = run_vsphere(oracle_factory(oracle), str(tmp_path / "ora"), str(tmp_path / "ora.log"), monkeypatch)
+    check_vsphere(*a)
+    fix = lambda s: s.replace(str(tmp_path / "gpu").encode(), b"<root>").replace(str(tmp_path / "ora").encode(), b"<root>")
+    assert fix(a[0]) == fix(b[0]) and fix(a[1]) == fix(b[1]) and a[2:] == b[2:]
+
+
+def test_vsphere_ladders(oracle, tmp_path):
+    make = oracle_factory(oracle)
+    store = str(tmp_path / "s")
+    e = lambda fn, s: err(fn, make(store, s))
+    os.makedirs(tmp_path / "s" / "dev")
+    base = dict(cluster_manager="dev", cluster_cloud_provider="vsphere", name="v1", k8s_version="v", k8s_network_provider="calico",
+                private_registry="", k8s_registry="")
+    nc = flows.create.new_cluster
+    assert e(nc, base) == "vsphere_user must be specified."
+    keys = ["vsphere_user", "vsphere_password", "vsphere_server", "vsphere_datacenter_name", "vsphere_datastore_name",
+            "vsphere_resource_pool_name", "vsphere_network_name"]
+    for i in range(1, len(keys)):
+        assert e(nc, dict(base, **{k: "x" for k in keys[:i]})) == "%s must be specified." % keys[i]
+    assert flows.create._expand_home("~/a") == os.path.expanduser("~") + "/a" and flows.create._expand_home("/abs") == "/abs"
+    with pytest.raises(flows.FlowError):
+        flows.create._expand_home("~other/a")

@@ -1,7 +1,9 @@
-"""create/manager.go:29-154, create/cluster.go:45-290, create/node.go:43-347 and the bare-metal
-renderers (create/{manager,cluster,node}_bare_metal.go), non-interactive mode only."""
+"""create/manager.go:29-154, create/cluster.go:45-290, create/node.go:43-347, the bare-metal renderers
+(create/{manager,cluster,node}_bare_metal.go) and the vSphere ones (create/{cluster,node}_vsphere.go),
+non-interactive mode only."""
 from __future__ import annotations
 
+import os
 import re
 
 from . import shell
@@ -98,7 +100,9 @@ def new_cluster(env):
     provider = _need(cfg, "cluster_cloud_provider")
     if provider == "baremetal":
         cluster_name = _new_bare_metal_cluster(env, state)
-    elif provider in CLOUD_API or provider == "vsphere":
+    elif provider == "vsphere":
+        cluster_name = _new_vsphere_cluster(env, state)
+    elif provider in CLOUD_API:
         raise FlowError("cluster_cloud_provider '%s' needs cloud API calls, which this build leaves out" % provider)
     else:
         raise FlowError("Unsupported cloud provider '%s', cannot create cluster" % provider)
@@ -150,6 +154,19 @@ def _new_bare_metal_cluster(env, state):                                        
     return s["name"]
 
 
+VSPHERE_CLUSTER_KEYS = ("vsphere_user", "vsphere_password", "vsphere_server", "vsphere_datacenter_name", "vsphere_datastore_name",
+                        "vsphere_resource_pool_name", "vsphere_network_name")
+
+
+def _new_vsphere_cluster(env, state):                                               # create/cluster_vsphere.go:29-195
+    cfg = env.config
+    s = _base_cluster(env, "vsphere")
+    for key in VSPHERE_CLUSTER_KEYS:                                                # the ladder, in the reference's order
+        s[key] = _need(cfg, key, "%s must be specified." % key)
+    state.AddCluster("vsphere", s["name"], env.render("vSphereClusterTerraformConfig", s))
+    return s["name"]
+
+
 # ---------------------------------------------------------------------------------- node
 
 def new_node(env):                                                                  # create/node.go:43-169
@@ -176,7 +193,9 @@ def new_node_in(env, manager, cluster_key, state):                              
         raise FlowError("Could not determine cloud provider for cluster '%s'" % cluster_key)
     if parts[1] == "baremetal":
         return _new_bare_metal_node(env, cluster_key, state)
-    if parts[1] in CLOUD_API or parts[1] == "vsphere":
+    if parts[1] == "vsphere":
+        return _new_vsphere_node(env, cluster_key, state)
+    if parts[1] in CLOUD_API:
         raise FlowError("provider '%s' needs cloud API calls, which this build leaves out" % parts[1])
     raise FlowError("Unsupported cloud provider '%s', cannot create node" % parts[1])
 
@@ -226,6 +245,33 @@ def _new_bare_metal_node(env, cluster_key, state):                              
         raise FlowError("not enough hosts")
     for host, hostname in zip(hosts, hostnames):
         state.AddNode(cluster_key, hostname, env.render("bareMetalNodeTerraformConfig", dict(s, hostname=hostname, host=host)))
+    return hostnames
+
+
+def _expand_home(path):
+    """homedir.Expand: a leading ~ (alone or before a slash) becomes $HOME; anything else is left alone"""
+    if path == "~" or path.startswith("~/"):
+        return os.path.expanduser("~") + path[1:]
+    if path.startswith("~"):
+        raise FlowError("cannot expand user-specific home dir")
+    return path
+
+
+def _new_vsphere_node(env, cluster_key, state):                                     # create/node_vsphere.go:37-158
+    cfg = env.config
+    s, count = _base_node(env, "vsphere", cluster_key, state)
+    get = lambda p: state.Get(p).decode()
+    for key in ("vsphere_user", "vsphere_password", "vsphere_server"):              # copied from the cluster's block
+        s[key] = get("module.%s.%s" % (cluster_key, key))
+    for key in ("vsphere_datacenter_name", "vsphere_datastore_name", "vsphere_resource_pool_name", "vsphere_network_name"):
+        s[key] = "${module.%s.%s}" % (cluster_key, key)                             # terraform outputs of the cluster module
+    s["vsphere_template_name"] = _need(cfg, "vsphere_template_name")
+    s["ssh_user"] = _need(cfg, "ssh_user")
+    s["key_path"] = _expand_home(_need(cfg, "key_path"))
+    existing = [h.decode() for h in state.Nodes(cluster_key)]
+    hostnames = env.state.getNewHostnames(existing, s["hostname"], count)
+    for hostname in hostnames:
+        state.AddNode(cluster_key, hostname, env.render("vSphereNodeTerraformConfig", dict(s, hostname=hostname)))
     return hostnames
 
 
