@@ -484,8 +484,10 @@ namespace {
 // P2a: per-tile prefixes over the token stream
 // =================================================================================================
 
-__device__ __forceinline__ bool is_opener(uint32_t k) { return k == T_LBRACE || k == T_LBRACKET; }
-__device__ __forceinline__ bool is_closer(uint32_t k) { return k == T_RBRACE || k == T_RBRACKET; }
+// T_LBRACE 0, T_RBRACE 1, T_LBRACKET 2, T_RBRACKET 3: bit 1 tells braces from brackets, bit 0 openers from closers
+__device__ __forceinline__ bool is_opener(uint32_t k) { return (k & ~2u) == 0u; }
+__device__ __forceinline__ bool is_closer(uint32_t k) { return (k & ~2u) == 1u; }
+static_assert(T_LBRACE == 0 && T_RBRACE == 1 && T_LBRACKET == 2 && T_RBRACKET == 3, "is_opener / is_closer");
 
 // Which tokens start a tape row: scalars, openers, the opening quote of a string VALUE (no colon
 // two tokens on), and closers other than the one of an empty container (which rides on the
@@ -520,10 +522,9 @@ __device__ __forceinline__ KindWindow load_kinds(const uint8_t *kind, uint32_t b
     return kw;
 }
 __device__ __forceinline__ bool emits_row_k(uint32_t k, uint32_t prev, uint32_t next2) {
-    if (k == T_SCALAR || is_opener(k)) return true;
-    if (k == T_STR_OPEN) return next2 != T_COLON;
-    if (is_closer(k)) return !is_opener(prev);
-    return false;
+    // (bitwise on purpose: no branches)
+    return ((uint32_t)(k == T_SCALAR) | (uint32_t)is_opener(k) | ((uint32_t)(k == T_STR_OPEN) & (uint32_t)(next2 != T_COLON)) |
+            ((uint32_t)is_closer(k) & (uint32_t)!is_opener(prev))) != 0u;
 }
 
 // exclusive block scan of (depth delta, rows, brackets) over TP_THREADS threads, plus block totals
@@ -1134,7 +1135,9 @@ __global__ void __launch_bounds__(TP_THREADS) rows_kernel(const uint8_t *__restr
         const uint32_t i = base + j;
         const uint32_t k = kind[i];   // 0xff past the end
         const bool op = is_opener(k), cl = is_closer(k);
-        const uint32_t row = (k == T_SCALAR || op || (k == T_STR_OPEN && kind[i + 2] != T_COLON) || (cl && !is_opener(kind[i - 1]))) ? 1u : 0u;
+        // (bitwise on purpose: no branches, both neighbours are read unconditionally)
+        const uint32_t row = (uint32_t)(k == T_SCALAR) | (uint32_t)op | ((uint32_t)(k == T_STR_OPEN) & (uint32_t)(kind[i + 2] != T_COLON)) |
+                             ((uint32_t)cl & (uint32_t)!is_opener(kind[i - 1]));
         d += (op ? 1 : 0) - (cl ? 1 : 0);
         b += (op || cl) ? 1u : 0u;
         r += row;
