@@ -682,16 +682,20 @@ __global__ void __launch_bounds__(TBP_THREADS) token_blocks_kernel(const TokAgg 
         if (warp == 0) { bd = 0; br = 0; bb2 = 0; }
         TilePrefix p;
         p.depth = run_d + bd + xd - d; p.rows = run_r + br + xr - r; p.brackets = run_b + bb2 + xb - b; p.pad = 0;
+        int lo = 0, hi = 0;   // lowest / highest depth reached inside this thread's blocks (0: nothing to report)
 #pragma unroll
         for (int j = 0; j < TBP_ITEMS; j++) {
             if (first + j < n_blocks) {
                 tiles[first + j] = p;
-                if (a[j].mn != 0x7fffffff) {
-                    if (p.depth + a[j].mn < 0) atomicMin(&s_lo, p.depth + a[j].mn);
-                    if (p.depth + a[j].mx > 0) atomicMax(&s_hi, p.depth + a[j].mx);
-                }
+                if (a[j].mn != 0x7fffffff) { lo = min(lo, p.depth + a[j].mn); hi = max(hi, p.depth + a[j].mx); }
                 p.depth += a[j].d; p.rows += a[j].rows; p.brackets += a[j].brackets;
             }
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) { lo = min(lo, __shfl_xor_sync(FULL, lo, o)); hi = max(hi, __shfl_xor_sync(FULL, hi, o)); }
+        if (lane == 0) {   // one shared-memory atomic per warp, not per block of tokens
+            if (lo < 0) atomicMin(&s_lo, lo);
+            if (hi > 0) atomicMax(&s_hi, hi);
         }
         run_d += td; run_r += tr; run_b += tbk;
     }

@@ -1,12 +1,17 @@
 // parse.cuh -- GPU side of state.New: raw JSON text -> validated line tape (tape.hpp), all on the
 // device.  Implemented in parse.cu; driven by Engine::parse (engine.cu).
 //
-// Pipeline (every kernel is byte/integer work bounded by HBM/L2 bandwidth):
-//   P1 scan_tokens     bytes -> token stream.  String/escape state is carried across the whole
-//                      text with a two-stage decoupled look-back (backslash-run carry, then
-//                      quote parity + token count); tokens (position, kind) are compacted in
-//                      order.  Also checks string bodies (control bytes, escape codes) and marks
-//                      strings that need decoding (escapes or non-ASCII bytes).
+// Pipeline (byte/integer kernels; see DESIGN.md section 3 for what bounds each):
+//   P1 scan            bytes -> token stream, with no block waiting on another (scan_fast.cuh):
+//                      scan_count  per 8 KiB tile (quote parity, tokens if entered outside a string,
+//                                  tokens if entered inside);
+//                      scan_prefix one block folds those in order: string state and token count
+//                                  at the start of every tile;
+//                      scan_emit   tokens (position, kind) written in order at their final places;
+//                                  string bodies checked (control bytes, escape codes); strings that
+//                                  need decoding (escapes, non-ASCII bytes, < > &) marked.
+//                      A backslash run longer than 512 bytes sends the text through the older
+//                      single-pass kernel (scan_tokens_kernel: two-stage decoupled look-back).
 //   P2a token_prefix   per 2,048-token block: nesting depth, row count and bracket count before it
 //                      (per-block aggregates, then one block folds them in order)
 //   P2b brackets       bracket tokens compacted with their nesting level
