@@ -30,18 +30,20 @@ __global__ void child_refs_kernel(TapeView t, uint32_t module_row, const uint32_
                                   const uint32_t *__restrict__ rank, ChildRef *refs) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= t.n_rows || r <= module_row) return;
+    // independent loads first, so that they are in flight together (the kernel is a chain of
+    // dependent look-ups otherwise: meta -> key length -> key bytes -> rank)
+    const uint32_t meta = t.meta[r], kl = t.klen[r], rk = rank[r];
     const uint32_t module_end = closing_row(t, module_row, br_match, br_row);
     if (r >= module_end) return;
-    const uint32_t meta = t.meta[r];
     if (starts_child(meta, r, module_row, module_end)) {
-        ChildRef *c = refs + rank[r];
+        ChildRef *c = refs + rk;
         c->koff = t.koff[r];
-        c->klen = t.klen[r];
+        c->klen = kl;
         return;
     }
-    if (row_depth(meta) != 3 || !(meta & META_HAS_KEY) || (meta & 15u) != ROW_STR) return;
-    const uint32_t ko = t.koff[r], kl = t.klen[r];
-    ChildRef *c = refs + (rank[r] - 1);
+    if (row_depth(meta) != 3 || !(meta & META_HAS_KEY) || (meta & 15u) != ROW_STR || (kl != 4 && kl != 8)) return;
+    const uint32_t ko = t.koff[r];
+    ChildRef *c = refs + (rk - 1);
     if (key_is(t.arena, ko, kl, "name", 4)) { c->noff = t.voff[r]; c->nlen = t.vlen[r]; }
     else if (key_is(t.arena, ko, kl, "hostname", 8)) { c->hoff = t.voff[r]; c->hlen = t.vlen[r]; }
 }
