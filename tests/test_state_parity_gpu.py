@@ -327,3 +327,40 @@ def test_index_module_not_an_object(tk, raw, err):
             call()
         assert str(e.value) == err
     assert tk.New("x", b'{"module":{}}').Clusters() == {}
+
+
+def test_document_larger_than_one_fold_round(tk, oracle):
+    """1,400 clusters x 100 nodes (87 MB, 9.8 M tokens, 563 k brackets): the one-block folds of the
+    parser (tile triples: 8,192 per round; token blocks: 4,096; radix run starts: 4,096 entries)
+    all need more than one round, which config #4 does not reach."""
+    b = oracle.New("big", synth.document(1400, 100))
+    raw = b.Bytes()                                     # the persisted form: keys in order, so the document stays on the device
+    a = tk.New("big", raw)
+    text = a.Bytes()
+    assert len(text) > 64 * 8192 * 128 and text == raw
+    assert not a.host_tree_built
+    ca = a.Clusters()
+    assert ca == b.Clusters() and len(ca) == 1400
+    for c in (0, 1, 777, 1399):
+        assert a.Nodes(synth.cluster_key(c)) == b.Nodes(synth.cluster_key(c))
+    assert tk.New("big", text).Bytes() == text
+
+
+@pytest.mark.parametrize("bad_at", [1, 31, 32, 33, 63, 64, 100, 198])
+def test_index_order_violation_anywhere_in_a_run(tk, oracle, bad_at):
+    """200 nodes of one cluster whose hostnames ascend with their keys except at one place: the run
+    is not in field order, which the index records in a bitmap (one bit per record) -- also for
+    records past the first words of it -- and the lookup must then sort like the reference."""
+    mod = {"cluster_a_c": {"name": "c"}}
+    for i in range(200):
+        host = "h%03d" % i
+        if i == bad_at:
+            host = "h%03d" % (i - 1) if i % 2 else "a-first"        # a duplicate of the previous name / one that sorts before all
+        mod["node_a_c_%03d" % i] = {"hostname": host}
+    mod["node_a_c_150x"] = {"name": "no hostname here"}              # a child without the field inside the run
+    raw = oracle.New("x", json.dumps({"module": mod}).encode()).Bytes()
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    got = a.Nodes("cluster_a_c")
+    assert got == b.Nodes("cluster_a_c") and len(got) in (199, 200)
+    assert not a.host_tree_built
+    assert a.Clusters() == b.Clusters() == {b"c": b"cluster_a_c"}
