@@ -271,8 +271,14 @@ def test_config4_full_size(tk, oracle):
     again = tk.New("bench", text)
     assert again.Bytes() == text                                    # serialise(parse(x)) is a fixed point
     assert sum(len(a.Nodes(ck)) for ck in list(ca.values())[::50]) == 20 * 100
-    a.Delete("module." + synth.node_key(7, 7))
-    assert len(a.Nodes(synth.cluster_key(7))) == 99 and len(a.Bytes()) < len(text)
+    # an edit moves the document to the host tree; Bytes() then flattens it (the 101,001 members of
+    # "module" by several threads) and serialises the uploaded tape
+    for s in (a, b):
+        s.Delete("module." + synth.node_key(7, 7))
+        s.AddNode(synth.cluster_key(3), "extra<&>", {"hostname": "extra<&>", "n": [1, 2.5, None, True, {}], "s": "\u00e9\n"})
+    assert len(a.Nodes(synth.cluster_key(7))) == 99 and a.Nodes(synth.cluster_key(3)) == b.Nodes(synth.cluster_key(3))
+    edited = a.Bytes()
+    assert edited == b.Bytes() and len(edited) != len(text)
 
 
 def _module_doc(rng, n):
@@ -364,3 +370,27 @@ def test_index_order_violation_anywhere_in_a_run(tk, oracle, bad_at):
     assert got == b.Nodes("cluster_a_c") and len(got) in (199, 200)
     assert not a.host_tree_built
     assert a.Clusters() == b.Clusters() == {b"c": b"cluster_a_c"}
+
+
+def test_wide_unsorted_object_is_rebuilt_by_several_threads(tk, oracle):
+    """30,000 members in shuffled order with duplicates (the last one wins), one of them an
+    out-of-range number nowhere / everywhere: the host tree of such a wide object is built by several
+    threads (engine.cu, build_value) and flattened by several threads, and must come out exactly
+    as the single-threaded oracle's."""
+    rng = random.Random(31337)
+    ids = list(range(30000)) + [rng.randrange(30000) for _ in range(500)]
+    rng.shuffle(ids)
+    body = ",".join('"k%05d":{"v":%d,"s":["a<%d>",null]}' % (i, pos, i) for pos, i in enumerate(ids))
+    raw = ('{"z":1,"wide":{' + body + '},"a":[]}').encode()
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    assert a.host_tree_built                      # keys out of order: the tree is built at once
+    assert a.Bytes() == b.Bytes()
+    assert a.Get("wide.k00007.v") == b.Get("wide.k00007.v")
+    # the first out-of-range number in text order is the one reported, whichever thread met it
+    bad = raw.replace(b'"k%05d":{"v":' % ids[20000], b'"k%05d":{"v":1e999,"w":' % ids[20000], 1).replace(
+        b'"k%05d":{"v":' % ids[100], b'"k%05d":{"v":2e999,"w":' % ids[100], 1)
+    with pytest.raises(oracle.OracleError) as want:
+        oracle.New("x", bad)
+    with pytest.raises(tk.StateError) as got:
+        tk.New("x", bad)
+    assert str(got.value) == str(want.value) and "2e999" in str(got.value)

@@ -8,6 +8,7 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <thread>
 
 #include "kernels.cuh"
 #include "tk_state.h"
@@ -234,70 +235,135 @@ static bool is_plain(const char *s, size_t n) {
     return true;
 }
 
-void Engine::push_row(uint32_t kind, uint32_t depth, const std::string *key, const char *val, size_t vlen, bool comma, bool last) {
+// Where the rows of a flatten go: the handle's pinned arrays (FlatPinned) or, for a worker thread
+// of a wide object, plain vectors that are appended to them afterwards (FlatLocal).
+struct FlatPinned {
+    PinVec<uint32_t> &meta, &koff, &klen, &voff, &vlen;
+    PinVec<uint8_t> &arena;
+    static constexpr bool may_fork = true;
+    size_t put(const char *p, size_t n) { return arena.append(reinterpret_cast<const uint8_t *>(p), n); }
+    void row(uint32_t m, uint32_t ko, uint32_t kl, uint32_t vo, uint32_t vl) { meta.push(m); koff.push(ko); klen.push(kl); voff.push(vo); vlen.push(vl); }
+};
+struct FlatLocal {
+    std::vector<uint32_t> meta, koff, klen, voff, vlen;
+    std::vector<uint8_t> arena;
+    static constexpr bool may_fork = false;
+    size_t put(const char *p, size_t n) { const size_t at = arena.size(); arena.insert(arena.end(), p, p + n); return at; }
+    void row(uint32_t m, uint32_t ko, uint32_t kl, uint32_t vo, uint32_t vl) {
+        meta.push_back(m); koff.push_back(ko); klen.push_back(kl); voff.push_back(vo); vlen.push_back(vl);
+    }
+};
+
+template <class Sink>
+static void push_row(Sink &out, uint32_t kind, uint32_t depth, const std::string *key, const char *val, size_t vlen, bool comma, bool last) {
     uint32_t meta = kind | (depth << META_DEPTH_SHIFT);
     uint32_t koff = 0, klen = 0, voff = 0;
     if (kind == ROW_STR && is_plain(val, vlen)) meta |= META_VAL_PLAIN;
     if (key) {
         meta |= META_HAS_KEY;
         if (is_plain(key->data(), key->size())) meta |= META_KEY_PLAIN;
-        koff = (uint32_t)h_arena_.append(reinterpret_cast<const uint8_t *>(key->data()), key->size());
+        koff = (uint32_t)out.put(key->data(), key->size());
         klen = (uint32_t)key->size();
     }
-    if (vlen) voff = (uint32_t)h_arena_.append(reinterpret_cast<const uint8_t *>(val), vlen);
+    if (vlen) voff = (uint32_t)out.put(val, vlen);
     if (comma) meta |= META_COMMA;
     if (last) meta |= META_LAST;
-    h_meta_.push(meta);
-    h_koff_.push(koff);
-    h_klen_.push(klen);
-    h_voff_.push(voff);
-    h_vlen_.push((uint32_t)vlen);
+    out.row(meta, koff, klen, voff, (uint32_t)vlen);
+}
+
+template <class Sink>
+static void flat_value(Sink &out, const Node *n, uint32_t depth, const std::string *key, bool comma, bool last);
+
+// An object with very many members (the "module" of a large state document): the members are
+// flattened by several threads, each into its own vectors, and appended in order.  The tree is
+// only read.  Offsets of a worker's rows are relative to its own arena and are moved on append.
+constexpr size_t FORK_MIN_MEMBERS = 8192;
+static void flat_members_forked(FlatPinned &out, const MapNode *node, uint32_t depth) {
+    const size_t n = node->m.size();
+    std::vector<const std::pair<const std::string, Node *> *> members;
+    members.reserve(n);
+    for (auto &kv : node->m) members.push_back(&kv);
+    const size_t hw = std::max<size_t>(1, std::thread::hardware_concurrency());
+    const size_t workers = std::max<size_t>(2, std::min<size_t>({hw, 16, n / 1024}));
+    std::vector<FlatLocal> parts(workers);
+    std::vector<std::thread> threads;
+    std::atomic<bool> failed{false};
+    for (size_t w = 0; w < workers; w++)
+        threads.emplace_back([&, w] {
+            try {
+                FlatLocal &p = parts[w];
+                for (size_t i = w * n / workers; i < (w + 1) * n / workers; i++)
+                    flat_value(p, members[i]->second, depth, &members[i]->first, i + 1 < n, false);
+            } catch (...) {   // out of memory: reported like a failed pinned allocation
+                failed = true;
+            }
+        });
+    for (auto &t : threads) t.join();
+    if (failed) { out.arena.failed = true; return; }
+    // one growth step for everything the workers produced (pinned allocations are not cheap)
+    size_t rows = 0, bytes = 0;
+    for (const FlatLocal &p : parts) { rows += p.meta.size(); bytes += p.arena.size(); }
+    out.arena.reserve(out.arena.n + bytes + 4096);
+    for (PinVec<uint32_t> *v : {&out.meta, &out.koff, &out.klen, &out.voff, &out.vlen}) v->reserve(v->n + rows + 64);
+    for (const FlatLocal &p : parts) {
+        const uint32_t base = (uint32_t)out.arena.append(p.arena.data(), p.arena.size());
+        for (size_t r = 0; r < p.meta.size(); r++)
+            out.row(p.meta[r], p.klen[r] ? p.koff[r] + base : 0u, p.klen[r], p.vlen[r] ? p.voff[r] + base : 0u, p.vlen[r]);
+    }
 }
 
 // One row per output line, in the order encoding/json writes them: map keys ascending, record
 // members as given, arrays in index order.
-void Engine::flat_value(const Node *n, uint32_t depth, const std::string *key, bool comma, bool last) {
-    if (!n) { push_row(ROW_RAW, depth, key, "null", 4, comma, last); return; }
+template <class Sink>
+static void flat_value(Sink &out, const Node *n, uint32_t depth, const std::string *key, bool comma, bool last) {
+    if (!n) { push_row(out, ROW_RAW, depth, key, "null", 4, comma, last); return; }
     switch (n->kind) {
     case Kind::Bool: {
         bool v = static_cast<const BoolNode *>(n)->v;
-        push_row(ROW_RAW, depth, key, v ? "true" : "false", v ? 4 : 5, comma, last);
+        push_row(out, ROW_RAW, depth, key, v ? "true" : "false", v ? 4 : 5, comma, last);
         break;
     }
     case Kind::Num: {
         std::string t;
         format_go_float(static_cast<const NumNode *>(n)->v, &t);
-        push_row(ROW_RAW, depth, key, t.data(), t.size(), comma, last);
+        push_row(out, ROW_RAW, depth, key, t.data(), t.size(), comma, last);
         break;
     }
     case Kind::Str: {
         const std::string &s = static_cast<const StrNode *>(n)->s;
-        push_row(ROW_STR, depth, key, s.data(), s.size(), comma, last);
+        push_row(out, ROW_STR, depth, key, s.data(), s.size(), comma, last);
         break;
     }
     case Kind::Arr: {
         auto &items = static_cast<const ArrNode *>(n)->items;
-        if (items.empty()) { push_row(ROW_EMPTY_ARR, depth, key, nullptr, 0, comma, last); break; }
-        push_row(ROW_OPEN_ARR, depth, key, nullptr, 0, false, false);
-        for (size_t i = 0; i < items.size(); i++) flat_value(items[i], depth + 1, nullptr, i + 1 < items.size(), false);
-        push_row(ROW_CLOSE_ARR, depth, nullptr, nullptr, 0, comma, last);
+        if (items.empty()) { push_row(out, ROW_EMPTY_ARR, depth, key, nullptr, 0, comma, last); break; }
+        push_row(out, ROW_OPEN_ARR, depth, key, nullptr, 0, false, false);
+        for (size_t i = 0; i < items.size(); i++) flat_value(out, items[i], depth + 1, nullptr, i + 1 < items.size(), false);
+        push_row(out, ROW_CLOSE_ARR, depth, nullptr, nullptr, 0, comma, last);
         break;
     }
     case Kind::Map: {
         auto &m = static_cast<const MapNode *>(n)->m;
-        if (m.empty()) { push_row(ROW_EMPTY_OBJ, depth, key, nullptr, 0, comma, last); break; }
-        push_row(ROW_OPEN_OBJ, depth, key, nullptr, 0, false, false);
+        if (m.empty()) { push_row(out, ROW_EMPTY_OBJ, depth, key, nullptr, 0, comma, last); break; }
+        push_row(out, ROW_OPEN_OBJ, depth, key, nullptr, 0, false, false);
+        if constexpr (Sink::may_fork) {
+            if (m.size() >= FORK_MIN_MEMBERS) {
+                flat_members_forked(out, static_cast<const MapNode *>(n), depth + 1);
+                push_row(out, ROW_CLOSE_OBJ, depth, nullptr, nullptr, 0, comma, last);
+                break;
+            }
+        }
         size_t i = 0;
-        for (auto &kv : m) flat_value(kv.second, depth + 1, &kv.first, ++i < m.size(), false);
-        push_row(ROW_CLOSE_OBJ, depth, nullptr, nullptr, 0, comma, last);
+        for (auto &kv : m) flat_value(out, kv.second, depth + 1, &kv.first, ++i < m.size(), false);
+        push_row(out, ROW_CLOSE_OBJ, depth, nullptr, nullptr, 0, comma, last);
         break;
     }
     case Kind::Rec: {
         auto &m = static_cast<const RecNode *>(n)->m;
-        if (m.empty()) { push_row(ROW_EMPTY_OBJ, depth, key, nullptr, 0, comma, last); break; }
-        push_row(ROW_OPEN_OBJ, depth, key, nullptr, 0, false, false);
-        for (size_t i = 0; i < m.size(); i++) flat_value(m[i].second, depth + 1, &m[i].first, i + 1 < m.size(), false);
-        push_row(ROW_CLOSE_OBJ, depth, nullptr, nullptr, 0, comma, last);
+        if (m.empty()) { push_row(out, ROW_EMPTY_OBJ, depth, key, nullptr, 0, comma, last); break; }
+        push_row(out, ROW_OPEN_OBJ, depth, key, nullptr, 0, false, false);
+        for (size_t i = 0; i < m.size(); i++) flat_value(out, m[i].second, depth + 1, &m[i].first, i + 1 < m.size(), false);
+        push_row(out, ROW_CLOSE_OBJ, depth, nullptr, nullptr, 0, comma, last);
         break;
     }
     }
@@ -305,9 +371,10 @@ void Engine::flat_value(const Node *n, uint32_t depth, const std::string *key, b
 
 void Engine::flatten(const Document &doc) {
     h_meta_.clear(); h_koff_.clear(); h_klen_.clear(); h_voff_.clear(); h_vlen_.clear(); h_arena_.clear();
+    FlatPinned out{h_meta_, h_koff_, h_klen_, h_voff_, h_vlen_, h_arena_};
     // the LAST flag (no trailing newline) lands on the root's own row, or on its closing row
-    if (!doc.root) push_row(ROW_EMPTY_OBJ, 0, nullptr, nullptr, 0, false, true);  // gabs: nil -> "{}"
-    else flat_value(doc.root, 0, nullptr, false, true);
+    if (!doc.root) push_row(out, ROW_EMPTY_OBJ, 0, nullptr, nullptr, 0, false, true);  // gabs: nil -> "{}"
+    else flat_value(out, doc.root, 0, nullptr, false, true);
     pin_failed_ = pin_failed_ || h_meta_.failed || h_koff_.failed || h_klen_.failed || h_voff_.failed || h_vlen_.failed ||
                   h_arena_.failed;
 }
@@ -680,6 +747,119 @@ int Engine::parse(const char *raw, size_t n, bool raw_on_device, Document *doc, 
     return TK_OK;
 }
 
+// Builds tree nodes from tape rows (rows in input order).  Map insertion keeps the last duplicate
+// (encoding/json objectInterface) and orders keys bytewise.  One builder per thread: the only state
+// it writes is its own first range error.
+struct TreeBuilder {
+    const uint32_t *meta, *koff, *klen, *voff, *vlen, *close_of;   // close_of[r]: the closing row of opener r
+    const char *arena;
+    std::string range_err;
+
+    void attach(Node *parent, Node *v, uint32_t r) const {
+        if (parent->kind == Kind::Map) {
+            auto &m = static_cast<MapNode *>(parent)->m;
+            std::string_view key(arena + koff[r], klen[r]);
+            auto hint = m.end();
+            if (!m.empty() && std::prev(hint)->first < key) {
+                m.emplace_hint(hint, std::string(key), v);  // ascending input: O(1) append
+            } else {
+                auto it = m.find(key);
+                if (it != m.end()) { free_node(it->second); it->second = v; }
+                else m.emplace(std::string(key), v);
+            }
+        } else {
+            static_cast<ArrNode *>(parent)->items.push_back(v);
+        }
+    }
+
+    Node *scalar(uint32_t r) {
+        if ((meta[r] & 15u) == ROW_STR) return new StrNode(std::string(arena + voff[r], vlen[r]));
+        std::string_view t(arena + voff[r], vlen[r]);
+        if (t == "true") return new BoolNode(true);
+        if (t == "false") return new BoolNode(false);
+        if (t == "null") return nullptr;
+        const std::string txt(t);
+        double d = strtod(txt.c_str(), nullptr);
+        if (std::isinf(d)) {
+            if (range_err.empty()) range_err = "json: cannot unmarshal number " + txt + " into Go value of type float64";
+            d = 0;
+        }
+        return new NumNode(d);
+    }
+
+    // the value that starts at row r; *next = the row after it.  Containers are walked with an
+    // explicit stack (nesting may be 10,000 deep).
+    Node *value(uint32_t r, uint32_t *next) {
+        const uint32_t kind = meta[r] & 15u;
+        if (kind == ROW_EMPTY_OBJ) { *next = r + 1; return new MapNode(); }
+        if (kind == ROW_EMPTY_ARR) { *next = r + 1; return new ArrNode(); }
+        if (kind != ROW_OPEN_OBJ && kind != ROW_OPEN_ARR) { *next = r + 1; return scalar(r); }
+        const uint32_t end = close_of[r];
+        Node *top = kind == ROW_OPEN_OBJ ? static_cast<Node *>(new MapNode()) : static_cast<Node *>(new ArrNode());
+        std::vector<Node *> stack{top};
+        for (uint32_t i = r + 1; i < end; i++) {
+            const uint32_t k = meta[i] & 15u;
+            if (k == ROW_CLOSE_OBJ || k == ROW_CLOSE_ARR) { stack.pop_back(); continue; }
+            Node *v;
+            if (k == ROW_OPEN_OBJ) v = new MapNode();
+            else if (k == ROW_OPEN_ARR) v = new ArrNode();
+            else if (k == ROW_EMPTY_OBJ) v = new MapNode();
+            else if (k == ROW_EMPTY_ARR) v = new ArrNode();
+            else v = scalar(i);
+            attach(stack.back(), v, i);
+            if (k == ROW_OPEN_OBJ || k == ROW_OPEN_ARR) stack.push_back(v);
+        }
+        *next = end + 1;
+        return top;
+    }
+};
+
+// A container that spans very many rows.  With many members (the "module" of a large state
+// document) they are built by several threads, each with its own builder, and attached in order;
+// with few (the root above it) each member is looked at the same way in turn.
+constexpr uint32_t FORK_MIN_ROWS = 65536, FORK_MIN_MEMBERS_BUILD = 1024;
+
+static Node *build_value(TreeBuilder &tb, uint32_t r, uint32_t *next, int levels) {
+    const uint32_t kind = tb.meta[r] & 15u;
+    if ((kind != ROW_OPEN_OBJ && kind != ROW_OPEN_ARR) || levels == 0 || tb.close_of[r] - r < FORK_MIN_ROWS) return tb.value(r, next);
+    const uint32_t end = tb.close_of[r];
+    std::vector<uint32_t> starts;   // first row of every member
+    for (uint32_t i = r + 1; i < end;) {
+        starts.push_back(i);
+        const uint32_t k = tb.meta[i] & 15u;
+        i = (k == ROW_OPEN_OBJ || k == ROW_OPEN_ARR) ? tb.close_of[i] + 1 : i + 1;
+    }
+    Node *top = kind == ROW_OPEN_OBJ ? static_cast<Node *>(new MapNode()) : static_cast<Node *>(new ArrNode());
+    const size_t n = starts.size();
+    std::vector<Node *> nodes(n, nullptr);
+    if (n < FORK_MIN_MEMBERS_BUILD) {
+        for (size_t i = 0; i < n; i++) { uint32_t nx; nodes[i] = build_value(tb, starts[i], &nx, levels - 1); }
+    } else {
+        const size_t hw = std::max<size_t>(1, std::thread::hardware_concurrency());
+        const size_t workers = std::max<size_t>(2, std::min<size_t>({hw, 16, n / 256}));
+        std::vector<TreeBuilder> builders(workers, tb);
+        std::vector<std::thread> threads;
+        std::atomic<bool> failed{false};
+        for (size_t w = 0; w < workers; w++) {
+            builders[w].range_err.clear();
+            threads.emplace_back([&, w] {
+                try {
+                    for (size_t i = w * n / workers; i < (w + 1) * n / workers; i++) { uint32_t nx; nodes[i] = builders[w].value(starts[i], &nx); }
+                } catch (...) {
+                    failed = true;
+                }
+            });
+        }
+        for (auto &t : threads) t.join();
+        if (failed) throw std::bad_alloc();
+        for (size_t w = 0; w < workers; w++)   // the first error in row order, as the single-threaded walk reports it
+            if (tb.range_err.empty() && !builders[w].range_err.empty()) tb.range_err = builders[w].range_err;
+    }
+    for (size_t i = 0; i < n; i++) tb.attach(top, nodes[i], starts[i]);
+    *next = end + 1;
+    return top;
+}
+
 // Rows arrive in input order; a stack of open containers rebuilds the tree.  Map insertion keeps
 // the last duplicate (encoding/json objectInterface) and orders keys bytewise.
 int Engine::materialise(Document *doc, std::string *err) {
@@ -699,57 +879,21 @@ int Engine::materialise(Document *doc, std::string *err) {
     for (int i = 0; i < 5; i++) hrows[i]->n = 0;  // scratch use only: the flattener starts from empty
     h_arena_.n = 0;
 
+    // the closing row of every opener, then the tree (wide containers by several threads)
     const char *arena = reinterpret_cast<const char *>(h_arena_.p);
-    std::vector<Node *> stack;
-    Node *root = nullptr;
-    std::string range_err;
-    auto attach = [&](Node *v, uint32_t r) {
-        if (stack.empty()) { root = v; return; }
-        Node *top = stack.back();
-        if (top->kind == Kind::Map) {
-            auto &m = static_cast<MapNode *>(top)->m;
-            std::string_view key(arena + h_koff_.p[r], h_klen_.p[r]);
-            auto hint = m.end();
-            if (!m.empty() && std::prev(hint)->first < key) {
-                m.emplace_hint(hint, std::string(key), v);  // ascending input: O(1) append
-            } else {
-                auto it = m.find(key);
-                if (it != m.end()) { free_node(it->second); it->second = v; }
-                else m.emplace(std::string(key), v);
-            }
-        } else {
-            static_cast<ArrNode *>(top)->items.push_back(v);
-        }
-    };
-    for (uint32_t r = 0; r < n; r++) {
-        const uint32_t meta = h_meta_.p[r];
-        switch (meta & 15u) {
-        case ROW_STR: attach(new StrNode(std::string(arena + h_voff_.p[r], h_vlen_.p[r])), r); break;
-        case ROW_RAW: {
-            std::string_view t(arena + h_voff_.p[r], h_vlen_.p[r]);
-            Node *v = nullptr;
-            if (t == "true") v = new BoolNode(true);
-            else if (t == "false") v = new BoolNode(false);
-            else if (t == "null") v = nullptr;
-            else {
-                const std::string txt(t);
-                double d = strtod(txt.c_str(), nullptr);
-                if (std::isinf(d)) {
-                    if (range_err.empty()) range_err = "json: cannot unmarshal number " + txt + " into Go value of type float64";
-                    d = 0;
-                }
-                v = new NumNode(d);
-            }
-            attach(v, r);
-            break;
-        }
-        case ROW_OPEN_OBJ: { Node *v = new MapNode(); attach(v, r); stack.push_back(v); break; }
-        case ROW_OPEN_ARR: { Node *v = new ArrNode(); attach(v, r); stack.push_back(v); break; }
-        case ROW_EMPTY_OBJ: attach(new MapNode(), r); break;
-        case ROW_EMPTY_ARR: attach(new ArrNode(), r); break;
-        default: if (!stack.empty()) stack.pop_back(); break;  // closers
+    std::vector<uint32_t> close_of(n, 0);
+    {
+        std::vector<uint32_t> open;
+        for (uint32_t r = 0; r < n; r++) {
+            const uint32_t k = h_meta_.p[r] & 15u;
+            if (k == ROW_OPEN_OBJ || k == ROW_OPEN_ARR) open.push_back(r);
+            else if ((k == ROW_CLOSE_OBJ || k == ROW_CLOSE_ARR) && !open.empty()) { close_of[open.back()] = r; open.pop_back(); }
         }
     }
+    TreeBuilder tb{h_meta_.p, h_koff_.p, h_klen_.p, h_voff_.p, h_vlen_.p, close_of.data(), arena, {}};
+    uint32_t next = 0;
+    Node *root = build_value(tb, 0, &next, 3);
+    const std::string &range_err = tb.range_err;
     if (!range_err.empty()) {
         free_node(root);
         *err = range_err;

@@ -145,8 +145,6 @@ private:
 
     void flatten(const Document &doc);
     void flatten_keys(const Document &doc);
-    void flat_value(const Node *n, uint32_t depth, const std::string *key, bool comma, bool last);
-    void push_row(uint32_t kind, uint32_t depth, const std::string *key, const char *val, size_t vlen, bool comma, bool last);
 
     bool ready_ = false;
     int device_ = -1;
