@@ -5,7 +5,8 @@ One STEP is one pass of the hot path over the 62,177,405-byte synthetic document
     state.New(text) -> Clusters() -> Nodes(ck) for each of the 1,000 cluster keys -> Bytes()
 = 1,003 state.State operations (destroy/cluster.go:64-161 and get/cluster.go:65-118 walk a
 document this way).  The step itself is a compiled loop over the C ABI (tools/bench_driver.c), for
-both arms, so that Python call overhead is not measured as if it were the library.
+both arms, and so is the loop over steps with its worker threads (tkb_product_run), so that
+Python call overhead and the GIL are not measured as if they were the library.
 
   value  the step with the text already resident in HBM and the result left in HBM
   e2e    the same step through the public C ABI with HOST buffers: pinned host text in, the
@@ -68,7 +69,7 @@ def driver():
     """tools/libtkbench.so: built on first use (gcc is part of the image, here and on the GPU box)."""
     src, lib = os.path.join(ROOT, "tools", "bench_driver.c"), os.path.join(ROOT, "tools", "libtkbench.so")
     if not os.path.exists(lib) or os.path.getmtime(lib) < os.path.getmtime(src):
-        subprocess.check_call(["gcc", "-O2", "-fPIC", "-shared", "-I" + os.path.join(ROOT, "include"), "-o", lib, src,
+        subprocess.check_call(["gcc", "-O2", "-fPIC", "-shared", "-pthread", "-I" + os.path.join(ROOT, "include"), "-o", lib, src,
                                "-L" + os.path.join(ROOT, "triton-kubernetes_b200"), "-ltkstate",
                                "-Wl,-rpath," + os.path.join(ROOT, "triton-kubernetes_b200")])
     importlib.import_module("triton-kubernetes_b200").state.lib()   # libtkstate first, by full path
@@ -282,70 +283,41 @@ def run_ours(args, rank, local_rank, world):
         L.tk_set_default_timing(0)
         return total, stats
 
+    AT_START = ctypes.CFUNCTYPE(None)
+    D.tkb_product_run.argtypes = [POINTER(c_void_p), c_size_t, c_size_t, c_int, c_int, c_int, POINTER(c_char_p), POINTER(c_size_t), c_size_t,
+                                  c_size_t, c_size_t, c_size_t, c_size_t, c_size_t, c_char_p, c_char_p, c_size_t, AT_START,
+                                  POINTER(c_double), POINTER(ctypes.c_ulonglong), POINTER(ctypes.c_ulonglong)]
+    dev_ptrs = (c_void_p * R_COPIES)(*[t.data_ptr() for t in dev_copies])
+    host_ptrs = (c_void_p * 1)(pinned.data_ptr())
+
     def run_overlapped(steps, inflight, to_host, warmup):
-        """`steps` whole steps, `inflight` at a time: each host thread runs whole steps on its own
-        handle (own stream, own buffers).  The same threads first run the warm-up steps and meet at a
-        barrier, so that the clock starts on a device that is idle but has not had time to drop its
-        clocks; the timed region is bracketed by CUDA events (start after that barrier and a device
-        synchronize, end after every thread has waited for its last step).
-        Returns (ms, phases, copy stats, kernel launches inside the timed region)."""
-        inflight = max(1, inflight)
-        lock, nxt, errs, copy, phases = threading.Lock(), [0], [], [0, 0], []
-        warmed, go = threading.Barrier(inflight + 1), threading.Barrier(inflight + 1)
+        """`steps` whole steps, `inflight` at a time: tools/bench_driver.c starts that many threads,
+        each running whole steps on its own handle (own stream, own buffers).  The threads first run
+        the warm-up steps and meet at a barrier, so that the clock starts on a device that is idle
+        but has not had time to drop its clocks; the timed region is bracketed by CUDA events (start
+        after that barrier and a device synchronize, end after every thread has waited for its last
+        step).  Returns (ms, phases, copy stats, kernel launches inside the timed region)."""
+        mark = {}
 
-        def one(i, phase):
-            src = pinned.data_ptr() if to_host else dev_copies[i % R_COPIES].data_ptr()
-            h, out = step(src, not to_host, to_host, phase)
-            if to_host:
-                ok = ctypes.string_at(out + len(text) - 64, 64) == text[-64:] and ctypes.string_at(out, 64) == text[:64]
-                a, b = ctypes.c_ulonglong(), ctypes.c_ulonglong()
-                L.tk_state_copy_stats(h, byref(a), byref(b))
-                copy[0], copy[1] = a.value, b.value
-                if not ok:
-                    errs.append("a step returned a wrong result")
-            L.tk_state_free(h)   # waits for the handle's stream (the emit kernel of a resident step is still queued)
+        def at_start():
+            barrier()
+            mark["launches"] = tk.state.kernel_launches()
+            mark["a"], mark["b"] = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            mark["a"].record()
+            mark["t0"] = time.perf_counter()
 
-        def work(w):
-            torch.cuda.set_device(local_rank)
-            scratch_phase, phase = (c_double * 5)(), (c_double * 5)()
-            phases.append(phase)
-            try:
-                for k in range(max(1, -(-warmup // inflight))):
-                    one(w + k * inflight, scratch_phase)
-            except BaseException as e:  # noqa: BLE001 -- reported by the caller
-                errs.append(repr(e))
-            warmed.wait()
-            go.wait()
-            while True:
-                with lock:
-                    i = nxt[0]
-                    nxt[0] += 1
-                if i >= steps or errs:
-                    return
-                try:
-                    one(i, phase)
-                except BaseException as e:  # noqa: BLE001
-                    errs.append(repr(e))
-
-        ts = [threading.Thread(target=work, args=(w,)) for w in range(inflight)]
-        for t in ts: t.start()
-        warmed.wait()
-        barrier()
-        launches0 = tk.state.kernel_launches()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        t0 = time.perf_counter()
-        go.wait()
-        for t in ts: t.join()
+        phase, h2d, d2h = (c_double * 5)(), ctypes.c_ulonglong(), ctypes.c_ulonglong()
+        rc = D.tkb_product_run(host_ptrs if to_host else dev_ptrs, 1 if to_host else R_COPIES, len(text), local_rank, 0 if to_host else 1,
+                               1 if to_host else 0, arr, lens, len(cks), args.clusters, args.clusters * args.nodes, steps, warmup,
+                               max(1, inflight), text[:64], text[-64:], len(text), AT_START(at_start), phase, byref(h2d), byref(d2h))
         torch.cuda.synchronize()
-        b.record()
-        b.synchronize()
-        wall = (time.perf_counter() - t0) * 1e3
-        launches = tk.state.kernel_launches() - launches0
-        if errs:
-            raise SystemExit("bench.py: " + errs[0])
-        ph = [sum(p[i] for p in phases) / steps for i in range(4)]
-        return max(a.elapsed_time(b), wall), ph, tuple(copy), launches
+        mark["b"].record()
+        mark["b"].synchronize()
+        wall = (time.perf_counter() - mark["t0"]) * 1e3
+        if rc:
+            raise SystemExit("bench.py: a step failed (%d): %s" % (rc, L.tk_last_error(None)))
+        launches = tk.state.kernel_launches() - mark["launches"]
+        return max(mark["a"].elapsed_time(mark["b"]), wall), [phase[i] / steps for i in range(4)], (h2d.value, d2h.value), launches
 
     inflight = args.inflight if args.inflight > 0 else max(1, min(4, (os.cpu_count() or 1) // max(1, world)))
     sampler = ClockSampler(local_rank)

@@ -237,6 +237,13 @@ TK_API unsigned long long tk_kernel_launches(void);
 /* Library/ABI version string. */
 TK_API const char *tk_version(void);
 
+/* Selects the CUDA device for the calling thread: handles the thread creates from now on bind to
+ * it (a handle binds to the device current at creation).  For callers that have no CUDA binding
+ * of their own -- a Go program driving several GPUs, one goroutine locked to a thread per device.
+ * No counterpart in the reference.  TK_ECUDA (text from tk_last_error(NULL)) if there is no such
+ * device. */
+TK_API int tk_set_device(int device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -54,6 +54,95 @@ int tkb_product_step(const void *text, size_t n, int device_text, int to_host, c
     return 0;
 }
 
+/* ---- `steps` whole steps with `inflight` documents in flight: that many threads, each running
+ * whole steps on its own handle (own stream, own buffers).  The threads first run the warm-up
+ * steps, meet at a barrier, the caller's `at_start` runs on the calling thread (bench.py records
+ * its CUDA start event there, on an idle but still warm device), and the timed steps begin.
+ * texts[i % n_texts] is the input of step i.  Returns 0, or the first failing step's code. */
+#include <pthread.h>
+
+typedef struct {
+    const void *const *texts; size_t n_texts, n; int device, device_text, to_host;
+    const char *const *cks; const size_t *ck_lens; size_t n_cks, want_clusters, want_nodes;
+    size_t steps, warmup_each; int worker;
+    pthread_barrier_t *warmed, *go;
+    size_t *next; pthread_mutex_t *mu; int *rc;
+    double phase_ms[5]; size_t out_len; unsigned long long h2d, d2h;
+    const char *expect_head, *expect_tail; size_t expect_n;
+} tkb_worker;
+
+static int tkb_one(tkb_worker *w, size_t i, double *phase) {
+    tk_state *s = NULL;
+    const char *out = NULL;
+    size_t out_len = 0;
+    int rc = tkb_product_step(w->texts[i % w->n_texts], w->n, w->device_text, w->to_host, w->cks, w->ck_lens, w->n_cks, w->want_clusters,
+                              w->want_nodes, phase, &s, &out, &out_len);
+    if (!rc && out_len != w->expect_n) rc = -1;
+    if (!rc && w->to_host && w->expect_n >= 64 &&
+        (memcmp(out, w->expect_head, 64) != 0 || memcmp(out + out_len - 64, w->expect_tail, 64) != 0)) rc = -1;
+    if (s) {
+        tk_state_copy_stats(s, &w->h2d, &w->d2h);
+        tk_state_free(s);   /* waits for the handle's stream: the emit kernel of a resident step is still queued */
+    }
+    return rc;
+}
+
+static void *tkb_worker_main(void *arg) {
+    tkb_worker *w = (tkb_worker *)arg;
+    double scratch_phase[5] = {0, 0, 0, 0, 0};
+    int rc = tk_set_device(w->device);
+    for (size_t k = 0; !rc && k < w->warmup_each; k++) rc = tkb_one(w, (size_t)w->worker + k * 64, scratch_phase);
+    pthread_barrier_wait(w->warmed);
+    pthread_barrier_wait(w->go);
+    while (!rc) {
+        pthread_mutex_lock(w->mu);
+        const size_t i = (*w->next)++;
+        const int stop = *w->rc != 0;
+        pthread_mutex_unlock(w->mu);
+        if (i >= w->steps || stop) break;
+        rc = tkb_one(w, i, w->phase_ms);
+    }
+    if (rc) { pthread_mutex_lock(w->mu); if (!*w->rc) *w->rc = rc; pthread_mutex_unlock(w->mu); }
+    return NULL;
+}
+
+int tkb_product_run(const void *const *texts, size_t n_texts, size_t n, int device, int device_text, int to_host, const char *const *cks,
+                    const size_t *ck_lens, size_t n_cks, size_t want_clusters, size_t want_nodes, size_t steps, size_t warmup,
+                    size_t inflight, const char *expect_head, const char *expect_tail, size_t expect_n, void (*at_start)(void),
+                    double *phase_ms, unsigned long long *h2d, unsigned long long *d2h) {
+    if (inflight < 1) inflight = 1;
+    if (inflight > 64) inflight = 64;
+    pthread_barrier_t warmed, go;
+    pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+    pthread_t th[64];
+    tkb_worker w[64];
+    size_t next = 0;
+    int rc = 0;
+    pthread_barrier_init(&warmed, NULL, (unsigned)inflight + 1);
+    pthread_barrier_init(&go, NULL, (unsigned)inflight + 1);
+    for (size_t t = 0; t < inflight; t++) {
+        memset(&w[t], 0, sizeof w[t]);
+        w[t].texts = texts; w[t].n_texts = n_texts; w[t].n = n; w[t].device = device; w[t].device_text = device_text; w[t].to_host = to_host;
+        w[t].cks = cks; w[t].ck_lens = ck_lens; w[t].n_cks = n_cks; w[t].want_clusters = want_clusters; w[t].want_nodes = want_nodes;
+        w[t].steps = steps; w[t].warmup_each = (warmup + inflight - 1) / inflight; if (!w[t].warmup_each) w[t].warmup_each = 1;
+        w[t].worker = (int)t; w[t].warmed = &warmed; w[t].go = &go; w[t].next = &next; w[t].mu = &mu; w[t].rc = &rc;
+        w[t].expect_head = expect_head; w[t].expect_tail = expect_tail; w[t].expect_n = expect_n;
+        pthread_create(&th[t], NULL, tkb_worker_main, &w[t]);
+    }
+    pthread_barrier_wait(&warmed);
+    if (at_start) at_start();
+    pthread_barrier_wait(&go);
+    for (size_t t = 0; t < inflight; t++) pthread_join(th[t], NULL);
+    for (int k = 0; k < 5; k++) phase_ms[k] = 0;
+    for (size_t t = 0; t < inflight; t++) {
+        for (int k = 0; k < 5; k++) phase_ms[k] += w[t].phase_ms[k];
+        if (w[t].h2d) { *h2d = w[t].h2d; *d2h = w[t].d2h; }
+    }
+    pthread_barrier_destroy(&warmed);
+    pthread_barrier_destroy(&go);
+    return rc;
+}
+
 /* ---- per-operation loops (SURVEY.md 8d, config #4 op mix; tools/op_mix.py).  Each returns the
  * seconds the loop took, or a negative number on the first failing call.  strs/lens are parallel
  * arrays; `total` calls cycle through the n entries in order. */

@@ -38,6 +38,14 @@ extern "C" {
 const char *tk_version(void) { return "libtkstate 0.1 (sm_100a)"; }
 unsigned long long tk_kernel_launches(void) { return kernel_launch_count() + parse_launch_count(); }
 
+int tk_set_device(int device) {
+    const cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) return TK_OK;
+    g_err = std::string("cuda: cudaSetDevice: ") + cudaGetErrorString(e);
+    (void)cudaGetLastError();
+    return TK_ECUDA;
+}
+
 const char *tk_last_error(tk_state *s) { return s ? s->err.c_str() : g_err.c_str(); }
 
 static int new_from(const char *name, size_t name_len, const char *raw, size_t raw_len, bool on_device, tk_state **out);

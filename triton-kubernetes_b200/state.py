@@ -30,7 +30,7 @@ SYMBOLS = [
     "tk_state_copy_stats", "tk_row_offsets_noalloc", "tk_state_host_tree_built", "tk_state_new_device",
     "tk_set_default_timing", "tk_render_record", "tk_record_struct_name", "tk_module_source", "tk_record_table",
     "tk_local_backend_new", "tk_backend_free", "tk_backend_last_error", "tk_backend_state", "tk_backend_delete_state",
-    "tk_backend_persist_state", "tk_backend_states", "tk_backend_state_terraform_config",
+    "tk_backend_persist_state", "tk_backend_states", "tk_backend_state_terraform_config", "tk_set_device",
 ]
 
 _lib = None
@@ -332,6 +332,12 @@ def NewDevice(name, device_address, length) -> State:
 
 def set_default_timing(on: bool):
     lib().tk_set_default_timing(1 if on else 0)
+
+
+def set_device(device: int):
+    """tk_set_device: the CUDA device for handles the calling thread creates from now on."""
+    if lib().tk_set_device(int(device)) != TK_OK:
+        raise StateError(TK_ECUDA, lib().tk_last_error(None).decode("utf-8", "replace"))
 
 
 def kernel_launches() -> int:
