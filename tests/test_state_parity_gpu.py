@@ -394,3 +394,41 @@ def test_wide_unsorted_object_is_rebuilt_by_several_threads(tk, oracle):
     with pytest.raises(tk.StateError) as got:
         tk.New("x", bad)
     assert str(got.value) == str(want.value) and "2e999" in str(got.value)
+
+
+def test_input_already_in_output_form_and_near_misses(tk, oracle):
+    """Text that is already json.MarshalIndent output is copied line by line after every line has
+    been checked against the tape (emit_kernel, emit_verbatim); text that only nearly is -- spaces
+    for tabs, a missing or extra blank, CRLF, blanks inside empty containers, a blank before a
+    comma -- must come out in the one true form all the same."""
+    doc = {"module": {"m%03d" % i: {"name": "n%d" % i, "list": [1, "two", {}, [], {"k": None}], "e": {}, "t": True, "s": "x y"}
+                      for i in range(300)}, "z": [], "a": -0.5e-7}
+    # -0.5e-7 is not in floatEncoder's form: that document goes through the host tree, the rest stays on the device
+    doc.pop("a")
+    pretty = oracle.New("x", json.dumps(doc).encode()).Bytes()
+    a = tk.New("x", pretty)
+    assert not a.host_tree_built and a.Bytes() == pretty
+    rng = random.Random(99)
+    lines = pretty.split(b"\n")
+    mutations = [
+        lambda l: l.replace(b"\t", b"    ", 1),                    # spaces for a tab
+        lambda l: l.replace(b'": ', b'":', 1),                     # no blank after the colon
+        lambda l: l.replace(b'": ', b'":  ', 1),                   # two blanks
+        lambda l: l.replace(b'": ', b'" : ', 1),                   # a blank before the colon
+        lambda l: l + b"\r",                                       # CRLF
+        lambda l: l.replace(b"{}", b"{ }").replace(b"[]", b"[\t]"),
+        lambda l: l[:-1] + b" ," if l.endswith(b",") else l + b" ",
+        lambda l: b"\t" + l,                                       # one tab too many
+        lambda l: l[1:] if l.startswith(b"\t") else l,             # one too few
+    ]
+    for trial in range(60):
+        ls = list(lines)
+        for _ in range(rng.choice([1, 1, 2, 5])):
+            i = rng.randrange(len(ls))
+            ls[i] = rng.choice(mutations)(ls[i])
+        raw = b"\n".join(ls)
+        s = tk.New("x", raw)
+        assert s.Bytes() == pretty, trial
+    # several lines on one line, and a line split in two
+    assert tk.New("x", pretty.replace(b",\n\t\t\t", b", ", 7)).Bytes() == pretty
+    assert tk.New("x", pretty.replace(b'": ', b'":\n ', 3)).Bytes() == pretty

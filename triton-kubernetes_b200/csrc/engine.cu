@@ -429,6 +429,7 @@ int Engine::stage_tape(const Document &doc, std::string *err) {
     if ((e = d_scratch_.reserve(scan_scratch_words((uint32_t)n) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
     tape_.n_rows = (uint32_t)n;
     tape_.arena_bytes = (uint32_t)h_arena_.n;
+    tape_.text_len = 0;
     tape_.meta = d_meta_.as<uint32_t>(); tape_.koff = d_koff_.as<uint32_t>(); tape_.klen = d_klen_.as<uint32_t>();
     tape_.voff = d_voff_.as<uint32_t>(); tape_.vlen = d_vlen_.as<uint32_t>(); tape_.arena = d_arena_.as<uint8_t>();
     staged_version_ = doc.version;
@@ -539,7 +540,7 @@ int Engine::upload_text(const char *raw, size_t n, std::string *err) {
     int rc = init(err);
     if (rc) return rc;
     if (n >= 0xfff00000ull) { *err = "document too large: the text must stay below 4 GiB"; return TK_ELIMIT; }
-    const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 32;
+    const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 64;
     cudaError_t e;
     if ((e = d_arena_.reserve(padded)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
     if (n && (e = copy_h2d(d_arena_.p, raw, n)) != cudaSuccess) return fail(e, "copy text", err);
@@ -555,7 +556,7 @@ int Engine::upload_text_device(const void *dev_raw, size_t n, std::string *err) 
     int rc = init(err);
     if (rc) return rc;
     if (n >= 0xfff00000ull) { *err = "document too large: the text must stay below 4 GiB"; return TK_ELIMIT; }
-    const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 32;
+    const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 64;
     cudaError_t e;
     if ((e = d_arena_.reserve(padded)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
     if (n && (e = cudaMemcpyAsync(d_arena_.p, dev_raw, n, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return fail(e, "copy text", err);
@@ -672,7 +673,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
         if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy decode size", err);
         if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "decode_lengths", err);
         const size_t side = (size_t)h_words_.p[0];
-        const size_t side_base = ((size_t)p1_tiles(n) * P1_TILE + 32 + 15) & ~size_t(15);
+        const size_t side_base = ((size_t)p1_tiles(n) * P1_TILE + 64 + 15) & ~size_t(15);
         if (side_base + side >= 0xfffffff0ull) { *err = "document too large: text plus decoded strings must stay below 4 GiB"; return TK_ELIMIT; }
         if ((e = d_arena_.reserve(side_base + side + 32, side_base, stream_)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
         raw = d_arena_.as<uint8_t>();
@@ -702,6 +703,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     if ((e = d_scratch_.reserve(scan_scratch_words(n_rows) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
     tape_.n_rows = n_rows;
     tape_.arena_bytes = (uint32_t)arena_used_;
+    tape_.text_len = (uint32_t)n;
     tape_.meta = rb.meta; tape_.koff = rb.koff; tape_.klen = rb.klen; tape_.voff = rb.voff; tape_.vlen = rb.vlen;
     tape_.arena = d_arena_.as<uint8_t>();
     tape_from_parse_ = true;

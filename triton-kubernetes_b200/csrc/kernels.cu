@@ -365,6 +365,71 @@ __device__ __forceinline__ void warp_copy_deferred(uint8_t *dst, const uint8_t *
     }
 }
 
+// Input that is already in output form.  A state file that this library or the reference wrote
+// is json.MarshalIndent text, so when it is loaded and serialised again, line r of the output is
+// byte for byte a stretch of the input, and the 32 lines of a warp's tile one contiguous stretch.
+// The warp copies text[ls0, ls0 + span) -- ls0 = where the first row's line would start -- into
+// its output slice (realigned to the destination's 16-byte phase) and every lane then CHECKS its
+// own line there: the tabs, the quotes, `": `, the comma and the newline by value, the key, the
+// value and the brackets by position (they are referred to in place, so "at the right place"
+// means "the right bytes").  One lane saying no sends the tile down the general path.
+__device__ __forceinline__ bool emit_verbatim(const TapeView &t, const Row &w, uint32_t o, bool valid, uint32_t lane, uint4 *staging,
+                                              uint8_t *slice, uint32_t out0, uint32_t span, uint32_t shift) {
+    const uint32_t d = w.meta >> META_DEPTH_SHIFT, kind = w.meta & 15u;
+    // text position of the first byte after the indentation, as the row's own fields give it
+    uint32_t q;
+    if (w.meta & META_HAS_KEY) q = w.koff - 1;
+    else if (kind == ROW_STR) q = w.voff - 1;
+    else if (kind == ROW_RAW) q = w.voff;
+    else q = w.vlen;   // containers: the bracket (TapeView::text_len)
+    const uint32_t ls0 = __shfl_sync(FULL, q - d, 0);
+    if (ls0 > t.text_len || span > t.text_len - ls0 || ls0 < shift) return false;
+    // text[ls0 - shift ...] -> slice[0 ...]: the text in 16-byte chunks into the input staging,
+    // then word by word into the slice with the two phases reconciled by a funnel shift
+    {
+        const uint32_t first = ls0 - shift, a0 = first & ~15u, delta = first - a0;
+        const uint32_t chunks = (delta + shift + span + 15u) >> 4;
+        if (chunks * 16u + 16u > (uint32_t)WARP_IN_BYTES) return false;
+        const uint4 *src = reinterpret_cast<const uint4 *>(t.arena + a0);
+        for (uint32_t c = lane; c <= chunks; c += 32) staging[c] = __ldg(src + c);   // one chunk more: the funnel reads a word ahead
+        __syncwarp();
+        const uint32_t *sw = reinterpret_cast<const uint32_t *>(staging) + (delta >> 2);
+        uint32_t *dw = reinterpret_cast<uint32_t *>(slice);
+        const uint32_t words = (shift + span + 3u) >> 2, sh = (delta & 3u) * 8u;
+        for (uint32_t j = lane; j < words; j += 32) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
+    }
+    __syncwarp();
+    bool ok = true;
+    if (valid) {
+        uint32_t c = shift + (o - out0);       // slice offset of this line
+        uint32_t tq = ls0 + (o - out0) + d;    // text position its first non-tab byte must have
+        ok = q == tq && d <= 64;
+        for (uint32_t i = 0; ok && i < d; i++) ok = slice[c + i] == '\t';
+        c += d;
+        if (ok && (w.meta & META_HAS_KEY)) {
+            ok = (w.meta & META_KEY_PLAIN) && slice[c] == '"' && slice[c + 1 + w.klen] == '"' && slice[c + 2 + w.klen] == ':' &&
+                 slice[c + 3 + w.klen] == ' ';
+            c += w.klen + 4;
+            tq += w.klen + 4;
+        }
+        if (ok) {
+            switch (kind) {
+            case ROW_STR:
+                ok = (w.meta & META_VAL_PLAIN) && w.voff == tq + 1 && slice[c] == '"' && slice[c + 1 + w.vlen] == '"';
+                c += w.vlen + 2;
+                break;
+            case ROW_RAW: ok = w.voff == tq; c += w.vlen; break;
+            case ROW_EMPTY_OBJ: ok = w.vlen == tq && slice[c + 1] == '}'; c += 2; break;
+            case ROW_EMPTY_ARR: ok = w.vlen == tq && slice[c + 1] == ']'; c += 2; break;
+            default: ok = w.vlen == tq; c += 1; break;   // { [ } ]
+            }
+        }
+        if (ok && (w.meta & META_COMMA)) { ok = slice[c] == ','; c++; }
+        if (ok && !(w.meta & META_LAST)) ok = slice[c] == '\n';
+    }
+    return __all_sync(FULL, ok);
+}
+
 __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const uint32_t *__restrict__ off,
                                                            uint8_t *__restrict__ out) {
     extern __shared__ uint4 emit_smem[];  // [WARPS][WARP_IN_BYTES/16] then [WARPS][WARP_OUT_BYTES/16]
@@ -380,8 +445,6 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const ui
     Row w = {0, 0, 0, 0, 0};
     uint32_t o = 0;
     if (valid) { w = load_row(t, r); o = __ldg(off + r); }
-    uint32_t base;
-    const bool staged = stage_warp_input(t, w, valid, s_in[warp], &base);
 
     const uint32_t r_end = min(r0 + 32u, t.n_rows);
     const uint32_t out0 = __ldg(off + r0), out1 = __ldg(off + r_end);  // off has n_rows + 1 entries
@@ -391,7 +454,13 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const ui
 
     uint8_t *slice = reinterpret_cast<uint8_t *>(s_out[warp]);
     Deferred dk = {0, 0, 0}, dv = {0, 0, 0};
-    if (staged && fits) {
+    uint32_t base = 0;
+    bool staged = false;
+    const bool verbatim = t.text_len != 0 && fits && emit_verbatim(t, w, o, valid, lane, s_in[warp], slice, out0, span, shift);
+    if (!verbatim) staged = stage_warp_input(t, w, valid, s_in[warp], &base);
+    if (verbatim) {
+        // the slice already holds the 32 lines
+    } else if (staged && fits) {
         // the usual case, kept apart so that every access below is a 32-bit shared-memory access:
         // arena byte x is s_src[x - base]; output byte y is slice[y - out0 + shift]
         const uint8_t *s_src = reinterpret_cast<const uint8_t *>(s_in[warp]);
@@ -582,6 +651,7 @@ extern "C" int tk_row_offsets_noalloc(const uint32_t *meta, const uint32_t *koff
     tk::TapeView t;
     t.n_rows = n_rows; t.arena_bytes = arena_bytes;
     t.meta = meta; t.koff = koff; t.klen = klen; t.voff = voff; t.vlen = vlen; t.arena = arena;
+    t.text_len = 0;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     // the array still holds the previous call's counter and status words: they must start at zero
     e = cudaMemsetAsync(scratch, 0, tk::scan_scratch_words(n_rows) * sizeof(unsigned long long), s);

@@ -1223,9 +1223,11 @@ __global__ void __launch_bounds__(TP_THREADS) rows_kernel(const uint8_t *__restr
             if (depth < 1) { res->invalid = 1; continue; }
             meta = (k == T_RBRACE ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR) | ((depth - 1) << META_DEPTH_SHIFT);
             koff = bb.match[my_b];  // the opener's bracket: key_order and the module index find its row through bb.row
+            vlen = pos[i];          // (container rows: where the bracket is in the text, see TapeView::text_len)
             bb.row[my_b] = rr;
         } else {
             if (op) {
+                vlen = pos[i];
                 if (is_closer(k1)) { meta = (k == T_LBRACE ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR); after = k2 == T_SCALAR_END ? kind[i + 3] : k2; }
                 else { meta = (k == T_LBRACE ? ROW_OPEN_OBJ : ROW_OPEN_ARR); bb.row[my_b] = rr; voff = my_b; }  // voff of an opening row: its bracket
             } else if (k == T_STR_OPEN) {

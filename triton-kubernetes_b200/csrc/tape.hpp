@@ -40,6 +40,11 @@ struct TapeView {        // pointers may be host (pinned) or device
     uint32_t arena_bytes;
     const uint32_t *meta, *koff, *klen, *voff, *vlen;
     const uint8_t *arena;  // allocation padded so that 16 bytes past arena_bytes are readable
+    // != 0: the tape came from the parser -- arena[0, text_len) IS the input text, keys and plain
+    // strings are referred to in place, and the rows of containers ({ [ } ] {} []) carry the text
+    // position of their bracket in vlen (otherwise 0).  emit_kernel uses it to recognise input that
+    // is already in output form.  0 for a tape flattened from the host tree.
+    uint32_t text_len;
 };
 
 #ifdef __CUDACC__
