@@ -391,7 +391,19 @@ __device__ __forceinline__ bool emit_verbatim(const TapeView &t, const Row &w, u
         const uint32_t chunks = (delta + shift + span + 15u) >> 4;
         if (chunks * 16u + 16u > (uint32_t)WARP_IN_BYTES) return false;
         const uint4 *src = reinterpret_cast<const uint4 *>(t.arena + a0);
-        for (uint32_t c = lane; c <= chunks; c += 32) staging[c] = __ldg(src + c);   // one chunk more: the funnel reads a word ahead
+        // (one chunk more than the span: the funnel reads a word ahead; all loads issued before any is used)
+        constexpr int ROUNDS = WARP_IN_BYTES / 16 / 32;
+        uint4 v[ROUNDS];
+#pragma unroll
+        for (int k = 0; k < ROUNDS; k++) {
+            const uint32_t c = lane + 32u * k;
+            if (c <= chunks) v[k] = __ldg(src + c);
+        }
+#pragma unroll
+        for (int k = 0; k < ROUNDS; k++) {
+            const uint32_t c = lane + 32u * k;
+            if (c <= chunks) staging[c] = v[k];
+        }
         __syncwarp();
         const uint32_t *sw = reinterpret_cast<const uint32_t *>(staging) + (delta >> 2);
         uint32_t *dw = reinterpret_cast<uint32_t *>(slice);
