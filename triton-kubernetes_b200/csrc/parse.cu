@@ -1331,14 +1331,13 @@ static cudaError_t fast_scan_grid(uint32_t *count_blocks, uint32_t *emit_blocks)
 cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, unsigned long long *scratch, ParseResult *res,
                                bool carry_protocol, int stage, cudaStream_t s) {
     cudaError_t e;
-    if (stage == 0) {
-        if ((e = cudaMemsetAsync(res, 0, sizeof(ParseResult), s)) != cudaSuccess) return e;
-        if ((e = cudaMemsetAsync(tb.decode_bits, 0, ((size_t)tb.cap + 31) / 32 * 4 + 4, s)) != cudaSuccess) return e;
-    }
-    if (n == 0) return cudaSuccess;
+    const size_t decode_words = ((size_t)tb.cap + 31) / 32 + 1;
+    if (stage == 0 && (e = cudaMemsetAsync(res, 0, sizeof(ParseResult), s)) != cudaSuccess) return e;
+    if (n == 0) return stage == 0 ? cudaMemsetAsync(tb.decode_bits, 0, decode_words * 4, s) : cudaSuccess;
     const uint32_t n_tiles = p1_tiles(n);
     if (carry_protocol) {
         if (stage != 0) return cudaSuccess;
+        if ((e = cudaMemsetAsync(tb.decode_bits, 0, decode_words * 4, s)) != cudaSuccess) return e;
         if ((e = cudaMemsetAsync(scratch, 0, p1_scratch_words(n) * 8, s)) != cudaSuccess) return e;
         scan_tokens_kernel<<<n_tiles, P1_THREADS, 0, s>>>(raw, (u64)n, tb, scratch, res);
         g_parse_launches++;
@@ -1349,7 +1348,8 @@ cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, un
     uint32_t *tile_agg = reinterpret_cast<uint32_t *>(scratch + 4 + n_tiles);
     uint32_t g_count = 0, g_emit = 0;
     if ((e = fast_scan_grid(&g_count, &g_emit)) != cudaSuccess) return e;
-    if (stage == 0) scan_count_kernel<<<std::min(n_tiles, g_count), P1_THREADS, 0, s>>>(raw, n_tiles, tile_agg, res);
+    if (stage == 0)   // (also clears the "needs decoding" bitmap the emit kernel sets bits in)
+        scan_count_kernel<<<std::min(n_tiles, g_count), P1_THREADS, 0, s>>>(raw, n_tiles, tile_agg, tb.decode_bits, (uint32_t)decode_words, res);
     else if (stage == 1) scan_prefix_kernel<<<1, PFX_THREADS, 0, s>>>(tile_agg, n_tiles, tile_pre, res);
     else scan_emit_kernel<<<std::min(n_tiles, g_emit), P1_THREADS, 0, s>>>(raw, (u64)n, n_tiles, tb, tile_pre, res);
     g_parse_launches++;

@@ -133,11 +133,13 @@ __device__ __forceinline__ void load_tables(uint32_t *s_lut, uint8_t *s_klut) {
 
 // ---- count: one packed triple per tile
 __global__ void __launch_bounds__(P1_THREADS) scan_count_kernel(const uint8_t *__restrict__ raw, uint32_t n_tiles, uint32_t *__restrict__ tile_agg,
-                                                               ParseResult *res) {
+                                                               uint32_t *__restrict__ decode_bits, uint32_t decode_words, ParseResult *res) {
     __shared__ uint32_t s_lut[4 * 256];
     __shared__ uint8_t s_klut[256];
     __shared__ uint32_t s_warp_agg[2][P1_THREADS / 32];
     load_tables(s_lut, s_klut);
+    // the "needs decoding" bitmap, for the emit kernel that follows on the stream
+    for (uint32_t w = blockIdx.x * P1_THREADS + threadIdx.x; w < decode_words; w += gridDim.x * P1_THREADS) decode_bits[w] = 0u;
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t it = 0;
