@@ -8,6 +8,11 @@
 // Rows are stored as five parallel u32 arrays (struct of arrays, so a warp reads each field
 // with one coalesced request) plus one byte arena that holds the UNESCAPED key and string
 // bytes.  Escaping, quoting, indentation and separators are produced on the GPU.
+//
+// A tape the parser built (TapeView::text_len != 0) refers to the input text in place and uses the
+// fields a container row has no use for: voff of an opening row is the index of its bracket
+// (BracketBuffers), koff of a closing row the bracket of its opener, vlen of any container row the
+// text position of the bracket.  A tape flattened from the host tree has zeros there.
 #pragma once
 #include <cstdint>
 
