@@ -13,16 +13,22 @@ Python call overhead and the GIL are not measured as if they were the library.
          host->device copy, kernels, and the device->host copy of the result text, all inside the
          timed region
 
-Both are whole-job throughput: K steps with `--inflight` documents in flight per GPU (default 4) --
+  e2e_pageable  e2e as the reference's own callers would drive it (backend/local/backend.go:60-65,94):
+         the text in plain malloc'd memory, the result copied out of the library's buffer
+
+All are whole-job throughput: K steps with `--inflight` documents in flight per GPU (default 4) --
 that many host threads each run whole steps on their own handle, i.e. their own stream and
 buffers, so one document's copies and host-side waits overlap another's kernels.  The path shards
-by document and the CPU arm runs one document per host thread the same way.  The
-timed region is bracketed by CUDA events recorded on an idle device before the first step and
-after every thread has waited for its last one.  The latency of a single document (one in flight;
-for `value` with L2 flushed before every step) is reported beside it in config.latency_ms_per_step,
-and the per-kernel times for the roofline come from that serial, L2-flushed run.
+by document and the CPU arm runs one document per host thread the same way.  After
+the warm-up the block of K steps is run BLOCKS (7) times back to back; every block is bracketed by
+CUDA events recorded on an idle device before its first step and after every thread has waited for
+its last one, and the reported number is the MEDIAN block (min and max beside it in
+config.blocks).  The latency of a single document (one in flight; for `value` with L2 flushed
+before every step) is reported in config.latency_ms_per_step, and the per-kernel times for the
+roofline come from that serial, L2-flushed run.
   --impl reference   the CPU oracle (oracle/tk_oracle.c, a restatement of the reference's Go
-         code; the Go toolchain is absent) on every host core, same step, same metric
+         code; the Go toolchain is absent) on every host core, same step, same metric.  That
+         process loads the oracle and tools/oracle_driver.c only, never the product library.
 
 Under torchrun (N > 1) every rank runs the step on its own document on its own GPU (the path
 shards by document: one manager per worker, no exchange step, so no collective in the data
@@ -44,6 +50,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 OPS_PER_STEP = 1003
+BLOCKS = 7   # timed blocks of --steps steps each; the median block is the reported one
 WORKLOAD = ("config #4: synthetic state document, 1000 clusters x 100 nodes (62,177,405 B tab-indented); "
             "step = New + Clusters + 1000 x Nodes(ck) + Bytes = 1003 state.State ops")
 
@@ -65,20 +72,42 @@ def parse_args():
 
 # ------------------------------------------------------------------------------------ driver
 
-def driver():
-    """tools/libtkbench.so: built on first use (gcc is part of the image, here and on the GPU box)."""
-    src, lib = os.path.join(ROOT, "tools", "bench_driver.c"), os.path.join(ROOT, "tools", "libtkbench.so")
+def _build(src, lib, extra=()):
     if not os.path.exists(lib) or os.path.getmtime(lib) < os.path.getmtime(src):
-        subprocess.check_call(["gcc", "-O2", "-fPIC", "-shared", "-pthread", "-I" + os.path.join(ROOT, "include"), "-o", lib, src,
-                               "-L" + os.path.join(ROOT, "triton-kubernetes_b200"), "-ltkstate",
-                               "-Wl,-rpath," + os.path.join(ROOT, "triton-kubernetes_b200")])
+        subprocess.check_call(["gcc", "-O2", "-fPIC", "-shared", "-pthread", "-I" + os.path.join(ROOT, "include"), "-o", lib, src] + list(extra))
+    return lib
+
+
+def driver():
+    """tools/libtkbench.so, the step loop over the product's C ABI: built on first use (gcc is part
+    of the image, here and on the GPU box)."""
+    pkg = os.path.join(ROOT, "triton-kubernetes_b200")
+    lib = _build(os.path.join(ROOT, "tools", "bench_driver.c"), os.path.join(ROOT, "tools", "libtkbench.so"),
+                 ["-L" + pkg, "-ltkstate", "-Wl,-rpath," + pkg])
     importlib.import_module("triton-kubernetes_b200").state.lib()   # libtkstate first, by full path
     D = ctypes.CDLL(lib)
     D.tkb_product_step.argtypes = [c_void_p, c_size_t, c_int, c_int, POINTER(c_char_p), POINTER(c_size_t), c_size_t, c_size_t,
                                    c_size_t, POINTER(c_double), POINTER(c_void_p), POINTER(c_void_p), POINTER(c_size_t)]
+    return D
+
+
+def oracle_driver():
+    """tools/libtkbench_oracle.so, the same loops over the CPU oracle through function pointers.
+    Links nothing of this repository: the reference arm's process never maps libtkstate.so."""
+    D = ctypes.CDLL(_build(os.path.join(ROOT, "tools", "oracle_driver.c"), os.path.join(ROOT, "tools", "libtkbench_oracle.so")))
     D.tkb_oracle_step.argtypes = [POINTER(c_void_p), c_char_p, c_size_t, POINTER(c_char_p), POINTER(c_size_t), c_size_t, c_size_t,
                                   c_size_t, c_size_t]
     return D
+
+
+def load_synth():
+    """triton-kubernetes_b200/synth.py by file path: the document generator is plain Python, and the
+    reference arm must not import the product package."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("tk_synth", os.path.join(ROOT, "triton-kubernetes_b200", "synth.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
 
 
 def key_arrays(cks):
@@ -90,7 +119,7 @@ def key_arrays(cks):
 # ------------------------------------------------------------------------------------ clocks
 
 class ClockSampler:
-    """nvidia-smi clocks and throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks and throttle reasons sampled every 100 ms from before the first timed block to after the last."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -101,7 +130,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
@@ -137,7 +166,7 @@ class OracleArm:
         from oracle import oracle as O
         O.build()
         L = O.lib()
-        self.D = driver()
+        self.D = oracle_driver()
         names = ["ora_new", "ora_free", "ora_free_buf", "ora_clusters", "ora_nodes", "ora_bytes"]
         self.fns = (c_void_p * len(names))(*[ctypes.cast(getattr(L, n), c_void_p).value for n in names])
         self.text, self.cks, self.clusters, self.nodes = text, cks, clusters, nodes
@@ -170,7 +199,7 @@ class OracleArm:
 
 
 def oracle_text(args):
-    synth = importlib.import_module("triton-kubernetes_b200.synth")
+    synth = load_synth()
     from oracle import oracle as O
     O.build()
     return O.New("bench", synth.document(args.clusters, args.nodes)).Bytes()
@@ -179,7 +208,7 @@ def oracle_text(args):
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    synth = importlib.import_module("triton-kubernetes_b200.synth")
+    synth = load_synth()
     text = oracle_text(args)
     cks = [synth.cluster_key(c).encode() for c in range(args.clusters)]
     arm = OracleArm(text, cks, args.clusters, args.nodes)
@@ -283,57 +312,87 @@ def run_ours(args, rank, local_rank, world):
         L.tk_set_default_timing(0)
         return total, stats
 
-    AT_START = ctypes.CFUNCTYPE(None)
-    D.tkb_product_run.argtypes = [POINTER(c_void_p), c_size_t, c_size_t, c_int, c_int, c_int, POINTER(c_char_p), POINTER(c_size_t), c_size_t,
-                                  c_size_t, c_size_t, c_size_t, c_size_t, c_size_t, c_char_p, c_char_p, c_size_t, AT_START,
-                                  POINTER(c_double), POINTER(ctypes.c_ulonglong), POINTER(ctypes.c_ulonglong)]
+    AT_BLOCK = ctypes.CFUNCTYPE(None, c_int)
+    D.tkb_product_run.argtypes = [POINTER(c_void_p), c_size_t, c_size_t, c_int, c_int, c_int, c_int, POINTER(c_char_p), POINTER(c_size_t),
+                                  c_size_t, c_size_t, c_size_t, c_size_t, c_size_t, c_size_t, c_size_t, c_char_p, c_char_p, c_size_t,
+                                  AT_BLOCK, AT_BLOCK, POINTER(c_double), POINTER(ctypes.c_ulonglong), POINTER(ctypes.c_ulonglong)]
     dev_ptrs = (c_void_p * R_COPIES)(*[t.data_ptr() for t in dev_copies])
     host_ptrs = (c_void_p * 1)(pinned.data_ptr())
+    # what a Go caller holds: the text in ordinary heap memory (ioutil.ReadFile's slice), not pinned
+    libc = ctypes.CDLL(None)
+    libc.malloc.restype, libc.malloc.argtypes = c_void_p, [c_size_t]
+    heap_text = libc.malloc(len(text))
+    ctypes.memmove(heap_text, text, len(text))
+    heap_ptrs = (c_void_p * 1)(heap_text)
 
-    def run_overlapped(steps, inflight, to_host, warmup):
-        """`steps` whole steps, `inflight` at a time: tools/bench_driver.c starts that many threads,
-        each running whole steps on its own handle (own stream, own buffers).  The threads first run
-        the warm-up steps and meet at a barrier, so that the clock starts on a device that is idle
-        but has not had time to drop its clocks; the timed region is bracketed by CUDA events (start
-        after that barrier and a device synchronize, end after every thread has waited for its last
-        step).  Returns (ms, phases, copy stats, kernel launches inside the timed region)."""
-        mark = {}
+    def run_overlapped(steps, inflight, mode, warmup, blocks=BLOCKS):
+        """`blocks` timed blocks of `steps` whole steps, `inflight` at a time: tools/bench_driver.c starts
+        that many threads, each running whole steps on its own handle (own stream, own buffers).  The
+        threads first run the warm-up steps; before every block they meet at a barrier, so that the
+        clock starts on a device that is idle but has not had time to drop its clocks; every block
+        is bracketed by CUDA events (start after that barrier and a device synchronize, end after
+        every thread has waited for its last step and another synchronize).
+        mode: "resident" (device text in, device text out), "pinned" or "pageable" (host text in and out).
+        Returns (per-block ms, per-step phases, copy stats, kernel launches of one block)."""
+        marks = [dict() for _ in range(blocks)]
 
-        def at_start():
+        def at_start(b):
             barrier()
-            mark["launches"] = tk.state.kernel_launches()
-            mark["a"], mark["b"] = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            mark["a"].record()
-            mark["t0"] = time.perf_counter()
+            m = marks[b]
+            m["launches"] = tk.state.kernel_launches()
+            m["a"], m["b"] = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            m["a"].record()
+            m["t0"] = time.perf_counter()
 
+        def at_end(b):
+            m = marks[b]
+            torch.cuda.synchronize()
+            m["b"].record()
+            m["b"].synchronize()
+            m["wall"] = (time.perf_counter() - m["t0"]) * 1e3
+            m["n_launches"] = tk.state.kernel_launches() - m["launches"]
+
+        to_host = mode != "resident"
+        ptrs, n_ptrs = {"resident": (dev_ptrs, R_COPIES), "pinned": (host_ptrs, 1), "pageable": (heap_ptrs, 1)}[mode]
         phase, h2d, d2h = (c_double * 5)(), ctypes.c_ulonglong(), ctypes.c_ulonglong()
-        rc = D.tkb_product_run(host_ptrs if to_host else dev_ptrs, 1 if to_host else R_COPIES, len(text), local_rank, 0 if to_host else 1,
-                               1 if to_host else 0, arr, lens, len(cks), args.clusters, args.clusters * args.nodes, steps, warmup,
-                               max(1, inflight), text[:64], text[-64:], len(text), AT_START(at_start), phase, byref(h2d), byref(d2h))
-        torch.cuda.synchronize()
-        mark["b"].record()
-        mark["b"].synchronize()
-        wall = (time.perf_counter() - mark["t0"]) * 1e3
+        cb_a, cb_b = AT_BLOCK(at_start), AT_BLOCK(at_end)
+        rc = D.tkb_product_run(ptrs, n_ptrs, len(text), local_rank, 0 if to_host else 1, 1 if to_host else 0,
+                               1 if mode == "pageable" else 0, arr, lens, len(cks), args.clusters, args.clusters * args.nodes, steps,
+                               blocks, warmup, max(1, inflight), text[:64], text[-64:], len(text), cb_a, cb_b, phase, byref(h2d), byref(d2h))
         if rc:
             raise SystemExit("bench.py: a step failed (%d): %s" % (rc, L.tk_last_error(None)))
-        launches = tk.state.kernel_launches() - mark["launches"]
-        return max(mark["a"].elapsed_time(mark["b"]), wall), [phase[i] / steps for i in range(4)], (h2d.value, d2h.value), launches
+        ms = [max(m["a"].elapsed_time(m["b"]), m["wall"]) for m in marks]
+        return ms, [phase[i] / (steps * blocks) for i in range(4)], (h2d.value, d2h.value), marks[len(marks) // 2]["n_launches"]
+
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor(ms, device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return t.tolist()
+        return list(ms)
+
+    def spread(ms, steps):
+        per = sorted(x / steps for x in ms)
+        return {"median": statistics.median(per), "min": per[0], "max": per[-1], "blocks": len(per)}
 
     inflight = args.inflight if args.inflight > 0 else max(1, min(4, (os.cpu_count() or 1) // max(1, world)))
     sampler = ClockSampler(local_rank)
     sampler.start()
     # ---- value: text resident in HBM, result left in HBM
-    ms_value, _, _, launches = run_overlapped(args.steps, inflight, False, args.warmup)
+    ms_value, _, _, launches = run_overlapped(args.steps, inflight, "resident", args.warmup)
     barrier()
-    ms_serial, _ = timed_resident(min(args.steps, 10), per_kernel=False)
-    ms_serial /= min(args.steps, 10)
+    n_serial = min(args.steps, 10)
+    ms_serial, _ = timed_resident(n_serial, per_kernel=False)
+    ms_serial /= n_serial
 
-    # ---- e2e: pinned host text in, host text out
-    ms_e2e, ph, copy_stats, _ = run_overlapped(args.steps, inflight, True, args.warmup)
+    # ---- e2e: pinned host text in, host text out; and the same with pageable buffers on both sides
+    ms_e2e, ph, copy_stats, _ = run_overlapped(args.steps, inflight, "pinned", args.warmup)
     phase_ms = {k: ph[i] for i, k in enumerate(("new", "clusters", "nodes_x%d" % len(cks), "bytes"))}
     barrier()
-    ms_e2e_serial, _, _, _ = run_overlapped(min(args.steps, 10), 1, True, 1)
-    ms_e2e_serial /= min(args.steps, 10)
+    ms_page, ph_page, _, _ = run_overlapped(args.steps, inflight, "pageable", args.warmup)
+    barrier()
+    ms_e2e_serial, _, _, _ = run_overlapped(n_serial, 1, "pinned", 1, blocks=1)
+    ms_e2e_serial = ms_e2e_serial[0] / n_serial
     clocks = sampler.stop()
 
     # ---- per-kernel device times for the roofline (the same steps again, events around every launch)
@@ -344,7 +403,8 @@ def run_ours(args, rank, local_rank, world):
             kern[name] = {"launches_per_step": st["timed"] / args.steps, "avg_us": st["ms"] / st["timed"] * 1e3,
                           "ms_per_step": st["ms"] / args.steps}
     # algorithmic bytes per launch: New = input length, Bytes = output length
-    algo = {"scan_count_kernel": len(text), "scan_emit_kernel": len(text), "emit_kernel": len(text), "row_offsets_kernel": len(text)}
+    algo = {"scan_count_kernel": len(text), "scan_emit_kernel": len(text), "scan_kernel (fused)": len(text), "emit_kernel": len(text),
+            "row_offsets_kernel": len(text)}
     for k, v in kern.items():
         if k in algo:
             v["algorithmic_bytes"] = algo[k]
@@ -361,22 +421,34 @@ def run_ours(args, rank, local_rank, world):
             traffic, traffic_src = k["dram_read_bytes"] + k["dram_write_bytes"], os.path.relpath(newest, ROOT)
     except (IndexError, OSError, ValueError, KeyError):
         pass
+    # the whole step against the same peak: New reads the text once, Bytes writes it once, the module
+    # index is the key bytes + 4 B per key -- over the sum of all kernel times of a step
+    key_bytes = sum(len(synth.cluster_key(c)) for c in range(args.clusters)) + len("cluster-manager") + \
+        sum(len(synth.node_key(c, i)) for c in range(args.clusters) for i in range(1, args.nodes + 1))
+    n_keys = 1 + args.clusters * (1 + args.nodes)
+    step_bytes = 2 * len(text) + key_bytes + 4 * n_keys
+    kernel_ms = sum(v["ms_per_step"] for v in kern.values())
     roofline = {"kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo[dominant], "avg_launch_us": kern[dominant]["avg_us"],
-                "kernel_ms_per_step_total": sum(v["ms_per_step"] for v in kern.values()), "kernels": kern}
+                "kernel_ms_per_step_total": kernel_ms, "step_algorithmic_bytes": step_bytes,
+                "step_frac": step_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak if kernel_ms else None,
+                "step_frac_serial_latency": step_bytes / (ms_serial * 1e-3) / 1e9 / hbm_peak,
+                "value_serial_l2_flushed_ms": ms_serial, "kernels": kern}
 
-    # ---- max over ranks
-    if world > 1:
-        t = torch.tensor([ms_value, ms_e2e], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_value, ms_e2e = t.tolist()
+    # ---- max over ranks, block by block; the median block is the reported one
+    ms_value, ms_e2e, ms_page = max_over_ranks(ms_value), max_over_ranks(ms_e2e), max_over_ranks(ms_page)
     if rank == 0:
+        sv, se, sp = spread(ms_value, args.steps), spread(ms_e2e, args.steps), spread(ms_page, args.steps)
+        ops = lambda ms_step: world * OPS_PER_STEP / (ms_step * 1e-3)
         line = {
-            "metric": "state.State ops/sec", "value": world * OPS_PER_STEP * args.steps / (ms_value * 1e-3), "unit": "ops/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_value / args.steps,
+            "metric": "state.State ops/sec", "value": ops(sv["median"]), "unit": "ops/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sv["median"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": WORKLOAD, "documents_in_flight": inflight,
+                       "blocks": {"note": "the block of --steps steps is timed %d times back to back after the warm-up; value / e2e are the "
+                                          "median block, ms per step" % BLOCKS,
+                                  "value": sv, "e2e": se, "e2e_pageable": sp},
                        "l2": ("every step reads one of %d device copies of the text in turn and streams about 400 MB of its own "
                               "buffers: far more than the 126 MB L2 between two uses of anything" % R_COPIES) if inflight > 1 else
                              "inputs rotate over %d device copies (249 MB > L2); the serial latency run flushes L2 (256 MiB write) "
@@ -384,11 +456,17 @@ def run_ours(args, rank, local_rank, world):
                        "latency_ms_per_step": {"value_serial_l2_flushed": ms_serial, "e2e_serial": ms_e2e_serial},
                        "value_covers": "the whole step with the text already in HBM and the result left in HBM "
                                        "(the module index is copied to the host once per step: Clusters/Nodes look it up there)",
+                       "e2e_variants": {"pinned": {"value": ops(se["median"]), "ms_per_step": se["median"],
+                                                   "what": "caller's text in pinned host memory; result read in place from the handle's pinned buffer"},
+                                        "pageable": {"value": ops(sp["median"]), "ms_per_step": sp["median"],
+                                                     "what": "caller's text in malloc'd memory (ioutil.ReadFile's slice, backend/local/backend.go:60-65); "
+                                                             "result memcpy'd out of the handle's buffer (C.GoBytes, :94)",
+                                                     "phase_ms": {k: ph_page[i] for i, k in enumerate(("new", "clusters", "nodes", "bytes"))}}},
                        "driver": "tools/bench_driver.c (the step is a compiled loop over the C ABI)",
                        "clusters": args.clusters, "nodes_per_cluster": args.nodes, "document_bytes": len(text)},
-            "e2e": {"value": world * OPS_PER_STEP * args.steps / (ms_e2e * 1e-3), "unit": "ops/s",
-                    "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": copy_stats[0], "d2h_bytes_per_step": copy_stats[1],
-                    "phase_ms": phase_ms},
+            "e2e": {"value": ops(se["median"]), "unit": "ops/s",
+                    "ms_per_step": se["median"], "h2d_bytes_per_step": copy_stats[0], "d2h_bytes_per_step": copy_stats[1],
+                    "phase_ms": phase_ms, "pageable": {"value": ops(sp["median"]), "ms_per_step": sp["median"]}},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
         }
         if world == 1:
@@ -399,6 +477,8 @@ def run_ours(args, rank, local_rank, world):
                                     "sample": "%d full passes of the %d-byte document in %.1f s (oracle/tk_oracle.c, gcc -O2, one thread)"
                                               % (steps, len(text), dt)}
         print(json.dumps(line), flush=True)
+    libc.free.argtypes = [c_void_p]
+    libc.free(heap_text)
     if world > 1:
         dist.destroy_process_group()
 

@@ -6,7 +6,8 @@
  * type called directly from create/, destroy/, get/, shell/ and backend/.  This header is the
  * boundary a maintainer would bind with cgo to swap that type's body for this library; each
  * entry point cites the reference method it replaces (paths relative to the reference root).
- * INTEGRATION.md shows the cgo stub.
+ * INTEGRATION.md shows the cgo stub.  The measurement hooks bench.py uses (per-kernel timing,
+ * copy and launch counters) are not part of the drop-in surface: they live in tk_state_bench.h.
  *
  * Conventions
  *   - Every function returns TK_OK (0) or a TK_E* code; the Go error text (err.Error()) of the
@@ -177,22 +178,6 @@ TK_API int tk_state_stage(tk_state *s);
  * handle.  Runs only the kernels (the document must have been staged). */
 TK_API int tk_state_bytes_device(tk_state *s, const void **dev_out, size_t *out_len);
 
-/* The classification step of Clusters()/Nodes() alone: matching module keys are counted and
- * their indices left in device memory; no host copy of the pairs is built. */
-TK_API int tk_state_prefix_count_device(tk_state *s, const char *prefix, size_t prefix_len, size_t *count);
-
-/* Measurement hooks for bench.py.  With timing enabled every kernel launch on this handle is
- * bracketed by CUDA events on the handle's stream; tk_state_kernel_stats synchronises the stream
- * and reports, for kernel number `kind` (0 .. until it returns TK_EARG), its name, the summed
- * device time of the launches made while timing was on, how many those were, and all launches. */
-TK_API int tk_state_timing(tk_state *s, int enable);
-/* Handles created after this call start with timing on (or off): lets state.New itself be timed. */
-TK_API int tk_set_default_timing(int enable);
-TK_API int tk_state_kernel_stats(tk_state *s, int kind, const char **name, double *ms,
-                                 unsigned long long *timed_launches, unsigned long long *launches);
-/* Bytes this handle has copied host->device and device->host so far. */
-TK_API int tk_state_copy_stats(tk_state *s, unsigned long long *h2d_bytes, unsigned long long *d2h_bytes);
-
 /* Allocation-free line-offset pass.  (No counterpart in the reference: this entry point exists
  * only on the GPU side of the boundary.)
  *
@@ -230,9 +215,6 @@ TK_API int tk_state_host_tree_built(tk_state *s);
 
 /* The handle's CUDA stream (a cudaStream_t), so a caller can time or order work on it. */
 TK_API void *tk_state_stream(tk_state *s);
-
-/* Number of kernels this library has launched in this process (for bench.py's gpu_launches). */
-TK_API unsigned long long tk_kernel_launches(void);
 
 /* Library/ABI version string. */
 TK_API const char *tk_version(void);

@@ -14,7 +14,9 @@ class LocalBackend:
 
     def State(self, name):
         path = os.path.join(self.root, name, "main.tf.json")
-        if not os.path.exists(path):
+        try:
+            os.stat(path)
+        except FileNotFoundError:                                                         # os.IsNotExist: ENOENT only
             return O.New(name, b"{}")                                                     # :51-55
         return O.New(name, open(path, "rb").read())                                      # :60-65
 

@@ -1,5 +1,5 @@
-"""CPU-side checks of the product library: it loads, exports every symbol include/tk_state.h
-declares, its host logic (path operations, key parts, hostnames) matches the oracle, and the
+"""CPU-side checks of the product library: it loads, exports every symbol include/*.h
+declare, its host logic (path operations, key parts, hostnames) matches the oracle, and the
 bulk operations refuse to run without a GPU instead of falling back."""
 import os
 import random
@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def header_symbols():
-    text = open(os.path.join(ROOT, "include", "tk_state.h")).read()
+    text = "".join(open(os.path.join(ROOT, "include", h)).read() for h in sorted(os.listdir(os.path.join(ROOT, "include"))) if h.endswith(".h"))
     return re.findall(r"TK_API\s+[\w\s\*]+?\b(tk_\w+)\s*\(", text)
 
 

@@ -26,7 +26,7 @@ def test_kernels_really_launch(tk):
     before = tk.state.kernel_launches()
     s = tk.New("x", b'{"module":{"cluster_a_b":{"name":"b"}}}')
     s.Bytes(); s.Clusters(); s.Nodes("cluster_a_b")
-    assert tk.state.kernel_launches() - before >= 4   # row_offsets + emit + 2 x prefix_match
+    assert tk.state.kernel_launches() - before >= 4   # the parse, row_offsets + emit, the module index
 
 
 def test_new_keeps_canonical_documents_on_the_device(tk, oracle):
@@ -432,3 +432,53 @@ def test_input_already_in_output_form_and_near_misses(tk, oracle):
     # several lines on one line, and a line split in two
     assert tk.New("x", pretty.replace(b",\n\t\t\t", b", ", 7)).Bytes() == pretty
     assert tk.New("x", pretty.replace(b'": ', b'":\n ', 3)).Bytes() == pretty
+
+
+# ---- several devices / several threads in one process (tk_set_device, include/tk_state.h)
+
+def _new_bytes_on(tk, oracle, device, raw, out, slot):
+    """What a Go program does per goroutine locked to a thread: pick the device, then use handles."""
+    try:
+        assert tk.state.lib().tk_set_device(device) == 0
+        want = oracle.New("x", raw).Bytes()
+        for _ in range(3):
+            s = tk.New("x", raw)
+            assert s.Bytes() == want
+            assert dict(s.Clusters()) == dict(oracle.New("x", raw).Clusters())
+            s.close()
+        out[slot] = True
+    except BaseException as e:   # reported by the test thread
+        out[slot] = e
+
+
+def test_set_device_from_two_threads_on_one_device(tk, oracle):
+    """Two host threads select device 0 and run New + Clusters + Bytes at the same time: the per-device
+    set-up of the kernels (opt-in shared memory of emit_kernel, the resident grid of the scans) is
+    entered concurrently."""
+    import threading
+    raws = [oracle.New("x", synth.document(7, 5)).Bytes(), oracle.New("x", synth.document(3, 9)).Bytes()]
+    out = [None, None]
+    ts = [threading.Thread(target=_new_bytes_on, args=(tk, oracle, 0, raws[i], out, i)) for i in range(2)]
+    for t in ts: t.start()
+    for t in ts: t.join()
+    assert out == [True, True], out
+
+
+def test_handles_on_two_devices_in_one_process(tk, oracle):
+    """Device 1 after device 0 in the same process: function attributes are per device, so the second
+    device needs its own opt-in before emit_kernel can launch there (one process per GPU, the way
+    torchrun runs bench.py, never sees this)."""
+    import threading
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    raw = oracle.New("x", synth.document(9, 6)).Bytes()
+    out = [None, None]
+    _new_bytes_on(tk, oracle, 0, raw, out, 0)
+    _new_bytes_on(tk, oracle, 1, raw, out, 1)
+    assert out == [True, True], out
+    ts = [threading.Thread(target=_new_bytes_on, args=(tk, oracle, d, raw, out, d)) for d in range(2)]
+    for t in ts: t.start()
+    for t in ts: t.join()
+    assert tk.state.lib().tk_set_device(0) == 0
+    assert out == [True, True], out

@@ -3,8 +3,9 @@
  * bench.py drives the library from Python; a Python-level loop of 1,000 Nodes() calls costs
  * ~3 us of ctypes overhead per call, which would be measured as if it were the library.  This
  * driver runs one whole step (New -> Clusters -> Nodes(ck) for every cluster key -> Bytes) in C,
- * for the product (through include/tk_state.h) and for the CPU oracle (through function pointers
- * bench.py hands in, so that nothing here links the oracle).  Bench infrastructure, not product.
+ * for the product, through include/tk_state.h.  The same loops over the CPU oracle live in
+ * tools/oracle_driver.c, a library of its own, so that the process that times the reference arm
+ * never maps libtkstate.so.  Bench infrastructure, not product.
  */
 #define _GNU_SOURCE
 #include <stddef.h>
@@ -13,6 +14,7 @@
 #include <time.h>
 
 #include "tk_state.h"
+#include "tk_state_bench.h"
 
 static double now_ms(void) {
     struct timespec t;
@@ -54,21 +56,29 @@ int tkb_product_step(const void *text, size_t n, int device_text, int to_host, c
     return 0;
 }
 
-/* ---- `steps` whole steps with `inflight` documents in flight: that many threads, each running
- * whole steps on its own handle (own stream, own buffers).  The threads first run the warm-up
- * steps, meet at a barrier, the caller's `at_start` runs on the calling thread (bench.py records
- * its CUDA start event there, on an idle but still warm device), and the timed steps begin.
- * texts[i % n_texts] is the input of step i.  Returns 0, or the first failing step's code. */
+/* ---- `blocks` timed blocks of `steps` whole steps each, with `inflight` documents in flight: that
+ * many threads, each running whole steps on its own handle (own stream, own buffers).  The threads
+ * first run the warm-up steps; then, for every block, they meet at a barrier, the caller's
+ * `at_start(block)` runs on the calling thread (bench.py synchronises the device and records its
+ * CUDA start event there, on an idle but still warm device), the steps of the block are handed out
+ * from a shared counter, and when every thread has finished its last one `at_end(block)` runs.
+ * texts[i % n_texts] is the input of step i.
+ * pageable != 0 (host text only): the text is what a Go caller holds -- plain malloc'd memory, not
+ * pinned -- and the result of Bytes() is copied out of the handle's buffer into the worker's own
+ * malloc'd buffer, as C.GoBytes does.
+ * Returns 0, or the first failing step's code. */
 #include <pthread.h>
+#include <stdlib.h>
 
 typedef struct {
-    const void *const *texts; size_t n_texts, n; int device, device_text, to_host;
+    const void *const *texts; size_t n_texts, n; int device, device_text, to_host, pageable;
     const char *const *cks; const size_t *ck_lens; size_t n_cks, want_clusters, want_nodes;
-    size_t steps, warmup_each; int worker;
-    pthread_barrier_t *warmed, *go;
+    size_t steps, blocks, warmup_each; int worker;
+    pthread_barrier_t *go, *done;
     size_t *next; pthread_mutex_t *mu; int *rc;
     double phase_ms[5]; size_t out_len; unsigned long long h2d, d2h;
     const char *expect_head, *expect_tail; size_t expect_n;
+    char *copy_out; size_t copy_cap;
 } tkb_worker;
 
 static int tkb_one(tkb_worker *w, size_t i, double *phase) {
@@ -78,6 +88,11 @@ static int tkb_one(tkb_worker *w, size_t i, double *phase) {
     int rc = tkb_product_step(w->texts[i % w->n_texts], w->n, w->device_text, w->to_host, w->cks, w->ck_lens, w->n_cks, w->want_clusters,
                               w->want_nodes, phase, &s, &out, &out_len);
     if (!rc && out_len != w->expect_n) rc = -1;
+    if (!rc && w->to_host && w->pageable) {
+        if (w->copy_cap < out_len) { free(w->copy_out); w->copy_out = (char *)malloc(out_len ? out_len : 1); w->copy_cap = out_len; }
+        if (!w->copy_out) rc = -3;
+        else { memcpy(w->copy_out, out, out_len); out = w->copy_out; }
+    }
     if (!rc && w->to_host && w->expect_n >= 64 &&
         (memcmp(out, w->expect_head, 64) != 0 || memcmp(out + out_len - 64, w->expect_tail, 64) != 0)) rc = -1;
     if (s) {
@@ -92,54 +107,69 @@ static void *tkb_worker_main(void *arg) {
     double scratch_phase[5] = {0, 0, 0, 0, 0};
     int rc = tk_set_device(w->device);
     for (size_t k = 0; !rc && k < w->warmup_each; k++) rc = tkb_one(w, (size_t)w->worker + k * 64, scratch_phase);
-    pthread_barrier_wait(w->warmed);
-    pthread_barrier_wait(w->go);
-    while (!rc) {
-        pthread_mutex_lock(w->mu);
-        const size_t i = (*w->next)++;
-        const int stop = *w->rc != 0;
-        pthread_mutex_unlock(w->mu);
-        if (i >= w->steps || stop) break;
-        rc = tkb_one(w, i, w->phase_ms);
+    for (size_t b = 0; b < w->blocks; b++) {
+        pthread_barrier_wait(w->done);   /* warm-up / previous block finished everywhere */
+        pthread_barrier_wait(w->go);     /* the caller has started its clock */
+        while (!rc) {
+            pthread_mutex_lock(w->mu);
+            const size_t i = (*w->next)++;
+            const int stop = *w->rc != 0;
+            pthread_mutex_unlock(w->mu);
+            if (i >= (b + 1) * w->steps || stop) {
+                if (i >= (b + 1) * w->steps) { pthread_mutex_lock(w->mu); (*w->next)--; pthread_mutex_unlock(w->mu); }
+                break;
+            }
+            rc = tkb_one(w, i, w->phase_ms);
+        }
+        if (rc) { pthread_mutex_lock(w->mu); if (!*w->rc) *w->rc = rc; pthread_mutex_unlock(w->mu); }
     }
-    if (rc) { pthread_mutex_lock(w->mu); if (!*w->rc) *w->rc = rc; pthread_mutex_unlock(w->mu); }
+    pthread_barrier_wait(w->done);
+    free(w->copy_out);
     return NULL;
 }
 
-int tkb_product_run(const void *const *texts, size_t n_texts, size_t n, int device, int device_text, int to_host, const char *const *cks,
-                    const size_t *ck_lens, size_t n_cks, size_t want_clusters, size_t want_nodes, size_t steps, size_t warmup,
-                    size_t inflight, const char *expect_head, const char *expect_tail, size_t expect_n, void (*at_start)(void),
-                    double *phase_ms, unsigned long long *h2d, unsigned long long *d2h) {
+int tkb_product_run(const void *const *texts, size_t n_texts, size_t n, int device, int device_text, int to_host, int pageable,
+                    const char *const *cks, const size_t *ck_lens, size_t n_cks, size_t want_clusters, size_t want_nodes, size_t steps,
+                    size_t blocks, size_t warmup, size_t inflight, const char *expect_head, const char *expect_tail, size_t expect_n,
+                    void (*at_start)(int), void (*at_end)(int), double *phase_ms, unsigned long long *h2d, unsigned long long *d2h) {
     if (inflight < 1) inflight = 1;
     if (inflight > 64) inflight = 64;
-    pthread_barrier_t warmed, go;
+    if (blocks < 1) blocks = 1;
+    pthread_barrier_t go, done;
     pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
     pthread_t th[64];
     tkb_worker w[64];
     size_t next = 0;
     int rc = 0;
-    pthread_barrier_init(&warmed, NULL, (unsigned)inflight + 1);
     pthread_barrier_init(&go, NULL, (unsigned)inflight + 1);
+    pthread_barrier_init(&done, NULL, (unsigned)inflight + 1);
     for (size_t t = 0; t < inflight; t++) {
         memset(&w[t], 0, sizeof w[t]);
         w[t].texts = texts; w[t].n_texts = n_texts; w[t].n = n; w[t].device = device; w[t].device_text = device_text; w[t].to_host = to_host;
+        w[t].pageable = pageable;
         w[t].cks = cks; w[t].ck_lens = ck_lens; w[t].n_cks = n_cks; w[t].want_clusters = want_clusters; w[t].want_nodes = want_nodes;
-        w[t].steps = steps; w[t].warmup_each = (warmup + inflight - 1) / inflight; if (!w[t].warmup_each) w[t].warmup_each = 1;
-        w[t].worker = (int)t; w[t].warmed = &warmed; w[t].go = &go; w[t].next = &next; w[t].mu = &mu; w[t].rc = &rc;
+        w[t].steps = steps; w[t].blocks = blocks;
+        w[t].warmup_each = (warmup + inflight - 1) / inflight; if (!w[t].warmup_each) w[t].warmup_each = 1;
+        w[t].worker = (int)t; w[t].go = &go; w[t].done = &done; w[t].next = &next; w[t].mu = &mu; w[t].rc = &rc;
         w[t].expect_head = expect_head; w[t].expect_tail = expect_tail; w[t].expect_n = expect_n;
         pthread_create(&th[t], NULL, tkb_worker_main, &w[t]);
     }
-    pthread_barrier_wait(&warmed);
-    if (at_start) at_start();
-    pthread_barrier_wait(&go);
+    for (size_t b = 0; b < blocks; b++) {
+        pthread_barrier_wait(&done);
+        if (b && at_end) at_end((int)b - 1);
+        if (at_start) at_start((int)b);
+        pthread_barrier_wait(&go);
+    }
+    pthread_barrier_wait(&done);
+    if (at_end) at_end((int)blocks - 1);
     for (size_t t = 0; t < inflight; t++) pthread_join(th[t], NULL);
     for (int k = 0; k < 5; k++) phase_ms[k] = 0;
     for (size_t t = 0; t < inflight; t++) {
         for (int k = 0; k < 5; k++) phase_ms[k] += w[t].phase_ms[k];
         if (w[t].h2d) { *h2d = w[t].h2d; *d2h = w[t].d2h; }
     }
-    pthread_barrier_destroy(&warmed);
     pthread_barrier_destroy(&go);
+    pthread_barrier_destroy(&done);
     return rc;
 }
 
@@ -214,123 +244,4 @@ double tkb_destroy_sweep(tk_state *s, const char *const *cks, const size_t *ck_l
     }
     *deleted = done;
     return (now_ms() - t0) * 1e-3;
-}
-
-/* the same loops through the CPU oracle's exported functions */
-typedef int (*ora_get_fn)(void *, const char *, size_t, const char **, size_t *);
-typedef int (*ora_add_node_fn)(void *, const char *, size_t, const char *, size_t, const char *, size_t, int, char *, size_t);
-typedef int (*ora_delete_fn)(void *, const char *, size_t, char *, size_t);
-typedef int (*ora_nodes_fn2)(void *, const char *, size_t, char **, size_t *, size_t *, char *, size_t);
-typedef void (*ora_free_buf_fn2)(char *);
-
-double tkb_ora_get_loop(void *fn, void *h, const char *const *paths, const size_t *lens, size_t n, size_t total, size_t *value_bytes) {
-    ora_get_fn f = (ora_get_fn)fn;
-    const char *v;
-    size_t vl, sum = 0;
-    double t0 = now_ms();
-    for (size_t i = 0, k = 0; i < total; i++, k = (k + 1 == n ? 0 : k + 1)) {
-        if (f(h, paths[k], lens[k], &v, &vl)) return -1.0;
-        sum += vl;
-    }
-    *value_bytes = sum;
-    return (now_ms() - t0) * 1e-3;
-}
-
-double tkb_ora_add_node_loop(void *fn, void *h, const char *const *cks, const size_t *ck_lens, const char *const *names,
-                             const size_t *name_lens, const char *const *jsons, const size_t *json_lens, size_t n, int is_record) {
-    ora_add_node_fn f = (ora_add_node_fn)fn;
-    char err[256];
-    double t0 = now_ms();
-    for (size_t i = 0; i < n; i++)
-        if (f(h, cks[i], ck_lens[i], names[i], name_lens[i], jsons[i], json_lens[i], is_record, err, sizeof err)) return -1.0;
-    return (now_ms() - t0) * 1e-3;
-}
-
-double tkb_ora_delete_loop(void *fn, void *h, const char *const *paths, const size_t *lens, size_t n) {
-    ora_delete_fn f = (ora_delete_fn)fn;
-    char err[256];
-    double t0 = now_ms();
-    for (size_t i = 0; i < n; i++)
-        if (f(h, paths[i], lens[i], err, sizeof err)) return -1.0;
-    return (now_ms() - t0) * 1e-3;
-}
-
-double tkb_ora_nodes_loop(void *fn_nodes, void *fn_free, void *h, const char *const *cks, const size_t *ck_lens, size_t n, size_t *pairs) {
-    ora_nodes_fn2 f = (ora_nodes_fn2)fn_nodes;
-    ora_free_buf_fn2 fr = (ora_free_buf_fn2)fn_free;
-    char err[256], *out;
-    size_t out_len, count, sum = 0;
-    double t0 = now_ms();
-    for (size_t i = 0; i < n; i++) {
-        if (f(h, cks[i], ck_lens[i], &out, &out_len, &count, err, sizeof err)) return -1.0;
-        fr(out);
-        sum += count;
-    }
-    *pairs = sum;
-    return (now_ms() - t0) * 1e-3;
-}
-
-double tkb_ora_destroy_sweep(void *fn_nodes, void *fn_free, void *fn_delete, void *h, const char *const *cks, const size_t *ck_lens,
-                             const char *const *cluster_paths, const size_t *cluster_path_lens, size_t n, size_t *deleted) {
-    ora_nodes_fn2 f = (ora_nodes_fn2)fn_nodes;
-    ora_free_buf_fn2 fr = (ora_free_buf_fn2)fn_free;
-    ora_delete_fn del = (ora_delete_fn)fn_delete;
-    char err[256], *out, path[512];
-    size_t out_len, count, done = 0;
-    double t0 = now_ms();
-    memcpy(path, "module.", 7);
-    for (size_t i = 0; i < n; i++) {
-        if (f(h, cks[i], ck_lens[i], &out, &out_len, &count, err, sizeof err)) return -1.0;
-        for (size_t at = 0, k = 0; k < count; k++) {
-            uint32_t fl, kl;
-            memcpy(&fl, out + at, 4); at += 4 + fl;
-            memcpy(&kl, out + at, 4); at += 4;
-            if (kl + 7 >= sizeof path) { fr(out); return -2.0; }
-            memcpy(path + 7, out + at, kl); at += kl;
-            if (del(h, path, 7 + kl, err, sizeof err)) { fr(out); return -1.0; }
-            done++;
-        }
-        fr(out);
-        if (del(h, cluster_paths[i], cluster_path_lens[i], err, sizeof err)) return -1.0;
-        done++;
-    }
-    *deleted = done;
-    return (now_ms() - t0) * 1e-3;
-}
-
-/* The same step through the CPU oracle (oracle/tk_oracle.c), via its exported functions. */
-typedef void *(*ora_new_fn)(const char *, size_t, char *, size_t);
-typedef void (*ora_free_fn)(void *);
-typedef void (*ora_free_buf_fn)(char *);
-typedef int (*ora_clusters_fn)(void *, char **, size_t *, size_t *, char *, size_t);
-typedef int (*ora_nodes_fn)(void *, const char *, size_t, char **, size_t *, size_t *, char *, size_t);
-typedef int (*ora_bytes_fn)(void *, int, char **, size_t *);
-
-int tkb_oracle_step(void **fns, const char *text, size_t n, const char *const *cks, const size_t *ck_lens, size_t n_cks,
-                    size_t want_clusters, size_t want_nodes, size_t want_len) {
-    ora_new_fn f_new = (ora_new_fn)fns[0];
-    ora_free_fn f_free = (ora_free_fn)fns[1];
-    ora_free_buf_fn f_free_buf = (ora_free_buf_fn)fns[2];
-    ora_clusters_fn f_clusters = (ora_clusters_fn)fns[3];
-    ora_nodes_fn f_nodes = (ora_nodes_fn)fns[4];
-    ora_bytes_fn f_bytes = (ora_bytes_fn)fns[5];
-    char err[512];
-    char *out;
-    size_t out_len, count, nodes = 0;
-    void *h = f_new(text, n, err, sizeof err);
-    if (!h) return 1;
-    if (f_clusters(h, &out, &out_len, &count, err, sizeof err)) { f_free(h); return 1; }
-    f_free_buf(out);
-    if (count != want_clusters) { f_free(h); return -1; }
-    for (size_t i = 0; i < n_cks; i++) {
-        if (f_nodes(h, cks[i], ck_lens[i], &out, &out_len, &count, err, sizeof err)) { f_free(h); return 1; }
-        f_free_buf(out);
-        nodes += count;
-    }
-    if (nodes != want_nodes) { f_free(h); return -1; }
-    f_bytes(h, 1, &out, &out_len);
-    int ok = out_len == want_len;
-    f_free_buf(out);
-    f_free(h);
-    return ok ? 0 : -1;
 }

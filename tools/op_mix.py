@@ -2,7 +2,7 @@
 """tools/op_mix.py -- the per-operation table of SURVEY.md 8(d), config #4 and config #5.
 
 Every operation of the state.State method set is timed on its own, single handle, single host
-thread, through the C ABI (compiled loops in tools/bench_driver.c), for the product (libtkstate on
+thread, through the C ABI (compiled loops in tools/bench_driver.c and tools/oracle_driver.c), for the product (libtkstate on
 the GPU in this box) and for the CPU oracle (oracle/tk_oracle.c), on the config #4 document
 (1,000 clusters x 100 nodes, 62,177,405 bytes).  The document is built once outside the timed
 regions; any loop that changes it gets a fresh handle.  Prints one JSON object; nothing here reads
@@ -47,23 +47,24 @@ def main():
     O.build()
     OL = O.lib()
     D = bench.driver()
+    DO = bench.oracle_driver()
     L = tk.state.lib()
     dbl = c_double
     D.tkb_get_loop.restype = D.tkb_add_node_loop.restype = D.tkb_delete_loop.restype = D.tkb_nodes_loop.restype = dbl
     D.tkb_destroy_sweep.restype = dbl
-    D.tkb_ora_get_loop.restype = D.tkb_ora_add_node_loop.restype = D.tkb_ora_delete_loop.restype = D.tkb_ora_nodes_loop.restype = dbl
-    D.tkb_ora_destroy_sweep.restype = dbl
+    DO.tkb_ora_get_loop.restype = DO.tkb_ora_add_node_loop.restype = DO.tkb_ora_delete_loop.restype = DO.tkb_ora_nodes_loop.restype = dbl
+    DO.tkb_ora_destroy_sweep.restype = dbl
     SA, ZA = POINTER(c_char_p), POINTER(c_size_t)
     D.tkb_get_loop.argtypes = [c_void_p, SA, ZA, c_size_t, c_size_t, POINTER(c_size_t)]
     D.tkb_add_node_loop.argtypes = [c_void_p, SA, ZA, SA, ZA, SA, ZA, c_size_t, c_int]
     D.tkb_delete_loop.argtypes = [c_void_p, SA, ZA, c_size_t]
     D.tkb_nodes_loop.argtypes = [c_void_p, SA, ZA, c_size_t, POINTER(c_size_t)]
     D.tkb_destroy_sweep.argtypes = [c_void_p, SA, ZA, SA, ZA, c_size_t, POINTER(c_size_t)]
-    D.tkb_ora_get_loop.argtypes = [c_void_p, c_void_p, SA, ZA, c_size_t, c_size_t, POINTER(c_size_t)]
-    D.tkb_ora_add_node_loop.argtypes = [c_void_p, c_void_p, SA, ZA, SA, ZA, SA, ZA, c_size_t, c_int]
-    D.tkb_ora_delete_loop.argtypes = [c_void_p, c_void_p, SA, ZA, c_size_t]
-    D.tkb_ora_nodes_loop.argtypes = [c_void_p, c_void_p, c_void_p, SA, ZA, c_size_t, POINTER(c_size_t)]
-    D.tkb_ora_destroy_sweep.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, SA, ZA, SA, ZA, c_size_t, POINTER(c_size_t)]
+    DO.tkb_ora_get_loop.argtypes = [c_void_p, c_void_p, SA, ZA, c_size_t, c_size_t, POINTER(c_size_t)]
+    DO.tkb_ora_add_node_loop.argtypes = [c_void_p, c_void_p, SA, ZA, SA, ZA, SA, ZA, c_size_t, c_int]
+    DO.tkb_ora_delete_loop.argtypes = [c_void_p, c_void_p, SA, ZA, c_size_t]
+    DO.tkb_ora_nodes_loop.argtypes = [c_void_p, c_void_p, c_void_p, SA, ZA, c_size_t, POINTER(c_size_t)]
+    DO.tkb_ora_destroy_sweep.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, SA, ZA, SA, ZA, c_size_t, POINTER(c_size_t)]
 
     def fn(name):
         return ctypes.cast(getattr(OL, name), c_void_p)
@@ -194,18 +195,18 @@ def main():
         for _ in range(100):
             OL.ora_clusters(oh, byref(o), byref(n), byref(cnt), err, 512); OL.ora_free_buf(o)
         ora["Clusters"] = {"calls_per_s": 100 / (time.perf_counter() - t0), "calls": 100}
-        dt = D.tkb_ora_nodes_loop(fn("ora_nodes"), fn("ora_free_buf"), oh, ck_arr, ck_lens, C, byref(pairs))
+        dt = DO.tkb_ora_nodes_loop(fn("ora_nodes"), fn("ora_free_buf"), oh, ck_arr, ck_lens, C, byref(pairs))
         assert dt > 0 and pairs.value == C * N
         ora["Nodes"] = {"calls_per_s": C / dt, "calls": C, "pairs": pairs.value}
-        dt = D.tkb_ora_get_loop(fn("ora_get"), oh, g_arr, g_lens, len(get_paths), args.gets, byref(vb))
+        dt = DO.tkb_ora_get_loop(fn("ora_get"), oh, g_arr, g_lens, len(get_paths), args.gets, byref(vb))
         assert dt > 0
         ora["Get"] = {"ops_per_s": args.gets / dt, "ops": args.gets}
-        dt = D.tkb_ora_delete_loop(fn("ora_delete"), oh, d_arr, d_lens, len(del_paths))
+        dt = DO.tkb_ora_delete_loop(fn("ora_delete"), oh, d_arr, d_lens, len(del_paths))
         assert dt > 0
         ora["Delete"] = {"ops_per_s": len(del_paths) / dt, "ops": len(del_paths)}
         OL.ora_free(oh)
         oh = OL.ora_new(base, len(base), err, 512)
-        dt = D.tkb_ora_add_node_loop(fn("ora_add_node"), oh, a_cks, a_ck_lens, a_names, a_name_lens, a_jsons, a_json_lens, len(add), 0)
+        dt = DO.tkb_ora_add_node_loop(fn("ora_add_node"), oh, a_cks, a_ck_lens, a_names, a_name_lens, a_jsons, a_json_lens, len(add), 0)
         assert dt > 0
         ora["AddNode"] = {"ops_per_s": len(add) / dt, "ops": len(add)}
         o, n = c_void_p(), c_size_t()
@@ -213,7 +214,7 @@ def main():
         assert ctypes.string_at(o.value, n.value) == text
         OL.ora_free_buf(o); OL.ora_free(oh)
         oh = OL.ora_new(text, len(text), err, 512)
-        dt = D.tkb_ora_destroy_sweep(fn("ora_nodes"), fn("ora_free_buf"), fn("ora_delete"), oh, ck_arr, ck_lens, cp_arr, cp_lens, C, byref(deleted))
+        dt = DO.tkb_ora_destroy_sweep(fn("ora_nodes"), fn("ora_free_buf"), fn("ora_delete"), oh, ck_arr, ck_lens, cp_arr, cp_lens, C, byref(deleted))
         assert dt > 0
         t0 = time.perf_counter(); OL.ora_bytes(oh, 1, byref(o), byref(n)); tbytes = time.perf_counter() - t0
         ofinal = ctypes.string_at(o.value, n.value)

@@ -12,11 +12,13 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
 
+#include "engine.hpp"
 #include "handle.hpp"
 #include "records.hpp"
 #include "tk_state.h"
@@ -111,23 +113,45 @@ int tk_backend_state(tk_backend *b, const char *name, size_t name_len, tk_state 
     const std::string path = b->root + "/" + std::string(sv(name, name_len)) + "/main.tf.json";
     struct stat st;
     if (stat(path.c_str(), &st) != 0) {
-        if (errno == ENOENT || errno == ENOTDIR) return tk_state_new_empty(name, name_len, out);  // state.New(name, []byte("{}"))
+        // os.IsNotExist is true for ENOENT only: any other stat error (ENOTDIR, EACCES ...) is returned
+        if (errno == ENOENT) return tk_state_new_empty(name, name_len, out);  // state.New(name, []byte("{}"))
         return fail(b, TK_EIO, path_error("stat", path, errno));
     }
     int fd = open(path.c_str(), O_RDONLY);
     if (fd < 0) return fail(b, TK_EIO, path_error("open", path, errno));
-    std::string content;
-    content.resize((size_t)st.st_size);
-    size_t got = 0;
+    // The file is read straight into a pinned block from the library's pool, so that the
+    // host->device copy of state.New is a DMA from where read(2) put the bytes (a pageable buffer
+    // would be staged through the driver's bounce buffers first).  Without a device there is no
+    // pinned memory; plain memory then carries the text to tk_state_new, which reports TK_ECUDA.
+    size_t cap = (size_t)st.st_size + 65536, pin_bytes = 0, got = 0;
+    char *pin = static_cast<char *>(pool_alloc_pinned(cap, &pin_bytes));
+    std::string plain;
+    char *buf = pin;
+    if (pin) cap = pin_bytes; else { plain.resize(cap); buf = plain.data(); }
+    int io_errno = 0;
     for (;;) {
-        if (got == content.size()) content.resize(content.size() + 65536);
-        ssize_t r = read(fd, content.data() + got, content.size() - got);
-        if (r < 0) { int e = errno; close(fd); return fail(b, TK_EIO, path_error("read", path, e)); }
+        if (got == cap) {   // the file grew under us: carry on in a larger block
+            size_t more_bytes = 0;
+            char *more = pin ? static_cast<char *>(pool_alloc_pinned(cap * 2, &more_bytes)) : nullptr;
+            if (more) {
+                memcpy(more, buf, got);
+                pool_free_pinned(pin, pin_bytes);
+                pin = buf = more; pin_bytes = cap = more_bytes;
+            } else {
+                if (pin) { plain.assign(buf, got); pool_free_pinned(pin, pin_bytes); pin = nullptr; }
+                plain.resize(cap * 2);
+                buf = plain.data(); cap = plain.size();
+            }
+        }
+        ssize_t r = read(fd, buf + got, cap - got);
+        if (r < 0) { if (errno == EINTR) continue; io_errno = errno; break; }
         if (r == 0) break;
         got += (size_t)r;
     }
     close(fd);
-    int rc = tk_state_new(name, name_len, content.data(), got, out);
+    int rc = io_errno ? TK_EIO : tk_state_new(name, name_len, buf, got, out);
+    if (pin) pool_free_pinned(pin, pin_bytes);   // tk_state_new has waited for its copy of the text
+    if (io_errno) return fail(b, TK_EIO, path_error("read", path, io_errno));
     if (rc) return fail(b, rc, tk_last_error(nullptr));
     return TK_OK;
 }
@@ -150,9 +174,19 @@ int tk_backend_persist_state(tk_backend *b, tk_state *s) {
     size_t n;
     int rc = tk_state_bytes(s, &text, &n);
     if (rc) return fail(b, rc, tk_last_error(s));
-    const std::string path = dir + "/main.tf.json", tmp = dir + "/.main.tf.json.tmp";
-    int fd = open(tmp.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
-    if (fd < 0) return fail(b, TK_EIO, path_error("open", path, errno));
+    // a temporary file of its own name (two processes may persist the same manager at once)
+    const std::string path = dir + "/main.tf.json";
+    // (O_EXCL with mode 0644, not mkstemp: the kernel then applies the umask as it does for the
+    //  reference's ioutil.WriteFile(path, bytes, 0644))
+    static std::atomic<unsigned> serial{0};
+    std::string tmp;
+    int fd = -1;
+    for (int attempt = 0; attempt < 100 && fd < 0; attempt++) {
+        tmp = dir + "/.main.tf.json." + std::to_string((long)getpid()) + "." + std::to_string(serial++) + ".tmp";
+        fd = open(tmp.c_str(), O_WRONLY | O_CREAT | O_EXCL, 0644);
+        if (fd < 0 && errno != EEXIST) break;
+    }
+    if (fd < 0) return fail(b, TK_EIO, path_error("open", tmp, errno));
     size_t put = 0;
     while (put < n) {
         ssize_t w = write(fd, text + put, n - put);

@@ -10,6 +10,7 @@
 #include "kernels.cuh"
 #include "records.hpp"
 #include "tk_state.h"
+#include "tk_state_bench.h"
 
 using namespace tk;
 

@@ -2,12 +2,22 @@
 #include "doc.hpp"
 
 #include <charconv>
+#include <clocale>
+#include <locale.h>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
 namespace tk {
+
+// strtod in the "C" locale whatever the host program's LC_NUMERIC is (a decimal-comma locale would
+// stop at the '.'): the library is loaded into other people's processes.
+double strtod_c(const char *s) {
+    static const locale_t c_locale = newlocale(LC_ALL_MASK, "C", (locale_t)0);
+    return c_locale ? strtod_l(s, nullptr, c_locale) : strtod(s, nullptr);
+}
+
 
 const char *const kErrCollision = "encountered value collision whilst building path";
 const char *const kErrNotObj = "not an object";
@@ -201,7 +211,7 @@ private:
             while (i_ < n_ && is_digit(p_[i_])) i_++;
         }
         std::string txt((const char *)p_ + st, i_ - st);
-        double v = strtod(txt.c_str(), nullptr);
+        double v = strtod_c(txt.c_str());
         if (std::isinf(v)) {
             // strconv.ParseFloat range error: reported after the whole input proved valid
             if (range_err_.empty()) range_err_ = "json: cannot unmarshal number " + txt + " into Go value of type float64";

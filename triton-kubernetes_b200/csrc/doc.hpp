@@ -55,6 +55,8 @@ bool syntax_error_text(std::string_view text, std::string *err);
 
 // encoding/json floatEncoder (64 bit) -- ES6-style shortest text
 void format_go_float(double v, std::string *out);
+// strtod in the "C" locale, whatever LC_NUMERIC the host program has set
+double strtod_c(const char *s);
 
 std::vector<std::string_view> split(std::string_view s, char sep);
 

@@ -75,6 +75,13 @@ void pool_free_pinned(void *p, size_t bytes) {
     g_pin_pool.free_blocks[{0, bytes}].push_back(p);
 }
 
+static thread_local cudaStream_t tl_scope_stream = nullptr;
+StreamScope::StreamScope(cudaStream_t s) : prev_(tl_scope_stream) { tl_scope_stream = s; }
+StreamScope::~StreamScope() { tl_scope_stream = prev_; }
+void pool_release_sync() {
+    if (tl_scope_stream && cudaStreamSynchronize(tl_scope_stream) != cudaSuccess) (void)cudaGetLastError();
+}
+
 cudaError_t DevBuf::reserve(size_t bytes, size_t keep_bytes, cudaStream_t s) {
     if (bytes <= cap) return cudaSuccess;
     size_t got = 0;
@@ -86,7 +93,7 @@ cudaError_t DevBuf::reserve(size_t bytes, size_t keep_bytes, cudaStream_t s) {
         // the old block goes back to the pool; work queued on other streams never uses it
         if ((e = cudaStreamSynchronize(s)) != cudaSuccess) { pool_free_device(q, got); return e; }
     }
-    if (p) pool_free_device(p, cap);
+    if (p) { pool_release_sync(); pool_free_device(p, cap); }
     p = q;
     cap = got;
     return cudaSuccess;
@@ -404,9 +411,12 @@ int Engine::stage(const Document &doc, std::string *err) {
 int Engine::stage_tape(const Document &doc, std::string *err) {
     int rc = init(err);
     if (rc) return rc;
+    StreamScope scope(stream_);
     if (staged_version_ == doc.version) return TK_OK;
     if (!doc.host_valid) { *err = "internal: no host tree to flatten"; return TK_EARG; }
     tape_from_parse_ = false;
+    // copies of the previous staging may still be reading the pinned arrays flatten() rewrites
+    { cudaError_t e0 = cudaStreamSynchronize(stream_); if (e0 != cudaSuccess) return fail(e0, "synchronize", err); }
     flatten(doc);
     if (pin_failed_) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
     if (h_arena_.n >= 0xfffffff0ull || h_meta_.n >= 0xfffffff0ull) {
@@ -439,7 +449,9 @@ int Engine::stage_tape(const Document &doc, std::string *err) {
 int Engine::stage_keys(const Document &doc, std::string *err) {
     int rc = init(err);
     if (rc) return rc;
+    StreamScope scope(stream_);
     if (keys_version_ == doc.version) return TK_OK;
+    { cudaError_t e0 = cudaStreamSynchronize(stream_); if (e0 != cudaSuccess) return fail(e0, "synchronize", err); }
     flatten_keys(doc);
     if (pin_failed_) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
     if (h_keys_.n >= 0xfffffff0ull) { *err = "document too large: module keys must stay below 4 GiB"; return TK_ELIMIT; }
@@ -465,6 +477,7 @@ int Engine::stage_keys(const Document &doc, std::string *err) {
 int Engine::bytes(const Document &doc, bool to_host, const void **out, size_t *len, std::string *err) {
     int rc = stage_tape(doc, err);
     if (rc) return rc;
+    StreamScope scope(stream_);
     cudaError_t e;
     if (!h_total_.reserve(1)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
     unsigned long long *scratch = d_scratch_.as<unsigned long long>();
@@ -495,6 +508,7 @@ int Engine::prefix_hits(const Document &doc, std::string_view prefix, bool to_ho
                         size_t *count, std::string *err) {
     int rc = stage_keys(doc, err);
     if (rc) return rc;
+    StreamScope scope(stream_);
     cudaError_t e;
     const size_t nk = keys_.n_keys;
     if ((e = d_prefix_.reserve(prefix.size() + 16)) != cudaSuccess) return fail(e, "cudaMalloc(prefix)", err);
@@ -539,6 +553,7 @@ int Engine::fetch_result(std::string *err) {
 int Engine::upload_text(const char *raw, size_t n, std::string *err) {
     int rc = init(err);
     if (rc) return rc;
+    StreamScope scope(stream_);
     if (n >= 0xfff00000ull) { *err = "document too large: the text must stay below 4 GiB"; return TK_ELIMIT; }
     const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 64;
     cudaError_t e;
@@ -555,6 +570,7 @@ int Engine::upload_text(const char *raw, size_t n, std::string *err) {
 int Engine::upload_text_device(const void *dev_raw, size_t n, std::string *err) {
     int rc = init(err);
     if (rc) return rc;
+    StreamScope scope(stream_);
     if (n >= 0xfff00000ull) { *err = "document too large: the text must stay below 4 GiB"; return TK_ELIMIT; }
     const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 64;
     cudaError_t e;
@@ -573,6 +589,7 @@ int Engine::upload_text_device(const void *dev_raw, size_t n, std::string *err) 
 // last kernel; two more only if some string needs decoding.
 int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     cudaError_t e;
+    StreamScope scope(stream_);
     const uint8_t *raw = d_arena_.as<uint8_t>();
     memset(out, 0, sizeof *out);
     if ((e = d_res_.reserve(sizeof(ParseResult))) != cudaSuccess) return fail(e, "cudaMalloc(result)", err);
@@ -781,7 +798,7 @@ struct TreeBuilder {
         if (t == "false") return new BoolNode(false);
         if (t == "null") return nullptr;
         const std::string txt(t);
-        double d = strtod(txt.c_str(), nullptr);
+        double d = strtod_c(txt.c_str());
         if (std::isinf(d)) {
             if (range_err.empty()) range_err = "json: cannot unmarshal number " + txt + " into Go value of type float64";
             d = 0;
@@ -866,6 +883,7 @@ static Node *build_value(TreeBuilder &tb, uint32_t r, uint32_t *next, int levels
 // the last duplicate (encoding/json objectInterface) and orders keys bytewise.
 int Engine::materialise(Document *doc, std::string *err) {
     if (doc->host_valid) return TK_OK;
+    StreamScope scope(stream_);
     if (!tape_from_parse_ || !tape_.n_rows) { *err = "internal: no device tape to build the tree from"; return TK_EARG; }
     const size_t n = tape_.n_rows;
     cudaError_t e;
@@ -919,6 +937,7 @@ namespace tk {
 // (it sizes the second half), one at the end.
 int Engine::build_index(const Document &doc, std::string *err) {
     if (index_version_ == doc.version) return TK_OK;
+    StreamScope scope(stream_);
     if (!device_resident(doc)) { *err = "internal: module index needs the parser's tape"; return TK_EARG; }
     cudaError_t e;
     const size_t rows = tape_.n_rows;

@@ -23,6 +23,21 @@ void *pool_alloc_device(size_t bytes, size_t *got);
 void pool_free_device(void *p, size_t bytes);
 void *pool_alloc_pinned(size_t bytes, size_t *got);
 void pool_free_pinned(void *p, size_t bytes);
+// A handle's buffers grow by taking a larger block and handing the old one back to the pool, where
+// another handle (another thread, another stream) may pick it up at once.  Work this handle has
+// queued may still be using the old block, so the handle's stream is drained first: every Engine
+// entry point names its stream for the calling thread (StreamScope), and the two reserve()s below
+// call pool_release_sync() before they give a block back.  Growth of a block that is in use is
+// rare (a handle re-staging a document that got larger), so the wait costs nothing that matters.
+void pool_release_sync();
+struct StreamScope {
+    explicit StreamScope(cudaStream_t s);
+    ~StreamScope();
+    StreamScope(const StreamScope &) = delete;
+    StreamScope &operator=(const StreamScope &) = delete;
+private:
+    cudaStream_t prev_;
+};
 
 // grow-only pinned host array: host<->device copies from it are true DMA
 template <class T>
@@ -40,7 +55,7 @@ struct PinVec {
         T *q = static_cast<T *>(pool_alloc_pinned(want * sizeof(T), &got));
         if (!q) { failed = true; return false; }
         if (n) memcpy(q, p, n * sizeof(T));
-        if (p) pool_free_pinned(p, cap_bytes);
+        if (p) { pool_release_sync(); pool_free_pinned(p, cap_bytes); }
         p = q;
         cap_bytes = got;
         cap = got / sizeof(T);

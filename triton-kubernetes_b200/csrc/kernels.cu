@@ -557,11 +557,16 @@ cudaError_t launch_row_offsets(const TapeView &t, uint32_t *off, unsigned long l
 
 cudaError_t launch_emit(const TapeView &t, const uint32_t *off, uint8_t *out, cudaStream_t s) {
     constexpr int smem = WARPS * (WARP_IN_BYTES + WARP_OUT_BYTES);
-    static bool configured = false;  // per process; every device runs the same image
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return e;
-        configured = true;
+    // the opt-in above 48 KiB is a per-device (per-context) attribute of the function: asked for
+    // once on every device a handle of this process launches on
+    static std::atomic<bool> configured[64];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const bool slot = dev >= 0 && dev < 64;
+    if (!slot || !configured[dev].load(std::memory_order_acquire)) {
+        if ((e = cudaFuncSetAttribute(emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
+        if (slot) configured[dev].store(true, std::memory_order_release);
     }
     emit_kernel<<<emit_tiles(t.n_rows), EMIT_THREADS, smem, s>>>(t, off, out);
     g_launches++;
