@@ -482,3 +482,36 @@ def test_handles_on_two_devices_in_one_process(tk, oracle):
     for t in ts: t.join()
     assert tk.state.lib().tk_set_device(0) == 0
     assert out == [True, True], out
+
+
+def test_index_lists_that_outgrow_their_first_buffer(tk, oracle):
+    """The field lists of the module index are sized by a guess from the text length (one "name" /
+    "hostname" member per 256 bytes); 6,000 children of a dozen bytes each are far denser than that,
+    so the lists are counted on the first pass and filled on a second one."""
+    mod = {"cluster_a_%04d" % i: {"name": "n%04d" % i} for i in range(3000)}
+    mod.update({"node_a_0007_%04d" % i: {"hostname": "h%04d" % i} for i in range(3000)})
+    raw = oracle.New("x", json.dumps({"module": mod}).encode()).Bytes()
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    ca = a.Clusters()
+    assert ca == b.Clusters() and len(ca) == 3000
+    na = a.Nodes("cluster_a_0007")
+    assert na == b.Nodes("cluster_a_0007") and len(na) == 3000
+    assert not a.host_tree_built
+
+
+def test_index_gives_way_to_the_host_tree_for_a_child_with_thousands_of_members(tk, oracle):
+    """The index pass finds the child a "name" member belongs to by walking up through at most 4,096
+    rows; a child with more members than that before its name sends Clusters()/Nodes() to the host
+    tree, with the same answers."""
+    wide = {"k%05d" % i: "v" for i in range(6000)}
+    wide["name"] = "wide"                                # sorts after every k....
+    mod = {"cluster_a_b": {"name": "b"}, "cluster_a_wide": wide, "node_a_b_1": {"hostname": "h1", "x": {"name": "too deep"}, "y": [{"hostname": "in array"}]}}
+    raw = oracle.New("x", json.dumps({"module": mod, "name": "at the root", "m2": {"cluster_a_q": {"name": "q"}}}).encode()).Bytes()
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    assert a.Clusters() == b.Clusters() == {b"b": b"cluster_a_b", b"wide": b"cluster_a_wide"}
+    assert a.Nodes("cluster_a_b") == b.Nodes("cluster_a_b") == {b"h1": b"node_a_b_1"}
+    assert a.host_tree_built
+    small = oracle.New("x", json.dumps({"module": {"cluster_a_b": {"name": "b"}, "node_a_b_1": {"hostname": "h1", "x": {"name": "too deep"},
+                                                   "y": [{"hostname": "in array"}]}}, "name": "at the root"}).encode()).Bytes()
+    c = tk.New("x", small)
+    assert c.Clusters() == {b"b": b"cluster_a_b"} and c.Nodes("cluster_a_b") == {b"h1": b"node_a_b_1"} and not c.host_tree_built

@@ -26,7 +26,9 @@ for i in range(steps + 3):
     flush.fill_(i & 255)   # evict the text and the tables from L2, as bench.py does between steps
     torch.cuda.synchronize()
     s = tk.state.NewDevice("bench", dev_text.data_ptr(), len(text))
-    s.ClustersCount(); s.NodesCount(synth.cluster_key(0)); s.BytesDevice()
+    if not os.environ.get("TK_SKIP_INDEX"):
+        s.ClustersCount(); s.NodesCount(synth.cluster_key(0))
+    s.BytesDevice()
     st = s.KernelStats()
     s.close()
     if i >= 3:

@@ -228,7 +228,7 @@ static int children_by_prefix(tk_state *s, std::string_view prefix, std::string_
     std::string err;
     auto &pairs = s->pairs;  // (field value, module key); kept on the handle so a sweep of calls re-uses its storage
     pairs.clear();
-    if (!s->doc.host_valid && s->eng.device_resident(s->doc)) {
+    if (!s->doc.host_valid && s->eng.index_usable(s->doc)) {
         // the document lives on the device: one GPU pass per version builds the packed index, and
         // the finished answer is usually a byte range of the result records packed alongside it
         bool module_ok = false, direct = false;

@@ -3,7 +3,9 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -99,13 +101,32 @@ cudaError_t DevBuf::reserve(size_t bytes, size_t keep_bytes, cudaStream_t s) {
     return cudaSuccess;
 }
 
+// Development aid: TK_TRACE=1 prints, per handle, the host time at which each phase of New / Bytes /
+// the index build was reached (microseconds since the phase list was started), to stderr.
+namespace {
+struct Trace {
+    bool on;
+    std::chrono::steady_clock::time_point t0;
+    std::string line;
+    Trace() : on(getenv("TK_TRACE") != nullptr) { if (on) t0 = std::chrono::steady_clock::now(); }
+    void mark(const char *what) {
+        if (!on) return;
+        const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+        char buf[64];
+        snprintf(buf, sizeof buf, " %s=%.0f", what, us);
+        line += buf;
+    }
+    ~Trace() { if (on && !line.empty()) fprintf(stderr, "[tk trace]%s\n", line.c_str()); }
+};
+}  // namespace
+
 static std::atomic<bool> g_default_timing{false};
 void set_default_timing(bool on) { g_default_timing = on; }
 
 const char *kernel_name(int kind) {
     static const char *const names[K_COUNT] = {"row_offsets_kernel", "emit_kernel", "prefix_match_kernel", "scan_tokens_kernel (carry protocol)",
                                                "token_agg + token_blocks kernels", "brackets_kernel", "sort_brackets (radix passes)", "match_kernel",
-                                               "decode kernels", "rows_kernel", "key_order_kernel", "module index kernels",
+                                               "decode kernels", "rows_kernel", "key_order_kernel", "field_pack_kernel (module index)", "field_find_kernel",
                                                "scan_count_kernel", "scan_prefix_kernel", "scan_emit_kernel"};
     return kind >= 0 && kind < K_COUNT ? names[kind] : "";
 }
@@ -592,6 +613,8 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     StreamScope scope(stream_);
     const uint8_t *raw = d_arena_.as<uint8_t>();
     memset(out, 0, sizeof *out);
+    Trace tr;
+    tr.mark("new:start");
     if ((e = d_res_.reserve(sizeof(ParseResult))) != cudaSuccess) return fail(e, "cudaMalloc(result)", err);
     ParseResult *d_res = d_res_.as<ParseResult>();
     if (n == 0) { out->invalid = 1; return TK_OK; }
@@ -613,7 +636,9 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
                      return launch_scan_tokens(raw, n, tb, d_scratch_.as<unsigned long long>(), d_res, carry_protocol, stage, stream_);
                  })) != cudaSuccess)
                 return fail(e, "scan_tokens", err);
+        tr.mark("scan:queued");
         int rc = fetch_result(err);
+        tr.mark("scan:done");
         if (rc) return rc;
         if (h_res_.p->slow_scan && !carry_protocol) { carry_protocol = true; continue; }
         if (h_res_.p->n_tokens <= cap) break;
@@ -631,7 +656,9 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     TilePrefix *tiles = d_tiles_.as<TilePrefix>();
     if ((e = timed(K_TOKEN_PREFIX, [&] { return launch_token_prefix(tb, n_tok, tiles, d_scratch_.as<unsigned long long>(), d_res, stream_); })) != cudaSuccess)
         return fail(e, "token_prefix", err);
+    tr.mark("tokprefix:queued");
     int rc = fetch_result(err);
+    tr.mark("tokprefix:done");
     if (rc) return rc;
     *out = *h_res_.p;
     if (out->invalid) return TK_OK;
@@ -709,7 +736,30 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
         return fail(e, "rows", err);
     if (n_rows && (e = timed(K_KEY_ORDER, [&] { return launch_key_order(raw, rb, n_rows, bb, d_res, stream_); })) != cudaSuccess)
         return fail(e, "key_order", err);
+    // module index lists (index.cu), while the verdict is on its way: sized by guess (a "name" /
+    // "hostname" member per 256 bytes of text is four times what config #4 has); a list that outgrows
+    // its buffer is counted, and build_index runs the kernel again with room for it
+    tape_.n_rows = n_rows;
+    tape_.arena_bytes = (uint32_t)arena_used_;
+    tape_.text_len = (uint32_t)n;
+    tape_.meta = rb.meta; tape_.koff = rb.koff; tape_.klen = rb.klen; tape_.voff = rb.voff; tape_.vlen = rb.vlen;
+    tape_.arena = d_arena_.as<uint8_t>();
+    for (int f = 0; f < 2; f++) {
+        const size_t cap = std::min<size_t>(n_rows, n / 256 + 1024);
+        if ((e = d_frefs_[f].reserve(cap * sizeof(FieldRef))) != cudaSuccess || (e = d_foff_[f].reserve((cap + 1) * 4)) != cudaSuccess)
+            return fail(e, "cudaMalloc(index)", err);
+        fx_.refs[f] = d_frefs_[f].as<FieldRef>();
+        fx_.off[f] = d_foff_[f].as<uint32_t>();
+        fx_.cap[f] = (uint32_t)cap;
+    }
+    if ((e = d_find_status_.reserve(field_status_words(n_rows) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    fx_.status = d_find_status_.as<unsigned long long>();
+    bb_ = bb;
+    if (n_rows && (e = timed(K_FIELD_FIND, [&] { return launch_field_find(tape_, n_rows, bb.match, bb.row, fx_, d_res, stream_); })) != cudaSuccess)
+        return fail(e, "field_find", err);
+    tr.mark("rest:queued");
     rc = fetch_result(err);
+    tr.mark("rest:done");
     if (rc) return rc;
     const unsigned long long side = out->side_bytes;
     *out = *h_res_.p;
@@ -718,13 +768,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
 
     if ((e = d_off_.reserve(((size_t)n_rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(off)", err);
     if ((e = d_scratch_.reserve(scan_scratch_words(n_rows) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
-    tape_.n_rows = n_rows;
-    tape_.arena_bytes = (uint32_t)arena_used_;
-    tape_.text_len = (uint32_t)n;
-    tape_.meta = rb.meta; tape_.koff = rb.koff; tape_.klen = rb.klen; tape_.voff = rb.voff; tape_.vlen = rb.vlen;
-    tape_.arena = d_arena_.as<uint8_t>();
     tape_from_parse_ = true;
-    bb_ = bb;
     parsed_ = *out;
     index_version_ = 0;
     return TK_OK;
@@ -931,95 +975,73 @@ int Engine::materialise(Document *doc, std::string *err) {
 
 namespace tk {
 
-// One pass per document version (csrc/index.cu): children of "module" found and ranked, their key /
-// name / hostname strings located, then keys and per-field result records packed and copied to the
-// host together with the prefix tables.  Two synchronisations: one to learn the number of children
-// (it sizes the second half), one at the end.
+// Once per document version: the field lists the parse left on the device (rows_kernel) are packed
+// into result records (csrc/index.cu) and copied to the host with their offsets and order bitmaps.
+// The sizes of everything are known from the parse verdict, so the host waits once, at the end.
 int Engine::build_index(const Document &doc, std::string *err) {
     if (index_version_ == doc.version) return TK_OK;
     StreamScope scope(stream_);
     if (!device_resident(doc)) { *err = "internal: module index needs the parser's tape"; return TK_EARG; }
     cudaError_t e;
-    const size_t rows = tape_.n_rows;
-    // the parse has already said where "module" is (rows_kernel) and what kind of value it has
     index_module_ok_ = parsed_.root_kind == ROW_OPEN_OBJ && parsed_.module_row != 0 &&
                        (parsed_.module_kind == ROW_OPEN_OBJ || parsed_.module_kind == ROW_EMPTY_OBJ);
-    const uint32_t module_row = parsed_.module_row - 1;
-    uint32_t n = 0;
-    if ((e = d_minfo_.reserve(64)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    unsigned long long *totals = d_minfo_.as<unsigned long long>();  // per field: records << 32 | blob bytes
-    unsigned long long *scratch = nullptr;
-    uint32_t *rank = nullptr;
-    if (index_module_ok_ && parsed_.module_kind == ROW_OPEN_OBJ) {
-        if ((e = d_crank_.reserve((rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-        if ((e = d_scratch_.reserve(parse_scan_scratch_words((uint32_t)rows) * 8 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
-        if (!h_words_.reserve(8)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
-        scratch = d_scratch_.as<unsigned long long>();
-        rank = d_crank_.as<uint32_t>();
-        e = timed(K_MODULE_INDEX, [&] { return scan_child_rank(tape_, module_row, bb_.match, bb_.row, rank, scratch, stream_); });  // children -> scratch[1]
-        if (e != cudaSuccess) return fail(e, "module index", err);
-        if ((e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess) return fail(e, "copy child count", err);
-        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
-        n = (uint32_t)h_words_.p[0];
-    }
     index_m_[0] = index_m_[1] = 0;
     index_hint_[0] = index_hint_[1] = 0;
-    if (n) {
-        DevBuf *need4[] = {&d_cviol_[0], &d_cviol_[1], &d_foff_[0], &d_foff_[1]};
-        for (DevBuf *b : need4)
-            if ((e = b->reserve(((size_t)n + 2) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-        DevBuf *need8[] = {&d_crec_[0], &d_crec_[1], &d_crec_excl_[0], &d_crec_excl_[1]};
-        for (DevBuf *b : need8)
-            if ((e = b->reserve(((size_t)n + 2) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-        const size_t bit_words = ((size_t)n + 31) / 32 + 1;
-        if ((e = d_fviolbits_[0].reserve(bit_words * 4)) != cudaSuccess || (e = d_fviolbits_[1].reserve(bit_words * 4)) != cudaSuccess)
-            return fail(e, "cudaMalloc(index)", err);
-        if ((e = d_crefs_.reserve(((size_t)n + 1) * sizeof(ChildRef))) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-        // records cannot outgrow the strings they are copied from
-        const size_t cap = arena_used_ + 8 * (size_t)n + 64;
-        if ((e = d_fblob_[0].reserve(cap)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-        if ((e = d_fblob_[1].reserve(cap)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-        ChildRef *refs = d_crefs_.as<ChildRef>();
-        IndexTables tb;
+    if (parsed_.index_slow) { *err = "internal: module index not available for this document"; return TK_EARG; }
+    if (index_module_ok_ && (parsed_.field_count[0] > fx_.cap[0] || parsed_.field_count[1] > fx_.cap[1])) {
+        // a list outgrew its buffer: the kernel has counted it, run it again with room (same tape, same verdict)
         for (int f = 0; f < 2; f++) {
-            tb.rec[f] = d_crec_[f].as<unsigned long long>();
-            tb.rec_excl[f] = d_crec_excl_[f].as<unsigned long long>();
-            tb.viol[f] = d_cviol_[f].as<uint32_t>();
-            tb.blob[f] = d_fblob_[f].as<uint8_t>();
-            tb.off[f] = d_foff_[f].as<uint32_t>();
-            tb.viol_bits[f] = d_fviolbits_[f].as<uint32_t>();
+            const size_t cap = std::max<size_t>(parsed_.field_count[f], fx_.cap[f]);
+            if ((e = d_frefs_[f].reserve(cap * sizeof(FieldRef))) != cudaSuccess || (e = d_foff_[f].reserve((cap + 1) * 4)) != cudaSuccess)
+                return fail(e, "cudaMalloc(index)", err);
+            fx_.refs[f] = d_frefs_[f].as<FieldRef>();
+            fx_.off[f] = d_foff_[f].as<uint32_t>();
+            fx_.cap[f] = (uint32_t)cap;
         }
-        tb.totals = totals;
+        e = timed(K_FIELD_FIND, [&] { return launch_field_find(tape_, tape_.n_rows, bb_.match, bb_.row, fx_, d_res_.as<ParseResult>(), stream_); });
+        if (e != cudaSuccess) return fail(e, "field_find", err);
+    }
+    uint32_t m[2] = {0, 0};
+    size_t bytes[2] = {0, 0}, bit_words[2] = {0, 0};
+    uint32_t *viol[2] = {nullptr, nullptr};
+    uint8_t *blob[2] = {nullptr, nullptr};
+    for (int f = 0; index_module_ok_ && f < 2; f++) {
+        m[f] = parsed_.field_count[f];
+        if (!m[f]) continue;
+        if (parsed_.field_bytes[f] >= 0xfffffff0ull) { *err = "document too large: the module index must stay below 4 GiB"; return TK_ELIMIT; }
+        bytes[f] = (size_t)parsed_.field_bytes[f];
+        bit_words[f] = ((size_t)m[f] + 31) / 32 + 1;
+        if ((e = d_fviolbits_[f].reserve(bit_words[f] * 4)) != cudaSuccess || (e = d_fblob_[f].reserve(bytes[f] + 64)) != cudaSuccess)
+            return fail(e, "cudaMalloc(index)", err);
+        if (!h_foff_[f].reserve((size_t)m[f] + 1) || !h_fviolbits_[f].reserve(bit_words[f]) || !h_fblob_[f].reserve(bytes[f] + 1)) {
+            *err = "cuda: pinned host allocation failed";
+            return TK_ECUDA;
+        }
+        viol[f] = d_fviolbits_[f].as<uint32_t>();
+        blob[f] = d_fblob_[f].as<uint8_t>();
+    }
+    if (m[0] || m[1]) {
         e = timed(K_MODULE_INDEX, [&] {
             cudaError_t x;
-            if ((x = cudaMemsetAsync(refs, 0xff, (size_t)n * sizeof(ChildRef), stream_)) != cudaSuccess) return x;
             for (int f = 0; f < 2; f++)
-                if ((x = cudaMemsetAsync(d_fviolbits_[f].p, 0, bit_words * 4, stream_)) != cudaSuccess) return x;
-            if ((x = launch_child_refs(tape_, module_row, bb_.match, bb_.row, rank, refs, stream_)) != cudaSuccess) return x;
-            if ((x = launch_child_sizes(tape_.arena, refs, n, d_crec_[0].as<unsigned long long>(), d_crec_[1].as<unsigned long long>(),
-                                        d_cviol_[0].as<uint32_t>(), d_cviol_[1].as<uint32_t>(), stream_)) != cudaSuccess) return x;
-            for (int f = 0; f < 2; f++)
-                if ((x = scan_u64(d_crec_[f].as<unsigned long long>(), d_crec_excl_[f].as<unsigned long long>(), n, scratch, stream_)) != cudaSuccess) return x;
-            return launch_child_pack(tape_.arena, refs, n, tb, stream_);
+                if (m[f] && (x = cudaMemsetAsync(viol[f], 0, bit_words[f] * 4, stream_)) != cudaSuccess) return x;
+            return launch_field_pack(tape_.arena, fx_, m, viol, blob, stream_);
         });
         if (e != cudaSuccess) return fail(e, "module index", err);
-        if ((e = copy_d2h(h_words_.p, totals, 16)) != cudaSuccess) return fail(e, "copy index sizes", err);
-        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
         for (int f = 0; f < 2; f++) {
-            const uint32_t m = (uint32_t)(h_words_.p[f] >> 32);
-            const size_t bytes = (size_t)(uint32_t)h_words_.p[f];
-            index_m_[f] = m;
-            if (!m) continue;
-            if (!h_foff_[f].reserve((size_t)m + 1) || !h_fviolbits_[f].reserve(((size_t)m + 31) / 32 + 1) || !h_fblob_[f].reserve(bytes + 1)) {
-                *err = "cuda: pinned host allocation failed";
-                return TK_ECUDA;
-            }
-            if ((e = copy_d2h(h_foff_[f].p, d_foff_[f].p, ((size_t)m + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
-            if ((e = copy_d2h(h_fviolbits_[f].p, d_fviolbits_[f].p, (((size_t)m + 31) / 32) * 4)) != cudaSuccess) return fail(e, "copy index", err);
-            if ((e = copy_d2h(h_fblob_[f].p, d_fblob_[f].p, bytes)) != cudaSuccess) return fail(e, "copy index", err);
+            if (!m[f]) continue;
+            if ((e = copy_d2h(h_foff_[f].p, fx_.off[f], ((size_t)m[f] + 1) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+            if ((e = copy_d2h(h_fviolbits_[f].p, viol[f], (((size_t)m[f] + 31) / 32) * 4)) != cudaSuccess) return fail(e, "copy index", err);
+            if ((e = copy_d2h(h_fblob_[f].p, blob[f], bytes[f])) != cudaSuccess) return fail(e, "copy index", err);
+            index_m_[f] = m[f];
         }
         if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "module index", err);
     }
+    for (int f = 0; f < 2; f++)
+        if (index_m_[f] && h_foff_[f].p[index_m_[f]] != (uint32_t)bytes[f]) {
+            *err = "internal: module index sizes disagree";
+            return TK_ECUDA;
+        }
     index_version_ = doc.version;
     return TK_OK;
 }

@@ -89,7 +89,7 @@ struct DevBuf {
 
 enum KernelKind {
     K_ROW_OFFSETS = 0, K_EMIT, K_PREFIX_MATCH, K_SCAN_TOKENS, K_TOKEN_PREFIX, K_BRACKETS, K_SORT_BRACKETS, K_MATCH,
-    K_DECODE, K_ROWS, K_KEY_ORDER, K_MODULE_INDEX, K_SCAN_COUNT, K_SCAN_PREFIX, K_SCAN_EMIT, K_COUNT
+    K_DECODE, K_ROWS, K_KEY_ORDER, K_MODULE_INDEX, K_FIELD_FIND, K_SCAN_COUNT, K_SCAN_PREFIX, K_SCAN_EMIT, K_COUNT
 };
 const char *kernel_name(int kind);
 void set_default_timing(bool on);  // engines created from now on start with per-kernel timing on/off
@@ -131,6 +131,8 @@ public:
     // The packed index is built on the GPU once per document version; the lookup is a binary search.
     // *module_ok false: "module" is missing or not an object (gabs.ErrNotObj).
     bool device_resident(const Document &doc) const { return tape_from_parse_ && staged_version_ == doc.version; }
+    // false for the rare document whose children have more members than the index pass walks through
+    bool index_usable(const Document &doc) const { return device_resident(doc) && !parsed_.index_slow; }
     int index_lookup(const Document &doc, std::string_view prefix, bool hostname, bool *module_ok,
                      std::vector<std::pair<std::string_view, std::string_view>> *pairs, std::string *err);
     // The same query answered without copying when possible: *blob / *blob_len / *count describe the
@@ -195,16 +197,17 @@ private:
     PinVec<ParseResult> h_res_;
     PinVec<unsigned long long> h_words_;
 
-    // module index (csrc/index.cu)
-    DevBuf d_minfo_, d_crank_, d_crefs_;
-    DevBuf d_crec_[2], d_crec_excl_[2], d_cviol_[2], d_fviolbits_[2], d_fblob_[2], d_foff_[2];
+    // module index: the field lists field_find_kernel leaves at the end of the parse, packed on demand (csrc/index.cu)
+    DevBuf d_frefs_[2], d_find_status_;
+    DevBuf d_fviolbits_[2], d_fblob_[2], d_foff_[2];
     PinVec<uint8_t> h_fblob_[2];
     PinVec<uint32_t> h_foff_[2], h_fviolbits_[2];
     uint64_t index_version_ = 0;
     uint32_t index_m_[2] = {0, 0}, index_hint_[2] = {0, 0};   // per field: records in the index, where the last run ended
     bool index_module_ok_ = false;
-    BracketBuffers bb_{};  // bracket tables of the last parse (match / row are read by the index kernels)
-    ParseResult parsed_{};  // its verdict: where "module" is, among other things
+    ParseResult parsed_{};  // the verdict of the last parse: where "module" is, the sizes of the field lists
+    FieldIndexBuffers fx_{};   // the lists field_find_kernel filled, and the bracket tables it read (for a second run)
+    BracketBuffers bb_{};
 
     // results
     PinVec<uint8_t> h_out_;

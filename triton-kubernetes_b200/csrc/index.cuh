@@ -9,24 +9,27 @@
 
 namespace tk {
 
-struct ChildRef { uint32_t koff, klen, noff, nlen, hoff, hlen; };  // nlen / hlen == 0xffffffff: no such string field
-
-// device-side views of what child_pack_kernel reads and writes (field 0 = "name", 1 = "hostname")
-struct IndexTables {
-    const unsigned long long *rec[2];         // per child: (has field) << 32 | record bytes
-    const unsigned long long *rec_excl[2];    // its exclusive scan: (records before) << 32 | bytes before
-    const uint32_t *viol[2];                  // per child: 1 if its field does not sort strictly after the previous child's
-    uint8_t *blob[2];                         // packed result records of the children that have the field
-    uint32_t *off[2];                         // m + 1 offsets into blob, m = number of such children
-    uint32_t *viol_bits[2];                   // m bits, cleared beforehand
-    unsigned long long *totals;               // [2]: m << 32 | blob bytes
+// What State.Clusters() / State.Nodes() read (state/state.go:94-147): every string member called
+// "name" (field 0) or "hostname" (field 1) of an object that is a child of the root's "module", as
+// (field value, child key) references into the arena, in document order.
+struct FieldRef { uint32_t foff, flen, koff, klen; };
+struct FieldIndexBuffers {
+    FieldRef *refs[2];
+    uint32_t *off[2];             // cap + 1 entries: where record j starts in the packed blob; off[m] = its size
+    uint32_t cap[2];              // a list that outgrows its buffer is counted, not stored: the caller runs the kernel again
+    unsigned long long *status;   // field_status_words(n_rows) words, cleared by the launch wrapper
 };
+size_t field_status_words(uint32_t n_rows);
+// One pass over the rows of a tape the parser built; reads where "module" is from *res (rows_kernel
+// left it there) and leaves the list sizes in res->field_count / field_bytes.  n_rows_bound: the
+// grid covers that many rows; the real count is read from *res on the device.
+cudaError_t launch_field_find(const TapeView &t, uint32_t n_rows_bound, const uint32_t *br_match, const uint32_t *br_row, FieldIndexBuffers fx,
+                              ParseResult *res, cudaStream_t s);
 
-// refs must be pre-filled with 0xff bytes
-cudaError_t launch_child_refs(const TapeView &t, uint32_t module_row, const uint32_t *br_match, const uint32_t *br_row, const uint32_t *rank,
-                              ChildRef *refs, cudaStream_t s);
-cudaError_t launch_child_sizes(const uint8_t *arena, const ChildRef *refs, uint32_t n, unsigned long long *rec_n,
-                               unsigned long long *rec_h, uint32_t *viol_n, uint32_t *viol_h, cudaStream_t s);
-cudaError_t launch_child_pack(const uint8_t *arena, const ChildRef *refs, uint32_t n, const IndexTables &tb, cudaStream_t s);
+// Both lists packed into result records { u32 len, field, u32 len, key } at the offsets field_find
+// left (fx.off), in one launch; bit j of viol_bits[f] (m[f] bits, cleared beforehand) marks a record
+// whose field does not sort strictly after the record before.
+cudaError_t launch_field_pack(const uint8_t *arena, const FieldIndexBuffers &fx, const uint32_t m[2], uint32_t *const viol_bits[2],
+                              uint8_t *const blob[2], cudaStream_t s);
 
 }  // namespace tk

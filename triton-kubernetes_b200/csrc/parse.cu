@@ -379,15 +379,6 @@ template <class T> struct ArrayIn {
     const T *p;
     __device__ __forceinline__ T operator()(uint32_t i) const { return p[i]; }
 };
-struct ChildFlagIn {   // 1 for every row that starts a child of the object opened at row `first`
-    TapeView t;
-    uint32_t first;
-    const uint32_t *br_match, *br_row;
-    __device__ __forceinline__ uint32_t operator()(uint32_t r) const {
-        return starts_child(t.meta[r], r, first, closing_row(t, first, br_match, br_row)) ? 1u : 0u;
-    }
-};
-
 template <class T, class In>
 __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const In in, T *__restrict__ out, uint32_t n, u64 *scratch) {
     __shared__ uint32_t s_tile;
@@ -463,16 +454,6 @@ cudaError_t scan_u64(const unsigned long long *in, unsigned long long *out, uint
     if (e != cudaSuccess) return e;
     if (n == 0) return cudaSuccess;
     scan_kernel<u64><<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(ArrayIn<u64>{in}, out, n, scratch);
-    g_parse_launches++;
-    return cudaGetLastError();
-}
-cudaError_t scan_child_rank(const TapeView &t, uint32_t module_row, const uint32_t *br_match, const uint32_t *br_row, uint32_t *rank,
-                            unsigned long long *scratch, cudaStream_t s) {
-    const uint32_t n = t.n_rows;
-    cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words_u32(n) * 8, s);
-    if (e != cudaSuccess) return e;
-    if (n == 0) return cudaSuccess;
-    scan_kernel<uint32_t><<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_THREADS, 0, s>>>(ChildFlagIn{t, module_row, br_match, br_row}, rank, n, scratch);
     g_parse_launches++;
     return cudaGetLastError();
 }

@@ -62,6 +62,12 @@ struct ParseResult {
     unsigned int root_kind;       // RowKind of row 0
     unsigned int module_row;      // 1 + the row of the root object's "module" member; 0: there is none
     unsigned int module_kind;     // its RowKind
+    // module index (field_find_kernel, index.cu): per field -- 0 "name", 1 "hostname" -- how many
+    // children of "module" carry it as a string member, and the bytes of their packed result records;
+    // index_slow: a child had more members than the kernel walks through (Clusters / Nodes then use the host tree)
+    unsigned int field_count[2];
+    unsigned long long field_bytes[2];
+    unsigned int index_slow, pad_;
 };
 
 inline uint32_t p1_tiles(size_t n) { return (uint32_t)((n + P1_TILE - 1) / P1_TILE); }
@@ -137,11 +143,6 @@ size_t parse_scan_scratch_words(uint32_t n);
 cudaError_t scan_u32(const uint32_t *in, uint32_t *out, uint32_t n, unsigned long long *scratch, cudaStream_t s);
 // same for 64-bit words holding two packed sums (high half must stay below 2^30)
 cudaError_t scan_u64(const unsigned long long *in, unsigned long long *out, uint32_t n, unsigned long long *scratch, cudaStream_t s);
-// Children of "module" ranked in one pass: rank[r] = number of rows before r that start a child
-// (a depth-2 row other than a closer, strictly inside the member that opens at module_row); the
-// count lands in scratch[1].  scratch: parse_scan_scratch_words(t.n_rows) words.
-cudaError_t scan_child_rank(const TapeView &t, uint32_t module_row, const uint32_t *br_match, const uint32_t *br_row, uint32_t *rank,
-                            unsigned long long *scratch, cudaStream_t s);
 void count_parse_launch();
 unsigned long long parse_launch_count();
 

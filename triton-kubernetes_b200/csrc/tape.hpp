@@ -69,15 +69,6 @@ __device__ __forceinline__ int compare_bytes(const uint8_t *arena, uint32_t ao, 
     }
     return al < bl ? -1 : (al > bl ? 1 : 0);
 }
-// the row that closes the object opened at row `open_row` (voff of an opening row is its bracket)
-__device__ __forceinline__ uint32_t closing_row(const TapeView &t, uint32_t open_row, const uint32_t *br_match, const uint32_t *br_row) {
-    return br_row[br_match[t.voff[open_row]]];
-}
-// does row r start a child of the object that spans rows (first, last)?
-__device__ __forceinline__ bool starts_child(uint32_t meta, uint32_t r, uint32_t first, uint32_t last) {
-    const uint32_t kind = meta & 15u;
-    return r > first && r < last && (meta >> META_DEPTH_SHIFT) == 2 && kind != ROW_CLOSE_OBJ && kind != ROW_CLOSE_ARR;
-}
 #endif
 
 // Packed keys of the children of "module", in bytewise key order: key i is
