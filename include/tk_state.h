@@ -192,14 +192,18 @@ TK_API int tk_state_bytes_device(tk_state *s, const void **dev_out, size_t *out_
  * NULL = default stream) and the call returns without waiting for it.
  *
  * It calls no cudaMalloc, cudaFree or other allocating routine.  The scan's scratch (a tile
- * counter, a total and one status word per 256 rows) is a fixed array inside the library,
- * 65,552 bytes on every GPU that loads it, which limits n_rows to TK_NOALLOC_MAX_ROWS; larger
- * tapes are rejected with TK_ELIMIT and a message in err.  Things to know:
+ * counter, a total and one look-back status word per tile of 2,048 rows) is a fixed array inside
+ * the library, 8,208 bytes on every GPU that loads it, which limits n_rows to TK_NOALLOC_MAX_ROWS
+ * (1,024 tiles); larger tapes are rejected with TK_ELIMIT and a message in err.  Things to know:
  *   - the first call on each device looks up the array's device address; make that first call
  *     with the device current and before any stream capture begins;
  *   - every call on a GPU uses the same array, which keeps the previous call's contents: the
  *     part a call needs is cleared on `stream` first, and two calls whose GPU work overlaps
- *     (different streams, or different threads) race on it -- serialise them.
+ *     (different streams, or different threads) race on it -- serialise them;
+ *   - offsets are 32-bit.  The length of the whole text is summed in 64 bits inside the library's
+ *     scratch, where the caller cannot see it, so a text of 4 GiB or more is reported in band:
+ *     off_out[n_rows] is then 0xffffffff and the other offsets have wrapped and must not be used
+ *     (a real length never reaches 0xffffffff: tk_state_bytes refuses such documents too).
  * err (may be NULL) receives the error text; nothing is allocated for it either. */
 #define TK_NOALLOC_MAX_ROWS 2097152u
 TK_API int tk_row_offsets_noalloc(const uint32_t *meta, const uint32_t *koff, const uint32_t *klen,

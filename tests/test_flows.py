@@ -366,3 +366,108 @@ def test_vsphere_ladders(oracle, tmp_path):
     assert flows.create._expand_home("~/a") == os.path.expanduser("~") + "/a" and flows.create._expand_home("/abs") == "/abs"
     with pytest.raises(flows.FlowError):
         flows.create._expand_home("~other/a")
+
+
+# ------------------------------------------------------------------ the reference's silent-install examples as loader fixtures
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "silent-install")
+
+
+def test_silent_install_examples_load():
+    """examples/silent-install/*.yaml (copied by tests/golden/gen_silent_install.py) through the settings
+    loader: the keys it sees are the ones docs/guide/silent-install-yaml.md:11-49 documents.  (They need
+    the Triton API to RENDER -- create/manager_triton.go:179 -- not to LOAD.)"""
+    docs = json.load(open(os.path.join(GOLDEN, "docs_keys.json")))
+    m = Config.from_yaml(os.path.join(GOLDEN, "create-manager.yaml"), environ={})
+    keys = set(m._file)
+    assert keys <= set(docs["Cluster Manager YAML"])                                   # nothing undocumented in the example
+    assert set(docs["Cluster Manager YAML"]) - keys == {"manta_url"}                   # (documented for the manta backend only)
+    assert m.GetString("backend_provider") == "local" and m.GetString("name") == "test-manager"
+    assert m.IsSet("private_registry") and m.GetString("private_registry") == ""       # set to "" IS set: no prompt, no registry
+    assert m.GetStringSlice("triton_network_names") == ["Joyent-SDC-Public"]
+    assert m.GetString("triton_image_version") == "20180109" and m.GetString("rancher_admin_password") == "admin"
+    assert not m.IsSet("triton_key_id") and not m.IsSet("manager_cloud_provider")      # the example leaves the provider to the prompt
+    c = Config.from_yaml(os.path.join(GOLDEN, "cluster-triton-ha.yaml"), environ={"K8S_VERSION": "v1.10.0-rancher1-1"})
+    assert set(docs["Cluster YAML"]) <= set(c._file)
+    assert set(c._file) - set(docs["Cluster YAML"]) == {"triton_account", "triton_key_path", "triton_key_id", "triton_url"}
+    assert c.GetString("cluster_cloud_provider") == "triton" and c.GetString("k8s_version") == "v1.10.0-rancher1-1"   # AutomaticEnv
+    nodes = c.Get("nodes")
+    assert [n["node_count"] for n in nodes] == [3, 3, 4] and [n["rancher_host_label"] for n in nodes] == ["etcd", "control", "worker"]
+    assert all(n["triton_network_names"] == ["Joyent-SDC-Public"] for n in nodes)
+
+
+def test_silent_install_cluster_example_stops_at_the_cloud_api(oracle, tmp_path):
+    """The flow takes the example as far as the reference does without a network: manager selection and
+    the ladder run, then the Triton renderer is refused by name."""
+    store = tmp_path / "s"
+    os.makedirs(store / "test-manager")
+    from oracle import records as orec
+    from oracle.backend_local import LocalBackend as OB
+    cfg = Config.from_yaml(os.path.join(GOLDEN, "cluster-triton-ha.yaml"), environ={})
+    cfg.Set("non-interactive", True)
+    env = Env(state=oracle, backend=OB(str(store)), render=orec.render, module_source=orec.module_source, config=cfg)
+    assert "triton" in err(flows.create.new_cluster, env)
+
+
+# ------------------------------------------------------------------ the command line (cmd/root.go, cmd/create.go, cmd/destroy.go, cmd/get.go)
+
+def cli(argv):
+    main = importlib.import_module("triton-kubernetes_b200.__main__").main
+    lines = []
+    rc = main(argv, out=lines.append)
+    return rc, lines
+
+
+def test_cli_argument_checks(tmp_path):
+    assert cli(["create"]) == (1, ['Error: "triton-kubernetes create" requires one argument'])
+    assert cli(["destroy", "a", "b"]) == (1, ['Error: "triton-kubernetes destory" requires one argument'])      # (sic, cmd/destroy.go:22)
+    assert cli(["get", "node"]) == (1, ['Error: invalid argument "node" for "triton-kubernetes get"'])
+    assert cli(["create", "volume"]) == (1, ['Error: invalid argument "volume" for "triton-kubernetes create"'])
+    rc, lines = cli(["create", "manager"])
+    assert rc == 1 and "--non-interactive" in lines[-1]                                      # prompts are not part of this build
+    empty = tmp_path / "empty.yaml"
+    empty.write_text("{}\n")
+    assert cli(["--non-interactive", "--config", str(empty), "create", "manager"]) == \
+        (1, ["Running in non interactive mode", "Using config file: %s" % empty, "backend_provider must be provided"])
+    cfg = tmp_path / "c.yaml"
+    cfg.write_text("backend_provider: local\n")
+    assert cli(["--config=%s" % cfg, "--non-interactive", "--store", str(tmp_path / "s"), "get", "manager"]) == \
+        (1, ["Running in non interactive mode", "Using config file: %s" % cfg, "get manager called", "No cluster managers."])
+
+
+def _yaml(path, settings):
+    import yaml
+    with open(path, "w") as f:
+        yaml.safe_dump(settings, f)
+    return str(path)
+
+
+@pytest.mark.gpu
+def test_cli_configs_2_and_3_match_the_oracle_flows(tk, oracle, tmp_path, monkeypatch):
+    """BASELINE.json config #2 (`create manager --non-interactive`, local backend, terraform stubbed) and
+    config #3 (`create cluster` with three node groups) through the command line, product underneath;
+    the persisted documents equal what the same settings give through the oracle's flows."""
+    stub_dir = tmp_path / "bin"
+    os.makedirs(stub_dir)
+    stub = stub_dir / "terraform"
+    stub.write_text(STUB)
+    os.chmod(stub, os.stat(stub).st_mode | stat.S_IEXEC)
+    monkeypatch.setenv("PATH", str(stub_dir) + os.pathsep + os.environ["PATH"])
+    monkeypatch.setenv("TK_STUB_LOG", str(tmp_path / "stub.log"))
+    gpu, ora = str(tmp_path / "gpu"), str(tmp_path / "ora")
+    rc, lines = cli(["--non-interactive", "--config", _yaml(tmp_path / "m.yaml", dict(MANAGER, backend_provider="local")), "--store", gpu,
+                     "create", "manager"])
+    assert (rc, lines[0], lines[2]) == (0, "Running in non interactive mode", "create manager called")
+    rc, lines = cli(["--non-interactive", "--config", _yaml(tmp_path / "c.yaml", dict(CLUSTER, backend_provider="local")), "--store", gpu,
+                     "create", "cluster"])
+    assert rc == 0 and lines[-3:] == ["3 nodes added: c1-e-1, c1-e-2, c1-e-3", "1 node added: c1-c-1", "2 nodes added: c1-w-1, c1-w-2"]
+    make = oracle_factory(oracle)
+    flows.create.new_manager(make(ora, MANAGER))
+    flows.create.new_cluster(make(ora, CLUSTER))
+    a = open(os.path.join(gpu, "dev", "main.tf.json"), "rb").read().replace(gpu.encode(), b"<root>")
+    b = open(os.path.join(ora, "dev", "main.tf.json"), "rb").read().replace(ora.encode(), b"<root>")
+    assert a == b and len(json.loads(a)["module"]) == 8
+    rc, lines = cli(["--non-interactive", "--config", _yaml(tmp_path / "g.yaml", dict(backend_provider="local", cluster_manager="dev", cluster_name="c1")),
+                     "--store", gpu, "get", "cluster"])
+    assert rc == 0 and lines[2] == "get cluster called"
+    assert open(tmp_path / "stub.log").read().splitlines()[-1].startswith("output -module cluster_baremetal_c1 ")

@@ -4,10 +4,12 @@ Some users of this library cannot let it allocate GPU memory -- their program ga
 its own pool at start-up, or they sit on a latency-critical path where a cudaMalloc could stall
 the whole device.  For them the entry point takes every buffer from the caller.  This test plays
 such a caller: it builds the line tape itself, keeps it in its own device buffers, and checks
-the offsets it gets back against the text the ordinary entry point (tk_state_bytes) produces for
-the same document -- line r must start exactly where the allocation-free pass says it does.
-Two calls in a row, the second on a different and smaller document, show that what the first
-call left in the shared scratch does not leak into the second.
+the offsets it gets back against the text of the same document -- as the CPU oracle serialises it
+and as the ordinary entry point (tk_state_bytes) does: line r must start exactly where the
+allocation-free pass says it does.  Two calls in a row, the second on a different and smaller
+document and on a stream of the caller's own, show that what the first call left in the shared
+scratch does not leak into the second; around that second call the free device memory is read
+(cudaMemGetInfo) before and after, and must not have moved.
 
 Lives in a file of its own, named so that pytest collects it last.
 """
@@ -68,7 +70,7 @@ def build_tape(doc):
     return meta, koff, klen, voff, vlen, bytes(arena)
 
 
-def offsets_noalloc(tk, torch, doc):
+def offsets_noalloc(tk, torch, doc, own_stream=False, watch_memory=False):
     meta, koff, klen, voff, vlen, arena = build_tape(doc)
     n = len(meta)
     dev = torch.device("cuda", torch.cuda.current_device())
@@ -77,11 +79,16 @@ def offsets_noalloc(tk, torch, doc):
     a[:len(arena)] = torch.frombuffer(bytearray(arena or b"\0"), dtype=torch.uint8)[:len(arena)].to(dev)
     off = torch.full((n + 1,), -1, dtype=torch.int32, device=dev)
     err = ctypes.create_string_buffer(256)
-    stream = torch.cuda.current_stream().cuda_stream
+    side = torch.cuda.Stream() if own_stream else None                     # (created before the memory reading below)
+    stream = side.cuda_stream if own_stream else torch.cuda.current_stream().cuda_stream
+    torch.cuda.synchronize()                                               # the caller's buffers are ready on every stream
+    free_before = torch.cuda.mem_get_info()[0]
     rc = tk.state.lib().tk_row_offsets_noalloc(*[c.data_ptr() for c in cols], a.data_ptr(), len(arena), n,
                                                off.data_ptr(), stream, err, 256)
     assert rc == 0, err.value
     torch.cuda.synchronize()
+    if watch_memory:
+        assert torch.cuda.mem_get_info()[0] == free_before                 # nothing was allocated, by anyone, during the call
     return [x & 0xffffffff for x in off.tolist()]
 
 
@@ -103,11 +110,14 @@ def documents():
     return big, small
 
 
-def test_two_calls_in_a_row_match_the_ordinary_entry_point(tk):
+def test_two_calls_in_a_row_match_the_oracle_and_the_ordinary_entry_point(tk, oracle):
     import torch
-    for doc in documents():                                       # big first, then small: stale scratch must not matter
-        text = tk.New("noalloc", json.dumps(doc, ensure_ascii=False).encode("utf-8", "surrogateescape")).Bytes()
-        assert offsets_noalloc(tk, torch, doc) == offsets_from_text(text)
+    for i, doc in enumerate(documents()):                         # big first, then small: stale scratch must not matter
+        raw = json.dumps(doc, ensure_ascii=False).encode("utf-8", "surrogateescape")
+        want = oracle.New("noalloc", raw).Bytes()
+        assert tk.New("noalloc", raw).Bytes() == want
+        # the second call runs on a stream of the caller's own, with the free device memory watched
+        assert offsets_noalloc(tk, torch, doc, own_stream=i == 1, watch_memory=i == 1) == offsets_from_text(want)
 
 
 def test_sizes_beyond_the_fixed_scratch_are_rejected(tk):

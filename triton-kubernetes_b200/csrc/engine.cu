@@ -754,8 +754,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     }
     if ((e = d_find_status_.reserve(field_status_words(n_rows) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
     fx_.status = d_find_status_.as<unsigned long long>();
-    bb_ = bb;
-    if (n_rows && (e = timed(K_FIELD_FIND, [&] { return launch_field_find(tape_, n_rows, bb.match, bb.row, fx_, d_res, stream_); })) != cudaSuccess)
+    if (n_rows && (e = timed(K_FIELD_FIND, [&] { return launch_field_find(tape_, fx_, d_res, stream_); })) != cudaSuccess)
         return fail(e, "field_find", err);
     tr.mark("rest:queued");
     rc = fetch_result(err);
@@ -998,7 +997,7 @@ int Engine::build_index(const Document &doc, std::string *err) {
             fx_.off[f] = d_foff_[f].as<uint32_t>();
             fx_.cap[f] = (uint32_t)cap;
         }
-        e = timed(K_FIELD_FIND, [&] { return launch_field_find(tape_, tape_.n_rows, bb_.match, bb_.row, fx_, d_res_.as<ParseResult>(), stream_); });
+        e = timed(K_FIELD_FIND, [&] { return launch_field_find(tape_, fx_, d_res_.as<ParseResult>(), stream_); });
         if (e != cudaSuccess) return fail(e, "field_find", err);
     }
     uint32_t m[2] = {0, 0};

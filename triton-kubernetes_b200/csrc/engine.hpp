@@ -206,8 +206,7 @@ private:
     uint32_t index_m_[2] = {0, 0}, index_hint_[2] = {0, 0};   // per field: records in the index, where the last run ended
     bool index_module_ok_ = false;
     ParseResult parsed_{};  // the verdict of the last parse: where "module" is, the sizes of the field lists
-    FieldIndexBuffers fx_{};   // the lists field_find_kernel filled, and the bracket tables it read (for a second run)
-    BracketBuffers bb_{};
+    FieldIndexBuffers fx_{};   // the lists field_find_kernel filled (kept for a second run with more room)
 
     // results
     PinVec<uint8_t> h_out_;

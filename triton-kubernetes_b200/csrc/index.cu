@@ -31,119 +31,79 @@ __device__ __forceinline__ u64 ld_relaxed(const u64 *p) {
 __device__ __forceinline__ void st_relaxed(u64 *p, u64 v) { asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 
 // ---- the field lists ---------------------------------------------------------------------------
-// A row qualifies if it is a string member three levels down whose key reads "name" or "hostname";
-// the object it sits in is the first row above it that is no deeper than level 2, and that row
-// must open an object strictly inside "module".  A block takes 1,024 consecutive rows (and the 64
-// before them, for the search upwards) and keeps their meta words in shared memory; every thread
-// looks at four rows, a phase at a time -- key lengths, key offsets, key text, the child's and the
-// value's references -- so that the loads of a phase are in flight together.  The place of a
-// reference in its list, and of its record in the packed blob, is the number / the record bytes of
-// the qualifying rows before it: summed per block and handed from block to block by decoupled
-// look-back (one status word per field: count in the low 30 bits, bytes above), blocks taking
-// their tile from a ticket counter so that a block only ever waits for blocks that have started.
-constexpr int FF_THREADS = 256, FF_ITEMS = 4, FF_TILE = FF_THREADS * FF_ITEMS, FF_HALO = 64;
+// A row qualifies if key_order_kernel marked it (a string member three levels down whose key reads
+// "name" or "hostname"); the object it sits in is the first row above it that is no deeper than
+// level 2, and that row must open an object strictly inside "module".  A block takes 4,096
+// consecutive rows (and the 64 before them, for the search upwards) and brings their meta words
+// into shared memory; the few qualifying rows then fetch their value's and their child's key
+// reference.  The place of a reference in its list, and of its record in the packed blob, is the
+// number / the record bytes of the qualifying rows before it: summed per block and handed from
+// block to block by decoupled look-back (one status word per field: count in the low 30 bits,
+// bytes above), blocks taking their tile from a ticket counter so that a block only ever waits
+// for blocks that have started.  (4,096 rows per block: the 344 blocks of config #4 are all
+// resident at once, so the kernel is one wave.)
+constexpr int FF_THREADS = 512, FF_ITEMS = 8, FF_TILE = FF_THREADS * FF_ITEMS, FF_HALO = 64;
 constexpr uint32_t FF_MAX_WALK = 4096;   // rows looked through for the child before giving up (index_slow)
 
-__global__ void __launch_bounds__(FF_THREADS) field_find_kernel(TapeView t, const uint32_t *__restrict__ br_match, const uint32_t *__restrict__ br_row,
-                                                               FieldIndexBuffers fx, ParseResult *res) {
-    __shared__ uint32_t s_tile, s_module_row, s_module_end;
+__global__ void __launch_bounds__(FF_THREADS, 3) field_find_kernel(TapeView t, uint32_t n_rows, FieldIndexBuffers fx, ParseResult *res) {
+    __shared__ uint32_t s_tile;
     __shared__ uint32_t s_meta[FF_HALO + FF_TILE];
+    __shared__ uint16_t s_up[FF_TILE];            // field rows: rows between the row and its child (at most FF_MAX_WALK)
     __shared__ u64 s_wc[FF_THREADS / 32], s_wb0[FF_THREADS / 32], s_wb1[FF_THREADS / 32];
     __shared__ u64 s_prefix[2];   // per field: records before this block | record bytes before it << 32
-    const uint32_t n_rows = res->n_rows;
-    if (threadIdx.x == 0) {
-        s_tile = (uint32_t)atomicAdd(&fx.status[0], 1ull);
-        // "module" must be an object member of a root object; its closing row through the bracket tables
-        uint32_t first = 0xffffffffu, last = 0;
-        if (res->invalid == 0 && res->root_kind == ROW_OPEN_OBJ && res->module_row != 0 && res->module_kind == ROW_OPEN_OBJ) {
-            first = res->module_row - 1;
-            const uint32_t ob = t.voff[first];               // voff of an opening row: its bracket
-            const uint32_t cb = br_match[ob];
-            last = cb != 0xffffffffu ? br_row[cb] : 0;
-        }
-        s_module_row = first;
-        s_module_end = last;
+    if (threadIdx.x == 0) s_tile = (uint32_t)atomicAdd(&fx.status[0], 1ull);
+    // where "module" is: an object member of a root object (rows_kernel and key_order_kernel left it in *res)
+    uint32_t module_row = 0xffffffffu, module_end = 0;
+    if (res->invalid == 0 && res->root_kind == ROW_OPEN_OBJ && res->module_row != 0 && res->module_kind == ROW_OPEN_OBJ) {
+        module_row = res->module_row - 1;
+        module_end = res->module_end;
     }
     __syncthreads();
     const uint32_t tile = s_tile, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t n_tiles = (n_rows + FF_TILE - 1) / FF_TILE;
-    if (tile >= n_tiles) return;                             // (the grid covers a bound on the row count)
-    const uint32_t module_row = s_module_row, module_end = s_module_end;
     const uint32_t tile0 = tile * FF_TILE;
     for (uint32_t x = threadIdx.x; x < FF_HALO + FF_TILE; x += FF_THREADS) {
         const long long r = (long long)tile0 - FF_HALO + x;
         s_meta[x] = r >= 0 && r < (long long)n_rows ? __ldg(t.meta + r) : 0u;   // (depth 0: stops any search upwards)
     }
     __syncthreads();
-    const uint32_t *meta_at = s_meta + FF_HALO - tile0;       // meta_at[r] for rows in the window
-    const uint32_t base = tile0 + threadIdx.x * FF_ITEMS;
+    const uint32_t base = tile0 + threadIdx.x * FF_ITEMS, sbase = FF_HALO + threadIdx.x * FF_ITEMS;   // rows, and their place in the window
 
-    // phase 1: which rows can be field rows at all
-    uint32_t kl[FF_ITEMS], ko[FF_ITEMS], fld[FF_ITEMS];
-    bool cand[FF_ITEMS];
+    // per row: 0 / 1 the field, 2 not a field row (two bits each in fbits); how far up the child's row is
+    uint32_t fbits = 0;
 #pragma unroll
-    for (int q = 0; q < FF_ITEMS; q++) {
-        const uint32_t r = base + q;
-        const bool in = r < n_rows && r > module_row && r < module_end;
-        const uint32_t meta = in ? meta_at[r] : 0u;
-        cand[q] = in && (meta >> META_DEPTH_SHIFT) == 3 && (meta & (15u | META_HAS_KEY)) == (ROW_STR | META_HAS_KEY);
-        kl[q] = cand[q] ? __ldg(t.klen + r) : 0u;
-    }
-#pragma unroll
-    for (int q = 0; q < FF_ITEMS; q++) {
-        cand[q] = cand[q] && (kl[q] == 4 || kl[q] == 8);
-        ko[q] = cand[q] ? __ldg(t.koff + base + q) : 0u;
-    }
-    // phase 2: the key text, as three aligned words that cover its 8 bytes
-    uint32_t w[FF_ITEMS][3];
-#pragma unroll
-    for (int q = 0; q < FF_ITEMS; q++) {
-        const uint32_t *p = reinterpret_cast<const uint32_t *>(t.arena + (ko[q] & ~3u));
-#pragma unroll
-        for (int k = 0; k < 3; k++) w[q][k] = cand[q] ? __ldg(p + k) : 0u;
-    }
-    // phase 3: the child (searched in shared memory; past the window, in global memory) and the references
-    FieldRef ref[FF_ITEMS];
-    uint32_t child[FF_ITEMS];
-#pragma unroll
-    for (int q = 0; q < FF_ITEMS; q++) {
-        fld[q] = 2;
-        child[q] = 0;
-        if (!cand[q]) continue;
-        const uint32_t sh = (ko[q] & 3u) * 8u;
-        const uint32_t a = __byte_perm(__funnelshift_r(w[q][0], w[q][1], sh), 0, 0x0123), b = __byte_perm(__funnelshift_r(w[q][1], w[q][2], sh), 0, 0x0123);
+    for (int i = 0; i < FF_ITEMS; i++) {
+        const uint32_t r = base + i, meta = s_meta[sbase + i];
         uint32_t f = 2;
-        if (kl[q] == 4) { if (a == 0x6e616d65u) f = 0; }                          // "name"
-        else if (a == 0x686f7374u && b == 0x6e616d65u) f = 1;                      // "hostname"
-        if (f == 2) continue;
-        const uint32_t r = base + q;
-        uint32_t c = r, cm = 0;
-        bool found = false;
-        for (uint32_t step = 0; step < FF_MAX_WALK && c > module_row + 1; step++) {
-            c--;
-            cm = c + FF_HALO >= tile0 ? meta_at[c] : __ldg(t.meta + c);
-            if ((cm >> META_DEPTH_SHIFT) <= 2) { found = true; break; }
+        if (r < n_rows && r > module_row && r < module_end && (meta & (META_KEY_IS_NAME | META_KEY_IS_HOSTNAME))) {
+            f = (meta & META_KEY_IS_HOSTNAME) ? 1u : 0u;
+            // the child: searched upwards in the window; past it, in global memory
+            uint32_t c = r, cm = 0;
+            bool found = false;
+            for (uint32_t step = 0; step < FF_MAX_WALK && c > module_row + 1; step++) {
+                c--;
+                cm = c + FF_HALO >= tile0 ? s_meta[c + FF_HALO - tile0] : __ldg(t.meta + c);
+                if ((cm >> META_DEPTH_SHIFT) <= 2) { found = true; break; }
+            }
+            if (!found) { if (c > module_row + 1) res->index_slow = 1; f = 2; }
+            else if ((cm >> META_DEPTH_SHIFT) != 2 || (cm & 15u) != ROW_OPEN_OBJ || !(cm & META_HAS_KEY)) f = 2;
+            s_up[threadIdx.x * FF_ITEMS + i] = (uint16_t)(r - c);
         }
-        if (!found) { if (c > module_row + 1) res->index_slow = 1; continue; }
-        if ((cm >> META_DEPTH_SHIFT) != 2 || (cm & 15u) != ROW_OPEN_OBJ || !(cm & META_HAS_KEY)) continue;
-        fld[q] = f;
-        child[q] = c;
+        fbits |= f << (2 * i);
     }
+    // (a thread has a field row or two at most: their four loads go out together, row after row)
+    auto load_ref = [&](int i) {
+        const uint32_t r = base + i, c = r - s_up[threadIdx.x * FF_ITEMS + i];
+        return FieldRef{__ldg(t.voff + r), __ldg(t.vlen + r), __ldg(t.koff + c), __ldg(t.klen + c)};
+    };
     u64 cnt = 0, b0 = 0, b1 = 0;                               // count of field 0 | count of field 1 << 32; record bytes per field
 #pragma unroll
-    for (int q = 0; q < FF_ITEMS; q++) {
-        const bool is = fld[q] != 2;
-        const uint32_t r = base + q;
-        ref[q].foff = is ? __ldg(t.voff + r) : 0u;
-        ref[q].flen = is ? __ldg(t.vlen + r) : 0u;
-        ref[q].koff = is ? __ldg(t.koff + child[q]) : 0u;
-        ref[q].klen = is ? __ldg(t.klen + child[q]) : 0u;
-    }
-#pragma unroll
-    for (int q = 0; q < FF_ITEMS; q++) {
-        if (fld[q] == 2) continue;
-        const u64 rec = 8ull + ref[q].flen + ref[q].klen;      // { u32 len, field, u32 len, key }
-        if (fld[q]) { cnt += 1ull << 32; b1 += rec; } else { cnt += 1ull; b0 += rec; }
+    for (int i = 0; i < FF_ITEMS; i++) {
+        const uint32_t f = (fbits >> (2 * i)) & 3u;
+        if (f == 2) continue;
+        const FieldRef ref = load_ref(i);
+        const u64 rec = 8ull + ref.flen + ref.klen;            // { u32 len, field, u32 len, key }
+        if (f) { cnt += 1ull << 32; b1 += rec; } else { cnt += 1ull; b0 += rec; }
     }
 
     // exclusive scans over the block
@@ -156,6 +116,7 @@ __global__ void __launch_bounds__(FF_THREADS) field_find_kernel(TapeView t, cons
     if (lane == 31) { s_wc[warp] = ic; s_wb0[warp] = i0; s_wb1[warp] = i1; }
     __syncthreads();
     u64 wc = 0, w0 = 0, w1 = 0, tc = 0, t0 = 0, t1 = 0;
+#pragma unroll
     for (uint32_t i = 0; i < FF_THREADS / 32; i++) {
         if (i < warp) { wc += s_wc[i]; w0 += s_wb0[i]; w1 += s_wb1[i]; }
         tc += s_wc[i]; t0 += s_wb0[i]; t1 += s_wb1[i];
@@ -199,65 +160,110 @@ __global__ void __launch_bounds__(FF_THREADS) field_find_kernel(TapeView t, cons
         }
     }
     __syncthreads();
-    uint32_t rank[2] = {(uint32_t)s_prefix[0] + (uint32_t)(wc + ic - cnt), (uint32_t)s_prefix[1] + (uint32_t)((wc + ic - cnt) >> 32)};
-    uint32_t at_byte[2] = {(uint32_t)(s_prefix[0] >> 32) + (uint32_t)(w0 + i0 - b0), (uint32_t)(s_prefix[1] >> 32) + (uint32_t)(w1 + i1 - b1)};
+    uint32_t rank0 = (uint32_t)s_prefix[0] + (uint32_t)(wc + ic - cnt), rank1 = (uint32_t)s_prefix[1] + (uint32_t)((wc + ic - cnt) >> 32);
+    uint32_t byte0 = (uint32_t)(s_prefix[0] >> 32) + (uint32_t)(w0 + i0 - b0), byte1 = (uint32_t)(s_prefix[1] >> 32) + (uint32_t)(w1 + i1 - b1);
 #pragma unroll
-    for (int q = 0; q < FF_ITEMS; q++) {
-        if (fld[q] == 2) continue;
-        const uint32_t f = fld[q], at = rank[f]++;
-        if (at < fx.cap[f]) { fx.refs[f][at] = ref[q]; fx.off[f][at] = at_byte[f]; }
-        at_byte[f] += 8u + ref[q].flen + ref[q].klen;
+    for (int i = 0; i < FF_ITEMS; i++) {
+        const uint32_t f = (fbits >> (2 * i)) & 3u;
+        if (f == 2) continue;
+        const FieldRef ref = load_ref(i);
+        const uint32_t rec = 8u + ref.flen + ref.klen;
+        const uint32_t at = f ? rank1 : rank0, at_byte = f ? byte1 : byte0;
+        if (f) { rank1++; byte1 += rec; } else { rank0++; byte0 += rec; }
+        if (at < fx.cap[f]) { fx.refs[f][at] = ref; fx.off[f][at] = at_byte; }
     }
 }
 
 // ---- the packed records ------------------------------------------------------------------------
-// One warp per PACK_RECORDS records of one field (both fields in one launch): the first lanes
-// fetch one reference each and say whether their field sorts strictly after the record before
-// (viol_bits: m bits per field, cleared beforehand), then the warp writes the records one after
-// another, a lane per byte, so that the stores of a record are contiguous.  (Few records per warp:
-// the copy loop is a chain of L2 round trips, and it is the number of warps in flight that hides
-// them.)
-constexpr uint32_t PACK_RECORDS = 8;
+// A block takes PACK_RECORDS consecutive records of one field (both fields in one launch).  Every
+// thread builds its record -- { u32 len, field, u32 len, key } -- in shared memory at the place it
+// has among the block's records, reading the two strings as aligned words, and says whether its
+// field sorts strictly after the record before (viol_bits: m bits per field, cleared beforehand);
+// the block then copies the finished stretch to the blob with coalesced stores.  Records too long
+// for the staging area (PACK_STAGE bytes for the block) are written straight to the blob.
+constexpr uint32_t PACK_RECORDS = 64, PACK_STAGE = 8192;
 struct PackArgs {
     const FieldRef *refs[2];
     const uint32_t *off[2];
     uint32_t *viol_bits[2];
     uint8_t *blob[2];
     uint32_t m[2];
-    uint32_t warps0;   // warps that work on field 0; the rest on field 1
+    uint32_t blocks0;   // blocks that work on field 0; the rest on field 1
 };
-__global__ void __launch_bounds__(128) field_pack_kernel(const uint8_t *__restrict__ arena, PackArgs a) {
-    const uint32_t lane = threadIdx.x & 31;
-    uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t f = warp >= a.warps0 ? 1u : 0u;
-    if (f) warp -= a.warps0;
+__device__ __forceinline__ void put_u32(uint8_t *dst, uint32_t v) { dst[0] = (uint8_t)v; dst[1] = (uint8_t)(v >> 8); dst[2] = (uint8_t)(v >> 16); dst[3] = (uint8_t)(v >> 24); }
+// n bytes of the arena from offset off to dst (any alignment on both sides), read as aligned words,
+// COPY_BATCH words at a time so that the loads of a batch are in flight together
+constexpr int COPY_BATCH = 12;
+__device__ __forceinline__ void copy_string(uint8_t *dst, const uint8_t *__restrict__ arena, uint32_t off, uint32_t n) {
+    const uint32_t *wp = reinterpret_cast<const uint32_t *>(arena + (off & ~3u));
+    const uint32_t sh = (off & 3u) * 8u;
+    for (uint32_t i0 = 0; i0 < n; i0 += 4 * COPY_BATCH) {
+        uint32_t v[COPY_BATCH + 1];
+#pragma unroll
+        for (int k = 0; k <= COPY_BATCH; k++) v[k] = i0 + 4 * k < n + 4 ? __ldg(wp + (i0 >> 2) + k) : 0u;   // (every arena is readable 7 bytes past a string)
+#pragma unroll
+        for (int k = 0; k < COPY_BATCH; k++) {
+            const uint32_t i = i0 + 4 * k;
+            if (i >= n) break;
+            const uint32_t x = __funnelshift_r(v[k], v[k + 1], sh), left = n - i;
+            dst[i] = (uint8_t)x;
+            if (left > 1) dst[i + 1] = (uint8_t)(x >> 8);
+            if (left > 2) dst[i + 2] = (uint8_t)(x >> 16);
+            if (left > 3) dst[i + 3] = (uint8_t)(x >> 24);
+        }
+    }
+}
+// memcmp-style order of two byte strings in shared or global memory, byte by byte (short strings)
+__device__ __forceinline__ int compare_plain(const uint8_t *a, uint32_t al, const uint8_t *b, uint32_t bl) {
+    const uint32_t m = al < bl ? al : bl;
+    for (uint32_t i = 0; i < m; i++)
+        if (a[i] != b[i]) return a[i] < b[i] ? -1 : 1;
+    return al < bl ? -1 : (al > bl ? 1 : 0);
+}
+__global__ void __launch_bounds__(PACK_RECORDS) field_pack_kernel(const uint8_t *__restrict__ arena, PackArgs a) {
+    __shared__ __align__(16) uint8_t s_stage[PACK_STAGE + 16];
+    uint32_t block = blockIdx.x;
+    const uint32_t f = block >= a.blocks0 ? 1u : 0u;
+    if (f) block -= a.blocks0;
     const uint32_t m = a.m[f];
     const FieldRef *refs = a.refs[f];
-    const uint32_t j = lane < PACK_RECORDS ? warp * PACK_RECORDS + lane : m;   // this lane's record (none for the other lanes)
+    const uint32_t *off = a.off[f];
+    const uint32_t j0 = block * PACK_RECORDS, j = j0 + threadIdx.x, j1 = min(j0 + PACK_RECORDS, m);
+    const uint32_t out0 = off[j0], out1 = off[j1];       // the block's stretch of the blob (off has m + 1 entries)
+    const uint32_t shift = out0 & 15u;                     // staged at the blob's own 16-byte phase
+    const bool staged = shift + (out1 - out0) <= PACK_STAGE;
+    uint8_t *blob = a.blob[f];
     FieldRef c = {0, 0, 0, 0};
     uint32_t at = 0;
-    if (j < m) { c = refs[j]; at = a.off[f][j]; }
-    // field order against the record before: the lane below holds it, lane 0 fetches it
-    {
-        uint32_t po = __shfl_up_sync(FULL, c.foff, 1), pl = __shfl_up_sync(FULL, c.flen, 1);
-        if (lane == 0 && j > 0 && j < m) { const FieldRef p = refs[j - 1]; po = p.foff; pl = p.flen; }
-        if (j > 0 && j < m && compare_bytes(arena, po, pl, c.foff, c.flen) >= 0) atomicOr(a.viol_bits[f] + (j >> 5), 1u << (j & 31));
-    }
-    uint8_t *blob = a.blob[f];
-    for (unsigned who = __ballot_sync(FULL, j < m); who; who &= who - 1) {
-        const int src = __ffs(who) - 1;
-        const uint32_t r_fo = __shfl_sync(FULL, c.foff, src), r_fl = __shfl_sync(FULL, c.flen, src);
-        const uint32_t r_ko = __shfl_sync(FULL, c.koff, src), r_kl = __shfl_sync(FULL, c.klen, src);
-        uint8_t *w = blob + __shfl_sync(FULL, at, src);
-        const uint32_t total = 8 + r_fl + r_kl;
-        for (uint32_t x = lane; x < total; x += 32) {
-            uint32_t v;
-            if (x < 4) v = r_fl >> (8 * x);
-            else if (x < 4 + r_fl) v = arena[r_fo + x - 4];
-            else if (x < 8 + r_fl) v = r_kl >> (8 * (x - 4 - r_fl));
-            else v = arena[r_ko + x - 8 - r_fl];
-            w[x] = (uint8_t)v;
+    if (j < m) {
+        c = refs[j];
+        at = off[j];
+        uint8_t *w = staged ? s_stage + shift + (at - out0) : blob + at;
+        put_u32(w, c.flen);
+        copy_string(w + 4, arena, c.foff, c.flen);
+        put_u32(w + 4 + c.flen, c.klen);
+        copy_string(w + 8 + c.flen, arena, c.koff, c.klen);
+        // field order against the record before: the block's first record (and any record of a block that is
+        // not staged) fetches its predecessor's field from the arena, the others find it in the staging area
+        if (j > 0 && (!staged || j == j0)) {
+            const FieldRef p = refs[j - 1];
+            if (compare_bytes(arena, p.foff, p.flen, c.foff, c.flen) >= 0) atomicOr(a.viol_bits[f] + (j >> 5), 1u << (j & 31));
         }
+    }
+    if (!staged) return;
+    __syncthreads();
+    if (j < m && j > j0) {
+        const uint8_t *mine = s_stage + shift + (at - out0), *prev = s_stage + shift + (off[j - 1] - out0);
+        uint32_t pl = (uint32_t)prev[0] | ((uint32_t)prev[1] << 8) | ((uint32_t)prev[2] << 16) | ((uint32_t)prev[3] << 24);
+        if (compare_plain(prev + 4, pl, mine + 4, c.flen) >= 0) atomicOr(a.viol_bits[f] + (j >> 5), 1u << (j & 31));
+    }
+    // whole 16-byte chunks as vectors, the ragged first and last chunk (shared with the neighbouring blocks) byte by byte
+    uint8_t *g = blob + (out0 - shift);
+    const uint32_t end = shift + (out1 - out0), chunks = (end + 15u) >> 4;
+    for (uint32_t c = threadIdx.x; c < chunks; c += PACK_RECORDS) {
+        const uint32_t b0 = c << 4;
+        if (b0 >= shift && b0 + 16 <= end) reinterpret_cast<uint4 *>(g)[c] = reinterpret_cast<const uint4 *>(s_stage)[c];
+        else for (uint32_t b = max(b0, shift); b < min(b0 + 16, end); b++) g[b] = s_stage[b];
     }
 }
 
@@ -265,15 +271,14 @@ __global__ void __launch_bounds__(128) field_pack_kernel(const uint8_t *__restri
 
 size_t field_status_words(uint32_t n_rows) { return 2 + 2 * (size_t)((n_rows + FF_TILE - 1) / FF_TILE); }
 
-cudaError_t launch_field_find(const TapeView &t, uint32_t n_rows_bound, const uint32_t *br_match, const uint32_t *br_row, FieldIndexBuffers fx,
-                              ParseResult *res, cudaStream_t s) {
-    cudaError_t e = cudaMemsetAsync(fx.status, 0, field_status_words(n_rows_bound) * 8, s);   // ticket counter and look-back status words
+cudaError_t launch_field_find(const TapeView &t, FieldIndexBuffers fx, ParseResult *res, cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(fx.status, 0, field_status_words(t.n_rows) * 8, s);   // ticket counter and look-back status words
     if (e != cudaSuccess) return e;
     // (a second run -- with larger lists -- starts the totals again)
     if ((e = cudaMemsetAsync(reinterpret_cast<char *>(res) + offsetof(ParseResult, field_count), 0,
                              sizeof(ParseResult) - offsetof(ParseResult, field_count), s)) != cudaSuccess) return e;
-    if (n_rows_bound == 0) return cudaSuccess;
-    field_find_kernel<<<(n_rows_bound + FF_TILE - 1) / FF_TILE, FF_THREADS, 0, s>>>(t, br_match, br_row, fx, res);
+    if (t.n_rows == 0) return cudaSuccess;
+    field_find_kernel<<<(t.n_rows + FF_TILE - 1) / FF_TILE, FF_THREADS, 0, s>>>(t, t.n_rows, fx, res);
     count_parse_launch();
     return cudaGetLastError();
 }
@@ -281,14 +286,14 @@ cudaError_t launch_field_find(const TapeView &t, uint32_t n_rows_bound, const ui
 cudaError_t launch_field_pack(const uint8_t *arena, const FieldIndexBuffers &fx, const uint32_t m[2], uint32_t *const viol_bits[2],
                               uint8_t *const blob[2], cudaStream_t s) {
     PackArgs a;
-    uint32_t warps[2];
+    uint32_t blocks[2];
     for (int f = 0; f < 2; f++) {
         a.refs[f] = fx.refs[f]; a.off[f] = fx.off[f]; a.viol_bits[f] = viol_bits[f]; a.blob[f] = blob[f]; a.m[f] = m[f];
-        warps[f] = (m[f] + PACK_RECORDS - 1) / PACK_RECORDS;
+        blocks[f] = (m[f] + PACK_RECORDS - 1) / PACK_RECORDS;
     }
-    a.warps0 = warps[0];
-    if (warps[0] + warps[1] == 0) return cudaSuccess;
-    field_pack_kernel<<<(warps[0] + warps[1] + 3) / 4, 128, 0, s>>>(arena, a);
+    a.blocks0 = blocks[0];
+    if (blocks[0] + blocks[1] == 0) return cudaSuccess;
+    field_pack_kernel<<<blocks[0] + blocks[1], PACK_RECORDS, 0, s>>>(arena, a);
     count_parse_launch();
     return cudaGetLastError();
 }

@@ -20,11 +20,9 @@ struct FieldIndexBuffers {
     unsigned long long *status;   // field_status_words(n_rows) words, cleared by the launch wrapper
 };
 size_t field_status_words(uint32_t n_rows);
-// One pass over the rows of a tape the parser built; reads where "module" is from *res (rows_kernel
-// left it there) and leaves the list sizes in res->field_count / field_bytes.  n_rows_bound: the
-// grid covers that many rows; the real count is read from *res on the device.
-cudaError_t launch_field_find(const TapeView &t, uint32_t n_rows_bound, const uint32_t *br_match, const uint32_t *br_row, FieldIndexBuffers fx,
-                              ParseResult *res, cudaStream_t s);
+// One pass over the rows of a tape the parser built; reads where "module" is from *res (rows_kernel and
+// key_order_kernel left it there) and leaves the list sizes in res->field_count / field_bytes.
+cudaError_t launch_field_find(const TapeView &t, FieldIndexBuffers fx, ParseResult *res, cudaStream_t s);
 
 // Both lists packed into result records { u32 len, field, u32 len, key } at the offsets field_find
 // left (fx.off), in one launch; bit j of viol_bits[f] (m[f] bits, cleared beforehand) marks a record

@@ -181,9 +181,6 @@ __device__ __forceinline__ void st_status(unsigned long long *p, unsigned long l
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-constexpr int RO_ITEMS = 8;                             // consecutive rows per thread
-constexpr int RO_TILE = EMIT_THREADS * RO_ITEMS;        // 2,048 rows per block: one look-back per 2,048 rows
-
 __global__ void __launch_bounds__(EMIT_THREADS) row_offsets_kernel(TapeView t, uint32_t *__restrict__ off,
                                                                   unsigned long long *scratch) {
     __shared__ unsigned long long s_warp_sum[WARPS];
@@ -282,7 +279,7 @@ __global__ void __launch_bounds__(EMIT_THREADS) row_offsets_kernel(TapeView t, u
     for (int j = 0; j < RO_ITEMS; j++) {
         if (r0 + j < t.n_rows) off[r0 + j] = (uint32_t)o;
         o += len[j];
-        if (r0 + j + 1 == t.n_rows) off[r0 + j + 1] = (uint32_t)o;
+        if (r0 + j + 1 == t.n_rows) off[r0 + j + 1] = o >= 0xffffffffull ? 0xffffffffu : (uint32_t)o;   // (4 GiB or more: the offsets have wrapped)
     }
 }
 
@@ -550,7 +547,7 @@ __global__ void __launch_bounds__(PREFIX_THREADS) prefix_match_kernel(KeyIndexVi
 cudaError_t launch_row_offsets(const TapeView &t, uint32_t *off, unsigned long long *scratch, cudaStream_t s) {
     cudaError_t e = cudaMemsetAsync(scratch, 0, scan_scratch_words(t.n_rows) * sizeof(unsigned long long), s);
     if (e != cudaSuccess) return e;
-    row_offsets_kernel<<<(t.n_rows + RO_TILE - 1) / RO_TILE, EMIT_THREADS, 0, s>>>(t, off, scratch);
+    row_offsets_kernel<<<row_offsets_tiles(t.n_rows), EMIT_THREADS, 0, s>>>(t, off, scratch);
     g_launches++;
     return cudaGetLastError();
 }
@@ -594,9 +591,9 @@ cudaError_t launch_prefix_match(const KeyIndexView &k, const uint8_t *prefix, ui
 // has budgeted for something else), and code on a latency-critical path where cudaMalloc /
 // cudaFree are unwelcome because they can synchronise the whole device and stall unrelated
 // streams.  Such a caller owns every input and output buffer; the only thing the offset pass
-// needs beyond those is its small scan scratch (one tile counter, one total, one status word
-// per 256-row tile), and here that lives in the fixed array below instead of a cudaMalloc'd
-// buffer.  The price is a size limit and one shared scratch per GPU.
+// needs beyond those is its small scan scratch (one tile counter, one total, one look-back status
+// word per tile of 2,048 rows), and here that lives in the fixed array below instead of a
+// cudaMalloc'd buffer.  The price is a size limit and one shared scratch per GPU.
 // ---------------------------------------------------------------------------------------------
 
 #include <cstdio>
@@ -606,8 +603,9 @@ cudaError_t launch_prefix_match(const KeyIndexView &k, const uint8_t *prefix, ui
 
 namespace {
 
-constexpr uint32_t NOALLOC_MAX_TILES = TK_NOALLOC_MAX_ROWS / tk::EMIT_ROWS_PER_BLOCK;
-// 2 + 8192 words = 65,552 bytes of device memory per GPU that loads this library, held until
+constexpr uint32_t NOALLOC_MAX_TILES = TK_NOALLOC_MAX_ROWS / tk::RO_TILE;
+static_assert(TK_NOALLOC_MAX_ROWS % tk::RO_TILE == 0, "the row limit is a whole number of tiles");
+// 2 + 1,024 words = 8,208 bytes of device memory per GPU that loads this library, held until
 // the process exits.
 static __device__ __align__(256) unsigned long long g_noalloc_scratch[2 + NOALLOC_MAX_TILES];
 
@@ -638,15 +636,21 @@ extern "C" int tk_row_offsets_noalloc(const uint32_t *meta, const uint32_t *koff
     if (n_rows == 0 || n_rows > TK_NOALLOC_MAX_ROWS) {
         if (err && err_cap)
             snprintf(err, err_cap, "tk_row_offsets_noalloc: n_rows = %u is outside 1..%u (the fixed scratch holds one status word per %d rows)",
-                     n_rows, (unsigned)TK_NOALLOC_MAX_ROWS, tk::EMIT_ROWS_PER_BLOCK);
+                     n_rows, (unsigned)TK_NOALLOC_MAX_ROWS, tk::RO_TILE);
         return TK_ELIMIT;
     }
     int dev = -1;
     cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess || dev < 0 || dev >= NOALLOC_MAX_DEVICES) {
+    if (e != cudaSuccess) {
         noalloc_err(err, err_cap, "tk_row_offsets_noalloc: cudaGetDevice", e);
         (void)cudaGetLastError();
         return TK_ECUDA;
+    }
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) {
+        if (err && err_cap)
+            snprintf(err, err_cap, "tk_row_offsets_noalloc: device index %d is outside 0..%d, the devices this entry point keeps an address for",
+                     dev, NOALLOC_MAX_DEVICES - 1);
+        return TK_ELIMIT;
     }
     unsigned long long *scratch;
     {
@@ -673,7 +677,7 @@ extern "C" int tk_row_offsets_noalloc(const uint32_t *meta, const uint32_t *koff
     // the array still holds the previous call's counter and status words: they must start at zero
     e = cudaMemsetAsync(scratch, 0, tk::scan_scratch_words(n_rows) * sizeof(unsigned long long), s);
     if (e == cudaSuccess) {
-        tk::row_offsets_kernel<<<(n_rows + tk::RO_TILE - 1) / tk::RO_TILE, tk::EMIT_THREADS, 0, s>>>(t, off_out, scratch);
+        tk::row_offsets_kernel<<<tk::row_offsets_tiles(n_rows), tk::EMIT_THREADS, 0, s>>>(t, off_out, scratch);
         tk::g_launches++;
         e = cudaGetLastError();
     }

@@ -16,11 +16,17 @@ constexpr int WARP_OUT_BYTES = 4096;                    // per-warp staging of o
 
 inline uint32_t emit_tiles(uint32_t n_rows) { return (n_rows + EMIT_ROWS_PER_BLOCK - 1) / EMIT_ROWS_PER_BLOCK; }
 
-// scratch needed by row_offsets: 2 + tiles 64-bit words (tile counter, total, per-tile status)
-inline size_t scan_scratch_words(uint32_t n_rows) { return 2 + (size_t)emit_tiles(n_rows); }
+// row_offsets works on tiles of RO_TILE rows; its scratch is 2 + tiles 64-bit words (tile counter,
+// total, one look-back status word per tile)
+constexpr int RO_ITEMS = 8;                             // consecutive rows per thread
+constexpr int RO_TILE = EMIT_THREADS * RO_ITEMS;        // 2,048 rows per block: one look-back per 2,048 rows
+inline uint32_t row_offsets_tiles(uint32_t n_rows) { return (n_rows + RO_TILE - 1) / RO_TILE; }
+inline size_t scan_scratch_words(uint32_t n_rows) { return 2 + (size_t)row_offsets_tiles(n_rows); }
 
 // K1: per-row output length (escaping included) and its exclusive prefix sum.
-//     off[r] = byte offset of line r (n_rows + 1 entries); scratch[1] = serialised length.
+//     off[r] = byte offset of line r (n_rows + 1 entries); scratch[1] = serialised length as a
+//     64-bit number.  Offsets are 32-bit: if the length is 4 GiB or more they have wrapped, and
+//     off[n_rows] is set to 0xffffffff to say so.
 //     scratch must hold scan_scratch_words(n) words; it is cleared on the stream first.
 cudaError_t launch_row_offsets(const TapeView &t, uint32_t *off, unsigned long long *scratch, cudaStream_t s);
 

@@ -1259,15 +1259,31 @@ __global__ void __launch_bounds__(TP_THREADS) rows_kernel(const uint8_t *__restr
 __global__ void key_order_kernel(const uint8_t *__restrict__ arena, RowBuffers rb, uint32_t n_rows, BracketBuffers bb, ParseResult *res) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_rows) return;
+    if (r == 0 && res->module_row != 0 && res->module_kind == ROW_OPEN_OBJ) {
+        // for the module index, which runs next: the row that closes "module" (voff of an opening row is its bracket)
+        const uint32_t cb = bb.match[rb.voff[res->module_row - 1]];
+        res->module_end = cb != 0xffffffffu ? bb.row[cb] : 0u;
+    }
     uint32_t meta = rb.meta[r];
     const uint32_t kind = meta & 15u;
     if (kind == ROW_CLOSE_OBJ || kind == ROW_CLOSE_ARR) {
         // nothing to compare; leave the opener's row in koff for the sibling lookup below
         return;
     }
-    if (!(meta & (1u << 7))) return;
-    rb.meta[r] = meta & ~(1u << 7);
-    if (r == 0) return;
+    // for the module index: a string member three levels down called "name" / "hostname" (the key's bytes are about
+    // to be read for the comparison below anyway)
+    uint32_t marks = 0;
+    if ((meta >> META_DEPTH_SHIFT) == 3 && (meta & (15u | META_HAS_KEY)) == (ROW_STR | META_HAS_KEY)) {
+        const uint32_t kl = rb.klen[r];
+        if (kl == 4 || kl == 8) {
+            const uint32_t ko = rb.koff[r], w0 = load4_be(arena, ko);
+            if (kl == 4) { if (w0 == 0x6e616d65u) marks = META_KEY_IS_NAME; }
+            else if (w0 == 0x686f7374u && load4_be(arena, ko + 4) == 0x6e616d65u) marks = META_KEY_IS_HOSTNAME;
+        }
+    }
+    const bool has_sibling = (meta & (1u << 7)) != 0;
+    if (has_sibling || marks) rb.meta[r] = (meta & ~(1u << 7)) | marks;
+    if (!has_sibling || r == 0) return;
     uint32_t s = r - 1;  // previous sibling: the row before, or the opener of the container that just closed
     const uint32_t sk = rb.meta[s] & 15u;
     if (sk == ROW_CLOSE_OBJ || sk == ROW_CLOSE_ARR) {

@@ -32,12 +32,16 @@ enum RowKind : uint32_t {
 // meta word: bits 0-3 kind, 4 has_key, 5 comma after the value, 6 last row (no newline),
 // 8 key is "plain", 9 string value is "plain" (every byte is printable ASCII other than " \ < > &,
 // so the escaped form IS the byte string and serialising it is a copy),
+// 10 / 11 (tapes the parser built only) the key reads "name" / "hostname" and the row is a string
+// member three levels down: what the module index looks for (index.cu),
 // bits 16-31 indentation depth (<= TK_MAX_DEPTH = 10000)
 constexpr uint32_t META_HAS_KEY = 1u << 4;
 constexpr uint32_t META_COMMA = 1u << 5;
 constexpr uint32_t META_LAST = 1u << 6;
 constexpr uint32_t META_KEY_PLAIN = 1u << 8;
 constexpr uint32_t META_VAL_PLAIN = 1u << 9;
+constexpr uint32_t META_KEY_IS_NAME = 1u << 10;
+constexpr uint32_t META_KEY_IS_HOSTNAME = 1u << 11;
 constexpr uint32_t META_DEPTH_SHIFT = 16;
 
 struct TapeView {        // pointers may be host (pinned) or device
