@@ -25,6 +25,34 @@ namespace {
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int WARPS = EMIT_THREADS / 32;
 
+// ---- bulk asynchronous copies (the copy unit moves the bytes; no registers in between) ----------
+// A warp's staging slice is filled by ONE cp.async.bulk from global memory, completion signalled on
+// an mbarrier in shared memory that the whole warp waits on, and drained by ONE cp.async.bulk to
+// global memory.  Source, destination and size must be multiples of 16 bytes.
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t arrivals) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(arrivals) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)), "l"(gmem_src),
+                 "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// what this thread wrote to shared memory with ordinary stores becomes visible to the copy unit
+__device__ __forceinline__ void fence_smem_for_bulk() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void bulk_store(void *gmem_dst, const void *smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }   // the source may be reused / released
+
 // ---- byte classification (encoding/json: htmlSafeSet) -----------------------------------
 
 // 1 bit per ASCII code: the byte is copied as is
@@ -128,7 +156,8 @@ __device__ __forceinline__ bool row_has_value_bytes(const Row &w) { return (w.me
 // Stages the arena bytes the 32 rows of a warp refer to into that warp's shared-memory slice with
 // coalesced 16-byte loads.  Returns true and sets *base (arena offset of slice byte 0) when the
 // span fits; the caller then reads arena byte x at slice[x - *base].
-__device__ __forceinline__ bool stage_warp_input(const TapeView &t, const Row &w, bool valid, uint4 *slice, uint32_t *base) {
+__device__ __forceinline__ bool stage_warp_input(const TapeView &t, const Row &w, bool valid, uint4 *slice, uint32_t *base, uint64_t *bar,
+                                                 uint32_t *parity) {
     uint32_t lo = 0xffffffffu, hi = 0;
     if (valid) {
         if ((w.meta & META_HAS_KEY) && w.klen) { lo = min(lo, w.koff); hi = max(hi, w.koff + w.klen); }
@@ -140,9 +169,10 @@ __device__ __forceinline__ bool stage_warp_input(const TapeView &t, const Row &w
     const uint32_t b = lo & ~15u;
     if (hi - b > (uint32_t)WARP_IN_BYTES) return false;
     const uint32_t chunks = (hi - b + 15u) >> 4;
-    const uint4 *src = reinterpret_cast<const uint4 *>(t.arena + b);
-    for (uint32_t c = threadIdx.x & 31; c < chunks; c += 32) slice[c] = __ldg(src + c);
-    __syncwarp();
+    // one bulk copy for the whole span (the arena is readable 16 bytes past its end)
+    if ((threadIdx.x & 31) == 0) bulk_load(slice, t.arena + b, chunks << 4, bar);
+    mbar_wait(bar, *parity);
+    *parity ^= 1u;
     *base = b;
     return true;
 }
@@ -371,7 +401,7 @@ __device__ __forceinline__ void warp_copy_deferred(uint8_t *dst, const uint8_t *
 // value and the brackets by position (they are referred to in place, so "at the right place"
 // means "the right bytes").  One lane saying no sends the tile down the general path.
 __device__ __forceinline__ bool emit_verbatim(const TapeView &t, const Row &w, uint32_t o, bool valid, uint32_t lane, uint4 *staging,
-                                              uint8_t *slice, uint32_t out0, uint32_t span, uint32_t shift) {
+                                              uint8_t *slice, uint32_t out0, uint32_t span, uint32_t shift, uint64_t *bar, uint32_t *parity) {
     const uint32_t d = w.meta >> META_DEPTH_SHIFT, kind = w.meta & 15u;
     // text position of the first byte after the indentation, as the row's own fields give it
     uint32_t q;
@@ -381,9 +411,16 @@ __device__ __forceinline__ bool emit_verbatim(const TapeView &t, const Row &w, u
     else q = w.vlen;   // containers: the bracket (TapeView::text_len)
     const uint32_t ls0 = __shfl_sync(FULL, q - d, 0);
     if (ls0 > t.text_len || span > t.text_len - ls0 || ls0 < shift) return false;
-    // text[ls0 - shift ...] -> slice[0 ...]: the text in 16-byte chunks into the input staging,
-    // then word by word into the slice with the two phases reconciled by a funnel shift
-    {
+    // text[ls0 - shift ...] -> slice[0 ...].  Where nothing before this tile has changed length, the
+    // text sits at the output's own 16-byte phase and ONE bulk copy brings it straight into the
+    // slice; otherwise the text goes in 16-byte chunks into the input staging and from there word
+    // by word into the slice, the two phases reconciled by a funnel shift.
+    if (((ls0 - shift) & 15u) == 0u) {
+        const uint32_t bytes = ((shift + span + 15u) >> 4) << 4;   // <= WARP_OUT_BYTES (the tile fits), within the padded text
+        if (lane == 0) bulk_load(slice, t.arena + (ls0 - shift), bytes, bar);
+        mbar_wait(bar, *parity);
+        *parity ^= 1u;
+    } else {
         const uint32_t first = ls0 - shift, a0 = first & ~15u, delta = first - a0;
         const uint32_t chunks = (delta + shift + span + 15u) >> 4;
         if (chunks * 16u + 16u > (uint32_t)WARP_IN_BYTES) return false;
@@ -462,11 +499,15 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const ui
     const bool fits = shift + span <= (uint32_t)WARP_OUT_BYTES;        // else: straight to global memory
 
     uint8_t *slice = reinterpret_cast<uint8_t *>(s_out[warp]);
+    __shared__ __align__(8) uint64_t s_bar[WARPS];   // one mbarrier per warp: its bulk loads complete on it, one after another
+    if (lane == 0) mbar_init(&s_bar[warp], 1);
+    __syncwarp();
+    uint32_t parity = 0;
     Deferred dk = {0, 0, 0}, dv = {0, 0, 0};
     uint32_t base = 0;
     bool staged = false;
-    const bool verbatim = t.text_len != 0 && fits && emit_verbatim(t, w, o, valid, lane, s_in[warp], slice, out0, span, shift);
-    if (!verbatim) staged = stage_warp_input(t, w, valid, s_in[warp], &base);
+    const bool verbatim = t.text_len != 0 && fits && emit_verbatim(t, w, o, valid, lane, s_in[warp], slice, out0, span, shift, &s_bar[warp], &parity);
+    if (!verbatim) staged = stage_warp_input(t, w, valid, s_in[warp], &base, &s_bar[warp], &parity);
     if (verbatim) {
         // the slice already holds the 32 lines
     } else if (staged && fits) {
@@ -489,22 +530,21 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_kernel(TapeView t, const ui
         warp_copy_deferred(dst, src, dv, lane);
     }
     if (!fits) return;
-    __syncwarp();
-    // copy out: whole 16-byte chunks as vectors; the ragged first and last chunk (shared with the
-    // neighbouring warps' tiles) a byte per lane -- lanes 0..15 the first, 16..31 the last
+    // copy out: the whole 16-byte chunks of the slice in ONE bulk copy; the ragged first and last
+    // chunk (shared with the neighbouring warps' tiles) a byte per lane -- lanes 0..15 the first,
+    // 16..31 the last
     uint8_t *g = out + (out0 - shift);  // 16-byte aligned
     const uint32_t end = shift + span;
-    const uint32_t chunks = (end + 15u) >> 4;
-    for (uint32_t c = lane; c < chunks; c += 32) {
-        const uint32_t b0 = c << 4;
-        if (b0 >= shift && b0 + 16 <= end) reinterpret_cast<uint4 *>(g)[c] = s_out[warp][c];
+    const uint32_t c0 = (shift + 15u) >> 4, c1 = end >> 4;                 // whole chunks: [c0, c1)
+    const uint32_t head_end = min(c0 << 4, end), tail_start = max(c1 << 4, head_end);
+    if (!verbatim) fence_smem_for_bulk();   // (the lines were written with ordinary stores)
+    __syncwarp();
+    if (lane == 0 && c1 > c0) bulk_store(g + (c0 << 4), slice + (c0 << 4), (c1 - c0) << 4);
+    {
+        const uint32_t b = lane < 16 ? shift + lane : tail_start + (lane - 16);
+        if (lane < 16 ? b < head_end : b < end) g[b] = slice[b];
     }
-    if (chunks) {
-        const uint32_t b = lane < 16 ? lane : ((chunks - 1) << 4) + (lane - 16);
-        const bool head = lane < 16 && (shift != 0 || end < 16);
-        const bool tail = lane >= 16 && chunks > 1 && (end & 15u) != 0;
-        if ((head || tail) && b >= shift && b < end) g[b] = slice[b];
-    }
+    if (lane == 0 && c1 > c0) bulk_store_wait_read();   // the slice must outlive the copy unit's reads of it
 }
 
 // ---- K3: key prefix classification -------------------------------------------------------------

@@ -11,8 +11,14 @@ namespace tk {
 // geometry shared by the two serialisation kernels
 constexpr int EMIT_THREADS = 256;                       // 8 warps, one 32-row warp tile each per step
 constexpr int EMIT_ROWS_PER_BLOCK = EMIT_THREADS;       // rows handled by one block
-constexpr int WARP_IN_BYTES = 3072;                     // per-warp staging of arena bytes
-constexpr int WARP_OUT_BYTES = 4096;                    // per-warp staging of output text
+#ifndef TK_WARP_IN_BYTES
+#define TK_WARP_IN_BYTES 2048
+#endif
+#ifndef TK_WARP_OUT_BYTES
+#define TK_WARP_OUT_BYTES 3072
+#endif
+constexpr int WARP_IN_BYTES = TK_WARP_IN_BYTES;         // per-warp staging of arena bytes
+constexpr int WARP_OUT_BYTES = TK_WARP_OUT_BYTES;       // per-warp staging of output text
 
 inline uint32_t emit_tiles(uint32_t n_rows) { return (n_rows + EMIT_ROWS_PER_BLOCK - 1) / EMIT_ROWS_PER_BLOCK; }
 
