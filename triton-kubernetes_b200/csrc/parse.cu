@@ -1335,7 +1335,7 @@ cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, un
     if (carry_protocol) {
         if (stage != 0) return cudaSuccess;
         if ((e = cudaMemsetAsync(tb.decode_bits, 0, decode_words * 4, s)) != cudaSuccess) return e;
-        if ((e = cudaMemsetAsync(scratch, 0, p1_scratch_words(n) * 8, s)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(scratch, 0, (4 + 2 * (size_t)n_tiles) * 8, s)) != cudaSuccess) return e;   // ticket and the two status tables
         scan_tokens_kernel<<<n_tiles, P1_THREADS, 0, s>>>(raw, (u64)n, tb, scratch, res);
         g_parse_launches++;
         return cudaGetLastError();
@@ -1345,10 +1345,14 @@ cudaError_t launch_scan_tokens(const uint8_t *raw, size_t n, TokenBuffers tb, un
     uint32_t *tile_agg = reinterpret_cast<uint32_t *>(scratch + 4 + n_tiles);
     uint32_t g_count = 0, g_emit = 0;
     if ((e = fast_scan_grid(&g_count, &g_emit)) != cudaSuccess) return e;
+    // per-chunk masks handed from count to emit, behind the two tile tables (p1_scratch_words covers them)
+    const size_t chunks = (size_t)n_tiles * P1_THREADS;
+    u64 *masks = scratch + 4 + n_tiles + (n_tiles + 1) / 2;
+    const ChunkStore cs{masks, masks + chunks, masks + 2 * chunks, masks + 3 * chunks, reinterpret_cast<uint32_t *>(masks + 4 * chunks)};
     if (stage == 0)   // (also clears the "needs decoding" bitmap the emit kernel sets bits in)
-        scan_count_kernel<<<std::min(n_tiles, g_count), P1_THREADS, 0, s>>>(raw, n_tiles, tile_agg, tb.decode_bits, (uint32_t)decode_words, res);
+        scan_count_kernel<<<std::min(n_tiles, g_count), P1_THREADS, 0, s>>>(raw, n_tiles, tile_agg, tb.decode_bits, (uint32_t)decode_words, cs, res);
     else if (stage == 1) scan_prefix_kernel<<<1, PFX_THREADS, 0, s>>>(tile_agg, n_tiles, tile_pre, res);
-    else scan_emit_kernel<<<std::min(n_tiles, g_emit), P1_THREADS, 0, s>>>(raw, (u64)n, n_tiles, tb, tile_pre, res);
+    else scan_emit_kernel<<<std::min(n_tiles, g_emit), P1_THREADS, 0, s>>>(raw, (u64)n, n_tiles, tb, tile_pre, cs, res);
     g_parse_launches++;
     return cudaGetLastError();
 }

@@ -75,7 +75,11 @@ inline uint32_t p1_tiles(size_t n) { return (uint32_t)((n + P1_TILE - 1) / P1_TI
 inline uint32_t tok_tiles(size_t t) { return (uint32_t)((t + TOK_TILE - 1) / TOK_TILE); }
 
 // scratch sizes in 64-bit words
-inline size_t p1_scratch_words(size_t n) { return 4 + 2 * (size_t)p1_tiles(n); }
+// (two tile tables, then per 64-byte chunk four mask words and one "rare" bit that count hands to emit)
+inline size_t p1_scratch_words(size_t n) {
+    const size_t tiles = p1_tiles(n), chunks = tiles * P1_THREADS;
+    return 4 + 2 * tiles + 4 * chunks + chunks / 64 + 2;
+}
 inline size_t tok_scratch_words(size_t t) { return 4 + 3 * (size_t)tok_tiles(t); }   // 20 bytes per token block
 
 struct TokenBuffers {

@@ -98,7 +98,7 @@ __device__ __forceinline__ ChunkMasks classify64(const uint32_t *s_lut, const Ch
 struct ChunkStrings { u64 RQ, SBx, E, T0, T1; };
 
 __device__ __forceinline__ ChunkStrings chunk_strings(const uint8_t *__restrict__ raw, u64 chunk, uint32_t lane, const uint8_t *s_klut,
-                                                      const ChunkMasks &m, u64 B, ParseResult *res) {
+                                                      const ChunkMasks &m, u64 B, ParseResult *res, u64 *carry_in = nullptr) {
     const bool all_bs = (B == ~0ull);
     const uint32_t trail = all_bs ? 0u : ((uint32_t)__clzll((long long)~B) & 1u);  // odd trailing backslash run
     const u64 SCc = ~(m.WS | m.ST | m.Q);   // bytes that would be scalar characters outside a string
@@ -113,6 +113,7 @@ __device__ __forceinline__ ChunkStrings chunk_strings(const uint8_t *__restrict_
         prev_sc_if_out = chunk ? s_klut[__ldg(raw + chunk - 1)] == T_SCALAR : false;
         carry = carry_before(raw, chunk, res);
     }
+    if (carry_in) *carry_in = carry;
     ChunkStrings s;
     s.E = find_escaped(B, carry);
     s.RQ = m.Q & ~s.E;                      // real (unescaped) quotes
@@ -132,8 +133,15 @@ __device__ __forceinline__ void load_tables(uint32_t *s_lut, uint8_t *s_klut) {
 }
 
 // ---- count: one packed triple per tile
+// What count hands to emit per 64-byte chunk, so that emit does not classify the text again: the
+// token masks for both entry states, the string state and the white-space mask (T0 & T1 are the
+// real quotes).  A chunk with a rare byte, or one entered right after an odd run of backslashes,
+// is marked in rare_bits (one bit per chunk, a word per warp) and emit classifies it itself.
+struct ChunkStore { u64 *T0, *T1, *SBx, *WS; uint32_t *rare_bits; };
+
 __global__ void __launch_bounds__(P1_THREADS) scan_count_kernel(const uint8_t *__restrict__ raw, uint32_t n_tiles, uint32_t *__restrict__ tile_agg,
-                                                               uint32_t *__restrict__ decode_bits, uint32_t decode_words, ParseResult *res) {
+                                                               uint32_t *__restrict__ decode_bits, uint32_t decode_words, ChunkStore cs,
+                                                               ParseResult *res) {
     __shared__ uint32_t s_lut[4 * 256];
     __shared__ uint8_t s_klut[256];
     __shared__ uint32_t s_warp_agg[2][P1_THREADS / 32];
@@ -151,7 +159,14 @@ __global__ void __launch_bounds__(P1_THREADS) scan_count_kernel(const uint8_t *_
             const int i = __ffsll((long long)r) - 1;
             if (__ldg(raw + chunk + i) == '\\') B |= 1ull << i;
         }
-        const ChunkStrings s = chunk_strings(raw, chunk, lane, s_klut, m, B, res);
+        u64 carry_in;
+        const ChunkStrings s = chunk_strings(raw, chunk, lane, s_klut, m, B, res, &carry_in);
+        {
+            const size_t ci = (size_t)tile * P1_THREADS + threadIdx.x;
+            cs.T0[ci] = s.T0; cs.T1[ci] = s.T1; cs.SBx[ci] = s.SBx; cs.WS[ci] = m.WS;
+            const unsigned rare = __ballot_sync(FULL, m.R != 0 || carry_in != 0);
+            if (lane == 0) cs.rare_bits[ci >> 5] = rare;
+        }
         uint32_t agg = chunk_triple(s);
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {   // ordered fold: lane L ends up with lanes L .. L + 2d - 1
@@ -241,7 +256,7 @@ __global__ void __launch_bounds__(PFX_THREADS) scan_prefix_kernel(const uint32_t
 
 // ---- emit: tokens of every tile at their final places, string checks, decode marks
 __global__ void __launch_bounds__(P1_THREADS) scan_emit_kernel(const uint8_t *__restrict__ raw, u64 n, uint32_t n_tiles, TokenBuffers tb,
-                                                              const u64 *__restrict__ tile_pre, ParseResult *res) {
+                                                              const u64 *__restrict__ tile_pre, ChunkStore cs, ParseResult *res) {
     __shared__ uint32_t s_lut[4 * 256];
     __shared__ uint8_t s_klut[256];
     constexpr int TOK_STAGE = 2048;                     // (JSON text averages one token per 8 to 9 bytes: 8 KiB -> about 1,000)
@@ -259,19 +274,32 @@ __global__ void __launch_bounds__(P1_THREADS) scan_emit_kernel(const uint8_t *__
         const u64 pre = tile_pre[tile];
         const uint32_t V = (uint32_t)pre & 1u;          // in-string state entering the tile
         const u64 base = pre >> 1;                      // tokens before the tile
-        const ChunkMasks m = classify64(s_lut, load_chunk(raw + chunk));
-        // rare bytes, told apart one by one
+        // What count left for this chunk; a warp with a rare chunk classifies its text again (all its
+        // lanes: the neighbours' backslash runs travel by shuffle).
+        const size_t ci = (size_t)tile * P1_THREADS + threadIdx.x;
+        const unsigned rare_warp = __ldg(cs.rare_bits + (ci >> 5));
+        ChunkMasks m;
+        ChunkStrings s;
         u64 B = 0, CT = 0, NA = 0, HT = 0;
-        for (u64 r = m.R; r; r &= r - 1) {
-            const int i = __ffsll((long long)r) - 1;
-            const uint32_t c = __ldg(raw + chunk + i);
-            const u64 bit = 1ull << i;
-            if (c == '\\') B |= bit;
-            else if (c >= 0x80) NA |= bit;
-            else if (c < 0x20) CT |= bit;
-            else HT |= bit;
+        if (rare_warp == 0) {
+            s.T0 = __ldg(cs.T0 + ci); s.T1 = __ldg(cs.T1 + ci); s.SBx = __ldg(cs.SBx + ci); m.WS = __ldg(cs.WS + ci);
+            s.RQ = s.T0 & s.T1;   // a real quote is a token whatever the state; anything else only outside a string
+            s.E = 0;
+            m.Q = s.RQ; m.ST = 0; m.R = 0;
+        } else {
+            m = classify64(s_lut, load_chunk(raw + chunk));
+            // rare bytes, told apart one by one
+            for (u64 r = m.R; r; r &= r - 1) {
+                const int i = __ffsll((long long)r) - 1;
+                const uint32_t c = __ldg(raw + chunk + i);
+                const u64 bit = 1ull << i;
+                if (c == '\\') B |= bit;
+                else if (c >= 0x80) NA |= bit;
+                else if (c < 0x20) CT |= bit;
+                else HT |= bit;
+            }
+            s = chunk_strings(raw, chunk, lane, s_klut, m, B, res);
         }
-        const ChunkStrings s = chunk_strings(raw, chunk, lane, s_klut, m, B, res);
 
         // exclusive ordered scan of the triples over the tile
         uint32_t incl = chunk_triple(s);
