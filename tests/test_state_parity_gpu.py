@@ -515,3 +515,113 @@ def test_index_gives_way_to_the_host_tree_for_a_child_with_thousands_of_members(
                                                    "y": [{"hostname": "in array"}]}}, "name": "at the root"}).encode()).Bytes()
     c = tk.New("x", small)
     assert c.Clusters() == {b"b": b"cluster_a_b"} and c.Nodes("cluster_a_b") == {b"h1": b"node_a_b_1"} and not c.host_tree_built
+
+
+# ---- edits of module's children on a document that stays on the device ---------------------------
+
+def test_config5_destroy_sweep_on_the_device(tk, oracle):
+    """The destroy sweep (destroy/cluster.go:126-158) over a document loaded from its persisted form:
+    Nodes / Delete work on the index and the child list, Bytes() rebuilds the tape on the device, and
+    the host tree is never built."""
+    raw = oracle.New("x", synth.document(30, 12)).Bytes()
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    assert not a.host_tree_built
+    snaps = {id(a): [], id(b): []}
+    for s in (a, b):
+        for i, (name, ck) in enumerate(sorted(s.Clusters().items())):
+            for host, nk in sorted(s.Nodes(ck).items()):
+                s.Delete(b"module." + nk)
+            assert s.Nodes(ck) == {}
+            s.Delete(b"module." + ck)
+            s.Delete(b"module." + ck)          # deleting an absent key is not an error
+            if i in (0, 7, 28):
+                snaps[id(s)].append((s.Bytes(), s.Clusters()))
+    assert snaps[id(a)] == snaps[id(b)]
+    want = json.dumps({"module": {"cluster-manager": synth.manager_record()},
+                       "terraform": {"backend": {"local": {"path": "/root/.triton-kubernetes/bench/terraform.tfstate"}}}},
+                      indent="\t", sort_keys=True).encode()
+    assert a.Bytes() == b.Bytes() == want
+    assert not a.host_tree_built
+    a.Delete("module.cluster-manager"); b.Delete("module.cluster-manager")     # the last child: "module": {} -- left to the host tree
+    assert a.Bytes() == b.Bytes() and a.host_tree_built
+
+
+def test_device_edits_first_last_replace_and_records(tk, oracle):
+    """SetManager / AddCluster / AddNode / Delete on children of "module", document on the device: a new
+    child that sorts first, one that sorts last (the comma moves), a replaced one, a record (opaque
+    to Clusters / Nodes / Get, members in the given order), add-then-delete, and what Get sees once
+    the host tree is finally built."""
+    raw = oracle.New("x", synth.document(3, 2)).Bytes()
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    steps = [
+        lambda s, m: s._set("module.aaa-first", {"name": "first", "x": [1, {"y": None}], "e": {}}),
+        lambda s, m: s._set("module.zzz-last", {"hostname": "h<last>&", "name": "zl"}),
+        lambda s, m: s.Delete("module.zzz-last"),
+        lambda s, m: s._set("module.zzz-last2", "a plain string child"),
+        lambda s, m: s.AddCluster("baremetal", "c0001", {"name": "c0001-replaced", "k8s_version": "v2"}),
+        lambda s, m: s.AddNode("cluster_baremetal_c0001", "n-rec", m.Record([("source", "s"), ("hostname", "rec-host"), ("a", m.Record([("z", "1"), ("b", "2")]))])),
+        lambda s, m: s.AddNode("cluster_baremetal_c0001", "n-map", {"hostname": "map-host", "source": "s"}),
+        lambda s, m: s.SetManager(m.Record([("source", "new"), ("name", "mgr")])),
+        lambda s, m: s.Delete("module." + synth.node_key(0, 1)),
+        lambda s, m: s.Delete("module.not-there"),
+        lambda s, m: s._set("module.tmp", {"name": "tmp"}),
+        lambda s, m: s.Delete("module.tmp"),
+        lambda s, m: s._set("module.zzzz-null", None),
+    ]
+    for i, step in enumerate(steps):
+        step(a, tk); step(b, oracle)
+        assert a.Clusters() == b.Clusters(), i
+        for c in range(3):
+            assert a.Nodes(synth.cluster_key(c)) == b.Nodes(synth.cluster_key(c)), i
+        if i % 3 == 2 or i + 1 == len(steps):
+            assert a.Bytes() == b.Bytes(), i
+        assert not a.host_tree_built, i
+    # the first look through Get builds the tree from the edited tape; records are still opaque in it
+    for path in ("module.aaa-first.name", "module.node_baremetal_c0001_n-rec.hostname", "module.node_baremetal_c0001_n-map.hostname",
+                 "module.cluster-manager.name", "module.zzz-last2", "module.cluster_baremetal_c0001.k8s_version"):
+        assert a.Get(path) == b.Get(path), path
+    assert a.host_tree_built and a.Bytes() == b.Bytes()
+    a._set("module.after", {"name": "after"}); b._set("module.after", {"name": "after"})
+    assert a.Bytes() == b.Bytes() and a.Clusters() == b.Clusters()
+    # and the text written along the way loads like the oracle's (records become maps: keys sorted from then on)
+    assert tk.New("y", a.Bytes()).Bytes() == oracle.New("y", b.Bytes()).Bytes()
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_module_child_edits_stay_on_the_device(tk, oracle, seed):
+    """Random Set (maps and records) / Delete of module children interleaved with Clusters, Nodes and
+    Bytes on a document that starts on the device: the results match the oracle and the host tree is
+    not built until something other than a module child is touched."""
+    rng = random.Random(4100 + seed)
+    raw = oracle.New("x", json.dumps(_module_doc(rng, rng.choice([3, 20, 120]))).encode()).Bytes()
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    if len(json.loads(raw)["module"]) == 0:
+        return
+    keys = sorted(json.loads(raw)["module"])
+    for step in range(150):
+        r = rng.random()
+        key = rng.choice(keys + ["cluster_a_x", "node_a_x_%d" % rng.randrange(8), "zz-new-%d" % rng.randrange(5), "0-first"])
+        if r < 0.35:
+            if len(json.loads(b.Bytes())["module"]) <= 1:
+                continue                       # (the last child goes through the host tree: another test)
+            a.Delete("module." + key); b.Delete("module." + key)
+        elif r < 0.75:
+            val = rng.choice([{"name": "n%d" % rng.randrange(6), "hostname": "h%d" % rng.randrange(9)}, {"hostname": "dup"}, {"name": "é<"}, "str", 5, None,
+                              {"x": {"name": "inner"}}, [1, 2]])
+            rec = rng.random() < 0.3 and isinstance(val, dict)
+            va = tk.Record(list(val.items())) if rec else val
+            vb = oracle.Record(list(val.items())) if rec else val
+            a._set("module." + key, va); b._set("module." + key, vb)
+            if key not in keys:
+                keys.append(key)
+        elif r < 0.9:
+            assert a.Clusters() == b.Clusters()
+            ck = rng.choice(["cluster_a_x", "cluster_b_y", "cluster_aa_x_y", "cluster_a_xy"])
+            assert a.Nodes(ck) == b.Nodes(ck)
+        else:
+            assert a.Bytes() == b.Bytes()
+        assert not a.host_tree_built, step
+    assert a.Bytes() == b.Bytes() and a.Clusters() == b.Clusters()
+    assert not a.host_tree_built
+    a._set("other.deep", {"k": "v"}); b._set("other.deep", {"k": "v"})          # not a module child: the tree takes over
+    assert a.host_tree_built and a.Bytes() == b.Bytes() and a.Clusters() == b.Clusters()

@@ -101,9 +101,24 @@ int tk_state_get(tk_state *s, const char *path, size_t path_len, const char **va
 
 int tk_state_set(tk_state *s, const char *path, size_t path_len, const char *json, size_t json_len, int value_kind) {
     if (!s) return set_err(s, TK_EARG, "tk_state_set: NULL handle");
-    if (int rc = ensure_host(s)) return rc;
     Node *v = nullptr;
     std::string err;
+    if (!s->doc.host_valid) {
+        // a document on the device: a child of "module" is set there (no host tree, no second upload);
+        // for any other path the tree is built first, as for every other point operation
+        if (!parse_value(sv(json, json_len), value_kind == TK_VALUE_RECORD, &v, &err)) {
+            if (int rc = ensure_host(s)) return rc;      // (gabs walks the path before json.Marshal's result is looked at: same order of errors)
+            return set_err(s, TK_ESYNTAX, err);
+        }
+        bool handled = false;
+        int rc = s->eng.edit_set(&s->doc, sv(path, path_len), v, &handled, &err);
+        if (rc) { free_node(v); return set_err(s, rc, err); }
+        if (handled) return TK_OK;
+        if ((rc = ensure_host(s)) != 0) { free_node(v); return rc; }
+        rc = s->doc.set(sv(path, path_len), v, &err);
+        if (rc) return set_err(s, rc, err);
+        return TK_OK;
+    }
     if (!parse_value(sv(json, json_len), value_kind == TK_VALUE_RECORD, &v, &err)) return set_err(s, TK_ESYNTAX, err);
     int rc = s->doc.set(sv(path, path_len), v, &err);
     if (rc) return set_err(s, rc, err);
@@ -146,8 +161,14 @@ int tk_state_add_node(tk_state *s, const char *cluster_key, size_t cluster_key_l
 
 int tk_state_delete(tk_state *s, const char *path, size_t path_len) {
     if (!s) return set_err(s, TK_EARG, "tk_state_delete: NULL handle");
-    if (int rc = ensure_host(s)) return rc;
     std::string err;
+    if (!s->doc.host_valid) {
+        bool handled = false;
+        int rc0 = s->eng.edit_delete(&s->doc, sv(path, path_len), &handled, &err);   // a child of "module", on the device
+        if (rc0) return set_err(s, rc0, err);
+        if (handled) return TK_OK;
+    }
+    if (int rc = ensure_host(s)) return rc;
     int rc = s->doc.del(sv(path, path_len), &err);
     if (rc) return set_err(s, rc, err);
     return TK_OK;
@@ -228,7 +249,7 @@ static int children_by_prefix(tk_state *s, std::string_view prefix, std::string_
     std::string err;
     auto &pairs = s->pairs;  // (field value, module key); kept on the handle so a sweep of calls re-uses its storage
     pairs.clear();
-    if (!s->doc.host_valid && s->eng.index_usable(s->doc)) {
+    if (!s->doc.host_valid && (s->eng.edits_active() || s->eng.index_usable(s->doc))) {
         // the document lives on the device: one GPU pass per version builds the packed index, and
         // the finished answer is usually a byte range of the result records packed alongside it
         bool module_ok = false, direct = false;

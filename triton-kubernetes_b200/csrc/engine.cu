@@ -198,6 +198,7 @@ struct StreamPool {
 }  // namespace
 
 Engine::~Engine() {
+    drop_edit_state();
     for (auto &p : pending_) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto ev : free_events_) cudaEventDestroy(ev);
     if (stream_) {
@@ -434,6 +435,7 @@ int Engine::stage_tape(const Document &doc, std::string *err) {
     if (rc) return rc;
     StreamScope scope(stream_);
     if (staged_version_ == doc.version) return TK_OK;
+    if (!doc.host_valid && edit_) return apply_edits(doc, err);   // edited on the device: the tape is rebuilt there
     if (!doc.host_valid) { *err = "internal: no host tree to flatten"; return TK_EARG; }
     tape_from_parse_ = false;
     // copies of the previous staging may still be reading the pinned arrays flatten() rewrites
@@ -768,6 +770,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     if ((e = d_off_.reserve(((size_t)n_rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(off)", err);
     if ((e = d_scratch_.reserve(scan_scratch_words(n_rows) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
     tape_from_parse_ = true;
+    bb_ = bb;
     parsed_ = *out;
     index_version_ = 0;
     return TK_OK;
@@ -927,6 +930,7 @@ static Node *build_value(TreeBuilder &tb, uint32_t r, uint32_t *next, int levels
 int Engine::materialise(Document *doc, std::string *err) {
     if (doc->host_valid) return TK_OK;
     StreamScope scope(stream_);
+    if (edit_) { int rc = apply_edits(*doc, err); if (rc) return rc; }   // the tree is built from the tape as edited
     if (!tape_from_parse_ || !tape_.n_rows) { *err = "internal: no device tape to build the tree from"; return TK_EARG; }
     const size_t n = tape_.n_rows;
     cudaError_t e;
@@ -965,6 +969,7 @@ int Engine::materialise(Document *doc, std::string *err) {
     free_node(doc->root);
     doc->root = root;
     doc->host_valid = true;
+    adopt_added_values(doc);
     return TK_OK;
 }
 
@@ -978,7 +983,7 @@ namespace tk {
 // into result records (csrc/index.cu) and copied to the host with their offsets and order bitmaps.
 // The sizes of everything are known from the parse verdict, so the host waits once, at the end.
 int Engine::build_index(const Document &doc, std::string *err) {
-    if (index_version_ == doc.version) return TK_OK;
+    if (index_version_ == doc.version || edit_) return TK_OK;   // (once edits begin, the index is what was built then plus the edit list)
     StreamScope scope(stream_);
     if (!device_resident(doc)) { *err = "internal: module index needs the parser's tape"; return TK_EARG; }
     cudaError_t e;
@@ -1115,11 +1120,14 @@ int Engine::index_lookup(const Document &doc, std::string_view prefix, bool host
     *module_ok = index_module_ok_;
     pairs->clear();
     const int f = hostname ? 1 : 0;
-    if (!index_module_ok_ || index_m_[f] == 0) return TK_OK;
+    if (!index_module_ok_) return TK_OK;
+    if (index_m_[f] == 0) { edit_added_pairs(f, prefix, pairs); return TK_OK; }
     uint32_t lo, hi;
     index_range(f, prefix, &lo, &hi);
     const IndexView v{h_foff_[f].p, reinterpret_cast<const char *>(h_fblob_[f].p), index_m_[f]};
-    for (uint32_t j = lo; j < hi; j++) pairs->emplace_back(v.field(j), v.key(j));
+    for (uint32_t j = lo; j < hi; j++)
+        if (!edit_record_dead(f, j)) pairs->emplace_back(v.field(j), v.key(j));
+    edit_added_pairs(f, prefix, pairs);
     return TK_OK;
 }
 
@@ -1135,10 +1143,14 @@ int Engine::index_lookup_direct(const Document &doc, std::string_view prefix, bo
     *blob_len = 0;
     *count = 0;
     const int f = hostname ? 1 : 0;
-    if (!index_module_ok_ || index_m_[f] == 0) return TK_OK;
+    if (!index_module_ok_) return TK_OK;
+    if (edit_added_any(f, prefix)) { *direct = false; return TK_OK; }   // children added since: the pairs are put together one by one
+    if (index_m_[f] == 0) return TK_OK;
     uint32_t lo, hi;
     index_range(f, prefix, &lo, &hi);
     if (lo == hi) return TK_OK;
+    for (uint32_t j = lo; edit_ && j < hi; j++)
+        if (edit_record_dead(f, j)) { *direct = false; return TK_OK; }     // children deleted since
     // order violations strictly inside the run (record lo may compare with a child outside it):
     // any bit set among records lo + 1 .. hi - 1
     const uint32_t *bits = h_fviolbits_[f].p;
@@ -1157,3 +1169,361 @@ int Engine::index_lookup_direct(const Document &doc, std::string_view prefix, bo
 }
 
 }  // namespace tk
+
+// ============================================================================ edits on the device
+
+namespace tk {
+
+// What the host knows about module's children while a document is edited on the device.
+struct Engine::EditState {
+    struct Base { uint32_t key_off, key_len, rows, tape_row; bool live; };        // a child the parser found
+    struct Added {                                                               // a child set since
+        Node *value = nullptr;      // as given (a record stays a record: opaque, members in the given order)
+        bool on_device = false;
+        uint32_t rows = 0, tape_row = 0;
+        bool has[2] = {false, false};   // a map with a string "name" / "hostname": visible to Clusters() / Nodes()
+        std::string field[2];
+        FlatLocal flat;             // its rows, until they have been uploaded
+    };
+    std::vector<Base> base;         // in key order
+    const char *keys = nullptr;     // their keys, one after another (h_ckeys_)
+    std::map<std::string, Added, std::less<>> added;
+    std::vector<uint8_t> dead[2];   // per field: index records whose child has been deleted or replaced
+    uint32_t n_rows = 0;            // rows of the device tape as last rebuilt
+    uint32_t head_rows = 0;         // [0, head_rows): everything before module's first child
+    uint32_t tail_row = 0;          // [tail_row, n_rows): module's closing row and everything after it
+    size_t live = 0;                // children alive, found and added
+    // the child whose last row carries no comma on the device tape: the last in key order when it was last rebuilt
+    bool last_is_added = false;
+    size_t last_base = 0;
+    std::string last_added;
+    bool dirty = false;             // edited since the tape was last rebuilt
+    ~EditState() { for (auto &kv : added) free_node(kv.second.value); }
+    std::string_view key(const Base &b) const { return std::string_view(keys + b.key_off, b.key_len); }
+    Base *find_base(std::string_view k) {
+        size_t lo = 0, hi = base.size();
+        while (lo < hi) { const size_t mid = (lo + hi) >> 1; if (key(base[mid]) < k) lo = mid + 1; else hi = mid; }
+        return lo < base.size() && key(base[lo]) == k ? &base[lo] : nullptr;
+    }
+};
+
+void Engine::drop_edit_state() { delete edit_; edit_ = nullptr; }
+
+bool Engine::edit_record_dead(int f, uint32_t j) const { return edit_ && j < edit_->dead[f].size() && edit_->dead[f][j]; }
+
+bool Engine::edit_added_any(int f, std::string_view prefix) const {
+    if (!edit_) return false;
+    for (auto it = edit_->added.lower_bound(prefix); it != edit_->added.end(); ++it) {
+        if (it->first.size() < prefix.size() || it->first.compare(0, prefix.size(), prefix) != 0) break;
+        if (it->second.has[f]) return true;
+    }
+    return false;
+}
+
+void Engine::edit_added_pairs(int f, std::string_view prefix, std::vector<std::pair<std::string_view, std::string_view>> *pairs) const {
+    if (!edit_) return;
+    for (auto it = edit_->added.lower_bound(prefix); it != edit_->added.end(); ++it) {
+        if (it->first.size() < prefix.size() || it->first.compare(0, prefix.size(), prefix) != 0) break;
+        if (it->second.has[f]) pairs->emplace_back(it->second.field[f], it->first);
+    }
+}
+
+// After the tree has been built from the edited tape: the children set since take their original
+// values back (the tape knows objects only; a record must stay opaque and keep its member order
+// until the document is parsed again -- SURVEY.md 8a note 1), and the edit list is done with.
+void Engine::adopt_added_values(Document *doc) {
+    if (!edit_) return;
+    MapNode *mod = nullptr;
+    if (doc->root && doc->root->kind == Kind::Map) {
+        auto &m = static_cast<MapNode *>(doc->root)->m;
+        auto it = m.find(std::string_view("module"));
+        if (it != m.end() && it->second && it->second->kind == Kind::Map) mod = static_cast<MapNode *>(it->second);
+    }
+    for (auto &kv : edit_->added) {
+        if (!mod) break;
+        auto it = mod->m.find(kv.first);
+        if (it == mod->m.end()) continue;
+        free_node(it->second);
+        it->second = kv.second.value;
+        kv.second.value = nullptr;
+    }
+    drop_edit_state();
+}
+
+// "module.<key>" on a document the device path can edit: *key set, true.  Anything else: false
+// (*rc != 0: a CUDA failure on the way into edit mode).
+bool Engine::edit_path_key(const Document &doc, std::string_view path, std::string_view *key, std::string *err, int *rc) {
+    *rc = TK_OK;
+    if (doc.host_valid) return false;
+    const size_t dot = path.find('.');
+    if (dot == std::string_view::npos || path.substr(0, dot) != "module" || path.find('.', dot + 1) != std::string_view::npos) return false;
+    if (!edit_) {
+        if (!index_usable(doc)) return false;
+        if (!(parsed_.root_kind == ROW_OPEN_OBJ && parsed_.module_row != 0 && parsed_.module_kind == ROW_OPEN_OBJ && parsed_.module_end != 0)) return false;
+        *rc = enter_edit_mode(doc, err);
+        if (*rc || !edit_) return false;
+    }
+    *key = path.substr(dot + 1);
+    return true;
+}
+
+// The list of module's children, once, from the tape as parsed: flags -> ranks -> (first row, last
+// row, key) per child -> keys packed -> host.
+int Engine::enter_edit_mode(const Document &doc, std::string *err) {
+    StreamScope scope(stream_);
+    int rc = build_index(doc, err);
+    if (rc) return rc;
+    cudaError_t e;
+    const uint32_t n = tape_.n_rows, module_row = parsed_.module_row - 1, module_end = parsed_.module_end;
+    if (!h_words_.reserve(8)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+    if ((e = d_cflags_.reserve((size_t)n * 4)) != cudaSuccess || (e = d_crank_.reserve((size_t)n * 4)) != cudaSuccess ||
+        (e = d_scratch_.reserve(parse_scan_scratch_words(n) * 8 + 64)) != cudaSuccess)
+        return fail(e, "cudaMalloc(children)", err);
+    unsigned long long *scratch = d_scratch_.as<unsigned long long>();
+    if ((e = launch_child_flags(tape_, module_row, module_end, d_cflags_.as<uint32_t>(), stream_)) != cudaSuccess ||
+        (e = scan_u32(d_cflags_.as<uint32_t>(), d_crank_.as<uint32_t>(), n, scratch, stream_)) != cudaSuccess ||
+        (e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess || (e = cudaStreamSynchronize(stream_)) != cudaSuccess)
+        return fail(e, "child list", err);
+    const uint32_t nc = (uint32_t)h_words_.p[0];
+    if (nc == 0) return TK_OK;   // (cannot be for a non-empty object; the caller then builds the host tree)
+    for (int i = 0; i < 4; i++)
+        if ((e = d_clist_[i].reserve((size_t)nc * 4)) != cudaSuccess) return fail(e, "cudaMalloc(children)", err);
+    if ((e = d_ckeyoff_.reserve(((size_t)nc + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(children)", err);
+    ChildList cl{d_clist_[0].as<uint32_t>(), d_clist_[1].as<uint32_t>(), d_clist_[2].as<uint32_t>(), d_clist_[3].as<uint32_t>()};
+    if ((e = launch_child_entries(tape_, d_cflags_.as<uint32_t>(), d_crank_.as<uint32_t>(), bb_.match, bb_.row, cl, stream_)) != cudaSuccess ||
+        (e = scan_u32(cl.klen, d_ckeyoff_.as<uint32_t>(), nc, scratch, stream_)) != cudaSuccess ||
+        (e = copy_d2h(h_words_.p, scratch + 1, 8)) != cudaSuccess || (e = cudaStreamSynchronize(stream_)) != cudaSuccess)
+        return fail(e, "child list", err);
+    const size_t key_bytes = (size_t)h_words_.p[0];
+    if ((e = d_ckeys_.reserve(key_bytes + 32)) != cudaSuccess) return fail(e, "cudaMalloc(children)", err);
+    if (!h_clist_[0].reserve(nc) || !h_clist_[1].reserve(nc) || !h_clist_[2].reserve((size_t)nc + 1) || !h_ckeys_.reserve(key_bytes + 1)) {
+        *err = "cuda: pinned host allocation failed";
+        return TK_ECUDA;
+    }
+    if ((e = launch_child_keys(tape_.arena, cl, d_ckeyoff_.as<uint32_t>(), nc, d_ckeys_.as<uint8_t>(), stream_)) != cudaSuccess ||
+        (e = copy_d2h(h_clist_[0].p, cl.row, (size_t)nc * 4)) != cudaSuccess || (e = copy_d2h(h_clist_[1].p, cl.end, (size_t)nc * 4)) != cudaSuccess ||
+        (e = copy_d2h(h_clist_[2].p, d_ckeyoff_.p, (size_t)nc * 4)) != cudaSuccess ||
+        (key_bytes && (e = copy_d2h(h_ckeys_.p, d_ckeys_.p, key_bytes)) != cudaSuccess) || (e = cudaStreamSynchronize(stream_)) != cudaSuccess)
+        return fail(e, "child list", err);
+    h_clist_[2].p[nc] = (uint32_t)key_bytes;
+    auto *E = new EditState();
+    E->keys = reinterpret_cast<const char *>(h_ckeys_.p);
+    E->base.resize(nc);
+    for (uint32_t j = 0; j < nc; j++) {
+        const uint32_t row = h_clist_[0].p[j], end = h_clist_[1].p[j];
+        E->base[j] = EditState::Base{h_clist_[2].p[j], h_clist_[2].p[j + 1] - h_clist_[2].p[j], end - row + 1, row, true};
+    }
+    E->n_rows = n;
+    E->head_rows = module_row + 1;
+    E->tail_row = module_end;
+    E->live = nc;
+    E->last_base = nc - 1;
+    for (int f = 0; f < 2; f++) E->dead[f].assign(index_m_[f], 0);
+    edit_ = E;
+    return TK_OK;
+}
+
+// the index record of child `key` under field f, if it has one, is no longer part of any answer
+static void tombstone(std::vector<uint8_t> &dead, const uint32_t *off, const char *blob, uint32_t m, std::string_view key) {
+    auto key_at = [&](uint32_t j) {
+        const char *rec = blob + off[j];
+        uint32_t fl, kl;
+        memcpy(&fl, rec, 4);
+        memcpy(&kl, rec + 4 + fl, 4);
+        return std::string_view(rec + 8 + fl, kl);
+    };
+    uint32_t lo = 0, hi = m;
+    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (key_at(mid) < key) lo = mid + 1; else hi = mid; }
+    if (lo < m && key_at(lo) == key) dead[lo] = 1;
+}
+
+int Engine::edit_delete(Document *doc, std::string_view path, bool *handled, std::string *err) {
+    *handled = false;
+    std::string_view key;
+    int rc;
+    if (!edit_path_key(*doc, path, &key, err, &rc)) return rc;
+    EditState &E = *edit_;
+    auto it = E.added.find(key);
+    EditState::Base *b = it == E.added.end() ? E.find_base(key) : nullptr;
+    const bool present = it != E.added.end() || (b && b->live);
+    if (present && E.live == 1) return TK_OK;   // module would become empty ("{}" is one row, not two): left to the host tree
+    *handled = true;
+    if (!present) return TK_OK;                  // gabs: deleting an absent key succeeds and changes nothing
+    if (it != E.added.end()) {
+        free_node(it->second.value);
+        it->second.value = nullptr;
+        E.added.erase(it);
+    } else {
+        b->live = false;
+        for (int f = 0; f < 2; f++)
+            if (index_m_[f]) tombstone(E.dead[f], h_foff_[f].p, reinterpret_cast<const char *>(h_fblob_[f].p), index_m_[f], key);
+    }
+    E.live--;
+    E.dirty = true;
+    doc->version++;
+    return TK_OK;
+}
+
+int Engine::edit_set(Document *doc, std::string_view path, Node *value, bool *handled, std::string *err) {
+    *handled = false;
+    std::string_view key;
+    int rc;
+    if (!edit_path_key(*doc, path, &key, err, &rc)) return rc;
+    EditState &E = *edit_;
+    EditState::Added a;
+    const std::string k(key);
+    try {
+        flat_value(a.flat, value, 2, &k, true, false);   // a child of module: depth 2, a comma after it (taken off the last one when the tape is rebuilt)
+    } catch (...) {
+        *err = "out of memory";
+        return TK_ELIMIT;
+    }
+    a.rows = (uint32_t)a.flat.meta.size();
+    if (value && value->kind == Kind::Map) {
+        auto &m = static_cast<const MapNode *>(value)->m;
+        static const char *const names[2] = {"name", "hostname"};
+        for (int f = 0; f < 2; f++) {
+            auto fi = m.find(std::string_view(names[f]));
+            if (fi != m.end() && fi->second && fi->second->kind == Kind::Str) { a.has[f] = true; a.field[f] = static_cast<const StrNode *>(fi->second)->s; }
+        }
+    }
+    a.value = value;
+    *handled = true;
+    auto it = E.added.find(key);
+    if (it != E.added.end()) {
+        free_node(it->second.value);
+        it->second = std::move(a);
+    } else {
+        if (EditState::Base *b = E.find_base(key); b && b->live) {
+            b->live = false;
+            for (int f = 0; f < 2; f++)
+                if (index_m_[f]) tombstone(E.dead[f], h_foff_[f].p, reinterpret_cast<const char *>(h_fblob_[f].p), index_m_[f], key);
+        } else {
+            E.live++;
+        }
+        E.added.emplace(k, std::move(a));
+    }
+    E.dirty = true;
+    doc->version++;
+    return TK_OK;
+}
+
+// The device tape rebuilt to match the child list: runs of surviving rows and the rows of the
+// children set since (uploaded behind the old rows first), in key order, gathered into the second
+// set of row arrays; then the comma after the last child taken off and the one after the child
+// that used to be last put back.
+int Engine::apply_edits(const Document &doc, std::string *err) {
+    if (!edit_) return TK_OK;
+    EditState &E = *edit_;
+    if (!E.dirty) { staged_version_ = doc.version; return TK_OK; }
+    StreamScope scope(stream_);
+    cudaError_t e;
+    // (the pinned staging below may still be in flight from the previous rebuild)
+    if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "synchronize", err);
+    h_segs_.clear(); h_addarena_.clear();
+    for (auto &v : h_addrows_) v.clear();
+    uint32_t cur = 0, upload_rows = 0;
+    auto add_seg = [&](uint32_t src, uint32_t n) {
+        if (!n) return;
+        if (h_segs_.n && h_segs_.p[h_segs_.n - 1].src + h_segs_.p[h_segs_.n - 1].n == src) h_segs_.p[h_segs_.n - 1].n += n;
+        else h_segs_.push(RowSegment{cur, src, n});
+        cur += n;
+    };
+    add_seg(0, E.head_rows);
+    // what used to be last, by new row number (0xffffffff: gone), and what is last now
+    uint32_t old_last_row = 0xffffffffu, new_last_row = 0xffffffffu;
+    bool new_last_is_added = false;
+    size_t new_last_base = 0;
+    const std::string *new_last_added = nullptr;
+    size_t bi = 0;
+    auto ai = E.added.begin();
+    const size_t side_base = (arena_used_ + 15) & ~size_t(15);
+    while (bi < E.base.size() || ai != E.added.end()) {
+        while (bi < E.base.size() && !E.base[bi].live) bi++;
+        const bool take_base = bi < E.base.size() && (ai == E.added.end() || E.key(E.base[bi]) < std::string_view(ai->first));
+        if (take_base) {
+            EditState::Base &b = E.base[bi];
+            const uint32_t at = cur;
+            add_seg(b.tape_row, b.rows);
+            b.tape_row = at;
+            if (!E.last_is_added && E.last_base == bi) old_last_row = cur - 1;
+            new_last_row = cur - 1; new_last_is_added = false; new_last_base = bi;
+            bi++;
+        } else if (ai != E.added.end()) {
+            EditState::Added &a = ai->second;
+            const uint32_t at = cur;
+            if (a.on_device) {
+                add_seg(a.tape_row, a.rows);
+            } else {
+                // its rows go behind the old ones, its strings behind the arena
+                const uint32_t base_off = (uint32_t)(side_base + h_addarena_.n);
+                for (uint32_t r = 0; r < a.rows; r++) {
+                    h_addrows_[0].push(a.flat.meta[r]);
+                    h_addrows_[1].push(a.flat.klen[r] ? a.flat.koff[r] + base_off : 0u);
+                    h_addrows_[2].push(a.flat.klen[r]);
+                    h_addrows_[3].push(a.flat.vlen[r] ? a.flat.voff[r] + base_off : 0u);
+                    h_addrows_[4].push(a.flat.vlen[r]);
+                }
+                h_addarena_.append(a.flat.arena.data(), a.flat.arena.size());
+                add_seg(E.n_rows + upload_rows, a.rows);
+                upload_rows += a.rows;
+                a.on_device = true;
+                a.flat = FlatLocal();
+            }
+            a.tape_row = at;
+            if (E.last_is_added && E.last_added == ai->first) old_last_row = cur - 1;
+            new_last_row = cur - 1; new_last_is_added = true; new_last_added = &ai->first;
+            ++ai;
+        }
+    }
+    const uint32_t new_tail = cur;
+    add_seg(E.tail_row, E.n_rows - E.tail_row);
+    const uint32_t new_n = cur;
+    bool pin_ok = !h_segs_.failed && !h_addarena_.failed;
+    for (auto &v : h_addrows_) pin_ok = pin_ok && !v.failed;
+    if (!pin_ok) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+    if (side_base + h_addarena_.n >= 0xfffffff0ull || (size_t)E.n_rows + upload_rows >= 0xfffffff0ull) {
+        *err = "document too large: string arena and row count must stay below 4 GiB";
+        return TK_ELIMIT;
+    }
+    // new rows and their strings
+    DevBuf *rows[5] = {&d_meta_, &d_koff_, &d_klen_, &d_voff_, &d_vlen_};
+    if (upload_rows) {
+        for (int i = 0; i < 5; i++) {
+            if ((e = rows[i]->reserve(((size_t)E.n_rows + upload_rows) * 4, (size_t)E.n_rows * 4, stream_)) != cudaSuccess) return fail(e, "cudaMalloc(rows)", err);
+            if ((e = copy_h2d(rows[i]->as<uint32_t>() + E.n_rows, h_addrows_[i].p, (size_t)upload_rows * 4)) != cudaSuccess) return fail(e, "copy rows", err);
+        }
+        if ((e = d_arena_.reserve(side_base + h_addarena_.n + 32, arena_used_, stream_)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
+        if (h_addarena_.n && (e = copy_h2d(d_arena_.as<uint8_t>() + side_base, h_addarena_.p, h_addarena_.n)) != cudaSuccess) return fail(e, "copy arena", err);
+        arena_used_ = side_base + h_addarena_.n;
+    }
+    // gather
+    if ((e = d_segs_.reserve(h_segs_.n * sizeof(RowSegment))) != cudaSuccess) return fail(e, "cudaMalloc(segments)", err);
+    if ((e = copy_h2d(d_segs_.p, h_segs_.p, h_segs_.n * sizeof(RowSegment))) != cudaSuccess) return fail(e, "copy segments", err);
+    for (int i = 0; i < 5; i++)
+        if ((e = d_rows2_[i].reserve(((size_t)new_n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(rows)", err);
+    const RowArrays from{d_meta_.as<uint32_t>(), d_koff_.as<uint32_t>(), d_klen_.as<uint32_t>(), d_voff_.as<uint32_t>(), d_vlen_.as<uint32_t>()};
+    const RowArrays to{d_rows2_[0].as<uint32_t>(), d_rows2_[1].as<uint32_t>(), d_rows2_[2].as<uint32_t>(), d_rows2_[3].as<uint32_t>(), d_rows2_[4].as<uint32_t>()};
+    if ((e = launch_gather_rows(from, to, d_segs_.as<RowSegment>(), (uint32_t)h_segs_.n, new_n, stream_)) != cudaSuccess) return fail(e, "gather_rows", err);
+    if (old_last_row == new_last_row) old_last_row = 0xffffffffu;
+    if ((e = launch_patch_commas(to.meta, old_last_row, new_last_row, stream_)) != cudaSuccess) return fail(e, "patch_commas", err);
+    for (int i = 0; i < 5; i++) { std::swap(rows[i]->p, d_rows2_[i].p); std::swap(rows[i]->cap, d_rows2_[i].cap); }
+    tape_.n_rows = new_n;
+    tape_.meta = d_meta_.as<uint32_t>(); tape_.koff = d_koff_.as<uint32_t>(); tape_.klen = d_klen_.as<uint32_t>();
+    tape_.voff = d_voff_.as<uint32_t>(); tape_.vlen = d_vlen_.as<uint32_t>();
+    tape_.arena = d_arena_.as<uint8_t>();
+    tape_.arena_bytes = (uint32_t)arena_used_;
+    if ((e = d_off_.reserve(((size_t)new_n + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(off)", err);
+    if ((e = d_scratch_.reserve(scan_scratch_words(new_n) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    E.n_rows = new_n;
+    E.tail_row = new_tail;
+    E.last_is_added = new_last_is_added;
+    E.last_base = new_last_base;
+    E.last_added = new_last_added ? *new_last_added : std::string();
+    E.dirty = false;
+    staged_version_ = doc.version;
+    return TK_OK;
+}
+
+}  // namespace tk
+

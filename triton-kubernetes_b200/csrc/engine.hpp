@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "doc.hpp"
+#include "edit.cuh"
 #include "index.cuh"
 #include "parse.cuh"
 #include "tape.hpp"
@@ -141,6 +142,16 @@ public:
     int index_lookup_direct(const Document &doc, std::string_view prefix, bool hostname, bool *module_ok, bool *direct,
                             const uint8_t **blob, size_t *blob_len, size_t *count, std::string *err);
 
+    // ---- edits of module's children on a document that lives on the device (State.Delete,
+    // AddNode, AddCluster, SetManager: a two-part path "module.<key>").  The host keeps the list of
+    // children and what was done to it; Clusters() / Nodes() answer from the index plus that list;
+    // the device tape is rebuilt from row segments when Bytes() or the host tree next need it
+    // (apply_edits).  *handled false: not an edit this path takes -- the caller builds the host tree.
+    bool edits_active() const { return edit_ != nullptr; }
+    int edit_delete(Document *doc, std::string_view path, bool *handled, std::string *err);
+    int edit_set(Document *doc, std::string_view path, Node *value, bool *handled, std::string *err);   // owns value if handled
+    int apply_edits(const Document &doc, std::string *err);
+
     // measurement hooks
     void set_timing(bool on) { timing_ = on; }
     int collect_times(std::string *err);
@@ -207,6 +218,22 @@ private:
     bool index_module_ok_ = false;
     ParseResult parsed_{};  // the verdict of the last parse: where "module" is, the sizes of the field lists
     FieldIndexBuffers fx_{};   // the lists field_find_kernel filled (kept for a second run with more room)
+    BracketBuffers bb_{};      // bracket tables of the last parse (the child list of a first edit reads match / row)
+
+    // edits (see above): host state, the child list's device and host buffers, the second set of row arrays
+    struct EditState;
+    EditState *edit_ = nullptr;
+    void drop_edit_state();
+    bool edit_record_dead(int f, uint32_t j) const;
+    bool edit_added_any(int f, std::string_view prefix) const;
+    void edit_added_pairs(int f, std::string_view prefix, std::vector<std::pair<std::string_view, std::string_view>> *pairs) const;
+    void adopt_added_values(Document *doc);
+    int enter_edit_mode(const Document &doc, std::string *err);
+    bool edit_path_key(const Document &doc, std::string_view path, std::string_view *key, std::string *err, int *rc);
+    DevBuf d_cflags_, d_crank_, d_clist_[4], d_ckeyoff_, d_ckeys_, d_rows2_[5], d_segs_;
+    PinVec<uint32_t> h_clist_[3], h_addrows_[5];
+    PinVec<uint8_t> h_ckeys_, h_addarena_;
+    PinVec<RowSegment> h_segs_;
 
     // results
     PinVec<uint8_t> h_out_;
