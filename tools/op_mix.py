@@ -159,14 +159,34 @@ def main():
     assert ctypes.string_at(o, n) == text
     L.tk_state_free(h)
 
+    # the same edits on a document that stays on the device (no Get first: the host tree is never built)
+    L.tk_state_host_tree_built.argtypes = [c_void_p]
+    h = p_new(ctypes.addressof(hb), len(base))
+    dt = D.tkb_add_node_loop(h, a_cks, a_ck_lens, a_names, a_name_lens, a_jsons, a_json_lens, len(add), tk.state.TK_VALUE_MAP)
+    assert dt > 0 and not L.tk_state_host_tree_built(h)
+    prod["AddNode (document on the device)"] = {"ops_per_s": len(add) / dt, "ops": len(add)}
+    t0 = time.perf_counter(); o, n = p_bytes(h); tdev = time.perf_counter() - t0
+    prod["Bytes after edits (document on the device)"] = {"seconds (tape rebuilt on the GPU from row segments, serialised, copied back)": tdev,
+                                                          "MB_per_s": n / 1e6 / tdev}
+    assert ctypes.string_at(o, n) == text and not L.tk_state_host_tree_built(h)
+    L.tk_state_free(h)
+    h = p_new(pinned.data_ptr(), len(text))
+    dt = D.tkb_delete_loop(h, d_arr, d_lens, len(del_paths))
+    assert dt > 0 and not L.tk_state_host_tree_built(h)
+    t0 = time.perf_counter(); _, n = p_bytes(h); tdev = time.perf_counter() - t0
+    assert n == len(base), (n, len(base))
+    prod["Delete (document on the device)"] = {"ops_per_s": len(del_paths) / dt, "ops": len(del_paths), "Bytes_afterwards_s": tdev}
+    L.tk_state_free(h)
+
     h = p_new(pinned.data_ptr(), len(text))
     deleted = c_size_t()
     dt = D.tkb_destroy_sweep(h, ck_arr, ck_lens, cp_arr, cp_lens, C, byref(deleted))
     assert dt > 0, dt
     t0 = time.perf_counter(); o, n = p_bytes(h); tbytes = time.perf_counter() - t0
     final = ctypes.string_at(o, n)
+    built_after_sweep = L.tk_state_host_tree_built(h)
     L.tk_state_free(h)
-    prod["config5_destroy_sweep"] = {"seconds": dt, "deletes": deleted.value, "ops_per_s (Nodes + Delete calls)": (deleted.value + C) / dt,
+    prod["config5_destroy_sweep"] = {"host_tree_built": bool(built_after_sweep), "seconds": dt, "deletes": deleted.value, "ops_per_s (Nodes + Delete calls)": (deleted.value + C) / dt,
                                      "final_Bytes_s": tbytes, "final_document_bytes": len(final)}
     out["product"] = prod
 

@@ -307,11 +307,22 @@ static void flat_value(Sink &out, const Node *n, uint32_t depth, const std::stri
 // flattened by several threads, each into its own vectors, and appended in order.  The tree is
 // only read.  Offsets of a worker's rows are relative to its own arena and are moved on append.
 constexpr size_t FORK_MIN_MEMBERS = 8192;
+typedef std::pair<const std::string *, const Node *> MemberRef;
+static void flat_pairs_forked(FlatPinned &out, const std::vector<MemberRef> &members, uint32_t depth, bool comma_after_last);
 static void flat_members_forked(FlatPinned &out, const MapNode *node, uint32_t depth) {
-    const size_t n = node->m.size();
-    std::vector<const std::pair<const std::string, Node *> *> members;
-    members.reserve(n);
-    for (auto &kv : node->m) members.push_back(&kv);
+    std::vector<MemberRef> members;
+    members.reserve(node->m.size());
+    for (auto &kv : node->m) members.emplace_back(&kv.first, kv.second);
+    flat_pairs_forked(out, members, depth, false);
+}
+// members (key, value) flattened one after another at `depth`, a comma after each but -- unless
+// comma_after_last -- the last
+static void flat_pairs_forked(FlatPinned &out, const std::vector<MemberRef> &members, uint32_t depth, bool comma_after_last) {
+    const size_t n = members.size();
+    if (n < 1024) {
+        for (size_t i = 0; i < n; i++) flat_value(out, members[i].second, depth, members[i].first, comma_after_last || i + 1 < n, false);
+        return;
+    }
     const size_t hw = std::max<size_t>(1, std::thread::hardware_concurrency());
     const size_t workers = std::max<size_t>(2, std::min<size_t>({hw, 16, n / 1024}));
     std::vector<FlatLocal> parts(workers);
@@ -322,7 +333,7 @@ static void flat_members_forked(FlatPinned &out, const MapNode *node, uint32_t d
             try {
                 FlatLocal &p = parts[w];
                 for (size_t i = w * n / workers; i < (w + 1) * n / workers; i++)
-                    flat_value(p, members[i]->second, depth, &members[i]->first, i + 1 < n, false);
+                    flat_value(p, members[i].second, depth, members[i].first, comma_after_last || i + 1 < n, false);
             } catch (...) {   // out of memory: reported like a failed pinned allocation
                 failed = true;
             }
@@ -1176,14 +1187,13 @@ namespace tk {
 
 // What the host knows about module's children while a document is edited on the device.
 struct Engine::EditState {
-    struct Base { uint32_t key_off, key_len, rows, tape_row; bool live; };        // a child the parser found
+    struct Base { uint32_t key_off, key_len, rows, tape_row; uint32_t rec[2]; bool live; };   // a child the parser found; rec: its index records (or none)
     struct Added {                                                               // a child set since
         Node *value = nullptr;      // as given (a record stays a record: opaque, members in the given order)
         bool on_device = false;
         uint32_t rows = 0, tape_row = 0;
         bool has[2] = {false, false};   // a map with a string "name" / "hostname": visible to Clusters() / Nodes()
         std::string field[2];
-        FlatLocal flat;             // its rows, until they have been uploaded
     };
     std::vector<Base> base;         // in key order
     const char *keys = nullptr;     // their keys, one after another (h_ckeys_)
@@ -1311,7 +1321,17 @@ int Engine::enter_edit_mode(const Document &doc, std::string *err) {
     E->base.resize(nc);
     for (uint32_t j = 0; j < nc; j++) {
         const uint32_t row = h_clist_[0].p[j], end = h_clist_[1].p[j];
-        E->base[j] = EditState::Base{h_clist_[2].p[j], h_clist_[2].p[j + 1] - h_clist_[2].p[j], end - row + 1, row, true};
+        E->base[j] = EditState::Base{h_clist_[2].p[j], h_clist_[2].p[j + 1] - h_clist_[2].p[j], end - row + 1, row, {0xffffffffu, 0xffffffffu}, true};
+    }
+    // which index records belong to which child: both lists are in key order, one walk each
+    for (int f = 0; f < 2; f++) {
+        const IndexView v{h_foff_[f].p, reinterpret_cast<const char *>(h_fblob_[f].p), index_m_[f]};
+        uint32_t c = 0;
+        for (uint32_t j = 0; j < v.m; j++) {
+            const std::string_view k = v.key(j);
+            while (c < nc && E->key(E->base[c]) < k) c++;
+            if (c < nc && E->key(E->base[c]) == k) E->base[c].rec[f] = j;
+        }
     }
     E->n_rows = n;
     E->head_rows = module_row + 1;
@@ -1321,20 +1341,6 @@ int Engine::enter_edit_mode(const Document &doc, std::string *err) {
     for (int f = 0; f < 2; f++) E->dead[f].assign(index_m_[f], 0);
     edit_ = E;
     return TK_OK;
-}
-
-// the index record of child `key` under field f, if it has one, is no longer part of any answer
-static void tombstone(std::vector<uint8_t> &dead, const uint32_t *off, const char *blob, uint32_t m, std::string_view key) {
-    auto key_at = [&](uint32_t j) {
-        const char *rec = blob + off[j];
-        uint32_t fl, kl;
-        memcpy(&fl, rec, 4);
-        memcpy(&kl, rec + 4 + fl, 4);
-        return std::string_view(rec + 8 + fl, kl);
-    };
-    uint32_t lo = 0, hi = m;
-    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (key_at(mid) < key) lo = mid + 1; else hi = mid; }
-    if (lo < m && key_at(lo) == key) dead[lo] = 1;
 }
 
 int Engine::edit_delete(Document *doc, std::string_view path, bool *handled, std::string *err) {
@@ -1356,7 +1362,7 @@ int Engine::edit_delete(Document *doc, std::string_view path, bool *handled, std
     } else {
         b->live = false;
         for (int f = 0; f < 2; f++)
-            if (index_m_[f]) tombstone(E.dead[f], h_foff_[f].p, reinterpret_cast<const char *>(h_fblob_[f].p), index_m_[f], key);
+            if (b->rec[f] != 0xffffffffu) E.dead[f][b->rec[f]] = 1;
     }
     E.live--;
     E.dirty = true;
@@ -1370,15 +1376,7 @@ int Engine::edit_set(Document *doc, std::string_view path, Node *value, bool *ha
     int rc;
     if (!edit_path_key(*doc, path, &key, err, &rc)) return rc;
     EditState &E = *edit_;
-    EditState::Added a;
-    const std::string k(key);
-    try {
-        flat_value(a.flat, value, 2, &k, true, false);   // a child of module: depth 2, a comma after it (taken off the last one when the tape is rebuilt)
-    } catch (...) {
-        *err = "out of memory";
-        return TK_ELIMIT;
-    }
-    a.rows = (uint32_t)a.flat.meta.size();
+    EditState::Added a;   // (its rows are made when the tape is next rebuilt)
     if (value && value->kind == Kind::Map) {
         auto &m = static_cast<const MapNode *>(value)->m;
         static const char *const names[2] = {"name", "hostname"};
@@ -1397,11 +1395,11 @@ int Engine::edit_set(Document *doc, std::string_view path, Node *value, bool *ha
         if (EditState::Base *b = E.find_base(key); b && b->live) {
             b->live = false;
             for (int f = 0; f < 2; f++)
-                if (index_m_[f]) tombstone(E.dead[f], h_foff_[f].p, reinterpret_cast<const char *>(h_fblob_[f].p), index_m_[f], key);
+                if (b->rec[f] != 0xffffffffu) E.dead[f][b->rec[f]] = 1;
         } else {
             E.live++;
         }
-        E.added.emplace(k, std::move(a));
+        E.added.emplace(std::string(key), std::move(a));
     }
     E.dirty = true;
     doc->version++;
@@ -1422,6 +1420,44 @@ int Engine::apply_edits(const Document &doc, std::string *err) {
     if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return fail(e, "synchronize", err);
     h_segs_.clear(); h_addarena_.clear();
     for (auto &v : h_addrows_) v.clear();
+    // the rows of the children set since the last rebuild: flattened (many of them: by several threads)
+    // straight into the pinned upload buffers, one child after another in key order
+    const size_t side_base = (arena_used_ + 15) & ~size_t(15);
+    {
+        std::vector<MemberRef> fresh;
+        std::vector<EditState::Added *> fresh_added;
+        for (auto &kv : E.added)
+            if (!kv.second.on_device) { fresh.emplace_back(&kv.first, kv.second.value); fresh_added.push_back(&kv.second); }
+        if (!fresh.empty()) {
+            FlatPinned sink{h_addrows_[0], h_addrows_[1], h_addrows_[2], h_addrows_[3], h_addrows_[4], h_addarena_};
+            try {
+                flat_pairs_forked(sink, fresh, 2, true);   // children of module: depth 2, a comma after each (taken off the last one below)
+            } catch (...) {
+                *err = "out of memory";
+                return TK_ELIMIT;
+            }
+            // how many rows each child took: a child ends where depth 2 is reached again
+            const uint32_t *meta = h_addrows_[0].p;
+            const size_t total = h_addrows_[0].n;
+            size_t r = 0;
+            for (EditState::Added *a : fresh_added) {
+                const size_t start = r;
+                const uint32_t kind = meta[r] & 15u;
+                r++;
+                if (kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR) {
+                    while (r < total && !((meta[r] >> META_DEPTH_SHIFT) == 2 && ((meta[r] & 15u) == ROW_CLOSE_OBJ || (meta[r] & 15u) == ROW_CLOSE_ARR))) r++;
+                    r++;   // its closing row
+                }
+                a->rows = (uint32_t)(r - start);
+            }
+            // (FlatPinned keeps offsets relative to its own arena, the second and fourth array: moved behind the device arena)
+            uint32_t *ko = h_addrows_[1].p, *kl = h_addrows_[2].p, *vo = h_addrows_[3].p, *vl = h_addrows_[4].p;
+            for (size_t i = 0; i < total; i++) {
+                ko[i] = kl[i] ? ko[i] + (uint32_t)side_base : 0u;
+                vo[i] = vl[i] ? vo[i] + (uint32_t)side_base : 0u;
+            }
+        }
+    }
     uint32_t cur = 0, upload_rows = 0;
     auto add_seg = [&](uint32_t src, uint32_t n) {
         if (!n) return;
@@ -1437,7 +1473,6 @@ int Engine::apply_edits(const Document &doc, std::string *err) {
     const std::string *new_last_added = nullptr;
     size_t bi = 0;
     auto ai = E.added.begin();
-    const size_t side_base = (arena_used_ + 15) & ~size_t(15);
     while (bi < E.base.size() || ai != E.added.end()) {
         while (bi < E.base.size() && !E.base[bi].live) bi++;
         const bool take_base = bi < E.base.size() && (ai == E.added.end() || E.key(E.base[bi]) < std::string_view(ai->first));
@@ -1455,20 +1490,10 @@ int Engine::apply_edits(const Document &doc, std::string *err) {
             if (a.on_device) {
                 add_seg(a.tape_row, a.rows);
             } else {
-                // its rows go behind the old ones, its strings behind the arena
-                const uint32_t base_off = (uint32_t)(side_base + h_addarena_.n);
-                for (uint32_t r = 0; r < a.rows; r++) {
-                    h_addrows_[0].push(a.flat.meta[r]);
-                    h_addrows_[1].push(a.flat.klen[r] ? a.flat.koff[r] + base_off : 0u);
-                    h_addrows_[2].push(a.flat.klen[r]);
-                    h_addrows_[3].push(a.flat.vlen[r] ? a.flat.voff[r] + base_off : 0u);
-                    h_addrows_[4].push(a.flat.vlen[r]);
-                }
-                h_addarena_.append(a.flat.arena.data(), a.flat.arena.size());
+                // its rows were flattened above, in this order: they go behind the old rows, its strings behind the arena
                 add_seg(E.n_rows + upload_rows, a.rows);
                 upload_rows += a.rows;
                 a.on_device = true;
-                a.flat = FlatLocal();
             }
             a.tape_row = at;
             if (E.last_is_added && E.last_added == ai->first) old_last_row = cur - 1;
