@@ -315,7 +315,16 @@ def run_ours(args, rank, local_rank, world):
     AT_BLOCK = ctypes.CFUNCTYPE(None, c_int)
     D.tkb_product_run.argtypes = [POINTER(c_void_p), c_size_t, c_size_t, c_int, c_int, c_int, c_int, POINTER(c_char_p), POINTER(c_size_t),
                                   c_size_t, c_size_t, c_size_t, c_size_t, c_size_t, c_size_t, c_size_t, c_char_p, c_char_p, c_size_t,
-                                  AT_BLOCK, AT_BLOCK, POINTER(c_double), POINTER(ctypes.c_ulonglong), POINTER(ctypes.c_ulonglong)]
+                                  AT_BLOCK, AT_BLOCK, POINTER(c_int), c_size_t, POINTER(c_double), POINTER(ctypes.c_ulonglong),
+                                  POINTER(ctypes.c_ulonglong)]
+    # this rank's share of the host cores: its worker threads are pinned inside it (one core each)
+    try:
+        allowed = sorted(os.sched_getaffinity(0))
+    except AttributeError:
+        allowed = list(range(os.cpu_count() or 1))
+    per_rank = max(1, len(allowed) // max(1, world))
+    my_cpus = allowed[local_rank * per_rank:(local_rank + 1) * per_rank] if world > 1 else []
+    cpu_arr = (c_int * max(1, len(my_cpus)))(*(my_cpus or [0]))
     dev_ptrs = (c_void_p * R_COPIES)(*[t.data_ptr() for t in dev_copies])
     host_ptrs = (c_void_p * 1)(pinned.data_ptr())
     # what a Go caller holds: the text in ordinary heap memory (ioutil.ReadFile's slice), not pinned
@@ -358,7 +367,8 @@ def run_ours(args, rank, local_rank, world):
         cb_a, cb_b = AT_BLOCK(at_start), AT_BLOCK(at_end)
         rc = D.tkb_product_run(ptrs, n_ptrs, len(text), local_rank, 0 if to_host else 1, 1 if to_host else 0,
                                1 if mode == "pageable" else 0, arr, lens, len(cks), args.clusters, args.clusters * args.nodes, steps,
-                               blocks, warmup, max(1, inflight), text[:64], text[-64:], len(text), cb_a, cb_b, phase, byref(h2d), byref(d2h))
+                               blocks, warmup, max(1, inflight), text[:64], text[-64:], len(text), cb_a, cb_b, cpu_arr, len(my_cpus), phase,
+                               byref(h2d), byref(d2h))
         if rc:
             raise SystemExit("bench.py: a step failed (%d): %s" % (rc, L.tk_last_error(None)))
         ms = [max(m["a"].elapsed_time(m["b"]), m["wall"]) for m in marks]
@@ -375,7 +385,9 @@ def run_ours(args, rank, local_rank, world):
         per = sorted(x / steps for x in ms)
         return {"median": statistics.median(per), "min": per[0], "max": per[-1], "blocks": len(per)}
 
-    inflight = args.inflight if args.inflight > 0 else max(1, min(4, (os.cpu_count() or 1) // max(1, world)))
+    # documents in flight: 4, but never more spinning worker threads than this rank's share of the cores less one
+    # (left for the main thread, NCCL's proxy thread and the driver's own threads)
+    inflight = args.inflight if args.inflight > 0 else max(1, min(4, per_rank - 1 if world > 1 else (os.cpu_count() or 1)))
     sampler = ClockSampler(local_rank)
     sampler.start()
     # ---- value: text resident in HBM, result left in HBM
@@ -463,6 +475,11 @@ def run_ours(args, rank, local_rank, world):
                                                              "result memcpy'd out of the handle's buffer (C.GoBytes, :94)",
                                                      "phase_ms": {k: ph_page[i] for i, k in enumerate(("new", "clusters", "nodes", "bytes"))}}},
                        "driver": "tools/bench_driver.c (the step is a compiled loop over the C ABI)",
+                       "host_threads": {"workers_per_rank": inflight, "cores_per_rank": per_rank if world > 1 else len(allowed),
+                                        "pinned_to": my_cpus if world > 1 else "not pinned (one rank)"},
+                       "pcie_per_rank_GBps": {"e2e_h2d": copy_stats[0] / (se["median"] * 1e-3) / 1e9, "e2e_d2h": copy_stats[1] / (se["median"] * 1e-3) / 1e9,
+                                              "note": "bytes copied per step / e2e step time, per GPU; with both directions busy one B200 on "
+                                                      "this pool's hosts sustains about 49 GB/s each way alone"},
                        "clusters": args.clusters, "nodes_per_cluster": args.nodes, "document_bytes": len(text)},
             "e2e": {"value": ops(se["median"]), "unit": "ops/s",
                     "ms_per_step": se["median"], "h2d_bytes_per_step": copy_stats[0], "d2h_bytes_per_step": copy_stats[1],

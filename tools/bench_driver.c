@@ -68,6 +68,7 @@ int tkb_product_step(const void *text, size_t n, int device_text, int to_host, c
  * malloc'd buffer, as C.GoBytes does.
  * Returns 0, or the first failing step's code. */
 #include <pthread.h>
+#include <sched.h>
 #include <stdlib.h>
 
 typedef struct {
@@ -79,6 +80,7 @@ typedef struct {
     double phase_ms[5]; size_t out_len; unsigned long long h2d, d2h;
     const char *expect_head, *expect_tail; size_t expect_n;
     char *copy_out; size_t copy_cap;
+    const int *cpus; size_t n_cpus;   /* the cores this rank's workers stay on (n_cpus 0: wherever the scheduler puts them) */
 } tkb_worker;
 
 static int tkb_one(tkb_worker *w, size_t i, double *phase) {
@@ -105,6 +107,14 @@ static int tkb_one(tkb_worker *w, size_t i, double *phase) {
 static void *tkb_worker_main(void *arg) {
     tkb_worker *w = (tkb_worker *)arg;
     double scratch_phase[5] = {0, 0, 0, 0, 0};
+    if (w->n_cpus) {
+        /* one core per worker, out of this rank's share: spinning waits of one rank do not push another rank's
+         * workers off their cores, and the pinned buffers a worker allocates are first touched near where it runs */
+        cpu_set_t set;
+        CPU_ZERO(&set);
+        CPU_SET(w->cpus[(size_t)w->worker % w->n_cpus], &set);
+        pthread_setaffinity_np(pthread_self(), sizeof set, &set);
+    }
     int rc = tk_set_device(w->device);
     for (size_t k = 0; !rc && k < w->warmup_each; k++) rc = tkb_one(w, (size_t)w->worker + k * 64, scratch_phase);
     for (size_t b = 0; b < w->blocks; b++) {
@@ -131,7 +141,8 @@ static void *tkb_worker_main(void *arg) {
 int tkb_product_run(const void *const *texts, size_t n_texts, size_t n, int device, int device_text, int to_host, int pageable,
                     const char *const *cks, const size_t *ck_lens, size_t n_cks, size_t want_clusters, size_t want_nodes, size_t steps,
                     size_t blocks, size_t warmup, size_t inflight, const char *expect_head, const char *expect_tail, size_t expect_n,
-                    void (*at_start)(int), void (*at_end)(int), double *phase_ms, unsigned long long *h2d, unsigned long long *d2h) {
+                    void (*at_start)(int), void (*at_end)(int), const int *cpus, size_t n_cpus, double *phase_ms, unsigned long long *h2d,
+                    unsigned long long *d2h) {
     if (inflight < 1) inflight = 1;
     if (inflight > 64) inflight = 64;
     if (blocks < 1) blocks = 1;
@@ -152,6 +163,7 @@ int tkb_product_run(const void *const *texts, size_t n_texts, size_t n, int devi
         w[t].warmup_each = (warmup + inflight - 1) / inflight; if (!w[t].warmup_each) w[t].warmup_each = 1;
         w[t].worker = (int)t; w[t].go = &go; w[t].done = &done; w[t].next = &next; w[t].mu = &mu; w[t].rc = &rc;
         w[t].expect_head = expect_head; w[t].expect_tail = expect_tail; w[t].expect_n = expect_n;
+        w[t].cpus = cpus; w[t].n_cpus = n_cpus;
         pthread_create(&th[t], NULL, tkb_worker_main, &w[t]);
     }
     for (size_t b = 0; b < blocks; b++) {

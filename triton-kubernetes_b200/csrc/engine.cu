@@ -199,6 +199,7 @@ struct StreamPool {
 
 Engine::~Engine() {
     drop_edit_state();
+    for (auto &ev : stage_ev_) if (ev) cudaEventDestroy(ev);
     for (auto &p : pending_) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto ev : free_events_) cudaEventDestroy(ev);
     if (stream_) {
@@ -592,7 +593,33 @@ int Engine::upload_text(const char *raw, size_t n, std::string *err) {
     const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 64;
     cudaError_t e;
     if ((e = d_arena_.reserve(padded)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
-    if (n && (e = copy_h2d(d_arena_.p, raw, n)) != cudaSuccess) return fail(e, "copy text", err);
+    // Text in ordinary (pageable) host memory -- what a Go caller holds: ioutil.ReadFile's slice,
+    // backend/local/backend.go:60-65 -- is not copied by the driver's own staging (a few GB/s) but
+    // through two pinned blocks of this handle: the calling thread fills one while the copy engine
+    // drains the other.  Pinned or registered memory is copied from where it is.
+    bool pageable = false;
+    if (n >= STAGE_MIN) {
+        cudaPointerAttributes attr;
+        if (cudaPointerGetAttributes(&attr, raw) != cudaSuccess) { (void)cudaGetLastError(); pageable = true; }
+        else pageable = attr.type == cudaMemoryTypeUnregistered;
+    }
+    if (pageable) {
+        if (!h_stage_[0].reserve(STAGE_CHUNK) || !h_stage_[1].reserve(STAGE_CHUNK)) { *err = "cuda: pinned host allocation failed"; return TK_ECUDA; }
+        for (int k = 0; k < 2; k++)
+            if (!stage_ev_[k] && (e = cudaEventCreateWithFlags(&stage_ev_[k], cudaEventDisableTiming)) != cudaSuccess) return fail(e, "cudaEventCreate", err);
+        bool busy[2] = {false, false};
+        int k = 0;
+        for (size_t off = 0; off < n; off += STAGE_CHUNK, k ^= 1) {
+            const size_t len = std::min(STAGE_CHUNK, n - off);
+            if (busy[k] && (e = cudaEventSynchronize(stage_ev_[k])) != cudaSuccess) return fail(e, "copy text", err);
+            memcpy(h_stage_[k].p, raw + off, len);
+            if ((e = copy_h2d(d_arena_.as<uint8_t>() + off, h_stage_[k].p, len)) != cudaSuccess) return fail(e, "copy text", err);
+            if ((e = cudaEventRecord(stage_ev_[k], stream_)) != cudaSuccess) return fail(e, "copy text", err);
+            busy[k] = true;
+        }
+    } else if (n && (e = copy_h2d(d_arena_.p, raw, n)) != cudaSuccess) {
+        return fail(e, "copy text", err);
+    }
     if ((e = cudaMemsetAsync(d_arena_.as<uint8_t>() + n, ' ', padded - n, stream_)) != cudaSuccess) return fail(e, "pad text", err);
     raw_len_ = n;
     arena_used_ = padded;

@@ -188,6 +188,11 @@ private:
     unsigned long long timed_launches_[K_COUNT] = {}, launches_[K_COUNT] = {};
     unsigned long long h2d_bytes_ = 0, d2h_bytes_ = 0;
 
+    // staging of text that arrives in pageable host memory (upload_text)
+    static constexpr size_t STAGE_CHUNK = size_t(4) << 20, STAGE_MIN = size_t(1) << 20;
+    PinVec<uint8_t> h_stage_[2];
+    cudaEvent_t stage_ev_[2] = {nullptr, nullptr};
+
     // host (pinned) tape + key index
     PinVec<uint32_t> h_meta_, h_koff_, h_klen_, h_voff_, h_vlen_, h_koffs_;
     PinVec<uint8_t> h_arena_, h_keys_;
