@@ -14,9 +14,14 @@ import torch
 tk = importlib.import_module("triton-kubernetes_b200")
 synth = importlib.import_module("triton-kubernetes_b200.synth")
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 15
-seed = tk.New("bench", synth.document(1000, 100))
-text = seed.Bytes()
-seed.close()
+if os.environ.get("TK_TEXT_FROM_ORACLE"):      # (for experiments with kernels that deliberately compute the wrong thing)
+    from oracle import oracle as O
+    O.build()
+    text = O.New("bench", synth.document(1000, 100)).Bytes()
+else:
+    seed = tk.New("bench", synth.document(1000, 100))
+    text = seed.Bytes()
+    seed.close()
 dev_text = torch.frombuffer(bytearray(text), dtype=torch.uint8).to("cuda:0")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:0")
 torch.cuda.synchronize()
