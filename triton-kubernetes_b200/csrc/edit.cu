@@ -29,9 +29,10 @@ __global__ void child_entries_kernel(TapeView t, const uint32_t *__restrict__ fl
     if (r >= t.n_rows || !flags[r]) return;
     const uint32_t j = rank[r], kind = __ldg(t.meta + r) & 15u;
     uint32_t end = r;
-    if (kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR) {   // voff of an opening row is its bracket
-        const uint32_t cb = br_match[__ldg(t.voff + r)];
-        end = cb != 0xffffffffu ? br_row[cb] : r;
+    if (kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR) {   // voff of an opening row: the row that closes it, or its bracket
+        const uint32_t v = __ldg(t.voff + r);
+        if (t.rows_direct) end = v;
+        else { const uint32_t cb = br_match[v]; end = cb != 0xffffffffu ? br_row[cb] : r; }
     }
     out.row[j] = r;
     out.end[j] = end;

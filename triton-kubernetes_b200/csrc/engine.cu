@@ -13,6 +13,7 @@
 #include <thread>
 
 #include "kernels.cuh"
+#include "lines.cuh"
 #include "tk_state.h"
 
 namespace tk {
@@ -127,6 +128,7 @@ const char *kernel_name(int kind) {
     static const char *const names[K_COUNT] = {"row_offsets_kernel", "emit_kernel", "prefix_match_kernel", "scan_tokens_kernel (carry protocol)",
                                                "token_agg + token_blocks kernels", "brackets_kernel", "sort_brackets (radix passes)", "match_kernel",
                                                "decode kernels", "rows_kernel", "key_order_kernel", "field_pack_kernel (module index)", "field_find_kernel",
+                                               "lines_count + lines_prefix kernels", "lines_rows_kernel", "lines structure kernels",
                                                "scan_count_kernel", "scan_prefix_kernel", "scan_emit_kernel"};
     return kind >= 0 && kind < K_COUNT ? names[kind] : "";
 }
@@ -475,6 +477,7 @@ int Engine::stage_tape(const Document &doc, std::string *err) {
     tape_.n_rows = (uint32_t)n;
     tape_.arena_bytes = (uint32_t)h_arena_.n;
     tape_.text_len = 0;
+    tape_.rows_direct = false;
     tape_.meta = d_meta_.as<uint32_t>(); tape_.koff = d_koff_.as<uint32_t>(); tape_.klen = d_klen_.as<uint32_t>();
     tape_.voff = d_voff_.as<uint32_t>(); tape_.vlen = d_vlen_.as<uint32_t>(); tape_.arena = d_arena_.as<uint8_t>();
     staged_version_ = doc.version;
@@ -644,6 +647,61 @@ int Engine::upload_text_device(const void *dev_raw, size_t n, std::string *err) 
     return TK_OK;
 }
 
+// state.New for text in the indented form (lines.cu): every launch queued at once -- sizes come from
+// bounds, the real counts stay on the device -- and one wait at the end for the verdict.
+int Engine::parse_lines(size_t n, ParseResult *out, bool *accepted, std::string *err) {
+    *accepted = false;
+    cudaError_t e;
+    const uint8_t *raw = d_arena_.as<uint8_t>();
+    ParseResult *d_res = d_res_.as<ParseResult>();
+    // (a line of the indented form is rarely under 16 bytes; a text with more lines than that is declined)
+    const size_t row_cap = std::min<size_t>(n / 16 + 4096, 0x7fffffffu);
+    DevBuf *rows[5] = {&d_meta_, &d_koff_, &d_klen_, &d_voff_, &d_vlen_};
+    for (int i = 0; i < 5; i++)
+        if ((e = rows[i]->reserve((row_cap + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(rows)", err);
+    if ((e = d_scratch_.reserve(lines_scratch_words(n) * 4 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    if ((e = d_tiles_.reserve((size_t)lines_row_blocks((uint32_t)row_cap) * 8 * 4 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    RowBuffers rb{d_meta_.as<uint32_t>(), d_koff_.as<uint32_t>(), d_klen_.as<uint32_t>(), d_voff_.as<uint32_t>(), d_vlen_.as<uint32_t>()};
+    uint32_t *scratch = d_scratch_.as<uint32_t>();
+    if ((e = timed(K_LINES_COUNT, [&] { return launch_lines_count(raw, n, scratch, d_res, stream_); })) != cudaSuccess) return fail(e, "lines_count", err);
+    if ((e = timed(K_LINES_ROWS, [&] { return launch_lines_rows(raw, n, scratch, rb, (uint32_t)row_cap, d_res, stream_); })) != cudaSuccess)
+        return fail(e, "lines_rows", err);
+    if ((e = timed(K_LINES_STRUCTURE, [&] { return launch_lines_structure(raw, rb, (uint32_t)row_cap, d_tiles_.as<uint32_t>(), d_res, stream_); })) != cudaSuccess)
+        return fail(e, "lines_structure", err);
+    // module index lists, as after the general parse (the row count is still on the device: the grid covers the bound)
+    tape_.n_rows = (uint32_t)row_cap;
+    tape_.arena_bytes = (uint32_t)arena_used_;
+    tape_.text_len = (uint32_t)n;
+    tape_.rows_direct = true;
+    tape_.meta = rb.meta; tape_.koff = rb.koff; tape_.klen = rb.klen; tape_.voff = rb.voff; tape_.vlen = rb.vlen;
+    tape_.arena = raw;
+    for (int f = 0; f < 2; f++) {
+        const size_t cap = std::min<size_t>(row_cap, n / 256 + 1024);
+        if ((e = d_frefs_[f].reserve(cap * sizeof(FieldRef))) != cudaSuccess || (e = d_foff_[f].reserve((cap + 1) * 4)) != cudaSuccess)
+            return fail(e, "cudaMalloc(index)", err);
+        fx_.refs[f] = d_frefs_[f].as<FieldRef>();
+        fx_.off[f] = d_foff_[f].as<uint32_t>();
+        fx_.cap[f] = (uint32_t)cap;
+    }
+    if ((e = d_find_status_.reserve(field_status_words((uint32_t)row_cap) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
+    fx_.status = d_find_status_.as<unsigned long long>();
+    if ((e = timed(K_FIELD_FIND, [&] { return launch_field_find(tape_, fx_, d_res, stream_); })) != cudaSuccess) return fail(e, "field_find", err);
+    int rc = fetch_result(err);
+    if (rc) return rc;
+    if (h_res_.p->fast_reject || h_res_.p->n_rows == 0 || h_res_.p->n_rows > row_cap) return TK_OK;
+    *out = *h_res_.p;
+    *accepted = true;
+    const uint32_t n_rows = out->n_rows;
+    if ((e = d_off_.reserve(((size_t)n_rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(off)", err);
+    if ((e = d_scratch_.reserve(scan_scratch_words(n_rows) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    tape_.n_rows = n_rows;
+    tape_from_parse_ = true;
+    bb_ = BracketBuffers{};
+    parsed_ = *out;
+    index_version_ = 0;
+    return TK_OK;
+}
+
 // Every kernel of the pipeline, on the text already resident at the start of the arena.  Leaves
 // the tape (rows in input order) on the device and the verdict in *out.  Host synchronisations:
 // after P1 (token count sizes the later buffers), after P2a (row / bracket counts), after the
@@ -658,6 +716,17 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     if ((e = d_res_.reserve(sizeof(ParseResult))) != cudaSuccess) return fail(e, "cudaMalloc(result)", err);
     ParseResult *d_res = d_res_.as<ParseResult>();
     if (n == 0) { out->invalid = 1; return TK_OK; }
+
+    // ---- text that is already in the indented form (every file this library or the reference wrote):
+    //      the line-by-line pass builds the tape; anything else it declines, and the general pipeline runs
+    static const bool no_fast_path = getenv("TK_NO_FAST_PATH") != nullptr;   // (development: compare the two)
+    if (!no_fast_path) {
+        bool accepted = false;
+        int rc = parse_lines(n, out, &accepted, err);
+        tr.mark("lines:done");
+        if (rc || accepted) return rc;
+        memset(out, 0, sizeof *out);
+    }
 
     // ---- P1 (re-run with a larger token buffer in the rare case the estimate was too small)
     size_t cap = n / 4 + 4096;
@@ -782,6 +851,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
     tape_.n_rows = n_rows;
     tape_.arena_bytes = (uint32_t)arena_used_;
     tape_.text_len = (uint32_t)n;
+    tape_.rows_direct = false;
     tape_.meta = rb.meta; tape_.koff = rb.koff; tape_.klen = rb.klen; tape_.voff = rb.voff; tape_.vlen = rb.vlen;
     tape_.arena = d_arena_.as<uint8_t>();
     for (int f = 0; f < 2; f++) {

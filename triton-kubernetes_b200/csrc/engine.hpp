@@ -90,7 +90,7 @@ struct DevBuf {
 
 enum KernelKind {
     K_ROW_OFFSETS = 0, K_EMIT, K_PREFIX_MATCH, K_SCAN_TOKENS, K_TOKEN_PREFIX, K_BRACKETS, K_SORT_BRACKETS, K_MATCH,
-    K_DECODE, K_ROWS, K_KEY_ORDER, K_MODULE_INDEX, K_FIELD_FIND, K_SCAN_COUNT, K_SCAN_PREFIX, K_SCAN_EMIT, K_COUNT
+    K_DECODE, K_ROWS, K_KEY_ORDER, K_MODULE_INDEX, K_FIELD_FIND, K_LINES_COUNT, K_LINES_ROWS, K_LINES_STRUCTURE, K_SCAN_COUNT, K_SCAN_PREFIX, K_SCAN_EMIT, K_COUNT
 };
 const char *kernel_name(int kind);
 void set_default_timing(bool on);  // engines created from now on start with per-kernel timing on/off
@@ -167,6 +167,7 @@ private:
     cudaError_t copy_d2h(void *dst, const void *src, size_t bytes);
     template <class F> cudaError_t timed(int kind, F &&launch);
     int fetch_result(std::string *err);
+    int parse_lines(size_t n, ParseResult *out, bool *accepted, std::string *err);
     int build_index(const Document &doc, std::string *err);
     struct IndexView;
     void index_range(int field, std::string_view prefix, uint32_t *lo, uint32_t *hi);

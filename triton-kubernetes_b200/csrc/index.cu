@@ -45,7 +45,8 @@ __device__ __forceinline__ void st_relaxed(u64 *p, u64 v) { asm volatile("st.rel
 constexpr int FF_THREADS = 512, FF_ITEMS = 8, FF_TILE = FF_THREADS * FF_ITEMS, FF_HALO = 64;
 constexpr uint32_t FF_MAX_WALK = 4096;   // rows looked through for the child before giving up (index_slow)
 
-__global__ void __launch_bounds__(FF_THREADS, 3) field_find_kernel(TapeView t, uint32_t n_rows, FieldIndexBuffers fx, ParseResult *res) {
+__global__ void __launch_bounds__(FF_THREADS, 3) field_find_kernel(TapeView t, uint32_t n_rows_bound, FieldIndexBuffers fx, ParseResult *res) {
+    const uint32_t n_rows = min(n_rows_bound, res->n_rows);   // (the real count is on the device; the launch may only have a bound)
     __shared__ uint32_t s_tile;
     __shared__ uint32_t s_meta[FF_HALO + FF_TILE];
     __shared__ uint16_t s_up[FF_TILE];            // field rows: rows between the row and its child (at most FF_MAX_WALK)
@@ -61,6 +62,7 @@ __global__ void __launch_bounds__(FF_THREADS, 3) field_find_kernel(TapeView t, u
     __syncthreads();
     const uint32_t tile = s_tile, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t n_tiles = (n_rows + FF_TILE - 1) / FF_TILE;
+    if (tile >= n_tiles) return;                             // (the grid may cover a bound on the row count)
     const uint32_t tile0 = tile * FF_TILE;
     for (uint32_t x = threadIdx.x; x < FF_HALO + FF_TILE; x += FF_THREADS) {
         const long long r = (long long)tile0 - FF_HALO + x;

@@ -1,0 +1,815 @@
+// lines.cu -- state.New for text that is already in encoding/json's indented form: see lines.cuh.
+//
+// Reference semantics restated: encoding/json Indent("", "\t") and encodeState (what the indented
+// form looks like, line by line), the scanner's grammar (what makes a line sequence valid JSON),
+// and map keys in sorted order (state/state.go:88-90 via gabs.go:395-402).  The general pipeline
+// (parse.cu) is the authority: this pass only ever accepts a subset of what that one keeps on the
+// device, and builds the same rows for it.
+#include "lines.cuh"
+
+#include <algorithm>
+#include <atomic>
+
+#include "bulkcopy.cuh"
+
+namespace tk {
+namespace {
+
+constexpr unsigned FULL = 0xffffffffu;
+typedef unsigned long long u64;
+constexpr int LN_THREADS = 128, LN_CHUNK = 64;
+static_assert(LN_THREADS * LN_CHUNK == LN_TILE, "a tile is one 64-byte chunk per thread");
+
+__device__ __forceinline__ u64 low_bits(uint32_t k) { return k >= 64 ? ~0ull : ((1ull << k) - 1); }
+
+// bit i: byte i of the 64-byte chunk at p (16-byte aligned) is '\n'
+__device__ __forceinline__ u64 newline_mask(const uint8_t *p) {
+    const uint4 *q = reinterpret_cast<const uint4 *>(p);
+    u64 m = 0;
+#pragma unroll
+    for (int v = 0; v < 4; v++) {
+        const uint4 x = __ldg(q + v);
+        const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t t = w[k] ^ 0x0a0a0a0au;
+            const uint32_t z = ~(((t & 0x7f7f7f7fu) + 0x7f7f7f7fu) | t) & 0x80808080u;   // 0x80 in every byte that was '\n'
+            m |= (u64)(((z >> 7) * 0x01020408u) >> 24) << ((v * 4 + k) * 4);
+        }
+    }
+    return m;
+}
+
+// line ends of the chunk that starts at `chunk`: newlines, and position n itself (the end of the text)
+__device__ __forceinline__ u64 chunk_line_ends(const uint8_t *raw, u64 chunk, u64 n) {
+    if (chunk > n) return 0;
+    u64 m = newline_mask(raw + chunk);
+    if (n - chunk < 64) m = (m & low_bits((uint32_t)(n - chunk))) | (1ull << (n - chunk));
+    return m;
+}
+
+// ---- stage 0: count -------------------------------------------------------------------------
+__global__ void __launch_bounds__(LN_THREADS) lines_count_kernel(const uint8_t *__restrict__ raw, u64 n, uint32_t *__restrict__ counts,
+                                                                uint32_t *__restrict__ last_end) {
+    __shared__ uint32_t s_cnt[LN_THREADS / 32], s_last[LN_THREADS / 32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u64 chunk = (u64)blockIdx.x * LN_TILE + (u64)threadIdx.x * LN_CHUNK;
+    const u64 m = chunk_line_ends(raw, chunk, n);
+    uint32_t c = (uint32_t)__popcll(m);
+    uint32_t last = m ? (uint32_t)(chunk + 63 - __clzll((long long)m)) + 1u : 0u;   // position + 1; 0: none
+#pragma unroll
+    for (int d = 16; d; d >>= 1) { c += __shfl_xor_sync(FULL, c, d); last = max(last, __shfl_xor_sync(FULL, last, d)); }
+    if (lane == 0) { s_cnt[warp] = c; s_last[warp] = last; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t tc = 0, tl = 0;
+        for (int w = 0; w < LN_THREADS / 32; w++) { tc += s_cnt[w]; tl = max(tl, s_last[w]); }
+        counts[blockIdx.x] = tc;
+        last_end[blockIdx.x] = tl;
+    }
+}
+
+// in place: counts[t] -> line ends before tile t; the total is the number of lines
+__global__ void __launch_bounds__(1024) lines_prefix_kernel(uint32_t *counts, uint32_t n_tiles, ParseResult *res) {
+    __shared__ uint32_t s_w[32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t run = 0;
+    for (uint32_t base = 0; base < n_tiles; base += 1024 * 4) {
+        const uint32_t first = base + threadIdx.x * 4;
+        uint32_t v[4], sum = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) { v[j] = first + j < n_tiles ? counts[first + j] : 0u; sum += v[j]; }
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, incl, o);
+            if (lane >= (uint32_t)o) incl += y;
+        }
+        __syncthreads();
+        if (lane == 31) s_w[warp] = incl;
+        __syncthreads();
+        uint32_t w = s_w[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, w, o);
+            if (lane >= (uint32_t)o) w += y;
+        }
+        const uint32_t total = __shfl_sync(FULL, w, 31);
+        uint32_t before = __shfl_sync(FULL, w, warp ? warp - 1 : 0);
+        if (warp == 0) before = 0;
+        uint32_t x = run + before + incl - sum;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (first + j < n_tiles) counts[first + j] = x;
+            x += v[j];
+        }
+        run += total;
+    }
+    if (threadIdx.x == 0) res->n_rows = run;
+}
+
+// ---- stage 1: one row per line --------------------------------------------------------------
+
+// ---- reading the text eight bytes at a time ----------------------------------------------------
+constexpr u64 ONES = 0x0101010101010101ull, HIGHS = 0x8080808080808080ull;
+// The text as the line parser reads it: a window of it sits in shared memory (positions lo .. hi,
+// brought in by one bulk copy), the rest is fetched from global memory.  Thirty-two lanes reading
+// thirty-two different lines are thirty-two different sectors to the L1 cache -- one tag look-up
+// each -- but only a few bank conflicts to shared memory.
+struct Text {
+    const uint8_t *win;     // shared memory; win[0] is position lo (lo a multiple of 16)
+    u64 lo, hi;
+    const uint8_t *raw;     // global memory, readable 64 bytes past the end of the text
+    // the 8 bytes at position p (any alignment), first byte lowest
+    __device__ __forceinline__ u64 load8(u64 p) const {
+        const u64 a = p & ~7ull;
+        u64 x0, x1;
+        if (a >= lo && a + 16 <= hi) {
+            const u64 *w = reinterpret_cast<const u64 *>(win + (a - lo));
+            x0 = w[0]; x1 = w[1];
+        } else {
+            const u64 *w = reinterpret_cast<const u64 *>(raw + a);
+            x0 = __ldg(w); x1 = __ldg(w + 1);
+        }
+        const uint32_t sh = (uint32_t)(p & 7u) * 8u;
+        return sh ? (x0 >> sh) | (x1 << (64u - sh)) : x0;
+    }
+    __device__ __forceinline__ uint32_t byte(u64 p) const { return p >= lo && p < hi ? (uint32_t)win[p - lo] : (uint32_t)__ldg(raw + p); }
+    __device__ __forceinline__ uint32_t tabs(u64 p) const;                 // tabs at p: 0 .. 8, or 9 for "more than 8"
+    __device__ __forceinline__ u64 string_end(u64 p, u64 end) const;      // see below
+};
+
+// 0x80 in bytes of x that equal c -- and possibly in bytes ABOVE such a byte (a borrow), never below
+// the lowest one: the first flagged byte is always a true one, which is all the callers look at
+__device__ __forceinline__ u64 eq_bytes(u64 x, uint32_t c) {
+    const u64 v = x ^ (ONES * c);
+    return (v - ONES) & ~v & HIGHS;
+}
+// likewise for bytes that may not stand for themselves in a string of the indented form: below 0x20,
+// 0x80 and above, and \ < > &   (the quote is looked for separately)
+__device__ __forceinline__ u64 bad_bytes(u64 x) {
+    return (x & HIGHS) | ((x - ONES * 0x20u) & ~x & HIGHS) | eq_bytes(x, '\\') | eq_bytes(x, '<') | eq_bytes(x, '>') | eq_bytes(x, '&');
+}
+// from p (the byte after an opening quote) to the closing quote, which must come before `end`, every
+// byte on the way one that stands for itself: its position, or 0
+__device__ __forceinline__ u64 Text::string_end(u64 p, u64 end) const {
+    const Text &raw = *this;
+    for (; p < end; p += 8) {
+        const u64 x = raw.load8(p);
+        u64 q = eq_bytes(x, '"'), bad = bad_bytes(x);
+        if (end - p < 8) { const u64 keep = (1ull << ((end - p) * 8)) - 1; q &= keep; bad &= keep; }
+        if (q | bad) {
+            const uint32_t iq = q ? (uint32_t)__ffsll((long long)q) : 65u, ib = bad ? (uint32_t)__ffsll((long long)bad) : 65u;
+            return iq < ib ? p + ((iq - 1) >> 3) : 0;
+        }
+    }
+    return 0;
+}
+// true / false / null, or an integer floatEncoder prints back unchanged (at most 15 digits, no leading zero)
+template <class Reader>
+__device__ __forceinline__ bool canonical_scalar(const Reader &raw, u64 a, u64 b) {
+    const uint32_t len = (uint32_t)(b - a);
+    if (len == 0 || len > 16) return false;
+    const uint32_t c0 = raw.byte(a);
+    if (c0 == 't') return len == 4 && raw.byte(a + 1) == 'r' && raw.byte(a + 2) == 'u' && raw.byte(a + 3) == 'e';
+    if (c0 == 'n') return len == 4 && raw.byte(a + 1) == 'u' && raw.byte(a + 2) == 'l' && raw.byte(a + 3) == 'l';
+    if (c0 == 'f') return len == 5 && raw.byte(a + 1) == 'a' && raw.byte(a + 2) == 'l' && raw.byte(a + 3) == 's' && raw.byte(a + 4) == 'e';
+    u64 p = a;
+    if (c0 == '-') p++;
+    const uint32_t digits = (uint32_t)(b - p);
+    if (digits == 0 || digits > 15) return false;
+    if (raw.byte(p) == '0' && digits > 1) return false;
+    for (; p < b; p++) { const uint32_t c = raw.byte(p); if (c < '0' || c > '9') return false; }
+    return true;
+}
+// the same reads straight from global memory (the structure pass compares a few keys far apart)
+struct GlobalText {
+    const uint8_t *raw;
+    __device__ __forceinline__ u64 load8(u64 p) const {
+        const u64 *w = reinterpret_cast<const u64 *>(raw + (p & ~7ull));
+        const u64 x0 = __ldg(w), x1 = __ldg(w + 1);
+        const uint32_t sh = (uint32_t)(p & 7u) * 8u;
+        return sh ? (x0 >> sh) | (x1 << (64u - sh)) : x0;
+    }
+};
+// bytes of x reversed, so that comparing numbers compares byte strings
+__device__ __forceinline__ u64 big_endian(u64 x) {
+    return ((u64)__byte_perm((uint32_t)x, 0, 0x0123) << 32) | __byte_perm((uint32_t)(x >> 32), 0, 0x0123);
+}
+// strictly ascending, bytewise (the shorter first on a tie)?
+template <class T>
+__device__ __forceinline__ bool key_less(const T &raw, u64 a, uint32_t al, u64 b, uint32_t bl) {
+    const uint32_t m = al < bl ? al : bl;
+    for (uint32_t i = 0; i < m; i += 8) {
+        u64 x = big_endian(raw.load8(a + i)), y = big_endian(raw.load8(b + i));
+        if (m - i < 8) { const u64 keep = ~0ull << ((8 - (m - i)) * 8); x &= keep; y &= keep; }
+        if (x != y) return x < y;
+    }
+    return al < bl;
+}
+// tabs at raw + p: 0 .. 8, or 9 for "more than 8"
+__device__ __forceinline__ uint32_t Text::tabs(u64 p) const {
+    const Text &raw = *this;
+    const u64 t = raw.load8(p) ^ (ONES * 0x09u);
+    const u64 nz = (((t & ~HIGHS) + ~HIGHS) | t) & HIGHS;     // 0x80 in every byte that is not a tab (exact)
+    if (nz) return ((uint32_t)__ffsll((long long)nz) - 1) >> 3;
+    return raw.byte(p + 8) == '\t' ? 9u : 8u;
+}
+
+// the row written, with what the module index and the verdict want to know about it
+template <class Reader>
+__device__ __forceinline__ void finish_row(const Reader &raw, uint32_t r, uint32_t d, uint32_t meta, uint32_t koff, uint32_t klen, uint32_t voff,
+                                           uint32_t vlen, RowBuffers rb, ParseResult *res) {
+    const uint32_t kind = meta & 15u;
+    if (d == 3 && kind == ROW_STR && (meta & META_HAS_KEY) && (klen == 4 || klen == 8)) {   // for the module index (index.cu)
+        const u64 k8 = raw.load8(koff);
+        if (klen == 4 && (uint32_t)k8 == 0x656d616eu) meta |= META_KEY_IS_NAME;                           // "name"
+        else if (klen == 8 && k8 == 0x656d616e74736f68ull) meta |= META_KEY_IS_HOSTNAME;                  // "hostname"
+    }
+    rb.meta[r] = meta; rb.koff[r] = koff; rb.klen[r] = klen; rb.voff[r] = voff; rb.vlen[r] = vlen;
+    if (r == 0) res->root_kind = kind;
+    if (d == 1 && (meta & META_HAS_KEY) && klen == 6 && (raw.load8(koff) & 0xffffffffffffull) == 0x656c75646f6dull) {   // "module"
+        res->module_row = r + 1;
+        res->module_kind = kind;
+    }
+}
+
+// The line raw[s, e) becomes row r.  Returns false for anything that is not the indented form.
+template <class Reader>
+__device__ __forceinline__ bool line_to_row(const Reader &raw, u64 s, u64 e, u64 n, uint32_t r, RowBuffers rb, ParseResult *res) {
+    const uint32_t d = raw.tabs(s);
+    u64 p = s + d;
+    if (d > LINES_MAX_DEPTH + 1 || p >= e) return false;
+    if (r == 0 && d != 0) return false;
+    uint32_t meta = 0, koff = 0, klen = 0, voff = 0, vlen = 0;
+    uint32_t c = raw.byte(p);
+    u64 after;   // the byte after the value
+    bool value_done = false;
+    if (c == '"') {
+        const u64 q = raw.string_end(p + 1, e);
+        if (!q) return false;
+        if (q + 1 < e && raw.byte(q + 1) == ':') {
+            // "key": value
+            if (q + 2 >= e || raw.byte(q + 2) != ' ') return false;
+            meta |= META_HAS_KEY | META_KEY_PLAIN;
+            koff = (uint32_t)(p + 1);
+            klen = (uint32_t)(q - p - 1);
+            p = q + 3;
+            if (p >= e) return false;
+            c = raw.byte(p);
+        } else {
+            meta |= ROW_STR | META_VAL_PLAIN;
+            voff = (uint32_t)(p + 1);
+            vlen = (uint32_t)(q - p - 1);
+            after = q + 1;
+            value_done = true;
+        }
+    }
+    if (!value_done) {
+        if (c == '"') {
+            const u64 q = raw.string_end(p + 1, e);
+            if (!q) return false;
+            meta |= ROW_STR | META_VAL_PLAIN;
+            voff = (uint32_t)(p + 1);
+            vlen = (uint32_t)(q - p - 1);
+            after = q + 1;
+        } else if (c == '{' || c == '[') {
+            const uint32_t closer = c == '{' ? '}' : ']';
+            vlen = (uint32_t)p;   // container rows keep the text position of their bracket (TapeView::text_len)
+            if (p + 1 < e && raw.byte(p + 1) == closer) { meta |= c == '{' ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR; after = p + 2; }
+            else { meta |= c == '{' ? ROW_OPEN_OBJ : ROW_OPEN_ARR; after = p + 1; }
+        } else if (c == '}' || c == ']') {
+            if (meta & META_HAS_KEY) return false;
+            meta |= c == '}' ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR;
+            vlen = (uint32_t)p;
+            after = p + 1;
+        } else {
+            u64 q = p;
+            while (q < e && raw.byte(q) != ',') q++;
+            if (!canonical_scalar(raw, p, q)) return false;
+            meta |= ROW_RAW;
+            voff = (uint32_t)p;
+            vlen = (uint32_t)(q - p);
+            after = q;
+        }
+    }
+    const uint32_t kind = meta & 15u;
+    const bool is_open = kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR;
+    bool comma = false;
+    if (after < e && raw.byte(after) == ',') { comma = true; after++; }
+    if (after != e || (comma && is_open)) return false;
+    if (comma) meta |= META_COMMA;
+    meta |= d << META_DEPTH_SHIFT;
+
+    // ---- this line against the next one: indentation, comma, key order
+    if (e >= n) {
+        if (d != 0 || comma || is_open) return false;
+        meta |= META_LAST;
+    } else {
+        const uint32_t dn = raw.tabs(e + 1);
+        const u64 q = e + 1 + dn;
+        if (dn > LINES_MAX_DEPTH + 1 || q >= n) return false;   // (too deep, or an empty last line)
+        const uint32_t cn = raw.byte(q);
+        const bool next_closes = cn == '}' || cn == ']';
+        if (is_open) {
+            if (dn != d + 1 || next_closes) return false;   // ("{" then "}" is written "{}")
+        } else if (next_closes) {
+            if (d == 0 || dn != d - 1 || comma) return false;
+        } else {
+            if (dn != d || !comma) return false;
+            if (meta & META_HAS_KEY) {
+                // the next member of the same object: its key must sort strictly after this one
+                if (cn != '"') return false;
+                const u64 qe = raw.string_end(q + 1, n);    // (a newline on the way is not a byte that stands for itself)
+                if (!qe || !key_less(raw, koff, klen, q + 1, (uint32_t)(qe - q - 1))) return false;
+            }
+        }
+    }
+    finish_row(raw, r, d, meta, koff, klen, voff, vlen, rb, res);
+    return true;
+}
+
+// ---- the same reads answered from byte-class masks ------------------------------------------------
+// A tile's bytes are classified once, 64 bytes per thread and every thread doing the same thing
+// (positioned table look-ups, as in the general scan): one bit per byte and class -- line feed,
+// tab, quote, "stop" (a byte that may not stand for itself in a string: control bytes, 0x80 and
+// above, \ < > &).  A line then finds its tabs, its quotes and whether anything in it stops a
+// string by bit arithmetic on those masks instead of walking its bytes, which is what made the
+// byte-wise parser thirty times slower: lanes walking different lines run different code.
+constexpr bool ln_plain(uint32_t c) { return c >= 0x20 && c < 0x80 && c != '"' && c != '\\' && c != '<' && c != '>' && c != '&'; }
+struct LineLut { uint32_t v[4 * 256]; };
+constexpr LineLut make_line_lut() {
+    LineLut t{};
+    for (uint32_t j = 0; j < 4; j++)
+        for (uint32_t c = 0; c < 256; c++)
+            t.v[j * 256 + c] = ((c == '\n' ? 1u : 0u) << j) | ((c == '\t' ? 1u : 0u) << (8 + j)) | ((c == '"' ? 1u : 0u) << (16 + j)) |
+                               ((!(ln_plain(c) || c == '"') ? 1u : 0u) << (24 + j));   // stop: includes line feed and tab
+    return t;
+}
+__device__ const LineLut g_line_lut = make_line_lut();
+
+__device__ __forceinline__ uint32_t lut_word(const uint32_t *lut, uint32_t x) {
+    const char *b = reinterpret_cast<const char *>(lut);
+    const uint32_t i0 = (x * 4u) & 0x3fcu, i1 = __umulhi(x, 1u << 26) & 0x3fcu, i2 = __umulhi(x, 1u << 18) & 0x3fcu, i3 = __umulhi(x, 1u << 10) & 0x3fcu;
+    return *reinterpret_cast<const uint32_t *>(b + i0) | *reinterpret_cast<const uint32_t *>(b + 1024 + i1) |
+           *reinterpret_cast<const uint32_t *>(b + 2048 + i2) | *reinterpret_cast<const uint32_t *>(b + 3072 + i3);
+}
+struct LineMasks { u64 NL, TAB, Q, STOP; };
+__device__ __forceinline__ LineMasks classify_chunk(const uint32_t *s_lut, const uint4 *chunk) {
+    uint32_t m[4][2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        uint32_t y[4];
+#pragma unroll
+        for (int v = 0; v < 2; v++) {
+            const uint4 q = chunk[h * 2 + v];
+            y[v * 2 + 0] = lut_word(s_lut, q.x) | (lut_word(s_lut, q.y) << 4);
+            y[v * 2 + 1] = lut_word(s_lut, q.z) | (lut_word(s_lut, q.w) << 4);
+        }
+        // 4 x 4 byte transpose: byte c of y[r] (class c of text bytes 8r .. 8r+7) -> byte r of class word c
+        const uint32_t t01l = __byte_perm(y[0], y[1], 0x5140), t23l = __byte_perm(y[2], y[3], 0x5140);
+        const uint32_t t01h = __byte_perm(y[0], y[1], 0x7362), t23h = __byte_perm(y[2], y[3], 0x7362);
+        m[0][h] = __byte_perm(t01l, t23l, 0x5410);
+        m[1][h] = __byte_perm(t01l, t23l, 0x7632);
+        m[2][h] = __byte_perm(t01h, t23h, 0x5410);
+        m[3][h] = __byte_perm(t01h, t23h, 0x7632);
+    }
+    LineMasks r;
+    r.NL = (u64)m[0][0] | ((u64)m[0][1] << 32);
+    r.TAB = (u64)m[1][0] | ((u64)m[1][1] << 32);
+    r.Q = (u64)m[2][0] | ((u64)m[2][1] << 32);
+    r.STOP = (u64)m[3][0] | ((u64)m[3][1] << 32);
+    return r;
+}
+
+constexpr int WIN_BEFORE = 512, WIN_AFTER = 256, WIN_BYTES = WIN_BEFORE + LN_TILE + WIN_AFTER, WIN_CHUNKS = WIN_BYTES / 64;
+constexpr int TILE_LINES = 2048;   // line ends of a tile listed in shared memory; a tile with more (lines under 4 bytes) is declined
+
+struct MaskText {
+    const uint8_t *win;               // the text window in shared memory; win[0] is position lo
+    u64 lo, hi;
+    const uint8_t *raw;
+    const u64 *tabm, *qm, *stopm;     // one word per 64 bytes of the window [w0, w1); w0 may lie before the text (tile 0)
+    long long w0, w1;
+    mutable bool overrun;             // a question reached past the window: the caller asks the byte-wise reader instead
+    __device__ __forceinline__ u64 load8(u64 p) const {
+        const u64 a = p & ~7ull;
+        u64 x0, x1;
+        if (a >= lo && a + 16 <= hi) { const u64 *w = reinterpret_cast<const u64 *>(win + (a - lo)); x0 = w[0]; x1 = w[1]; }
+        else { const u64 *w = reinterpret_cast<const u64 *>(raw + a); x0 = __ldg(w); x1 = __ldg(w + 1); }
+        const uint32_t sh = (uint32_t)(p & 7u) * 8u;
+        return sh ? (x0 >> sh) | (x1 << (64u - sh)) : x0;
+    }
+    __device__ __forceinline__ uint32_t byte(u64 p) const { return p >= lo && p < hi ? (uint32_t)win[p - lo] : (uint32_t)__ldg(raw + p); }
+    // 64 mask bits from position p on (p inside the window)
+    __device__ __forceinline__ u64 bits(const u64 *m, u64 p) const {
+        const uint32_t b = (uint32_t)((long long)p - w0), i = b >> 6, sh = b & 63u;
+        const u64 x0 = m[i], x1 = i + 1 < (uint32_t)WIN_CHUNKS ? m[i + 1] : 0ull;
+        return sh ? (x0 >> sh) | (x1 << (64u - sh)) : x0;
+    }
+    __device__ __forceinline__ uint32_t tabs(u64 p) const {
+        if ((long long)p + 64 > w1) { overrun = true; return 9; }
+        const u64 t = bits(tabm, p);
+        return min(t == ~0ull ? 64u : (uint32_t)__ffsll((long long)~t) - 1u, 9u);
+    }
+    __device__ __forceinline__ u64 string_end(u64 p, u64 end) const {
+        const u64 lim = (long long)end < w1 ? end : (u64)w1;
+        for (u64 a = p; a < lim; a += 64) {
+            u64 q = bits(qm, a), st = bits(stopm, a);
+            if (lim - a < 64) { const u64 keep = (1ull << (lim - a)) - 1; q &= keep; st &= keep; }
+            if (q | st) {
+                const uint32_t iq = q ? (uint32_t)__ffsll((long long)q) : 65u, is = st ? (uint32_t)__ffsll((long long)st) : 65u;
+                return iq < is ? a + iq - 1 : 0;
+            }
+        }
+        if ((long long)end > w1) overrun = true;
+        return 0;
+    }
+};
+
+// A line of at most 120 bytes that is not the last one, decided by arithmetic on the class masks: how many
+// quotes and where, nothing between the indentation and the end that stops a string, the few bytes
+// that must be exactly ':' ' ' ',' or a bracket read by position.  1: accepted, row written; 0: not
+// the indented form; 2: not for this function (too long, at the edge of the window, the last line) --
+// line_to_row decides.  Same rules as line_to_row, same rows.
+__device__ __forceinline__ u64 shift192(u64 a, u64 b, u64 c, uint32_t by) {   // bits [by, by + 64) of the 192-bit number c:b:a, by < 128
+    if (by >= 64) { a = b; b = c; by -= 64; }
+    return by ? (a >> by) | (b << (64u - by)) : a;
+}
+__device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n, uint32_t r, RowBuffers rb, ParseResult *res) {
+    const uint32_t L = (uint32_t)(e - s);
+    if (L == 0 || L > 120 || (long long)s + 256 > t.w1 || e >= n) return 2;   // (120: the look at the next line stays inside 192 mask bits)
+    const u64 T0 = t.bits(t.tabm, s), T1 = t.bits(t.tabm, s + 64), T2 = t.bits(t.tabm, s + 128);
+    const uint32_t d = T0 == ~0ull ? 64u : (uint32_t)__ffsll((long long)~T0) - 1u;
+    if (d > LINES_MAX_DEPTH + 1 || d >= L || (r == 0 && d != 0)) return 0;
+    const u64 Q0 = t.bits(t.qm, s), Q1 = t.bits(t.qm, s + 64), Q2 = t.bits(t.qm, s + 128);
+    const u64 S0 = t.bits(t.stopm, s), S1 = t.bits(t.stopm, s + 64);
+    const u64 in0 = low_bits(L), in1 = L > 64 ? low_bits(L - 64) : 0ull;       // the line's own bits
+    if ((S0 & in0 & ~low_bits(d)) | (S1 & in1)) return 0;                          // something that cannot stand for itself
+    u64 q0 = Q0 & in0, q1 = Q1 & in1;
+    const uint32_t nq = (uint32_t)__popcll(q0) + (uint32_t)__popcll(q1);
+    if (nq != 0 && nq != 2 && nq != 4) return 0;
+    uint32_t qp[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        if ((uint32_t)i < nq) {
+            if (q0) { qp[i] = (uint32_t)__ffsll((long long)q0) - 1u; q0 &= q0 - 1; }
+            else { qp[i] = 64u + (uint32_t)__ffsll((long long)q1) - 1u; q1 &= q1 - 1; }
+        }
+    }
+    uint32_t meta = 0, koff = 0, klen = 0, voff = 0, vlen = 0, v = d, used = 0;   // v: where the value starts; used: quotes accounted for
+    if (nq >= 2 && qp[0] == d && qp[1] + 1 < L && t.byte(s + qp[1] + 1) == ':') {
+        if (qp[1] + 2 >= L || t.byte(s + qp[1] + 2) != ' ') return 0;
+        meta |= META_HAS_KEY | META_KEY_PLAIN;
+        koff = (uint32_t)s + d + 1;
+        klen = qp[1] - d - 1;
+        v = qp[1] + 3;
+        used = 2;
+        if (v >= L) return 0;
+    }
+    const uint32_t c = t.byte(s + v);
+    uint32_t after;
+    if (c == '"') {
+        if (nq != used + 2 || qp[used] != v) return 0;
+        meta |= ROW_STR | META_VAL_PLAIN;
+        voff = (uint32_t)s + v + 1;
+        vlen = qp[used + 1] - v - 1;
+        after = qp[used + 1] + 1;
+    } else {
+        if (nq != used) return 0;                   // a quote where no string can be
+        if (c == '{' || c == '[') {
+            vlen = (uint32_t)s + v;                 // container rows keep the text position of their bracket
+            if (v + 1 < L && t.byte(s + v + 1) == (c == '{' ? '}' : ']')) { meta |= c == '{' ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR; after = v + 2; }
+            else { meta |= c == '{' ? ROW_OPEN_OBJ : ROW_OPEN_ARR; after = v + 1; }
+        } else if (c == '}' || c == ']') {
+            if (meta & META_HAS_KEY) return 0;
+            meta |= c == '}' ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR;
+            vlen = (uint32_t)s + v;
+            after = v + 1;
+        } else {
+            after = t.byte(e - 1) == ',' ? L - 1 : L;
+            if (after <= v || !canonical_scalar(t, s + v, s + after)) return 0;
+            meta |= ROW_RAW;
+            voff = (uint32_t)s + v;
+            vlen = after - v;
+        }
+    }
+    const uint32_t kind = meta & 15u;
+    const bool is_open = kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR;
+    bool comma = false;
+    if (after < L && t.byte(s + after) == ',') { comma = true; after++; }
+    if (after != L || (comma && is_open)) return 0;
+    if (comma) meta |= META_COMMA;
+    meta |= d << META_DEPTH_SHIFT;
+    // ---- this line against the next one: indentation, comma, key order
+    const uint32_t nb = L + 1;                                             // where the next line starts, from s
+    const u64 tn = shift192(T0, T1, T2, nb);
+    const uint32_t dn = tn == ~0ull ? 64u : (uint32_t)__ffsll((long long)~tn) - 1u;
+    const u64 q = e + 1 + dn;
+    if (dn > LINES_MAX_DEPTH + 1 || q >= n) return 0;
+    const uint32_t cn = t.byte(q);
+    const bool next_closes = cn == '}' || cn == ']';
+    if (is_open) {
+        if (dn != d + 1 || next_closes) return 0;
+    } else if (next_closes) {
+        if (d == 0 || dn != d - 1 || comma) return 0;
+    } else {
+        if (dn != d || !comma) return 0;
+        if (meta & META_HAS_KEY) {
+            if (cn != '"') return 0;
+            // the next key ends at the next quote (whether that line is well formed is its own thread's business)
+            const uint32_t from = nb + dn + 1;                            // first byte of the next key, from s
+            if (from >= 128) return 2;
+            const u64 qn = shift192(Q0, Q1, Q2, from);
+            if (!qn) return 2;
+            const uint32_t nl = (uint32_t)__ffsll((long long)qn) - 1u;
+            if (!key_less(t, koff, klen, s + from, nl)) return 0;
+        }
+    }
+    finish_row(t, r, d, meta, koff, klen, voff, vlen, rb, res);
+    return 1;
+}
+
+__global__ void __launch_bounds__(LN_THREADS) lines_rows_kernel(const uint8_t *__restrict__ raw, u64 n, u64 readable_end, uint32_t n_tiles,
+                                                               const uint32_t *__restrict__ first_line, const uint32_t *__restrict__ last_end,
+                                                               RowBuffers rb, uint32_t row_cap, ParseResult *res) {
+    __shared__ uint32_t s_lut[4 * 256];
+    __shared__ __align__(16) uint8_t s_text[WIN_BYTES];
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ u64 s_tab[WIN_CHUNKS], s_q[WIN_CHUNKS], s_stop[WIN_CHUNKS];
+    __shared__ uint16_t s_end[TILE_LINES];
+    __shared__ uint32_t s_warp[LN_THREADS / 32];
+    __shared__ u64 s_prev_end;      // position + 1 of the last line end before the tile
+    if (res->n_rows > row_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) res->fast_reject = 1; return; }
+    for (int i = threadIdx.x; i < 4 * 256; i += LN_THREADS) s_lut[i] = g_line_lut.v[i];
+    if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t parity = 0;
+    bool ok = true;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const u64 tile0 = (u64)tile * LN_TILE;
+        // the tile, the end of the line that runs into it and the start of the one that runs out of it: one bulk copy
+        const u64 lo = tile0 >= WIN_BEFORE ? tile0 - WIN_BEFORE : 0, hi = min(tile0 + LN_TILE + WIN_AFTER, readable_end);
+        const long long w0 = (long long)tile0 - WIN_BEFORE;
+        if (threadIdx.x == 0) {
+            bulk_load(s_text, raw + lo, (uint32_t)(hi - lo), &s_bar);
+            int tt = (int)tile - 1;
+            while (tt >= 0 && last_end[tt] == 0) tt--;
+            s_prev_end = tt >= 0 ? (u64)last_end[tt] : 0;
+        }
+        mbar_wait(&s_bar, parity);
+        parity ^= 1u;
+        // classes of every 64 bytes of the window: a chunk per thread, the few chunks of the margins by the first threads
+        u64 my_ends = 0;
+        for (int j = threadIdx.x; j < WIN_CHUNKS; j += LN_THREADS) {
+            const int wc = j < LN_THREADS ? j + WIN_BEFORE / 64 : (j - LN_THREADS < WIN_BEFORE / 64 ? j - LN_THREADS : j);   // own chunk first
+            const long long at = w0 + (long long)wc * 64;
+            LineMasks m = {0, 0, 0, 0};
+            if (at >= 0 && (u64)at + 64 <= hi) {
+                m = classify_chunk(s_lut, reinterpret_cast<const uint4 *>(s_text + ((u64)at - lo)));
+                if ((u64)at + 64 > n) {   // past the end of the text nothing counts; the end itself ends the last line
+                    const u64 keep = (u64)at >= n ? 0ull : low_bits((uint32_t)(n - (u64)at));
+                    m.NL &= keep; m.TAB &= keep; m.Q &= keep; m.STOP &= keep;
+                    if ((u64)at <= n) { m.NL |= 1ull << (n - (u64)at); m.STOP |= 1ull << (n - (u64)at); }
+                }
+            }
+            s_tab[wc] = m.TAB; s_q[wc] = m.Q; s_stop[wc] = m.STOP;
+            if (j < LN_THREADS) my_ends = m.NL;
+        }
+        // the tile's line ends listed in order
+        const uint32_t c = (uint32_t)__popcll(my_ends);
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, incl, o);
+            if (lane >= (uint32_t)o) incl += y;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        uint32_t before = incl - c, total = 0;
+        for (uint32_t w = 0; w < LN_THREADS / 32; w++) { if (w < warp) before += s_warp[w]; total += s_warp[w]; }
+        {
+            uint32_t k = before;
+            for (u64 left = my_ends; left; left &= left - 1, k++)
+                if (k < TILE_LINES) s_end[k] = (uint16_t)(threadIdx.x * LN_CHUNK + (uint32_t)__ffsll((long long)left) - 1);
+        }
+        __syncthreads();
+        if (total > TILE_LINES) { ok = false; total = 0; }
+        // a line per thread, in order
+        const uint32_t row0 = first_line[tile];
+        for (uint32_t k = threadIdx.x; k < total; k += LN_THREADS) {
+            const u64 e = tile0 + s_end[k], s = k ? tile0 + s_end[k - 1] + 1 : s_prev_end;
+            bool done = false;
+            if ((long long)s >= w0 && s >= lo) {
+                const MaskText mt{s_text, lo, hi, raw, s_tab, s_q, s_stop, w0, w0 + WIN_BYTES, false};
+                const int fast = line_fast(mt, s, e, n, row0 + k, rb, res);
+                if (fast != 2) { ok = ok && fast == 1; done = true; }
+                else {
+                    const bool good = line_to_row(mt, s, e, n, row0 + k, rb, res);
+                    if (!mt.overrun) { ok = ok && good; done = true; }
+                }
+            }
+            if (!done) {   // a line that starts before the window, or looks past it: byte by byte
+                const Text text{s_text, lo, hi, raw};
+                ok = ok && line_to_row(text, s, e, n, row0 + k, rb, res);
+            }
+        }
+        __syncthreads();   // (the window and the lists are rewritten by the next tile)
+    }
+    if (!ok) res->fast_reject = 1;
+}
+
+// ---- stage 2: closers and openers, containers -----------------------------------------------
+// The state that travels along the rows: for every depth k <= LINES_MAX_DEPTH the last opening row
+// seen at that depth, as (row + 1) << 1 | is-an-object (0: none yet).  Later rows have larger
+// numbers, so "the last one" is a maximum: the state of a stretch of rows is combined by max.
+constexpr int ST_DEPTHS = LINES_MAX_DEPTH + 1;
+struct OpenState { uint32_t v[ST_DEPTHS]; };
+__device__ __forceinline__ void state_note(OpenState &st, uint32_t meta, uint32_t r) {
+    const uint32_t kind = meta & 15u, d = meta >> META_DEPTH_SHIFT;
+    if (kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR) {
+        const uint32_t enc = ((r + 1) << 1) | (kind == ROW_OPEN_OBJ ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < ST_DEPTHS; k++)
+            if (d == (uint32_t)k) st.v[k] = enc;
+    }
+}
+__device__ __forceinline__ uint32_t state_at(const OpenState &st, uint32_t d) {
+    uint32_t x = 0;
+#pragma unroll
+    for (int k = 0; k < ST_DEPTHS; k++)
+        if (d == (uint32_t)k) x = st.v[k];
+    return x;
+}
+constexpr int SR_THREADS = 256, SR_ITEMS = LN_ROWS_PER_BLOCK / SR_THREADS;
+
+__global__ void __launch_bounds__(SR_THREADS) lines_open_agg_kernel(const uint32_t *__restrict__ meta, uint32_t *__restrict__ agg, ParseResult *res) {
+    __shared__ uint32_t s_w[SR_THREADS / 32][ST_DEPTHS];
+    const uint32_t n_rows = res->n_rows, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (res->fast_reject || blockIdx.x * LN_ROWS_PER_BLOCK >= n_rows) return;
+    const uint32_t base = blockIdx.x * LN_ROWS_PER_BLOCK + threadIdx.x * SR_ITEMS;
+    OpenState st = {};
+#pragma unroll
+    for (int j = 0; j < SR_ITEMS; j++)
+        if (base + j < n_rows) state_note(st, __ldg(meta + base + j), base + j);
+#pragma unroll
+    for (int k = 0; k < ST_DEPTHS; k++) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) st.v[k] = max(st.v[k], __shfl_xor_sync(FULL, st.v[k], o));
+        if (lane == 0) s_w[warp][k] = st.v[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < ST_DEPTHS) {
+        uint32_t x = 0;
+        for (int w = 0; w < SR_THREADS / 32; w++) x = max(x, s_w[w][threadIdx.x]);
+        agg[blockIdx.x * ST_DEPTHS + threadIdx.x] = x;
+    }
+}
+
+// in place: agg[b][k] -> the last opening row at depth k in the blocks before b (a warp per depth)
+__global__ void __launch_bounds__(32 * ST_DEPTHS) lines_open_prefix_kernel(uint32_t *agg, ParseResult *res) {
+    const uint32_t n_blocks = (res->n_rows + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK;
+    if (res->fast_reject) return;
+    const uint32_t lane = threadIdx.x & 31, k = threadIdx.x >> 5;
+    uint32_t run = 0;
+    for (uint32_t base = 0; base < n_blocks; base += 32) {
+        const uint32_t b = base + lane;
+        const uint32_t mine = b < n_blocks ? agg[b * ST_DEPTHS + k] : 0u;
+        uint32_t incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, incl, o);
+            if (lane >= (uint32_t)o) incl = max(incl, y);
+        }
+        uint32_t excl = __shfl_up_sync(FULL, incl, 1);
+        if (lane == 0) excl = 0;
+        if (b < n_blocks) agg[b * ST_DEPTHS + k] = max(run, excl);
+        run = max(run, __shfl_sync(FULL, incl, 31));
+    }
+}
+
+__global__ void __launch_bounds__(SR_THREADS) lines_resolve_kernel(const uint8_t *__restrict__ raw, RowBuffers rb, const uint32_t *__restrict__ prefix,
+                                                                  ParseResult *res) {
+    __shared__ uint32_t s_w[SR_THREADS / 32][ST_DEPTHS];
+    const uint32_t n_rows = res->n_rows, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (res->fast_reject || blockIdx.x * LN_ROWS_PER_BLOCK >= n_rows) return;
+    const uint32_t base = blockIdx.x * LN_ROWS_PER_BLOCK + threadIdx.x * SR_ITEMS;
+    uint32_t meta[SR_ITEMS];
+    OpenState mine = {};
+#pragma unroll
+    for (int j = 0; j < SR_ITEMS; j++) {
+        meta[j] = base + j < n_rows ? __ldg(rb.meta + base + j) : 0xffffffffu;
+        if (base + j < n_rows) state_note(mine, meta[j], base + j);
+    }
+    // the state before this thread's first row: blocks before (prefix), warps before, lanes before
+    OpenState st;
+#pragma unroll
+    for (int k = 0; k < ST_DEPTHS; k++) {
+        uint32_t incl = mine.v[k];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, incl, o);
+            if (lane >= (uint32_t)o) incl = max(incl, y);
+        }
+        if (lane == 31) s_w[warp][k] = incl;
+        uint32_t excl = __shfl_up_sync(FULL, incl, 1);
+        if (lane == 0) excl = 0;
+        st.v[k] = excl;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < ST_DEPTHS; k++) {
+        uint32_t x = __ldg(prefix + blockIdx.x * ST_DEPTHS + k);
+        for (uint32_t w = 0; w < warp; w++) x = max(x, s_w[w][k]);
+        st.v[k] = max(st.v[k], x);
+    }
+    const uint32_t module_row = res->module_row;   // 1 + row, 0: none (stage 1 has finished)
+    bool ok = true;
+    uint32_t prev_meta = base > 0 && base < n_rows ? __ldg(rb.meta + base - 1) : 0xffffffffu;
+#pragma unroll
+    for (int j = 0; j < SR_ITEMS; j++) {
+        const uint32_t r = base + j;
+        if (r >= n_rows) break;
+        const uint32_t m = meta[j], kind = m & 15u, d = m >> META_DEPTH_SHIFT;
+        if (kind == ROW_CLOSE_OBJ || kind == ROW_CLOSE_ARR) {
+            // the container it closes opened at the same depth, and was of the same kind
+            const uint32_t o = d <= LINES_MAX_DEPTH ? state_at(st, d) : 0u;
+            if (o == 0 || (o & 1u) != (kind == ROW_CLOSE_OBJ ? 1u : 0u)) { ok = false; }
+            else {
+                const uint32_t orow = (o >> 1) - 1;
+                rb.koff[r] = orow;        // (TapeView::rows_direct: rows, not bracket numbers)
+                rb.voff[orow] = r;
+                if (module_row && orow == module_row - 1) res->module_end = r;
+            }
+        } else {
+            // a value: at the top there is exactly one; inside an object it has a key, inside an array none
+            if (d == 0) { if (r != 0) ok = false; }
+            else {
+                const uint32_t c = d - 1 <= LINES_MAX_DEPTH ? state_at(st, d - 1) : 0u;
+                if (c == 0 || ((c & 1u) != 0) != ((m & META_HAS_KEY) != 0)) ok = false;
+            }
+            // key order across a container that has just closed: the member before this one is the
+            // one that opened at this depth last
+            const uint32_t pk = prev_meta & 15u;
+            if (ok && (m & META_HAS_KEY) && r > 0 && (pk == ROW_CLOSE_OBJ || pk == ROW_CLOSE_ARR) && (prev_meta >> META_DEPTH_SHIFT) == d) {
+                const uint32_t o = d <= LINES_MAX_DEPTH ? state_at(st, d) : 0u;
+                if (o == 0) ok = false;
+                else {
+                    const uint32_t orow = (o >> 1) - 1;
+                    const uint32_t ao = __ldg(rb.koff + orow), al = __ldg(rb.klen + orow), bo = __ldg(rb.koff + r), bl = __ldg(rb.klen + r);
+                    if (!(__ldg(rb.meta + orow) & META_HAS_KEY) || !key_less(GlobalText{raw}, ao, al, bo, bl)) ok = false;
+                }
+            }
+            state_note(st, m, r);
+        }
+        prev_meta = m;
+    }
+    if (!ok) res->fast_reject = 1;
+}
+
+}  // namespace
+
+cudaError_t launch_lines_count(const uint8_t *raw, size_t n, uint32_t *scratch, ParseResult *res, cudaStream_t s) {
+    const uint32_t tiles = lines_tiles(n);
+    cudaError_t e = cudaMemsetAsync(res, 0, sizeof(ParseResult), s);
+    if (e != cudaSuccess) return e;
+    lines_count_kernel<<<tiles, LN_THREADS, 0, s>>>(raw, (u64)n, scratch, scratch + tiles);
+    lines_prefix_kernel<<<1, 1024, 0, s>>>(scratch, tiles, res);
+    count_parse_launch(); count_parse_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lines_rows(const uint8_t *raw, size_t n, const uint32_t *scratch, RowBuffers rb, uint32_t row_cap, ParseResult *res,
+                              cudaStream_t s) {
+    const uint32_t tiles = lines_tiles(n);
+    // (the text is padded to a whole tile of the general scan and 64 bytes more: engine.cu, upload_text)
+    const size_t readable_end = (size_t)p1_tiles(n) * P1_TILE + 64;
+    static std::atomic<uint32_t> cached[64];   // resident blocks of the persistent kernel, per device
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    uint32_t grid = dev >= 0 && dev < 64 ? cached[dev].load() : 0;
+    if (!grid) {
+        int per_sm = 0, sms = 0;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lines_rows_kernel, LN_THREADS, 0)) != cudaSuccess) return e;
+        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+        grid = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)(sms > 0 ? sms : 1);
+        if (dev >= 0 && dev < 64) cached[dev].store(grid);
+    }
+    lines_rows_kernel<<<std::min(tiles, grid), LN_THREADS, 0, s>>>(raw, (u64)n, (u64)readable_end, tiles, scratch, scratch + tiles, rb, row_cap, res);
+    count_parse_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lines_structure(const uint8_t *raw, RowBuffers rb, uint32_t row_cap, uint32_t *open_state, ParseResult *res, cudaStream_t s) {
+    const uint32_t blocks = lines_row_blocks(row_cap);
+    if (!blocks) return cudaSuccess;
+    lines_open_agg_kernel<<<blocks, SR_THREADS, 0, s>>>(rb.meta, open_state, res);
+    lines_open_prefix_kernel<<<1, 32 * ST_DEPTHS, 0, s>>>(open_state, res);
+    lines_resolve_kernel<<<blocks, SR_THREADS, 0, s>>>(raw, rb, open_state, res);
+    count_parse_launch(); count_parse_launch(); count_parse_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace tk

@@ -63,6 +63,7 @@ struct ParseResult {
     unsigned int module_row;      // 1 + the row of the root object's "module" member; 0: there is none
     unsigned int module_kind;     // its RowKind
     unsigned int module_end;      // the row that closes it (an object), else 0
+    unsigned int fast_reject;     // the pass for text in indented form (lines.cu) declined: run the general pipeline
     // module index (field_find_kernel, index.cu): per field -- 0 "name", 1 "hostname" -- how many
     // children of "module" carry it as a string member, and the bytes of their packed result records;
     // index_slow: a child had more members than the kernel walks through (Clusters / Nodes then use the host tree)

@@ -54,6 +54,10 @@ struct TapeView {        // pointers may be host (pinned) or device
     // position of their bracket in vlen (otherwise 0).  emit_kernel uses it to recognise input that
     // is already in output form.  0 for a tape flattened from the host tree.
     uint32_t text_len;
+    // true: the tape came from the pass for text in indented form (lines.cu) -- voff of an opening row
+    // is the ROW that closes it, koff of a closing row the ROW that opened it.  false (with text_len
+    // != 0): they are bracket numbers (BracketBuffers), as the general parse leaves them.
+    bool rows_direct;
 };
 
 #ifdef __CUDACC__
