@@ -415,8 +415,8 @@ def run_ours(args, rank, local_rank, world):
             kern[name] = {"launches_per_step": st["timed"] / args.steps, "avg_us": st["ms"] / st["timed"] * 1e3,
                           "ms_per_step": st["ms"] / args.steps}
     # algorithmic bytes per launch: New = input length, Bytes = output length
-    algo = {"scan_count_kernel": len(text), "scan_emit_kernel": len(text), "scan_kernel (fused)": len(text), "emit_kernel": len(text),
-            "row_offsets_kernel": len(text)}
+    algo = {"scan_count_kernel": len(text), "scan_emit_kernel": len(text), "emit_kernel": len(text), "row_offsets_kernel": len(text),
+            "lines_count + lines_prefix kernels": len(text), "lines_rows_kernel": len(text)}
     for k, v in kern.items():
         if k in algo:
             v["algorithmic_bytes"] = algo[k]

@@ -625,3 +625,104 @@ def test_random_module_child_edits_stay_on_the_device(tk, oracle, seed):
     assert not a.host_tree_built
     a._set("other.deep", {"k": "v"}); b._set("other.deep", {"k": "v"})          # not a module child: the tree takes over
     assert a.host_tree_built and a.Bytes() == b.Bytes() and a.Clusters() == b.Clusters()
+
+
+# ---- text in the indented form: the line-by-line pass (csrc/lines.cu) and what it must decline --------
+
+def _outcome(mod, raw):
+    try:
+        s = mod.New("x", raw)
+        return ("ok", s.Bytes(), s.Clusters() if b'"module"' in raw[:40] else None)
+    except Exception as e:       # the Go error text
+        return ("err", str(e))
+
+
+def _pretty(oracle, doc):
+    return oracle.New("x", json.dumps(doc).encode()).Bytes()
+
+
+NEAR_MISSES = [
+    (b'"name": "c0001"', b'"name":"c0001"'), (b'"name": "c0001"', b'"name":  "c0001"'), (b'"name": "c0001",', b'"name": "c0001" ,'),
+    (b'"name": "c0001",', b'"name": "c0001"'), (b'"name": "c0001",', b'"name": "c0001",,'), (b'"name": "c0001",', b'"name": "c0001", '),
+    (b'"name": "c0001",', b'"name": "c0001",\r'), (b'\t\t\t"name": "c0001"', b'\t\t"name": "c0001"'), (b'\t\t\t"name": "c0001"', b'\t\t\t\t"name": "c0001"'),
+    (b'\t\t\t"name": "c0001"', b'\t\t \t"name": "c0001"'), (b'"name": "c0001"', b'"name": "c0\\u0030001"'), (b'"name": "c0001"', b'"name": "c<1"'),
+    (b'"name": "c0001"', b'"name": "c\xc3\xa91"'), (b'"name": "c0001"', b'"name": "c\xff1"'), (b'"name": "c0001"', b'"name": "c\x011"'),
+    (b'"name": "c0001"', b'"name": "c\t1"'), (b'"name": "c0001"', b'"name": 17'), (b'"name": "c0001"', b'"name": 1.50'), (b'"name": "c0001"', b'"name": 1e3'),
+    (b'"name": "c0001"', b'"name": 01'), (b'"name": "c0001"', b'"name": -0'), (b'"name": "c0001"', b'"name": 1234567890123456'),
+    (b'"name": "c0001"', b'"name": 123456789012345'), (b'"name": "c0001"', b'"name": tru'), (b'"name": "c0001"', b'"name": null'),
+    (b'"name": "c0001"', b'"name": {}'), (b'"name": "c0001"', b'"name": []'), (b'"name": "c0001"', b'"name": [ ]'), (b'"name": "c0001"', b'"name": "c0001" "x"'),
+    (b'"name": "c0001"', b'"name" "c0001"'), (b'"name": "c0001"', b'"name": "c0001'), (b'"name": "c0001"', b'name: "c0001"'), (b'"name": "c0001"', b'"c0001"'),
+    (b'"name": "c0001"', b'"aame": "c0001"'), (b'"name": "c0001"', b'"zame": "c0001"'), (b'"name": "c0001"', b'"k8s_version": "c0001"'),
+    (b'"cluster_baremetal_c0001": {', b'"cluster_baremetal_c0001": ['), (b'"cluster_baremetal_c0001": {', b'"cluster_baremetal_c0001": {}'),
+    (b'"cluster_baremetal_c0001": {', b'"cluster_baremetal_c0001": {,'), (b'"cluster_baremetal_c0001": {', b'"cluster_baremetal_b": {'),
+    (b'"cluster_baremetal_c0001": {', b'"cluster_baremetal_c0000": {'), (b'"cluster_baremetal_c0001": {', b'"a": {'), (b'"cluster_baremetal_c0001": {', b'{'),
+    (b'"worker": "true"\n', b'"worker": "true",\n'), (b'"worker": "true"\n', b'"worker": "true"\n\n'), (b'"worker": "true"\n', b'"worker": "true"\n\t\t\t\t"zz": 1\n'),
+]
+
+
+def test_near_misses_of_the_indented_form_are_declined_or_agree(tk, oracle):
+    """A document in the indented form with one small thing wrong -- a space, a comma, a tab, a key out of
+    order, a number that would be re-formatted, a byte that would be escaped, the wrong bracket -- at the
+    start, in the middle and at the end of a text that spans several tiles of the line pass: whatever the
+    product makes of it (a document, or Go's error text) is what the oracle makes of it."""
+    base = _pretty(oracle, json.loads(synth.document(25, 8)))
+    assert len(base) > 3 * 8192 and _outcome(tk, base) == _outcome(oracle, base)
+    assert not tk.New("x", base).host_tree_built
+    for old, new in NEAR_MISSES:
+        for which in (0, -1):
+            at = base.find(old) if which == 0 else base.rfind(old)
+            if at < 0:
+                continue
+            raw = base[:at] + new + base[at + len(old):]
+            assert _outcome(tk, raw) == _outcome(oracle, raw), (old, new, which)
+    for raw in (base + b"\n", base + b" ", b"\n" + base, base[:-1], base[:-2] + b"]", base + b"}", base.replace(b"\n", b"\r\n"), base.replace(b"\t", b"  "),
+                base[:1] + b"\n" + base[1:], base.replace(b"{\n\t\"module\"", b"[\n\t\"module\"", 1)):
+        assert _outcome(tk, raw) == _outcome(oracle, raw), raw[:30]
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_random_damage_to_the_indented_form(tk, oracle, seed):
+    """Random single-byte and single-line damage anywhere in an indented document (several tiles long)."""
+    rng = random.Random(7700 + seed)
+    base = _pretty(oracle, rand_tree(rng, 5) if seed % 2 else json.loads(synth.document(12, 6)))
+    if seed % 2:
+        base = _pretty(oracle, {"module": {("k%04d" % i): rand_tree(rng, 3) for i in range(300)}, "z": [1, "two", None, {}]})
+    lines = base.split(b"\n")
+    for _ in range(60):
+        r = rng.random()
+        if r < 0.4:
+            i = rng.randrange(len(base))
+            raw = base[:i] + bytes([rng.choice(b' \t\n",:{}[]\\0a<\xc3\x00')]) + base[i + (rng.random() < 0.7):]
+        elif r < 0.7:
+            i = rng.randrange(len(lines))
+            raw = b"\n".join(lines[:i] + lines[i + 1:])
+        elif r < 0.85:
+            i, j = rng.randrange(len(lines)), rng.randrange(len(lines))
+            l2 = list(lines); l2[i], l2[j] = l2[j], l2[i]
+            raw = b"\n".join(l2)
+        else:
+            i = rng.randrange(len(lines))
+            raw = b"\n".join(lines[:i] + [lines[i]] + lines[i:])
+        assert _outcome(tk, raw) == _outcome(oracle, raw), raw[:60]
+
+
+def test_indented_form_long_lines_deep_nesting_and_dense_tiles(tk, oracle):
+    """Shapes at the limits of the line pass: strings longer than its fast path (120 bytes), than its window
+    margins (512) and than a tile (8 KiB), nesting at and past the depth it tracks, a tile with thousands of
+    tiny lines, empty containers everywhere -- all must come out as from the oracle, on the device when the
+    general parse would have left them there."""
+    docs = [
+        {"module": {"a": {"name": "x" * n, "hostname": "y" * (n + 3)} for n in (100, 119, 120, 121, 127, 128, 129, 300, 511, 512, 513, 700)}},
+        {"module": {"k%02d" % i: {"name": "n" * (8100 + i * 17)} for i in range(6)}, "tail": "t" * 20000},
+        {"a": [list(range(3000))], "b": {"c": [[], {}, [[]], [{}], {"d": {}}]}},
+    ]
+    for depth in (6, 7, 8, 9, 10, 12):
+        d = "leaf"
+        for i in range(depth):
+            d = {"k%d" % i: d, "l": [d]} if i % 2 else [d, {"m": i}]
+        docs.append({"module": {"deep": d, "zz": {"name": "after"}}})
+    for doc in docs:
+        raw = _pretty(oracle, doc)
+        assert _outcome(tk, raw) == _outcome(oracle, raw)
+        s = tk.New("x", raw)
+        assert not s.host_tree_built and s.Bytes() == raw

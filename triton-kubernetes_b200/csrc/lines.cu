@@ -401,6 +401,13 @@ struct MaskText {
         return sh ? (x0 >> sh) | (x1 << (64u - sh)) : x0;
     }
     __device__ __forceinline__ uint32_t byte(u64 p) const { return p >= lo && p < hi ? (uint32_t)win[p - lo] : (uint32_t)__ldg(raw + p); }
+    // the same for an offset into the window the caller knows to be inside it (16 bytes to spare)
+    __device__ __forceinline__ u64 load8_in(uint32_t off) const {
+        const u64 *w = reinterpret_cast<const u64 *>(win + (off & ~7u));
+        const u64 x0 = w[0], x1 = w[1];
+        const uint32_t sh = (off & 7u) * 8u;
+        return sh ? (x0 >> sh) | (x1 << (64u - sh)) : x0;
+    }
     // 64 mask bits from position p on (p inside the window)
     __device__ __forceinline__ u64 bits(const u64 *m, u64 p) const {
         const uint32_t b = (uint32_t)((long long)p - w0), i = b >> 6, sh = b & 63u;
@@ -436,9 +443,22 @@ __device__ __forceinline__ u64 shift192(u64 a, u64 b, u64 c, uint32_t by) {   //
     if (by >= 64) { a = b; b = c; by -= 64; }
     return by ? (a >> by) | (b << (64u - by)) : a;
 }
+// strictly ascending, bytewise, two keys inside the window (offsets into it)
+__device__ __forceinline__ bool key_less_in(const MaskText &t, uint32_t a, uint32_t al, uint32_t b, uint32_t bl) {
+    const uint32_t m = al < bl ? al : bl;
+    for (uint32_t i = 0; i < m; i += 8) {
+        u64 x = big_endian(t.load8_in(a + i)), y = big_endian(t.load8_in(b + i));
+        if (m - i < 8) { const u64 keep = ~0ull << ((8 - (m - i)) * 8); x &= keep; y &= keep; }
+        if (x != y) return x < y;
+    }
+    return al < bl;
+}
 __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n, uint32_t r, RowBuffers rb, ParseResult *res) {
     const uint32_t L = (uint32_t)(e - s);
-    if (L == 0 || L > 120 || (long long)s + 256 > t.w1 || e >= n) return 2;   // (120: the look at the next line stays inside 192 mask bits)
+    // (120: the look at the next line stays inside 192 mask bits; 288: every read below stays inside the window)
+    if (L == 0 || L > 120 || (long long)s + 288 > t.w1 || s + 288 > t.hi || e >= n) return 2;
+    const uint8_t *w = t.win + (uint32_t)(s - t.lo);      // w[x]: the byte x places into the line
+    const uint32_t so = (uint32_t)(s - t.lo);
     const u64 T0 = t.bits(t.tabm, s), T1 = t.bits(t.tabm, s + 64), T2 = t.bits(t.tabm, s + 128);
     const uint32_t d = T0 == ~0ull ? 64u : (uint32_t)__ffsll((long long)~T0) - 1u;
     if (d > LINES_MAX_DEPTH + 1 || d >= L || (r == 0 && d != 0)) return 0;
@@ -457,47 +477,48 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
             else { qp[i] = 64u + (uint32_t)__ffsll((long long)q1) - 1u; q1 &= q1 - 1; }
         }
     }
+    const uint32_t s32 = (uint32_t)s;              // (the text is under 4 GiB)
     uint32_t meta = 0, koff = 0, klen = 0, voff = 0, vlen = 0, v = d, used = 0;   // v: where the value starts; used: quotes accounted for
-    if (nq >= 2 && qp[0] == d && qp[1] + 1 < L && t.byte(s + qp[1] + 1) == ':') {
-        if (qp[1] + 2 >= L || t.byte(s + qp[1] + 2) != ' ') return 0;
+    if (nq >= 2 && qp[0] == d && qp[1] + 1 < L && w[qp[1] + 1] == ':') {
+        if (qp[1] + 2 >= L || w[qp[1] + 2] != ' ') return 0;
         meta |= META_HAS_KEY | META_KEY_PLAIN;
-        koff = (uint32_t)s + d + 1;
+        koff = s32 + d + 1;
         klen = qp[1] - d - 1;
         v = qp[1] + 3;
         used = 2;
         if (v >= L) return 0;
     }
-    const uint32_t c = t.byte(s + v);
+    const uint32_t c = w[v];
     uint32_t after;
     if (c == '"') {
         if (nq != used + 2 || qp[used] != v) return 0;
         meta |= ROW_STR | META_VAL_PLAIN;
-        voff = (uint32_t)s + v + 1;
+        voff = s32 + v + 1;
         vlen = qp[used + 1] - v - 1;
         after = qp[used + 1] + 1;
     } else {
         if (nq != used) return 0;                   // a quote where no string can be
         if (c == '{' || c == '[') {
-            vlen = (uint32_t)s + v;                 // container rows keep the text position of their bracket
-            if (v + 1 < L && t.byte(s + v + 1) == (c == '{' ? '}' : ']')) { meta |= c == '{' ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR; after = v + 2; }
+            vlen = s32 + v;                         // container rows keep the text position of their bracket
+            if (v + 1 < L && w[v + 1] == (c == '{' ? '}' : ']')) { meta |= c == '{' ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR; after = v + 2; }
             else { meta |= c == '{' ? ROW_OPEN_OBJ : ROW_OPEN_ARR; after = v + 1; }
         } else if (c == '}' || c == ']') {
             if (meta & META_HAS_KEY) return 0;
             meta |= c == '}' ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR;
-            vlen = (uint32_t)s + v;
+            vlen = s32 + v;
             after = v + 1;
         } else {
-            after = t.byte(e - 1) == ',' ? L - 1 : L;
+            after = w[L - 1] == ',' ? L - 1 : L;
             if (after <= v || !canonical_scalar(t, s + v, s + after)) return 0;
             meta |= ROW_RAW;
-            voff = (uint32_t)s + v;
+            voff = s32 + v;
             vlen = after - v;
         }
     }
     const uint32_t kind = meta & 15u;
     const bool is_open = kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR;
     bool comma = false;
-    if (after < L && t.byte(s + after) == ',') { comma = true; after++; }
+    if (after < L && w[after] == ',') { comma = true; after++; }
     if (after != L || (comma && is_open)) return 0;
     if (comma) meta |= META_COMMA;
     meta |= d << META_DEPTH_SHIFT;
@@ -505,9 +526,8 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
     const uint32_t nb = L + 1;                                             // where the next line starts, from s
     const u64 tn = shift192(T0, T1, T2, nb);
     const uint32_t dn = tn == ~0ull ? 64u : (uint32_t)__ffsll((long long)~tn) - 1u;
-    const u64 q = e + 1 + dn;
-    if (dn > LINES_MAX_DEPTH + 1 || q >= n) return 0;
-    const uint32_t cn = t.byte(q);
+    if (dn > LINES_MAX_DEPTH + 1 || e + 1 + dn >= n) return 0;
+    const uint32_t cn = w[nb + dn];
     const bool next_closes = cn == '}' || cn == ']';
     if (is_open) {
         if (dn != d + 1 || next_closes) return 0;
@@ -523,14 +543,26 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
             const u64 qn = shift192(Q0, Q1, Q2, from);
             if (!qn) return 2;
             const uint32_t nl = (uint32_t)__ffsll((long long)qn) - 1u;
-            if (!key_less(t, koff, klen, s + from, nl)) return 0;
+            if (!key_less_in(t, so + d + 1, klen, so + from, nl)) return 0;
         }
     }
-    finish_row(t, r, d, meta, koff, klen, voff, vlen, rb, res);
+    // the row, with what the module index and the verdict want to know about it (finish_row, from the window)
+    if (d == 3 && kind == ROW_STR && (meta & META_HAS_KEY) && (klen == 4 || klen == 8)) {
+        const u64 k8 = t.load8_in(so + d + 1);
+        if (klen == 4 && (uint32_t)k8 == 0x656d616eu) meta |= META_KEY_IS_NAME;
+        else if (klen == 8 && k8 == 0x656d616e74736f68ull) meta |= META_KEY_IS_HOSTNAME;
+    }
+    rb.meta[r] = meta; rb.koff[r] = koff; rb.klen[r] = klen; rb.voff[r] = voff; rb.vlen[r] = vlen;
+    if (r == 0) res->root_kind = kind;
+    if (d == 1 && (meta & META_HAS_KEY) && klen == 6 && (t.load8_in(so + d + 1) & 0xffffffffffffull) == 0x656c75646f6dull) {   // "module"
+        res->module_row = r + 1;
+        res->module_kind = kind;
+    }
     return 1;
 }
 
-__global__ void __launch_bounds__(LN_THREADS) lines_rows_kernel(const uint8_t *__restrict__ raw, u64 n, u64 readable_end, uint32_t n_tiles,
+constexpr int LR_THREADS = 192;   // 128 classify the tile (the first 12 also its margins); about 186 lines of config #4 per tile: one line each
+__global__ void __launch_bounds__(LR_THREADS) lines_rows_kernel(const uint8_t *__restrict__ raw, u64 n, u64 readable_end, uint32_t n_tiles,
                                                                const uint32_t *__restrict__ first_line, const uint32_t *__restrict__ last_end,
                                                                RowBuffers rb, uint32_t row_cap, ParseResult *res) {
     __shared__ uint32_t s_lut[4 * 256];
@@ -538,10 +570,10 @@ __global__ void __launch_bounds__(LN_THREADS) lines_rows_kernel(const uint8_t *_
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ u64 s_tab[WIN_CHUNKS], s_q[WIN_CHUNKS], s_stop[WIN_CHUNKS];
     __shared__ uint16_t s_end[TILE_LINES];
-    __shared__ uint32_t s_warp[LN_THREADS / 32];
+    __shared__ uint32_t s_warp[LR_THREADS / 32];
     __shared__ u64 s_prev_end;      // position + 1 of the last line end before the tile
     if (res->n_rows > row_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) res->fast_reject = 1; return; }
-    for (int i = threadIdx.x; i < 4 * 256; i += LN_THREADS) s_lut[i] = g_line_lut.v[i];
+    for (int i = threadIdx.x; i < 4 * 256; i += LR_THREADS) s_lut[i] = g_line_lut.v[i];
     if (threadIdx.x == 0) mbar_init(&s_bar, 1);
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -562,8 +594,8 @@ __global__ void __launch_bounds__(LN_THREADS) lines_rows_kernel(const uint8_t *_
         parity ^= 1u;
         // classes of every 64 bytes of the window: a chunk per thread, the few chunks of the margins by the first threads
         u64 my_ends = 0;
-        for (int j = threadIdx.x; j < WIN_CHUNKS; j += LN_THREADS) {
-            const int wc = j < LN_THREADS ? j + WIN_BEFORE / 64 : (j - LN_THREADS < WIN_BEFORE / 64 ? j - LN_THREADS : j);   // own chunk first
+        for (int j = threadIdx.x; j < WIN_CHUNKS; j += LR_THREADS) {
+            const int wc = j < LN_THREADS ? j + WIN_BEFORE / 64 : (j - LN_THREADS < WIN_BEFORE / 64 ? j - LN_THREADS : j);   // the tile's chunks first
             const long long at = w0 + (long long)wc * 64;
             LineMasks m = {0, 0, 0, 0};
             if (at >= 0 && (u64)at + 64 <= hi) {
@@ -588,7 +620,7 @@ __global__ void __launch_bounds__(LN_THREADS) lines_rows_kernel(const uint8_t *_
         if (lane == 31) s_warp[warp] = incl;
         __syncthreads();
         uint32_t before = incl - c, total = 0;
-        for (uint32_t w = 0; w < LN_THREADS / 32; w++) { if (w < warp) before += s_warp[w]; total += s_warp[w]; }
+        for (uint32_t w = 0; w < LR_THREADS / 32; w++) { if (w < warp) before += s_warp[w]; total += s_warp[w]; }
         {
             uint32_t k = before;
             for (u64 left = my_ends; left; left &= left - 1, k++)
@@ -598,7 +630,7 @@ __global__ void __launch_bounds__(LN_THREADS) lines_rows_kernel(const uint8_t *_
         if (total > TILE_LINES) { ok = false; total = 0; }
         // a line per thread, in order
         const uint32_t row0 = first_line[tile];
-        for (uint32_t k = threadIdx.x; k < total; k += LN_THREADS) {
+        for (uint32_t k = threadIdx.x; k < total; k += LR_THREADS) {
             const u64 e = tile0 + s_end[k], s = k ? tile0 + s_end[k - 1] + 1 : s_prev_end;
             bool done = false;
             if ((long long)s >= w0 && s >= lo) {
@@ -792,12 +824,12 @@ cudaError_t launch_lines_rows(const uint8_t *raw, size_t n, const uint32_t *scra
     uint32_t grid = dev >= 0 && dev < 64 ? cached[dev].load() : 0;
     if (!grid) {
         int per_sm = 0, sms = 0;
-        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lines_rows_kernel, LN_THREADS, 0)) != cudaSuccess) return e;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lines_rows_kernel, LR_THREADS, 0)) != cudaSuccess) return e;
         if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
         grid = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)(sms > 0 ? sms : 1);
         if (dev >= 0 && dev < 64) cached[dev].store(grid);
     }
-    lines_rows_kernel<<<std::min(tiles, grid), LN_THREADS, 0, s>>>(raw, (u64)n, (u64)readable_end, tiles, scratch, scratch + tiles, rb, row_cap, res);
+    lines_rows_kernel<<<std::min(tiles, grid), LR_THREADS, 0, s>>>(raw, (u64)n, (u64)readable_end, tiles, scratch, scratch + tiles, rb, row_cap, res);
     count_parse_launch();
     return cudaGetLastError();
 }
