@@ -457,106 +457,83 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
     const uint32_t L = (uint32_t)(e - s);
     // (120: the look at the next line stays inside 192 mask bits; 288: every read below stays inside the window)
     if (L == 0 || L > 120 || (long long)s + 288 > t.w1 || s + 288 > t.hi || e >= n) return 2;
+    // Straight-line code from here on: what is wrong is collected in `bad`, not returned at once, so that the lanes
+    // of a warp -- thirty-two different lines -- stay together and the rows are written by all of them at once.
     const uint8_t *w = t.win + (uint32_t)(s - t.lo);      // w[x]: the byte x places into the line
-    const uint32_t so = (uint32_t)(s - t.lo);
+    const uint32_t so = (uint32_t)(s - t.lo), s32 = (uint32_t)s;   // (the text is under 4 GiB)
     const u64 T0 = t.bits(t.tabm, s), T1 = t.bits(t.tabm, s + 64), T2 = t.bits(t.tabm, s + 128);
     const uint32_t d = T0 == ~0ull ? 64u : (uint32_t)__ffsll((long long)~T0) - 1u;
-    if (d > LINES_MAX_DEPTH + 1 || d >= L || (r == 0 && d != 0)) return 0;
+    bool bad = d > LINES_MAX_DEPTH + 1 || d >= L || (r == 0 && d != 0);
     const u64 Q0 = t.bits(t.qm, s), Q1 = t.bits(t.qm, s + 64), Q2 = t.bits(t.qm, s + 128);
     const u64 S0 = t.bits(t.stopm, s), S1 = t.bits(t.stopm, s + 64);
     const u64 in0 = low_bits(L), in1 = L > 64 ? low_bits(L - 64) : 0ull;       // the line's own bits
-    if ((S0 & in0 & ~low_bits(d)) | (S1 & in1)) return 0;                          // something that cannot stand for itself
+    bad = bad || ((S0 & in0 & ~low_bits(min(d, 63u))) | (S1 & in1)) != 0;          // something that cannot stand for itself
     u64 q0 = Q0 & in0, q1 = Q1 & in1;
     const uint32_t nq = (uint32_t)__popcll(q0) + (uint32_t)__popcll(q1);
-    if (nq != 0 && nq != 2 && nq != 4) return 0;
-    uint32_t qp[4] = {0, 0, 0, 0};
+    bad = bad || (nq != 0 && nq != 2 && nq != 4);
+    uint32_t qp[4];
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-        if ((uint32_t)i < nq) {
-            if (q0) { qp[i] = (uint32_t)__ffsll((long long)q0) - 1u; q0 &= q0 - 1; }
-            else { qp[i] = 64u + (uint32_t)__ffsll((long long)q1) - 1u; q1 &= q1 - 1; }
-        }
+        const bool lo_has = q0 != 0;
+        const u64 src = lo_has ? q0 : q1;
+        qp[i] = src ? (lo_has ? 0u : 64u) + (uint32_t)__ffsll((long long)src) - 1u : 127u;   // 127: no such quote (inside the window all the same)
+        if (lo_has) q0 &= q0 - 1; else q1 &= q1 - 1;
     }
-    const uint32_t s32 = (uint32_t)s;              // (the text is under 4 GiB)
-    uint32_t meta = 0, koff = 0, klen = 0, voff = 0, vlen = 0, v = d, used = 0;   // v: where the value starts; used: quotes accounted for
-    if (nq >= 2 && qp[0] == d && qp[1] + 1 < L && w[qp[1] + 1] == ':') {
-        if (qp[1] + 2 >= L || w[qp[1] + 2] != ' ') return 0;
-        meta |= META_HAS_KEY | META_KEY_PLAIN;
-        koff = s32 + d + 1;
-        klen = qp[1] - d - 1;
-        v = qp[1] + 3;
-        used = 2;
-        if (v >= L) return 0;
-    }
-    const uint32_t c = w[v];
-    uint32_t after;
-    if (c == '"') {
-        if (nq != used + 2 || qp[used] != v) return 0;
-        meta |= ROW_STR | META_VAL_PLAIN;
-        voff = s32 + v + 1;
-        vlen = qp[used + 1] - v - 1;
-        after = qp[used + 1] + 1;
-    } else {
-        if (nq != used) return 0;                   // a quote where no string can be
-        if (c == '{' || c == '[') {
-            vlen = s32 + v;                         // container rows keep the text position of their bracket
-            if (v + 1 < L && w[v + 1] == (c == '{' ? '}' : ']')) { meta |= c == '{' ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR; after = v + 2; }
-            else { meta |= c == '{' ? ROW_OPEN_OBJ : ROW_OPEN_ARR; after = v + 1; }
-        } else if (c == '}' || c == ']') {
-            if (meta & META_HAS_KEY) return 0;
-            meta |= c == '}' ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR;
-            vlen = s32 + v;
-            after = v + 1;
-        } else {
-            after = w[L - 1] == ',' ? L - 1 : L;
-            if (after <= v || !canonical_scalar(t, s + v, s + after)) return 0;
-            meta |= ROW_RAW;
-            voff = s32 + v;
-            vlen = after - v;
-        }
-    }
-    const uint32_t kind = meta & 15u;
-    const bool is_open = kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR;
-    bool comma = false;
-    if (after < L && w[after] == ',') { comma = true; after++; }
-    if (after != L || (comma && is_open)) return 0;
-    if (comma) meta |= META_COMMA;
-    meta |= d << META_DEPTH_SHIFT;
+    // "key": -- a quote right after the indentation, the next quote followed by a colon and a space
+    const bool key_shape = nq >= 2 && qp[0] == d && qp[1] + 1 < L && w[qp[1] + 1] == ':';
+    bad = bad || (key_shape && (qp[1] + 2 >= L || w[qp[1] + 2] != ' ' || qp[1] + 3 >= L));
+    const uint32_t used = key_shape ? 2u : 0u;                  // quotes accounted for
+    const uint32_t v = key_shape ? min(qp[1] + 3, 127u) : min(d, 127u);   // where the value starts
+    const uint32_t koff = key_shape ? s32 + d + 1 : 0u, klen = key_shape ? qp[1] - d - 1 : 0u;
+    const uint32_t c = w[v], c1 = w[v + 1];
+    const bool is_str = c == '"', is_brace = c == '{', is_brack = c == '[', is_cl = c == '}' || c == ']';
+    const bool is_empty = (is_brace && c1 == '}' && v + 1 < L) || (is_brack && c1 == ']' && v + 1 < L);
+    const bool is_open = (is_brace || is_brack) && !is_empty, is_scalar = !(is_str || is_brace || is_brack || is_cl);
+    const uint32_t qa = used ? qp[2] : qp[0], qb = used ? qp[3] : qp[1];          // the value's quotes, if it is a string
+    bad = bad || (is_str ? (nq != used + 2 || qa != v) : nq != used);            // a quote where no string can be, or one too few
+    bad = bad || (is_cl && key_shape);
+    uint32_t kind, after, voff = 0, vlen = 0;
+    if (is_str) { kind = ROW_STR | META_VAL_PLAIN; voff = s32 + v + 1; vlen = qb - v - 1; after = qb + 1; }
+    else if (is_empty) { kind = is_brace ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR; vlen = s32 + v; after = v + 2; }
+    else if (is_open) { kind = is_brace ? ROW_OPEN_OBJ : ROW_OPEN_ARR; vlen = s32 + v; after = v + 1; }
+    else if (is_cl) { kind = c == '}' ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR; vlen = s32 + v; after = v + 1; }
+    else { kind = ROW_RAW; after = w[L - 1] == ',' ? L - 1 : L; voff = s32 + v; vlen = after - v; }
+    if (is_scalar && !bad) bad = after <= v || !canonical_scalar(t, s + v, s + after);   // (container rows keep the position of their bracket in vlen)
+    const bool comma = after < L && w[min(after, 127u)] == ',';
+    after += comma ? 1u : 0u;
+    bad = bad || after != L || (comma && is_open);
+    uint32_t meta = kind | (key_shape ? META_HAS_KEY | META_KEY_PLAIN : 0u) | (comma ? META_COMMA : 0u) | (d << META_DEPTH_SHIFT);
     // ---- this line against the next one: indentation, comma, key order
     const uint32_t nb = L + 1;                                             // where the next line starts, from s
     const u64 tn = shift192(T0, T1, T2, nb);
     const uint32_t dn = tn == ~0ull ? 64u : (uint32_t)__ffsll((long long)~tn) - 1u;
-    if (dn > LINES_MAX_DEPTH + 1 || e + 1 + dn >= n) return 0;
-    const uint32_t cn = w[nb + dn];
+    bad = bad || dn > LINES_MAX_DEPTH + 1 || e + 1 + dn >= n;
+    const uint32_t cn = w[nb + min(dn, 16u)];
     const bool next_closes = cn == '}' || cn == ']';
-    if (is_open) {
-        if (dn != d + 1 || next_closes) return 0;
-    } else if (next_closes) {
-        if (d == 0 || dn != d - 1 || comma) return 0;
-    } else {
-        if (dn != d || !comma) return 0;
-        if (meta & META_HAS_KEY) {
-            if (cn != '"') return 0;
-            // the next key ends at the next quote (whether that line is well formed is its own thread's business)
-            const uint32_t from = nb + dn + 1;                            // first byte of the next key, from s
-            if (from >= 128) return 2;
-            const u64 qn = shift192(Q0, Q1, Q2, from);
-            if (!qn) return 2;
-            const uint32_t nl = (uint32_t)__ffsll((long long)qn) - 1u;
-            if (!key_less_in(t, so + d + 1, klen, so + from, nl)) return 0;
-        }
+    bad = bad || (is_open ? (dn != d + 1 || next_closes) : next_closes ? (d == 0 || dn != d - 1 || comma) : (dn != d || !comma));
+    int verdict = 1;
+    if (!bad && key_shape && !is_open && !next_closes) {
+        // the next member of the same object: its key -- up to the next quote; whether that line is well formed is
+        // its own thread's business -- must sort strictly after this one
+        const uint32_t from = nb + dn + 1;                                // first byte of the next key, from s
+        const u64 qn = from < 128 ? shift192(Q0, Q1, Q2, from) : 0ull;
+        if (cn != '"') bad = true;
+        else if (!qn) verdict = 2;
+        else bad = !key_less_in(t, so + d + 1, klen, so + from, (uint32_t)__ffsll((long long)qn) - 1u);
     }
+    if (bad) return 0;
+    if (verdict == 2) return 2;
     // the row, with what the module index and the verdict want to know about it (finish_row, from the window)
-    if (d == 3 && kind == ROW_STR && (meta & META_HAS_KEY) && (klen == 4 || klen == 8)) {
-        const u64 k8 = t.load8_in(so + d + 1);
-        if (klen == 4 && (uint32_t)k8 == 0x656d616eu) meta |= META_KEY_IS_NAME;
-        else if (klen == 8 && k8 == 0x656d616e74736f68ull) meta |= META_KEY_IS_HOSTNAME;
+    const u64 k8 = t.load8_in(so + d + 1);
+    if (d == 3 && (kind & 15u) == ROW_STR && key_shape) {
+        if (klen == 4 && (uint32_t)k8 == 0x656d616eu) meta |= META_KEY_IS_NAME;                    // "name"
+        else if (klen == 8 && k8 == 0x656d616e74736f68ull) meta |= META_KEY_IS_HOSTNAME;           // "hostname"
     }
     rb.meta[r] = meta; rb.koff[r] = koff; rb.klen[r] = klen; rb.voff[r] = voff; rb.vlen[r] = vlen;
-    if (r == 0) res->root_kind = kind;
-    if (d == 1 && (meta & META_HAS_KEY) && klen == 6 && (t.load8_in(so + d + 1) & 0xffffffffffffull) == 0x656c75646f6dull) {   // "module"
+    if (r == 0) res->root_kind = kind & 15u;
+    if (d == 1 && key_shape && klen == 6 && (k8 & 0xffffffffffffull) == 0x656c75646f6dull) {       // "module"
         res->module_row = r + 1;
-        res->module_kind = kind;
+        res->module_kind = kind & 15u;
     }
     return 1;
 }
