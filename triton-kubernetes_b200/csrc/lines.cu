@@ -408,11 +408,18 @@ struct MaskText {
         const uint32_t sh = (off & 7u) * 8u;
         return sh ? (x0 >> sh) | (x1 << (64u - sh)) : x0;
     }
-    // 64 mask bits from position p on (p inside the window)
+    // 64 mask bits from position p on (p inside the window; the arrays have a spare word behind them).  Read as
+    // 32-bit words and put together with funnel shifts: a 64-bit shift by a variable amount costs several times that.
     __device__ __forceinline__ u64 bits(const u64 *m, u64 p) const {
-        const uint32_t b = (uint32_t)((long long)p - w0), i = b >> 6, sh = b & 63u;
-        const u64 x0 = m[i], x1 = i + 1 < (uint32_t)WIN_CHUNKS ? m[i + 1] : 0ull;
-        return sh ? (x0 >> sh) | (x1 << (64u - sh)) : x0;
+        const uint32_t b = (uint32_t)((long long)p - w0), i = b >> 5, sh = b & 31u;
+        const uint32_t *m32 = reinterpret_cast<const uint32_t *>(m);
+        const uint32_t x0 = m32[i], x1 = m32[i + 1], x2 = m32[i + 2];
+        return (u64)__funnelshift_r(x0, x1, sh) | ((u64)__funnelshift_r(x1, x2, sh) << 32);
+    }
+    // 32 mask bits from window bit b on
+    __device__ __forceinline__ uint32_t bits32(const u64 *m, uint32_t b) const {
+        const uint32_t *m32 = reinterpret_cast<const uint32_t *>(m);
+        return __funnelshift_r(m32[b >> 5], m32[(b >> 5) + 1], b & 31u);
     }
     __device__ __forceinline__ uint32_t tabs(u64 p) const {
         if ((long long)p + 64 > w1) { overrun = true; return 9; }
@@ -461,8 +468,8 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
     // of a warp -- thirty-two different lines -- stay together and the rows are written by all of them at once.
     const uint8_t *w = t.win + (uint32_t)(s - t.lo);      // w[x]: the byte x places into the line
     const uint32_t so = (uint32_t)(s - t.lo), s32 = (uint32_t)s;   // (the text is under 4 GiB)
-    const u64 T0 = t.bits(t.tabm, s), T1 = t.bits(t.tabm, s + 64), T2 = t.bits(t.tabm, s + 128);
-    const uint32_t d = T0 == ~0ull ? 64u : (uint32_t)__ffsll((long long)~T0) - 1u;
+    const uint32_t sb = (uint32_t)((long long)s - t.w0);          // the line's first bit in the masks
+    const uint32_t d = (uint32_t)__ffs((int)~t.bits32(t.tabm, sb)) - 1u;   // (32 tabs: 0xffffffff -> far too deep)
     bool bad = d > LINES_MAX_DEPTH + 1 || d >= L || (r == 0 && d != 0);
     const u64 Q0 = t.bits(t.qm, s), Q1 = t.bits(t.qm, s + 64), Q2 = t.bits(t.qm, s + 128);
     const u64 S0 = t.bits(t.stopm, s), S1 = t.bits(t.stopm, s + 64);
@@ -505,8 +512,7 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
     uint32_t meta = kind | (key_shape ? META_HAS_KEY | META_KEY_PLAIN : 0u) | (comma ? META_COMMA : 0u) | (d << META_DEPTH_SHIFT);
     // ---- this line against the next one: indentation, comma, key order
     const uint32_t nb = L + 1;                                             // where the next line starts, from s
-    const u64 tn = shift192(T0, T1, T2, nb);
-    const uint32_t dn = tn == ~0ull ? 64u : (uint32_t)__ffsll((long long)~tn) - 1u;
+    const uint32_t dn = (uint32_t)__ffs((int)~t.bits32(t.tabm, sb + nb)) - 1u;
     bad = bad || dn > LINES_MAX_DEPTH + 1 || e + 1 + dn >= n;
     const uint32_t cn = w[nb + min(dn, 16u)];
     const bool next_closes = cn == '}' || cn == ']';
@@ -545,12 +551,13 @@ __global__ void __launch_bounds__(LR_THREADS) lines_rows_kernel(const uint8_t *_
     __shared__ uint32_t s_lut[4 * 256];
     __shared__ __align__(16) uint8_t s_text[WIN_BYTES];
     __shared__ __align__(8) uint64_t s_bar;
-    __shared__ u64 s_tab[WIN_CHUNKS], s_q[WIN_CHUNKS], s_stop[WIN_CHUNKS];
+    __shared__ u64 s_tab[WIN_CHUNKS + 1], s_q[WIN_CHUNKS + 1], s_stop[WIN_CHUNKS + 1];   // (a spare word: MaskText::bits reads one ahead)
     __shared__ uint16_t s_end[TILE_LINES];
     __shared__ uint32_t s_warp[LR_THREADS / 32];
     __shared__ u64 s_prev_end;      // position + 1 of the last line end before the tile
     if (res->n_rows > row_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) res->fast_reject = 1; return; }
     for (int i = threadIdx.x; i < 4 * 256; i += LR_THREADS) s_lut[i] = g_line_lut.v[i];
+    if (threadIdx.x == 0) { s_tab[WIN_CHUNKS] = 0; s_q[WIN_CHUNKS] = 0; s_stop[WIN_CHUNKS] = 0; }
     if (threadIdx.x == 0) mbar_init(&s_bar, 1);
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
