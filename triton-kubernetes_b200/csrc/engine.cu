@@ -661,9 +661,11 @@ int Engine::parse_lines(size_t n, ParseResult *out, bool *accepted, std::string 
         if ((e = rows[i]->reserve((row_cap + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(rows)", err);
     if ((e = d_scratch_.reserve(lines_scratch_words(n) * 4 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
     if ((e = d_tiles_.reserve((size_t)lines_row_blocks((uint32_t)row_cap) * 8 * 4 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
-    RowBuffers rb{d_meta_.as<uint32_t>(), d_koff_.as<uint32_t>(), d_klen_.as<uint32_t>(), d_voff_.as<uint32_t>(), d_vlen_.as<uint32_t>()};
+    RowBuffers rb{d_meta_.as<uint32_t>(), d_koff_.as<uint32_t>(), d_klen_.as<uint32_t>(), d_voff_.as<uint32_t>(), d_vlen_.as<uint32_t>(),
+                  d_tiles_.as<uint32_t>()};
     uint32_t *scratch = d_scratch_.as<uint32_t>();
-    if ((e = timed(K_LINES_COUNT, [&] { return launch_lines_count(raw, n, scratch, d_res, stream_); })) != cudaSuccess) return fail(e, "lines_count", err);
+    if ((e = timed(K_LINES_COUNT, [&] { return launch_lines_count(raw, n, scratch, rb.open, (uint32_t)row_cap, d_res, stream_); })) != cudaSuccess)
+        return fail(e, "lines_count", err);
     if ((e = timed(K_LINES_ROWS, [&] { return launch_lines_rows(raw, n, scratch, rb, (uint32_t)row_cap, d_res, stream_); })) != cudaSuccess)
         return fail(e, "lines_rows", err);
     if ((e = timed(K_LINES_STRUCTURE, [&] { return launch_lines_structure(raw, rb, (uint32_t)row_cap, d_tiles_.as<uint32_t>(), d_res, stream_); })) != cudaSuccess)

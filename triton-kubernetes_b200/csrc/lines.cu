@@ -50,9 +50,14 @@ __device__ __forceinline__ u64 chunk_line_ends(const uint8_t *raw, u64 chunk, u6
 
 // ---- stage 0: count -------------------------------------------------------------------------
 __global__ void __launch_bounds__(LN_THREADS) lines_count_kernel(const uint8_t *__restrict__ raw, u64 n, uint32_t *__restrict__ counts,
-                                                                uint32_t *__restrict__ last_end) {
+                                                                uint32_t *__restrict__ last_end, uint32_t *__restrict__ open_state,
+                                                                uint32_t open_words) {
     __shared__ uint32_t s_cnt[LN_THREADS / 32], s_last[LN_THREADS / 32];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    {   // the row pass notes its openers in open_state with atomicMax: cleared here, a slice per block
+        const uint32_t per = (open_words + gridDim.x - 1) / gridDim.x, w0 = blockIdx.x * per;
+        for (uint32_t i = threadIdx.x; i < per && w0 + i < open_words; i += LN_THREADS) open_state[w0 + i] = 0;
+    }
     const u64 chunk = (u64)blockIdx.x * LN_TILE + (u64)threadIdx.x * LN_CHUNK;
     const u64 m = chunk_line_ends(raw, chunk, n);
     uint32_t c = (uint32_t)__popcll(m);
@@ -69,43 +74,59 @@ __global__ void __launch_bounds__(LN_THREADS) lines_count_kernel(const uint8_t *
     }
 }
 
-// in place: counts[t] -> line ends before tile t; the total is the number of lines
-__global__ void __launch_bounds__(1024) lines_prefix_kernel(uint32_t *counts, uint32_t n_tiles, ParseResult *res) {
-    __shared__ uint32_t s_w[32];
+// in place: counts[t] -> line ends before tile t (the total is the number of lines), last_end[t] ->
+// position + 1 of the last line end before tile t (0: none).  Text with fewer than one line end
+// per LN_MIN_DENSITY bytes is not what this path is for (compact JSON is one line): left to the
+// general parser before the row pass looks at it.
+constexpr u64 LN_MIN_DENSITY = 512;
+__global__ void __launch_bounds__(1024) lines_prefix_kernel(uint32_t *counts, uint32_t *last_end, uint32_t n_tiles, u64 n, ParseResult *res) {
+    __shared__ uint32_t s_w[32], s_m[32];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t run = 0;
+    uint32_t run = 0, run_end = 0;
     for (uint32_t base = 0; base < n_tiles; base += 1024 * 4) {
         const uint32_t first = base + threadIdx.x * 4;
-        uint32_t v[4], sum = 0;
-#pragma unroll
-        for (int j = 0; j < 4; j++) { v[j] = first + j < n_tiles ? counts[first + j] : 0u; sum += v[j]; }
-        uint32_t incl = sum;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t y = __shfl_up_sync(FULL, incl, o);
-            if (lane >= (uint32_t)o) incl += y;
-        }
-        __syncthreads();
-        if (lane == 31) s_w[warp] = incl;
-        __syncthreads();
-        uint32_t w = s_w[lane];
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t y = __shfl_up_sync(FULL, w, o);
-            if (lane >= (uint32_t)o) w += y;
-        }
-        const uint32_t total = __shfl_sync(FULL, w, 31);
-        uint32_t before = __shfl_sync(FULL, w, warp ? warp - 1 : 0);
-        if (warp == 0) before = 0;
-        uint32_t x = run + before + incl - sum;
+        uint32_t v[4], e[4], sum = 0, top = 0;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            if (first + j < n_tiles) counts[first + j] = x;
+            v[j] = first + j < n_tiles ? counts[first + j] : 0u;
+            e[j] = first + j < n_tiles ? last_end[first + j] : 0u;
+            sum += v[j];
+            top = max(top, e[j]);
+        }
+        uint32_t incl = sum, mincl = top;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, incl, o), z = __shfl_up_sync(FULL, mincl, o);
+            if (lane >= (uint32_t)o) { incl += y; mincl = max(mincl, z); }
+        }
+        __syncthreads();
+        if (lane == 31) { s_w[warp] = incl; s_m[warp] = mincl; }
+        __syncthreads();
+        uint32_t w = s_w[lane], wm = s_m[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, w, o), z = __shfl_up_sync(FULL, wm, o);
+            if (lane >= (uint32_t)o) { w += y; wm = max(wm, z); }
+        }
+        const uint32_t total = __shfl_sync(FULL, w, 31), total_end = __shfl_sync(FULL, wm, 31);
+        uint32_t before = __shfl_sync(FULL, w, warp ? warp - 1 : 0), before_end = __shfl_sync(FULL, wm, warp ? warp - 1 : 0);
+        if (warp == 0) { before = 0; before_end = 0; }
+        uint32_t lane_end = __shfl_up_sync(FULL, mincl, 1);
+        if (lane == 0) lane_end = 0;
+        uint32_t x = run + before + incl - sum, m = max(run_end, max(before_end, lane_end));
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (first + j < n_tiles) { counts[first + j] = x; last_end[first + j] = m; }
             x += v[j];
+            m = max(m, e[j]);
         }
         run += total;
+        run_end = max(run_end, total_end);
     }
-    if (threadIdx.x == 0) res->n_rows = run;
+    if (threadIdx.x == 0) {
+        res->n_rows = run;
+        if ((u64)run * LN_MIN_DENSITY < n) res->fast_reject = 1;
+    }
 }
 
 // ---- stage 1: one row per line --------------------------------------------------------------
@@ -217,6 +238,12 @@ __device__ __forceinline__ uint32_t Text::tabs(u64 p) const {
 }
 
 // the row written, with what the module index and the verdict want to know about it
+// Stage 2 wants, per block of LN_ROWS_PER_BLOCK rows and per depth, the last row that opens a container there,
+// as (row + 1) << 1 | is-an-object: every opening row says so as it is written (about one row in seven).
+__device__ __forceinline__ void note_opener(const RowBuffers &rb, uint32_t r, uint32_t kind, uint32_t d) {
+    if ((kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR) && d <= LINES_MAX_DEPTH)
+        atomicMax(rb.open + (r / LN_ROWS_PER_BLOCK) * (LINES_MAX_DEPTH + 1) + d, ((r + 1) << 1) | (kind == ROW_OPEN_OBJ ? 1u : 0u));
+}
 template <class Reader>
 __device__ __forceinline__ void finish_row(const Reader &raw, uint32_t r, uint32_t d, uint32_t meta, uint32_t koff, uint32_t klen, uint32_t voff,
                                            uint32_t vlen, RowBuffers rb, ParseResult *res) {
@@ -227,6 +254,7 @@ __device__ __forceinline__ void finish_row(const Reader &raw, uint32_t r, uint32
         else if (klen == 8 && k8 == 0x656d616e74736f68ull) meta |= META_KEY_IS_HOSTNAME;                  // "hostname"
     }
     rb.meta[r] = meta; rb.koff[r] = koff; rb.klen[r] = klen; rb.voff[r] = voff; rb.vlen[r] = vlen;
+    note_opener(rb, r, kind, d);
     if (r == 0) res->root_kind = kind;
     if (d == 1 && (meta & META_HAS_KEY) && klen == 6 && (raw.load8(koff) & 0xffffffffffffull) == 0x656c75646f6dull) {   // "module"
         res->module_row = r + 1;
@@ -536,6 +564,7 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
         else if (klen == 8 && k8 == 0x656d616e74736f68ull) meta |= META_KEY_IS_HOSTNAME;           // "hostname"
     }
     rb.meta[r] = meta; rb.koff[r] = koff; rb.klen[r] = klen; rb.voff[r] = voff; rb.vlen[r] = vlen;
+    note_opener(rb, r, kind & 15u, d);
     if (r == 0) res->root_kind = kind & 15u;
     if (d == 1 && key_shape && klen == 6 && (k8 & 0xffffffffffffull) == 0x656c75646f6dull) {       // "module"
         res->module_row = r + 1;
@@ -545,7 +574,7 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
 }
 
 constexpr int LR_THREADS = 192;   // 128 classify the tile (the first 12 also its margins); about 186 lines of config #4 per tile: one line each
-__global__ void __launch_bounds__(LR_THREADS) lines_rows_kernel(const uint8_t *__restrict__ raw, u64 n, u64 readable_end, uint32_t n_tiles,
+__global__ void __launch_bounds__(LR_THREADS, 8) lines_rows_kernel(const uint8_t *__restrict__ raw, u64 n, u64 readable_end, uint32_t n_tiles,
                                                                const uint32_t *__restrict__ first_line, const uint32_t *__restrict__ last_end,
                                                                RowBuffers rb, uint32_t row_cap, ParseResult *res) {
     __shared__ uint32_t s_lut[4 * 256];
@@ -555,6 +584,7 @@ __global__ void __launch_bounds__(LR_THREADS) lines_rows_kernel(const uint8_t *_
     __shared__ uint16_t s_end[TILE_LINES];
     __shared__ uint32_t s_warp[LR_THREADS / 32];
     __shared__ u64 s_prev_end;      // position + 1 of the last line end before the tile
+    if (res->fast_reject) return;
     if (res->n_rows > row_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) res->fast_reject = 1; return; }
     for (int i = threadIdx.x; i < 4 * 256; i += LR_THREADS) s_lut[i] = g_line_lut.v[i];
     if (threadIdx.x == 0) { s_tab[WIN_CHUNKS] = 0; s_q[WIN_CHUNKS] = 0; s_stop[WIN_CHUNKS] = 0; }
@@ -570,9 +600,7 @@ __global__ void __launch_bounds__(LR_THREADS) lines_rows_kernel(const uint8_t *_
         const long long w0 = (long long)tile0 - WIN_BEFORE;
         if (threadIdx.x == 0) {
             bulk_load(s_text, raw + lo, (uint32_t)(hi - lo), &s_bar);
-            int tt = (int)tile - 1;
-            while (tt >= 0 && last_end[tt] == 0) tt--;
-            s_prev_end = tt >= 0 ? (u64)last_end[tt] : 0;
+            s_prev_end = (u64)last_end[tile];
         }
         mbar_wait(&s_bar, parity);
         parity ^= 1u;
@@ -640,158 +668,151 @@ __global__ void __launch_bounds__(LR_THREADS) lines_rows_kernel(const uint8_t *_
 // The state that travels along the rows: for every depth k <= LINES_MAX_DEPTH the last opening row
 // seen at that depth, as (row + 1) << 1 | is-an-object (0: none yet).  Later rows have larger
 // numbers, so "the last one" is a maximum: the state of a stretch of rows is combined by max.
+// Stage 1 has left that maximum per block of LN_ROWS_PER_BLOCK rows (note_opener).
 constexpr int ST_DEPTHS = LINES_MAX_DEPTH + 1;
-struct OpenState { uint32_t v[ST_DEPTHS]; };
-__device__ __forceinline__ void state_note(OpenState &st, uint32_t meta, uint32_t r) {
-    const uint32_t kind = meta & 15u, d = meta >> META_DEPTH_SHIFT;
-    if (kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR) {
-        const uint32_t enc = ((r + 1) << 1) | (kind == ROW_OPEN_OBJ ? 1u : 0u);
-#pragma unroll
-        for (int k = 0; k < ST_DEPTHS; k++)
-            if (d == (uint32_t)k) st.v[k] = enc;
-    }
-}
-__device__ __forceinline__ uint32_t state_at(const OpenState &st, uint32_t d) {
-    uint32_t x = 0;
-#pragma unroll
-    for (int k = 0; k < ST_DEPTHS; k++)
-        if (d == (uint32_t)k) x = st.v[k];
-    return x;
-}
 constexpr int SR_THREADS = 256, SR_ITEMS = LN_ROWS_PER_BLOCK / SR_THREADS;
 
-__global__ void __launch_bounds__(SR_THREADS) lines_open_agg_kernel(const uint32_t *__restrict__ meta, uint32_t *__restrict__ agg, ParseResult *res) {
-    __shared__ uint32_t s_w[SR_THREADS / 32][ST_DEPTHS];
-    const uint32_t n_rows = res->n_rows, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (res->fast_reject || blockIdx.x * LN_ROWS_PER_BLOCK >= n_rows) return;
-    const uint32_t base = blockIdx.x * LN_ROWS_PER_BLOCK + threadIdx.x * SR_ITEMS;
-    OpenState st = {};
-#pragma unroll
-    for (int j = 0; j < SR_ITEMS; j++)
-        if (base + j < n_rows) state_note(st, __ldg(meta + base + j), base + j);
-#pragma unroll
-    for (int k = 0; k < ST_DEPTHS; k++) {
-#pragma unroll
-        for (int o = 16; o; o >>= 1) st.v[k] = max(st.v[k], __shfl_xor_sync(FULL, st.v[k], o));
-        if (lane == 0) s_w[warp][k] = st.v[k];
-    }
-    __syncthreads();
-    if (threadIdx.x < ST_DEPTHS) {
-        uint32_t x = 0;
-        for (int w = 0; w < SR_THREADS / 32; w++) x = max(x, s_w[w][threadIdx.x]);
-        agg[blockIdx.x * ST_DEPTHS + threadIdx.x] = x;
-    }
-}
-
-// in place: agg[b][k] -> the last opening row at depth k in the blocks before b (a warp per depth)
-__global__ void __launch_bounds__(32 * ST_DEPTHS) lines_open_prefix_kernel(uint32_t *agg, ParseResult *res) {
+// in place: agg[b][k] -> the last opening row at depth k in the blocks before b.  One block: thread
+// (c, k) folds depth k over the c-th of 128 runs of blocks -- its loads are independent of each
+// other, so one memory round trip for all of them --, a warp per depth scans the 128 run totals.
+constexpr int OP_RUNS = 128;
+__global__ void __launch_bounds__(OP_RUNS * ST_DEPTHS) lines_open_prefix_kernel(uint32_t *agg, ParseResult *res) {
+    __shared__ uint32_t s_top[ST_DEPTHS][OP_RUNS];
     const uint32_t n_blocks = (res->n_rows + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK;
     if (res->fast_reject) return;
-    const uint32_t lane = threadIdx.x & 31, k = threadIdx.x >> 5;
-    uint32_t run = 0;
-    for (uint32_t base = 0; base < n_blocks; base += 32) {
-        const uint32_t b = base + lane;
-        const uint32_t mine = b < n_blocks ? agg[b * ST_DEPTHS + k] : 0u;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, k = threadIdx.x % ST_DEPTHS, c = threadIdx.x / ST_DEPTHS;
+    const uint32_t per = (n_blocks + OP_RUNS - 1) / OP_RUNS, b0 = min(c * per, n_blocks), b1 = min(b0 + per, n_blocks);
+    uint32_t top = 0;
+#pragma unroll 4
+    for (uint32_t b = b0; b < b1; b++) top = max(top, agg[b * ST_DEPTHS + k]);
+    s_top[k][c] = top;
+    __syncthreads();
+    if (warp < ST_DEPTHS) {
+        constexpr int PER_LANE = OP_RUNS / 32;
+        uint32_t v[PER_LANE], mine = 0;
+#pragma unroll
+        for (int j = 0; j < PER_LANE; j++) { v[j] = s_top[warp][lane * PER_LANE + j]; mine = max(mine, v[j]); }
         uint32_t incl = mine;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t y = __shfl_up_sync(FULL, incl, o);
             if (lane >= (uint32_t)o) incl = max(incl, y);
         }
-        uint32_t excl = __shfl_up_sync(FULL, incl, 1);
-        if (lane == 0) excl = 0;
-        if (b < n_blocks) agg[b * ST_DEPTHS + k] = max(run, excl);
-        run = max(run, __shfl_sync(FULL, incl, 31));
+        uint32_t x = __shfl_up_sync(FULL, incl, 1);
+        if (lane == 0) x = 0;
+#pragma unroll
+        for (int j = 0; j < PER_LANE; j++) { s_top[warp][lane * PER_LANE + j] = x; x = max(x, v[j]); }
+    }
+    __syncthreads();
+    uint32_t x = s_top[k][c];
+#pragma unroll 4
+    for (uint32_t b = b0; b < b1; b++) {
+        const uint32_t v = agg[b * ST_DEPTHS + k];
+        agg[b * ST_DEPTHS + k] = x;
+        x = max(x, v);
     }
 }
 
+// The block's 1,024 rows as bit masks: for every depth the rows that open a container there (a
+// word per 32 rows, made by four ballots), and which of those words are non-zero.  "The last
+// opener at depth k before row r" is then two count-leading-zeros away, or the block's prefix.
 __global__ void __launch_bounds__(SR_THREADS) lines_resolve_kernel(const uint8_t *__restrict__ raw, RowBuffers rb, const uint32_t *__restrict__ prefix,
                                                                   ParseResult *res) {
-    __shared__ uint32_t s_w[SR_THREADS / 32][ST_DEPTHS];
+    constexpr int WORDS = LN_ROWS_PER_BLOCK / 32;
+    static_assert(WORDS == 32 && SR_THREADS / 32 == ST_DEPTHS, "a warp per depth folds the 32 words of that depth");
+    __shared__ uint32_t s_open[ST_DEPTHS][WORDS], s_obj[WORDS], s_nz[ST_DEPTHS], s_before[ST_DEPTHS], s_meta[LN_ROWS_PER_BLOCK], s_jobs;
+    __shared__ uint2 s_job[LN_ROWS_PER_BLOCK / 2];   // (a job needs a closing row before it)
     const uint32_t n_rows = res->n_rows, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (res->fast_reject || blockIdx.x * LN_ROWS_PER_BLOCK >= n_rows) return;
-    const uint32_t base = blockIdx.x * LN_ROWS_PER_BLOCK + threadIdx.x * SR_ITEMS;
+    const uint32_t block0 = blockIdx.x * LN_ROWS_PER_BLOCK;
     uint32_t meta[SR_ITEMS];
-    OpenState mine = {};
 #pragma unroll
-    for (int j = 0; j < SR_ITEMS; j++) {
-        meta[j] = base + j < n_rows ? __ldg(rb.meta + base + j) : 0xffffffffu;
-        if (base + j < n_rows) state_note(mine, meta[j], base + j);
+    for (int j = 0; j < SR_ITEMS; j++) {   // rows j * 256 + thread: a warp's 32 rows are one word of the masks
+        const uint32_t rl = j * SR_THREADS + threadIdx.x, r = block0 + rl;
+        meta[j] = r < n_rows ? __ldg(rb.meta + r) : 0xffffffffu;
+        s_meta[rl] = meta[j];
+        const uint32_t kind = meta[j] & 15u, d = meta[j] >> META_DEPTH_SHIFT;
+        const bool opens = r < n_rows && (kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR) && d <= LINES_MAX_DEPTH;
+        const uint32_t op = __ballot_sync(FULL, opens), b0 = __ballot_sync(FULL, d & 1u), b1 = __ballot_sync(FULL, d & 2u),
+                       b2 = __ballot_sync(FULL, d & 4u), ob = __ballot_sync(FULL, kind == ROW_OPEN_OBJ);
+        if (lane < ST_DEPTHS)
+            s_open[lane][j * (SR_THREADS / 32) + warp] = op & (lane & 1u ? b0 : ~b0) & (lane & 2u ? b1 : ~b1) & (lane & 4u ? b2 : ~b2);
+        if (lane == ST_DEPTHS) s_obj[j * (SR_THREADS / 32) + warp] = ob;
     }
-    // the state before this thread's first row: blocks before (prefix), warps before, lanes before
-    OpenState st;
-#pragma unroll
-    for (int k = 0; k < ST_DEPTHS; k++) {
-        uint32_t incl = mine.v[k];
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t y = __shfl_up_sync(FULL, incl, o);
-            if (lane >= (uint32_t)o) incl = max(incl, y);
-        }
-        if (lane == 31) s_w[warp][k] = incl;
-        uint32_t excl = __shfl_up_sync(FULL, incl, 1);
-        if (lane == 0) excl = 0;
-        st.v[k] = excl;
+    if (threadIdx.x < ST_DEPTHS) s_before[threadIdx.x] = __ldg(prefix + blockIdx.x * ST_DEPTHS + threadIdx.x);
+    if (threadIdx.x == 0) s_jobs = 0;
+    __syncthreads();
+    {
+        const uint32_t nz = __ballot_sync(FULL, s_open[warp][lane] != 0);
+        if (lane == 0) s_nz[warp] = nz;
     }
     __syncthreads();
-#pragma unroll
-    for (int k = 0; k < ST_DEPTHS; k++) {
-        uint32_t x = __ldg(prefix + blockIdx.x * ST_DEPTHS + k);
-        for (uint32_t w = 0; w < warp; w++) x = max(x, s_w[w][k]);
-        st.v[k] = max(st.v[k], x);
-    }
+    // (row + 1) << 1 | is-an-object of the last opener at depth k before local row rl; 0: none
+    auto state_at = [&](uint32_t k, uint32_t rl) -> uint32_t {
+        uint32_t w = rl >> 5, m = s_open[k][w] & ((1u << (rl & 31u)) - 1u);
+        if (!m) {
+            const uint32_t nz = s_nz[k] & ((1u << w) - 1u);
+            if (!nz) return s_before[k];
+            w = 31u - (uint32_t)__clz((int)nz);
+            m = s_open[k][w];
+        }
+        const uint32_t at = 31u - (uint32_t)__clz((int)m);
+        return ((block0 + w * 32u + at + 1u) << 1) | ((s_obj[w] >> at) & 1u);
+    };
+    auto s_meta_of = [&](uint32_t row) -> uint32_t { return row >= block0 ? s_meta[row - block0] : __ldg(rb.meta + row); };
     const uint32_t module_row = res->module_row;   // 1 + row, 0: none (stage 1 has finished)
     bool ok = true;
-    uint32_t prev_meta = base > 0 && base < n_rows ? __ldg(rb.meta + base - 1) : 0xffffffffu;
 #pragma unroll
     for (int j = 0; j < SR_ITEMS; j++) {
-        const uint32_t r = base + j;
+        const uint32_t rl = j * SR_THREADS + threadIdx.x, r = block0 + rl;
         if (r >= n_rows) break;
         const uint32_t m = meta[j], kind = m & 15u, d = m >> META_DEPTH_SHIFT;
-        if (kind == ROW_CLOSE_OBJ || kind == ROW_CLOSE_ARR) {
+        const bool closes = kind == ROW_CLOSE_OBJ || kind == ROW_CLOSE_ARR;
+        // one look-up for every row: a closer wants its opener (same depth), a value its container (one up)
+        const uint32_t dq = closes ? d : d - 1u;
+        const uint32_t o = dq <= LINES_MAX_DEPTH ? state_at(dq, rl) : 0u;
+        if (closes) {
             // the container it closes opened at the same depth, and was of the same kind
-            const uint32_t o = d <= LINES_MAX_DEPTH ? state_at(st, d) : 0u;
-            if (o == 0 || (o & 1u) != (kind == ROW_CLOSE_OBJ ? 1u : 0u)) { ok = false; }
+            if (o == 0 || (o & 1u) != (kind == ROW_CLOSE_OBJ ? 1u : 0u)) ok = false;
             else {
                 const uint32_t orow = (o >> 1) - 1;
                 rb.koff[r] = orow;        // (TapeView::rows_direct: rows, not bracket numbers)
                 rb.voff[orow] = r;
                 if (module_row && orow == module_row - 1) res->module_end = r;
-            }
-        } else {
-            // a value: at the top there is exactly one; inside an object it has a key, inside an array none
-            if (d == 0) { if (r != 0) ok = false; }
-            else {
-                const uint32_t c = d - 1 <= LINES_MAX_DEPTH ? state_at(st, d - 1) : 0u;
-                if (c == 0 || ((c & 1u) != 0) != ((m & META_HAS_KEY) != 0)) ok = false;
-            }
-            // key order across a container that has just closed: the member before this one is the
-            // one that opened at this depth last
-            const uint32_t pk = prev_meta & 15u;
-            if (ok && (m & META_HAS_KEY) && r > 0 && (pk == ROW_CLOSE_OBJ || pk == ROW_CLOSE_ARR) && (prev_meta >> META_DEPTH_SHIFT) == d) {
-                const uint32_t o = d <= LINES_MAX_DEPTH ? state_at(st, d) : 0u;
-                if (o == 0) ok = false;
-                else {
-                    const uint32_t orow = (o >> 1) - 1;
-                    const uint32_t ao = __ldg(rb.koff + orow), al = __ldg(rb.klen + orow), bo = __ldg(rb.koff + r), bl = __ldg(rb.klen + r);
-                    if (!(__ldg(rb.meta + orow) & META_HAS_KEY) || !key_less(GlobalText{raw}, ao, al, bo, bl)) ok = false;
+                // key order across the container that has just closed: if the next row is a member of the same
+                // object, the member before it is the one that opened here.  About one row in fourteen at
+                // config #4: listed, and compared below by neighbouring threads
+                const uint32_t nm = rl + 1 < (uint32_t)LN_ROWS_PER_BLOCK ? s_meta[rl + 1] : (r + 1 < n_rows ? __ldg(rb.meta + r + 1) : 0xffffffffu);
+                const uint32_t nk = nm & 15u;
+                if (nm != 0xffffffffu && nk != ROW_CLOSE_OBJ && nk != ROW_CLOSE_ARR && (nm & META_HAS_KEY) && (nm >> META_DEPTH_SHIFT) == d) {
+                    const uint32_t at = atomicAdd(&s_jobs, 1u);
+                    s_job[at] = make_uint2(r + 1, orow);
                 }
             }
-            state_note(st, m, r);
+        } else if (d == 0) {
+            if (r != 0) ok = false;       // at the top there is exactly one value
+        } else if (o == 0 || ((o & 1u) != 0) != ((m & META_HAS_KEY) != 0)) {
+            ok = false;                   // inside an object a value has a key, inside an array none
         }
-        prev_meta = m;
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < s_jobs; i += SR_THREADS) {
+        const uint32_t r = s_job[i].x, orow = s_job[i].y;
+        const uint32_t ao = __ldg(rb.koff + orow), al = __ldg(rb.klen + orow), bo = __ldg(rb.koff + r), bl = __ldg(rb.klen + r);
+        if (!(s_meta_of(orow) & META_HAS_KEY) || !key_less(GlobalText{raw}, ao, al, bo, bl)) ok = false;
     }
     if (!ok) res->fast_reject = 1;
 }
 
 }  // namespace
 
-cudaError_t launch_lines_count(const uint8_t *raw, size_t n, uint32_t *scratch, ParseResult *res, cudaStream_t s) {
+cudaError_t launch_lines_count(const uint8_t *raw, size_t n, uint32_t *scratch, uint32_t *open_state, uint32_t row_cap, ParseResult *res,
+                               cudaStream_t s) {
     const uint32_t tiles = lines_tiles(n);
     cudaError_t e = cudaMemsetAsync(res, 0, sizeof(ParseResult), s);
     if (e != cudaSuccess) return e;
-    lines_count_kernel<<<tiles, LN_THREADS, 0, s>>>(raw, (u64)n, scratch, scratch + tiles);
-    lines_prefix_kernel<<<1, 1024, 0, s>>>(scratch, tiles, res);
+    lines_count_kernel<<<tiles, LN_THREADS, 0, s>>>(raw, (u64)n, scratch, scratch + tiles, open_state, lines_row_blocks(row_cap) * (LINES_MAX_DEPTH + 1));
+    lines_prefix_kernel<<<1, 1024, 0, s>>>(scratch, scratch + tiles, tiles, (u64)n, res);
     count_parse_launch(); count_parse_launch();
     return cudaGetLastError();
 }
@@ -821,10 +842,9 @@ cudaError_t launch_lines_rows(const uint8_t *raw, size_t n, const uint32_t *scra
 cudaError_t launch_lines_structure(const uint8_t *raw, RowBuffers rb, uint32_t row_cap, uint32_t *open_state, ParseResult *res, cudaStream_t s) {
     const uint32_t blocks = lines_row_blocks(row_cap);
     if (!blocks) return cudaSuccess;
-    lines_open_agg_kernel<<<blocks, SR_THREADS, 0, s>>>(rb.meta, open_state, res);
-    lines_open_prefix_kernel<<<1, 32 * ST_DEPTHS, 0, s>>>(open_state, res);
+    lines_open_prefix_kernel<<<1, OP_RUNS * ST_DEPTHS, 0, s>>>(open_state, res);
     lines_resolve_kernel<<<blocks, SR_THREADS, 0, s>>>(raw, rb, open_state, res);
-    count_parse_launch(); count_parse_launch(); count_parse_launch();
+    count_parse_launch(); count_parse_launch();
     return cudaGetLastError();
 }
 

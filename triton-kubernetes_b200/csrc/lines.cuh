@@ -35,13 +35,15 @@ constexpr int LN_ROWS_PER_BLOCK = 1024;   // rows per block of the structure pas
 inline uint32_t lines_row_blocks(uint32_t rows) { return (rows + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK; }
 
 // raw: the text at the start of the arena, space padded to a whole tile and 64 bytes more.
-// Stage 0: line ends counted per tile, folded (res->n_rows known on the device afterwards).
-cudaError_t launch_lines_count(const uint8_t *raw, size_t n, uint32_t *scratch, ParseResult *res, cudaStream_t s);
-// Stage 1: one row per line into rb (capacity row_cap rows; more lines than that: fast_reject).
+// Stage 0: line ends counted per tile, folded (res->n_rows known on the device afterwards);
+// open_state (8 words per block of LN_ROWS_PER_BLOCK rows, row_cap rows at most) cleared.
+cudaError_t launch_lines_count(const uint8_t *raw, size_t n, uint32_t *scratch, uint32_t *open_state, uint32_t row_cap, ParseResult *res,
+                               cudaStream_t s);
+// Stage 1: one row per line into rb (capacity row_cap rows; more lines than that: fast_reject);
+// rb.open = open_state, where every opening row leaves its mark.
 cudaError_t launch_lines_rows(const uint8_t *raw, size_t n, const uint32_t *scratch, RowBuffers rb, uint32_t row_cap, ParseResult *res,
                               cudaStream_t s);
-// Stage 2: closers paired with openers, containers checked.  open_state: 8 words per block of
-// LN_ROWS_PER_BLOCK rows (row_cap rows at most).
+// Stage 2: closers paired with openers, containers checked.
 cudaError_t launch_lines_structure(const uint8_t *raw, RowBuffers rb, uint32_t row_cap, uint32_t *open_state, ParseResult *res, cudaStream_t s);
 
 }  // namespace tk

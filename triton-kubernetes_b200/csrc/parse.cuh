@@ -137,7 +137,7 @@ cudaError_t launch_decode_lengths(const uint8_t *raw, TokenBuffers tb, DecodeBuf
 cudaError_t launch_decode_write(uint8_t *arena, uint32_t side_base, TokenBuffers tb, DecodeBuffers db, uint32_t n_dec,
                                 cudaStream_t s);
 // rows: the tape arrays are written in input order; arena = raw text (+ side arena)
-struct RowBuffers { uint32_t *meta, *koff, *klen, *voff, *vlen; };
+struct RowBuffers { uint32_t *meta, *koff, *klen, *voff, *vlen; uint32_t *open = nullptr; };   // open: lines.cu only
 cudaError_t launch_rows(const uint8_t *raw, size_t n, TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles,
                         BracketBuffers bb, DecodeBuffers db, uint32_t n_dec, RowBuffers rb, uint32_t n_rows,
                         ParseResult *res, cudaStream_t s);
