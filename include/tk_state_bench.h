@@ -25,6 +25,10 @@ TK_API int tk_state_prefix_count_device(tk_state *s, const char *prefix, size_t 
 TK_API int tk_state_timing(tk_state *s, int enable);
 /* Handles created after this call start with timing on (or off): lets state.New itself be timed. */
 TK_API int tk_set_default_timing(int enable);
+/* state.New for handles parsed after this call: 1 (default) tries the line-by-line pass for text in
+ * json.MarshalIndent form first, 0 sends everything through the general pipeline.  Both build the same
+ * tape and give the same verdict; the switch exists so that tests and measurements can run both. */
+TK_API int tk_set_line_pass(int enable);
 TK_API int tk_state_kernel_stats(tk_state *s, int kind, const char **name, double *ms,
                                  unsigned long long *timed_launches, unsigned long long *launches);
 /* Bytes this handle has copied host->device and device->host so far. */

@@ -726,3 +726,40 @@ def test_indented_form_long_lines_deep_nesting_and_dense_tiles(tk, oracle):
         assert _outcome(tk, raw) == _outcome(oracle, raw)
         s = tk.New("x", raw)
         assert not s.host_tree_built and s.Bytes() == raw
+
+
+def _full_outcome(tk, raw):
+    try:
+        s = tk.New("x", raw)
+        pairs = s.Clusters() if b'"module"' in raw[:40] else None
+        nodes = [s.Nodes(k) for _, k in sorted(pairs.items())[:3]] if pairs else None
+        return ("ok", s.host_tree_built, s.Bytes(), pairs, nodes)
+    except Exception as e:
+        return ("err", str(e))
+
+
+def test_line_pass_and_general_pipeline_give_the_same_result(tk, oracle):
+    """state.New has two parsers for text in the indented form (lines.cu first, parse.cu when that one
+    declines).  Every shape here goes through the library twice -- tk_set_line_pass(1), then (0) -- and
+    the verdict, the text, the pairs and where the document lives must not differ (and agree with the oracle)."""
+    rng = random.Random(4242)
+    base = _pretty(oracle, json.loads(synth.document(25, 8)))
+    texts = [base, _pretty(oracle, json.loads(synth.document(3, 2))), _pretty(oracle, {}), _pretty(oracle, []), _pretty(oracle, {"a": 1}),
+             b'{"module":{"b":{"name":"x"}}}', _pretty(oracle, {"module": {"a": {"name": "n" * 300, "hostname": "h" * 9000}}, "t": "t" * 20000})]
+    texts += [_pretty(oracle, rand_tree(rng, 5)) for _ in range(10)]
+    for old, new in NEAR_MISSES:
+        at = base.rfind(old)
+        if at >= 0:
+            texts.append(base[:at] + new + base[at + len(old):])
+    try:
+        for raw in texts:
+            tk.state.set_line_pass(True)
+            with_lines = _full_outcome(tk, raw)
+            tk.state.set_line_pass(False)
+            without = _full_outcome(tk, raw)
+            assert with_lines == without, raw[:60]
+            assert with_lines[0] == _outcome(oracle, raw)[0]
+            if with_lines[0] == "ok":
+                assert with_lines[2] == oracle.New("x", raw).Bytes()
+    finally:
+        tk.state.set_line_pass(True)

@@ -58,6 +58,7 @@ int tk_state_new_device(const char *name, size_t name_len, const void *dev_raw, 
     return new_from(name, name_len, static_cast<const char *>(dev_raw), raw_len, true, out);
 }
 int tk_set_default_timing(int enable) { set_default_timing(enable != 0); return TK_OK; }
+int tk_set_line_pass(int enable) { set_line_pass(enable != 0); return TK_OK; }
 
 static int new_from(const char *name, size_t name_len, const char *raw, size_t raw_len, bool on_device, tk_state **out) {
     if (!out) return set_err(nullptr, TK_EARG, "tk_state_new: out is NULL");

@@ -123,6 +123,13 @@ struct Trace {
 
 static std::atomic<bool> g_default_timing{false};
 void set_default_timing(bool on) { g_default_timing = on; }
+static std::atomic<int> g_line_pass{-1};   // -1: not asked yet (TK_NO_FAST_PATH in the environment switches it off)
+void set_line_pass(bool on) { g_line_pass.store(on ? 1 : 0); }
+static bool line_pass_on() {
+    int v = g_line_pass.load();
+    if (v < 0) { v = getenv("TK_NO_FAST_PATH") ? 0 : 1; g_line_pass.store(v); }
+    return v != 0;
+}
 
 const char *kernel_name(int kind) {
     static const char *const names[K_COUNT] = {"row_offsets_kernel", "emit_kernel", "prefix_match_kernel", "scan_tokens_kernel (carry protocol)",
@@ -721,8 +728,7 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
 
     // ---- text that is already in the indented form (every file this library or the reference wrote):
     //      the line-by-line pass builds the tape; anything else it declines, and the general pipeline runs
-    static const bool no_fast_path = getenv("TK_NO_FAST_PATH") != nullptr;   // (development: compare the two)
-    if (!no_fast_path) {
+    if (line_pass_on()) {   // (tk_set_line_pass / TK_NO_FAST_PATH: the tests run every vector through both)
         bool accepted = false;
         int rc = parse_lines(n, out, &accepted, err);
         tr.mark("lines:done");

@@ -93,6 +93,7 @@ enum KernelKind {
     K_DECODE, K_ROWS, K_KEY_ORDER, K_MODULE_INDEX, K_FIELD_FIND, K_LINES_COUNT, K_LINES_ROWS, K_LINES_STRUCTURE, K_SCAN_COUNT, K_SCAN_PREFIX, K_SCAN_EMIT, K_COUNT
 };
 const char *kernel_name(int kind);
+void set_line_pass(bool on);       // state.New tries the line-by-line pass first (default) or goes straight to the general pipeline
 void set_default_timing(bool on);  // engines created from now on start with per-kernel timing on/off
 
 class Engine {

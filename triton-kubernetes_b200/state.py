@@ -28,7 +28,7 @@ SYMBOLS = [
     "tk_new_hostnames", "tk_state_stage", "tk_state_bytes_device", "tk_state_prefix_count_device",
     "tk_state_stream", "tk_kernel_launches", "tk_version", "tk_state_timing", "tk_state_kernel_stats",
     "tk_state_copy_stats", "tk_row_offsets_noalloc", "tk_state_host_tree_built", "tk_state_new_device",
-    "tk_set_default_timing", "tk_render_record", "tk_record_struct_name", "tk_module_source", "tk_record_table",
+    "tk_set_default_timing", "tk_set_line_pass", "tk_render_record", "tk_record_struct_name", "tk_module_source", "tk_record_table",
     "tk_local_backend_new", "tk_backend_free", "tk_backend_last_error", "tk_backend_state", "tk_backend_delete_state",
     "tk_backend_persist_state", "tk_backend_states", "tk_backend_state_terraform_config", "tk_set_device",
 ]
@@ -49,6 +49,7 @@ def lib():
     L.tk_state_new.argtypes = [c_char_p, c_size_t, c_char_p, c_size_t, POINTER(P)]
     L.tk_state_new_device.argtypes = [c_char_p, c_size_t, P, c_size_t, POINTER(P)]
     L.tk_set_default_timing.argtypes = [c_int]
+    L.tk_set_line_pass.argtypes = [c_int]
     L.tk_render_record.argtypes = [c_char_p, c_size_t, c_char_p, c_size_t, POINTER(P), POINTER(c_size_t)]
     L.tk_record_struct_name.argtypes = [c_char_p, c_char_p, POINTER(P), POINTER(c_size_t)]
     L.tk_module_source.argtypes = [c_char_p, c_char_p, c_char_p, c_char_p, POINTER(P), POINTER(c_size_t)]
@@ -332,6 +333,11 @@ def NewDevice(name, device_address, length) -> State:
 
 def set_default_timing(on: bool):
     lib().tk_set_default_timing(1 if on else 0)
+
+
+def set_line_pass(on: bool):
+    """tk_set_line_pass: state.New with (default) or without the line-by-line pass for indented text."""
+    lib().tk_set_line_pass(1 if on else 0)
 
 
 def set_device(device: int):
