@@ -500,17 +500,23 @@ def test_index_lists_that_outgrow_their_first_buffer(tk, oracle):
 
 
 def test_index_gives_way_to_the_host_tree_for_a_child_with_thousands_of_members(tk, oracle):
-    """The index pass finds the child a "name" member belongs to by walking up through at most 4,096
-    rows; a child with more members than that before its name sends Clusters()/Nodes() to the host
-    tree, with the same answers."""
+    """The index pass of the general pipeline finds the child a "name" member belongs to by walking up through
+    at most 4,096 rows; a child with more members than that before its name sends Clusters()/Nodes() to the
+    host tree, with the same answers.  (The line pass knows every row's container and has no such limit.)"""
     wide = {"k%05d" % i: "v" for i in range(6000)}
     wide["name"] = "wide"                                # sorts after every k....
     mod = {"cluster_a_b": {"name": "b"}, "cluster_a_wide": wide, "node_a_b_1": {"hostname": "h1", "x": {"name": "too deep"}, "y": [{"hostname": "in array"}]}}
     raw = oracle.New("x", json.dumps({"module": mod, "name": "at the root", "m2": {"cluster_a_q": {"name": "q"}}}).encode()).Bytes()
-    a, b = tk.New("x", raw), oracle.New("x", raw)
-    assert a.Clusters() == b.Clusters() == {b"b": b"cluster_a_b", b"wide": b"cluster_a_wide"}
-    assert a.Nodes("cluster_a_b") == b.Nodes("cluster_a_b") == {b"h1": b"node_a_b_1"}
-    assert a.host_tree_built
+    b = oracle.New("x", raw)
+    try:
+        for line_pass in (True, False):
+            tk.state.set_line_pass(line_pass)
+            a = tk.New("x", raw)
+            assert a.Clusters() == b.Clusters() == {b"b": b"cluster_a_b", b"wide": b"cluster_a_wide"}
+            assert a.Nodes("cluster_a_b") == b.Nodes("cluster_a_b") == {b"h1": b"node_a_b_1"}
+            assert a.host_tree_built == (not line_pass)
+    finally:
+        tk.state.set_line_pass(True)
     small = oracle.New("x", json.dumps({"module": {"cluster_a_b": {"name": "b"}, "node_a_b_1": {"hostname": "h1", "x": {"name": "too deep"},
                                                    "y": [{"hostname": "in array"}]}}, "name": "at the root"}).encode()).Bytes()
     c = tk.New("x", small)

@@ -667,23 +667,11 @@ int Engine::parse_lines(size_t n, ParseResult *out, bool *accepted, std::string 
     for (int i = 0; i < 5; i++)
         if ((e = rows[i]->reserve((row_cap + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(rows)", err);
     if ((e = d_scratch_.reserve(lines_scratch_words(n) * 4 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
-    if ((e = d_tiles_.reserve((size_t)lines_row_blocks((uint32_t)row_cap) * 8 * 4 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
+    if ((e = d_tiles_.reserve(lines_open_state_words((uint32_t)row_cap) * 4 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
     RowBuffers rb{d_meta_.as<uint32_t>(), d_koff_.as<uint32_t>(), d_klen_.as<uint32_t>(), d_voff_.as<uint32_t>(), d_vlen_.as<uint32_t>(),
                   d_tiles_.as<uint32_t>()};
     uint32_t *scratch = d_scratch_.as<uint32_t>();
-    if ((e = timed(K_LINES_COUNT, [&] { return launch_lines_count(raw, n, scratch, rb.open, (uint32_t)row_cap, d_res, stream_); })) != cudaSuccess)
-        return fail(e, "lines_count", err);
-    if ((e = timed(K_LINES_ROWS, [&] { return launch_lines_rows(raw, n, scratch, rb, (uint32_t)row_cap, d_res, stream_); })) != cudaSuccess)
-        return fail(e, "lines_rows", err);
-    if ((e = timed(K_LINES_STRUCTURE, [&] { return launch_lines_structure(raw, rb, (uint32_t)row_cap, d_tiles_.as<uint32_t>(), d_res, stream_); })) != cudaSuccess)
-        return fail(e, "lines_structure", err);
-    // module index lists, as after the general parse (the row count is still on the device: the grid covers the bound)
-    tape_.n_rows = (uint32_t)row_cap;
-    tape_.arena_bytes = (uint32_t)arena_used_;
-    tape_.text_len = (uint32_t)n;
-    tape_.rows_direct = true;
-    tape_.meta = rb.meta; tape_.koff = rb.koff; tape_.klen = rb.klen; tape_.voff = rb.voff; tape_.vlen = rb.vlen;
-    tape_.arena = raw;
+    // the module index's lists are made by the last stage (the row count is still on the device: sized by bounds)
     for (int f = 0; f < 2; f++) {
         const size_t cap = std::min<size_t>(row_cap, n / 256 + 1024);
         if ((e = d_frefs_[f].reserve(cap * sizeof(FieldRef))) != cudaSuccess || (e = d_foff_[f].reserve((cap + 1) * 4)) != cudaSuccess)
@@ -693,8 +681,19 @@ int Engine::parse_lines(size_t n, ParseResult *out, bool *accepted, std::string 
         fx_.cap[f] = (uint32_t)cap;
     }
     if ((e = d_find_status_.reserve(field_status_words((uint32_t)row_cap) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
-    fx_.status = d_find_status_.as<unsigned long long>();
-    if ((e = timed(K_FIELD_FIND, [&] { return launch_field_find(tape_, fx_, d_res, stream_); })) != cudaSuccess) return fail(e, "field_find", err);
+    fx_.status = d_find_status_.as<unsigned long long>();   // (for a second run of field_find with larger lists; the first is part of stage 2)
+    if ((e = timed(K_LINES_COUNT, [&] { return launch_lines_count(raw, n, scratch, rb.open, (uint32_t)row_cap, d_res, stream_); })) != cudaSuccess)
+        return fail(e, "lines_count", err);
+    if ((e = timed(K_LINES_ROWS, [&] { return launch_lines_rows(raw, n, scratch, rb, (uint32_t)row_cap, d_res, stream_); })) != cudaSuccess)
+        return fail(e, "lines_rows", err);
+    if ((e = timed(K_LINES_STRUCTURE, [&] { return launch_lines_structure(raw, rb, (uint32_t)row_cap, rb.open, fx_, d_res, stream_); })) != cudaSuccess)
+        return fail(e, "lines_structure", err);
+    tape_.n_rows = (uint32_t)row_cap;
+    tape_.arena_bytes = (uint32_t)arena_used_;
+    tape_.text_len = (uint32_t)n;
+    tape_.rows_direct = true;
+    tape_.meta = rb.meta; tape_.koff = rb.koff; tape_.klen = rb.klen; tape_.voff = rb.voff; tape_.vlen = rb.vlen;
+    tape_.arena = raw;
     int rc = fetch_result(err);
     if (rc) return rc;
     if (h_res_.p->fast_reject || h_res_.p->n_rows == 0 || h_res_.p->n_rows > row_cap) return TK_OK;

@@ -11,6 +11,7 @@
 #include <atomic>
 
 #include "bulkcopy.cuh"
+#include "index.cuh"
 
 namespace tk {
 namespace {
@@ -679,7 +680,10 @@ constexpr int OP_RUNS = 128;
 __global__ void __launch_bounds__(OP_RUNS * ST_DEPTHS) lines_open_prefix_kernel(uint32_t *agg, ParseResult *res) {
     __shared__ uint32_t s_top[ST_DEPTHS][OP_RUNS];
     const uint32_t n_blocks = (res->n_rows + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK;
-    if (res->fast_reject) return;
+    if (res->fast_reject) {   // what the blocks of the next launch go by (they set fast_reject themselves)
+        if (threadIdx.x == 0) res->reject_early = 1;
+        return;
+    }
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, k = threadIdx.x % ST_DEPTHS, c = threadIdx.x / ST_DEPTHS;
     const uint32_t per = (n_blocks + OP_RUNS - 1) / OP_RUNS, b0 = min(c * per, n_blocks), b1 = min(b0 + per, n_blocks);
     uint32_t top = 0;
@@ -716,92 +720,219 @@ __global__ void __launch_bounds__(OP_RUNS * ST_DEPTHS) lines_open_prefix_kernel(
 // The block's 1,024 rows as bit masks: for every depth the rows that open a container there (a
 // word per 32 rows, made by four ballots), and which of those words are non-zero.  "The last
 // opener at depth k before row r" is then two count-leading-zeros away, or the block's prefix.
+//
+// The module index's field lists (index.cuh) are made here as well, since every row has just been told
+// its container: a "name" / "hostname" string three levels down (marked by stage 1) whose container is
+// an object whose container is the root's "module".  Per block the hits are listed in row order (ballots
+// again), sized, and placed in the lists by a decoupled look-back over the blocks -- which therefore take
+// their number from a ticket counter, so that a block only ever waits for blocks that have started.
+__device__ __forceinline__ u64 ld_relaxed_u64(const u64 *p) {
+    u64 v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(u64 *p, u64 v) { asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+constexpr int FL_CAP = LN_ROWS_PER_BLOCK / 2;   // a hit needs the row of its own child as well: at most 512 per field and block
 __global__ void __launch_bounds__(SR_THREADS) lines_resolve_kernel(const uint8_t *__restrict__ raw, RowBuffers rb, const uint32_t *__restrict__ prefix,
-                                                                  ParseResult *res) {
+                                                                  FieldIndexBuffers fx, ParseResult *res) {
     constexpr int WORDS = LN_ROWS_PER_BLOCK / 32;
     static_assert(WORDS == 32 && SR_THREADS / 32 == ST_DEPTHS, "a warp per depth folds the 32 words of that depth");
     __shared__ uint32_t s_open[ST_DEPTHS][WORDS], s_obj[WORDS], s_nz[ST_DEPTHS], s_before[ST_DEPTHS], s_meta[LN_ROWS_PER_BLOCK], s_jobs;
     __shared__ uint2 s_job[LN_ROWS_PER_BLOCK / 2];   // (a job needs a closing row before it)
+    __shared__ uint32_t s_block, s_fmask[2][WORDS], s_fpre[2][WORDS], s_fcnt[2];
+    __shared__ uint16_t s_frow[2][FL_CAP];            // the block's hits per field, in row order: the row (local), ...
+    __shared__ uint32_t s_fchild[2][FL_CAP], s_fpos[2][FL_CAP];   // ... its child's row, the bytes of the records before it in the block
+    __shared__ u64 s_fbase[2];                        // records before the block | record bytes before it << 32
     const uint32_t n_rows = res->n_rows, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (res->fast_reject || blockIdx.x * LN_ROWS_PER_BLOCK >= n_rows) return;
-    const uint32_t block0 = blockIdx.x * LN_ROWS_PER_BLOCK;
-    uint32_t meta[SR_ITEMS];
-#pragma unroll
-    for (int j = 0; j < SR_ITEMS; j++) {   // rows j * 256 + thread: a warp's 32 rows are one word of the masks
-        const uint32_t rl = j * SR_THREADS + threadIdx.x, r = block0 + rl;
-        meta[j] = r < n_rows ? __ldg(rb.meta + r) : 0xffffffffu;
-        s_meta[rl] = meta[j];
-        const uint32_t kind = meta[j] & 15u, d = meta[j] >> META_DEPTH_SHIFT;
-        const bool opens = r < n_rows && (kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR) && d <= LINES_MAX_DEPTH;
-        const uint32_t op = __ballot_sync(FULL, opens), b0 = __ballot_sync(FULL, d & 1u), b1 = __ballot_sync(FULL, d & 2u),
-                       b2 = __ballot_sync(FULL, d & 4u), ob = __ballot_sync(FULL, kind == ROW_OPEN_OBJ);
-        if (lane < ST_DEPTHS)
-            s_open[lane][j * (SR_THREADS / 32) + warp] = op & (lane & 1u ? b0 : ~b0) & (lane & 2u ? b1 : ~b1) & (lane & 4u ? b2 : ~b2);
-        if (lane == ST_DEPTHS) s_obj[j * (SR_THREADS / 32) + warp] = ob;
-    }
-    if (threadIdx.x < ST_DEPTHS) s_before[threadIdx.x] = __ldg(prefix + blockIdx.x * ST_DEPTHS + threadIdx.x);
-    if (threadIdx.x == 0) s_jobs = 0;
-    __syncthreads();
-    {
-        const uint32_t nz = __ballot_sync(FULL, s_open[warp][lane] != 0);
-        if (lane == 0) s_nz[warp] = nz;
-    }
-    __syncthreads();
-    // (row + 1) << 1 | is-an-object of the last opener at depth k before local row rl; 0: none
-    auto state_at = [&](uint32_t k, uint32_t rl) -> uint32_t {
-        uint32_t w = rl >> 5, m = s_open[k][w] & ((1u << (rl & 31u)) - 1u);
-        if (!m) {
-            const uint32_t nz = s_nz[k] & ((1u << w) - 1u);
-            if (!nz) return s_before[k];
-            w = 31u - (uint32_t)__clz((int)nz);
-            m = s_open[k][w];
-        }
-        const uint32_t at = 31u - (uint32_t)__clz((int)m);
-        return ((block0 + w * 32u + at + 1u) << 1) | ((s_obj[w] >> at) & 1u);
-    };
-    auto s_meta_of = [&](uint32_t row) -> uint32_t { return row >= block0 ? s_meta[row - block0] : __ldg(rb.meta + row); };
-    const uint32_t module_row = res->module_row;   // 1 + row, 0: none (stage 1 has finished)
+    const uint32_t n_blocks = (n_rows + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK;
+    // (reject_early, not fast_reject: that one may be set by a block of this very launch, and a block that left
+    //  because of it would be waited for by its successors for ever)
+    if (res->reject_early) return;
     bool ok = true;
+    // Persistent blocks: as many as fit on the device at once, each taking the next 1,024 rows from the ticket
+    // counter until none are left (measured the same as one short-lived block per 1,024 rows; kept because a
+    // block then only ever waits for tickets that running blocks hold).
+    for (;;) {
+        __syncthreads();   // (the lists in shared memory are written again)
+        if (threadIdx.x == 0) s_block = (uint32_t)atomicAdd(fx.status, 1ull);
+        __syncthreads();
+        const uint32_t block = s_block;
+        if (block >= n_blocks) break;
+        const uint32_t block0 = block * LN_ROWS_PER_BLOCK;
+        uint32_t meta[SR_ITEMS];
 #pragma unroll
-    for (int j = 0; j < SR_ITEMS; j++) {
-        const uint32_t rl = j * SR_THREADS + threadIdx.x, r = block0 + rl;
-        if (r >= n_rows) break;
-        const uint32_t m = meta[j], kind = m & 15u, d = m >> META_DEPTH_SHIFT;
-        const bool closes = kind == ROW_CLOSE_OBJ || kind == ROW_CLOSE_ARR;
-        // one look-up for every row: a closer wants its opener (same depth), a value its container (one up)
-        const uint32_t dq = closes ? d : d - 1u;
-        const uint32_t o = dq <= LINES_MAX_DEPTH ? state_at(dq, rl) : 0u;
-        if (closes) {
-            // the container it closes opened at the same depth, and was of the same kind
-            if (o == 0 || (o & 1u) != (kind == ROW_CLOSE_OBJ ? 1u : 0u)) ok = false;
-            else {
-                const uint32_t orow = (o >> 1) - 1;
-                rb.koff[r] = orow;        // (TapeView::rows_direct: rows, not bracket numbers)
-                rb.voff[orow] = r;
-                if (module_row && orow == module_row - 1) res->module_end = r;
-                // key order across the container that has just closed: if the next row is a member of the same
-                // object, the member before it is the one that opened here.  About one row in fourteen at
-                // config #4: listed, and compared below by neighbouring threads
-                const uint32_t nm = rl + 1 < (uint32_t)LN_ROWS_PER_BLOCK ? s_meta[rl + 1] : (r + 1 < n_rows ? __ldg(rb.meta + r + 1) : 0xffffffffu);
-                const uint32_t nk = nm & 15u;
-                if (nm != 0xffffffffu && nk != ROW_CLOSE_OBJ && nk != ROW_CLOSE_ARR && (nm & META_HAS_KEY) && (nm >> META_DEPTH_SHIFT) == d) {
-                    const uint32_t at = atomicAdd(&s_jobs, 1u);
-                    s_job[at] = make_uint2(r + 1, orow);
+        for (int j = 0; j < SR_ITEMS; j++) {   // rows j * 256 + thread: a warp's 32 rows are one word of the masks
+            const uint32_t rl = j * SR_THREADS + threadIdx.x, r = block0 + rl;
+            meta[j] = r < n_rows ? __ldg(rb.meta + r) : 0xffffffffu;
+            s_meta[rl] = meta[j];
+            const uint32_t kind = meta[j] & 15u, d = meta[j] >> META_DEPTH_SHIFT;
+            const bool opens = r < n_rows && (kind == ROW_OPEN_OBJ || kind == ROW_OPEN_ARR) && d <= LINES_MAX_DEPTH;
+            const uint32_t op = __ballot_sync(FULL, opens), b0 = __ballot_sync(FULL, d & 1u), b1 = __ballot_sync(FULL, d & 2u),
+                           b2 = __ballot_sync(FULL, d & 4u), ob = __ballot_sync(FULL, kind == ROW_OPEN_OBJ);
+            if (lane < ST_DEPTHS)
+                s_open[lane][j * (SR_THREADS / 32) + warp] = op & (lane & 1u ? b0 : ~b0) & (lane & 2u ? b1 : ~b1) & (lane & 4u ? b2 : ~b2);
+            if (lane == ST_DEPTHS) s_obj[j * (SR_THREADS / 32) + warp] = ob;
+        }
+        if (threadIdx.x < ST_DEPTHS) s_before[threadIdx.x] = __ldg(prefix + block * ST_DEPTHS + threadIdx.x);
+        if (threadIdx.x == 0) s_jobs = 0;
+        __syncthreads();
+        {
+            const uint32_t nz = __ballot_sync(FULL, s_open[warp][lane] != 0);
+            if (lane == 0) s_nz[warp] = nz;
+        }
+        __syncthreads();
+        // (row + 1) << 1 | is-an-object of the last opener at depth k before local row rl; 0: none
+        auto state_at = [&](uint32_t k, uint32_t rl) -> uint32_t {
+            uint32_t w = rl >> 5, m = s_open[k][w] & ((1u << (rl & 31u)) - 1u);
+            if (!m) {
+                const uint32_t nz = s_nz[k] & ((1u << w) - 1u);
+                if (!nz) return s_before[k];
+                w = 31u - (uint32_t)__clz((int)nz);
+                m = s_open[k][w];
+            }
+            const uint32_t at = 31u - (uint32_t)__clz((int)m);
+            return ((block0 + w * 32u + at + 1u) << 1) | ((s_obj[w] >> at) & 1u);
+        };
+        auto s_meta_of = [&](uint32_t row) -> uint32_t { return row >= block0 ? s_meta[row - block0] : __ldg(rb.meta + row); };
+        const uint32_t module_row = res->module_row;   // 1 + row, 0: none (stage 1 has finished)
+        // "module" as the index wants it: an object member of a root object; as a container: (row + 1) << 1 | 1
+        const uint32_t module_enc = res->root_kind == ROW_OPEN_OBJ && module_row != 0 && res->module_kind == ROW_OPEN_OBJ ? (module_row << 1) | 1u : 0u;
+        uint32_t hit[SR_ITEMS];   // child row << 2 | field (0 "name", 1 "hostname", 2 none)
+#pragma unroll
+        for (int j = 0; j < SR_ITEMS; j++) {
+            const uint32_t rl = j * SR_THREADS + threadIdx.x, r = block0 + rl;
+            const bool valid = r < n_rows;
+            const uint32_t m = meta[j], kind = m & 15u, d = m >> META_DEPTH_SHIFT;
+            const bool closes = kind == ROW_CLOSE_OBJ || kind == ROW_CLOSE_ARR;
+            // one look-up for every row: a closer wants its opener (same depth), a value its container (one up)
+            const uint32_t dq = closes ? d : d - 1u;
+            const uint32_t o = valid && dq <= LINES_MAX_DEPTH ? state_at(dq, rl) : 0u;
+            hit[j] = 2u;
+            if (!valid) {
+            } else if (closes) {
+                // the container it closes opened at the same depth, and was of the same kind
+                if (o == 0 || (o & 1u) != (kind == ROW_CLOSE_OBJ ? 1u : 0u)) ok = false;
+                else {
+                    const uint32_t orow = (o >> 1) - 1;
+                    rb.koff[r] = orow;        // (TapeView::rows_direct: rows, not bracket numbers)
+                    rb.voff[orow] = r;
+                    if (module_row && orow == module_row - 1) res->module_end = r;
+                    // key order across the container that has just closed: if the next row is a member of the same
+                    // object, the member before it is the one that opened here.  About one row in fourteen at
+                    // config #4: listed, and compared below by neighbouring threads
+                    const uint32_t nm = rl + 1 < (uint32_t)LN_ROWS_PER_BLOCK ? s_meta[rl + 1] : (r + 1 < n_rows ? __ldg(rb.meta + r + 1) : 0xffffffffu);
+                    const uint32_t nk = nm & 15u;
+                    if (nm != 0xffffffffu && nk != ROW_CLOSE_OBJ && nk != ROW_CLOSE_ARR && (nm & META_HAS_KEY) && (nm >> META_DEPTH_SHIFT) == d) {
+                        const uint32_t at = atomicAdd(&s_jobs, 1u);
+                        s_job[at] = make_uint2(r + 1, orow);
+                    }
+                }
+            } else if (d == 0) {
+                if (r != 0) ok = false;       // at the top there is exactly one value
+            } else if (o == 0 || ((o & 1u) != 0) != ((m & META_HAS_KEY) != 0)) {
+                ok = false;                   // inside an object a value has a key, inside an array none
+            } else if ((m & (META_KEY_IS_NAME | META_KEY_IS_HOSTNAME)) && d == 3 && (o & 1u) && module_enc && state_at(1, rl) == module_enc) {
+                hit[j] = (((o >> 1) - 1) << 2) | ((m & META_KEY_IS_HOSTNAME) ? 1u : 0u);
+            }
+            const uint32_t h0 = __ballot_sync(FULL, (hit[j] & 3u) == 0u), h1 = __ballot_sync(FULL, (hit[j] & 3u) == 1u);
+            if (lane == 0) { s_fmask[0][j * (SR_THREADS / 32) + warp] = h0; s_fmask[1][j * (SR_THREADS / 32) + warp] = h1; }
+        }
+        __syncthreads();
+
+        // ---- the module index's lists
+        if (warp < 2) {   // hits before every 32-row word, per field
+            const uint32_t c = (uint32_t)__popc(s_fmask[warp][lane]);
+            uint32_t incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(FULL, incl, o);
+                if (lane >= (uint32_t)o) incl += y;
+            }
+            s_fpre[warp][lane] = incl - c;
+            if (lane == 31) s_fcnt[warp] = incl;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < SR_ITEMS; j++) {
+            const uint32_t f = hit[j] & 3u;
+            if (f == 2u) continue;
+            const uint32_t w = j * (SR_THREADS / 32) + warp, at = s_fpre[f][w] + (uint32_t)__popc(s_fmask[f][w] & ((1u << lane) - 1u));
+            if (at < (uint32_t)FL_CAP) { s_frow[f][at] = (uint16_t)(j * SR_THREADS + threadIdx.x); s_fchild[f][at] = hit[j] >> 2; }
+        }
+        __syncthreads();
+        const uint32_t cnt0 = min(s_fcnt[0], (uint32_t)FL_CAP), cnt1 = min(s_fcnt[1], (uint32_t)FL_CAP);   // (the cap cannot be met: see FL_CAP)
+        for (uint32_t i = threadIdx.x; i < cnt0 + cnt1; i += SR_THREADS) {
+            const uint32_t f = i >= cnt0 ? 1u : 0u, k = i - (f ? cnt0 : 0u);
+            s_fpos[f][k] = 8u + __ldg(rb.vlen + block0 + s_frow[f][k]) + __ldg(rb.klen + s_fchild[f][k]);   // { u32 len, field, u32 len, key }
+        }
+        __syncthreads();
+        // the listed key compares (each a chain of dependent loads), by the upper warps -- while the first two wait for the blocks before
+        for (uint32_t i = SR_THREADS - 1 - threadIdx.x; i < s_jobs; i += SR_THREADS) {
+            const uint32_t r = s_job[i].x, orow = s_job[i].y;
+            const uint32_t ao = __ldg(rb.koff + orow), al = __ldg(rb.klen + orow), bo = __ldg(rb.koff + r), bl = __ldg(rb.klen + r);
+            if (!(s_meta_of(orow) & META_HAS_KEY) || !key_less(GlobalText{raw}, ao, al, bo, bl)) ok = false;
+        }
+        if (!ok) res->fast_reject = 1;
+        if (warp < 2) {
+            // warp 0 carries field 0, warp 1 field 1: record bytes before each hit of the block, then the block's
+            // place among the blocks.  Payload of the look-back: records (30 bits) | record bytes (32 bits), as in index.cu
+            const uint32_t f = warp, cnt = f ? cnt1 : cnt0;
+            u64 run = 0;
+            for (uint32_t base = 0; base < cnt; base += 32) {
+                const uint32_t k = base + lane, v = k < cnt ? s_fpos[f][k] : 0u;
+                u64 incl = v;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const u64 y = __shfl_up_sync(FULL, incl, o);
+                    if (lane >= (uint32_t)o) incl += y;
+                }
+                if (k < cnt) s_fpos[f][k] = (uint32_t)(run + incl - v);
+                run += __shfl_sync(FULL, incl, 31);
+            }
+            constexpr u64 ST_AGG = 1ull << 62, ST_PREFIX = 2ull << 62, ST_MASK = (1ull << 62) - 1;
+            const u64 agg = ((u64)cnt & 0x3fffffffull) | ((run & 0xffffffffull) << 30);
+            u64 *status = fx.status + 2 + (size_t)f * n_blocks;
+            u64 before = 0;
+            if (block == 0) {
+                if (lane == 0) st_relaxed_u64(status, ST_PREFIX | agg);
+            } else {
+                if (lane == 0) st_relaxed_u64(status + block, ST_AGG | agg);
+                int look = (int)block - 1;   // (128 status words per step instead of 32 was measured: slower, 50 us against 44)
+                for (;;) {
+                    const int idx = look - (int)lane;
+                    u64 st = idx >= 0 ? ld_relaxed_u64(status + idx) : ST_PREFIX;
+                    while (__any_sync(FULL, (st >> 62) == 0)) { if ((st >> 62) == 0) st = ld_relaxed_u64(status + idx); }
+                    const unsigned pm = __ballot_sync(FULL, (st >> 62) == 2);
+                    const int first = pm ? __ffs(pm) - 1 : 32;
+                    u64 x = ((int)lane <= first) ? (st & ST_MASK) : 0ull;
+#pragma unroll
+                    for (int o = 16; o; o >>= 1) x += __shfl_xor_sync(FULL, x, o);
+                    before += x;
+                    if (pm) break;
+                    look -= 32;
+                }
+                if (lane == 0) st_relaxed_u64(status + block, ST_PREFIX | ((before + agg) & ST_MASK));
+            }
+            if (lane == 0) {
+                s_fbase[f] = (before & 0x3fffffffull) | (((before >> 30) & 0xffffffffull) << 32);
+                if (run) atomicAdd(&res->field_bytes[f], run);      // (the 64-bit total: a blob of 4 GiB or more is refused)
+                if (block + 1 == n_blocks) {
+                    const uint32_t m = (uint32_t)((before + agg) & 0x3fffffffull);
+                    res->field_count[f] = m;
+                    if (m <= (f ? fx.cap[1] : fx.cap[0])) (f ? fx.off[1] : fx.off[0])[m] = (uint32_t)(((before + agg) >> 30) & 0xffffffffull);
                 }
             }
-        } else if (d == 0) {
-            if (r != 0) ok = false;       // at the top there is exactly one value
-        } else if (o == 0 || ((o & 1u) != 0) != ((m & META_HAS_KEY) != 0)) {
-            ok = false;                   // inside an object a value has a key, inside an array none
         }
-    }
-    __syncthreads();
-    for (uint32_t i = threadIdx.x; i < s_jobs; i += SR_THREADS) {
-        const uint32_t r = s_job[i].x, orow = s_job[i].y;
-        const uint32_t ao = __ldg(rb.koff + orow), al = __ldg(rb.klen + orow), bo = __ldg(rb.koff + r), bl = __ldg(rb.klen + r);
-        if (!(s_meta_of(orow) & META_HAS_KEY) || !key_less(GlobalText{raw}, ao, al, bo, bl)) ok = false;
-    }
-    if (!ok) res->fast_reject = 1;
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < cnt0 + cnt1; i += SR_THREADS) {
+            const uint32_t f = i >= cnt0 ? 1u : 0u, k = i - (f ? cnt0 : 0u), r = block0 + s_frow[f][k], c = s_fchild[f][k];
+            const uint32_t at = (uint32_t)s_fbase[f] + k;
+            if (at < (f ? fx.cap[1] : fx.cap[0])) {   // (selects, not fx.cap[f]: indexing a kernel parameter by a run-time value copies it to local memory)
+                (f ? fx.refs[1] : fx.refs[0])[at] = FieldRef{__ldg(rb.voff + r), __ldg(rb.vlen + r), __ldg(rb.koff + c), __ldg(rb.klen + c)};
+                (f ? fx.off[1] : fx.off[0])[at] = (uint32_t)(s_fbase[f] >> 32) + s_fpos[f][k];
+            }
+        }
+    }   // next 1,024 rows
 }
 
 }  // namespace
@@ -811,7 +942,7 @@ cudaError_t launch_lines_count(const uint8_t *raw, size_t n, uint32_t *scratch, 
     const uint32_t tiles = lines_tiles(n);
     cudaError_t e = cudaMemsetAsync(res, 0, sizeof(ParseResult), s);
     if (e != cudaSuccess) return e;
-    lines_count_kernel<<<tiles, LN_THREADS, 0, s>>>(raw, (u64)n, scratch, scratch + tiles, open_state, lines_row_blocks(row_cap) * (LINES_MAX_DEPTH + 1));
+    lines_count_kernel<<<tiles, LN_THREADS, 0, s>>>(raw, (u64)n, scratch, scratch + tiles, open_state, (uint32_t)lines_open_state_words(row_cap));
     lines_prefix_kernel<<<1, 1024, 0, s>>>(scratch, scratch + tiles, tiles, (u64)n, res);
     count_parse_launch(); count_parse_launch();
     return cudaGetLastError();
@@ -839,11 +970,26 @@ cudaError_t launch_lines_rows(const uint8_t *raw, size_t n, const uint32_t *scra
     return cudaGetLastError();
 }
 
-cudaError_t launch_lines_structure(const uint8_t *raw, RowBuffers rb, uint32_t row_cap, uint32_t *open_state, ParseResult *res, cudaStream_t s) {
+cudaError_t launch_lines_structure(const uint8_t *raw, RowBuffers rb, uint32_t row_cap, uint32_t *open_state, FieldIndexBuffers fx, ParseResult *res,
+                                   cudaStream_t s) {
     const uint32_t blocks = lines_row_blocks(row_cap);
     if (!blocks) return cudaSuccess;
+    // (the ticket counter and the look-back words of the field lists sit behind the open-container words: cleared by stage 0)
+    fx.status = reinterpret_cast<unsigned long long *>(open_state + (size_t)blocks * ST_DEPTHS);
     lines_open_prefix_kernel<<<1, OP_RUNS * ST_DEPTHS, 0, s>>>(open_state, res);
-    lines_resolve_kernel<<<blocks, SR_THREADS, 0, s>>>(raw, rb, open_state, res);
+    static std::atomic<uint32_t> cached[64];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    uint32_t grid = dev >= 0 && dev < 64 ? cached[dev].load() : 0;
+    if (!grid) {
+        int per_sm = 0, sms = 0;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lines_resolve_kernel, SR_THREADS, 0)) != cudaSuccess) return e;
+        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+        grid = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)(sms > 0 ? sms : 1);
+        if (dev >= 0 && dev < 64) cached[dev].store(grid);
+    }
+    lines_resolve_kernel<<<std::min(blocks, grid), SR_THREADS, 0, s>>>(raw, rb, open_state, fx, res);
     count_parse_launch(); count_parse_launch();
     return cudaGetLastError();
 }

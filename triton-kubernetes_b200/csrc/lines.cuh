@@ -20,6 +20,7 @@
 
 #include <cstdint>
 
+#include "index.cuh"
 #include "parse.cuh"
 #include "tape.hpp"
 
@@ -33,17 +34,22 @@ inline uint32_t lines_tiles(size_t n) { return (uint32_t)((n + 1 + LN_TILE - 1) 
 inline size_t lines_scratch_words(size_t n) { return 2 * (size_t)lines_tiles(n) + 8; }
 constexpr int LN_ROWS_PER_BLOCK = 1024;   // rows per block of the structure pass
 inline uint32_t lines_row_blocks(uint32_t rows) { return (rows + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK; }
+// open_state in 32-bit words: per block of rows 8 open-container words, then (as 64-bit words) a ticket counter,
+// a spare, and per field and block one look-back word of the module index's lists
+inline size_t lines_open_state_words(uint32_t row_cap) { const size_t b = lines_row_blocks(row_cap); return b * 8 + 2 * (2 + 2 * b); }
 
 // raw: the text at the start of the arena, space padded to a whole tile and 64 bytes more.
 // Stage 0: line ends counted per tile, folded (res->n_rows known on the device afterwards);
-// open_state (8 words per block of LN_ROWS_PER_BLOCK rows, row_cap rows at most) cleared.
+// open_state (lines_open_state_words(row_cap) words) cleared.
 cudaError_t launch_lines_count(const uint8_t *raw, size_t n, uint32_t *scratch, uint32_t *open_state, uint32_t row_cap, ParseResult *res,
                                cudaStream_t s);
 // Stage 1: one row per line into rb (capacity row_cap rows; more lines than that: fast_reject);
 // rb.open = open_state, where every opening row leaves its mark.
 cudaError_t launch_lines_rows(const uint8_t *raw, size_t n, const uint32_t *scratch, RowBuffers rb, uint32_t row_cap, ParseResult *res,
                               cudaStream_t s);
-// Stage 2: closers paired with openers, containers checked.
-cudaError_t launch_lines_structure(const uint8_t *raw, RowBuffers rb, uint32_t row_cap, uint32_t *open_state, ParseResult *res, cudaStream_t s);
+// Stage 2: closers paired with openers, containers checked; the module index's field lists (fx.refs, fx.off,
+// fx.cap given; res->field_count / field_bytes as after launch_field_find) made on the way.
+cudaError_t launch_lines_structure(const uint8_t *raw, RowBuffers rb, uint32_t row_cap, uint32_t *open_state, FieldIndexBuffers fx, ParseResult *res,
+                                   cudaStream_t s);
 
 }  // namespace tk

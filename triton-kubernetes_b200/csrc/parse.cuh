@@ -69,7 +69,8 @@ struct ParseResult {
     // index_slow: a child had more members than the kernel walks through (Clusters / Nodes then use the host tree)
     unsigned int field_count[2];
     unsigned long long field_bytes[2];
-    unsigned int index_slow, pad_;
+    unsigned int index_slow;
+    unsigned int reject_early;    // lines.cu: fast_reject as it stood before the last launch of the pass
 };
 
 inline uint32_t p1_tiles(size_t n) { return (uint32_t)((n + P1_TILE - 1) / P1_TILE); }
