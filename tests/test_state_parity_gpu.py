@@ -769,3 +769,33 @@ def test_line_pass_and_general_pipeline_give_the_same_result(tk, oracle):
                 assert with_lines[2] == oracle.New("x", raw).Bytes()
     finally:
         tk.state.set_line_pass(True)
+
+
+def test_text_already_on_the_device(tk, oracle):
+    """tk_state_new_device: the text is in the caller's device buffer.  The line pass copies it into the handle's
+    arena while it counts the lines (16-byte aligned source), anything else goes through a device-to-device
+    copy first; lengths around the 64-byte chunks and 8 KiB tiles of that pass, aligned and not, indented and
+    compact, valid and not -- the outcome is that of tk_state_new on the same bytes."""
+    import torch
+    dev = torch.device("cuda", torch.cuda.current_device())
+    base = _pretty(oracle, json.loads(synth.document(30, 9)))
+    texts = [_pretty(oracle, {}), _pretty(oracle, {"a": "b"}), b'{"module":{"cluster_a_b":{"name":"b"}}}', base, base[:-1], base + b"\n", b"{", b"[1, 2"]
+    for n in (63, 64, 65, 127, 128, 8191, 8192, 8193, 16384):
+        filler = {"k": "v" * 4}
+        while len(_pretty(oracle, filler)) < n:
+            filler["k"] += "v"
+        t = _pretty(oracle, filler)
+        texts.append(t)                                   # (ends within a byte or two of n)
+        texts.append(base[:n])                            # cut off in mid-document: invalid
+    for raw in texts:
+        for shift in (0, 16, 1):
+            buf = torch.zeros(len(raw) + 64, dtype=torch.uint8, device=dev)
+            buf[shift:shift + len(raw)] = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
+            torch.cuda.synchronize()
+            want = _outcome(tk, raw)
+            try:
+                s = tk.state.NewDevice("x", buf.data_ptr() + shift, len(raw))
+                got = ("ok", s.Bytes(), s.Clusters() if b'"module"' in raw[:40] else None)
+            except Exception as e:
+                got = ("err", str(e))
+            assert got == want == _outcome(oracle, raw), (raw[:40], len(raw), shift)

@@ -135,7 +135,7 @@ const char *kernel_name(int kind) {
     static const char *const names[K_COUNT] = {"row_offsets_kernel", "emit_kernel", "prefix_match_kernel", "scan_tokens_kernel (carry protocol)",
                                                "token_agg + token_blocks kernels", "brackets_kernel", "sort_brackets (radix passes)", "match_kernel",
                                                "decode kernels", "rows_kernel", "key_order_kernel", "field_pack_kernel (module index)", "field_find_kernel",
-                                               "lines_count + lines_prefix kernels", "lines_rows_kernel", "lines structure kernels",
+                                               "lines_count + lines_prefix kernels", "lines_rows_kernel", "lines_open_prefix + lines_resolve kernels (containers, field lists)",
                                                "scan_count_kernel", "scan_prefix_kernel", "scan_emit_kernel"};
     return kind >= 0 && kind < K_COUNT ? names[kind] : "";
 }
@@ -599,6 +599,7 @@ int Engine::upload_text(const char *raw, size_t n, std::string *err) {
     int rc = init(err);
     if (rc) return rc;
     StreamScope scope(stream_);
+    pending_text_ = nullptr;
     if (n >= 0xfff00000ull) { *err = "document too large: the text must stay below 4 GiB"; return TK_ELIMIT; }
     const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 64;
     cudaError_t e;
@@ -646,7 +647,9 @@ int Engine::upload_text_device(const void *dev_raw, size_t n, std::string *err) 
     const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 64;
     cudaError_t e;
     if ((e = d_arena_.reserve(padded)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
-    if (n && (e = cudaMemcpyAsync(d_arena_.p, dev_raw, n, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return fail(e, "copy text", err);
+    // (the line pass brings the text over itself, in its first pass over it: parse_lines)
+    pending_text_ = n && line_pass_on() && (reinterpret_cast<uintptr_t>(dev_raw) & 15u) == 0 ? static_cast<const uint8_t *>(dev_raw) : nullptr;
+    if (n && !pending_text_ && (e = cudaMemcpyAsync(d_arena_.p, dev_raw, n, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return fail(e, "copy text", err);
     if ((e = cudaMemsetAsync(d_arena_.as<uint8_t>() + n, ' ', padded - n, stream_)) != cudaSuccess) return fail(e, "pad text", err);
     raw_len_ = n;
     arena_used_ = padded;
@@ -682,7 +685,9 @@ int Engine::parse_lines(size_t n, ParseResult *out, bool *accepted, std::string 
     }
     if ((e = d_find_status_.reserve(field_status_words((uint32_t)row_cap) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(index)", err);
     fx_.status = d_find_status_.as<unsigned long long>();   // (for a second run of field_find with larger lists; the first is part of stage 2)
-    if ((e = timed(K_LINES_COUNT, [&] { return launch_lines_count(raw, n, scratch, rb.open, (uint32_t)row_cap, d_res, stream_); })) != cudaSuccess)
+    const uint8_t *src = pending_text_;
+    pending_text_ = nullptr;
+    if ((e = timed(K_LINES_COUNT, [&] { return launch_lines_count(d_arena_.as<uint8_t>(), src, n, scratch, rb.open, (uint32_t)row_cap, d_res, stream_); })) != cudaSuccess)
         return fail(e, "lines_count", err);
     if ((e = timed(K_LINES_ROWS, [&] { return launch_lines_rows(raw, n, scratch, rb, (uint32_t)row_cap, d_res, stream_); })) != cudaSuccess)
         return fail(e, "lines_rows", err);
@@ -727,6 +732,10 @@ int Engine::parse_resident(size_t n, ParseResult *out, std::string *err) {
 
     // ---- text that is already in the indented form (every file this library or the reference wrote):
     //      the line-by-line pass builds the tape; anything else it declines, and the general pipeline runs
+    if (pending_text_ && !line_pass_on()) {   // (switched off between the upload and here)
+        if ((e = cudaMemcpyAsync(d_arena_.p, pending_text_, n, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return fail(e, "copy text", err);
+        pending_text_ = nullptr;
+    }
     if (line_pass_on()) {   // (tk_set_line_pass / TK_NO_FAST_PATH: the tests run every vector through both)
         bool accepted = false;
         int rc = parse_lines(n, out, &accepted, err);

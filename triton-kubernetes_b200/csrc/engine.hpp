@@ -118,6 +118,7 @@ public:
     int parse_resident(size_t n, ParseResult *out, std::string *err);
     int upload_text(const char *raw, size_t n, std::string *err);
     int upload_text_device(const void *dev_raw, size_t n, std::string *err);
+    const uint8_t *pending_text_ = nullptr;   // text still in the caller's device buffer: the line pass copies it as it counts (lines.cu)
 
     int stage(const Document &doc, std::string *err);
     int stage_tape(const Document &doc, std::string *err);

@@ -23,14 +23,12 @@ static_assert(LN_THREADS * LN_CHUNK == LN_TILE, "a tile is one 64-byte chunk per
 
 __device__ __forceinline__ u64 low_bits(uint32_t k) { return k >= 64 ? ~0ull : ((1ull << k) - 1); }
 
-// bit i: byte i of the 64-byte chunk at p (16-byte aligned) is '\n'
-__device__ __forceinline__ u64 newline_mask(const uint8_t *p) {
-    const uint4 *q = reinterpret_cast<const uint4 *>(p);
+// bit i: byte i of the 64 bytes in x[0..3] is '\n'
+__device__ __forceinline__ u64 newline_mask(const uint4 (&x)[4]) {
     u64 m = 0;
 #pragma unroll
     for (int v = 0; v < 4; v++) {
-        const uint4 x = __ldg(q + v);
-        const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+        const uint32_t w[4] = {x[v].x, x[v].y, x[v].z, x[v].w};
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const uint32_t t = w[k] ^ 0x0a0a0a0au;
@@ -41,16 +39,47 @@ __device__ __forceinline__ u64 newline_mask(const uint8_t *p) {
     return m;
 }
 
-// line ends of the chunk that starts at `chunk`: newlines, and position n itself (the end of the text)
-__device__ __forceinline__ u64 chunk_line_ends(const uint8_t *raw, u64 chunk, u64 n) {
+// line ends of the 64-byte chunk that starts at `chunk` (16-byte aligned): newlines, and position n itself (the
+// end of the text).  COPY: the text is still where the caller has it on the device (src, 16-byte aligned) and is
+// brought into the arena on the way -- one pass over it instead of a copy and then this one; only bytes below n
+// are read from src and written to raw (the padding behind the text is the caller's memset).
+template <bool COPY>
+__device__ __forceinline__ u64 chunk_line_ends(uint8_t *raw, const uint8_t *__restrict__ src, u64 chunk, u64 n) {
     if (chunk > n) return 0;
-    u64 m = newline_mask(raw + chunk);
+    uint4 x[4];
+    if (!COPY) {
+#pragma unroll
+        for (int v = 0; v < 4; v++) x[v] = __ldg(reinterpret_cast<const uint4 *>(raw + chunk) + v);
+    } else if (chunk + 64 <= n) {
+#pragma unroll
+        for (int v = 0; v < 4; v++) x[v] = __ldg(reinterpret_cast<const uint4 *>(src + chunk) + v);
+#pragma unroll
+        for (int v = 0; v < 4; v++) reinterpret_cast<uint4 *>(raw + chunk)[v] = x[v];
+    } else {
+        uint32_t w[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            uint32_t y = 0x20202020u;
+#pragma unroll
+            for (int b = 0; b < 4; b++)
+                if (chunk + i * 4 + b < n) {
+                    const uint32_t c = src[chunk + i * 4 + b];
+                    raw[chunk + i * 4 + b] = (uint8_t)c;
+                    y = (y & ~(0xffu << (8 * b))) | (c << (8 * b));
+                }
+            w[i] = y;
+        }
+#pragma unroll
+        for (int v = 0; v < 4; v++) x[v] = make_uint4(w[v * 4], w[v * 4 + 1], w[v * 4 + 2], w[v * 4 + 3]);
+    }
+    u64 m = newline_mask(x);
     if (n - chunk < 64) m = (m & low_bits((uint32_t)(n - chunk))) | (1ull << (n - chunk));
     return m;
 }
 
 // ---- stage 0: count -------------------------------------------------------------------------
-__global__ void __launch_bounds__(LN_THREADS) lines_count_kernel(const uint8_t *__restrict__ raw, u64 n, uint32_t *__restrict__ counts,
+template <bool COPY>
+__global__ void __launch_bounds__(LN_THREADS) lines_count_kernel(uint8_t *raw, const uint8_t *__restrict__ src, u64 n, uint32_t *__restrict__ counts,
                                                                 uint32_t *__restrict__ last_end, uint32_t *__restrict__ open_state,
                                                                 uint32_t open_words) {
     __shared__ uint32_t s_cnt[LN_THREADS / 32], s_last[LN_THREADS / 32];
@@ -60,7 +89,7 @@ __global__ void __launch_bounds__(LN_THREADS) lines_count_kernel(const uint8_t *
         for (uint32_t i = threadIdx.x; i < per && w0 + i < open_words; i += LN_THREADS) open_state[w0 + i] = 0;
     }
     const u64 chunk = (u64)blockIdx.x * LN_TILE + (u64)threadIdx.x * LN_CHUNK;
-    const u64 m = chunk_line_ends(raw, chunk, n);
+    const u64 m = chunk_line_ends<COPY>(raw, src, chunk, n);
     uint32_t c = (uint32_t)__popcll(m);
     uint32_t last = m ? (uint32_t)(chunk + 63 - __clzll((long long)m)) + 1u : 0u;   // position + 1; 0: none
 #pragma unroll
@@ -937,12 +966,13 @@ __global__ void __launch_bounds__(SR_THREADS) lines_resolve_kernel(const uint8_t
 
 }  // namespace
 
-cudaError_t launch_lines_count(const uint8_t *raw, size_t n, uint32_t *scratch, uint32_t *open_state, uint32_t row_cap, ParseResult *res,
-                               cudaStream_t s) {
+cudaError_t launch_lines_count(uint8_t *raw, const uint8_t *src, size_t n, uint32_t *scratch, uint32_t *open_state, uint32_t row_cap,
+                               ParseResult *res, cudaStream_t s) {
     const uint32_t tiles = lines_tiles(n);
     cudaError_t e = cudaMemsetAsync(res, 0, sizeof(ParseResult), s);
     if (e != cudaSuccess) return e;
-    lines_count_kernel<<<tiles, LN_THREADS, 0, s>>>(raw, (u64)n, scratch, scratch + tiles, open_state, (uint32_t)lines_open_state_words(row_cap));
+    if (src) lines_count_kernel<true><<<tiles, LN_THREADS, 0, s>>>(raw, src, (u64)n, scratch, scratch + tiles, open_state, (uint32_t)lines_open_state_words(row_cap));
+    else lines_count_kernel<false><<<tiles, LN_THREADS, 0, s>>>(raw, nullptr, (u64)n, scratch, scratch + tiles, open_state, (uint32_t)lines_open_state_words(row_cap));
     lines_prefix_kernel<<<1, 1024, 0, s>>>(scratch, scratch + tiles, tiles, (u64)n, res);
     count_parse_launch(); count_parse_launch();
     return cudaGetLastError();

@@ -41,8 +41,10 @@ inline size_t lines_open_state_words(uint32_t row_cap) { const size_t b = lines_
 // raw: the text at the start of the arena, space padded to a whole tile and 64 bytes more.
 // Stage 0: line ends counted per tile, folded (res->n_rows known on the device afterwards);
 // open_state (lines_open_state_words(row_cap) words) cleared.
-cudaError_t launch_lines_count(const uint8_t *raw, size_t n, uint32_t *scratch, uint32_t *open_state, uint32_t row_cap, ParseResult *res,
-                               cudaStream_t s);
+// src != nullptr: the text is not in the arena yet but at src in device memory (16-byte aligned); the count pass
+// copies its n bytes to raw as it reads them (the padding behind them must already be there).
+cudaError_t launch_lines_count(uint8_t *raw, const uint8_t *src, size_t n, uint32_t *scratch, uint32_t *open_state, uint32_t row_cap,
+                               ParseResult *res, cudaStream_t s);
 // Stage 1: one row per line into rb (capacity row_cap rows; more lines than that: fast_reject);
 // rb.open = open_state, where every opening row leaves its mark.
 cudaError_t launch_lines_rows(const uint8_t *raw, size_t n, const uint32_t *scratch, RowBuffers rb, uint32_t row_cap, ParseResult *res,
