@@ -460,11 +460,11 @@ struct MaskText {
     }
     __device__ __forceinline__ uint32_t byte(u64 p) const { return p >= lo && p < hi ? (uint32_t)win[p - lo] : (uint32_t)__ldg(raw + p); }
     // the same for an offset into the window the caller knows to be inside it (16 bytes to spare)
+    // (three aligned 32-bit words and two funnel shifts: a 64-bit shift by a variable amount costs several times that)
     __device__ __forceinline__ u64 load8_in(uint32_t off) const {
-        const u64 *w = reinterpret_cast<const u64 *>(win + (off & ~7u));
-        const u64 x0 = w[0], x1 = w[1];
-        const uint32_t sh = (off & 7u) * 8u;
-        return sh ? (x0 >> sh) | (x1 << (64u - sh)) : x0;
+        const uint32_t *w = reinterpret_cast<const uint32_t *>(win + (off & ~3u));
+        const uint32_t x0 = w[0], x1 = w[1], x2 = w[2], sh = (off & 3u) * 8u;
+        return (u64)__funnelshift_r(x0, x1, sh) | ((u64)__funnelshift_r(x1, x2, sh) << 32);
     }
     // 64 mask bits from position p on (p inside the window; the arrays have a spare word behind them).  Read as
     // 32-bit words and put together with funnel shifts: a 64-bit shift by a variable amount costs several times that.
@@ -508,11 +508,12 @@ __device__ __forceinline__ u64 shift192(u64 a, u64 b, u64 c, uint32_t by) {   //
     if (by >= 64) { a = b; b = c; by -= 64; }
     return by ? (a >> by) | (b << (64u - by)) : a;
 }
-// strictly ascending, bytewise, two keys inside the window (offsets into it)
-__device__ __forceinline__ bool key_less_in(const MaskText &t, uint32_t a, uint32_t al, uint32_t b, uint32_t bl) {
+// strictly ascending, bytewise, two keys inside the window (offsets into it); a8: the first eight bytes at a
+__device__ __forceinline__ bool key_less_in(const MaskText &t, u64 a8, uint32_t a, uint32_t al, uint32_t b, uint32_t bl) {
     const uint32_t m = al < bl ? al : bl;
+    u64 x = big_endian(a8), y = big_endian(t.load8_in(b));
     for (uint32_t i = 0; i < m; i += 8) {
-        u64 x = big_endian(t.load8_in(a + i)), y = big_endian(t.load8_in(b + i));
+        if (i) { x = big_endian(t.load8_in(a + i)); y = big_endian(t.load8_in(b + i)); }
         if (m - i < 8) { const u64 keep = ~0ull << ((8 - (m - i)) * 8); x &= keep; y &= keep; }
         if (x != y) return x < y;
     }
@@ -536,26 +537,26 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
     u64 q0 = Q0 & in0, q1 = Q1 & in1;
     const uint32_t nq = (uint32_t)__popcll(q0) + (uint32_t)__popcll(q1);
     bad = bad || (nq != 0 && nq != 2 && nq != 4);
-    uint32_t qp[4];
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        const bool lo_has = q0 != 0;
-        const u64 src = lo_has ? q0 : q1;
-        qp[i] = src ? (lo_has ? 0u : 64u) + (uint32_t)__ffsll((long long)src) - 1u : 127u;   // 127: no such quote (inside the window all the same)
-        if (lo_has) q0 &= q0 - 1; else q1 &= q1 - 1;
-    }
+    // Of the quotes only three places matter: whether one stands right after the indentation (then it is the first:
+    // tabs are no quotes), where the next one is (the end of the key, or of a string that is the whole value), and
+    // where the last one is (the end of a string value behind a key: with four quotes in all, and ": " after the
+    // second, the third is where the value starts).  127: no such quote (inside the window all the same).
+    const bool quote_at_d = ((q0 >> min(d, 63u)) & 1ull) != 0;
+    const u64 r0 = q0 & ~low_bits(min(d, 63u) + 1u);
+    const uint32_t p1 = r0 ? (uint32_t)__ffsll((long long)r0) - 1u : (q1 ? 64u + (uint32_t)__ffsll((long long)q1) - 1u : 127u);
+    const uint32_t plast = q1 ? 127u - (uint32_t)__clzll((long long)q1) : (q0 ? 63u - (uint32_t)__clzll((long long)q0) : 127u);
     // "key": -- a quote right after the indentation, the next quote followed by a colon and a space
-    const bool key_shape = nq >= 2 && qp[0] == d && qp[1] + 1 < L && w[qp[1] + 1] == ':';
-    bad = bad || (key_shape && (qp[1] + 2 >= L || w[qp[1] + 2] != ' ' || qp[1] + 3 >= L));
+    const bool key_shape = nq >= 2 && quote_at_d && p1 + 1 < L && w[p1 + 1] == ':';
+    bad = bad || (key_shape && (p1 + 2 >= L || w[p1 + 2] != ' ' || p1 + 3 >= L));
     const uint32_t used = key_shape ? 2u : 0u;                  // quotes accounted for
-    const uint32_t v = key_shape ? min(qp[1] + 3, 127u) : min(d, 127u);   // where the value starts
-    const uint32_t koff = key_shape ? s32 + d + 1 : 0u, klen = key_shape ? qp[1] - d - 1 : 0u;
+    const uint32_t v = key_shape ? min(p1 + 3, 127u) : min(d, 127u);   // where the value starts
+    const uint32_t koff = key_shape ? s32 + d + 1 : 0u, klen = key_shape ? p1 - d - 1 : 0u;
     const uint32_t c = w[v], c1 = w[v + 1];
     const bool is_str = c == '"', is_brace = c == '{', is_brack = c == '[', is_cl = c == '}' || c == ']';
     const bool is_empty = (is_brace && c1 == '}' && v + 1 < L) || (is_brack && c1 == ']' && v + 1 < L);
     const bool is_open = (is_brace || is_brack) && !is_empty, is_scalar = !(is_str || is_brace || is_brack || is_cl);
-    const uint32_t qa = used ? qp[2] : qp[0], qb = used ? qp[3] : qp[1];          // the value's quotes, if it is a string
-    bad = bad || (is_str ? (nq != used + 2 || qa != v) : nq != used);            // a quote where no string can be, or one too few
+    const uint32_t qb = used ? plast : p1;                                     // the value's closing quote, if it is a string
+    bad = bad || (is_str ? nq != used + 2 : nq != used);                        // a quote where no string can be, or one too few
     bad = bad || (is_cl && key_shape);
     uint32_t kind, after, voff = 0, vlen = 0;
     if (is_str) { kind = ROW_STR | META_VAL_PLAIN; voff = s32 + v + 1; vlen = qb - v - 1; after = qb + 1; }
@@ -575,6 +576,7 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
     const uint32_t cn = w[nb + min(dn, 16u)];
     const bool next_closes = cn == '}' || cn == ']';
     bad = bad || (is_open ? (dn != d + 1 || next_closes) : next_closes ? (d == 0 || dn != d - 1 || comma) : (dn != d || !comma));
+    const u64 k8 = t.load8_in(so + d + 1);   // the key's first bytes (or whatever stands there: used only if key_shape)
     int verdict = 1;
     if (!bad && key_shape && !is_open && !next_closes) {
         // the next member of the same object: its key -- up to the next quote; whether that line is well formed is
@@ -583,12 +585,11 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
         const u64 qn = from < 128 ? shift192(Q0, Q1, Q2, from) : 0ull;
         if (cn != '"') bad = true;
         else if (!qn) verdict = 2;
-        else bad = !key_less_in(t, so + d + 1, klen, so + from, (uint32_t)__ffsll((long long)qn) - 1u);
+        else bad = !key_less_in(t, k8, so + d + 1, klen, so + from, (uint32_t)__ffsll((long long)qn) - 1u);
     }
     if (bad) return 0;
     if (verdict == 2) return 2;
     // the row, with what the module index and the verdict want to know about it (finish_row, from the window)
-    const u64 k8 = t.load8_in(so + d + 1);
     if (d == 3 && (kind & 15u) == ROW_STR && key_shape) {
         if (klen == 4 && (uint32_t)k8 == 0x656d616eu) meta |= META_KEY_IS_NAME;                    // "name"
         else if (klen == 8 && k8 == 0x656d616e74736f68ull) meta |= META_KEY_IS_HOSTNAME;           // "hostname"
