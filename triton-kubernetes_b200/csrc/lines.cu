@@ -499,15 +499,6 @@ struct MaskText {
     }
 };
 
-// A line of at most 120 bytes that is not the last one, decided by arithmetic on the class masks: how many
-// quotes and where, nothing between the indentation and the end that stops a string, the few bytes
-// that must be exactly ':' ' ' ',' or a bracket read by position.  1: accepted, row written; 0: not
-// the indented form; 2: not for this function (too long, at the edge of the window, the last line) --
-// line_to_row decides.  Same rules as line_to_row, same rows.
-__device__ __forceinline__ u64 shift192(u64 a, u64 b, u64 c, uint32_t by) {   // bits [by, by + 64) of the 192-bit number c:b:a, by < 128
-    if (by >= 64) { a = b; b = c; by -= 64; }
-    return by ? (a >> by) | (b << (64u - by)) : a;
-}
 // strictly ascending, bytewise, two keys inside the window (offsets into it); a8: the first eight bytes at a
 __device__ __forceinline__ bool key_less_in(const MaskText &t, u64 a8, uint32_t a, uint32_t al, uint32_t b, uint32_t bl) {
     const uint32_t m = al < bl ? al : bl;
@@ -519,9 +510,14 @@ __device__ __forceinline__ bool key_less_in(const MaskText &t, u64 a8, uint32_t 
     }
     return al < bl;
 }
+// A line of at most 120 bytes that is not the last one, decided by arithmetic on the class masks: how many
+// quotes and where, nothing between the indentation and the end that stops a string, the few bytes
+// that must be exactly ':' ' ' ',' or a bracket read by position.  1: accepted, row written; 0: not
+// the indented form; 2: not for this function (too long, at the edge of the window, the last line) --
+// line_to_row decides.  Same rules as line_to_row, same rows.
 __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n, uint32_t r, RowBuffers rb, ParseResult *res) {
     const uint32_t L = (uint32_t)(e - s);
-    // (120: the look at the next line stays inside 192 mask bits; 288: every read below stays inside the window)
+    // (288: every read below -- this line, the start of the next, its key -- stays inside the window)
     if (L == 0 || L > 120 || (long long)s + 288 > t.w1 || s + 288 > t.hi || e >= n) return 2;
     // Straight-line code from here on: what is wrong is collected in `bad`, not returned at once, so that the lanes
     // of a warp -- thirty-two different lines -- stay together and the rows are written by all of them at once.
@@ -530,7 +526,7 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
     const uint32_t sb = (uint32_t)((long long)s - t.w0);          // the line's first bit in the masks
     const uint32_t d = (uint32_t)__ffs((int)~t.bits32(t.tabm, sb)) - 1u;   // (32 tabs: 0xffffffff -> far too deep)
     bool bad = d > LINES_MAX_DEPTH + 1 || d >= L || (r == 0 && d != 0);
-    const u64 Q0 = t.bits(t.qm, s), Q1 = t.bits(t.qm, s + 64), Q2 = t.bits(t.qm, s + 128);
+    const u64 Q0 = t.bits(t.qm, s), Q1 = t.bits(t.qm, s + 64);
     const u64 S0 = t.bits(t.stopm, s), S1 = t.bits(t.stopm, s + 64);
     const u64 in0 = low_bits(L), in1 = L > 64 ? low_bits(L - 64) : 0ull;       // the line's own bits
     bad = bad || ((S0 & in0 & ~low_bits(min(d, 63u))) | (S1 & in1)) != 0;          // something that cannot stand for itself
@@ -582,7 +578,7 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
         // the next member of the same object: its key -- up to the next quote; whether that line is well formed is
         // its own thread's business -- must sort strictly after this one
         const uint32_t from = nb + dn + 1;                                // first byte of the next key, from s
-        const u64 qn = from < 128 ? shift192(Q0, Q1, Q2, from) : 0ull;
+        const u64 qn = t.bits(t.qm, s + from);                             // (from <= 131: inside the 288 bytes the window has behind s)
         if (cn != '"') bad = true;
         else if (!qn) verdict = 2;
         else bad = !key_less_in(t, k8, so + d + 1, klen, so + from, (uint32_t)__ffsll((long long)qn) - 1u);
