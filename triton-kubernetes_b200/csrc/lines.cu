@@ -502,11 +502,17 @@ struct MaskText {
 // strictly ascending, bytewise, two keys inside the window (offsets into it); a8: the first eight bytes at a
 __device__ __forceinline__ bool key_less_in(const MaskText &t, u64 a8, uint32_t a, uint32_t al, uint32_t b, uint32_t bl) {
     const uint32_t m = al < bl ? al : bl;
-    u64 x = big_endian(a8), y = big_endian(t.load8_in(b));
+    u64 x = a8, y = t.load8_in(b);
     for (uint32_t i = 0; i < m; i += 8) {
-        if (i) { x = big_endian(t.load8_in(a + i)); y = big_endian(t.load8_in(b + i)); }
-        if (m - i < 8) { const u64 keep = ~0ull << ((8 - (m - i)) * 8); x &= keep; y &= keep; }
-        if (x != y) return x < y;
+        if (i) { x = t.load8_in(a + i); y = t.load8_in(b + i); }
+        // the first byte in which they differ (32-bit halves: no byte reversal, no 64-bit shifts)
+        const uint32_t xl = (uint32_t)x, yl = (uint32_t)y, xh = (uint32_t)(x >> 32), yh = (uint32_t)(y >> 32), dl = xl ^ yl, dh = xh ^ yh;
+        if (dl | dh) {
+            const uint32_t dw = dl ? dl : dh, xw = dl ? xl : xh, yw = dl ? yl : yh;
+            const uint32_t bit = (uint32_t)__ffs((int)dw) - 1u, sh = bit & 24u, at = i + (dl ? 0u : 4u) + (bit >> 3);
+            if (at < m) return ((xw >> sh) & 0xffu) < ((yw >> sh) & 0xffu);
+            break;   // the same as far as the shorter one goes
+        }
     }
     return al < bl;
 }
@@ -533,14 +539,13 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
     u64 q0 = Q0 & in0, q1 = Q1 & in1;
     const uint32_t nq = (uint32_t)__popcll(q0) + (uint32_t)__popcll(q1);
     bad = bad || (nq != 0 && nq != 2 && nq != 4);
-    // Of the quotes only three places matter: whether one stands right after the indentation (then it is the first:
-    // tabs are no quotes), where the next one is (the end of the key, or of a string that is the whole value), and
-    // where the last one is (the end of a string value behind a key: with four quotes in all, and ": " after the
-    // second, the third is where the value starts).  127: no such quote (inside the window all the same).
+    // Of the quotes only two places matter: whether one stands right after the indentation (then it is the first:
+    // tabs are no quotes) and where the next one is (the end of the key).  A string value then starts with a quote
+    // by the look of its first byte and must end with one right before the end of the line or its comma; that
+    // there are no others is a matter of counting.  127: no such quote (inside the window all the same).
     const bool quote_at_d = ((q0 >> min(d, 63u)) & 1ull) != 0;
     const u64 r0 = q0 & ~low_bits(min(d, 63u) + 1u);
     const uint32_t p1 = r0 ? (uint32_t)__ffsll((long long)r0) - 1u : (q1 ? 64u + (uint32_t)__ffsll((long long)q1) - 1u : 127u);
-    const uint32_t plast = q1 ? 127u - (uint32_t)__clzll((long long)q1) : (q0 ? 63u - (uint32_t)__clzll((long long)q0) : 127u);
     // "key": -- a quote right after the indentation, the next quote followed by a colon and a space
     const bool key_shape = nq >= 2 && quote_at_d && p1 + 1 < L && w[p1 + 1] == ':';
     bad = bad || (key_shape && (p1 + 2 >= L || w[p1 + 2] != ' ' || p1 + 3 >= L));
@@ -551,15 +556,16 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
     const bool is_str = c == '"', is_brace = c == '{', is_brack = c == '[', is_cl = c == '}' || c == ']';
     const bool is_empty = (is_brace && c1 == '}' && v + 1 < L) || (is_brack && c1 == ']' && v + 1 < L);
     const bool is_open = (is_brace || is_brack) && !is_empty, is_scalar = !(is_str || is_brace || is_brack || is_cl);
-    const uint32_t qb = used ? plast : p1;                                     // the value's closing quote, if it is a string
-    bad = bad || (is_str ? nq != used + 2 : nq != used);                        // a quote where no string can be, or one too few
+    const bool trail = w[L - 1] == ',';
+    const uint32_t qb = L - 1u - (trail ? 1u : 0u);                             // the value's closing quote, if it is a string
+    bad = bad || (is_str ? (nq != used + 2 || qb <= v || qb >= L || w[min(qb, 127u)] != '"') : nq != used);   // a quote where no string can be, or one too few
     bad = bad || (is_cl && key_shape);
     uint32_t kind, after, voff = 0, vlen = 0;
     if (is_str) { kind = ROW_STR | META_VAL_PLAIN; voff = s32 + v + 1; vlen = qb - v - 1; after = qb + 1; }
     else if (is_empty) { kind = is_brace ? ROW_EMPTY_OBJ : ROW_EMPTY_ARR; vlen = s32 + v; after = v + 2; }
     else if (is_open) { kind = is_brace ? ROW_OPEN_OBJ : ROW_OPEN_ARR; vlen = s32 + v; after = v + 1; }
     else if (is_cl) { kind = c == '}' ? ROW_CLOSE_OBJ : ROW_CLOSE_ARR; vlen = s32 + v; after = v + 1; }
-    else { kind = ROW_RAW; after = w[L - 1] == ',' ? L - 1 : L; voff = s32 + v; vlen = after - v; }
+    else { kind = ROW_RAW; after = trail ? L - 1 : L; voff = s32 + v; vlen = after - v; }
     if (is_scalar && !bad) bad = after <= v || !canonical_scalar(t, s + v, s + after);   // (container rows keep the position of their bracket in vlen)
     const bool comma = after < L && w[min(after, 127u)] == ',';
     after += comma ? 1u : 0u;
@@ -662,7 +668,14 @@ __global__ void __launch_bounds__(LR_THREADS, 8) lines_rows_kernel(const uint8_t
         for (uint32_t w = 0; w < LR_THREADS / 32; w++) { if (w < warp) before += s_warp[w]; total += s_warp[w]; }
         {
             uint32_t k = before;
-            for (u64 left = my_ends; left; left &= left - 1, k++)
+            u64 left = my_ends;
+#pragma unroll
+            for (int it = 0; it < 2; it++) {   // (a 64-byte chunk of config #4 holds one or two line ends: no loop for those)
+                if (left && k < TILE_LINES) s_end[k] = (uint16_t)(threadIdx.x * LN_CHUNK + (uint32_t)__ffsll((long long)left) - 1);
+                k += left ? 1u : 0u;
+                left &= left - 1;
+            }
+            for (; left; left &= left - 1, k++)
                 if (k < TILE_LINES) s_end[k] = (uint16_t)(threadIdx.x * LN_CHUNK + (uint32_t)__ffsll((long long)left) - 1);
         }
         __syncthreads();
