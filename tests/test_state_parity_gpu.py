@@ -41,7 +41,8 @@ def test_new_keeps_canonical_documents_on_the_device(tk, oracle):
         assert s.Bytes() == oracle.New("x", raw).Bytes()
         assert s.host_tree_built == (not resident)          # Bytes() alone never builds the tree
     s = tk.New("x", canon)
-    assert s.Get("module.cluster-manager.name") == b"bench" and s.host_tree_built
+    assert s.Get("module.cluster-manager.name") == b"bench" and not s.host_tree_built    # (from the module index)
+    assert s.Get("module.cluster-manager.source") == oracle.New("x", canon).Get("module.cluster-manager.source") and s.host_tree_built
     assert s.Bytes() == canon
 
 
@@ -799,3 +800,26 @@ def test_text_already_on_the_device(tk, oracle):
             except Exception as e:
                 got = ("err", str(e))
             assert got == want == _outcome(oracle, raw), (raw[:40], len(raw), shift)
+
+
+def test_get_of_a_module_childs_name_or_hostname_needs_no_host_tree(tk, oracle):
+    """Get("module.<key>.name") / (".hostname") on a document that lives on the device is answered from the module
+    index -- before and after edits of module's children --; every other path builds the host tree, as before.
+    Whatever the index does not hold (no such child, no such member, not a string, a record) is "" for Get too."""
+    mod = {"cluster_a_b": {"name": "b", "x": "1"}, "cluster_a_c": {"name": 7}, "cluster_a_d": ["name"], "cluster_a_e": {"hostname": {"name": "deep"}},
+           "node_a_b_1": {"hostname": "h1"}, "node_a_b_10": {"hostname": "h10", "name": "n10"}, "node_a_b_2": {}}
+    raw = oracle.New("x", json.dumps({"module": mod, "name": "root"}).encode()).Bytes()
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    paths = ["module.%s.%s" % (k, f) for k in list(mod) + ["absent", "node_a_b_", ""] for f in ("name", "hostname")]
+    for p in paths:
+        assert a.Get(p) == b.Get(p), p
+    assert not a.host_tree_built
+    for s in (a, b):
+        s.Delete("module.node_a_b_1")
+        s.AddNode("cluster_a_b", "zz", {"hostname": "hz"})
+        s.AddCluster("a", "q", tk.Record([("name", "opaque")]) if s is a else oracle.Record([("name", "opaque")]))
+    for p in paths + ["module.node_a_b_zz.hostname", "module.cluster_a_q.name"]:
+        assert a.Get(p) == b.Get(p), p
+    assert not a.host_tree_built and a.Bytes() == b.Bytes()
+    assert a.Get("module.cluster_a_b.x") == b.Get("module.cluster_a_b.x") == b"1" and a.host_tree_built
+    assert a.Get("name") == b.Get("name") == b"root"

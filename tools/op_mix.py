@@ -135,9 +135,17 @@ def main():
     assert dt > 0 and pairs.value == C * N
     prod["Nodes"] = {"calls_per_s": C / dt, "calls": C, "pairs": pairs.value}
     vb = c_size_t()
-    t0 = time.perf_counter(); dt1 = D.tkb_get_loop(h, g_arr, g_lens, len(get_paths), 1, byref(vb)); first = time.perf_counter() - t0
+    L.tk_state_host_tree_built.argtypes = [c_void_p]
+    # module.<node>.hostname: answered from the module index, the document stays on the device
     dt = D.tkb_get_loop(h, g_arr, g_lens, len(get_paths), args.gets, byref(vb))
-    assert dt > 0 and dt1 > 0
+    assert dt > 0 and vb.value > 0 and not L.tk_state_host_tree_built(h)
+    prod["Get (module.<key>.hostname, document on the device)"] = {"ops_per_s": args.gets / dt, "ops": args.gets}
+    # module.<node>.source: any other path builds the host tree first
+    src_paths = [b"module." + k + b".source" for k in node_keys]
+    s_arr, s_lens = arrays(src_paths)
+    t0 = time.perf_counter(); dt1 = D.tkb_get_loop(h, s_arr, s_lens, len(src_paths), 1, byref(vb)); first = time.perf_counter() - t0
+    dt = D.tkb_get_loop(h, s_arr, s_lens, len(src_paths), args.gets, byref(vb))
+    assert dt > 0 and dt1 > 0 and L.tk_state_host_tree_built(h)
     prod["Get"] = {"first_call_s (builds the host tree from the device tape)": first, "ops_per_s": args.gets / dt, "ops": args.gets}
     dt = D.tkb_delete_loop(h, d_arr, d_lens, len(del_paths))
     assert dt > 0

@@ -93,6 +93,30 @@ int tk_state_name(tk_state *s, const char **name, size_t *name_len) {
 
 int tk_state_get(tk_state *s, const char *path, size_t path_len, const char **value, size_t *value_len) {
     if (!s || !value || !value_len) return set_err(s, TK_EARG, "tk_state_get: NULL argument");
+    if (!s->doc.host_valid && (s->eng.edits_active() || s->eng.index_usable(s->doc))) {
+        // "module.<key>.name" / "module.<key>.hostname" of a document on the device -- what the flows ask a loaded state
+        // (create/node.go, destroy/*.go) -- is in the module index: no host tree for it.  Anything the index does
+        // not hold (no such child, the member missing or not a string) is "" for Get as well.
+        const std::string_view p = sv(path, path_len);
+        const size_t d1 = p.find('.'), d2 = d1 == std::string_view::npos ? d1 : p.find('.', d1 + 1);
+        if (d2 != std::string_view::npos && p.find('.', d2 + 1) == std::string_view::npos && p.substr(0, d1) == "module") {
+            const std::string_view key = p.substr(d1 + 1, d2 - d1 - 1), member = p.substr(d2 + 1);
+            if (member == "name" || member == "hostname") {
+                std::string err;
+                bool module_ok = false;
+                int rc = s->eng.index_lookup(s->doc, key, member == "hostname", &module_ok, &s->pairs, &err);
+                if (rc) return set_err(s, rc, err);
+                if (module_ok) {
+                    s->blob.clear();
+                    for (auto &pr : s->pairs)
+                        if (pr.second == key) { s->blob.assign(pr.first.data(), pr.first.size()); break; }
+                    *value = s->blob.data();
+                    *value_len = s->blob.size();
+                    return TK_OK;
+                }
+            }
+        }
+    }
     if (int rc = ensure_host(s)) return rc;
     std::string_view v = s->doc.get(sv(path, path_len));
     *value = v.data() ? v.data() : "";

@@ -772,7 +772,7 @@ __device__ __forceinline__ u64 ld_relaxed_u64(const u64 *p) {
 }
 __device__ __forceinline__ void st_relaxed_u64(u64 *p, u64 v) { asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 constexpr int FL_CAP = LN_ROWS_PER_BLOCK / 2;   // a hit needs the row of its own child as well: at most 512 per field and block
-__global__ void __launch_bounds__(SR_THREADS) lines_resolve_kernel(const uint8_t *__restrict__ raw, RowBuffers rb, const uint32_t *__restrict__ prefix,
+__global__ void __launch_bounds__(SR_THREADS, 6) lines_resolve_kernel(const uint8_t *__restrict__ raw, RowBuffers rb, const uint32_t *__restrict__ prefix,
                                                                   FieldIndexBuffers fx, ParseResult *res) {
     constexpr int WORDS = LN_ROWS_PER_BLOCK / 32;
     static_assert(WORDS == 32 && SR_THREADS / 32 == ST_DEPTHS, "a warp per depth folds the 32 words of that depth");
