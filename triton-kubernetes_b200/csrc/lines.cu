@@ -12,6 +12,7 @@
 
 #include "bulkcopy.cuh"
 #include "index.cuh"
+#include "pdl.cuh"
 
 namespace tk {
 namespace {
@@ -113,6 +114,7 @@ __global__ void __launch_bounds__(1024) lines_prefix_kernel(uint32_t *counts, ui
     __shared__ uint32_t s_w[32], s_m[32];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t run = 0, run_end = 0;
+    griddep_wait();   // (launched while the count pass is still running)
     for (uint32_t base = 0; base < n_tiles; base += 1024 * 4) {
         const uint32_t first = base + threadIdx.x * 4;
         uint32_t v[4], e[4], sum = 0, top = 0;
@@ -617,9 +619,10 @@ __global__ void __launch_bounds__(LR_THREADS, 8) lines_rows_kernel(const uint8_t
     __shared__ uint16_t s_end[TILE_LINES];
     __shared__ uint32_t s_warp[LR_THREADS / 32];
     __shared__ u64 s_prev_end;      // position + 1 of the last line end before the tile
+    for (int i = threadIdx.x; i < 4 * 256; i += LR_THREADS) s_lut[i] = g_line_lut.v[i];   // (before the wait: nothing of the kernels before)
+    griddep_wait();
     if (res->fast_reject) return;
     if (res->n_rows > row_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) res->fast_reject = 1; return; }
-    for (int i = threadIdx.x; i < 4 * 256; i += LR_THREADS) s_lut[i] = g_line_lut.v[i];
     if (threadIdx.x == 0) { s_tab[WIN_CHUNKS] = 0; s_q[WIN_CHUNKS] = 0; s_stop[WIN_CHUNKS] = 0; }
     if (threadIdx.x == 0) mbar_init(&s_bar, 1);
     __syncthreads();
@@ -718,6 +721,7 @@ constexpr int SR_THREADS = 256, SR_ITEMS = LN_ROWS_PER_BLOCK / SR_THREADS;
 constexpr int OP_RUNS = 128;
 __global__ void __launch_bounds__(OP_RUNS * ST_DEPTHS) lines_open_prefix_kernel(uint32_t *agg, ParseResult *res) {
     __shared__ uint32_t s_top[ST_DEPTHS][OP_RUNS];
+    griddep_wait();
     const uint32_t n_blocks = (res->n_rows + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK;
     if (res->fast_reject) {   // what the blocks of the next launch go by (they set fast_reject themselves)
         if (threadIdx.x == 0) res->reject_early = 1;
@@ -782,6 +786,7 @@ __global__ void __launch_bounds__(SR_THREADS, 6) lines_resolve_kernel(const uint
     __shared__ uint16_t s_frow[2][FL_CAP];            // the block's hits per field, in row order: the row (local), ...
     __shared__ uint32_t s_fchild[2][FL_CAP], s_fpos[2][FL_CAP];   // ... its child's row, the bytes of the records before it in the block
     __shared__ u64 s_fbase[2];                        // records before the block | record bytes before it << 32
+    griddep_wait();
     const uint32_t n_rows = res->n_rows, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t n_blocks = (n_rows + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK;
     // (reject_early, not fast_reject: that one may be set by a block of this very launch, and a block that left
@@ -983,7 +988,7 @@ cudaError_t launch_lines_count(uint8_t *raw, const uint8_t *src, size_t n, uint3
     if (e != cudaSuccess) return e;
     if (src) lines_count_kernel<true><<<tiles, LN_THREADS, 0, s>>>(raw, src, (u64)n, scratch, scratch + tiles, open_state, (uint32_t)lines_open_state_words(row_cap));
     else lines_count_kernel<false><<<tiles, LN_THREADS, 0, s>>>(raw, nullptr, (u64)n, scratch, scratch + tiles, open_state, (uint32_t)lines_open_state_words(row_cap));
-    lines_prefix_kernel<<<1, 1024, 0, s>>>(scratch, scratch + tiles, tiles, (u64)n, res);
+    if ((e = launch_dependent(lines_prefix_kernel, dim3(1), dim3(1024), s, scratch, scratch + tiles, tiles, (u64)n, res)) != cudaSuccess) return e;
     count_parse_launch(); count_parse_launch();
     return cudaGetLastError();
 }
@@ -1005,7 +1010,8 @@ cudaError_t launch_lines_rows(const uint8_t *raw, size_t n, const uint32_t *scra
         grid = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)(sms > 0 ? sms : 1);
         if (dev >= 0 && dev < 64) cached[dev].store(grid);
     }
-    lines_rows_kernel<<<std::min(tiles, grid), LR_THREADS, 0, s>>>(raw, (u64)n, (u64)readable_end, tiles, scratch, scratch + tiles, rb, row_cap, res);
+    if ((e = launch_dependent(lines_rows_kernel, dim3(std::min(tiles, grid)), dim3(LR_THREADS), s, raw, (u64)n, (u64)readable_end, tiles, scratch, scratch + tiles, rb, row_cap,
+                              res)) != cudaSuccess) return e;
     count_parse_launch();
     return cudaGetLastError();
 }
@@ -1016,7 +1022,8 @@ cudaError_t launch_lines_structure(const uint8_t *raw, RowBuffers rb, uint32_t r
     if (!blocks) return cudaSuccess;
     // (the ticket counter and the look-back words of the field lists sit behind the open-container words: cleared by stage 0)
     fx.status = reinterpret_cast<unsigned long long *>(open_state + (size_t)blocks * ST_DEPTHS);
-    lines_open_prefix_kernel<<<1, OP_RUNS * ST_DEPTHS, 0, s>>>(open_state, res);
+    cudaError_t e0 = launch_dependent(lines_open_prefix_kernel, dim3(1), dim3(OP_RUNS * ST_DEPTHS), s, open_state, res);
+    if (e0 != cudaSuccess) return e0;
     static std::atomic<uint32_t> cached[64];
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
@@ -1029,7 +1036,7 @@ cudaError_t launch_lines_structure(const uint8_t *raw, RowBuffers rb, uint32_t r
         grid = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)(sms > 0 ? sms : 1);
         if (dev >= 0 && dev < 64) cached[dev].store(grid);
     }
-    lines_resolve_kernel<<<std::min(blocks, grid), SR_THREADS, 0, s>>>(raw, rb, open_state, fx, res);
+    if ((e = launch_dependent(lines_resolve_kernel, dim3(std::min(blocks, grid)), dim3(SR_THREADS), s, raw, rb, open_state, fx, res)) != cudaSuccess) return e;
     count_parse_launch(); count_parse_launch();
     return cudaGetLastError();
 }
