@@ -841,42 +841,15 @@ __global__ void __launch_bounds__(SR_THREADS, 6) lines_resolve_kernel(const uint
         const uint32_t module_row = res->module_row;   // 1 + row, 0: none (stage 1 has finished)
         // "module" as the index wants it: an object member of a root object; as a container: (row + 1) << 1 | 1
         const uint32_t module_enc = res->root_kind == ROW_OPEN_OBJ && module_row != 0 && res->module_kind == ROW_OPEN_OBJ ? (module_row << 1) | 1u : 0u;
+        // ---- the module index's hits first: their number and sizes are what the blocks after this one wait for
         uint32_t hit[SR_ITEMS];   // child row << 2 | field (0 "name", 1 "hostname", 2 none)
 #pragma unroll
         for (int j = 0; j < SR_ITEMS; j++) {
-            const uint32_t rl = j * SR_THREADS + threadIdx.x, r = block0 + rl;
-            const bool valid = r < n_rows;
-            const uint32_t m = meta[j], kind = m & 15u, d = m >> META_DEPTH_SHIFT;
-            const bool closes = kind == ROW_CLOSE_OBJ || kind == ROW_CLOSE_ARR;
-            // one look-up for every row: a closer wants its opener (same depth), a value its container (one up)
-            const uint32_t dq = closes ? d : d - 1u;
-            const uint32_t o = valid && dq <= LINES_MAX_DEPTH ? state_at(dq, rl) : 0u;
+            const uint32_t rl = j * SR_THREADS + threadIdx.x, r = block0 + rl, m = meta[j];
             hit[j] = 2u;
-            if (!valid) {
-            } else if (closes) {
-                // the container it closes opened at the same depth, and was of the same kind
-                if (o == 0 || (o & 1u) != (kind == ROW_CLOSE_OBJ ? 1u : 0u)) ok = false;
-                else {
-                    const uint32_t orow = (o >> 1) - 1;
-                    rb.koff[r] = orow;        // (TapeView::rows_direct: rows, not bracket numbers)
-                    rb.voff[orow] = r;
-                    if (module_row && orow == module_row - 1) res->module_end = r;
-                    // key order across the container that has just closed: if the next row is a member of the same
-                    // object, the member before it is the one that opened here.  About one row in fourteen at
-                    // config #4: listed, and compared below by neighbouring threads
-                    const uint32_t nm = rl + 1 < (uint32_t)LN_ROWS_PER_BLOCK ? s_meta[rl + 1] : (r + 1 < n_rows ? __ldg(rb.meta + r + 1) : 0xffffffffu);
-                    const uint32_t nk = nm & 15u;
-                    if (nm != 0xffffffffu && nk != ROW_CLOSE_OBJ && nk != ROW_CLOSE_ARR && (nm & META_HAS_KEY) && (nm >> META_DEPTH_SHIFT) == d) {
-                        const uint32_t at = atomicAdd(&s_jobs, 1u);
-                        s_job[at] = make_uint2(r + 1, orow);
-                    }
-                }
-            } else if (d == 0) {
-                if (r != 0) ok = false;       // at the top there is exactly one value
-            } else if (o == 0 || ((o & 1u) != 0) != ((m & META_HAS_KEY) != 0)) {
-                ok = false;                   // inside an object a value has a key, inside an array none
-            } else if ((m & (META_KEY_IS_NAME | META_KEY_IS_HOSTNAME)) && d == 3 && (o & 1u) && module_enc && state_at(1, rl) == module_enc) {
-                hit[j] = (((o >> 1) - 1) << 2) | ((m & META_KEY_IS_HOSTNAME) ? 1u : 0u);
+            if (r < n_rows && (m & (META_KEY_IS_NAME | META_KEY_IS_HOSTNAME)) && (m >> META_DEPTH_SHIFT) == 3 && module_enc) {
+                const uint32_t o = state_at(2, rl);   // its container: an object, whose container is "module"
+                if (o != 0 && (o & 1u) && state_at(1, rl) == module_enc) hit[j] = (((o >> 1) - 1) << 2) | ((m & META_KEY_IS_HOSTNAME) ? 1u : 0u);
             }
             const uint32_t h0 = __ballot_sync(FULL, (hit[j] & 3u) == 0u), h1 = __ballot_sync(FULL, (hit[j] & 3u) == 1u);
             if (lane == 0) { s_fmask[0][j * (SR_THREADS / 32) + warp] = h0; s_fmask[1][j * (SR_THREADS / 32) + warp] = h1; }
@@ -910,13 +883,6 @@ __global__ void __launch_bounds__(SR_THREADS, 6) lines_resolve_kernel(const uint
             s_fpos[f][k] = 8u + __ldg(rb.vlen + block0 + s_frow[f][k]) + __ldg(rb.klen + s_fchild[f][k]);   // { u32 len, field, u32 len, key }
         }
         __syncthreads();
-        // the listed key compares (each a chain of dependent loads), by the upper warps -- while the first two wait for the blocks before
-        for (uint32_t i = SR_THREADS - 1 - threadIdx.x; i < s_jobs; i += SR_THREADS) {
-            const uint32_t r = s_job[i].x, orow = s_job[i].y;
-            const uint32_t ao = __ldg(rb.koff + orow), al = __ldg(rb.klen + orow), bo = __ldg(rb.koff + r), bl = __ldg(rb.klen + r);
-            if (!(s_meta_of(orow) & META_HAS_KEY) || !key_less(GlobalText{raw}, ao, al, bo, bl)) ok = false;
-        }
-        if (!ok) res->fast_reject = 1;
         if (warp < 2) {
             // warp 0 carries field 0, warp 1 field 1: record bytes before each hit of the block, then the block's
             // place among the blocks.  Payload of the look-back: records (30 bits) | record bytes (32 bits), as in index.cu
@@ -966,6 +932,48 @@ __global__ void __launch_bounds__(SR_THREADS, 6) lines_resolve_kernel(const uint
                     if (m <= (f ? fx.cap[1] : fx.cap[0])) (f ? fx.off[1] : fx.off[0])[m] = (uint32_t)(((before + agg) >> 30) & 0xffffffffull);
                 }
             }
+        } else {
+            // ---- meanwhile the other six warps: every row of the block against its container
+            constexpr uint32_t WORK_WARPS = SR_THREADS / 32 - 2;
+            for (uint32_t wd = warp - 2; wd < (uint32_t)WORDS; wd += WORK_WARPS) {
+                const uint32_t rl = wd * 32u + lane, r = block0 + rl;
+                if (r >= n_rows) continue;
+                const uint32_t m = s_meta[rl], kind = m & 15u, d = m >> META_DEPTH_SHIFT;
+                const bool closes = kind == ROW_CLOSE_OBJ || kind == ROW_CLOSE_ARR;
+                // one look-up for every row: a closer wants its opener (same depth), a value its container (one up)
+                const uint32_t dq = closes ? d : d - 1u;
+                const uint32_t o = dq <= LINES_MAX_DEPTH ? state_at(dq, rl) : 0u;
+                if (closes) {
+                    // the container it closes opened at the same depth, and was of the same kind
+                    if (o == 0 || (o & 1u) != (kind == ROW_CLOSE_OBJ ? 1u : 0u)) ok = false;
+                    else {
+                        const uint32_t orow = (o >> 1) - 1;
+                        rb.koff[r] = orow;        // (TapeView::rows_direct: rows, not bracket numbers)
+                        rb.voff[orow] = r;
+                        if (module_row && orow == module_row - 1) res->module_end = r;
+                        // key order across the container that has just closed: if the next row is a member of the same
+                        // object, the member before it is the one that opened here.  About one row in fourteen at
+                        // config #4: listed, and compared below by neighbouring threads
+                        const uint32_t nm = rl + 1 < (uint32_t)LN_ROWS_PER_BLOCK ? s_meta[rl + 1] : (r + 1 < n_rows ? __ldg(rb.meta + r + 1) : 0xffffffffu);
+                        const uint32_t nk = nm & 15u;
+                        if (nm != 0xffffffffu && nk != ROW_CLOSE_OBJ && nk != ROW_CLOSE_ARR && (nm & META_HAS_KEY) && (nm >> META_DEPTH_SHIFT) == d) {
+                            const uint32_t at = atomicAdd(&s_jobs, 1u);
+                            s_job[at] = make_uint2(r + 1, orow);
+                        }
+                    }
+                } else if (d == 0) {
+                    if (r != 0) ok = false;       // at the top there is exactly one value
+                } else if (o == 0 || ((o & 1u) != 0) != ((m & META_HAS_KEY) != 0)) {
+                    ok = false;                   // inside an object a value has a key, inside an array none
+                }
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(WORK_WARPS * 32) : "memory");   // (the six warps only: the job list is complete)
+            for (uint32_t i = threadIdx.x - 64u; i < s_jobs; i += WORK_WARPS * 32) {
+                const uint32_t r = s_job[i].x, orow = s_job[i].y;
+                const uint32_t ao = __ldg(rb.koff + orow), al = __ldg(rb.klen + orow), bo = __ldg(rb.koff + r), bl = __ldg(rb.klen + r);
+                if (!(s_meta_of(orow) & META_HAS_KEY) || !key_less(GlobalText{raw}, ao, al, bo, bl)) ok = false;
+            }
+            if (!ok) res->fast_reject = 1;
         }
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < cnt0 + cnt1; i += SR_THREADS) {
