@@ -30,7 +30,8 @@ def rand_string(rng, spice):
 def rand_value(rng, depth, spice):
     r = rng.random()
     if depth > rng.choice([2, 3, 5, 8, 10]) or r < 0.5:
-        return rng.choice([rand_string(rng, spice), rand_string(rng, spice), None, True, False, 0, -1, 7, 123456789012345, 1234567890123456, 1.5, 1e21, -0.0])
+        odd = [1234567890123456, 1.5, 1e21, -0.0] if rng.random() < 0.03 else []   # (numbers that are re-formatted send the document to the host tree)
+        return rng.choice([rand_string(rng, spice), rand_string(rng, spice), None, True, False, 0, -1, 7, 123456789012345] + odd)
     if r < 0.65:
         return [rand_value(rng, depth + 1, spice) for _ in range(rng.choice([0, 0, 1, 2, 3, 40]))]
     return {rand_string(rng, spice): rand_value(rng, depth + 1, spice) for _ in range(rng.choice([0, 0, 1, 2, 3, 5, 30]))}

@@ -1258,7 +1258,9 @@ __global__ void __launch_bounds__(TP_THREADS) rows_kernel(const uint8_t *__restr
 
 __global__ void key_order_kernel(const uint8_t *__restrict__ arena, RowBuffers rb, uint32_t n_rows, BracketBuffers bb, ParseResult *res) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n_rows) return;
+    // (text that rows_kernel has just found invalid leaves rows that refer to nothing -- with whatever an earlier, larger
+    //  document left in the recycled buffers as bracket numbers and offsets: found by tools/stress_lines.py, seed 1147)
+    if (r >= n_rows || res->invalid) return;
     if (r == 0 && res->module_row != 0 && res->module_kind == ROW_OPEN_OBJ) {
         // for the module index, which runs next: the row that closes "module" (voff of an opening row is its bracket)
         const uint32_t cb = bb.match[rb.voff[res->module_row - 1]];
