@@ -4,7 +4,7 @@ line pass keeps them, with numbers, empty containers, long strings, deep nesting
 in --, then random damage to them; for every text: outcome (document or Go's error text), serialised text,
 Clusters / Nodes pairs and a Get must be the oracle's, with the line pass on and off.
 
-    python tools/stress_lines.py [seeds] [first_seed]"""
+    python tools/stress_lines.py [seeds] [first_seed] [threads]"""
 import importlib
 import json
 import os
@@ -99,15 +99,17 @@ def damage(rng, base):
     return base + rng.choice([b"\n", b" ", b"}", b",", b"\t"])
 
 
-checked = bad = kept = 0
-for seed in range(first, first + seeds):
+def one_seed(seed, toggle=True):
+    """-> (outcomes checked, mismatches, undamaged document stayed on the device)"""
     rng = random.Random(9100000 + seed)
     base = O.New("x", json.dumps(rand_document(rng), ensure_ascii=False).encode("utf-8", "surrogatepass")).Bytes()
     texts = [base] + [damage(rng, base) for _ in range(6)]
+    checked = bad = 0
     for raw in texts:
         want = outcome(O, raw)
         for line_pass in (True, False):
-            tk.state.set_line_pass(line_pass)
+            if toggle:
+                tk.state.set_line_pass(line_pass)
             got = outcome(tk, raw)
             checked += 1
             if got != want:
@@ -115,8 +117,37 @@ for seed in range(first, first + seeds):
                 print("MISMATCH seed %d line_pass %s text %r...\n  got  %r\n  want %r" % (seed, line_pass, raw[:80], str(got)[:300], str(want)[:300]))
                 os.makedirs("gpurun_out", exist_ok=True)
                 open("gpurun_out/stress_fail_%d_%d.json" % (seed, bad), "wb").write(raw)
-    tk.state.set_line_pass(True)
+    if toggle:
+        tk.state.set_line_pass(True)
     s = tk.New("x", base)
-    kept += not s.host_tree_built
-print("%d outcomes checked over %d seeds, %d mismatches; %d of the undamaged documents stayed on the device" % (checked, seeds, bad, kept))
+    return checked, bad, int(not s.host_tree_built)
+
+
+threads = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+if threads <= 1:
+    results = [one_seed(seed) for seed in range(first, first + seeds)]
+else:
+    # several handles at work at once, buffers and streams recycled between threads; the switch between the two
+    # parsers is process-wide, so one more thread flips it while the others run
+    import concurrent.futures
+    import threading
+    import time
+    stop = threading.Event()
+
+    def flipper():
+        on = True
+        while not stop.is_set():
+            on = not on
+            tk.state.set_line_pass(on)
+            time.sleep(0.003)
+
+    f = threading.Thread(target=flipper)
+    f.start()
+    with concurrent.futures.ThreadPoolExecutor(threads) as pool:
+        results = list(pool.map(lambda seed: one_seed(seed, toggle=False), range(first, first + seeds)))
+    stop.set()
+    f.join()
+    tk.state.set_line_pass(True)
+checked, bad, kept = (sum(r[i] for r in results) for i in range(3))
+print("%d outcomes checked over %d seeds on %d thread(s), %d mismatches; %d of the undamaged documents stayed on the device" % (checked, seeds, threads, bad, kept))
 sys.exit(1 if bad else 0)
