@@ -847,3 +847,29 @@ def test_invalid_text_after_a_larger_document_in_recycled_buffers(tk, oracle):
                 assert _outcome(tk, raw) == _outcome(oracle, raw), raw[:40]
     finally:
         tk.state.set_line_pass(True)
+
+
+def test_indented_form_with_text_beyond_ascii_stays_on_the_device(tk, oracle):
+    """Strings with bytes from 0x80 up, as json.Marshal writes them (valid UTF-8 as it stands), are kept in place by
+    the line pass; what Marshal would have written differently -- invalid sequences, U+2028 / U+2029, overlong
+    forms, surrogates -- and everything around such bytes goes the way the oracle says, whichever parser sees it."""
+    doc = {"module": {"cluster_a_é": {"name": "é√ß", "k8s": "日本語 \U0001F600"}, "node_a_é_1": {"hostname": "hôte-1", "ключ": "значение", "z": "x" * 130 + "é"},
+                      "node_a_é_2": {"hostname": "\u07ff\u0800\uffff\U00010000\U0010ffff"}}, "é": ["√", {"ß": None}]}
+    raw = _pretty(oracle, doc)
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    assert not a.host_tree_built and a.Bytes() == b.Bytes() == raw
+    assert a.Clusters() == b.Clusters() and a.Nodes("cluster_a_é") == b.Nodes("cluster_a_é") and len(b.Nodes("cluster_a_é")) == 2
+    assert a.Get("module.node_a_é_1.hostname") == b.Get("module.node_a_é_1.hostname") == "hôte-1".encode()
+    assert not a.host_tree_built
+    e = "é".encode()
+    bad = [b"\xc3", b"\xa9", b"\xc0\xaf", b"\xe0\x80\xaf", b"\xed\xa0\x80", b"\xf4\x90\x80\x80", b"\xf8\x88\x80\x80\x80", b"\xff", b"\xe2\x80\xa8", b"\xe2\x80\xa9",
+           b"\xe2\x80\xaa", b"\xc3\xa9\xc3", "\u2027".encode(), b"\xf0\x9f\x98", b"\xc2\x80", b"\xdf\xbf", b"\xef\xbf\xbf", b"\xf4\x8f\xbf\xbf"]
+    try:
+        for line_pass in (True, False):
+            tk.state.set_line_pass(line_pass)
+            for seq in bad:
+                for at in (raw.find(e), raw.rfind(e)):
+                    t = raw[:at] + seq + raw[at + len(e):]
+                    assert _outcome(tk, t) == _outcome(oracle, t), (seq, at, line_pass)
+    finally:
+        tk.state.set_line_pass(True)

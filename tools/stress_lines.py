@@ -21,9 +21,12 @@ PLAIN = "abcdefghijklmnopqrstuvwxyzABCXYZ0123456789_-.$/:~ '()=?#@!*+,;[]{}|^%`"
 SPICE = "é√ <>&\t\n\"\\\x01"
 
 
+UTF8 = "é√ß日本語\U0001F600\u07ff\u0800\uffff"
+
+
 def rand_string(rng, spice):
     n = rng.choice([0, 1, 3, 7, 8, 9, 15, 16, 17, 30, 60, 100, 119, 120, 121, 130, 300, 600, 9000]) if rng.random() < 0.15 else rng.randrange(0, 14)
-    alphabet = PLAIN + (SPICE if spice else "")
+    alphabet = PLAIN + (SPICE if spice == 1 else UTF8 if spice == 2 else "")   # 2: text the line pass keeps in place
     return "".join(rng.choice(alphabet) for _ in range(n))
 
 
@@ -38,7 +41,7 @@ def rand_value(rng, depth, spice):
 
 
 def rand_document(rng):
-    spice = rng.random() < 0.15
+    spice = rng.choice([0, 0, 0, 0, 1, 2, 2])
     mod = {}
     for c in range(rng.randrange(0, 6)):
         ck = "cluster_%s_%s" % (rng.choice(["a", "aws", "b"]), rand_string(rng, False)[:5] or "c")
@@ -83,7 +86,7 @@ def damage(rng, base):
     r = rng.random()
     if r < 0.35:
         i = rng.randrange(len(base))
-        return base[:i] + bytes([rng.choice(b' \t\n",:{}[]\\0a1-.eE<\xc3\x00')]) + base[i + (rng.random() < 0.7):]
+        return base[:i] + bytes([rng.choice(b' \t\n",:{}[]\\0a1-.eE<\xc3\x00\xe2\x80\xa8\xed\xa0\xf4\x90\xc0\xff')]) + base[i + (rng.random() < 0.7):]
     if r < 0.55:
         i = rng.randrange(len(lines))
         return b"\n".join(lines[:i] + lines[i + 1:])

@@ -249,6 +249,38 @@ struct GlobalText {
 __device__ __forceinline__ u64 big_endian(u64 x) {
     return ((u64)__byte_perm((uint32_t)x, 0, 0x0123) << 32) | __byte_perm((uint32_t)(x >> 32), 0, 0x0123);
 }
+// The string whose first byte is at p (right after its opening quote): where its closing quote is, which must be
+// before `end`.  A string of bytes that all stand for themselves is "plain".  One with bytes from 0x80 up is taken
+// as it stands if those bytes are valid UTF-8 and spell neither U+2028 nor U+2029: that is how json.Marshal writes
+// such a string (invalid sequences would come back as \ufffd, the two separators as \u2028 / \u2029 -- not the
+// same text), and the decoded string is then the bytes themselves, in place.  Anything else -- an escape, a control
+// byte, < > & as they are -- is not the indented form: 0.
+template <class Reader>
+__device__ __forceinline__ u64 string_close(const Reader &raw, u64 p, u64 end, bool *plain) {
+    *plain = true;
+    const u64 q = raw.string_end(p, end);
+    if (q) return q;
+    *plain = false;
+    for (u64 i = p; i < end;) {
+        const uint32_t c = raw.byte(i);
+        if (c == '"') return i;
+        if (c < 0x20 || c == '\\' || c == '<' || c == '>' || c == '&') return 0;
+        if (c < 0x80) { i++; continue; }
+        uint32_t lo = 0x80, hi = 0xBF, len;
+        if (c >= 0xC2 && c <= 0xDF) len = 2;
+        else if (c >= 0xE0 && c <= 0xEF) { len = 3; if (c == 0xE0) lo = 0xA0; if (c == 0xED) hi = 0x9F; }
+        else if (c >= 0xF0 && c <= 0xF4) { len = 4; if (c == 0xF0) lo = 0x90; if (c == 0xF4) hi = 0x8F; }
+        else return 0;
+        if (i + len > end) return 0;
+        const uint32_t c1 = raw.byte(i + 1);
+        if (c1 < lo || c1 > hi) return 0;
+        for (uint32_t k = 2; k < len; k++)
+            if ((raw.byte(i + k) & 0xC0u) != 0x80u) return 0;
+        if (c == 0xE2 && c1 == 0x80 && (raw.byte(i + 2) | 1u) == 0xA9u) return 0;   // U+2028, U+2029
+        i += len;
+    }
+    return 0;
+}
 // strictly ascending, bytewise (the shorter first on a tie)?
 template <class T>
 __device__ __forceinline__ bool key_less(const T &raw, u64 a, uint32_t al, u64 b, uint32_t bl) {
@@ -306,19 +338,20 @@ __device__ __forceinline__ bool line_to_row(const Reader &raw, u64 s, u64 e, u64
     u64 after;   // the byte after the value
     bool value_done = false;
     if (c == '"') {
-        const u64 q = raw.string_end(p + 1, e);
+        bool plain;
+        const u64 q = string_close(raw, p + 1, e, &plain);
         if (!q) return false;
         if (q + 1 < e && raw.byte(q + 1) == ':') {
             // "key": value
             if (q + 2 >= e || raw.byte(q + 2) != ' ') return false;
-            meta |= META_HAS_KEY | META_KEY_PLAIN;
+            meta |= META_HAS_KEY | (plain ? META_KEY_PLAIN : 0u);
             koff = (uint32_t)(p + 1);
             klen = (uint32_t)(q - p - 1);
             p = q + 3;
             if (p >= e) return false;
             c = raw.byte(p);
         } else {
-            meta |= ROW_STR | META_VAL_PLAIN;
+            meta |= ROW_STR | (plain ? META_VAL_PLAIN : 0u);
             voff = (uint32_t)(p + 1);
             vlen = (uint32_t)(q - p - 1);
             after = q + 1;
@@ -327,9 +360,10 @@ __device__ __forceinline__ bool line_to_row(const Reader &raw, u64 s, u64 e, u64
     }
     if (!value_done) {
         if (c == '"') {
-            const u64 q = raw.string_end(p + 1, e);
+            bool plain;
+            const u64 q = string_close(raw, p + 1, e, &plain);
             if (!q) return false;
-            meta |= ROW_STR | META_VAL_PLAIN;
+            meta |= ROW_STR | (plain ? META_VAL_PLAIN : 0u);
             voff = (uint32_t)(p + 1);
             vlen = (uint32_t)(q - p - 1);
             after = q + 1;
@@ -380,7 +414,8 @@ __device__ __forceinline__ bool line_to_row(const Reader &raw, u64 s, u64 e, u64
             if (meta & META_HAS_KEY) {
                 // the next member of the same object: its key must sort strictly after this one
                 if (cn != '"') return false;
-                const u64 qe = raw.string_end(q + 1, n);    // (a newline on the way is not a byte that stands for itself)
+                bool next_plain;
+                const u64 qe = string_close(raw, q + 1, n, &next_plain);    // (a newline on the way is not a byte that stands for itself)
                 if (!qe || !key_less(raw, koff, klen, q + 1, (uint32_t)(qe - q - 1))) return false;
             }
         }
@@ -537,7 +572,7 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
     const u64 Q0 = t.bits(t.qm, s), Q1 = t.bits(t.qm, s + 64);
     const u64 S0 = t.bits(t.stopm, s), S1 = t.bits(t.stopm, s + 64);
     const u64 in0 = low_bits(L), in1 = L > 64 ? low_bits(L - 64) : 0ull;       // the line's own bits
-    bad = bad || ((S0 & in0 & ~low_bits(min(d, 63u))) | (S1 & in1)) != 0;          // something that cannot stand for itself
+    const bool stops = ((S0 & in0 & ~low_bits(min(d, 63u))) | (S1 & in1)) != 0;   // something that cannot stand for itself: line_to_row looks closer
     u64 q0 = Q0 & in0, q1 = Q1 & in1;
     const uint32_t nq = (uint32_t)__popcll(q0) + (uint32_t)__popcll(q1);
     bad = bad || (nq != 0 && nq != 2 && nq != 4);
@@ -592,7 +627,7 @@ __device__ __forceinline__ int line_fast(const MaskText &t, u64 s, u64 e, u64 n,
         else bad = !key_less_in(t, k8, so + d + 1, klen, so + from, (uint32_t)__ffsll((long long)qn) - 1u);
     }
     if (bad) return 0;
-    if (verdict == 2) return 2;
+    if (verdict == 2 || stops) return 2;
     // the row, with what the module index and the verdict want to know about it (finish_row, from the window)
     if (d == 3 && (kind & 15u) == ROW_STR && key_shape) {
         if (klen == 4 && (uint32_t)k8 == 0x656d616eu) meta |= META_KEY_IS_NAME;                    // "name"
