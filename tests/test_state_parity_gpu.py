@@ -873,3 +873,36 @@ def test_indented_form_with_text_beyond_ascii_stays_on_the_device(tk, oracle):
                     assert _outcome(tk, t) == _outcome(oracle, t), (seq, at, line_pass)
     finally:
         tk.state.set_line_pass(True)
+
+
+def test_indented_form_with_escaped_values_stays_on_the_device(tk, oracle):
+    """String values that read differently once decoded -- escape sequences, < > & (written \\u003c ...), control
+    characters, invalid UTF-8 left as it is -- are decoded into the side arena by the line pass, as the general
+    parser does; keys of that kind, and more such text than the side arena has room for, send the document to the
+    general parser.  Either way the results are the oracle's."""
+    vals = ['a"b', "back\\slash", "tab\there", "line\nfeed\r", "<tag attr=\"x\">&amp;</tag>", "\x01\x1f\x7f", "é<√>", "  ", "/", "", "\\u0041 literally",
+            "x" * 130 + "<", "q" * 9000 + "&" + "r" * 300, "\U0001F600&"]
+    doc = {"module": {"cluster_a_b": {"name": 'n"<1>', "v": vals}, "node_a_b_1": {"hostname": "h\\1", "labels": {"k": "<&>"}}, "node_a_b_2": {"hostname": "plain"}},
+           "z": vals[::-1]}
+    raw = _pretty(oracle, doc)
+    assert b"\\u003c" in raw and b'\\"' in raw and b"\\\\" in raw
+    a, b = tk.New("x", raw), oracle.New("x", raw)
+    assert not a.host_tree_built and a.Bytes() == b.Bytes() == raw
+    assert a.Clusters() == b.Clusters() == {b'n"<1>': b"cluster_a_b"} and a.Nodes("cluster_a_b") == b.Nodes("cluster_a_b") and len(b.Nodes("cluster_a_b")) == 2
+    assert a.Get("module.node_a_b_1.hostname") == b.Get("module.node_a_b_1.hostname") == b"h\\1" and not a.host_tree_built
+    a.Delete("module.node_a_b_2"); b.Delete("module.node_a_b_2")
+    a.AddNode("cluster_a_b", "3", {"hostname": "<3>"}); b.AddNode("cluster_a_b", "3", {"hostname": "<3>"})
+    assert a.Bytes() == b.Bytes() and not a.host_tree_built
+    # escapes written another way than Marshal writes them, invalid UTF-8 as it stands: valid JSON all the same
+    for old, new in ((b"\\u003c", b"\\u003C"), (b"\\u003c", b"<"), (b"\\n", b"\\u000a"), (b"/", b"\\/"), (b"\\u0001", b"\\u0001\\ud83d\\ude00\\ud83d"), ("é".encode(), b"\xc3"),
+                     ("é".encode(), b"\\u00e9"), (b"plain", b"pl\\u0061in"), (b'"hostname": "h', b'"host\\u006eame": "h'), (b'"z": [', b'"\\u007a": [')):
+        assert old in raw, old
+        t = raw.replace(old, new)
+        assert _outcome(tk, t) == _outcome(oracle, t), (old, new)
+    for old, new in ((b"\\u003c", b"\\u003"), (b"\\u003c", b"\\x3c"), (b"\\n", b"\n"), (b"\\t", b"\t"), (b'\\"', b'"'), (b"\\\\", b"\\")):
+        t = raw.replace(old, new, 1)
+        assert _outcome(tk, t) == _outcome(oracle, t), (old, new)
+    # more decoded text than the side arena takes (an eighth of the text): still right
+    many = _pretty(oracle, {"k%04d" % i: "<&>" * 40 for i in range(400)})
+    s = tk.New("x", many)
+    assert s.Bytes() == many == oracle.New("x", many).Bytes()

@@ -41,7 +41,7 @@ def rand_value(rng, depth, spice):
 
 
 def rand_document(rng):
-    spice = rng.choice([0, 0, 0, 0, 1, 2, 2])
+    spice = rng.choice([0, 0, 0, 1, 1, 2, 2])
     mod = {}
     for c in range(rng.randrange(0, 6)):
         ck = "cluster_%s_%s" % (rng.choice(["a", "aws", "b"]), rand_string(rng, False)[:5] or "c")

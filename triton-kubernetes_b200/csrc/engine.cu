@@ -125,6 +125,8 @@ static std::atomic<bool> g_default_timing{false};
 void set_default_timing(bool on) { g_default_timing = on; }
 static std::atomic<int> g_line_pass{-1};   // -1: not asked yet (TK_NO_FAST_PATH in the environment switches it off)
 void set_line_pass(bool on) { g_line_pass.store(on ? 1 : 0); }
+// bytes of side arena the line pass may fill with decoded strings (more than that: the general pipeline takes the text)
+static size_t lines_side_cap(size_t n) { return std::min<size_t>(n / 8 + 4096, 0xffffff00ull - std::min<size_t>(0xffffff00ull, (size_t)p1_tiles(n) * P1_TILE + 128)); }
 static bool line_pass_on() {
     int v = g_line_pass.load();
     if (v < 0) { v = getenv("TK_NO_FAST_PATH") ? 0 : 1; g_line_pass.store(v); }
@@ -603,7 +605,8 @@ int Engine::upload_text(const char *raw, size_t n, std::string *err) {
     if (n >= 0xfff00000ull) { *err = "document too large: the text must stay below 4 GiB"; return TK_ELIMIT; }
     const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 64;
     cudaError_t e;
-    if ((e = d_arena_.reserve(padded)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
+    // (with room behind the text for the strings the line pass has to decode: lines_side_cap)
+    if ((e = d_arena_.reserve(line_pass_on() ? ((padded + 15) & ~size_t(15)) + lines_side_cap(n) + 32 : padded)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
     // Text in ordinary (pageable) host memory -- what a Go caller holds: ioutil.ReadFile's slice,
     // backend/local/backend.go:60-65 -- is not copied by the driver's own staging (a few GB/s) but
     // through two pinned blocks of this handle: the calling thread fills one while the copy engine
@@ -646,7 +649,8 @@ int Engine::upload_text_device(const void *dev_raw, size_t n, std::string *err) 
     if (n >= 0xfff00000ull) { *err = "document too large: the text must stay below 4 GiB"; return TK_ELIMIT; }
     const size_t padded = (size_t)p1_tiles(n) * P1_TILE + 64;
     cudaError_t e;
-    if ((e = d_arena_.reserve(padded)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
+    // (with room behind the text for the strings the line pass has to decode: lines_side_cap)
+    if ((e = d_arena_.reserve(line_pass_on() ? ((padded + 15) & ~size_t(15)) + lines_side_cap(n) + 32 : padded)) != cudaSuccess) return fail(e, "cudaMalloc(arena)", err);
     // (the line pass brings the text over itself, in its first pass over it: parse_lines)
     pending_text_ = n && line_pass_on() && (reinterpret_cast<uintptr_t>(dev_raw) & 15u) == 0 ? static_cast<const uint8_t *>(dev_raw) : nullptr;
     if (n && !pending_text_ && (e = cudaMemcpyAsync(d_arena_.p, dev_raw, n, cudaMemcpyDeviceToDevice, stream_)) != cudaSuccess) return fail(e, "copy text", err);
@@ -673,6 +677,11 @@ int Engine::parse_lines(size_t n, ParseResult *out, bool *accepted, std::string 
     if ((e = d_tiles_.reserve(lines_open_state_words((uint32_t)row_cap) * 4 + 64)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);
     RowBuffers rb{d_meta_.as<uint32_t>(), d_koff_.as<uint32_t>(), d_klen_.as<uint32_t>(), d_voff_.as<uint32_t>(), d_vlen_.as<uint32_t>(),
                   d_tiles_.as<uint32_t>()};
+    // strings that have to be decoded go behind the text, as in the general parse (what upload_text left room for)
+    const size_t side_base = ((size_t)p1_tiles(n) * P1_TILE + 64 + 15) & ~size_t(15);
+    rb.side = d_arena_.as<uint8_t>();
+    rb.side_base = (uint32_t)side_base;
+    rb.side_cap = d_arena_.cap > side_base + 32 ? (uint32_t)std::min<size_t>(d_arena_.cap - side_base - 32, lines_side_cap(n)) : 0u;
     uint32_t *scratch = d_scratch_.as<uint32_t>();
     // the module index's lists are made by the last stage (the row count is still on the device: sized by bounds)
     for (int f = 0; f < 2; f++) {
@@ -704,6 +713,10 @@ int Engine::parse_lines(size_t n, ParseResult *out, bool *accepted, std::string 
     if (h_res_.p->fast_reject || h_res_.p->n_rows == 0 || h_res_.p->n_rows > row_cap) return TK_OK;
     *out = *h_res_.p;
     *accepted = true;
+    if (out->side_bytes) {   // (more may have been asked for than rows refer to -- a line looked at twice --: all of it counts as used)
+        arena_used_ = side_base + (size_t)std::min<unsigned long long>(out->side_bytes, rb.side_cap);
+        tape_.arena_bytes = (uint32_t)arena_used_;
+    }
     const uint32_t n_rows = out->n_rows;
     if ((e = d_off_.reserve(((size_t)n_rows + 1) * 4)) != cudaSuccess) return fail(e, "cudaMalloc(off)", err);
     if ((e = d_scratch_.reserve(scan_scratch_words(n_rows) * 8)) != cudaSuccess) return fail(e, "cudaMalloc(scratch)", err);

@@ -13,6 +13,7 @@
 #include "bulkcopy.cuh"
 #include "index.cuh"
 #include "pdl.cuh"
+#include "unquote.cuh"
 
 namespace tk {
 namespace {
@@ -250,36 +251,67 @@ __device__ __forceinline__ u64 big_endian(u64 x) {
     return ((u64)__byte_perm((uint32_t)x, 0, 0x0123) << 32) | __byte_perm((uint32_t)(x >> 32), 0, 0x0123);
 }
 // The string whose first byte is at p (right after its opening quote): where its closing quote is, which must be
-// before `end`.  A string of bytes that all stand for themselves is "plain".  One with bytes from 0x80 up is taken
-// as it stands if those bytes are valid UTF-8 and spell neither U+2028 nor U+2029: that is how json.Marshal writes
-// such a string (invalid sequences would come back as \ufffd, the two separators as \u2028 / \u2029 -- not the
-// same text), and the decoded string is then the bytes themselves, in place.  Anything else -- an escape, a control
-// byte, < > & as they are -- is not the indented form: 0.
+// before `end`, and how the row can refer to it:
+//   STR_PLAIN    every byte stands for itself;
+//   STR_IN_PLACE bytes from 0x80 up, all of them valid UTF-8 spelling neither U+2028 nor U+2029: that is how
+//                json.Marshal writes such a string, so the decoded string is the bytes themselves, where they are;
+//   STR_DECODE   a valid JSON string that reads differently once decoded (escape sequences, < > & as they are,
+//                invalid UTF-8, the two separators): the caller decodes it into the side arena (unquote.cuh).
+// 0: not a JSON string at all (a control byte, a bad escape, no closing quote) -- the general parser has the words for it.
+enum { STR_PLAIN = 0, STR_IN_PLACE = 1, STR_DECODE = 2 };
 template <class Reader>
-__device__ __forceinline__ u64 string_close(const Reader &raw, u64 p, u64 end, bool *plain) {
-    *plain = true;
+__device__ __forceinline__ u64 string_close(const Reader &raw, u64 p, u64 end, int *mode) {
+    *mode = STR_PLAIN;
     const u64 q = raw.string_end(p, end);
     if (q) return q;
-    *plain = false;
+    int m = STR_IN_PLACE;
     for (u64 i = p; i < end;) {
         const uint32_t c = raw.byte(i);
-        if (c == '"') return i;
-        if (c < 0x20 || c == '\\' || c == '<' || c == '>' || c == '&') return 0;
-        if (c < 0x80) { i++; continue; }
-        uint32_t lo = 0x80, hi = 0xBF, len;
+        if (c == '"') { *mode = m; return i; }
+        if (c < 0x20) return 0;
+        if (c == '\\') {
+            if (i + 1 >= end) return 0;
+            const uint32_t e = raw.byte(i + 1);
+            if (e == 'u') {
+                if (i + 6 > end) return 0;
+                for (uint32_t k = 2; k < 6; k++)
+                    if (!is_hex(raw.byte(i + k))) return 0;
+                i += 6;
+            } else if (e == '"' || e == '\\' || e == '/' || e == 'b' || e == 'f' || e == 'n' || e == 'r' || e == 't') {
+                i += 2;
+            } else return 0;
+            m = STR_DECODE;
+            continue;
+        }
+        if (c < 0x80) { if (c == '<' || c == '>' || c == '&') m = STR_DECODE; i++; continue; }
+        uint32_t lo = 0x80, hi = 0xBF, len = 0;
         if (c >= 0xC2 && c <= 0xDF) len = 2;
         else if (c >= 0xE0 && c <= 0xEF) { len = 3; if (c == 0xE0) lo = 0xA0; if (c == 0xED) hi = 0x9F; }
         else if (c >= 0xF0 && c <= 0xF4) { len = 4; if (c == 0xF0) lo = 0x90; if (c == 0xF4) hi = 0x8F; }
-        else return 0;
-        if (i + len > end) return 0;
-        const uint32_t c1 = raw.byte(i + 1);
-        if (c1 < lo || c1 > hi) return 0;
-        for (uint32_t k = 2; k < len; k++)
-            if ((raw.byte(i + k) & 0xC0u) != 0x80u) return 0;
-        if (c == 0xE2 && c1 == 0x80 && (raw.byte(i + 2) | 1u) == 0xA9u) return 0;   // U+2028, U+2029
-        i += len;
+        bool ok = len != 0 && i + len <= end;
+        if (ok) {
+            const uint32_t c1 = raw.byte(i + 1);
+            ok = c1 >= lo && c1 <= hi;
+            for (uint32_t k = 2; ok && k < len; k++) ok = (raw.byte(i + k) & 0xC0u) == 0x80u;
+            if (ok && c == 0xE2 && c1 == 0x80 && (raw.byte(i + 2) | 1u) == 0xA9u) ok = false;   // U+2028, U+2029: written escaped
+        }
+        if (ok) i += len;
+        else { m = STR_DECODE; i++; }   // (decodes to U+FFFD, or to the separator itself)
     }
     return 0;
+}
+// A string value that has to be decoded: room for it taken from the side arena (behind the text, rb.side_base
+// onwards), the string written there.  false: the arena is full (the document goes to the general parser).
+template <class Reader>
+__device__ __forceinline__ bool decode_value(const Reader &raw, u64 a, u64 b, const RowBuffers &rb, ParseResult *res, uint32_t *voff, uint32_t *vlen) {
+    const uint8_t *src = raw.raw + a;
+    const uint32_t n = (uint32_t)(b - a), len = unquote(src, n, nullptr);
+    const unsigned long long at = atomicAdd(&res->side_bytes, (unsigned long long)len);
+    if (at + len > rb.side_cap) return false;
+    unquote(src, n, rb.side + rb.side_base + at);
+    *voff = rb.side_base + (uint32_t)at;
+    *vlen = len;
+    return true;
 }
 // strictly ascending, bytewise (the shorter first on a tie)?
 template <class T>
@@ -338,34 +370,37 @@ __device__ __forceinline__ bool line_to_row(const Reader &raw, u64 s, u64 e, u64
     u64 after;   // the byte after the value
     bool value_done = false;
     if (c == '"') {
-        bool plain;
-        const u64 q = string_close(raw, p + 1, e, &plain);
+        int mode;
+        const u64 q = string_close(raw, p + 1, e, &mode);
         if (!q) return false;
         if (q + 1 < e && raw.byte(q + 1) == ':') {
-            // "key": value
-            if (q + 2 >= e || raw.byte(q + 2) != ' ') return false;
-            meta |= META_HAS_KEY | (plain ? META_KEY_PLAIN : 0u);
+            // "key": value   (a key that would have to be decoded: left to the general parser -- the order of keys is
+            // checked on the text as it stands)
+            if (q + 2 >= e || raw.byte(q + 2) != ' ' || mode == STR_DECODE) return false;
+            meta |= META_HAS_KEY | (mode == STR_PLAIN ? META_KEY_PLAIN : 0u);
             koff = (uint32_t)(p + 1);
             klen = (uint32_t)(q - p - 1);
             p = q + 3;
             if (p >= e) return false;
             c = raw.byte(p);
         } else {
-            meta |= ROW_STR | (plain ? META_VAL_PLAIN : 0u);
+            meta |= ROW_STR | (mode == STR_PLAIN ? META_VAL_PLAIN : 0u);
             voff = (uint32_t)(p + 1);
             vlen = (uint32_t)(q - p - 1);
+            if (mode == STR_DECODE && !decode_value(raw, p + 1, q, rb, res, &voff, &vlen)) return false;
             after = q + 1;
             value_done = true;
         }
     }
     if (!value_done) {
         if (c == '"') {
-            bool plain;
-            const u64 q = string_close(raw, p + 1, e, &plain);
+            int mode;
+            const u64 q = string_close(raw, p + 1, e, &mode);
             if (!q) return false;
-            meta |= ROW_STR | (plain ? META_VAL_PLAIN : 0u);
+            meta |= ROW_STR | (mode == STR_PLAIN ? META_VAL_PLAIN : 0u);
             voff = (uint32_t)(p + 1);
             vlen = (uint32_t)(q - p - 1);
+            if (mode == STR_DECODE && !decode_value(raw, p + 1, q, rb, res, &voff, &vlen)) return false;
             after = q + 1;
         } else if (c == '{' || c == '[') {
             const uint32_t closer = c == '{' ? '}' : ']';
@@ -414,9 +449,9 @@ __device__ __forceinline__ bool line_to_row(const Reader &raw, u64 s, u64 e, u64
             if (meta & META_HAS_KEY) {
                 // the next member of the same object: its key must sort strictly after this one
                 if (cn != '"') return false;
-                bool next_plain;
-                const u64 qe = string_close(raw, q + 1, n, &next_plain);    // (a newline on the way is not a byte that stands for itself)
-                if (!qe || !key_less(raw, koff, klen, q + 1, (uint32_t)(qe - q - 1))) return false;
+                int next_mode;
+                const u64 qe = string_close(raw, q + 1, n, &next_mode);    // (a newline on the way is not a byte that stands for itself)
+                if (!qe || next_mode == STR_DECODE || !key_less(raw, koff, klen, q + 1, (uint32_t)(qe - q - 1))) return false;
             }
         }
     }

@@ -9,8 +9,10 @@
 // key order), and one pass over the rows pairs closers with openers and checks what only the
 // enclosing container can tell (keys in objects, none in arrays, bracket kinds, order across a
 // closed container).  Strings with text beyond ASCII are kept where they stand if they are valid
-// UTF-8 as json.Marshal writes it.  Anything that is not exactly that form -- an escape, a byte
-// Marshal would have escaped, an invalid UTF-8 sequence, a number that would be re-formatted, a key out of order, nesting deeper than LINES_MAX_DEPTH, a
+// UTF-8 as json.Marshal writes it; string VALUES that read differently once decoded (escape
+// sequences, bytes Marshal would have escaped, invalid UTF-8) are decoded into a side arena behind
+// the text, as the general parser does.  Anything that is not that form -- a key that would have
+// to be decoded, a number that would be re-formatted, a key out of order, nesting deeper than LINES_MAX_DEPTH, a
 // space too many -- makes the pass say "not for me" (ParseResult::fast_reject) and the caller
 // runs the general pipeline on the same text, which also owns every error message.  A text the
 // pass accepts is valid JSON in canonical form, and the tape it leaves is row for row the one the

@@ -138,7 +138,14 @@ cudaError_t launch_decode_lengths(const uint8_t *raw, TokenBuffers tb, DecodeBuf
 cudaError_t launch_decode_write(uint8_t *arena, uint32_t side_base, TokenBuffers tb, DecodeBuffers db, uint32_t n_dec,
                                 cudaStream_t s);
 // rows: the tape arrays are written in input order; arena = raw text (+ side arena)
-struct RowBuffers { uint32_t *meta, *koff, *klen, *voff, *vlen; uint32_t *open = nullptr; };   // open: lines.cu only
+struct RowBuffers {
+    uint32_t *meta, *koff, *klen, *voff, *vlen;
+    // lines.cu only: the open-container words of its last stage; the arena, where its side arena starts and how many
+    // bytes of it there are (strings that have to be decoded go there, as in the general parse)
+    uint32_t *open = nullptr;
+    uint8_t *side = nullptr;
+    uint32_t side_base = 0, side_cap = 0;
+};
 cudaError_t launch_rows(const uint8_t *raw, size_t n, TokenBuffers tb, uint32_t n_tok, const TilePrefix *tiles,
                         BracketBuffers bb, DecodeBuffers db, uint32_t n_dec, RowBuffers rb, uint32_t n_rows,
                         ParseResult *res, cudaStream_t s);
