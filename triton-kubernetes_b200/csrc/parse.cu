@@ -1186,7 +1186,10 @@ __global__ void key_order_kernel(const uint8_t *__restrict__ arena, RowBuffers r
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     // (text that rows_kernel has just found invalid leaves rows that refer to nothing -- with whatever an earlier, larger
     //  document left in the recycled buffers as bracket numbers and offsets: found by tools/stress_lines.py, seed 1147)
-    if (r >= n_rows || res->invalid) return;
+    __shared__ uint32_t s_invalid;   // (asked once per block: a million threads asking for the same word queue up at one L2 line)
+    if (threadIdx.x == 0) s_invalid = res->invalid;
+    __syncthreads();
+    if (r >= n_rows || s_invalid) return;
     if (r == 0 && res->module_row != 0 && res->module_kind == ROW_OPEN_OBJ) {
         // for the module index, which runs next: the row that closes "module" (voff of an opening row is its bracket)
         const uint32_t cb = bb.match[rb.voff[res->module_row - 1]];
