@@ -4,7 +4,7 @@ line pass keeps them, with numbers, empty containers, long strings, deep nesting
 in --, then random damage to them; for every text: outcome (document or Go's error text), serialised text,
 Clusters / Nodes pairs and a Get must be the oracle's, with the line pass on and off.
 
-    python tools/stress_lines.py [seeds] [first_seed] [threads]"""
+    python tools/stress_lines.py [seeds] [first_seed] [threads]          (STRESS_TEXT_ON_DEVICE=1: through tk_state_new_device)"""
 import importlib
 import json
 import os
@@ -61,9 +61,20 @@ def rand_document(rng):
     return doc
 
 
+ON_DEVICE = bool(os.environ.get("STRESS_TEXT_ON_DEVICE"))   # the product gets its text in device memory (tk_state_new_device)
+
+
 def outcome(mod, raw):
     try:
-        s = mod.New("x", raw)
+        if ON_DEVICE and mod is tk and len(raw):
+            import torch
+            shift = len(raw) % 3 * 8                               # 0, 8 or 16: the line pass copies from 16-byte aligned text only
+            buf = torch.empty(len(raw) + 32, dtype=torch.uint8, device="cuda")
+            buf[shift:shift + len(raw)] = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to("cuda")
+            torch.cuda.synchronize()
+            s = mod.state.NewDevice("x", buf.data_ptr() + shift, len(raw))
+        else:
+            s = mod.New("x", raw)
     except Exception as e:
         return ("err", str(e))
     out = ["ok", s.Bytes()]
