@@ -41,45 +41,22 @@ __device__ __forceinline__ u64 newline_mask(const uint4 (&x)[4]) {
     return m;
 }
 
-// line ends of the 64-byte chunk that starts at `chunk` (16-byte aligned): newlines, and position n itself (the
-// end of the text).  COPY: the text is still where the caller has it on the device (src, 16-byte aligned) and is
-// brought into the arena on the way -- one pass over it instead of a copy and then this one; only bytes below n
-// are read from src and written to raw (the padding behind the text is the caller's memset).
-template <bool COPY>
-__device__ __forceinline__ u64 chunk_line_ends(uint8_t *raw, const uint8_t *__restrict__ src, u64 chunk, u64 n) {
+// line ends of the 64-byte chunk of the arena that starts at `chunk` (16-byte aligned): newlines, and position n
+// itself (the end of the text)
+__device__ __forceinline__ u64 chunk_line_ends(const uint8_t *raw, u64 chunk, u64 n) {
     if (chunk > n) return 0;
     uint4 x[4];
-    if (!COPY) {
 #pragma unroll
-        for (int v = 0; v < 4; v++) x[v] = __ldg(reinterpret_cast<const uint4 *>(raw + chunk) + v);
-    } else if (chunk + 64 <= n) {
-#pragma unroll
-        for (int v = 0; v < 4; v++) x[v] = __ldg(reinterpret_cast<const uint4 *>(src + chunk) + v);
-#pragma unroll
-        for (int v = 0; v < 4; v++) reinterpret_cast<uint4 *>(raw + chunk)[v] = x[v];
-    } else {
-        uint32_t w[16];
-#pragma unroll
-        for (int i = 0; i < 16; i++) {
-            uint32_t y = 0x20202020u;
-#pragma unroll
-            for (int b = 0; b < 4; b++)
-                if (chunk + i * 4 + b < n) {
-                    const uint32_t c = src[chunk + i * 4 + b];
-                    raw[chunk + i * 4 + b] = (uint8_t)c;
-                    y = (y & ~(0xffu << (8 * b))) | (c << (8 * b));
-                }
-            w[i] = y;
-        }
-#pragma unroll
-        for (int v = 0; v < 4; v++) x[v] = make_uint4(w[v * 4], w[v * 4 + 1], w[v * 4 + 2], w[v * 4 + 3]);
-    }
+    for (int v = 0; v < 4; v++) x[v] = __ldg(reinterpret_cast<const uint4 *>(raw + chunk) + v);
     u64 m = newline_mask(x);
     if (n - chunk < 64) m = (m & low_bits((uint32_t)(n - chunk))) | (1ull << (n - chunk));
     return m;
 }
 
 // ---- stage 0: count -------------------------------------------------------------------------
+// COPY: the text is still where the caller has it on the device (src, 16-byte aligned) and is brought into the arena
+// on the way -- one pass over it instead of a copy and then this one; only bytes below n are read from src and
+// written to raw (the padding behind the text is the caller's memset).
 template <bool COPY>
 __global__ void __launch_bounds__(LN_THREADS) lines_count_kernel(uint8_t *raw, const uint8_t *__restrict__ src, u64 n, uint32_t *__restrict__ counts,
                                                                 uint32_t *__restrict__ last_end, uint32_t *__restrict__ open_state,
@@ -91,7 +68,38 @@ __global__ void __launch_bounds__(LN_THREADS) lines_count_kernel(uint8_t *raw, c
         for (uint32_t i = threadIdx.x; i < per && w0 + i < open_words; i += LN_THREADS) open_state[w0 + i] = 0;
     }
     const u64 chunk = (u64)blockIdx.x * LN_TILE + (u64)threadIdx.x * LN_CHUNK;
-    const u64 m = chunk_line_ends<COPY>(raw, src, chunk, n);
+    u64 m;
+    if (COPY) {
+        // The tile goes through shared memory: one bulk copy in (the copy unit, no registers in between), the line ends
+        // read off it there, one bulk copy out to the arena.  Bulk copies move multiples of 16 bytes: what is left of
+        // the text's last tile behind the last multiple is moved by hand.
+        __shared__ __align__(16) uint8_t s_tile[LN_TILE];
+        __shared__ __align__(8) uint64_t s_bar;
+        const u64 tile0 = (u64)blockIdx.x * LN_TILE;
+        const uint32_t avail = n > tile0 ? (uint32_t)min((u64)LN_TILE, n - tile0) : 0u, bulk = avail & ~15u;
+        if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+        __syncthreads();
+        if (threadIdx.x == 0 && bulk) bulk_load(s_tile, src + tile0, bulk, &s_bar);
+        if (threadIdx.x < avail - bulk) {
+            const uint8_t b = src[tile0 + bulk + threadIdx.x];
+            s_tile[bulk + threadIdx.x] = b;
+            raw[tile0 + bulk + threadIdx.x] = b;
+        }
+        if (bulk) mbar_wait(&s_bar, 0);
+        __syncthreads();   // (the bytes moved by hand)
+        if (threadIdx.x == 0 && bulk) bulk_store(raw + tile0, s_tile, bulk);
+        if (chunk > n) m = 0;
+        else {
+            uint4 x[4];
+#pragma unroll
+            for (int v = 0; v < 4; v++) x[v] = reinterpret_cast<const uint4 *>(s_tile + threadIdx.x * LN_CHUNK)[v];
+            m = newline_mask(x);   // (bytes of the tile behind the end of the text are whatever was there: masked off)
+            if (n - chunk < 64) m = (m & low_bits((uint32_t)(n - chunk))) | (1ull << (n - chunk));
+        }
+        if (threadIdx.x == 0 && bulk) bulk_store_wait_read();
+    } else {
+        m = chunk_line_ends(raw, chunk, n);
+    }
     uint32_t c = (uint32_t)__popcll(m);
     uint32_t last = m ? (uint32_t)(chunk + 63 - __clzll((long long)m)) + 1u : 0u;   // position + 1; 0: none
 #pragma unroll
