@@ -1184,18 +1184,19 @@ __global__ void __launch_bounds__(TP_THREADS) rows_kernel(const uint8_t *__restr
 
 __global__ void key_order_kernel(const uint8_t *__restrict__ arena, RowBuffers rb, uint32_t n_rows, BracketBuffers bb, ParseResult *res) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    // (text that rows_kernel has just found invalid leaves rows that refer to nothing -- with whatever an earlier, larger
-    //  document left in the recycled buffers as bracket numbers and offsets: found by tools/stress_lines.py, seed 1147)
-    __shared__ uint32_t s_invalid;   // (asked once per block: a million threads asking for the same word queue up at one L2 line)
-    if (threadIdx.x == 0) s_invalid = res->invalid;
-    __syncthreads();
-    if (r >= n_rows || s_invalid) return;
+    if (r >= n_rows) return;
+    // Text that rows_kernel has just found invalid leaves rows that refer to nothing -- with whatever an earlier, larger
+    // document left in the recycled buffers as bracket numbers and offsets (tools/stress_lines.py, seed 1147): nothing
+    // is followed from a row before the verdict so far has been looked at.  (Asked for here, looked at after the row's
+    // own word has been asked for too: the two loads travel together.)
+    const uint32_t invalid = __ldg(&res->invalid);
+    uint32_t meta = rb.meta[r];
+    if (invalid) return;
     if (r == 0 && res->module_row != 0 && res->module_kind == ROW_OPEN_OBJ) {
         // for the module index, which runs next: the row that closes "module" (voff of an opening row is its bracket)
         const uint32_t cb = bb.match[rb.voff[res->module_row - 1]];
         res->module_end = cb != 0xffffffffu ? bb.row[cb] : 0u;
     }
-    uint32_t meta = rb.meta[r];
     const uint32_t kind = meta & 15u;
     if (kind == ROW_CLOSE_OBJ || kind == ROW_CLOSE_ARR) {
         // nothing to compare; leave the opener's row in koff for the sibling lookup below
